@@ -1,0 +1,198 @@
+"""ctypes face of oracle/ggml_ref.c + GGUF loading through gguf-py.  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module; the product package (localai_b200) never does.
+
+The GGUF container is parsed with gguf-py (llama.cpp's own Python package, gguf.GGUFReader), so the
+oracle's view of a file is independent of the product's C++ parser (localai_b200/csrc/gguf.cc).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "_build", "libggml_ref.so")
+
+T_F32, T_F16, T_Q8_0, T_Q4_K, T_Q5_K, T_Q6_K, T_Q8_K = 0, 1, 8, 12, 13, 14, 15
+(TK_TOK_EMBD, TK_OUTPUT_NORM, TK_OUTPUT, TK_ATTN_NORM, TK_WQ, TK_WK, TK_WV, TK_WO, TK_FFN_NORM, TK_GATE, TK_UP,
+ TK_DOWN) = range(12)
+
+_LAYER_TENSORS = {
+    "attn_norm": TK_ATTN_NORM, "attn_q": TK_WQ, "attn_k": TK_WK, "attn_v": TK_WV, "attn_output": TK_WO,
+    "ffn_norm": TK_FFN_NORM, "ffn_gate": TK_GATE, "ffn_up": TK_UP, "ffn_down": TK_DOWN,
+}
+_GLOBAL_TENSORS = {"token_embd": TK_TOK_EMBD, "output_norm": TK_OUTPUT_NORM, "output": TK_OUTPUT}
+
+
+def build(force: bool = False) -> str:
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(
+            os.path.join(_HERE, "ggml_ref.c")):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB_PATH)
+        vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
+        L.ref_row_bytes.restype = i64
+        L.ref_row_bytes.argtypes = [i32, i64]
+        L.ref_dequantize_row.argtypes = [i32, vp, vp, i64]
+        L.ref_quantize_row_q8_0.argtypes = [vp, vp, i64]
+        L.ref_quantize_row_q8_K.argtypes = [vp, vp, i64]
+        L.ref_vec_dot_type.restype = i32
+        L.ref_vec_dot_type.argtypes = [i32]
+        L.ref_quantize_activations.argtypes = [i32, vp, vp, i64]
+        L.ref_vec_dot.restype = f32
+        L.ref_vec_dot.argtypes = [i32, i32, vp, vp]
+        L.ref_mul_mat.argtypes = [i32, vp, i64, i64, vp, i32, vp]
+        L.ref_rope_cache.argtypes = [f32, f32, f32, i32, vp]
+        L.ref_ctx_new.restype = vp
+        L.ref_ctx_new.argtypes = [i32] * 7 + [f32] * 3
+        L.ref_ctx_free.argtypes = [vp]
+        L.ref_ctx_set_tensor.argtypes = [vp, i32, i32, vp, i32, i64, i64]
+        L.ref_ctx_set_debug.argtypes = [vp, vp]
+        L.ref_eval.restype = i32
+        L.ref_eval.argtypes = [vp, vp, i32, i32, vp, i32, vp]
+        L.ref_argmax.restype = i32
+        L.ref_argmax.argtypes = [vp, i32]
+        L.ref_generate_greedy.restype = i32
+        L.ref_generate_greedy.argtypes = [vp, vp, i32, i32, vp, vp, vp]
+        L.ref_num_threads.restype = i32
+        _lib = L
+    return _lib
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+# ----------------------------------------------------------------------------- block-level helpers
+def dequantize(gtype: int, raw: np.ndarray, n_elems: int) -> np.ndarray:
+    raw = np.ascontiguousarray(raw).view(np.uint8).reshape(-1)
+    out = np.empty(n_elems, dtype=np.float32)
+    lib().ref_dequantize_row(gtype, _ptr(raw), _ptr(out), n_elems)
+    return out
+
+
+def quantize_q8_0(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+    out = np.empty(x.size // 32 * 34, dtype=np.uint8)
+    lib().ref_quantize_row_q8_0(_ptr(x), _ptr(out), x.size)
+    return out
+
+
+def quantize_q8_K(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+    out = np.empty(x.size // 256 * 292, dtype=np.uint8)
+    lib().ref_quantize_row_q8_K(_ptr(x), _ptr(out), x.size)
+    return out
+
+
+def mul_mat(gtype: int, w_raw: np.ndarray, rows: int, cols: int, x: np.ndarray) -> np.ndarray:
+    """out[t, r] = dot(W[r], quantise(x[t])) with the reference's activation quantisation."""
+    w_raw = np.ascontiguousarray(w_raw).view(np.uint8).reshape(-1)
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, cols)
+    out = np.empty((x.shape[0], rows), dtype=np.float32)
+    lib().ref_mul_mat(gtype, _ptr(w_raw), rows, cols, _ptr(x), x.shape[0], _ptr(out))
+    return out
+
+
+def rope_cache(pos: int, freq_scale: float, freq_base: float, n_dims: int) -> np.ndarray:
+    out = np.empty(n_dims, dtype=np.float32)
+    lib().ref_rope_cache(float(pos), freq_scale, freq_base, n_dims, _ptr(out))
+    return out
+
+
+# ----------------------------------------------------------------------------- model
+class OracleModel:
+    """llama-arch GGUF evaluated by the C restatement (grpc-server.cpp:1910 llama_decode call site)."""
+
+    def __init__(self, path: str, n_ctx: int = 512):
+        import gguf  # llama.cpp's own reader
+
+        self.reader = gguf.GGUFReader(path)  # keeps the mmap alive
+        f = self.reader.fields
+
+        def scalar(key, default=None):
+            if key not in f:
+                return default
+            fld = f[key]
+            return fld.parts[fld.data[0]][0]
+
+        self.n_layer = int(scalar("llama.block_count"))
+        self.n_embd = int(scalar("llama.embedding_length"))
+        self.n_head = int(scalar("llama.attention.head_count"))
+        self.n_head_kv = int(scalar("llama.attention.head_count_kv", self.n_head))
+        self.n_ff = int(scalar("llama.feed_forward_length"))
+        self.rms_eps = float(scalar("llama.attention.layer_norm_rms_epsilon", 1e-5))
+        self.rope_theta = float(scalar("llama.rope.freq_base", 10000.0))
+        self.n_ctx = n_ctx
+        self.tensors = {t.name: t for t in self.reader.tensors}
+        self.n_vocab = int(self.tensors["token_embd.weight"].shape[1])
+        L = lib()
+        self.ctx = L.ref_ctx_new(self.n_layer, self.n_embd, self.n_head, self.n_head_kv, self.n_ff, self.n_vocab, n_ctx,
+                                 self.rms_eps, self.rope_theta, 1.0)
+        self._keep = []
+        for name, t in self.tensors.items():
+            base = name.rsplit(".weight", 1)[0]
+            data = np.ascontiguousarray(t.data).view(np.uint8).reshape(-1)
+            self._keep.append(data)
+            cols = int(t.shape[0])
+            rows = int(t.shape[1]) if len(t.shape) > 1 else 1
+            if base in _GLOBAL_TENSORS:
+                L.ref_ctx_set_tensor(self.ctx, _GLOBAL_TENSORS[base], 0, _ptr(data), int(t.tensor_type), rows, cols)
+            elif base.startswith("blk."):
+                _, il, nm = base.split(".", 2)
+                if nm in _LAYER_TENSORS:
+                    L.ref_ctx_set_tensor(self.ctx, _LAYER_TENSORS[nm], int(il), _ptr(data), int(t.tensor_type), rows,
+                                         cols)
+        self._dbg = None
+
+    def close(self):
+        if self.ctx:
+            lib().ref_ctx_free(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def enable_debug(self) -> np.ndarray:
+        self._dbg = np.zeros((self.n_layer + 1, self.n_embd), dtype=np.float32)
+        lib().ref_ctx_set_debug(self.ctx, _ptr(self._dbg))
+        return self._dbg
+
+    def eval(self, tokens, n_past: int = 0, logits_all: bool = False, want_embd: bool = False):
+        toks = np.ascontiguousarray(tokens, dtype=np.int32)
+        n = toks.size
+        logits = np.empty((n if logits_all else 1, self.n_vocab), dtype=np.float32)
+        embd = np.empty(self.n_embd, dtype=np.float32) if want_embd else None
+        rc = lib().ref_eval(self.ctx, _ptr(toks), n, n_past, _ptr(logits), int(logits_all),
+                            _ptr(embd) if want_embd else None)
+        if rc != 0:
+            raise RuntimeError("context exhausted")
+        return (logits, embd) if want_embd else logits
+
+    def generate_greedy(self, prompt, n_gen: int):
+        toks = np.ascontiguousarray(prompt, dtype=np.int32)
+        out = np.zeros(n_gen, dtype=np.int32)
+        last = np.empty(self.n_vocab, dtype=np.float32)
+        margins = np.zeros(n_gen, dtype=np.float32)
+        n = lib().ref_generate_greedy(self.ctx, _ptr(toks), toks.size, n_gen, _ptr(out), _ptr(last), _ptr(margins))
+        return out[:n], last, margins[:n]
+
+
+def num_threads() -> int:
+    return lib().ref_num_threads()

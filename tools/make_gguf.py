@@ -1,0 +1,409 @@
+#!/usr/bin/env python3
+"""Synthetic random-init GGUF writer (SURVEY.md §8d "Synthetic inputs").
+
+Writes llama-architecture GGUF v3 files whose quantised tensors are generated
+*directly as blocks* (gguf-py cannot quantise K-quants): random nibbles/bits,
+6-bit sub-block scales, small finite fp16 super-block scales chosen so that the
+dequantised weights have std ~= gain / sqrt(fan_in).  The type mix of the
+``q4_k_m`` preset follows llama.cpp's published Q4_K_M rule (Q4_K default,
+Q6_K for output.weight and for attn_v / ffn_down on "use_more_bits" layers,
+Q5_K for the remaining attn_v on 70B-class models).
+
+The file is streamed tensor by tensor, so an 8B (4.9 GB) or 70B (42.5 GB) file
+never has to fit in RAM.  Everything is deterministic in ``--seed``.
+
+Stand-alone on purpose: numpy only (runs on the GPU box, where /root/reference
+does not exist).  Tests cross-check the output with gguf-py's GGUFReader.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import struct
+import sys
+from dataclasses import dataclass, field
+
+import numpy as np
+
+GGUF_MAGIC = 0x46554747
+GGUF_VERSION = 3
+ALIGN = 32
+
+# ggml type ids
+F32, F16, Q8_0, Q4_K, Q5_K, Q6_K = 0, 1, 8, 12, 13, 14
+TYPE_NAMES = {F32: "F32", F16: "F16", Q8_0: "Q8_0", Q4_K: "Q4_K", Q5_K: "Q5_K", Q6_K: "Q6_K"}
+BLOCK = {F32: (1, 4), F16: (1, 2), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210)}
+
+# gguf metadata value types
+T_U8, T_I8, T_U16, T_I16, T_U32, T_I32, T_F32, T_BOOL, T_STR, T_ARR, T_U64, T_I64, T_F64 = range(13)
+
+
+# --------------------------------------------------------------------------- model presets
+@dataclass
+class Arch:
+    name: str
+    n_layer: int
+    n_embd: int
+    n_head: int
+    n_head_kv: int
+    n_ff: int
+    n_vocab: int
+    n_ctx_train: int = 2048
+    rope_theta: float = 10000.0
+    rms_eps: float = 1e-5
+    tokenizer: str = "spm"  # "spm" | "bpe"
+    is_70b: bool = False
+    head_dim: int = field(init=False)
+
+    def __post_init__(self):
+        self.head_dim = self.n_embd // self.n_head
+
+
+ARCHS = {
+    # unit-test sized models: every quant type has K % 256 == 0
+    "micro": Arch("micro", 2, 256, 4, 2, 512, 512, 512, 10000.0, 1e-5, "spm"),
+    "mini": Arch("mini", 3, 512, 8, 2, 1024, 2048, 1024, 500000.0, 1e-5, "bpe"),
+    # BASELINE.json configs
+    "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 5632, 32000, 2048, 10000.0, 1e-5, "spm"),
+    "llama3-8b": Arch("llama3-8b", 32, 4096, 32, 8, 14336, 128256, 8192, 500000.0, 1e-5, "bpe"),
+    "llama3-70b": Arch("llama3-70b", 80, 8192, 64, 8, 28672, 128256, 8192, 500000.0, 1e-5, "bpe", True),
+}
+
+
+def use_more_bits(i: int, n: int) -> bool:
+    return i < n // 8 or i >= 7 * n // 8 or (i - n // 8) % 3 == 2
+
+
+def tensor_type(preset: str, arch: Arch, name: str, layer: int) -> int:
+    if name.endswith("_norm.weight"):
+        return F32
+    if preset == "f32":
+        return F32
+    if preset == "f16":
+        return F16
+    if preset == "q8_0":
+        return Q8_0
+    if preset in ("q4_k", "q5_k", "q6_k"):
+        return {"q4_k": Q4_K, "q5_k": Q5_K, "q6_k": Q6_K}[preset]
+    if preset == "q4_k_m":
+        if name == "output.weight":
+            return Q6_K
+        if name.endswith("attn_v.weight"):
+            if use_more_bits(layer, arch.n_layer):
+                return Q6_K
+            return Q5_K if arch.is_70b else Q4_K
+        if name.endswith("ffn_down.weight"):
+            return Q6_K if use_more_bits(layer, arch.n_layer) else Q4_K
+        return Q4_K
+    if preset == "mixed":  # exercise every kernel inside one small model
+        order = [Q4_K, Q6_K, Q5_K, Q8_0, F16]
+        if name == "output.weight":
+            return Q6_K
+        if name == "token_embd.weight":
+            return Q4_K
+        return order[(hash_name(name) + layer) % len(order)]
+    raise ValueError(f"unknown preset {preset}")
+
+
+def hash_name(s: str) -> int:
+    h = 0
+    for c in s.encode():
+        h = (h * 131 + c) & 0xFFFFFFFF
+    return h
+
+
+# --------------------------------------------------------------------------- random blocks
+def _f16_bytes(x: np.ndarray) -> np.ndarray:
+    return x.astype(np.float16).view(np.uint8).reshape(x.shape[0], 2)
+
+
+def _pack_k_scales(sc: np.ndarray, mn: np.ndarray) -> np.ndarray:
+    """Pack 8 six-bit scales + 8 six-bit mins into the 12-byte K-quant layout."""
+    sc = sc.astype(np.uint8)
+    mn = mn.astype(np.uint8)
+    out = np.empty((sc.shape[0], 12), dtype=np.uint8)
+    out[:, 0:4] = (sc[:, 0:4] & 63) | ((sc[:, 4:8] >> 4) << 6)
+    out[:, 4:8] = (mn[:, 0:4] & 63) | ((mn[:, 4:8] >> 4) << 6)
+    out[:, 8:12] = (sc[:, 4:8] & 0x0F) | ((mn[:, 4:8] & 0x0F) << 4)
+    return out
+
+
+def random_blocks(rng: np.random.Generator, gtype: int, n_blocks: int, sigma: float) -> np.ndarray:
+    """Return uint8 [n_blocks, block_bytes] of random blocks with dequantised std ~ sigma."""
+    jitter = rng.uniform(0.8, 1.25, size=n_blocks).astype(np.float32)
+    if gtype == Q8_0:
+        qs = rng.integers(-127, 128, size=(n_blocks, 32), dtype=np.int8)
+        d = (sigma / 73.3) * jitter
+        return np.concatenate([_f16_bytes(d), qs.view(np.uint8)], axis=1)
+    if gtype in (Q4_K, Q5_K):
+        qmean = 7.5 if gtype == Q4_K else 15.5
+        qstd = 4.61 if gtype == Q4_K else 9.23
+        sc = rng.integers(24, 64, size=(n_blocks, 8))
+        mn = np.clip(sc + rng.integers(-3, 4, size=(n_blocks, 8)), 0, 63)
+        d = (sigma / (44.0 * qstd)) * jitter
+        dmin = d * qmean
+        scales = _pack_k_scales(sc, mn)
+        qs = rng.integers(0, 256, size=(n_blocks, 128), dtype=np.uint8)
+        if gtype == Q4_K:
+            return np.concatenate([_f16_bytes(d), _f16_bytes(dmin), scales, qs], axis=1)
+        qh = rng.integers(0, 256, size=(n_blocks, 32), dtype=np.uint8)
+        return np.concatenate([_f16_bytes(d), _f16_bytes(dmin), scales, qh, qs], axis=1)
+    if gtype == Q6_K:
+        ql = rng.integers(0, 256, size=(n_blocks, 128), dtype=np.uint8)
+        qh = rng.integers(0, 256, size=(n_blocks, 64), dtype=np.uint8)
+        sc = rng.integers(32, 128, size=(n_blocks, 16)).astype(np.int8)
+        flip = rng.random(size=(n_blocks, 16)) < 0.1
+        sc = np.where(flip, -sc, sc).astype(np.int8)
+        d = (sigma / (80.0 * 18.47)) * jitter
+        return np.concatenate([ql, qh, sc.view(np.uint8), _f16_bytes(d)], axis=1)
+    raise ValueError(gtype)
+
+
+def random_tensor_bytes(rng, gtype: int, rows: int, cols: int, sigma: float, chunk_rows: int = 4096):
+    """Yield the tensor's bytes in row chunks (rows x cols logical, cols innermost)."""
+    if gtype == F32:
+        for r0 in range(0, rows, chunk_rows):
+            r = min(chunk_rows, rows - r0)
+            yield (rng.standard_normal((r, cols), dtype=np.float32) * sigma).tobytes()
+        return
+    if gtype == F16:
+        for r0 in range(0, rows, chunk_rows):
+            r = min(chunk_rows, rows - r0)
+            yield (rng.standard_normal((r, cols), dtype=np.float32) * sigma).astype(np.float16).tobytes()
+        return
+    bs, _ = BLOCK[gtype]
+    assert cols % bs == 0, f"cols {cols} not a multiple of block {bs}"
+    bpr = cols // bs
+    for r0 in range(0, rows, chunk_rows):
+        r = min(chunk_rows, rows - r0)
+        yield random_blocks(rng, gtype, r * bpr, sigma).tobytes()
+
+
+# --------------------------------------------------------------------------- vocab
+def load_vocab(kind: str, n_vocab: int, vocab_dir: str):
+    """Return dict(tokens, scores, types, merges, bos, eos, model, pre) padded to n_vocab.
+
+    The trained base vocabularies live in tests/golden/vocab_{spm,bpe}.json (made by
+    tools/train_vocab.py); if absent a purely synthetic byte-level vocabulary is used.
+    """
+    path = os.path.join(vocab_dir, f"vocab_{kind}.json")
+    if os.path.exists(path):
+        with open(path, encoding="utf-8") as f:
+            v = json.load(f)
+    else:
+        v = _fallback_vocab(kind)
+    tokens, scores, types = list(v["tokens"]), list(v["scores"]), list(v["types"])
+    if len(tokens) > n_vocab:
+        raise ValueError(f"base vocab {len(tokens)} > n_vocab {n_vocab}")
+    i = len(tokens)
+    while len(tokens) < n_vocab:
+        tokens.append(f"<|pad_{i}|>")
+        scores.append(-1e9 if kind == "spm" else 0.0)
+        types.append(5)  # UNUSED
+        i += 1
+    v = dict(v)
+    v.update(tokens=tokens, scores=scores, types=types)
+    return v
+
+
+def _bytes_to_unicode():
+    bs = list(range(ord("!"), ord("~") + 1)) + list(range(0xA1, 0xAC + 1)) + list(range(0xAE, 0xFF + 1))
+    cs = bs[:]
+    n = 0
+    for b in range(256):
+        if b not in bs:
+            bs.append(b)
+            cs.append(256 + n)
+            n += 1
+    return {b: chr(c) for b, c in zip(bs, cs)}
+
+
+def _fallback_vocab(kind: str):
+    if kind == "spm":
+        tokens = ["<unk>", "<s>", "</s>"] + [f"<0x{b:02X}>" for b in range(256)]
+        types = [2, 3, 3] + [6] * 256
+        scores = [0.0] * len(tokens)
+        for i, p in enumerate(["▁", "e", "t", "a", "o", "▁t", "he", "▁the", "in", "▁a"]):
+            tokens.append(p)
+            types.append(1)
+            scores.append(-float(i + 1))
+        return dict(model="llama", pre="default", tokens=tokens, scores=scores, types=types, merges=[],
+                    bos=1, eos=2, unk=0, add_bos=True)
+    b2u = _bytes_to_unicode()
+    tokens = [b2u[b] for b in range(256)]
+    merges = ["Ġ t", "h e", "Ġt he", "i n", "Ġ a"]
+    for m in merges:
+        tokens.append(m.replace(" ", ""))
+    types = [1] * len(tokens)
+    tokens += ["<|begin_of_text|>", "<|end_of_text|>", "<|eot_id|>"]
+    types += [3, 3, 3]
+    return dict(model="gpt2", pre="llama-bpe", tokens=tokens, scores=[0.0] * len(tokens), types=types,
+                merges=merges, bos=len(tokens) - 3, eos=len(tokens) - 2, unk=-1, add_bos=True)
+
+
+# --------------------------------------------------------------------------- gguf writer
+def _s(b: bytes) -> bytes:
+    return struct.pack("<Q", len(b)) + b
+
+
+def kv_bytes(key: str, vtype: int, val) -> bytes:
+    out = _s(key.encode()) + struct.pack("<I", vtype)
+    return out + _val_bytes(vtype, val)
+
+
+def _val_bytes(vtype: int, val) -> bytes:
+    if vtype == T_U32:
+        return struct.pack("<I", val)
+    if vtype == T_I32:
+        return struct.pack("<i", val)
+    if vtype == T_F32:
+        return struct.pack("<f", val)
+    if vtype == T_BOOL:
+        return struct.pack("<B", 1 if val else 0)
+    if vtype == T_STR:
+        return _s(val.encode("utf-8"))
+    if vtype == T_U64:
+        return struct.pack("<Q", val)
+    if vtype == T_ARR:
+        etype, items = val
+        out = struct.pack("<IQ", etype, len(items))
+        if etype == T_STR:
+            return out + b"".join(_s(x.encode("utf-8")) for x in items)
+        if etype == T_F32:
+            return out + np.asarray(items, dtype="<f4").tobytes()
+        if etype == T_I32:
+            return out + np.asarray(items, dtype="<i4").tobytes()
+        raise ValueError(etype)
+    raise ValueError(vtype)
+
+
+def tensor_plan(arch: Arch, preset: str, gain_out: float):
+    """[(name, rows, cols, ggml_type, sigma, is_norm)] in file order."""
+    d, ff, hd = arch.n_embd, arch.n_ff, arch.head_dim
+    kvd = arch.n_head_kv * hd
+    plan = [("token_embd.weight", arch.n_vocab, d, tensor_type(preset, arch, "token_embd.weight", 0), 1.0, False)]
+    for i in range(arch.n_layer):
+        p = f"blk.{i}."
+        for nm, rows, cols in [
+            ("attn_norm.weight", 1, d), ("attn_q.weight", d, d), ("attn_k.weight", kvd, d),
+            ("attn_v.weight", kvd, d), ("attn_output.weight", d, d), ("ffn_norm.weight", 1, d),
+            ("ffn_gate.weight", ff, d), ("ffn_up.weight", ff, d), ("ffn_down.weight", d, ff),
+        ]:
+            t = tensor_type(preset, arch, p + nm, i)
+            norm = nm.endswith("_norm.weight")
+            plan.append((p + nm, rows, cols, t, 0.0 if norm else 1.0 / np.sqrt(cols), norm))
+    plan.append(("output_norm.weight", 1, d, F32, 0.0, True))
+    plan.append(("output.weight", arch.n_vocab, d, tensor_type(preset, arch, "output.weight", 0),
+                 gain_out / np.sqrt(d), False))
+    return plan
+
+
+def tensor_nbytes(rows, cols, t):
+    bs, bb = BLOCK[t]
+    return rows * (cols // bs) * bb
+
+
+def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: float = 4.0,
+               vocab_dir: str | None = None, n_ctx_train: int | None = None, quiet: bool = False) -> dict:
+    vocab_dir = vocab_dir or os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+    vocab = load_vocab(arch.tokenizer, arch.n_vocab, vocab_dir)
+    plan = tensor_plan(arch, preset, gain_out)
+
+    ftype = {"f32": 0, "f16": 1, "q8_0": 7, "q4_k_m": 15, "q4_k": 14, "q5_k": 16, "q6_k": 18, "mixed": 15}[preset]
+    kvs = [
+        kv_bytes("general.architecture", T_STR, "llama"),
+        kv_bytes("general.name", T_STR, f"{arch.name}-{preset}-random-seed{seed}"),
+        kv_bytes("general.file_type", T_U32, ftype),
+        kv_bytes("general.quantization_version", T_U32, 2),
+        kv_bytes("general.alignment", T_U32, ALIGN),
+        kv_bytes("llama.context_length", T_U32, n_ctx_train or arch.n_ctx_train),
+        kv_bytes("llama.embedding_length", T_U32, arch.n_embd),
+        kv_bytes("llama.block_count", T_U32, arch.n_layer),
+        kv_bytes("llama.feed_forward_length", T_U32, arch.n_ff),
+        kv_bytes("llama.attention.head_count", T_U32, arch.n_head),
+        kv_bytes("llama.attention.head_count_kv", T_U32, arch.n_head_kv),
+        kv_bytes("llama.attention.layer_norm_rms_epsilon", T_F32, arch.rms_eps),
+        kv_bytes("llama.rope.freq_base", T_F32, arch.rope_theta),
+        kv_bytes("llama.rope.dimension_count", T_U32, arch.head_dim),
+        kv_bytes("llama.vocab_size", T_U32, arch.n_vocab),
+        kv_bytes("tokenizer.ggml.model", T_STR, vocab["model"]),
+        kv_bytes("tokenizer.ggml.pre", T_STR, vocab["pre"]),
+        kv_bytes("tokenizer.ggml.tokens", T_ARR, (T_STR, vocab["tokens"])),
+        kv_bytes("tokenizer.ggml.scores", T_ARR, (T_F32, vocab["scores"])),
+        kv_bytes("tokenizer.ggml.token_type", T_ARR, (T_I32, vocab["types"])),
+        kv_bytes("tokenizer.ggml.bos_token_id", T_U32, vocab["bos"]),
+        kv_bytes("tokenizer.ggml.eos_token_id", T_U32, vocab["eos"]),
+        kv_bytes("tokenizer.ggml.add_bos_token", T_BOOL, bool(vocab.get("add_bos", True))),
+        kv_bytes("tokenizer.ggml.add_eos_token", T_BOOL, False),
+    ]
+    if vocab.get("unk", -1) >= 0:
+        kvs.append(kv_bytes("tokenizer.ggml.unknown_token_id", T_U32, vocab["unk"]))
+    if vocab["merges"]:
+        kvs.append(kv_bytes("tokenizer.ggml.merges", T_ARR, (T_STR, vocab["merges"])))
+    if vocab.get("eot", -1) >= 0:
+        kvs.append(kv_bytes("tokenizer.ggml.eot_token_id", T_U32, vocab["eot"]))
+
+    infos = []
+    off = 0
+    for name, rows, cols, t, _, _ in plan:
+        dims = [cols] if rows == 1 and name.endswith("_norm.weight") else [cols, rows]
+        infos.append(_s(name.encode()) + struct.pack("<I", len(dims)) + b"".join(struct.pack("<Q", x) for x in dims)
+                     + struct.pack("<IQ", t, off))
+        nb = tensor_nbytes(rows, cols, t)
+        off += (nb + ALIGN - 1) // ALIGN * ALIGN
+
+    header = struct.pack("<IIQQ", GGUF_MAGIC, GGUF_VERSION, len(plan), len(kvs))
+    meta = header + b"".join(kvs) + b"".join(infos)
+    pad = (-len(meta)) % ALIGN
+    total = 0
+    type_bytes: dict[str, int] = {}
+    with open(path, "wb") as f:
+        f.write(meta + b"\0" * pad)
+        total += len(meta) + pad
+        for idx, (name, rows, cols, t, sigma, is_norm) in enumerate(plan):
+            rng = np.random.default_rng([seed, idx])
+            n = 0
+            if is_norm:
+                w = (1.0 + 0.1 * rng.standard_normal(cols)).astype(np.float32)
+                f.write(w.tobytes())
+                n = w.nbytes
+            else:
+                for chunk in random_tensor_bytes(rng, t, rows, cols, sigma):
+                    f.write(chunk)
+                    n += len(chunk)
+            assert n == tensor_nbytes(rows, cols, t), (name, n)
+            p = (-n) % ALIGN
+            f.write(b"\0" * p)
+            total += n + p
+            type_bytes[TYPE_NAMES[t]] = type_bytes.get(TYPE_NAMES[t], 0) + n
+    # bytes streamed per decoded token = every weight except the embedding table
+    # (one row gathered) -- SURVEY.md §8(d)
+    stream = sum(tensor_nbytes(r, c, t) for (nm, r, c, t, _, _) in plan if nm != "token_embd.weight")
+    info = dict(path=path, arch=arch.name, preset=preset, seed=seed, file_bytes=total, n_tensors=len(plan),
+                type_bytes=type_bytes, decode_stream_bytes=stream)
+    if not quiet:
+        print(json.dumps(info))
+    return info
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("--arch", required=True, choices=sorted(ARCHS))
+    ap.add_argument("--preset", required=True,
+                    choices=["f32", "f16", "q8_0", "q4_k_m", "q4_k", "q5_k", "q6_k", "mixed"])
+    ap.add_argument("--out", required=True)
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--gain-out", type=float, default=4.0, help="output.weight std multiplier (argmax margin)")
+    ap.add_argument("--n-layer", type=int, default=None, help="override layer count (debug)")
+    args = ap.parse_args(argv)
+    arch = ARCHS[args.arch]
+    if args.n_layer:
+        arch = Arch(**{**{k: getattr(arch, k) for k in
+                          ["name", "n_layer", "n_embd", "n_head", "n_head_kv", "n_ff", "n_vocab", "n_ctx_train",
+                           "rope_theta", "rms_eps", "tokenizer", "is_70b"]}, "n_layer": args.n_layer})
+    write_gguf(args.out, arch, args.preset, args.seed, args.gain_out)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
