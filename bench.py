@@ -1,0 +1,322 @@
+#!/usr/bin/env python3
+"""bench.py -- BASELINE.json's metric on BASELINE.json's config, one JSON line on stdout.
+
+Workload (config.workload): configs[1] = Llama-3-8B-arch GGUF Q4_K_M, random-init, batch-1 greedy decode
+(the north-star number) at a short context; the same run also reports batch-64 decode and the 2048-token
+prefill as `extra`.  A "step" is one decode step (one token for every active sequence).
+
+  value     decode tok/s with everything resident in HBM (b2_bench_decode: CUDA events on the engine's stream)
+  e2e       the same metric through the request path a LocalAI backend uses (b2_submit / b2_poll, i.e.
+            PredictStream): host prompt ids in, token text out, per-step H2D/D2H inside the timed region;
+            tok/s = n_decoded / t_generation as the reference defines it (grpc-server.cpp:305-318)
+  roofline  the dominant kernel (streaming dequant-GEMV on the Q4_K ffn_gate matrices) timed alone with CUDA
+            events; achieved = rows x row_bytes / time against MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline  the oracle (C restatement of the llama.cpp CPU path, OpenMP) on a bounded sample, same GGUF
+
+N > 1 (torchrun): independent per-GPU replicas, no data-path collective ("replicas only");
+value = tokens of all ranks / max-over-ranks time.
+
+--impl reference times the CPU implementation alone (the reference's llama.cpp is not buildable here, so it is
+the oracle port), rank 0 only.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+METRIC = "Llama-3-8B Q4_K_M decode tok/s (b=1)"
+UNIT = "tok/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], 0.0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def ensure_model(arch: str, preset: str, seed: int, rank: int, barrier) -> tuple[str, dict]:
+    import make_gguf as mg
+
+    d = os.environ.get("B200LLM_BENCH_DIR", "/dev/shm/b200llm_bench" if os.path.isdir("/dev/shm") else "/tmp/b200llm_bench")
+    os.makedirs(d, exist_ok=True)
+    path = os.path.join(d, f"{arch}-{preset}-seed{seed}.gguf")
+    meta = path + ".json"
+    if rank == 0 and not (os.path.exists(path) and os.path.exists(meta)):
+        t0 = time.time()
+        info = mg.write_gguf(path + ".tmp", mg.ARCHS[arch], preset, seed=seed, quiet=True)
+        os.replace(path + ".tmp", path)
+        with open(meta, "w") as f:
+            json.dump(info, f)
+        log(f"[bench] wrote {path} ({info['file_bytes'] / 1e9:.2f} GB) in {time.time() - t0:.1f}s")
+    barrier()
+    with open(meta) as f:
+        return path, json.load(f)
+
+
+def cpu_sample(path: str, n_prompt: int, n_decode: int):
+    """Oracle port timed on the host cores: (decode tok/s, prompt tok/s, threads)."""
+    import numpy as np
+
+    from oracle import oracle as O
+
+    m = O.OracleModel(path, n_ctx=n_prompt + n_decode + 8)
+    prompt = (np.arange(n_prompt) * 7919 % 4000 + 3).astype(np.int32)
+    t0 = time.time()
+    lg = m.eval(prompt)
+    t1 = time.time()
+    tok = int(lg[0].argmax())
+    for i in range(n_decode):
+        lg = m.eval([tok], n_past=n_prompt + i)
+        tok = int(lg[0].argmax())
+    t2 = time.time()
+    return n_decode / (t2 - t1), n_prompt / (t1 - t0), O.num_threads()
+
+
+def run_reference(args, rank: int):
+    if rank != 0:
+        return
+    path, info = ensure_model(args.arch, args.preset, args.seed, 0, lambda: None)
+    import numpy as np
+
+    from oracle import oracle as O
+
+    n_prompt = 8
+    m = O.OracleModel(path, n_ctx=4096)
+    prompt = (np.arange(n_prompt) * 7919 % 4000 + 3).astype(np.int32)
+    lg = m.eval(prompt)
+    tok, pos = int(lg[0].argmax()), n_prompt
+    budget_s = float(os.environ.get("B200LLM_REF_BUDGET_S", "150"))
+    t_w = time.time()
+    for _ in range(max(1, min(args.warmup, 2))):
+        lg = m.eval([tok], n_past=pos)
+        tok, pos = int(lg[0].argmax()), pos + 1
+    per = (time.time() - t_w) / max(1, min(args.warmup, 2))
+    steps = max(1, min(args.steps, int(budget_s / max(per, 1e-3))))
+    t0 = time.time()
+    for _ in range(steps):
+        lg = m.eval([tok], n_past=pos)
+        tok, pos = int(lg[0].argmax()), pos + 1
+    dt = time.time() - t0
+    v = steps / dt
+    cores = O.num_threads()
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": max(1, min(args.warmup, 2)), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int8 x q4/q6 block dot, f32 accumulate", "data": "synthetic",
+        "config": {"workload": f"{args.arch} {args.preset} random-init GGUF, batch-1 greedy decode, ctx {n_prompt}+",
+                   "note": "CPU oracle port (reference llama.cpp is not buildable offline); steps bounded by a time budget"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{steps} greedy decode steps after an {n_prompt}-token prompt, OpenMP {cores} threads"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=256)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--arch", default="llama3-8b")
+    ap.add_argument("--preset", default="q4_k_m")
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--ctx", type=int, default=128, help="KV positions already in the cache for the decode legs")
+    ap.add_argument("--prefill", type=int, default=2048)
+    ap.add_argument("--batch", type=int, default=64, help="concurrent streams for the batched-decode extra")
+    ap.add_argument("--no-extras", action="store_true", help="skip the b=64 / prefill / cpu legs")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return 0
+
+    warmup = max(args.warmup, 3)
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_mod
+
+        torch.cuda.set_device(local_rank)
+        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_mod
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(x: float) -> float:
+        if dist is None:
+            return x
+        import torch
+
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    from localai_b200 import capi
+
+    if capi.device_count() < 1:
+        raise SystemExit("bench.py: no sm_100 device visible; there is no CPU fallback for the b200 arm")
+    path, info = ensure_model(args.arch, args.preset, args.seed, rank, barrier)
+    n_par = max(1, args.batch)
+    n_ctx_slot = max(args.prefill, args.ctx + args.steps + warmup) + 128
+    t0 = time.time()
+    eng = capi.Engine(path, n_ctx=n_ctx_slot * n_par, n_batch=512, n_parallel=n_par, device=local_rank)
+    log(f"[bench r{rank}] loaded in {time.time() - t0:.1f}s: {eng.info.name.decode()} weights {eng.info.weight_bytes_device / 1e9:.3f} GB")
+    stream_bytes = eng.info.decode_stream_bytes
+    kv_per_pos = eng.info.kv_bytes_per_pos
+    peak, peak_src = peaks()
+
+    # ---- value: device-resident batch-1 decode
+    barrier()
+    with ClockSampler(local_rank) as clk:
+        ms, launches = eng.bench_decode(1, args.ctx, args.steps, warmup)
+    ms = max_over_ranks(ms)
+    barrier()
+    value = world * 1e3 / ms
+    step_bytes = stream_bytes + kv_per_pos * args.ctx
+    clocks = clk.summary()
+
+    # ---- e2e: the PredictStream path (host ids in, text out)
+    import numpy as np
+
+    prompt = (np.arange(args.ctx) * 7919 % 4000 + 3).astype(np.int32)
+    rid = eng.submit(prompt_ids=prompt, n_predict=min(32, args.steps), temperature=0.0, ignore_eos=True, stream=True)
+    list(eng.events(rid))  # warm-up request
+    eng.release(rid)
+    barrier()
+    t0 = time.time()
+    rid = eng.submit(prompt_ids=prompt, n_predict=args.steps, temperature=0.0, ignore_eos=True, stream=True)
+    evs = list(eng.events(rid))
+    t_wall = time.time() - t0
+    eng.release(rid)
+    fin = evs[-1]
+    e2e_ms = max_over_ranks(fin["t_gen_ms"] / max(1, fin["n_decoded"] - 1))
+    e2e = {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": 48, "d2h_bytes_per_step": 4,
+           "prompt_ms": fin["t_prompt_ms"], "wall_s": t_wall, "n_decoded": fin["n_decoded"],
+           "path": "b2_submit/b2_poll (PredictStream), greedy, host prompt ids"}
+
+    # ---- roofline of the dominant kernel, timed alone
+    k_ms, k_bytes, k_type = eng.bench_gemv(4, 1, 8)
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": f"gemv_kernel<type {k_type}, NT=1> on ffn_gate [{eng.info.n_ff}x{eng.info.n_embd}]",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "bytes_per_launch": k_bytes, "us_per_launch": k_ms * 1e3, "peak_source": peak_src,
+                "step": {"bytes": step_bytes, "achieved_gbs": step_bytes / (ms * 1e-3) / 1e9,
+                         "frac_of_measured": step_bytes / (ms * 1e-3) / 1e9 / peak,
+                         "frac_of_8tbs": step_bytes / (ms * 1e-3) / 8e12}}
+
+    extra = {}
+    cpu = None
+    if not args.no_extras:
+        try:
+            bms, bl = eng.bench_decode(n_par, args.ctx, max(8, args.steps // 8), 3)
+            bms = max_over_ranks(bms)
+            extra["decode_b%d" % n_par] = {"tok_s": world * n_par * 1e3 / bms, "ms_per_step": bms, "launches_per_step": bl,
+                                           "hbm_frac_of_measured": (stream_bytes + n_par * kv_per_pos * args.ctx) / (bms * 1e-3) / 1e9 / peak}
+        except capi.B2Error as ex:
+            extra["decode_b%d" % n_par] = {"error": str(ex)}
+        try:
+            pms, pl = eng.bench_prefill(args.prefill, 2, 1)
+            pms = max_over_ranks(pms)
+            extra["prefill_%d" % args.prefill] = {"tok_s": world * args.prefill * 1e3 / pms, "ms": pms, "launches": pl}
+        except capi.B2Error as ex:
+            extra["prefill_%d" % args.prefill] = {"error": str(ex)}
+        if rank == 0 and world == 1:
+            try:
+                dv, pv, cores = cpu_sample(path, 8, 8)
+                cpu = {"value": dv, "unit": UNIT, "cores": cores, "kind": "port", "prompt_tok_s": pv,
+                       "sample": "oracle (C restatement of the llama.cpp CPU path, OpenMP): 8-token prompt + 8 greedy decode steps on the same GGUF"}
+            except Exception as ex:  # the checker failing must not void the GPU measurement
+                cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+    eng.close()
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int8 x q4/q6 block dot (dp4a), f32 accumulate", "data": "synthetic",
+            "config": {"workload": f"{args.arch} {args.preset} random-init GGUF, batch-1 greedy decode at ctx {args.ctx}",
+                       "replicas": world, "l2": "inputs larger than L2: every step streams %.2f GB of weights (L2 = 126 MB)" % (stream_bytes / 1e9),
+                       "decode_stream_bytes": stream_bytes, "kv_bytes_per_pos": kv_per_pos},
+            "e2e": e2e, "gpu_launches": int(launches) * args.steps, "gpu_launches_per_step": int(launches),
+            "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "extra": extra,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

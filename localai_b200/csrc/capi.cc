@@ -1,0 +1,291 @@
+// capi.cc -- extern "C" face of libb200llm.so (include/b200llm.h).
+#include <cuda_fp16.h>
+
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <vector>
+
+#include "engine.h"
+#include "kernels.h"
+#include "model.h"
+
+namespace b2 {
+static thread_local std::string g_err;
+void set_last_error(const std::string &m) { g_err = m; }
+} // namespace b2
+
+using namespace b2;
+
+#define B2_API_BEGIN try {
+#define B2_API_END(failret)                       \
+    }                                             \
+    catch (const b2::Error &e) {                  \
+        b2::set_last_error(e.what());             \
+        return (failret == 0 ? e.code : failret); \
+    }                                             \
+    catch (const std::exception &e) {             \
+        b2::set_last_error(e.what());             \
+        return (failret == 0 ? B2_EINVAL : failret); \
+    }
+
+// ------------------------------------------------------------------------------------------------ kernel test hooks
+namespace {
+struct DevBuf {
+    void *p = nullptr;
+    explicit DevBuf(size_t n) { B2_CUDA(cudaMalloc(&p, n ? n : 16)); }
+    ~DevBuf() { cudaFree(p); }
+    template <typename T> T *as() { return (T *)p; }
+};
+int sm100_device_count();
+void require_device() {
+    B2_CHECK(sm100_device_count() > 0, B2_ENODEV, "no sm_100 CUDA device (this library has no CPU fallback)");
+    B2_CUDA(cudaSetDevice(0));
+}
+DTensor upload_matrix(int type, const void *blocks, int64_t rows, int64_t cols, DevBuf &staging, DevBuf &dst) {
+    DTensor t;
+    t.type = type;
+    t.rows = rows;
+    t.cols = cols;
+    t.row_stride = device_row_stride(type, cols);
+    B2_CUDA(cudaMemcpy(staging.p, blocks, (size_t)(rows * gguf_row_bytes(type, cols)), cudaMemcpyHostToDevice));
+    launch_repack(type, staging.as<uint8_t>(), dst.as<uint8_t>(), rows, cols, 0);
+    t.data = dst.as<uint8_t>();
+    return t;
+}
+} // namespace
+
+extern "C" {
+
+int b2_abi_version(void) { return B2_ABI_VERSION; }
+const char *b2_last_error(void) { return b2::g_err.c_str(); }
+
+int b2_device_count(void) { return sm100_device_count(); }
+
+} // extern "C"
+namespace {
+int sm100_device_count() {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    int ok = 0;
+    for (int i = 0; i < n; i++) {
+        cudaDeviceProp p;
+        if (cudaGetDeviceProperties(&p, i) == cudaSuccess && p.major == 10) ok++;
+    }
+    return ok;
+}
+} // namespace
+extern "C" {
+
+b2_engine *b2_create(const b2_load_opts *opts) {
+    try {
+        B2_CHECK(opts && opts->model_path, B2_EINVAL, "b2_create: null options / model path");
+        b2_load_opts o;
+        memset(&o, 0, sizeof(o));
+        memcpy(&o, opts, std::min<size_t>(opts->struct_size ? opts->struct_size : sizeof(o), sizeof(o)));
+        return reinterpret_cast<b2_engine *>(new Engine(o));
+    } catch (const b2::Error &e) {
+        b2::set_last_error(e.what());
+    } catch (const std::exception &e) {
+        b2::set_last_error(e.what());
+    }
+    return nullptr;
+}
+
+void b2_destroy(b2_engine *e) { delete reinterpret_cast<Engine *>(e); }
+
+static Engine *E(b2_engine *e) {
+    B2_CHECK(e != nullptr, B2_EINVAL, "null engine handle");
+    return reinterpret_cast<Engine *>(e);
+}
+
+int b2_model_info(b2_engine *e, b2_model_info_t *out) {
+    B2_API_BEGIN
+    B2_CHECK(out, B2_EINVAL, "null out");
+    E(e)->model_info(out);
+    return 0;
+    B2_API_END(0)
+}
+
+int b2_tokenize(b2_engine *e, const char *text, size_t n, int add_bos, int parse_special, int32_t *out, int cap) {
+    B2_API_BEGIN
+    std::vector<int32_t> ids = E(e)->tokenize(std::string(text ? text : "", text ? n : 0), add_bos != 0, parse_special != 0);
+    if ((int)ids.size() > cap) return -(int)ids.size();
+    if (!ids.empty()) memcpy(out, ids.data(), ids.size() * 4);
+    return (int)ids.size();
+    B2_API_END(0)
+}
+
+int b2_token_to_piece(b2_engine *e, int32_t token, char *out, int cap) {
+    B2_API_BEGIN
+    const std::string p = E(e)->token_to_piece(token);
+    if ((int)p.size() > cap) return -(int)p.size();
+    memcpy(out, p.data(), p.size());
+    return (int)p.size();
+    B2_API_END(0)
+}
+
+int64_t b2_submit(b2_engine *e, const b2_request *req) {
+    B2_API_BEGIN
+    B2_CHECK(req, B2_EINVAL, "null request");
+    return E(e)->submit(*req);
+    B2_API_END(0)
+}
+
+int b2_poll(b2_engine *e, int64_t id, b2_event *ev, int timeout_ms) {
+    B2_API_BEGIN
+    B2_CHECK(ev, B2_EINVAL, "null event");
+    return E(e)->poll(id, ev, timeout_ms);
+    B2_API_END(0)
+}
+
+int b2_cancel(b2_engine *e, int64_t id) {
+    B2_API_BEGIN
+    return E(e)->cancel(id);
+    B2_API_END(0)
+}
+
+int b2_embed_result(b2_engine *e, int64_t id, float *out, int cap) {
+    B2_API_BEGIN
+    return E(e)->embed_result(id, out, cap);
+    B2_API_END(0)
+}
+
+int b2_release(b2_engine *e, int64_t id) {
+    B2_API_BEGIN
+    return E(e)->release(id);
+    B2_API_END(0)
+}
+
+int b2_metrics(b2_engine *e, b2_metrics_t *out) {
+    B2_API_BEGIN
+    B2_CHECK(out, B2_EINVAL, "null out");
+    E(e)->metrics(out);
+    return 0;
+    B2_API_END(0)
+}
+
+int b2_eval(b2_engine *e, int slot, const int32_t *tokens, int n, int n_past, float *logits, int logits_all, float *embd) {
+    B2_API_BEGIN
+    return E(e)->eval(slot, tokens, n, n_past, logits, logits_all != 0, embd);
+    B2_API_END(0)
+}
+
+int b2_decode_greedy(b2_engine *e, int slot, const int32_t *prompt, int n_prompt, int n_gen, int32_t *out, double *prefill_ms,
+                     double *decode_ms) {
+    B2_API_BEGIN
+    return E(e)->decode_greedy(slot, prompt, n_prompt, n_gen, out, prefill_ms, decode_ms);
+    B2_API_END(0)
+}
+
+int b2_debug_hidden(b2_engine *e, float *out, int cap_floats) {
+    B2_API_BEGIN
+    return E(e)->debug_hidden(out, cap_floats);
+    B2_API_END(0)
+}
+
+int b2_bench_decode(b2_engine *e, int batch, int ctx_len, int n_steps, int n_warmup, double *ms_per_step, int64_t *launches) {
+    B2_API_BEGIN
+    return E(e)->bench_decode(batch, ctx_len, n_steps, n_warmup, ms_per_step, launches);
+    B2_API_END(0)
+}
+
+int b2_bench_gemv(b2_engine *e, int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch,
+                  int *ggml_type) {
+    B2_API_BEGIN
+    return E(e)->bench_gemv(which, n_tok, n_rounds, ms_per_launch, bytes_per_launch, ggml_type);
+    B2_API_END(0)
+}
+
+int b2_bench_prefill(b2_engine *e, int n_tokens, int n_iters, int n_warmup, double *ms_per_iter, int64_t *launches) {
+    B2_API_BEGIN
+    return E(e)->bench_prefill(n_tokens, n_iters, n_warmup, ms_per_iter, launches);
+    B2_API_END(0)
+}
+
+
+int b2_dequantize(int type, const void *blocks, int64_t n_elems, float *out) {
+    B2_API_BEGIN
+    require_device();
+    const int be = type_block_elems(type);
+    B2_CHECK(be > 0, B2_EUNSUPPORTED, "unsupported ggml type");
+    const int64_t row_elems = 256; // every supported type packs 256 elements into whole blocks
+    B2_CHECK(n_elems > 0 && n_elems % row_elems == 0, B2_EINVAL, "n_elems must be a positive multiple of 256");
+    const int64_t rows = n_elems / row_elems;
+    DevBuf staging((size_t)(rows * gguf_row_bytes(type, row_elems))), dst((size_t)(rows * device_row_stride(type, row_elems))),
+        o((size_t)n_elems * 4);
+    DTensor W = upload_matrix(type, blocks, rows, row_elems, staging, dst);
+    launch_dequant_rows(W, nullptr, 0, (int)rows, o.as<float>(), row_elems, 0);
+    B2_CUDA(cudaMemcpy(out, o.p, (size_t)n_elems * 4, cudaMemcpyDeviceToHost));
+    return 0;
+    B2_API_END(0)
+}
+
+int b2_quantize_act(int wtype, const float *x, int64_t n_elems, void *out, size_t out_cap) {
+    B2_API_BEGIN
+    require_device();
+    B2_CHECK(n_elems > 0 && n_elems % 256 == 0, B2_EINVAL, "n_elems must be a positive multiple of 256");
+    const ActFmt f = act_format_for(wtype);
+    const int64_t K = n_elems;
+    const int64_t rb = act_row_bytes(f, K);
+    DevBuf dx((size_t)K * 4), dq((size_t)rb);
+    B2_CUDA(cudaMemcpy(dx.p, x, (size_t)K * 4, cudaMemcpyHostToDevice));
+    launch_quantize_act(f, dx.as<float>(), K, 1, K, dq.as<uint8_t>(), 0);
+    std::vector<uint8_t> soa((size_t)rb);
+    B2_CUDA(cudaMemcpy(soa.data(), dq.p, (size_t)rb, cudaMemcpyDeviceToHost));
+    uint8_t *o = (uint8_t *)out;
+    if (f == ACT_Q8_0) { // -> block_q8_0 { fp16 d; int8 qs[32]; }
+        const int64_t nb = K / 32;
+        B2_CHECK(out_cap >= (size_t)nb * 34, B2_ENOSPC, "output buffer too small");
+        const float *d = (const float *)(soa.data() + K);
+        for (int64_t b = 0; b < nb; b++) {
+            const __half h = __float2half_rn(d[b]);
+            memcpy(o + b * 34, &h, 2);
+            memcpy(o + b * 34 + 2, soa.data() + b * 32, 32);
+        }
+        return (int)(nb * 34);
+    }
+    if (f == ACT_Q8_K) { // -> block_q8_K { float d; int8 qs[256]; int16 bsums[16]; }
+        const int64_t nb = K / 256;
+        B2_CHECK(out_cap >= (size_t)nb * 292, B2_ENOSPC, "output buffer too small");
+        const uint8_t *d = soa.data() + K;
+        const uint8_t *bs = soa.data() + K + nb * 4;
+        for (int64_t b = 0; b < nb; b++) {
+            memcpy(o + b * 292, d + b * 4, 4);
+            memcpy(o + b * 292 + 4, soa.data() + b * 256, 256);
+            memcpy(o + b * 292 + 260, bs + b * 32, 32);
+        }
+        return (int)(nb * 292);
+    }
+    const size_t n = f == ACT_F16 ? (size_t)K * 2 : (size_t)K * 4;
+    B2_CHECK(out_cap >= n, B2_ENOSPC, "output buffer too small");
+    memcpy(o, soa.data(), n);
+    return (int)n;
+    B2_API_END(0)
+}
+
+int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const float *x, int n_tok, float *out, int path) {
+    B2_API_BEGIN
+    require_device();
+    B2_CHECK(type_block_elems(wtype) > 0, B2_EUNSUPPORTED, "unsupported ggml type");
+    B2_CHECK(rows > 0 && cols > 0 && n_tok > 0 && cols % 256 == 0, B2_EINVAL, "bad shape (cols must be a multiple of 256)");
+    B2_CHECK(path == 0 || path == 1, B2_EUNSUPPORTED, "tensor-core GEMM path not built yet");
+    DevBuf staging((size_t)(rows * gguf_row_bytes(wtype, cols))), dst((size_t)(rows * device_row_stride(wtype, cols)));
+    DTensor W = upload_matrix(wtype, blocks, rows, cols, staging, dst);
+    const ActFmt f = act_format_for(wtype);
+    const int64_t rb = act_row_bytes(f, cols);
+    DevBuf dx((size_t)n_tok * cols * 4), dq((size_t)n_tok * rb), dout((size_t)n_tok * rows * 4);
+    B2_CUDA(cudaMemcpy(dx.p, x, (size_t)n_tok * cols * 4, cudaMemcpyHostToDevice));
+    const uint8_t *xq = dq.as<uint8_t>();
+    if (f == ACT_F32) xq = dx.as<uint8_t>();
+    else launch_quantize_act(f, dx.as<float>(), cols, n_tok, cols, dq.as<uint8_t>(), 0);
+    launch_gemv(W, xq, f, n_tok, dout.as<float>(), rows, nullptr, 0, 0);
+    B2_CUDA(cudaMemcpy(out, dout.p, (size_t)n_tok * rows * 4, cudaMemcpyDeviceToHost));
+    return 0;
+    B2_API_END(0)
+}
+
+} // extern "C"

@@ -1,0 +1,54 @@
+// kernels.h -- launch wrappers for the hand-written sm_100a kernels (kernels_*.cu).
+#pragma once
+#include <cuda_fp16.h>
+
+#include "common.h"
+
+namespace b2 {
+
+// Counts kernel launches made through these wrappers (bench.py reports it as gpu_launches).
+extern thread_local int64_t g_launch_count;
+
+// --- load time ---------------------------------------------------------------------------------------
+// GGUF row layout -> device row layout (identity copy for Q4_K/Q5_K/F16/F32, SoA repack for Q8_0/Q6_K).
+void launch_repack(int type, const uint8_t *src_gguf, uint8_t *dst, int64_t rows, int64_t cols, cudaStream_t s);
+
+// --- dequantisation ----------------------------------------------------------------------------------
+// out[i, :] = dequant(W[row_ids ? row_ids[i] : row0 + i, :]) ; bit-exact with dequantize_row_* (unfused mul/sub).
+void launch_dequant_rows(const DTensor &W, const int32_t *row_ids_dev, int64_t row0, int n_rows, float *out,
+                         int64_t out_stride, cudaStream_t s);
+
+// --- activation quantisation (quantize_row_q8_0_ref / quantize_row_q8_K_ref semantics) ---------------
+void launch_quantize_act(ActFmt f, const float *x, int64_t x_stride, int n_tok, int64_t K, uint8_t *out, cudaStream_t s);
+
+// --- streaming dequant-GEMV: out[t*out_stride + r] = dot(W[r], xq[t]) (+ residual[t*res_stride + r]) ----
+void launch_gemv(const DTensor &W, const uint8_t *xq, ActFmt f, int n_tok, float *out, int64_t out_stride,
+                 const float *residual, int64_t res_stride, cudaStream_t s);
+
+// --- element-wise / normalisation --------------------------------------------------------------------
+// y[i] = rmsnorm(x[rows ? rows[i] : i]) * w
+void launch_rmsnorm(const float *x, int64_t x_stride, const int32_t *rows_dev, const float *w, float *y, int64_t y_stride,
+                    int n_tok, int d, float eps, cudaStream_t s);
+void launch_swiglu(const float *gate, const float *up, float *out, int64_t n, cudaStream_t s);
+
+// --- RoPE + paged KV store -----------------------------------------------------------------------------
+struct KVLayout {
+    __half *k_pool;            // [n_pages][page_size][kvd]
+    __half *v_pool;
+    const int32_t *page_table; // [n_slots][max_pages_per_slot]
+    int page_size, max_pages, kvd;
+};
+// q: [n_tok][n_head*hd] rotated in place; k,v: [n_tok][kvd]; pos/slot: per-token position and slot id (device)
+void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok,
+                          int n_head, int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, cudaStream_t s);
+// out[t][h*hd + i] = sum_j softmax_j(q_t . k_j * scale) v_j over positions j <= pos[t] of slot[t]
+void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv,
+                      int hd, const KVLayout &kv, float *out, int max_ctx, cudaStream_t s);
+
+// --- sampling -------------------------------------------------------------------------------------------
+// out[r] = first argmax of row r.  If feed_tok/feed_pos are given (device-side decode loop) the sampled id is also
+// written to feed_tok[r] and feed_pos[r] is incremented, so the next step needs no host round trip.
+void launch_argmax(const float *logits, int64_t stride, int n_rows, int n_vocab, int32_t *out, int32_t *feed_tok,
+                   int32_t *feed_pos, cudaStream_t s);
+
+} // namespace b2

@@ -1,0 +1,249 @@
+// kernels_misc.cu -- RMSNorm, SwiGLU, RoPE + paged-KV store, paged-KV attention, argmax.
+// Numerics follow the ggml CPU operators the reference executes (see oracle/ggml_ref.c for the restatement):
+// f32 everywhere, F16 KV cache, q and the soft-max probabilities rounded to f16 before their dot products.
+#include "kernels.h"
+#include "quant.cuh"
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------------------ RMSNorm (* weight)
+__global__ void __launch_bounds__(256)
+rmsnorm_kernel(const float *__restrict__ x, int64_t x_stride, const int32_t *__restrict__ rows, const float *__restrict__ w,
+               float *__restrict__ y, int64_t y_stride, int d, float eps) {
+    const float *xr = x + (int64_t)(rows ? rows[blockIdx.x] : blockIdx.x) * x_stride;
+    float *yr = y + (int64_t)blockIdx.x * y_stride;
+    double sum = 0.0;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+        const float v = xr[i];
+        sum += (double)__fmul_rn(v, v);
+    }
+    __shared__ double part[8];
+    __shared__ float s_scale;
+    sum = warp_sum_d(sum);
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int i = 0; i < (int)(blockDim.x >> 5); i++) tot += part[i];
+        const float mean = (float)(tot / (double)d);
+        s_scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+    }
+    __syncthreads();
+    const float scale = s_scale;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) yr[i] = __fmul_rn(__fmul_rn(xr[i], scale), w[i]);
+}
+
+void launch_rmsnorm(const float *x, int64_t x_stride, const int32_t *rows, const float *w, float *y, int64_t y_stride, int n_tok,
+                    int d, float eps, cudaStream_t s) {
+    if (n_tok <= 0) return;
+    rmsnorm_kernel<<<n_tok, 256, 0, s>>>(x, x_stride, rows, w, y, y_stride, d, eps);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------------ SwiGLU
+__global__ void swiglu_kernel(const float *__restrict__ g, const float *__restrict__ u, float *__restrict__ out, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float x = g[i];
+        const float s = __fdiv_rn(x, __fadd_rn(1.0f, expf(-x)));
+        out[i] = __fmul_rn(s, u[i]);
+    }
+}
+
+void launch_swiglu(const float *gate, const float *up, float *out, int64_t n, cudaStream_t s) {
+    if (n <= 0) return;
+    const int blocks = (int)std::min<int64_t>((n + 255) / 256, 148 * 8);
+    swiglu_kernel<<<blocks, 256, 0, s>>>(gate, up, out, n);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------------ RoPE (NORM pairs) + KV store
+__global__ void rope_kv_store_kernel(float *__restrict__ q, float *__restrict__ k, const float *__restrict__ v,
+                                     const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head, int n_head_kv,
+                                     int hd, const float *__restrict__ rope_table, KVLayout kv) {
+    const int t = blockIdx.x;
+    const int p = pos[t];
+    const int sl = slot[t];
+    const float *cs = rope_table + (int64_t)p * hd;
+    const int half = hd / 2;
+    const int page = kv.page_table[(int64_t)sl * kv.max_pages + p / kv.page_size];
+    const int64_t cell = ((int64_t)page * kv.page_size + p % kv.page_size) * kv.kvd;
+    float *qt = q + (int64_t)t * n_head * hd;
+    float *kt = k + (int64_t)t * n_head_kv * hd;
+    const float *vt = v + (int64_t)t * n_head_kv * hd;
+    const int nq = n_head * half, nk = n_head_kv * half;
+    for (int i = threadIdx.x; i < nq + nk; i += blockDim.x) {
+        const bool is_q = i < nq;
+        const int ii = is_q ? i : i - nq;
+        const int h = ii / half, pr = ii % half;
+        float *x = (is_q ? qt : kt) + h * hd + 2 * pr;
+        const float c = cs[2 * pr], sn = cs[2 * pr + 1];
+        const float x0 = x[0], x1 = x[1];
+        const float r0 = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn));
+        const float r1 = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+        if (is_q) {
+            x[0] = r0;
+            x[1] = r1;
+        } else {
+            *(__half2 *)(kv.k_pool + cell + h * hd + 2 * pr) = __halves2half2(__float2half_rn(r0), __float2half_rn(r1));
+        }
+    }
+    for (int i = threadIdx.x; i < kv.kvd; i += blockDim.x) kv.v_pool[cell + i] = __float2half_rn(vt[i]);
+}
+
+void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok, int n_head,
+                          int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, cudaStream_t s) {
+    if (n_tok <= 0) return;
+    rope_kv_store_kernel<<<n_tok, 256, 0, s>>>(q, k, v, pos, slot, n_head, n_head_kv, hd, rope_table, kv);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------------ attention (paged KV)
+// One CTA per (head, token).  Two passes so that the probabilities can be normalised and rounded to f16 before
+// the P.V product exactly as ggml's mul_mat(v_f16, soft_max(kq)) does.
+constexpr int ATT_THREADS = 128;
+
+__global__ void __launch_bounds__(ATT_THREADS)
+attention_kernel(const float *__restrict__ q, const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head,
+                 int n_head_kv, int hd, KVLayout kv, float *__restrict__ out, float scale) {
+    extern __shared__ __align__(16) float smem[];
+    const int h = blockIdx.x, t = blockIdx.y;
+    const int n_kv = pos[t] + 1;
+    const int sl = slot[t];
+    const int hk = h / (n_head / n_head_kv);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *qs = smem;                 // [hd] q rounded to f16
+    float *red = smem + hd;           // [ATT_THREADS] reduction scratch
+    float *sc = smem + hd + ATT_THREADS; // [n_kv] scores / probabilities
+    const int32_t *pt = kv.page_table + (int64_t)sl * kv.max_pages;
+    const float *qt = q + ((int64_t)t * n_head + h) * hd;
+    for (int i = threadIdx.x; i < hd; i += blockDim.x) qs[i] = __half2float(__float2half_rn(qt[i]));
+    __syncthreads();
+
+    // pass 1: scores
+    float lmax = -INFINITY;
+    for (int j = warp; j < n_kv; j += ATT_THREADS / 32) {
+        const __half *kr = kv.k_pool + ((int64_t)pt[j / kv.page_size] * kv.page_size + j % kv.page_size) * kv.kvd + hk * hd;
+        float a = 0.f;
+        for (int i = lane * 2; i < hd; i += 64) {
+            const float2 kk = __half22float2(*(const __half2 *)(kr + i));
+            a += kk.x * qs[i];
+            a += kk.y * qs[i + 1];
+        }
+        a = warp_sum(a) * scale;
+        if (lane == 0) sc[j] = a;
+        lmax = fmaxf(lmax, a);
+    }
+    red[threadIdx.x] = lmax;
+    __syncthreads();
+    float mx = -INFINITY;
+    for (int i = 0; i < ATT_THREADS; i += 32) mx = fmaxf(mx, red[i]); // lane-0 entries hold each warp's max (all lanes equal)
+    __syncthreads();
+    float lsum = 0.f;
+    for (int j = threadIdx.x; j < n_kv; j += blockDim.x) {
+        const float e = expf(sc[j] - mx);
+        sc[j] = e;
+        lsum += e;
+    }
+    lsum = warp_sum(lsum);
+    if (lane == 0) red[warp] = lsum;
+    __syncthreads();
+    double tot = 0.0;
+    for (int i = 0; i < ATT_THREADS / 32; i++) tot += (double)red[i];
+    const float inv = (float)(1.0 / tot);
+    __syncthreads();
+    for (int j = threadIdx.x; j < n_kv; j += blockDim.x) sc[j] = __half2float(__float2half_rn(__fmul_rn(sc[j], inv)));
+    __syncthreads();
+
+    // pass 2: out[i] = sum_j p_j * v_j[i]; thread groups of `hd` threads split the kv axis
+    const int ngroups = ATT_THREADS / hd > 0 ? ATT_THREADS / hd : 1;
+    for (int i0 = 0; i0 < hd; i0 += ATT_THREADS) {
+        const int i = i0 + (threadIdx.x % (hd < ATT_THREADS ? hd : ATT_THREADS));
+        const int g = hd < ATT_THREADS ? threadIdx.x / hd : 0;
+        float a = 0.f;
+        if (g < ngroups) {
+            for (int j = g; j < n_kv; j += ngroups) {
+                const __half *vr = kv.v_pool + ((int64_t)pt[j / kv.page_size] * kv.page_size + j % kv.page_size) * kv.kvd + hk * hd;
+                a += __half2float(vr[i]) * sc[j];
+            }
+        }
+        red[threadIdx.x] = a;
+        __syncthreads();
+        if (g == 0) {
+            for (int gg = 1; gg < ngroups; gg++) a += red[threadIdx.x + gg * hd];
+            out[((int64_t)t * n_head + h) * hd + i] = a;
+        }
+        __syncthreads();
+    }
+}
+
+void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv, int hd,
+                      const KVLayout &kv, float *out, int max_ctx, cudaStream_t s) {
+    if (n_tok <= 0) return;
+    B2_CHECK(hd % 2 == 0 && (hd >= ATT_THREADS ? hd % ATT_THREADS == 0 : ATT_THREADS % hd == 0), B2_EUNSUPPORTED,
+             "attention: unsupported head_dim");
+    const size_t smem = sizeof(float) * ((size_t)hd + ATT_THREADS + max_ctx);
+    B2_CHECK(smem <= 220 * 1024, B2_EUNSUPPORTED, "attention: context too long for the two-pass kernel");
+    static thread_local size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        B2_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        configured = 220 * 1024;
+    }
+    const float scale = 1.0f / sqrtf((float)hd);
+    attention_kernel<<<dim3(n_head, n_tok), ATT_THREADS, smem, s>>>(q, pos, slot, n_head, n_head_kv, hd, kv, out, scale);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------------ greedy sampling
+// first maximal element, like std::max_element in llama.cpp's greedy sampler
+__global__ void __launch_bounds__(1024)
+argmax_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, int32_t *__restrict__ out,
+              int32_t *__restrict__ feed_tok, int32_t *__restrict__ feed_pos) {
+    const float *x = logits + (int64_t)blockIdx.x * stride;
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < n_vocab; i += blockDim.x) {
+        const float v = x[i];
+        if (v > best) { best = v; bi = i; }
+    }
+    __shared__ float sv[32];
+    __shared__ int si[32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int nw = blockDim.x >> 5;
+        best = threadIdx.x < nw ? sv[threadIdx.x] : -INFINITY;
+        bi = threadIdx.x < nw ? si[threadIdx.x] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+        }
+        if (threadIdx.x == 0) {
+            const int tok = bi == 0x7fffffff ? 0 : bi;
+            out[blockIdx.x] = tok;
+            if (feed_tok) feed_tok[blockIdx.x] = tok;
+            if (feed_pos) feed_pos[blockIdx.x] += 1;
+        }
+    }
+}
+
+void launch_argmax(const float *logits, int64_t stride, int n_rows, int n_vocab, int32_t *out, int32_t *feed_tok,
+                   int32_t *feed_pos, cudaStream_t s) {
+    if (n_rows <= 0) return;
+    argmax_kernel<<<n_rows, 1024, 0, s>>>(logits, stride, n_vocab, out, feed_tok, feed_pos);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+} // namespace b2

@@ -1,0 +1,230 @@
+// kernels_sample.cu -- on-device sampling: greedy, temperature, top-k, top-p, min-p.
+// Chain order follows llama.cpp's default sampler chain (top_k -> top_p -> min_p -> temperature -> softmax ->
+// draw); one CTA per logits row; the vocabulary row (<= 513 KB) is read from L2 a handful of times.
+#include "kernels.h"
+#include "model.h"
+#include "quant.cuh"
+#include "sampling.h"
+
+namespace b2 {
+
+constexpr int SAMPLE_THREADS = 1024;
+constexpr int CAND_CAP = 2 * SAMPLE_MAX_CANDIDATES; // room for ties at the k-th value
+
+__device__ __forceinline__ uint32_t float_key(float f) { // monotonic float -> uint
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(uint32_t k) {
+    const uint32_t u = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
+    return __uint_as_float(u);
+}
+__device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
+__global__ void __launch_bounds__(SAMPLE_THREADS)
+sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, const SampleSpec *__restrict__ specs,
+              int32_t *__restrict__ out) {
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t s_prefix, s_remaining, s_count;
+    __shared__ unsigned long long cand[CAND_CAP]; // (key << 32) | (~idx): sorting descending gives key desc, idx asc
+    __shared__ float s_red[32];
+    __shared__ int s_redi[32];
+    __shared__ float s_scan[SAMPLE_THREADS];
+    const SampleSpec sp = specs[blockIdx.x];
+    const float *x = logits + (int64_t)blockIdx.x * stride;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    auto key_at = [&](int i) -> uint32_t { return i == sp.ban_token ? 0u : float_key(x[i]); };
+
+    // ---------------- greedy: first maximal element
+    if (sp.temperature <= 0.f) {
+        uint32_t best = 0;
+        int bi = 0x7fffffff;
+        for (int i = tid; i < n_vocab; i += SAMPLE_THREADS) {
+            const uint32_t k = key_at(i);
+            if (k > best) { best = k; bi = i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint32_t ok = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ok > best || (ok == best && oi < bi)) { best = ok; bi = oi; }
+        }
+        if (lane == 0) { s_red[warp] = __uint_as_float(best); s_redi[warp] = bi; }
+        __syncthreads();
+        if (warp == 0) {
+            best = __float_as_uint(s_red[lane]);
+            bi = s_redi[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const uint32_t ok = __shfl_xor_sync(0xffffffffu, best, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ok > best || (ok == best && oi < bi)) { best = ok; bi = oi; }
+            }
+            if (lane == 0) out[blockIdx.x] = bi == 0x7fffffff ? 0 : bi;
+        }
+        return;
+    }
+
+    const float u01 = (float)(splitmix64(sp.rng) >> 40) * (1.0f / 16777216.0f);
+    const float inv_t = 1.0f / sp.temperature;
+    int K = sp.top_k <= 0 ? n_vocab : min(sp.top_k, n_vocab);
+    const bool full = (K == n_vocab) && sp.top_p >= 1.0f && sp.min_p <= 0.0f;
+
+    // ---------------- no truncation at all: inverse-CDF over the whole vocabulary, no sort needed
+    if (full) {
+        float mx = -INFINITY;
+        for (int i = tid; i < n_vocab; i += SAMPLE_THREADS)
+            if (i != sp.ban_token) mx = fmaxf(mx, x[i]);
+        mx = warp_max(mx);
+        if (lane == 0) s_red[warp] = mx;
+        __syncthreads();
+        mx = s_red[0];
+        for (int i = 1; i < SAMPLE_THREADS / 32; i++) mx = fmaxf(mx, s_red[i]);
+        __syncthreads();
+        // contiguous chunk per thread so that the scan order is the index order
+        const int per = (n_vocab + SAMPLE_THREADS - 1) / SAMPLE_THREADS;
+        const int i0 = tid * per, i1 = min(n_vocab, i0 + per);
+        float part = 0.f;
+        for (int i = i0; i < i1; i++)
+            if (i != sp.ban_token) part += expf((x[i] - mx) * inv_t);
+        s_scan[tid] = part;
+        __syncthreads();
+        if (tid == 0) {
+            float tot = 0.f;
+            for (int i = 0; i < SAMPLE_THREADS; i++) tot += s_scan[i];
+            const float target = u01 * tot;
+            float acc = 0.f;
+            int t = 0;
+            for (; t < SAMPLE_THREADS - 1; t++) {
+                if (acc + s_scan[t] > target) break;
+                acc += s_scan[t];
+            }
+            int pick = -1;
+            const int j0 = t * per, j1 = min(n_vocab, j0 + per);
+            for (int i = j0; i < j1; i++) {
+                if (i == sp.ban_token) continue;
+                acc += expf((x[i] - mx) * inv_t);
+                pick = i;
+                if (acc > target) break;
+            }
+            if (pick < 0) pick = 0;
+            out[blockIdx.x] = pick;
+        }
+        return;
+    }
+
+    // ---------------- radix select of the K-th largest key (K capped to what fits on chip)
+    K = min(K, SAMPLE_MAX_CANDIDATES);
+    if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)K; }
+    __syncthreads();
+    for (int pass = 0; pass < 4; pass++) {
+        const int shift = 24 - 8 * pass;
+        if (tid < 256) hist[tid] = 0;
+        __syncthreads();
+        const uint32_t prefix = s_prefix;
+        const uint32_t mask = pass == 0 ? 0u : (0xFFFFFFFFu << (shift + 8));
+        for (int i = tid; i < n_vocab; i += SAMPLE_THREADS) {
+            const uint32_t k = key_at(i);
+            if ((k & mask) == prefix) atomicAdd(&hist[(k >> shift) & 0xFF], 1u);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t rem = s_remaining;
+            int b = 255;
+            for (; b > 0; b--) {
+                if (hist[b] >= rem) break;
+                rem -= hist[b];
+            }
+            s_prefix = prefix | ((uint32_t)b << shift);
+            s_remaining = rem;
+        }
+        __syncthreads();
+    }
+    const uint32_t kth = s_prefix; // key of the K-th largest element
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    for (int i = tid; i < n_vocab; i += SAMPLE_THREADS) {
+        const uint32_t k = key_at(i);
+        if (k >= kth && k != 0u) {
+            const uint32_t slot = atomicAdd(&s_count, 1u);
+            if (slot < CAND_CAP) cand[slot] = ((unsigned long long)k << 32) | (uint32_t)(~(uint32_t)i);
+        }
+    }
+    __syncthreads();
+    const int n_cand = min((int)s_count, CAND_CAP);
+    for (int i = n_cand + tid; i < CAND_CAP; i += SAMPLE_THREADS) cand[i] = 0ULL;
+    __syncthreads();
+    // bitonic sort, descending, CAND_CAP elements, 2 per thread
+    for (int k = 2; k <= CAND_CAP; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = tid; t < CAND_CAP; t += SAMPLE_THREADS) {
+                const int ixj = t ^ j;
+                if (ixj > t) {
+                    const unsigned long long a = cand[t], b = cand[ixj];
+                    const bool desc = (t & k) == 0;
+                    if (desc ? (a < b) : (a > b)) { cand[t] = b; cand[ixj] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    if (tid == 0) {
+        int n = min(n_cand, K);
+        if (n <= 0) { out[blockIdx.x] = 0; return; }
+        const float l0 = key_float((uint32_t)(cand[0] >> 32));
+        // top-p on the T=1 softmax of the surviving candidates
+        if (sp.top_p < 1.0f) {
+            float tot = 0.f;
+            for (int i = 0; i < n; i++) tot += expf(key_float((uint32_t)(cand[i] >> 32)) - l0);
+            float cum = 0.f;
+            int keep = n;
+            for (int i = 0; i < n; i++) {
+                cum += expf(key_float((uint32_t)(cand[i] >> 32)) - l0) / tot;
+                if (cum >= sp.top_p) { keep = i + 1; break; }
+            }
+            n = keep;
+        }
+        // min-p: p_i >= min_p * p_max  <=>  logit_i >= logit_max + log(min_p)
+        if (sp.min_p > 0.0f) {
+            const float thr = l0 + logf(sp.min_p);
+            int keep = 1;
+            while (keep < n && key_float((uint32_t)(cand[keep] >> 32)) >= thr) keep++;
+            n = keep;
+        }
+        // temperature, softmax, draw
+        float tot = 0.f;
+        for (int i = 0; i < n; i++) tot += expf((key_float((uint32_t)(cand[i] >> 32)) - l0) * inv_t);
+        const float target = u01 * tot;
+        float acc = 0.f;
+        int pick = n - 1;
+        for (int i = 0; i < n; i++) {
+            acc += expf((key_float((uint32_t)(cand[i] >> 32)) - l0) * inv_t);
+            if (acc > target) { pick = i; break; }
+        }
+        out[blockIdx.x] = (int32_t)(~(uint32_t)(cand[pick] & 0xFFFFFFFFu));
+    }
+}
+
+void launch_sample(const float *logits, int64_t stride, int n_rows, int n_vocab, const SampleSpec *specs_dev, int32_t *out,
+                   cudaStream_t s) {
+    if (n_rows <= 0) return;
+    sample_kernel<<<n_rows, SAMPLE_THREADS, 0, s>>>(logits, stride, n_vocab, specs_dev, out);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_host) {
+    const int n = (int)specs.size();
+    if (n == 0) return;
+    SampleSpec *dev = m.sample_specs_dev(n);
+    B2_CUDA(cudaMemcpyAsync(dev, specs.data(), sizeof(SampleSpec) * n, cudaMemcpyHostToDevice, m.stream));
+    launch_sample(m.logits_dev(), m.hp.n_vocab, n, m.hp.n_vocab, dev, const_cast<int32_t *>(m.next_tok_dev()), m.stream);
+    B2_CUDA(cudaMemcpyAsync(out_host, m.next_tok_dev(), sizeof(int32_t) * n, cudaMemcpyDeviceToHost, m.stream));
+}
+
+} // namespace b2

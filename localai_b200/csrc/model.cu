@@ -1,0 +1,359 @@
+// model.cu -- LoadModel (GGUF -> HBM) and the llama forward graph.
+//
+// Replaces llama_init_from_gpt_params + llama_decode as called from the reference engine
+// (backend/cpp/llama/grpc-server.cpp:461, :1910).  Graph = llm_build_llama.
+#include "model.h"
+#include "sampling.h"
+
+#include <cmath>
+#include <cstring>
+
+namespace b2 {
+
+void *Model::dalloc(size_t bytes) {
+    void *p = nullptr;
+    B2_CUDA(cudaMalloc(&p, bytes ? bytes : 16));
+    allocs_.push_back(p);
+    return p;
+}
+
+DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required) {
+    const GGUFTensorInfo *ti = f.tensor(name);
+    if (!ti) {
+        B2_CHECK(!required, B2_EIO, "gguf: missing tensor " + name);
+        return DTensor{};
+    }
+    B2_CHECK(ti->n_bytes >= 0, B2_EUNSUPPORTED, "gguf: tensor " + name + " has unsupported ggml type " + std::to_string(ti->type));
+    const int64_t cols = ti->ne[0];
+    const int64_t rows = ti->ne.size() > 1 ? ti->ne[1] : 1;
+    B2_CHECK(cols == want_cols && rows == want_rows, B2_EIO,
+             "gguf: tensor " + name + " has shape [" + std::to_string(rows) + "," + std::to_string(cols) + "], expected [" +
+                 std::to_string(want_rows) + "," + std::to_string(want_cols) + "]");
+    if (ti->type != B2_T_F32 && ti->type != B2_T_F16)
+        B2_CHECK(cols % 256 == 0, B2_EUNSUPPORTED, "tensor " + name + ": quantised row length must be a multiple of 256");
+    DTensor t;
+    t.type = ti->type;
+    t.rows = rows;
+    t.cols = cols;
+    t.row_stride = device_row_stride(ti->type, cols);
+    uint8_t *dst = (uint8_t *)dalloc((size_t)t.bytes());
+    if ((size_t)ti->n_bytes > staging_bytes_) {
+        if (staging_) cudaFree(staging_);
+        staging_bytes_ = (size_t)ti->n_bytes;
+        B2_CUDA(cudaMalloc((void **)&staging_, staging_bytes_));
+    }
+    B2_CUDA(cudaMemcpyAsync(staging_, ti->data, (size_t)ti->n_bytes, cudaMemcpyHostToDevice, stream));
+    launch_repack(t.type, staging_, dst, rows, cols, stream);
+    B2_CUDA(cudaStreamSynchronize(stream)); // staging buffer is reused by the next tensor
+    t.data = dst;
+    weight_bytes += t.bytes();
+    return t;
+}
+
+Model::Model(const GGUFFile &f, const b2_load_opts &o) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) throw Error(B2_ENODEV, "no CUDA device visible (this library has no CPU fallback)");
+    device = o.device;
+    B2_CHECK(device >= 0 && device < ndev, B2_EINVAL, "device ordinal out of range");
+    B2_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    B2_CUDA(cudaGetDeviceProperties(&prop, device));
+    B2_CHECK(prop.major == 10, B2_ENODEV,
+             std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) + "; this library is built for sm_100a only");
+    B2_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+
+    hp.arch = f.get_s("general.architecture", "");
+    B2_CHECK(hp.arch == "llama", B2_EUNSUPPORTED, "unsupported architecture '" + hp.arch + "' (only llama-family GGUF)");
+    hp.name = f.get_s("general.name", "");
+    const std::string a = hp.arch + ".";
+    hp.n_layer = (int)f.get_u(a + "block_count", 0);
+    hp.n_embd = (int)f.get_u(a + "embedding_length", 0);
+    hp.n_head = (int)f.get_u(a + "attention.head_count", 0);
+    hp.n_head_kv = (int)f.get_u(a + "attention.head_count_kv", hp.n_head);
+    hp.n_ff = (int)f.get_u(a + "feed_forward_length", 0);
+    hp.n_ctx_train = (int)f.get_u(a + "context_length", 2048);
+    hp.rms_eps = (float)f.get_f(a + "attention.layer_norm_rms_epsilon", 1e-5);
+    hp.rope_base = (float)f.get_f(a + "rope.freq_base", 10000.0);
+    hp.rope_scale = 1.0f;
+    B2_CHECK(hp.n_layer > 0 && hp.n_embd > 0 && hp.n_head > 0 && hp.n_ff > 0, B2_EIO, "gguf: missing llama hyper-parameters");
+    hp.head_dim = hp.n_embd / hp.n_head;
+    const int rope_dims = (int)f.get_u(a + "rope.dimension_count", hp.head_dim);
+    B2_CHECK(rope_dims == hp.head_dim, B2_EUNSUPPORTED, "partial rotary dimensions are not supported");
+    B2_CHECK(hp.n_head % hp.n_head_kv == 0, B2_EIO, "head_count not a multiple of head_count_kv");
+    if (o.rope_freq_base > 0) hp.rope_base = o.rope_freq_base;
+    if (o.rope_freq_scale > 0) hp.rope_scale = o.rope_freq_scale;
+
+    const GGUFTensorInfo *te = f.tensor("token_embd.weight");
+    B2_CHECK(te && te->ne.size() == 2, B2_EIO, "gguf: missing token_embd.weight");
+    hp.n_vocab = (int)te->ne[1];
+
+    n_ctx = o.n_ctx > 0 ? o.n_ctx : 1024;
+    n_parallel = o.n_parallel > 0 ? o.n_parallel : 1;
+    n_batch = o.n_batch > 0 ? o.n_batch : 512;
+    page_size = o.kv_page_size > 0 ? o.kv_page_size : 32;
+    n_ctx_slot = n_ctx / n_parallel; // grpc-server.cpp:512
+    B2_CHECK(n_ctx_slot > 0, B2_EINVAL, "context size smaller than the number of slots");
+    max_pages = (n_ctx_slot + page_size - 1) / page_size;
+
+    const int d = hp.n_embd, ff = hp.n_ff, kvd = hp.n_head_kv * hp.head_dim;
+    // ---- weights, in execution order
+    tok_embd = upload(f, "token_embd.weight", hp.n_vocab, d, true);
+    const int64_t embd_bytes = tok_embd.bytes();
+    layers.resize(hp.n_layer);
+    for (int l = 0; l < hp.n_layer; l++) {
+        const std::string p = "blk." + std::to_string(l) + ".";
+        LayerW &L = layers[l];
+        L.attn_norm = upload(f, p + "attn_norm.weight", 1, d, true);
+        L.wq = upload(f, p + "attn_q.weight", d, d, true);
+        L.wk = upload(f, p + "attn_k.weight", kvd, d, true);
+        L.wv = upload(f, p + "attn_v.weight", kvd, d, true);
+        L.wo = upload(f, p + "attn_output.weight", d, d, true);
+        L.ffn_norm = upload(f, p + "ffn_norm.weight", 1, d, true);
+        L.gate = upload(f, p + "ffn_gate.weight", ff, d, true);
+        L.up = upload(f, p + "ffn_up.weight", ff, d, true);
+        L.down = upload(f, p + "ffn_down.weight", d, ff, true);
+        B2_CHECK(L.attn_norm.type == B2_T_F32 && L.ffn_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
+    }
+    output_norm = upload(f, "output_norm.weight", 1, d, true);
+    B2_CHECK(output_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
+    output = upload(f, "output.weight", hp.n_vocab, d, false);
+    if (!output.data) { // tied embeddings
+        output = tok_embd;
+        decode_stream_bytes = weight_bytes;
+    } else {
+        decode_stream_bytes = weight_bytes - embd_bytes;
+    }
+    if (staging_) {
+        cudaFree(staging_);
+        staging_ = nullptr;
+        staging_bytes_ = 0;
+    }
+
+    // ---- KV cache (F16, paged; slot s statically owns pages [s*max_pages, (s+1)*max_pages))
+    const int64_t n_pages = (int64_t)n_parallel * max_pages;
+    pool_layer_stride_ = n_pages * page_size * kvd;
+    const size_t pool_bytes = (size_t)pool_layer_stride_ * hp.n_layer * sizeof(__half);
+    k_pool_ = (__half *)dalloc(pool_bytes);
+    v_pool_ = (__half *)dalloc(pool_bytes);
+    B2_CUDA(cudaMemsetAsync(k_pool_, 0, pool_bytes, stream));
+    B2_CUDA(cudaMemsetAsync(v_pool_, 0, pool_bytes, stream));
+    kv_bytes_per_pos = (int64_t)2 * hp.n_layer * kvd * sizeof(__half);
+    {
+        std::vector<int32_t> pt((size_t)n_parallel * max_pages);
+        for (size_t i = 0; i < pt.size(); i++) pt[i] = (int32_t)i;
+        page_table_ = (int32_t *)dalloc(pt.size() * 4);
+        B2_CUDA(cudaMemcpyAsync(page_table_, pt.data(), pt.size() * 4, cudaMemcpyHostToDevice, stream));
+        B2_CUDA(cudaStreamSynchronize(stream));
+    }
+    // ---- RoPE table, computed on the host exactly as ggml_rope_cache_init does (theta *= theta_scale, cosf/sinf)
+    {
+        const int hd = hp.head_dim;
+        std::vector<float> tab((size_t)n_ctx_slot * hd);
+        const float theta_scale = powf(hp.rope_base, -2.0f / hd);
+        for (int p = 0; p < n_ctx_slot; p++) {
+            float theta = (float)p;
+            for (int i0 = 0; i0 < hd; i0 += 2) {
+                const float t = hp.rope_scale * theta;
+                tab[(size_t)p * hd + i0] = cosf(t);
+                tab[(size_t)p * hd + i0 + 1] = sinf(t);
+                theta *= theta_scale;
+            }
+        }
+        rope_table_ = (float *)dalloc(tab.size() * 4);
+        B2_CUDA(cudaMemcpyAsync(rope_table_, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, stream));
+        B2_CUDA(cudaStreamSynchronize(stream));
+    }
+    // ---- scratch
+    const size_t nb = (size_t)n_batch;
+    x_ = (float *)dalloc(nb * d * 4);
+    xn_ = (float *)dalloc(nb * d * 4);
+    q_ = (float *)dalloc(nb * d * 4);
+    k_ = (float *)dalloc(nb * kvd * 4);
+    v_ = (float *)dalloc(nb * kvd * 4);
+    att_ = (float *)dalloc(nb * d * 4);
+    gate_ = (float *)dalloc(nb * ff * 4);
+    up_ = (float *)dalloc(nb * ff * 4);
+    const int64_t kmax = std::max(d, ff);
+    for (int fmt = ACT_F16; fmt <= ACT_Q8_K; fmt++) actq_[fmt] = (uint8_t *)dalloc(nb * (size_t)act_row_bytes((ActFmt)fmt, kmax));
+    tok_ = (int32_t *)dalloc(nb * 4);
+    pos_ = (int32_t *)dalloc(nb * 4);
+    slot_ = (int32_t *)dalloc(nb * 4);
+    out_rows_ = (int32_t *)dalloc(nb * 4);
+    next_tok_ = (int32_t *)dalloc(nb * 4);
+    xn_out_ = (float *)dalloc(nb * d * 4);
+    sample_specs_ = (SampleSpec *)dalloc(nb * sizeof(SampleSpec));
+    ensure_logits_rows(std::max(n_parallel, 1));
+}
+
+Model::~Model() {
+    cudaSetDevice(device);
+    if (stream) cudaStreamSynchronize(stream);
+    for (void *p : allocs_) cudaFree(p);
+    if (logits_) cudaFree(logits_);
+    if (staging_) cudaFree(staging_);
+    if (stream) cudaStreamDestroy(stream);
+}
+
+void Model::ensure_logits_rows(int n) {
+    if (n <= logits_rows_cap_) return;
+    B2_CUDA(cudaStreamSynchronize(stream));
+    if (logits_) cudaFree(logits_);
+    logits_ = nullptr;
+    B2_CUDA(cudaMalloc((void **)&logits_, (size_t)n * hp.n_vocab * 4));
+    logits_rows_cap_ = n;
+}
+
+SampleSpec *Model::sample_specs_dev(int n) {
+    B2_CHECK(n <= n_batch, B2_EINVAL, "too many rows to sample");
+    return sample_specs_;
+}
+
+void Model::enable_debug_hidden() {
+    if (!dbg_hidden_) dbg_hidden_ = (float *)dalloc((size_t)(hp.n_layer + 1) * hp.n_embd * 4);
+}
+
+// quantise activations the way ggml converts src1 for weights of W's type; cached per format until invalidated
+void Model::quantize_for(const DTensor &W, const float *x, int64_t x_stride, int n, uint8_t **out, ActFmt *fmt) {
+    const ActFmt f = act_format_for(W.type);
+    *fmt = f;
+    if (f == ACT_F32) {
+        B2_CHECK(x_stride == W.cols, B2_EINVAL, "f32 weights need densely packed activations");
+        *out = (uint8_t *)x;
+        return;
+    }
+    if (!actq_valid_[f]) {
+        launch_quantize_act(f, x, x_stride, n, W.cols, actq_[f], stream);
+        actq_valid_[f] = true;
+    }
+    *out = actq_[f];
+}
+
+void Model::matmul(const DTensor &W, const float *x, int64_t x_stride, int n, float *out, int64_t out_stride,
+                   const float *residual, int64_t res_stride) {
+    uint8_t *xq;
+    ActFmt f;
+    quantize_for(W, x, x_stride, n, &xq, &f);
+    launch_gemv(W, xq, f, n, out, out_stride, residual, res_stride, stream);
+}
+
+static inline void invalidate(bool (&v)[4]) { v[0] = v[1] = v[2] = v[3] = false; }
+void Model::invalidate_acts() { invalidate(actq_valid_); }
+
+void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
+    const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hd;
+    launch_dequant_rows(tok_embd, tok_, 0, n, x_, d, stream); // get_rows(tok_embd)
+    for (int l = 0; l < hp.n_layer; l++) {
+        const LayerW &L = layers[l];
+        KVLayout kv{k_pool_ + (size_t)l * pool_layer_stride_, v_pool_ + (size_t)l * pool_layer_stride_, page_table_, page_size,
+                    max_pages, kvd};
+        launch_rmsnorm(x_, d, nullptr, (const float *)L.attn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
+        invalidate(actq_valid_);
+        matmul(L.wq, xn_, d, n, q_, d, nullptr, 0);
+        matmul(L.wk, xn_, d, n, k_, kvd, nullptr, 0);
+        matmul(L.wv, xn_, d, n, v_, kvd, nullptr, 0);
+        launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+        launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+        invalidate(actq_valid_);
+        matmul(L.wo, att_, d, n, x_, d, x_, d); // x = x + wo.att
+        launch_rmsnorm(x_, d, nullptr, (const float *)L.ffn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
+        invalidate(actq_valid_);
+        matmul(L.up, xn_, d, n, up_, ff, nullptr, 0);
+        matmul(L.gate, xn_, d, n, gate_, ff, nullptr, 0);
+        launch_swiglu(gate_, up_, gate_, (int64_t)n * ff, stream);
+        invalidate(actq_valid_);
+        matmul(L.down, gate_, ff, n, x_, d, x_, d); // x = x + down.act
+        if (dbg_hidden_)
+            B2_CUDA(cudaMemcpyAsync(dbg_hidden_ + (size_t)l * d, x_ + (size_t)(n - 1) * d, d * 4, cudaMemcpyDeviceToDevice, stream));
+    }
+    if (n_out != 0) {
+        const int rows = n_out < 0 ? n : n_out;
+        ensure_logits_rows(rows);
+        launch_rmsnorm(x_, d, n_out < 0 ? nullptr : out_rows_dev, (const float *)output_norm.data, xn_out_, d, rows, d, hp.rms_eps,
+                       stream);
+        if (dbg_hidden_)
+            B2_CUDA(cudaMemcpyAsync(dbg_hidden_ + (size_t)hp.n_layer * d, xn_out_ + (size_t)(rows - 1) * d, d * 4,
+                                    cudaMemcpyDeviceToDevice, stream));
+        invalidate(actq_valid_);
+        matmul(output, xn_out_, d, rows, logits_, hp.n_vocab, nullptr, 0);
+    }
+}
+
+void Model::forward(const Batch &b) {
+    B2_CHECK(b.n > 0 && b.n <= n_batch, B2_EINVAL, "batch size must be in [1, n_batch]");
+    B2_CUDA(cudaSetDevice(device));
+    for (int i = 0; i < b.n; i++) {
+        B2_CHECK(b.slot[i] >= 0 && b.slot[i] < n_parallel, B2_EINVAL, "slot out of range");
+        B2_CHECK(b.pos[i] >= 0 && b.pos[i] < n_ctx_slot, B2_EINVAL, "position exceeds the slot's context");
+        if (b.tokens) B2_CHECK(b.tokens[i] >= 0 && b.tokens[i] < hp.n_vocab, B2_EINVAL, "token id out of range");
+    }
+    if (b.tokens) B2_CUDA(cudaMemcpyAsync(tok_, b.tokens, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
+    B2_CUDA(cudaMemcpyAsync(pos_, b.pos, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
+    B2_CUDA(cudaMemcpyAsync(slot_, b.slot, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
+    int n_out = b.n_out;
+    if (n_out > 0) B2_CUDA(cudaMemcpyAsync(out_rows_, b.out_rows, (size_t)n_out * 4, cudaMemcpyHostToDevice, stream));
+    run_graph(b.n, out_rows_, n_out);
+}
+
+void Model::set_device_inputs(const int32_t *tokens, const int32_t *pos, const int32_t *slot, int n) {
+    B2_CUDA(cudaSetDevice(device));
+    B2_CUDA(cudaMemcpyAsync(tok_, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+    B2_CUDA(cudaMemcpyAsync(pos_, pos, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+    B2_CUDA(cudaMemcpyAsync(slot_, slot, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+}
+
+void Model::forward_device_inputs(int n) {
+    B2_CUDA(cudaSetDevice(device));
+    run_graph(n, nullptr, -1);
+}
+
+void Model::sample_greedy(int n_rows, bool feed) {
+    launch_argmax(logits_, hp.n_vocab, n_rows, hp.n_vocab, next_tok_, feed ? tok_ : nullptr, feed ? pos_ : nullptr, stream);
+}
+
+} // namespace b2
+
+namespace b2 {
+// time the GEMV kernel alone, cycling over the layers so the weights of a launch are never L2-resident
+int Model::bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type) {
+    B2_CUDA(cudaSetDevice(device));
+    std::vector<const DTensor *> ws;
+    for (auto &L : layers) {
+        const DTensor *t = which == 0 ? &L.wq : which == 1 ? &L.wk : which == 2 ? &L.wv : which == 3 ? &L.wo
+                         : which == 4 ? &L.gate : which == 5 ? &L.up : which == 6 ? &L.down : nullptr;
+        if (t) ws.push_back(t);
+    }
+    if (which == 7) ws.push_back(&output);
+    B2_CHECK(!ws.empty(), B2_EINVAL, "bench_gemv: no such tensor");
+    const DTensor &W0 = *ws[0];
+    const int64_t K = W0.cols;
+    float *xin = which == 6 ? gate_ : xn_;
+    float *out = which == 7 ? logits_ : (which >= 4 && which <= 5 ? up_ : q_);
+    if (which == 7) ensure_logits_rows(n_tok);
+    // deterministic, O(1)-magnitude activations
+    std::vector<float> hx((size_t)n_tok * K);
+    for (size_t i = 0; i < hx.size(); i++) hx[i] = sinf(0.37f * (float)i) * 1.5f;
+    B2_CUDA(cudaMemcpyAsync(xin, hx.data(), hx.size() * 4, cudaMemcpyHostToDevice, stream));
+    uint8_t *xq;
+    ActFmt f;
+    invalidate_acts();
+    quantize_for(W0, xin, K, n_tok, &xq, &f);
+    for (auto *w : ws) B2_CHECK(w->type == W0.type, B2_EUNSUPPORTED, "bench_gemv: layers use different types for this tensor; pick another");
+    cudaEvent_t e0, e1;
+    B2_CUDA(cudaEventCreate(&e0));
+    B2_CUDA(cudaEventCreate(&e1));
+    for (auto *w : ws) launch_gemv(*w, xq, f, n_tok, out, w->rows, nullptr, 0, stream); // warm-up round
+    B2_CUDA(cudaEventRecord(e0, stream));
+    for (int r = 0; r < n_rounds; r++)
+        for (auto *w : ws) launch_gemv(*w, xq, f, n_tok, out, w->rows, nullptr, 0, stream);
+    B2_CUDA(cudaEventRecord(e1, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    float ms = 0;
+    B2_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (ms_per_launch) *ms_per_launch = ms / ((double)n_rounds * ws.size());
+    if (bytes_per_launch) *bytes_per_launch = W0.rows * gguf_row_bytes(W0.type, W0.cols);
+    if (ggml_type) *ggml_type = W0.type;
+    return 0;
+}
+} // namespace b2

@@ -1,0 +1,103 @@
+// model.h -- llama-architecture model resident in HBM + the forward pass (the llama_decode replacement).
+#pragma once
+#include <cuda_fp16.h>
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "common.h"
+#include "gguf.h"
+#include "kernels.h"
+
+namespace b2 {
+
+struct SampleSpec;
+
+struct HParams {
+    int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_ctx_train = 0;
+    float rms_eps = 1e-5f, rope_base = 10000.f, rope_scale = 1.f;
+    std::string arch, name;
+};
+
+struct LayerW {
+    DTensor attn_norm, wq, wk, wv, wo, ffn_norm, gate, up, down;
+};
+
+// A batch for one forward pass: n tokens, each with its own position and slot (sequence).
+struct Batch {
+    int n = 0;
+    const int32_t *tokens = nullptr; // host; nullptr => token ids are already in the device token buffer
+    const int32_t *pos = nullptr;    // host
+    const int32_t *slot = nullptr;   // host
+    // rows (token indices) whose logits are wanted; nullptr + n_out == -1 => all rows
+    const int32_t *out_rows = nullptr; // host
+    int n_out = 0;
+};
+
+class Model {
+  public:
+    Model(const GGUFFile &f, const b2_load_opts &o);
+    ~Model();
+    Model(const Model &) = delete;
+
+    // Runs the graph on `stream` (asynchronous).  Logits land in logits_dev() [n_out][n_vocab];
+    // the final-norm hidden states of the output rows land in embd_dev() [n_out][n_embd].
+    void forward(const Batch &b);
+    // greedy sample all output rows of the last forward into next_tok_dev(); if `feed`, also write them to
+    // the device token buffer and advance the device positions (device-side decode loop, no host round trip)
+    void sample_greedy(int n_rows, bool feed);
+    // decode step whose inputs (tokens/pos/slot for `n` sequences) already live on the device
+    void forward_device_inputs(int n);
+    void set_device_inputs(const int32_t *tokens, const int32_t *pos, const int32_t *slot, int n);
+
+    void sync() { B2_CUDA(cudaStreamSynchronize(stream)); }
+
+    const float *logits_dev() const { return logits_; }
+    const float *embd_dev() const { return xn_out_; }
+    const int32_t *next_tok_dev() const { return next_tok_; }
+    float *debug_hidden_dev() { return dbg_hidden_; }
+    SampleSpec *sample_specs_dev(int n);
+    void enable_debug_hidden();
+    int bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type);
+
+    HParams hp;
+    int n_ctx = 0, n_ctx_slot = 0, n_parallel = 1, n_batch = 512, page_size = 32, max_pages = 0;
+    int device = 0;
+    int64_t weight_bytes = 0, decode_stream_bytes = 0, kv_bytes_per_pos = 0;
+    cudaStream_t stream = nullptr;
+
+    std::vector<LayerW> layers;
+    DTensor tok_embd, output_norm, output;
+
+  private:
+    DTensor upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required);
+    void quantize_for(const DTensor &W, const float *x, int64_t x_stride, int n, uint8_t **out, ActFmt *fmt);
+    void matmul(const DTensor &W, const float *x, int64_t x_stride, int n, float *out, int64_t out_stride,
+                const float *residual, int64_t res_stride);
+    void run_graph(int n, const int32_t *out_rows_dev, int n_out);
+
+    std::vector<void *> allocs_;
+    uint8_t *staging_ = nullptr;
+    size_t staging_bytes_ = 0;
+    void *dalloc(size_t bytes);
+
+    // KV cache
+    __half *k_pool_ = nullptr, *v_pool_ = nullptr; // [n_layer][n_pages][page_size][kvd]
+    int32_t *page_table_ = nullptr;                // [n_parallel][max_pages]
+    int64_t pool_layer_stride_ = 0;
+    float *rope_table_ = nullptr; // [n_ctx_slot][head_dim] (cos, sin) pairs
+
+    // scratch (sized for n_batch tokens)
+    float *x_ = nullptr, *xn_ = nullptr, *q_ = nullptr, *k_ = nullptr, *v_ = nullptr, *att_ = nullptr, *gate_ = nullptr,
+          *up_ = nullptr, *logits_ = nullptr, *xn_out_ = nullptr, *dbg_hidden_ = nullptr;
+    uint8_t *actq_[4] = {nullptr, nullptr, nullptr, nullptr}; // per ActFmt quantised activation rows
+    bool actq_valid_[4] = {false, false, false, false};
+    int32_t *tok_ = nullptr, *pos_ = nullptr, *slot_ = nullptr, *out_rows_ = nullptr, *next_tok_ = nullptr;
+    int logits_rows_cap_ = 0;
+    SampleSpec *sample_specs_ = nullptr;
+    void ensure_logits_rows(int n);
+    void invalidate_acts();
+};
+
+} // namespace b2

@@ -1,0 +1,81 @@
+// quant.cuh -- device-side views of the GGUF block formats (device layout, see common.h) and helpers.
+#pragma once
+#include <cuda_fp16.h>
+#include <cstdint>
+
+namespace b2 {
+
+#define QK_K 256
+#define QK8_0 32
+
+__device__ __forceinline__ float h2f(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+
+// 6-bit scale / min of sub-block j (0..7) from the 12 packed bytes of a Q4_K / Q5_K block
+// (ggml-quants.c get_scale_min_k4)
+__device__ __forceinline__ void get_scale_min_k4(int j, const uint8_t *q, int &sc, int &m) {
+    if (j < 4) {
+        sc = q[j] & 63;
+        m = q[j + 4] & 63;
+    } else {
+        sc = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4);
+        m = (q[j + 4] >> 4) | ((q[j] >> 6) << 4);
+    }
+}
+
+// same, from the three 32-bit words of the packed scales held in registers
+__device__ __forceinline__ void get_scale_min_k4_w(int j, uint32_t w0, uint32_t w1, uint32_t w2, int &sc, int &m) {
+    // bytes 0..3 = w0, 4..7 = w1, 8..11 = w2
+    const int jj = j & 3;
+    const uint32_t b0 = (w0 >> (8 * jj)) & 0xFF, b1 = (w1 >> (8 * jj)) & 0xFF, b2 = (w2 >> (8 * jj)) & 0xFF;
+    if (j < 4) {
+        sc = b0 & 63;
+        m = b1 & 63;
+    } else {
+        sc = (b2 & 0xF) | ((b0 >> 6) << 4);
+        m = (b2 >> 4) | ((b1 >> 6) << 4);
+    }
+}
+
+// pointers to the sections of one Q6_K row in device (SoA) layout
+struct Q6Row {
+    const uint8_t *ql, *qh;
+    const int8_t *sc;
+    const uint16_t *d;
+    __device__ __forceinline__ Q6Row(const uint8_t *row, int nb)
+        : ql(row), qh(row + (size_t)nb * 128), sc((const int8_t *)(row + (size_t)nb * 192)),
+          d((const uint16_t *)(row + (size_t)nb * 208)) {}
+};
+// Q8_0 row in device (SoA) layout
+struct Q80Row {
+    const int8_t *qs;
+    const uint16_t *d;
+    __device__ __forceinline__ Q80Row(const uint8_t *row, int64_t cols)
+        : qs((const int8_t *)row), d((const uint16_t *)(row + cols)) {}
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// 128-bit streaming load of weights that are read exactly once per step (no L1 allocation)
+__device__ __forceinline__ int4 ld_stream(const void *p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+} // namespace b2

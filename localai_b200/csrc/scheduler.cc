@@ -1,0 +1,509 @@
+// scheduler.cc -- see scheduler.h.
+#include "scheduler.h"
+
+#include <algorithm>
+#include <cstring>
+
+#include "engine.h"
+#include "sampling.h"
+#include "tokenizer.h"
+
+namespace b2 {
+
+using clk = std::chrono::steady_clock;
+static double ms_since(clk::time_point t0) { return std::chrono::duration<double, std::milli>(clk::now() - t0).count(); }
+
+Scheduler::Scheduler(Engine *e) : eng_(e) {
+    const int n = e->model().n_parallel;
+    slots_.resize(n);
+    for (int i = 0; i < n; i++) {
+        slots_[i].id = i;
+        slots_[i].t_last_used = clk::now();
+    }
+    thread_ = std::thread([this] { loop(); });
+}
+
+Scheduler::~Scheduler() {
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        stop_ = true;
+    }
+    cv_.notify_all();
+    if (thread_.joinable()) thread_.join();
+    // wake any poller still blocked
+    for (auto &kv : requests_) {
+        std::lock_guard<std::mutex> lk(kv.second->mu);
+        if (!kv.second->finished) {
+            EventData ev;
+            ev.flags = B2_EV_FINAL | B2_EV_ERROR;
+            ev.text = "engine shut down";
+            kv.second->events.push_back(std::move(ev));
+            kv.second->finished = true;
+        }
+        kv.second->cv.notify_all();
+    }
+}
+
+int64_t Scheduler::submit(const b2_request &r) {
+    auto q = std::make_shared<Request>();
+    if (r.prompt && r.prompt_len) q->prompt.assign(r.prompt, r.prompt_len);
+    if (r.prompt_ids && r.n_prompt_ids > 0) {
+        q->prompt_ids.assign(r.prompt_ids, r.prompt_ids + r.n_prompt_ids);
+        q->has_ids = true;
+    }
+    q->n_predict = r.n_predict == 0 ? -1 : r.n_predict; // grpc-server.cpp:2098
+    q->temperature = r.temperature;
+    q->top_k = r.top_k;
+    q->top_p = r.top_p > 0 ? r.top_p : 1.f;
+    q->min_p = r.min_p;
+    q->repeat_penalty = r.repeat_penalty > 0 ? r.repeat_penalty : 1.f;
+    q->repeat_last_n = r.repeat_last_n;
+    q->frequency_penalty = r.frequency_penalty;
+    q->presence_penalty = r.presence_penalty;
+    q->seed = r.seed;
+    q->n_keep = r.n_keep;
+    q->ignore_eos = r.ignore_eos != 0;
+    q->cache_prompt = r.cache_prompt != 0;
+    q->embedding_mode = r.embedding_mode != 0;
+    q->stream = r.stream != 0;
+    if (q->embedding_mode) q->n_predict = 0;
+    for (int i = 0; i < r.n_stop; i++) {
+        if (!r.stop || !r.stop[i]) continue;
+        const size_t n = r.stop_len ? r.stop_len[i] : strlen(r.stop[i]);
+        if (n) q->stop.emplace_back(r.stop[i], n);
+    }
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        B2_CHECK(!stop_, B2_ESTATE, "engine is shutting down");
+        q->id = next_id_++;
+        requests_[q->id] = q;
+        pending_.push_back(q);
+    }
+    cv_.notify_all();
+    return q->id;
+}
+
+int Scheduler::poll(int64_t id, b2_event *ev, int timeout_ms) {
+    std::shared_ptr<Request> q;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        auto it = requests_.find(id);
+        B2_CHECK(it != requests_.end(), B2_ESTATE, "unknown request id");
+        q = it->second;
+    }
+    std::unique_lock<std::mutex> lk(q->mu);
+    auto ready = [&] { return !q->events.empty(); };
+    if (timeout_ms < 0) q->cv.wait(lk, ready);
+    else if (!q->cv.wait_for(lk, std::chrono::milliseconds(timeout_ms), ready)) return B2_ETIMEOUT;
+    EventData d = std::move(q->events.front());
+    q->events.pop_front();
+    q->last_text = std::move(d.text);
+    const uint32_t sz = ev->struct_size ? std::min<uint32_t>(ev->struct_size, sizeof(b2_event)) : (uint32_t)sizeof(b2_event);
+    b2_event out;
+    memset(&out, 0, sizeof(out));
+    out.struct_size = sz;
+    out.flags = d.flags;
+    out.text = q->last_text.data();
+    out.text_len = q->last_text.size();
+    out.n_prompt_tokens = d.n_prompt;
+    out.n_decoded = d.n_decoded;
+    out.slot_id = d.slot_id;
+    out.n_embd = d.n_embd;
+    out.t_prompt_ms = d.t_prompt_ms;
+    out.t_gen_ms = d.t_gen_ms;
+    memcpy(ev, &out, sz);
+    return 0;
+}
+
+int Scheduler::cancel(int64_t id) {
+    std::lock_guard<std::mutex> lk(mu_);
+    auto it = requests_.find(id);
+    B2_CHECK(it != requests_.end(), B2_ESTATE, "unknown request id");
+    it->second->cancelled = true;
+    cv_.notify_all();
+    return 0;
+}
+
+int Scheduler::embed_result(int64_t id, float *out, int cap) {
+    std::shared_ptr<Request> q;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        auto it = requests_.find(id);
+        B2_CHECK(it != requests_.end(), B2_ESTATE, "unknown request id");
+        q = it->second;
+    }
+    std::lock_guard<std::mutex> lk(q->mu);
+    const int n = (int)q->embedding.size();
+    if (n > cap) return -n;
+    if (n) memcpy(out, q->embedding.data(), (size_t)n * 4);
+    return n;
+}
+
+int Scheduler::release(int64_t id) {
+    std::lock_guard<std::mutex> lk(mu_);
+    auto it = requests_.find(id);
+    B2_CHECK(it != requests_.end(), B2_ESTATE, "unknown request id");
+    it->second->cancelled = true; // if still running, the engine thread drops it at the next step
+    requests_.erase(it);
+    return 0;
+}
+
+void Scheduler::metrics(b2_metrics_t *out) {
+    std::lock_guard<std::mutex> lk(metrics_mu_);
+    *out = metrics_;
+}
+
+void Scheduler::push_event(Request &r, EventData &&ev) {
+    {
+        std::lock_guard<std::mutex> lk(r.mu);
+        if (ev.flags & B2_EV_FINAL) r.finished = true;
+        r.events.push_back(std::move(ev));
+    }
+    r.cv.notify_all();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+void Scheduler::loop() {
+    for (;;) {
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] {
+                if (stop_ || !pending_.empty()) return true;
+                for (auto &s : slots_)
+                    if (s.state != IDLE) return true;
+                return false;
+            });
+            if (stop_) return;
+        }
+        try {
+            step();
+        } catch (const std::exception &e) { // a device error must not wedge pollers: fail every active request
+            for (auto &s : slots_)
+                if (s.state != IDLE) finish_slot(s, true, e.what());
+        }
+    }
+}
+
+// LRU free slot (get_slot, grpc-server.cpp:609-628)
+Scheduler::Slot *Scheduler::get_free_slot() {
+    Slot *best = nullptr;
+    for (auto &s : slots_)
+        if (s.state == IDLE && (!best || s.t_last_used < best->t_last_used)) best = &s;
+    return best;
+}
+
+bool Scheduler::has_budget(const Slot &s) const { // grpc-server.cpp:260-278
+    if (s.req->n_predict == -1) return true;
+    return s.req->n_predict - s.n_decoded > 0;
+}
+
+void Scheduler::launch_slot(Slot &s, std::shared_ptr<Request> r) {
+    Model &m = eng_->model();
+    const int n_ctx = m.n_ctx_slot;
+    s.req = r;
+    s.state = PROMPT;
+    s.n_decoded = 0;
+    s.generated_text.clear();
+    s.sent_count = 0;
+    s.has_next_token = true;
+    s.stopped_eos = s.stopped_word = s.stopped_limit = s.truncated = false;
+    s.t_start_prompt = clk::now();
+    s.t_prompt_ms = s.t_gen_ms = 0;
+    s.rng_state = r->seed < 0 ? (uint64_t)std::chrono::high_resolution_clock::now().time_since_epoch().count() : (uint64_t)(uint32_t)r->seed;
+    // tokenize (BOS iff the vocabulary asks for it; special tokens parsed: grpc-server.cpp:564,1689)
+    std::vector<int32_t> toks;
+    if (r->has_ids) toks = r->prompt_ids;
+    else if (!r->prompt.empty()) toks = eng_->tokenizer()->tokenize(r->prompt, true, true);
+    for (int32_t t : toks) B2_CHECK(t >= 0 && t < m.hp.n_vocab, B2_EINVAL, "prompt token id out of range");
+    s.n_prompt = (int)toks.size();
+    int n_keep = r->n_keep < 0 ? s.n_prompt : r->n_keep;
+    n_keep = std::min(n_ctx - 4, n_keep);
+    if (n_keep < 0) n_keep = 0;
+    if (s.n_prompt >= n_ctx) { // truncate keeping n_keep + the tail half-blocks (grpc-server.cpp:1700-1721)
+        const int n_left = n_ctx - n_keep;
+        const int n_block = std::max(1, n_left / 2);
+        const int erased = (s.n_prompt - n_keep - n_block) / n_block;
+        std::vector<int32_t> nt(toks.begin(), toks.begin() + n_keep);
+        nt.insert(nt.end(), toks.begin() + n_keep + erased * n_block, toks.end());
+        toks.swap(nt);
+        while ((int)toks.size() >= n_ctx) toks.erase(toks.begin() + n_keep); // defensive: must fit
+        s.truncated = true;
+        s.n_prompt = (int)toks.size();
+    }
+    if (!r->cache_prompt) {
+        s.n_past = 0;
+    } else { // in-memory prefix reuse (grpc-server.cpp:1740-1749)
+        size_t i = 0;
+        while (i < s.cache_tokens.size() && i < toks.size() && s.cache_tokens[i] == toks[i]) i++;
+        s.n_past = (int)i;
+        if (s.n_past > 0 && s.n_past == (int)s.cache_tokens.size()) s.n_past -= 1;
+    }
+    s.n_prompt_processed = s.n_prompt - s.n_past;
+    s.cache_tokens = toks;
+    s.prompt_tokens.swap(toks);
+    if (s.n_past == s.n_prompt && s.n_past > 0) s.n_past--; // at least one token must be evaluated
+}
+
+void Scheduler::finish_slot(Slot &s, bool error, const std::string &msg) {
+    if (s.n_decoded > 0) s.t_gen_ms = ms_since(s.t_start_gen);
+    EventData ev;
+    ev.flags = B2_EV_FINAL | (error ? B2_EV_ERROR : 0) | (s.stopped_eos ? B2_EV_STOP_EOS : 0) | (s.stopped_word ? B2_EV_STOP_WORD : 0) |
+               (s.stopped_limit ? B2_EV_STOP_LIMIT : 0);
+    if (error) ev.text = msg;
+    else if (!s.req->stream) ev.text = s.generated_text; // send_final_response: content only when not streaming
+    ev.n_prompt = s.n_prompt;
+    ev.n_decoded = s.n_decoded;
+    ev.slot_id = s.id;
+    ev.t_prompt_ms = s.t_prompt_ms;
+    ev.t_gen_ms = s.t_gen_ms;
+    {
+        std::lock_guard<std::mutex> lk(metrics_mu_);
+        metrics_.slot_id = s.id;
+        metrics_.tokens_generated = s.n_decoded;
+        metrics_.prompt_tokens_processed = s.n_prompt_processed;
+        metrics_.tokens_per_second = s.t_gen_ms > 0 ? (float)(1e3 / s.t_gen_ms * s.n_decoded) : 0.f;
+        metrics_.n_tokens_decoded_total += s.n_decoded;
+        metrics_.n_prompt_tokens_total += s.n_prompt_processed;
+    }
+    push_event(*s.req, std::move(ev));
+    s.req.reset();
+    s.state = IDLE;
+    s.t_last_used = clk::now();
+}
+
+static size_t find_partial_stop(const std::string &stop, const std::string &text) { // grpc-server.cpp:88-107
+    if (!text.empty() && !stop.empty()) {
+        const char last = text.back();
+        for (int64_t i = (int64_t)stop.size() - 1; i >= 0; i--) {
+            if (stop[i] == last) {
+                const size_t n = (size_t)i + 1;
+                if (text.size() >= n && text.compare(text.size() - n, n, stop, 0, n) == 0) return text.size() - n;
+            }
+        }
+    }
+    return std::string::npos;
+}
+
+// process_token (grpc-server.cpp:1010-1123): returns has_next_token
+bool Scheduler::process_token(Slot &s, int32_t tok) {
+    Request &r = *s.req;
+    const std::string piece = eng_->tokenizer()->token_to_piece(tok, true);
+    s.sampled = tok;
+    s.generated_text += piece;
+    s.has_next_token = true;
+    bool incomplete = false; // incomplete UTF-8 sequence at the end?
+    for (unsigned i = 1; i < 5 && i <= s.generated_text.size(); ++i) {
+        const unsigned char c = s.generated_text[s.generated_text.size() - i];
+        if ((c & 0xC0) == 0x80) continue;
+        if ((c & 0xE0) == 0xC0) incomplete = i < 2;
+        else if ((c & 0xF0) == 0xE0) incomplete = i < 3;
+        else if ((c & 0xF8) == 0xF0) incomplete = i < 4;
+        break;
+    }
+    if (!incomplete) {
+        size_t pos = std::min(s.sent_count, s.generated_text.size());
+        const std::string str_test = s.generated_text.substr(pos);
+        bool is_stop_full = false;
+        size_t stop_pos = std::string::npos;
+        for (const std::string &w : r.stop) { // full match
+            const size_t tmp = w.size() + piece.size();
+            const size_t from = str_test.size() > tmp ? str_test.size() - tmp : 0;
+            const size_t p = str_test.find(w, from);
+            if (p != std::string::npos && (stop_pos == std::string::npos || p < stop_pos)) {
+                s.stopped_word = true;
+                s.has_next_token = false;
+                stop_pos = p;
+            }
+        }
+        if (stop_pos != std::string::npos) {
+            is_stop_full = true;
+            s.generated_text.erase(pos + stop_pos);
+            pos = std::min(s.sent_count, s.generated_text.size());
+        } else {
+            for (const std::string &w : r.stop) { // partial match: hold the tail back
+                const size_t p = find_partial_stop(w, str_test);
+                if (p != std::string::npos && (stop_pos == std::string::npos || p < stop_pos)) stop_pos = p;
+            }
+        }
+        if (stop_pos == std::string::npos || (!s.has_next_token && !is_stop_full && stop_pos > 0)) {
+            std::string to_send = s.generated_text.substr(pos);
+            s.sent_count += to_send.size();
+            if (r.stream && !to_send.empty()) {
+                EventData ev;
+                ev.text = std::move(to_send);
+                ev.n_prompt = s.n_prompt;
+                ev.n_decoded = s.n_decoded;
+                ev.slot_id = s.id;
+                push_event(r, std::move(ev));
+            }
+        }
+    }
+    if (incomplete) s.has_next_token = true;
+    if (s.n_decoded > 0 && s.has_next_token && !has_budget(s)) {
+        s.stopped_limit = true;
+        s.has_next_token = false;
+    }
+    if (tok == eng_->tokenizer()->eos_id()) { // EOS only; EOT is the caller's stop word (grpc-server.cpp:1103)
+        s.stopped_eos = true;
+        s.has_next_token = false;
+    }
+    return s.has_next_token;
+}
+
+// one update_slots() (grpc-server.cpp:1546-1982)
+bool Scheduler::step() {
+    Model &m = eng_->model();
+    // cancellations and context exhaustion
+    for (auto &s : slots_) {
+        if (s.state == IDLE) continue;
+        if (s.req->cancelled) {
+            s.stopped_limit = true;
+            finish_slot(s);
+            continue;
+        }
+        if (s.state == GENERATING && (int)s.cache_tokens.size() >= m.n_ctx_slot) { // context-shift is disabled: release
+            s.stopped_limit = true;
+            finish_slot(s);
+            s.cache_tokens.clear();
+            s.n_past = 0;
+        }
+    }
+    // bind queued requests to free slots; requests that find none stay queued (deferred, grpc-server.cpp:1472-1478)
+    for (;;) {
+        std::shared_ptr<Request> r;
+        Slot *s = get_free_slot();
+        if (!s) break;
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            if (pending_.empty()) break;
+            r = pending_.front();
+            pending_.pop_front();
+        }
+        if (r->cancelled) {
+            EventData ev;
+            ev.flags = B2_EV_FINAL | B2_EV_STOP_LIMIT;
+            push_event(*r, std::move(ev));
+            continue;
+        }
+        try {
+            launch_slot(*s, r);
+        } catch (const std::exception &e) {
+            s->req = r;
+            s->n_prompt = 0;
+            finish_slot(*s, true, e.what());
+            continue;
+        }
+        if (s->n_prompt == 0) { // empty prompt -> empty final response (grpc-server.cpp:1645-1651)
+            finish_slot(*s);
+        }
+    }
+    // assemble the batch: one token per generating slot, then all pending prompt tokens
+    struct Row { int32_t tok, pos, slot; bool want; };
+    std::vector<Row> rows;
+    std::vector<std::pair<int, int>> out_of; // (slot index, row index) for rows that want logits
+    for (auto &s : slots_) {
+        if (s.state != GENERATING) continue;
+        out_of.emplace_back(s.id, (int)rows.size());
+        rows.push_back({s.sampled, s.n_past, s.id, true});
+        s.n_past += 1;
+    }
+    for (auto &s : slots_) {
+        if (s.state != PROMPT) continue;
+        for (; s.n_past < s.n_prompt; s.n_past++) rows.push_back({s.prompt_tokens[s.n_past], s.n_past, s.id, false});
+        rows.back().want = true; // logits only for the last prompt token
+        out_of.emplace_back(s.id, (int)rows.size() - 1);
+        s.n_decoded = 0;
+    }
+    if (rows.empty()) return false;
+
+    std::lock_guard<std::mutex> dev(eng_->device_mutex());
+    const int nb = m.n_batch;
+    std::vector<int32_t> tok(nb), pos(nb), sl(nb), orow(nb), sampled(nb);
+    for (int i0 = 0; i0 < (int)rows.size(); i0 += nb) {
+        const int c = std::min(nb, (int)rows.size() - i0);
+        int n_out = 0;
+        std::vector<int> out_slot;
+        std::vector<SampleSpec> specs;
+        for (int i = 0; i < c; i++) {
+            const Row &r = rows[i0 + i];
+            tok[i] = r.tok; pos[i] = r.pos; sl[i] = r.slot;
+            if (r.want) {
+                orow[n_out++] = i;
+                out_slot.push_back(r.slot);
+                Slot &s = slots_[r.slot];
+                SampleSpec sp;
+                sp.temperature = s.req->temperature;
+                sp.top_k = s.req->top_k;
+                sp.top_p = s.req->top_p;
+                sp.min_p = s.req->min_p;
+                sp.ban_token = s.req->ignore_eos ? eng_->tokenizer()->eos_id() : -1;
+                sp.rng = s.rng_state;
+                s.rng_state = s.rng_state * 6364136223846793005ULL + 1442695040888963407ULL;
+                specs.push_back(sp);
+            }
+        }
+        Batch b;
+        b.n = c;
+        b.tokens = tok.data(); b.pos = pos.data(); b.slot = sl.data();
+        b.out_rows = orow.data();
+        b.n_out = n_out;
+        m.forward(b);
+        if (n_out == 0) {
+            m.sync();
+            continue;
+        }
+        // embeddings first (they only need the final-norm rows), then sampling on device
+        std::vector<float> embd;
+        bool any_embd = false;
+        for (int k = 0; k < n_out; k++) any_embd |= slots_[out_slot[k]].req->embedding_mode;
+        if (any_embd) {
+            embd.resize((size_t)n_out * m.hp.n_embd);
+            B2_CUDA(cudaMemcpyAsync(embd.data(), m.embd_dev(), embd.size() * 4, cudaMemcpyDeviceToHost, m.stream));
+        }
+        sample_rows(m, specs, sampled.data());
+        m.sync();
+        {
+            std::lock_guard<std::mutex> lk(metrics_mu_);
+            metrics_.n_decode_steps++;
+            int busy = 0;
+            for (auto &s : slots_) busy += s.state != IDLE;
+            metrics_.n_slots_busy = busy;
+        }
+        for (int k = 0; k < n_out; k++) {
+            Slot &s = slots_[out_slot[k]];
+            if (s.state == IDLE) continue;
+            if (s.req->embedding_mode) { // send_embedding (grpc-server.cpp:1292-1321)
+                Request &r = *s.req;
+                {
+                    std::lock_guard<std::mutex> lk(r.mu);
+                    if (eng_->embeddings_enabled()) r.embedding.assign(embd.begin() + (size_t)k * m.hp.n_embd, embd.begin() + (size_t)(k + 1) * m.hp.n_embd);
+                    else r.embedding.assign(m.hp.n_embd, 0.0f);
+                }
+                s.t_prompt_ms = ms_since(s.t_start_prompt);
+                EventData ev;
+                ev.flags = B2_EV_FINAL | B2_EV_EMBEDDING;
+                ev.n_prompt = s.n_prompt;
+                ev.slot_id = s.id;
+                ev.n_embd = m.hp.n_embd;
+                ev.t_prompt_ms = s.t_prompt_ms;
+                push_event(r, std::move(ev));
+                s.req.reset();
+                s.state = IDLE;
+                s.t_last_used = clk::now();
+                continue;
+            }
+            const int32_t id = sampled[k];
+            if (s.state == PROMPT) s.state = GENERATING;
+            s.n_decoded += 1;
+            if (s.n_decoded == 1) {
+                s.t_start_gen = clk::now();
+                s.t_prompt_ms = ms_since(s.t_start_prompt);
+            }
+            s.cache_tokens.push_back(id);
+            if (!process_token(s, id)) finish_slot(s);
+        }
+    }
+    return true;
+}
+
+} // namespace b2

@@ -1,0 +1,46 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+
+
+def have_gpu() -> bool:
+    try:
+        from localai_b200 import capi
+        return capi.device_count() > 0
+    except Exception:
+        return False
+
+
+@pytest.fixture(scope="session")
+def gguf_dir(tmp_path_factory):
+    return str(tmp_path_factory.mktemp("gguf"))
+
+
+@pytest.fixture(scope="session")
+def model_files(gguf_dir):
+    """Small random-init GGUF models covering every quant type and both tokenisers."""
+    import make_gguf as mg
+
+    specs = {
+        "micro_mixed": ("micro", "mixed"),
+        "micro_q8_0": ("micro", "q8_0"),
+        "mini_q4_k_m": ("mini", "q4_k_m"),
+        "mini_q5_k": ("mini", "q5_k"),
+        "mini_f16": ("mini", "f16"),
+    }
+    out = {}
+    for name, (arch, preset) in specs.items():
+        path = os.path.join(gguf_dir, name + ".gguf")
+        mg.write_gguf(path, mg.ARCHS[arch], preset, seed=7, quiet=True)
+        out[name] = path
+    return out

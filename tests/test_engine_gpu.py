@@ -1,0 +1,187 @@
+"""Behavioural tests of the request path (submit / poll): the semantics of the reference's
+PredictStream / Predict / Embedding handlers and slot engine (backend/cpp/llama/grpc-server.cpp:1010-1123,
+1546-1982, 2333-2432), driven through the C ABI the way the Go backend drives it."""
+import threading
+
+import numpy as np
+import pytest
+
+from localai_b200 import capi
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def run(e, **kw):
+    rid = e.submit(**kw)
+    evs = list(e.events(rid))
+    e.release(rid)
+    return evs
+
+
+def text_of(evs):
+    return b"".join(ev["text"] for ev in evs)
+
+
+@pytest.fixture(scope="module")
+def eng(model_files):
+    with capi.Engine(model_files["mini_q4_k_m"], n_ctx=4 * 256, n_parallel=4, n_batch=64, embeddings=True) as e:
+        yield e
+
+
+PROMPT = "LocalAI is a drop-in replacement REST API"
+
+
+def test_stream_equals_non_stream_and_greedy_oracle(eng, model_files):
+    s = run(eng, prompt=PROMPT, n_predict=24, temperature=0.0, ignore_eos=True, stream=True)
+    n = run(eng, prompt=PROMPT, n_predict=24, temperature=0.0, ignore_eos=True, stream=False)
+    assert s[-1]["flags"] & capi.EV_FINAL and s[-1]["flags"] & capi.EV_STOP_LIMIT
+    assert s[-1]["n_decoded"] == 24 and n[-1]["n_decoded"] == 24
+    assert len(n) == 1 and text_of(s) == n[0]["text"] and s[-1]["text"] == b""
+    # the same tokens as the CPU oracle's greedy loop on the same prompt ids
+    ids = eng.tokenize(PROMPT, add_bos=True)
+    assert s[-1]["n_prompt_tokens"] == len(ids)
+    want, _, _ = O.OracleModel(model_files["mini_q4_k_m"], n_ctx=256).generate_greedy(ids, 24)
+    assert text_of(s) == b"".join(eng.token_to_piece(int(t)) for t in want)
+    # streamed pieces are complete UTF-8
+    for ev in s[:-1]:
+        ev["text"].decode("utf-8")
+
+
+def test_n_predict_zero_means_until_context_full(eng):
+    evs = run(eng, prompt="a b c", n_predict=0, temperature=0.0, ignore_eos=True, stream=False)
+    last = evs[-1]
+    assert last["flags"] & capi.EV_STOP_LIMIT
+    assert last["n_prompt_tokens"] + last["n_decoded"] >= eng.info.n_ctx_slot - 1
+
+
+def test_stop_word_is_trimmed_and_flagged(eng):
+    full = run(eng, prompt=PROMPT, n_predict=32, temperature=0.0, ignore_eos=True, stream=False)[0]["text"]
+    assert len(full) > 12
+    stop = full[8:12]  # a 4-byte sequence the model is known to produce
+    evs = run(eng, prompt=PROMPT, n_predict=32, temperature=0.0, ignore_eos=True, stream=True, stop=[stop])
+    got = text_of(evs)
+    assert evs[-1]["flags"] & capi.EV_STOP_WORD
+    assert stop not in got and full.startswith(got) and got == full[:full.find(stop)]
+
+
+def test_eos_stops_unless_ignored(eng):
+    # ban nothing: run until EOS or limit; then force EOS by making it the stop condition via ignore_eos=False
+    evs = run(eng, prompt=PROMPT, n_predict=16, temperature=0.0, ignore_eos=False, stream=False)
+    fl = evs[-1]["flags"]
+    assert fl & (capi.EV_STOP_EOS | capi.EV_STOP_LIMIT)
+    if fl & capi.EV_STOP_EOS:
+        assert evs[-1]["n_decoded"] <= 16
+
+
+def test_embedding_request(eng, model_files):
+    ids = eng.tokenize("embed me please", add_bos=True)
+    rid = eng.submit(prompt="embed me please", embedding_mode=True)
+    evs = list(eng.events(rid))
+    assert evs[-1]["flags"] & capi.EV_EMBEDDING and evs[-1]["n_embd"] == eng.info.n_embd
+    vec = eng.embed_result(rid)
+    eng.release(rid)
+    _, want = O.OracleModel(model_files["mini_q4_k_m"], n_ctx=64).eval(ids, want_embd=True)
+    assert vec.shape == (eng.info.n_embd,)
+    assert np.abs(vec - want).max() <= 2e-3 * np.abs(want).max()
+    # determinism: same input -> identical vector (core/http/app_test.go:856-881)
+    rid2 = eng.submit(prompt="embed me please", embedding_mode=True)
+    list(eng.events(rid2))
+    assert np.array_equal(vec, eng.embed_result(rid2))
+
+
+def test_embeddings_disabled_returns_zeros(model_files):
+    with capi.Engine(model_files["micro_q8_0"], n_ctx=64, embeddings=False) as e:
+        rid = e.submit(prompt_ids=[5, 6, 7], embedding_mode=True)
+        list(e.events(rid))
+        v = e.embed_result(rid)
+        assert v.shape == (e.info.n_embd,) and not v.any()  # grpc-server.cpp:1301-1309
+
+
+def test_concurrent_streams_are_independent(eng):
+    prompts = [f"request number {i} says hello to" for i in range(6)]  # more requests than slots: two get deferred
+    solo = [run(eng, prompt=p, n_predict=12, temperature=0.0, ignore_eos=True, stream=False)[0]["text"] for p in prompts]
+    out = [None] * len(prompts)
+
+    def worker(i):
+        out[i] = text_of(run(eng, prompt=prompts[i], n_predict=12, temperature=0.0, ignore_eos=True, stream=True))
+
+    th = [threading.Thread(target=worker, args=(i,)) for i in range(len(prompts))]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert out == solo
+    m = eng.metrics()
+    assert m["n_tokens_decoded_total"] >= 12 * 12 and m["tokens_per_second"] > 0
+
+
+def test_prompt_cache_reuses_prefix_and_keeps_output(eng):
+    base = run(eng, prompt=PROMPT + " compatible with", n_predict=10, temperature=0.0, ignore_eos=True, stream=False)
+    a = run(eng, prompt=PROMPT + " compatible with", n_predict=10, temperature=0.0, ignore_eos=True, stream=False,
+            cache_prompt=True)
+    b = run(eng, prompt=PROMPT + " compatible with", n_predict=10, temperature=0.0, ignore_eos=True, stream=False,
+            cache_prompt=True)
+    assert a[0]["text"] == base[0]["text"] == b[0]["text"]
+
+
+def test_long_prompt_is_truncated_not_rejected(eng):
+    ids = (np.arange(600) % 4000 + 3).astype(np.int32)  # > n_ctx_slot = 256
+    evs = run(eng, prompt_ids=ids, n_predict=4, temperature=0.0, ignore_eos=True, stream=False)
+    assert evs[-1]["flags"] & capi.EV_FINAL and not evs[-1]["flags"] & capi.EV_ERROR
+    assert evs[-1]["n_prompt_tokens"] < eng.info.n_ctx_slot
+
+
+def test_empty_prompt_gives_empty_final(eng):
+    evs = run(eng, prompt="", n_predict=4)
+    assert len(evs) == 1 and evs[0]["flags"] & capi.EV_FINAL and evs[0]["text"] == b"" and evs[0]["n_decoded"] == 0
+
+
+def test_cancel(eng):
+    rid = eng.submit(prompt=PROMPT, n_predict=0, temperature=0.0, ignore_eos=True, stream=True)
+    first = eng.poll(rid, 20000)
+    assert first is not None
+    eng.cancel(rid)
+    evs = [first] + list(eng.events(rid))
+    assert evs[-1]["flags"] & capi.EV_FINAL and evs[-1]["n_decoded"] < eng.info.n_ctx_slot - 20
+    eng.release(rid)
+    with pytest.raises(capi.B2Error):
+        eng.poll(rid, 0)
+
+
+def test_sampling_seeded_and_bounded(eng):
+    kw = dict(prompt=PROMPT, n_predict=16, ignore_eos=True, stream=False)
+    greedy = run(eng, temperature=0.0, **kw)[0]["text"]
+    assert run(eng, temperature=0.8, top_k=1, top_p=1.0, seed=1, **kw)[0]["text"] == greedy  # top-k 1 == greedy
+    a = run(eng, temperature=1.0, top_k=40, top_p=0.95, seed=123, **kw)[0]["text"]
+    b = run(eng, temperature=1.0, top_k=40, top_p=0.95, seed=123, **kw)[0]["text"]
+    c = run(eng, temperature=1.0, top_k=40, top_p=0.95, seed=124, **kw)[0]["text"]
+    assert a == b and (a != c or a != greedy)
+    # top_p -> 0 keeps only the most likely token
+    assert run(eng, temperature=1.0, top_k=0, top_p=1e-6, seed=5, **kw)[0]["text"] == greedy
+    # full-vocabulary sampling path (no truncation) runs and is reproducible
+    d1 = run(eng, temperature=1.0, top_k=0, top_p=1.0, seed=77, **kw)[0]["text"]
+    d2 = run(eng, temperature=1.0, top_k=0, top_p=1.0, seed=77, **kw)[0]["text"]
+    assert d1 == d2
+
+
+def test_sampling_distribution_matches_softmax(model_files):
+    """Draw many tokens from one fixed logits row and compare frequencies with softmax(top-k logits / T)."""
+    path = model_files["micro_q8_0"]
+    with capi.Engine(path, n_ctx=64) as e:
+        ids = [5, 6, 7, 8]
+        logits = e.eval(ids)[0].astype(np.float64)
+        T, K, N = 1.5, 8, 600
+        top = np.argsort(-logits, kind="stable")[:K]
+        p = np.exp((logits[top] - logits[top].max()) / T)
+        p /= p.sum()
+        counts = dict.fromkeys(top.tolist(), 0)
+        for s in range(N):
+            rid = e.submit(prompt_ids=ids, n_predict=1, temperature=T, top_k=K, top_p=1.0, seed=s, ignore_eos=True,
+                           stream=False)
+            ev = list(e.events(rid))[-1]
+            e.release(rid)
+            piece = ev["text"]
+            match = [t for t in top.tolist() if e.token_to_piece(t) == piece]
+            assert match, "sampled token outside the top-k set"
+            counts[match[0]] += 1
+        freq = np.array([counts[t] for t in top.tolist()]) / N
+        assert np.abs(freq - p).max() < 0.08

@@ -62,8 +62,8 @@ class Arch:
 
 ARCHS = {
     # unit-test sized models: every quant type has K % 256 == 0
-    "micro": Arch("micro", 2, 256, 4, 2, 512, 512, 512, 10000.0, 1e-5, "spm"),
-    "mini": Arch("mini", 3, 512, 8, 2, 1024, 2048, 1024, 500000.0, 1e-5, "bpe"),
+    "micro": Arch("micro", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm"),
+    "mini": Arch("mini", 3, 512, 8, 2, 1024, 4608, 1024, 500000.0, 1e-5, "bpe"),
     # BASELINE.json configs
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 5632, 32000, 2048, 10000.0, 1e-5, "spm"),
     "llama3-8b": Arch("llama3-8b", 32, 4096, 32, 8, 14336, 128256, 8192, 500000.0, 1e-5, "bpe"),
