@@ -180,6 +180,101 @@ def random_tensor_bytes(rng, gtype: int, rows: int, cols: int, sigma: float, chu
         yield random_blocks(rng, gtype, r * bpr, sigma).tobytes()
 
 
+# --------------------------------------------------------------------------- simple float -> block quantisers
+# Used only for the token embedding and the (structured) output matrix.  They are plain round-to-nearest
+# quantisers, NOT llama.cpp's search-based ones: any valid block is a valid test input, and the dequantised
+# values (which is what every implementation consumes) are what matters.
+def quantize_rows(x: np.ndarray, gtype: int) -> np.ndarray:
+    """x: float32 [rows, cols] -> uint8 [rows, row_bytes]."""
+    rows, cols = x.shape
+    if gtype == F32:
+        return x.astype(np.float32).view(np.uint8).reshape(rows, -1)
+    if gtype == F16:
+        return x.astype(np.float16).view(np.uint8).reshape(rows, -1)
+    if gtype == Q8_0:
+        b = x.reshape(-1, 32)
+        d = np.abs(b).max(axis=1, keepdims=True) / 127.0
+        with np.errstate(divide="ignore", invalid="ignore"):
+            inv = np.where(d == 0, 0, 1.0 / d)
+        q = np.clip(np.rint(b * inv), -127, 127).astype(np.int8)
+        return np.concatenate([d.astype(np.float16).view(np.uint8).reshape(-1, 2), q.view(np.uint8)], axis=1).reshape(rows, -1)
+    if gtype in (Q4_K, Q5_K):
+        qmax = 15 if gtype == Q4_K else 31
+        b = x.reshape(-1, 8, 32)
+        mn = np.minimum(b.min(axis=2), 0.0)
+        mx = b.max(axis=2)
+        scale = np.maximum((mx - mn) / qmax, 1e-12)
+        d = np.maximum(scale.max(axis=1, keepdims=True) / 63.0, 1e-12).astype(np.float16).astype(np.float32)
+        dmin = np.maximum((-mn).max(axis=1, keepdims=True) / 63.0, 1e-12).astype(np.float16).astype(np.float32)
+        sc = np.clip(np.rint(scale / d), 1, 63)
+        m = np.clip(np.rint(-mn / dmin), 0, 63)
+        q = np.clip(np.rint((b + (dmin * m)[:, :, None]) / (d * sc)[:, :, None]), 0, qmax).astype(np.uint8)
+        scales = _pack_k_scales(sc, m)
+        ql = q & 0x0F
+        qs = (ql[:, 0::2, :] | (ql[:, 1::2, :] << 4)).reshape(-1, 128)  # sub-block 2j -> low nibbles, 2j+1 -> high
+        parts = [_f16_bytes(d[:, 0]), _f16_bytes(dmin[:, 0]), scales]
+        if gtype == Q5_K:
+            hb = (q >> 4) & 1  # [n, 8, 32]: bit j of qh[l] belongs to sub-block j
+            qh = np.zeros((q.shape[0], 32), dtype=np.uint8)
+            for j in range(8):
+                qh |= (hb[:, j, :] << j).astype(np.uint8)
+            parts.append(qh)
+        parts.append(qs)
+        return np.concatenate(parts, axis=1).reshape(rows, -1)
+    if gtype == Q6_K:
+        b = x.reshape(-1, 16, 16)
+        amax = np.abs(b).max(axis=2)
+        scale = np.maximum(amax / 31.0, 1e-12)
+        d = np.maximum(scale.max(axis=1, keepdims=True) / 127.0, 1e-12).astype(np.float16).astype(np.float32)
+        sc = np.clip(np.rint(scale / d), 1, 127)
+        q = (np.clip(np.rint(b / (d * sc)[:, :, None]), -32, 31) + 32).astype(np.uint8).reshape(-1, 2, 4, 32)  # [n, half, quarter, l]
+        lo = q & 0x0F
+        ql = np.concatenate([lo[:, :, 0, :] | (lo[:, :, 2, :] << 4), lo[:, :, 1, :] | (lo[:, :, 3, :] << 4)], axis=2)  # [n, 2, 64]
+        hi = q >> 4
+        qh = hi[:, :, 0, :] | (hi[:, :, 1, :] << 2) | (hi[:, :, 2, :] << 4) | (hi[:, :, 3, :] << 6)  # [n, 2, 32]
+        return np.concatenate([ql.reshape(-1, 128), qh.reshape(-1, 64), sc.astype(np.int8).view(np.uint8), _f16_bytes(d[:, 0])],
+                              axis=1).reshape(rows, -1)
+    raise ValueError(gtype)
+
+
+_EMB_BLOCK_ROWS = 256
+
+
+def embedding_rows(seed: int, r0: int, r1: int, cols: int) -> np.ndarray:
+    """Deterministic N(0,1) embedding floats for rows [r0, r1): generated in fixed 256-row blocks so that any
+    row range can be re-created independently (the structured output matrix re-reads shifted rows)."""
+    out = np.empty((r1 - r0, cols), dtype=np.float32)
+    b0, b1 = r0 // _EMB_BLOCK_ROWS, (r1 - 1) // _EMB_BLOCK_ROWS
+    for b in range(b0, b1 + 1):
+        blk = np.random.default_rng([seed, 7_000_003, b]).standard_normal((_EMB_BLOCK_ROWS, cols), dtype=np.float32)
+        lo, hi = max(r0, b * _EMB_BLOCK_ROWS), min(r1, (b + 1) * _EMB_BLOCK_ROWS)
+        out[lo - r0:hi - r0] = blk[lo - b * _EMB_BLOCK_ROWS:hi - b * _EMB_BLOCK_ROWS]
+    return out
+
+
+NEXT_TOKEN_SHIFT = 1009  # structured models greedily continue t -> (t + 1009) mod n_vocab
+
+
+def structured_tensor_bytes(kind: str, seed: int, gtype: int, rows: int, cols: int, scale: float, chunk_rows: int = 2048):
+    """token_embd: quantise(e[r]);  output: quantise(scale * e[(v - SHIFT) mod V]).
+
+    With output rows aligned to (shifted) embedding rows the logit of token t+SHIFT stands ~5 sigma above the rest,
+    so the greedy continuation has a healthy top-1 margin instead of the near-ties a purely random output matrix
+    gives (SURVEY.md 7 "hard parts": argmax flips on 1e-3 noise).  All transformer layers stay random."""
+    for r0 in range(0, rows, chunk_rows):
+        r1 = min(rows, r0 + chunk_rows)
+        if kind == "embd":
+            x = embedding_rows(seed, r0, r1, cols)
+        else:
+            s0 = (r0 - NEXT_TOKEN_SHIFT) % rows
+            n = r1 - r0
+            if s0 + n <= rows:
+                x = embedding_rows(seed, s0, s0 + n, cols)
+            else:
+                x = np.concatenate([embedding_rows(seed, s0, rows, cols), embedding_rows(seed, 0, s0 + n - rows, cols)])
+        yield quantize_rows(x * np.float32(scale), gtype).tobytes()
+
+
 # --------------------------------------------------------------------------- vocab
 def load_vocab(kind: str, n_vocab: int, vocab_dir: str):
     """Return dict(tokens, scores, types, merges, bos, eos, model, pre) padded to n_vocab.
@@ -305,7 +400,8 @@ def tensor_nbytes(rows, cols, t):
 
 
 def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: float = 4.0,
-               vocab_dir: str | None = None, n_ctx_train: int | None = None, quiet: bool = False) -> dict:
+               vocab_dir: str | None = None, n_ctx_train: int | None = None, quiet: bool = False,
+               structured: bool = True) -> dict:
     vocab_dir = vocab_dir or os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
     vocab = load_vocab(arch.tokenizer, arch.n_vocab, vocab_dir)
     plan = tensor_plan(arch, preset, gain_out)
@@ -368,6 +464,11 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
                 w = (1.0 + 0.1 * rng.standard_normal(cols)).astype(np.float32)
                 f.write(w.tobytes())
                 n = w.nbytes
+            elif structured and name in ("token_embd.weight", "output.weight"):
+                kind = "embd" if name == "token_embd.weight" else "out"
+                for chunk in structured_tensor_bytes(kind, seed, t, rows, cols, sigma):
+                    f.write(chunk)
+                    n += len(chunk)
             else:
                 for chunk in random_tensor_bytes(rng, t, rows, cols, sigma):
                     f.write(chunk)
@@ -381,6 +482,7 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     # (one row gathered) -- SURVEY.md §8(d)
     stream = sum(tensor_nbytes(r, c, t) for (nm, r, c, t, _, _) in plan if nm != "token_embd.weight")
     info = dict(path=path, arch=arch.name, preset=preset, seed=seed, file_bytes=total, n_tensors=len(plan),
+                structured=structured, next_token_shift=NEXT_TOKEN_SHIFT if structured else None,
                 type_bytes=type_bytes, decode_stream_bytes=stream)
     if not quiet:
         print(json.dumps(info))
@@ -396,13 +498,14 @@ def main(argv=None):
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--gain-out", type=float, default=4.0, help="output.weight std multiplier (argmax margin)")
     ap.add_argument("--n-layer", type=int, default=None, help="override layer count (debug)")
+    ap.add_argument("--unstructured", action="store_true", help="purely random output matrix (near-flat logits)")
     args = ap.parse_args(argv)
     arch = ARCHS[args.arch]
     if args.n_layer:
         arch = Arch(**{**{k: getattr(arch, k) for k in
                           ["name", "n_layer", "n_embd", "n_head", "n_head_kv", "n_ff", "n_vocab", "n_ctx_train",
                            "rope_theta", "rms_eps", "tokenizer", "is_70b"]}, "n_layer": args.n_layer})
-    write_gguf(args.out, arch, args.preset, args.seed, args.gain_out)
+    write_gguf(args.out, arch, args.preset, args.seed, args.gain_out, structured=not args.unstructured)
 
 
 if __name__ == "__main__":
