@@ -156,10 +156,11 @@ def test_sampling_seeded_and_bounded(eng):
     kw = dict(prompt=PROMPT, n_predict=16, ignore_eos=True, stream=False)
     greedy = run(eng, temperature=0.0, **kw)[0]["text"]
     assert run(eng, temperature=0.8, top_k=1, top_p=1.0, seed=1, **kw)[0]["text"] == greedy  # top-k 1 == greedy
-    # the fixture's logits are sharply peaked (top-1 margin ~ 30), so flatten them with a high temperature
-    a = run(eng, temperature=40.0, top_k=40, top_p=0.95, seed=123, **kw)[0]["text"]
-    b = run(eng, temperature=40.0, top_k=40, top_p=0.95, seed=123, **kw)[0]["text"]
-    c = run(eng, temperature=40.0, top_k=40, top_p=0.95, seed=124, **kw)[0]["text"]
+    # the fixture logits are sharply peaked (margin ~30): flatten with a high temperature; top_p is applied BEFORE
+    # the temperature (llama.cpp chain order), so it must be 1.0 here or it would keep the top token only
+    a = run(eng, temperature=40.0, top_k=40, top_p=1.0, seed=123, **kw)[0]["text"]
+    b = run(eng, temperature=40.0, top_k=40, top_p=1.0, seed=123, **kw)[0]["text"]
+    c = run(eng, temperature=40.0, top_k=40, top_p=1.0, seed=124, **kw)[0]["text"]
     assert a == b and (a != c or a != greedy)
     # top_p -> 0 keeps only the most likely token
     assert run(eng, temperature=1.0, top_k=0, top_p=1e-6, seed=5, **kw)[0]["text"] == greedy
