@@ -218,6 +218,26 @@ int b2_dequantize(int type, const void *blocks, int64_t n_elems, float *out);
 int b2_quantize_act(int wtype, const float *x, int64_t n_elems, void *out, size_t out_cap);
 int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const float *x, int n_tok, float *out, int path);
 
+/* ------------------------------------------------------------------------------------------------
+ * b2_mul_mat_noalloc -- has no counterpart in the reference.
+ *
+ * The same quantised mat-mul as b2_mul_mat (out[t][r] = dot(W[r,:], quantise(x[t,:]))), for callers that must not
+ * allocate device memory: frameworks that have already handed all of HBM to their own pool, latency-critical
+ * loops that cannot afford cudaMalloc's locks and implicit synchronisation, embedders under a "no allocation
+ * after start-up" rule.  Everything is passed in as DEVICE pointers owned by the caller (weights in GGUF block
+ * layout, activations f32 [n_tok][cols], result f32 [n_tok][rows]); the scratch for the quantised activations is a
+ * fixed 128 KiB array inside the library, which every GPU that loads the library holds until exit.
+ *   - limits: wtype in {B2_T_Q4_K, B2_T_Q5_K, B2_T_F16}; cols % 256 == 0 and cols <= 16384; 1 <= n_tok <= 4.
+ *     Anything larger is rejected with B2_EINVAL.
+ *   - w_dev must be 16-byte aligned, x_dev 16-byte aligned; all pointers must belong to the CURRENT device.
+ *   - runs asynchronously on `cuda_stream` (a cudaStream_t, NULL = default stream); performs no allocation.
+ *   - the first call on each device looks up the scratch array's device address; make that first call before
+ *     starting any stream capture.
+ *   - all calls on a device share the one scratch array (it keeps the previous call's contents, and needs no
+ *     clearing: each call rewrites what it reads), so calls that overlap on the GPU race -- serialise them. */
+int b2_mul_mat_noalloc(int wtype, const void *w_dev, int64_t rows, int64_t cols, const float *x_dev, int n_tok,
+                       float *out_dev, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

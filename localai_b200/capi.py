@@ -23,7 +23,7 @@ EXPORTS = [
     "b2_abi_version", "b2_last_error", "b2_device_count", "b2_create", "b2_destroy", "b2_model_info", "b2_tokenize",
     "b2_token_to_piece", "b2_submit", "b2_poll", "b2_cancel", "b2_embed_result", "b2_release", "b2_metrics", "b2_eval",
     "b2_decode_greedy", "b2_debug_hidden", "b2_bench_decode", "b2_bench_prefill", "b2_bench_gemv", "b2_dequantize", "b2_quantize_act",
-    "b2_mul_mat",
+    "b2_mul_mat", "b2_mul_mat_noalloc",
 ]
 
 
@@ -117,6 +117,7 @@ def lib() -> C.CDLL:
     L.b2_dequantize.argtypes = [i32, vp, i64, vp]
     L.b2_quantize_act.argtypes = [i32, vp, i64, vp, C.c_size_t]
     L.b2_mul_mat.argtypes = [i32, vp, i64, i64, vp, i32, vp, i32]
+    L.b2_mul_mat_noalloc.argtypes = [i32, vp, i64, i64, vp, i32, vp, vp]
     _lib = L
     return L
 
@@ -156,6 +157,12 @@ def mul_mat(wtype: int, w_raw: np.ndarray, rows: int, cols: int, x: np.ndarray, 
     out = np.empty((x.shape[0], rows), dtype=np.float32)
     _check(lib().b2_mul_mat(wtype, _ptr(w_raw), rows, cols, _ptr(x), x.shape[0], _ptr(out), path))
     return out
+
+
+def mul_mat_noalloc(wtype: int, w_dev: int, rows: int, cols: int, x_dev: int, n_tok: int, out_dev: int, stream: int = 0):
+    """b2_mul_mat_noalloc on raw DEVICE addresses (ints); asynchronous on `stream`; allocates nothing."""
+    _check(lib().b2_mul_mat_noalloc(wtype, C.c_void_p(w_dev), rows, cols, C.c_void_p(x_dev), n_tok, C.c_void_p(out_dev),
+                                    C.c_void_p(stream)))
 
 
 # ------------------------------------------------------------------------------- engine
