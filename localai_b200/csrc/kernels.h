@@ -45,6 +45,43 @@ void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos
 void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv,
                       int hd, const KVLayout &kv, float *out, int max_ctx, cudaStream_t s);
 
+// --- fused decode mat-vec (kernels_fused.cu) -----------------------------------------------------------------
+enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_QKV = 2 };
+struct FusedJob {
+    const uint8_t *W;
+    int type;
+    int64_t rows, row_stride;
+};
+struct FusedGemv {
+    // activations: either already quantised rows (xq_pre) or fp32 rows x[(x_rows ? x_rows[t] : t)] that the kernel
+    // normalises (if norm_w) and quantises itself
+    const uint8_t *xq_pre = nullptr;
+    const float *x = nullptr;
+    int64_t x_stride = 0;
+    const int32_t *x_rows = nullptr; // device
+    const float *norm_w = nullptr;
+    float eps = 0.f;
+    float *xn_out = nullptr; // optional: normalised rows [n_tok][K]
+    int64_t K = 0;
+    int fmt = 0; // ActFmt of every job's weights
+    int n_jobs = 0;
+    FusedJob job[3];
+    int epi = EPI_PLAIN;
+    float *out = nullptr; // plain/swiglu: [n_tok][out_stride]; qkv: q rows
+    int64_t out_stride = 0;
+    const float *residual = nullptr;
+    int64_t res_stride = 0;
+    // EPI_QKV
+    const int32_t *pos = nullptr, *slot = nullptr; // device
+    const float *rope_table = nullptr;
+    KVLayout kv{};
+    int hd = 0;
+    // filled by the launcher
+    int64_t xrb = 0;
+    int n_tasks = 0;
+};
+void launch_fused_gemv(FusedGemv a, int n_tok, cudaStream_t s);
+
 // --- sampling -------------------------------------------------------------------------------------------
 // out[r] = first argmax of row r.  If feed_tok/feed_pos are given (device-side decode loop) the sampled id is also
 // written to feed_tok[r] and feed_pos[r] is incremented, so the next step needs no host round trip.

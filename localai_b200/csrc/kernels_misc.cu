@@ -1,6 +1,7 @@
 // kernels_misc.cu -- RMSNorm, SwiGLU, RoPE + paged-KV store, paged-KV attention, argmax.
 // Numerics follow the ggml CPU operators the reference executes (see oracle/ggml_ref.c for the restatement):
 // f32 everywhere, F16 KV cache, q and the soft-max probabilities rounded to f16 before their dot products.
+#include "attention.cuh"
 #include "kernels.h"
 #include "quant.cuh"
 
@@ -101,90 +102,27 @@ void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos
 }
 
 // ------------------------------------------------------------------------------------------ attention (paged KV)
-// One CTA per (head, token).  Two passes so that the probabilities can be normalised and rounded to f16 before
-// the P.V product exactly as ggml's mul_mat(v_f16, soft_max(kq)) does.
-constexpr int ATT_THREADS = 128;
-
+// One CTA per (head, token).  Two passes so that the probabilities can be normalised and rounded to f16 before the
+// P.V product exactly as ggml's mul_mat(v_f16, soft_max(kq)) does.
+//   pass 1: ONE LANE PER KV POSITION -- the lane streams the whole K row (hd halves, 16-byte loads, all independent)
+//           and accumulates q.k in index order; no shuffles, hd/8 loads in flight per lane
+//   pass 2: a warp reads a whole V row coalesced (lane owns hd/32 dims), warps split the positions 4 at a time,
+//           partial outputs are combined across warps in a fixed order (deterministic)
+// HBM/L2-bound: 2 x n_kv x hd x 2 B per head.  (see attention.cuh: also used by the decode mega-kernel)
 __global__ void __launch_bounds__(ATT_THREADS)
 attention_kernel(const float *__restrict__ q, const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head,
                  int n_head_kv, int hd, KVLayout kv, float *__restrict__ out, float scale) {
     extern __shared__ __align__(16) float smem[];
     const int h = blockIdx.x, t = blockIdx.y;
-    const int n_kv = pos[t] + 1;
-    const int sl = slot[t];
-    const int hk = h / (n_head / n_head_kv);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float *qs = smem;                 // [hd] q rounded to f16
-    float *red = smem + hd;           // [ATT_THREADS] reduction scratch
-    float *sc = smem + hd + ATT_THREADS; // [n_kv] scores / probabilities
-    const int32_t *pt = kv.page_table + (int64_t)sl * kv.max_pages;
-    const float *qt = q + ((int64_t)t * n_head + h) * hd;
-    for (int i = threadIdx.x; i < hd; i += blockDim.x) qs[i] = __half2float(__float2half_rn(qt[i]));
-    __syncthreads();
-
-    // pass 1: scores
-    float lmax = -INFINITY;
-    for (int j = warp; j < n_kv; j += ATT_THREADS / 32) {
-        const __half *kr = kv.k_pool + ((int64_t)pt[j / kv.page_size] * kv.page_size + j % kv.page_size) * kv.kvd + hk * hd;
-        float a = 0.f;
-        for (int i = lane * 2; i < hd; i += 64) {
-            const float2 kk = __half22float2(*(const __half2 *)(kr + i));
-            a += kk.x * qs[i];
-            a += kk.y * qs[i + 1];
-        }
-        a = warp_sum(a) * scale;
-        if (lane == 0) sc[j] = a;
-        lmax = fmaxf(lmax, a);
-    }
-    red[threadIdx.x] = lmax;
-    __syncthreads();
-    float mx = -INFINITY;
-    for (int i = 0; i < ATT_THREADS; i += 32) mx = fmaxf(mx, red[i]); // lane-0 entries hold each warp's max (all lanes equal)
-    __syncthreads();
-    float lsum = 0.f;
-    for (int j = threadIdx.x; j < n_kv; j += blockDim.x) {
-        const float e = expf(sc[j] - mx);
-        sc[j] = e;
-        lsum += e;
-    }
-    lsum = warp_sum(lsum);
-    if (lane == 0) red[warp] = lsum;
-    __syncthreads();
-    double tot = 0.0;
-    for (int i = 0; i < ATT_THREADS / 32; i++) tot += (double)red[i];
-    const float inv = (float)(1.0 / tot);
-    __syncthreads();
-    for (int j = threadIdx.x; j < n_kv; j += blockDim.x) sc[j] = __half2float(__float2half_rn(__fmul_rn(sc[j], inv)));
-    __syncthreads();
-
-    // pass 2: out[i] = sum_j p_j * v_j[i]; thread groups of `hd` threads split the kv axis
-    const int ngroups = ATT_THREADS / hd > 0 ? ATT_THREADS / hd : 1;
-    for (int i0 = 0; i0 < hd; i0 += ATT_THREADS) {
-        const int i = i0 + (threadIdx.x % (hd < ATT_THREADS ? hd : ATT_THREADS));
-        const int g = hd < ATT_THREADS ? threadIdx.x / hd : 0;
-        float a = 0.f;
-        if (g < ngroups) {
-            for (int j = g; j < n_kv; j += ngroups) {
-                const __half *vr = kv.v_pool + ((int64_t)pt[j / kv.page_size] * kv.page_size + j % kv.page_size) * kv.kvd + hk * hd;
-                a += __half2float(vr[i]) * sc[j];
-            }
-        }
-        red[threadIdx.x] = a;
-        __syncthreads();
-        if (g == 0) {
-            for (int gg = 1; gg < ngroups; gg++) a += red[threadIdx.x + gg * hd];
-            out[((int64_t)t * n_head + h) * hd + i] = a;
-        }
-        __syncthreads();
-    }
+    attention_head(q + ((int64_t)t * n_head + h) * hd, pos[t] + 1, kv.page_table + (int64_t)slot[t] * kv.max_pages, kv,
+                   h / (n_head / n_head_kv), hd, scale, out + ((int64_t)t * n_head + h) * hd, smem, threadIdx.x, ATT_THREADS);
 }
 
 void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv, int hd,
                       const KVLayout &kv, float *out, int max_ctx, cudaStream_t s) {
     if (n_tok <= 0) return;
-    B2_CHECK(hd % 2 == 0 && (hd >= ATT_THREADS ? hd % ATT_THREADS == 0 : ATT_THREADS % hd == 0), B2_EUNSUPPORTED,
-             "attention: unsupported head_dim");
-    const size_t smem = sizeof(float) * ((size_t)hd + ATT_THREADS + max_ctx);
+    B2_CHECK(hd % 32 == 0 && hd <= 256, B2_EUNSUPPORTED, "attention: head_dim must be a multiple of 32, at most 256");
+    const size_t smem = attention_smem_bytes(hd, max_ctx, ATT_THREADS);
     B2_CHECK(smem <= 220 * 1024, B2_EUNSUPPORTED, "attention: context too long for the two-pass kernel");
     static thread_local size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {

@@ -6,6 +6,7 @@
 #include "sampling.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace b2 {
@@ -61,6 +62,8 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     B2_CHECK(prop.major == 10, B2_ENODEV,
              std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) + "; this library is built for sm_100a only");
     B2_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    unfused_ = getenv("B200LLM_UNFUSED") && atoi(getenv("B200LLM_UNFUSED")) != 0;
+    no_graph_ = getenv("B200LLM_NO_GRAPH") && atoi(getenv("B200LLM_NO_GRAPH")) != 0;
 
     hp.arch = f.get_s("general.architecture", "");
     B2_CHECK(hp.arch == "llama", B2_EUNSUPPORTED, "unsupported architecture '" + hp.arch + "' (only llama-family GGUF)");
@@ -183,11 +186,15 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     xn_out_ = (float *)dalloc(nb * d * 4);
     sample_specs_ = (SampleSpec *)dalloc(nb * sizeof(SampleSpec));
     ensure_logits_rows(std::max(n_parallel, 1));
+    decode_graphs_.assign((size_t)std::min(n_parallel, 64) + 1, nullptr);
+    decode_graph_launches_.assign(decode_graphs_.size(), 0);
 }
 
 Model::~Model() {
     cudaSetDevice(device);
     if (stream) cudaStreamSynchronize(stream);
+    for (auto g : decode_graphs_)
+        if (g) cudaGraphExecDestroy(g);
     for (void *p : allocs_) cudaFree(p);
     if (logits_) cudaFree(logits_);
     if (staging_) cudaFree(staging_);
@@ -201,6 +208,10 @@ void Model::ensure_logits_rows(int n) {
     logits_ = nullptr;
     B2_CUDA(cudaMalloc((void **)&logits_, (size_t)n * hp.n_vocab * 4));
     logits_rows_cap_ = n;
+    for (auto &g : decode_graphs_) { // captured graphs hold the old logits pointer
+        if (g) cudaGraphExecDestroy(g);
+        g = nullptr;
+    }
 }
 
 SampleSpec *Model::sample_specs_dev(int n) {
@@ -239,43 +250,129 @@ void Model::matmul(const DTensor &W, const float *x, int64_t x_stride, int n, fl
 static inline void invalidate(bool (&v)[4]) { v[0] = v[1] = v[2] = v[3] = false; }
 void Model::invalidate_acts() { invalidate(actq_valid_); }
 
-void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
+static FusedJob job_of(const DTensor &W) { return FusedJob{W.data, W.type, W.rows, W.row_stride}; }
+
+// The original, one-op-per-kernel path.  Kept for layers whose matrices need different activation formats (the
+// fused kernel quantises the activation row once) and as the cross-check of the fused path in the tests
+// (B200LLM_UNFUSED=1).
+void Model::run_layer_unfused(const LayerW &L, const KVLayout &kv, int n) {
     const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hd;
+    launch_rmsnorm(x_, d, nullptr, (const float *)L.attn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
+    invalidate(actq_valid_);
+    matmul(L.wq, xn_, d, n, q_, d, nullptr, 0);
+    matmul(L.wk, xn_, d, n, k_, kvd, nullptr, 0);
+    matmul(L.wv, xn_, d, n, v_, kvd, nullptr, 0);
+    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+    launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+    invalidate(actq_valid_);
+    matmul(L.wo, att_, d, n, x_, d, x_, d); // x = x + wo.att
+    launch_rmsnorm(x_, d, nullptr, (const float *)L.ffn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
+    invalidate(actq_valid_);
+    matmul(L.up, xn_, d, n, up_, ff, nullptr, 0);
+    matmul(L.gate, xn_, d, n, gate_, ff, nullptr, 0);
+    launch_swiglu(gate_, up_, gate_, (int64_t)n * ff, stream);
+    invalidate(actq_valid_);
+    matmul(L.down, gate_, ff, n, x_, d, x_, d); // x = x + down.act
+}
+
+// 5 launches per layer: [norm+quant+QKV+RoPE+KV-store] [attention] [quant+wo+residual] [norm+quant+gate/up+SwiGLU]
+// [quant+down+residual]
+void Model::run_layer_fused(const LayerW &L, const KVLayout &kv, int n) {
+    const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim;
+    FusedGemv a;
+    a.x = x_; a.x_stride = d; a.norm_w = (const float *)L.attn_norm.data; a.eps = hp.rms_eps; a.K = d;
+    a.fmt = act_format_for(L.wq.type);
+    a.n_jobs = 3; a.job[0] = job_of(L.wq); a.job[1] = job_of(L.wk); a.job[2] = job_of(L.wv);
+    a.epi = EPI_QKV; a.out = q_; a.out_stride = d; a.pos = pos_; a.slot = slot_; a.rope_table = rope_table_; a.kv = kv; a.hd = hd;
+    launch_fused_gemv(a, n, stream);
+    launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+    FusedGemv o;
+    o.x = att_; o.x_stride = d; o.K = d; o.fmt = act_format_for(L.wo.type);
+    o.n_jobs = 1; o.job[0] = job_of(L.wo); o.epi = EPI_PLAIN; o.out = x_; o.out_stride = d; o.residual = x_; o.res_stride = d;
+    launch_fused_gemv(o, n, stream);
+    FusedGemv g;
+    g.x = x_; g.x_stride = d; g.norm_w = (const float *)L.ffn_norm.data; g.eps = hp.rms_eps; g.K = d;
+    g.fmt = act_format_for(L.gate.type);
+    g.n_jobs = 2; g.job[0] = job_of(L.gate); g.job[1] = job_of(L.up); g.epi = EPI_SWIGLU; g.out = gate_; g.out_stride = ff;
+    launch_fused_gemv(g, n, stream);
+    FusedGemv w;
+    w.x = gate_; w.x_stride = ff; w.K = ff; w.fmt = act_format_for(L.down.type);
+    w.n_jobs = 1; w.job[0] = job_of(L.down); w.epi = EPI_PLAIN; w.out = x_; w.out_stride = d; w.residual = x_; w.res_stride = d;
+    launch_fused_gemv(w, n, stream);
+}
+
+static bool layer_fusable(const LayerW &L) {
+    const ActFmt f = act_format_for(L.wq.type);
+    return f != ACT_F32 && act_format_for(L.wk.type) == f && act_format_for(L.wv.type) == f && L.gate.type == L.up.type &&
+           act_format_for(L.gate.type) != ACT_F32 && act_format_for(L.wo.type) != ACT_F32 && act_format_for(L.down.type) != ACT_F32 &&
+           L.wq.rows % 2 == 0 && L.wk.rows % 2 == 0 && L.wv.rows % 2 == 0;
+}
+
+void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
+    const int d = hp.n_embd, hd = hp.head_dim, kvd = hp.n_head_kv * hd;
     launch_dequant_rows(tok_embd, tok_, 0, n, x_, d, stream); // get_rows(tok_embd)
     for (int l = 0; l < hp.n_layer; l++) {
         const LayerW &L = layers[l];
         KVLayout kv{k_pool_ + (size_t)l * pool_layer_stride_, v_pool_ + (size_t)l * pool_layer_stride_, page_table_, page_size,
                     max_pages, kvd};
-        launch_rmsnorm(x_, d, nullptr, (const float *)L.attn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
-        invalidate(actq_valid_);
-        matmul(L.wq, xn_, d, n, q_, d, nullptr, 0);
-        matmul(L.wk, xn_, d, n, k_, kvd, nullptr, 0);
-        matmul(L.wv, xn_, d, n, v_, kvd, nullptr, 0);
-        launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
-        launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
-        invalidate(actq_valid_);
-        matmul(L.wo, att_, d, n, x_, d, x_, d); // x = x + wo.att
-        launch_rmsnorm(x_, d, nullptr, (const float *)L.ffn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
-        invalidate(actq_valid_);
-        matmul(L.up, xn_, d, n, up_, ff, nullptr, 0);
-        matmul(L.gate, xn_, d, n, gate_, ff, nullptr, 0);
-        launch_swiglu(gate_, up_, gate_, (int64_t)n * ff, stream);
-        invalidate(actq_valid_);
-        matmul(L.down, gate_, ff, n, x_, d, x_, d); // x = x + down.act
+        if (!unfused_ && n <= 4 && layer_fusable(L)) run_layer_fused(L, kv, n); // larger batches: quantise once, not per CTA
+        else run_layer_unfused(L, kv, n);
         if (dbg_hidden_)
             B2_CUDA(cudaMemcpyAsync(dbg_hidden_ + (size_t)l * d, x_ + (size_t)(n - 1) * d, d * 4, cudaMemcpyDeviceToDevice, stream));
     }
     if (n_out != 0) {
         const int rows = n_out < 0 ? n : n_out;
         ensure_logits_rows(rows);
-        launch_rmsnorm(x_, d, n_out < 0 ? nullptr : out_rows_dev, (const float *)output_norm.data, xn_out_, d, rows, d, hp.rms_eps,
-                       stream);
+        if (!unfused_ && rows <= 4 && act_format_for(output.type) != ACT_F32) {
+            FusedGemv a;
+            a.x = x_; a.x_stride = d; a.x_rows = n_out < 0 ? nullptr : out_rows_dev;
+            a.norm_w = (const float *)output_norm.data; a.eps = hp.rms_eps; a.xn_out = xn_out_; a.K = d;
+            a.fmt = act_format_for(output.type);
+            a.n_jobs = 1; a.job[0] = job_of(output); a.epi = EPI_PLAIN; a.out = logits_; a.out_stride = hp.n_vocab;
+            launch_fused_gemv(a, rows, stream);
+        } else {
+            launch_rmsnorm(x_, d, n_out < 0 ? nullptr : out_rows_dev, (const float *)output_norm.data, xn_out_, d, rows, d, hp.rms_eps,
+                           stream);
+            invalidate(actq_valid_);
+            matmul(output, xn_out_, d, rows, logits_, hp.n_vocab, nullptr, 0);
+        }
         if (dbg_hidden_)
             B2_CUDA(cudaMemcpyAsync(dbg_hidden_ + (size_t)hp.n_layer * d, xn_out_ + (size_t)(rows - 1) * d, d * 4,
                                     cudaMemcpyDeviceToDevice, stream));
-        invalidate(actq_valid_);
-        matmul(output, xn_out_, d, rows, logits_, hp.n_vocab, nullptr, 0);
     }
+}
+
+// Decode step for `n` sequences whose inputs are in the device buffers, replayed from a captured CUDA graph
+// (one graph per batch size; ~165 kernel launches collapse into one cudaGraphLaunch).
+void Model::run_decode_graphed(int n) {
+    if (no_graph_ || dbg_hidden_ || n > (int)decode_graphs_.size() - 1) {
+        run_graph(n, nullptr, -1);
+        return;
+    }
+    if (!decode_graphs_[n]) {
+        ensure_logits_rows(std::max(n, n_parallel));
+        run_graph(n, nullptr, -1); // warm-up outside capture: sets function attributes, validates shapes
+        B2_CUDA(cudaStreamSynchronize(stream));
+        cudaGraph_t g = nullptr;
+        const int64_t lc = g_launch_count;
+        B2_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+        try {
+            run_graph(n, nullptr, -1);
+        } catch (...) {
+            cudaStreamEndCapture(stream, &g);
+            if (g) cudaGraphDestroy(g);
+            throw;
+        }
+        B2_CUDA(cudaStreamEndCapture(stream, &g));
+        decode_graph_launches_[n] = g_launch_count - lc;
+        g_launch_count = lc;
+        cudaGraphExec_t ge = nullptr;
+        B2_CUDA(cudaGraphInstantiate(&ge, g, 0));
+        cudaGraphDestroy(g);
+        decode_graphs_[n] = ge;
+    }
+    B2_CUDA(cudaGraphLaunch(decode_graphs_[n], stream));
+    g_launch_count += decode_graph_launches_[n];
 }
 
 void Model::forward(const Batch &b) {
@@ -290,6 +387,12 @@ void Model::forward(const Batch &b) {
     B2_CUDA(cudaMemcpyAsync(pos_, b.pos, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaMemcpyAsync(slot_, b.slot, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
     int n_out = b.n_out;
+    bool pure_decode = n_out == b.n && b.n < (int)decode_graphs_.size(); // every row wants logits, in order
+    for (int i = 0; pure_decode && i < n_out; i++) pure_decode = b.out_rows[i] == i;
+    if (pure_decode) {
+        run_decode_graphed(b.n);
+        return;
+    }
     if (n_out > 0) B2_CUDA(cudaMemcpyAsync(out_rows_, b.out_rows, (size_t)n_out * 4, cudaMemcpyHostToDevice, stream));
     run_graph(b.n, out_rows_, n_out);
 }
@@ -303,7 +406,7 @@ void Model::set_device_inputs(const int32_t *tokens, const int32_t *pos, const i
 
 void Model::forward_device_inputs(int n) {
     B2_CUDA(cudaSetDevice(device));
-    run_graph(n, nullptr, -1);
+    run_decode_graphed(n);
 }
 
 void Model::sample_greedy(int n_rows, bool feed) {

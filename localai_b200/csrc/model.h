@@ -76,6 +76,12 @@ class Model {
     void matmul(const DTensor &W, const float *x, int64_t x_stride, int n, float *out, int64_t out_stride,
                 const float *residual, int64_t res_stride);
     void run_graph(int n, const int32_t *out_rows_dev, int n_out);
+    void run_layer_unfused(const LayerW &L, const KVLayout &kv, int n);
+    void run_layer_fused(const LayerW &L, const KVLayout &kv, int n);
+    void run_decode_graphed(int n);
+    bool unfused_ = false, no_graph_ = false;
+    std::vector<cudaGraphExec_t> decode_graphs_;
+    std::vector<int64_t> decode_graph_launches_;
 
     std::vector<void *> allocs_;
     uint8_t *staging_ = nullptr;
