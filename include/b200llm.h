@@ -212,7 +212,9 @@ int b2_bench_gemv(b2_engine *e, int which, int n_tok, int n_rounds, double *ms_p
  *   `wtype` (Q8_0 -> Q8_0 blocks, K-quants -> Q8_K blocks, F16 -> f16); out receives the blocks in
  *   ggml's AoS layout (block_q8_0 34 B / block_q8_K 292 B) so they can be compared byte for byte.
  * b2_mul_mat: out[t][r] = dot(W[r,:], quantise(x[t,:])), W = rows x cols of `wtype`, x = n_tok x cols f32.
- *   path: 0 = auto, 1 = streaming dequant-GEMV (decode path), 2 = tensor-core GEMM (prefill path).
+ *   path: 0 = auto, 1 = streaming dequant-GEMV (one op per kernel), 2 = tensor-core GEMM (prefill path),
+ *         3 = fused decode kernel (quantises in its prologue), 5 = fused decode kernel on pre-quantised rows,
+ *         4 = persistent decode mega-kernel with a single mat-vec phase (n_tok = 1, even rows).
  */
 int b2_dequantize(int type, const void *blocks, int64_t n_elems, float *out);
 int b2_quantize_act(int wtype, const float *x, int64_t n_elems, void *out, size_t out_cap);

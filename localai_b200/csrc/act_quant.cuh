@@ -1,10 +1,24 @@
 // act_quant.cuh -- warp-level activation quantisation of one 256-element block (lane l owns elements 8l..8l+7),
 // bit-exact with ggml's quantize_row_q8_K_ref / quantize_row_q8_0_ref.  `row` is the destination activation row in
 // the SoA layout of common.h (global or shared memory), `b` the 256-element block index inside it.
+//
+// SWZ: the int8 section of a row that lives in SHARED memory for the mat-vec kernels is stored with its 16-byte
+// chunks permuted (act_swz) so that the kernels' stride-64-byte reads are bank-conflict free.  Global-memory rows
+// (and the values themselves) are never swizzled.
 #pragma once
 #include "quant.cuh"
 
 namespace b2 {
+
+// chunk c (16 bytes) of the int8 section -> physical chunk; G = 64-byte group, k = chunk inside the group
+__host__ __device__ __forceinline__ int act_swz(int c) { return (c & ~3) | ((c & 3) ^ ((c >> 3) & 3)); }
+
+template <bool SWZ>
+__device__ __forceinline__ int8_t *act_q8_ptr(uint8_t *row, int64_t off) { // off: byte offset, multiple of 8
+    if (!SWZ) return (int8_t *)row + off;
+    const int c = (int)(off >> 4);
+    return (int8_t *)row + ((int64_t)act_swz(c) << 4) + (off & 15);
+}
 
 __device__ __forceinline__ void store_q8x8(int8_t *dst, const int (&q)[8]) {
     int2 packed;
@@ -14,6 +28,7 @@ __device__ __forceinline__ void store_q8x8(int8_t *dst, const int (&q)[8]) {
 }
 
 // Q8_K: [qs: K x int8][d: K/256 x f32][bsums: K/16 x int16]
+template <bool SWZ>
 __device__ __forceinline__ void quant_block_q8_K(const float (&v)[8], int lane, uint8_t *row, int64_t K, int64_t b) {
     const int64_t nb = K / 256;
     // first element (in index order) with the largest |x|
@@ -31,7 +46,7 @@ __device__ __forceinline__ void quant_block_q8_K(const float (&v)[8], int lane, 
         const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
         if (oa > amax || (oa == amax && oi < idx)) { amax = oa; mx = om; idx = oi; }
     }
-    int8_t *qs = (int8_t *)row + b * 256 + lane * 8;
+    int8_t *qs = act_q8_ptr<SWZ>(row, b * 256 + lane * 8);
     float *dptr = (float *)(row + K) + b;
     int16_t *bs = (int16_t *)(row + K + nb * 4) + b * 16;
     if (amax == 0.f) {
@@ -57,6 +72,7 @@ __device__ __forceinline__ void quant_block_q8_K(const float (&v)[8], int lane, 
 }
 
 // Q8_0: [qs: K x int8][d: K/32 x f32 (value of the fp16-rounded scale)]; a 32-element block = 4 lanes
+template <bool SWZ>
 __device__ __forceinline__ void quant_block_q8_0(const float (&v)[8], int lane, uint8_t *row, int64_t K, int64_t b) {
     float amax = 0.f;
 #pragma unroll
@@ -68,7 +84,7 @@ __device__ __forceinline__ void quant_block_q8_0(const float (&v)[8], int lane, 
     int q[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) q[i] = (int)roundf(__fmul_rn(v[i], id));
-    store_q8x8((int8_t *)row + b * 256 + lane * 8, q);
+    store_q8x8(act_q8_ptr<SWZ>(row, b * 256 + lane * 8), q);
     if ((lane & 3) == 0) ((float *)(row + K))[b * 8 + (lane >> 2)] = __half2float(__float2half_rn(d));
 }
 
@@ -86,9 +102,10 @@ __device__ __forceinline__ void quant_block_f32(const float (&v)[8], int lane, u
 }
 
 // fmt: ActFmt value (common.h)
+template <bool SWZ>
 __device__ __forceinline__ void quant_block(int fmt, const float (&v)[8], int lane, uint8_t *row, int64_t K, int64_t b) {
-    if (fmt == 3) quant_block_q8_K(v, lane, row, K, b);
-    else if (fmt == 2) quant_block_q8_0(v, lane, row, K, b);
+    if (fmt == 3) quant_block_q8_K<SWZ>(v, lane, row, K, b);
+    else if (fmt == 2) quant_block_q8_0<SWZ>(v, lane, row, K, b);
     else if (fmt == 1) quant_block_f16(v, lane, row, b);
     else quant_block_f32(v, lane, row, b);
 }

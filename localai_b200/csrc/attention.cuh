@@ -26,7 +26,7 @@ __device__ __forceinline__ void attention_head(const float *__restrict__ qrow, i
     float *sc = part + (size_t)nwarps * hd; // [n_kv]
     int *pbase = (int *)(sc + ((n_kv + 3) & ~3)); // page index per 32-position page
     const int n_pages = (n_kv + kv.page_size - 1) / kv.page_size;
-    for (int i = tid; i < hd; i += nthreads) qs[i] = __half2float(__float2half_rn(qrow[i]));
+    for (int i = tid; i < hd; i += nthreads) qs[i] = __half2float(__float2half_rn(__ldcg(qrow + i))); // L2: q may come from another SM
     for (int i = tid; i < n_pages; i += nthreads) pbase[i] = pt[i];
     att_sync(nthreads);
 
@@ -107,7 +107,9 @@ __device__ __forceinline__ void attention_head(const float *__restrict__ qrow, i
             }
         }
     }
-    for (int i = 0; i < dpl; i++) part[(size_t)warp * hd + lane * dpl + i] = acc[i];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+        if (i < dpl) part[(size_t)warp * hd + lane * dpl + i] = acc[i];
     att_sync(nthreads);
     for (int i = tid; i < hd; i += nthreads) {
         float a = 0.f;

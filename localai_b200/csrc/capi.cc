@@ -193,6 +193,13 @@ int b2_bench_decode(b2_engine *e, int batch, int ctx_len, int n_steps, int n_war
     B2_API_END(0)
 }
 
+// undocumented profiling hook (not part of the ABI header): per-CTA, per-phase clock64 stamps of the decode mega-kernel
+int b2_mega_debug(b2_engine *e, long long *out, int cap) {
+    B2_API_BEGIN
+    return E(e)->mega_debug(out, cap);
+    B2_API_END(0)
+}
+
 int b2_bench_gemv(b2_engine *e, int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch,
                   int *ggml_type) {
     B2_API_BEGIN
@@ -272,7 +279,7 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     require_device();
     B2_CHECK(type_block_elems(wtype) > 0, B2_EUNSUPPORTED, "unsupported ggml type");
     B2_CHECK(rows > 0 && cols > 0 && n_tok > 0 && cols % 256 == 0, B2_EINVAL, "bad shape (cols must be a multiple of 256)");
-    B2_CHECK(path == 0 || path == 1, B2_EUNSUPPORTED, "tensor-core GEMM path not built yet");
+    B2_CHECK(path >= 0 && path <= 5, B2_EUNSUPPORTED, "unknown mat-mul path");
     DevBuf staging((size_t)(rows * gguf_row_bytes(wtype, cols))), dst((size_t)(rows * device_row_stride(wtype, cols)));
     DTensor W = upload_matrix(wtype, blocks, rows, cols, staging, dst);
     const ActFmt f = act_format_for(wtype);
@@ -282,7 +289,40 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     const uint8_t *xq = dq.as<uint8_t>();
     if (f == ACT_F32) xq = dx.as<uint8_t>();
     else launch_quantize_act(f, dx.as<float>(), cols, n_tok, cols, dq.as<uint8_t>(), 0);
-    launch_gemv(W, xq, f, n_tok, dout.as<float>(), rows, nullptr, 0, 0);
+    if (path == 2) { // tensor-core GEMM (bf16 operands, fp32 accumulate)
+        DevBuf wt(gemm_w_tiles_bytes(rows, cols)), xt(gemm_x_tiles_bytes(n_tok, cols));
+        launch_gemm_prepare_x(dx.as<float>(), cols, n_tok, cols, xt.p, 0);
+        launch_gemm_tc(W, xt.p, n_tok, dout.as<float>(), rows, nullptr, 0, wt.p, 0);
+        B2_CUDA(cudaDeviceSynchronize());
+    } else if (path == 3 || path == 5) { // fused decode kernel: 3 = quantise in the prologue, 5 = pre-quantised rows
+        FusedGemv a;
+        if (path == 3) { a.x = dx.as<float>(); a.x_stride = cols; }
+        else a.xq_pre = xq;
+        a.K = cols; a.fmt = f; a.n_jobs = 1;
+        a.job[0] = FusedJob{W.data, W.type, W.rows, W.row_stride};
+        a.epi = EPI_PLAIN; a.out = dout.as<float>(); a.out_stride = rows;
+        launch_fused_gemv(a, n_tok, 0);
+    } else if (path == 4) { // persistent decode kernel with a single mat-vec phase
+        B2_CHECK(n_tok == 1 && rows % 2 == 0, B2_EINVAL, "mega path: one activation row, even row count");
+        MegaPhase ph;
+        ph.kind = PH_PLAIN; ph.K = cols; ph.fmt = f; ph.n_jobs = 1;
+        ph.job[0] = FusedJob{W.data, W.type, W.rows, W.row_stride};
+        ph.x = dx.as<float>(); ph.out = dout.as<float>(); ph.units = (int)(rows / 2);
+        B2_CHECK(mega_phase_supported(ph), B2_EUNSUPPORTED, "mega path: shape/type not supported");
+        DevBuf dph(sizeof(MegaPhase)), dbar(64), dps(64);
+        B2_CUDA(cudaMemcpy(dph.p, &ph, sizeof(ph), cudaMemcpyHostToDevice));
+        B2_CUDA(cudaMemset(dbar.p, 0, 64));
+        B2_CUDA(cudaMemset(dps.p, 0, 64));
+        MegaArgs a;
+        a.phases = dph.as<MegaPhase>(); a.n_phases = 1; a.pos = dps.as<int32_t>(); a.slot = dps.as<int32_t>() + 4;
+        a.bar = dbar.as<unsigned>(); a.page_size = 32; a.max_pages = 1; a.hd = 64; a.n_head = 1; a.n_head_kv = 1;
+        int n_sm = 0;
+        B2_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0));
+        launch_decode_mega(a, n_sm, 0);
+        B2_CUDA(cudaDeviceSynchronize());
+    } else {
+        launch_gemv(W, xq, f, n_tok, dout.as<float>(), rows, nullptr, 0, 0);
+    }
     B2_CUDA(cudaMemcpy(out, dout.p, (size_t)n_tok * rows * 4, cudaMemcpyDeviceToHost));
     return 0;
     B2_API_END(0)

@@ -238,6 +238,18 @@ int Engine::bench_decode(int batch, int ctx_len, int n_steps, int n_warmup, doub
     return 0;
 }
 
+int Engine::mega_debug(long long *out, int cap) {
+    Model &m = model();
+    std::lock_guard<std::mutex> lk(dev_mu_);
+    const int n = m.n_sm() * m.mega_n_phases() * 8;
+    if (!m.mega_dbg()) return 0;
+    if (!out) return n;
+    B2_CHECK(cap >= n, B2_ENOSPC, "mega_debug: buffer too small");
+    m.sync();
+    B2_CUDA(cudaMemcpy(out, m.mega_dbg(), (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost));
+    return n;
+}
+
 int Engine::bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type) {
     Model &m = model();
     B2_CHECK(which >= 0 && which <= 7 && n_tok >= 1 && n_tok <= 4 && n_rounds > 0, B2_EINVAL, "bench_gemv: bad arguments");

@@ -37,6 +37,7 @@ class Engine {
                       double *decode_ms);
     int debug_hidden(float *out, int cap_floats);
     int bench_decode(int batch, int ctx_len, int n_steps, int n_warmup, double *ms_per_step, int64_t *launches);
+    int mega_debug(long long *out, int cap);
     int bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type);
     int bench_prefill(int n_tokens, int n_iters, int n_warmup, double *ms_per_iter, int64_t *launches);
 

@@ -82,6 +82,46 @@ struct FusedGemv {
 };
 void launch_fused_gemv(FusedGemv a, int n_tok, cudaStream_t s);
 
+// --- persistent decode mega-kernel (kernels_mega.cu) ------------------------------------------------------------
+enum { PH_QKV = 0, PH_ATT = 1, PH_PLAIN = 2, PH_SWIGLU = 3 };
+struct MegaPhase {
+    int kind = PH_PLAIN;
+    int64_t K = 0;
+    int fmt = 0;
+    int n_jobs = 0;
+    FusedJob job[3];
+    const float *x = nullptr;      // fp32 activation row (PH_ATT: q)
+    const float *norm_w = nullptr; // RMSNorm weights applied before quantisation (optional)
+    float *out = nullptr;          // PLAIN/SWIGLU: output row; QKV: q; ATT: attention output
+    const float *residual = nullptr;
+    float *xn_out = nullptr;       // optional: the normalised row (LM head -> embeddings)
+    __half *k_pool = nullptr, *v_pool = nullptr; // this layer's KV pools (QKV, ATT)
+    int units = 0;                 // row pairs (PLAIN/QKV) or rows (SWIGLU) split across the CTAs
+};
+struct MegaArgs {
+    const MegaPhase *phases = nullptr; // device
+    int n_phases = 0;
+    const int32_t *pos = nullptr, *slot = nullptr; // device, one sequence
+    const float *rope_table = nullptr;
+    const int32_t *page_table = nullptr;
+    int page_size = 0, max_pages = 0, kvd = 0, n_head = 0, n_head_kv = 0, hd = 0;
+    float eps = 0.f, att_scale = 0.f;
+    unsigned *bar = nullptr; // [count, generation], zero-initialised once
+    long long *dbg = nullptr; // optional [n_cta][n_phases][4] clock64 stamps: start, after prologue, after stages, after barrier
+};
+void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s);
+bool mega_phase_supported(const MegaPhase &ph);
+size_t mega_attention_ctx_limit(int hd);
+
+// --- tensor-core GEMM for prefill / batched decode (kernels_gemm.cu) ----------------------------------------------
+size_t gemm_w_tiles_bytes(int64_t rows, int64_t cols);
+size_t gemm_x_tiles_bytes(int n_tok, int64_t cols);
+// fp32 activations [n_tok][K] -> bf16 operand tiles (do once per activation, shared by several matrices)
+void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
+// out[t][r] = W[r] . x[t] (+ residual): dequantises W into w_tiles (scratch), then tcgen05/TMEM GEMM
+void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
+                    int64_t res_stride, void *w_tiles, cudaStream_t s);
+
 // --- sampling -------------------------------------------------------------------------------------------
 // out[r] = first argmax of row r.  If feed_tok/feed_pos are given (device-side decode loop) the sampled id is also
 // written to feed_tok[r] and feed_pos[r] is incremented, so the next step needs no host round trip.

@@ -1,0 +1,351 @@
+// kernels_gemm.cu -- prefill / batched-decode mat-mul on the 5th-generation tensor cores (tcgen05 + TMEM).
+//
+// out[M tokens][N rows] = X[M][K] . W[N][K]^T, a real dense contraction once M is in the tens or more.
+//   1. dequant_tiles_kernel   quantised W (GGUF blocks in HBM) -> bf16, written straight into the UMMA "core matrix"
+//                             tile layout (below), so that a whole 256 x 64 operand tile is ONE contiguous 32 KB chunk
+//   2. convert_x_tiles_kernel fp32 activations -> bf16 in the same layout (128 x 64 tiles, rows zero-padded)
+//   3. gemm_tcgen05_kernel    persistent, warp-specialised: warp 0 = producer (one cp.async.bulk per operand tile,
+//                             mbarrier ring of 4 stages), warp 1 = MMA issuer (one elected lane issues
+//                             tcgen05.mma.cta_group::1.kind::f16, 128 x 256 x 16, fp32 accumulators in TMEM, two
+//                             accumulator stages = 512 columns), warp 2 = TMEM allocator, warps 4..7 = epilogue
+//                             (tcgen05.ld 32x32b -> registers -> fp32 rows (+ residual) to global).
+// Tile layout (no swizzle, K-major): a tile of R rows x 64 k-elements is stored as 8x8 core matrices (8 rows x 16 B,
+// 128 B contiguous): byte offset = (r/8) * 1024 + (k/8) * 128 + (r%8) * 16 + (k%8) * 2.  The shared-memory matrix
+// descriptor therefore has LBO (K direction) = 128 B and SBO (row direction) = 1024 B, and one K = 16 MMA step
+// advances the start address by 256 B.  Because the tiles are laid out this way in global memory already, no TMA
+// tensor map is needed.
+// Tensor-bound: 2 M N K flops; roofline = MEASURED_PEAKS.json bf16 (1392 TF/s sustained).
+#include <cuda_bf16.h>
+
+#include "kernels.h"
+#include "quant.cuh"
+
+namespace b2 {
+
+constexpr int GM_BM = 128, GM_BN = 256, GM_BK = 64;
+constexpr int GM_STAGES = 4;
+constexpr int GM_A_BYTES = GM_BM * GM_BK * 2; // 16 KB
+constexpr int GM_B_BYTES = GM_BN * GM_BK * 2; // 32 KB
+constexpr int GM_STAGE_BYTES = GM_A_BYTES + GM_B_BYTES;
+constexpr int GM_THREADS = 256;
+constexpr size_t GM_SMEM = (size_t)GM_STAGES * GM_STAGE_BYTES + 1024;
+
+__host__ __device__ inline int64_t tile_elem_offset(int r, int k) { // element offset inside a tile (rows x 64)
+    return (int64_t)(r >> 3) * 512 + (k >> 3) * 64 + (r & 7) * 8 + (k & 7);
+}
+
+// ------------------------------------------------------------------------------------------------ operand preparation
+// one thread = 8 consecutive k of one row = one 16-byte core-matrix row
+__global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, int64_t rows, int64_t cols, int64_t row_stride,
+                                     __nv_bfloat16 *__restrict__ out, int64_t rows_pad) {
+    const int64_t kc_per_row = cols / 8;
+    const int64_t total = rows_pad * kc_per_row;
+    const int64_t k_tiles = cols / GM_BK;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / kc_per_row;
+        const int k0 = (int)(i % kc_per_row) * 8;
+        float v[8];
+        if (r >= rows) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = 0.f;
+        } else {
+            const uint8_t *row = W + r * row_stride;
+            if (type == B2_T_F32) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) v[j] = ((const float *)row)[k0 + j];
+            } else if (type == B2_T_F16) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) v[j] = h2f(((const uint16_t *)row)[k0 + j]);
+            } else if (type == B2_T_Q8_0) {
+                Q80Row q(row, cols);
+                const float d = h2f(q.d[k0 / 32]);
+#pragma unroll
+                for (int j = 0; j < 8; j++) v[j] = (float)q.qs[k0 + j] * d;
+            } else if (type == B2_T_Q4_K || type == B2_T_Q5_K) {
+                const int bb = type == B2_T_Q4_K ? 144 : 176;
+                const uint8_t *blk = row + (size_t)(k0 / 256) * bb;
+                const int e = k0 % 256, sb = e / 32, l0 = e % 32; // sub-block, offset inside it
+                const float d = h2f(*(const uint16_t *)blk), dmin = h2f(*(const uint16_t *)(blk + 2));
+                int sc, m;
+                get_scale_min_k4(sb, blk + 4, sc, m);
+                const float d1 = d * (float)sc, m1 = dmin * (float)m;
+                const uint8_t *qh = blk + 16;
+                const uint8_t *qs = blk + (type == B2_T_Q4_K ? 16 : 48) + (sb / 2) * 32 + l0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    int q = (sb & 1) ? (qs[j] >> 4) : (qs[j] & 0xF);
+                    if (type == B2_T_Q5_K) q += ((qh[l0 + j] >> sb) & 1) ? 16 : 0;
+                    v[j] = d1 * (float)q - m1;
+                }
+            } else { // Q6_K (device SoA layout)
+                const int nb = (int)(cols / 256);
+                Q6Row q(row, nb);
+                const int64_t ib = k0 / 256;
+                const int e = k0 % 256, n = e / 128, c = (e % 128) / 32, l0 = e % 32;
+                const float d = h2f(q.d[ib]);
+                const uint8_t *ql = q.ql + ib * 128 + 64 * n + ((c & 1) ? 32 : 0) + l0;
+                const uint8_t *qh = q.qh + ib * 64 + 32 * n + l0;
+                const float ds = d * (float)q.sc[ib * 16 + 8 * n + 2 * c + l0 / 16];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int lo = (c < 2) ? (ql[j] & 0xF) : (ql[j] >> 4);
+                    const int hi = (qh[j] >> (2 * c)) & 3;
+                    v[j] = ds * (float)((lo | (hi << 4)) - 32);
+                }
+            }
+        }
+        const int64_t nt = r / GM_BN, kt = k0 / GM_BK;
+        __nv_bfloat16 *dst = out + (nt * k_tiles + kt) * (int64_t)(GM_BN * GM_BK) + tile_elem_offset((int)(r % GM_BN), k0 % GM_BK);
+        __nv_bfloat162 p[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) p[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+        *(int4 *)dst = *(const int4 *)p;
+    }
+}
+
+__global__ void convert_x_tiles_kernel(const float *__restrict__ x, int64_t x_stride, int n_tok, int64_t cols,
+                                       __nv_bfloat16 *__restrict__ out, int64_t m_pad) {
+    const int64_t kc_per_row = cols / 8;
+    const int64_t total = m_pad * kc_per_row;
+    const int64_t k_tiles = cols / GM_BK;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / kc_per_row;
+        const int k0 = (int)(i % kc_per_row) * 8;
+        float4 a = make_float4(0, 0, 0, 0), b = a;
+        if (r < n_tok) {
+            a = *(const float4 *)(x + r * x_stride + k0);
+            b = *(const float4 *)(x + r * x_stride + k0 + 4);
+        }
+        const int64_t mt = r / GM_BM, kt = k0 / GM_BK;
+        __nv_bfloat16 *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
+        __nv_bfloat162 p[4] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w), __floats2bfloat162_rn(b.x, b.y),
+                               __floats2bfloat162_rn(b.z, b.w)};
+        *(int4 *)dst = *(const int4 *)p;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t gm_s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void gm_mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(gm_s32(bar)), "r"(count));
+}
+__device__ __forceinline__ void gm_mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(gm_s32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void gm_mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(gm_s32(bar)) : "memory");
+}
+__device__ __forceinline__ void gm_mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "GM_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra GM_DONE;\n"
+        "bra GM_WAIT;\n"
+        "GM_DONE:\n"
+        "}\n" ::"r"(gm_s32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void gm_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(gm_s32(dst)),
+                 "l"(src), "r"(bytes), "r"(gm_s32(bar))
+                 : "memory");
+}
+// K-major, no swizzle: LBO = 128 B between core matrices along K, SBO = 1024 B between 8-row groups
+__device__ __forceinline__ uint64_t gm_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t)((saddr & 0x3FFFF) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) | (1ull << 46);
+}
+__device__ __forceinline__ void gm_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void gm_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(gm_s32(bar)) : "memory");
+}
+__device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct GemmArgs {
+    const __nv_bfloat16 *a_tiles; // [m_tiles][k_tiles][128 x 64]
+    const __nv_bfloat16 *b_tiles; // [n_tiles][k_tiles][256 x 64]
+    float *out;
+    int64_t out_stride;
+    const float *residual;
+    int64_t res_stride;
+    int M, N, k_tiles, m_tiles, n_tiles;
+    uint32_t lbo, sbo;
+};
+
+// ------------------------------------------------------------------------------------------------ the GEMM
+__global__ void __launch_bounds__(GM_THREADS, 1)
+gemm_tcgen05_kernel(const GemmArgs g) {
+    extern __shared__ __align__(1024) uint8_t gsm[];
+    uint8_t *stages = gsm;
+    uint64_t *full = (uint64_t *)(gsm + (size_t)GM_STAGES * GM_STAGE_BYTES);
+    uint64_t *empty = full + GM_STAGES;
+    uint64_t *tfull = empty + GM_STAGES;   // [2] accumulator ready
+    uint64_t *tempty = tfull + 2;          // [2] accumulator drained
+    uint32_t *tmem_slot = (uint32_t *)(tempty + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full + i, 1); gm_mbar_init(empty + i, 1); }
+        for (int i = 0; i < 2; i++) { gm_mbar_init(tfull + i, 1); gm_mbar_init(tempty + i, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) { // TMEM: 512 columns = two 128 x 256 fp32 accumulators
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(gm_s32(tmem_slot)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+    const int n_tiles_total = g.m_tiles * g.n_tiles;
+    // kind::f16, D = f32, A = B = bf16, both K-major, N = 256, M = 128
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(GM_BN >> 3) << 17) | ((uint32_t)(GM_BM >> 4) << 24);
+
+    if (warp == 0) {
+        if (lane == 0) { // ===== producer: one bulk copy per operand tile
+            uint32_t it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
+                const int mt = tile % g.m_tiles, nt = tile / g.m_tiles;
+                for (int kt = 0; kt < g.k_tiles; kt++, it++) {
+                    const int s = it % GM_STAGES;
+                    gm_mbar_wait(empty + s, ((it / GM_STAGES) & 1) ^ 1);
+                    uint8_t *sa = stages + (size_t)s * GM_STAGE_BYTES;
+                    gm_mbar_expect_tx(full + s, GM_STAGE_BYTES);
+                    gm_bulk_g2s(sa, g.a_tiles + ((int64_t)mt * g.k_tiles + kt) * (GM_BM * GM_BK), GM_A_BYTES, full + s);
+                    gm_bulk_g2s(sa + GM_A_BYTES, g.b_tiles + ((int64_t)nt * g.k_tiles + kt) * (GM_BN * GM_BK), GM_B_BYTES, full + s);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) { // ===== MMA issuer
+            uint32_t it = 0, acc_it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
+                const int acc = acc_it & 1;
+                gm_mbar_wait(tempty + acc, ((acc_it >> 1) & 1) ^ 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t d_tmem = tmem_base + acc * GM_BN;
+                for (int kt = 0; kt < g.k_tiles; kt++, it++) {
+                    const int s = it % GM_STAGES;
+                    gm_mbar_wait(full + s, (it / GM_STAGES) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = gm_s32(stages + (size_t)s * GM_STAGE_BYTES), sb = sa + GM_A_BYTES;
+#pragma unroll
+                    for (int k4 = 0; k4 < GM_BK / 16; k4++) { // one MMA = K 16 = two core matrices = 256 B
+                        gm_mma(d_tmem, gm_desc(sa + k4 * 256, g.lbo, g.sbo), gm_desc(sb + k4 * 256, g.lbo, g.sbo), idesc,
+                               (kt | k4) != 0);
+                    }
+                    gm_commit(empty + s); // frees the smem stage when these MMAs have read it
+                }
+                gm_commit(tfull + acc);   // accumulator complete
+            }
+        }
+    } else if (warp >= 4) { // ===== epilogue: TMEM -> registers -> global
+        const int q = warp & 3; // TMEM lane quarter this warp may access
+        uint32_t acc_it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
+            const int mt = tile % g.m_tiles, nt = tile / g.m_tiles;
+            const int acc = acc_it & 1;
+            gm_mbar_wait(tfull + acc, (acc_it >> 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int row = mt * GM_BM + q * 32 + lane;
+            for (int c0 = 0; c0 < GM_BN; c0 += 32) {
+                uint32_t r[32];
+                gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
+                const int col = nt * GM_BN + c0;
+                if (row < g.M && col < g.N) {
+                    float *o = g.out + (int64_t)row * g.out_stride + col;
+                    const float *res = g.residual ? g.residual + (int64_t)row * g.res_stride + col : nullptr;
+                    if (col + 32 <= g.N) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                                   __uint_as_float(r[j + 3]));
+                            if (res) {
+                                const float4 rr = *(const float4 *)(res + j);
+                                v.x += rr.x; v.y += rr.y; v.z += rr.z; v.w += rr.w;
+                            }
+                            *(float4 *)(o + j) = v;
+                        }
+                    } else {
+                        for (int j = 0; j < 32 && col + j < g.N; j++) o[j] = __uint_as_float(r[j]) + (res ? res[j] : 0.f);
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) gm_mbar_arrive(tempty + acc);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+size_t gemm_w_tiles_bytes(int64_t rows, int64_t cols) { return (size_t)align_up(rows, GM_BN) * cols * 2; }
+size_t gemm_x_tiles_bytes(int n_tok, int64_t cols) { return (size_t)align_up(n_tok, GM_BM) * cols * 2; }
+
+void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t K, void *x_tiles, cudaStream_t s) {
+    B2_CHECK(K % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
+    const int64_t m_pad = align_up(n_tok, GM_BM);
+    const int64_t total = m_pad * (K / 8);
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+    convert_x_tiles_kernel<<<blocks, 256, 0, s>>>(x, x_stride, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
+                    int64_t res_stride, void *w_tiles, cudaStream_t s) {
+    B2_CHECK(W.cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
+    static thread_local bool configured = false;
+    static thread_local uint32_t lbo = 128, sbo = 1024;
+    if (!configured) {
+        B2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GM_SMEM));
+        if (getenv("B200LLM_UMMA_SWAP") && atoi(getenv("B200LLM_UMMA_SWAP"))) { lbo = 1024; sbo = 128; }
+        configured = true;
+    }
+    const int64_t rows_pad = align_up(W.rows, GM_BN);
+    {   // 1. quantised W -> bf16 tiles
+        const int64_t total = rows_pad * (W.cols / 8);
+        const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+        dequant_tiles_kernel<<<blocks, 256, 0, s>>>(W.data, W.type, W.rows, W.cols, W.row_stride, (__nv_bfloat16 *)w_tiles, rows_pad);
+        g_launch_count++;
+        B2_CUDA(cudaGetLastError());
+    }
+    GemmArgs g;
+    g.a_tiles = (const __nv_bfloat16 *)x_tiles;
+    g.b_tiles = (const __nv_bfloat16 *)w_tiles;
+    g.out = out; g.out_stride = out_stride; g.residual = residual; g.res_stride = res_stride;
+    g.M = n_tok; g.N = (int)W.rows; g.k_tiles = (int)(W.cols / GM_BK);
+    g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = (int)(rows_pad / GM_BN);
+    g.lbo = lbo; g.sbo = sbo;
+    const int grid = std::min(g.m_tiles * g.n_tiles, 148);
+    gemm_tcgen05_kernel<<<grid, GM_THREADS, GM_SMEM, s>>>(g);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+} // namespace b2

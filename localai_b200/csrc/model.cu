@@ -64,6 +64,9 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     B2_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     unfused_ = getenv("B200LLM_UNFUSED") && atoi(getenv("B200LLM_UNFUSED")) != 0;
     no_graph_ = getenv("B200LLM_NO_GRAPH") && atoi(getenv("B200LLM_NO_GRAPH")) != 0;
+    no_mega_ = getenv("B200LLM_NO_MEGA") && atoi(getenv("B200LLM_NO_MEGA")) != 0;
+    no_gemm_ = getenv("B200LLM_NO_GEMM") && atoi(getenv("B200LLM_NO_GEMM")) != 0;
+    if (getenv("B200LLM_GEMM_MIN_TOKENS")) gemm_min_tokens_ = atoi(getenv("B200LLM_GEMM_MIN_TOKENS"));
 
     hp.arch = f.get_s("general.architecture", "");
     B2_CHECK(hp.arch == "llama", B2_EUNSUPPORTED, "unsupported architecture '" + hp.arch + "' (only llama-family GGUF)");
@@ -186,6 +189,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     xn_out_ = (float *)dalloc(nb * d * 4);
     sample_specs_ = (SampleSpec *)dalloc(nb * sizeof(SampleSpec));
     ensure_logits_rows(std::max(n_parallel, 1));
+    build_mega();
     decode_graphs_.assign((size_t)std::min(n_parallel, 64) + 1, nullptr);
     decode_graph_launches_.assign(decode_graphs_.size(), 0);
 }
@@ -197,6 +201,8 @@ Model::~Model() {
         if (g) cudaGraphExecDestroy(g);
     for (void *p : allocs_) cudaFree(p);
     if (logits_) cudaFree(logits_);
+    if (gemm_w_) cudaFree(gemm_w_);
+    if (gemm_x_) cudaFree(gemm_x_);
     if (staging_) cudaFree(staging_);
     if (stream) cudaStreamDestroy(stream);
 }
@@ -208,6 +214,7 @@ void Model::ensure_logits_rows(int n) {
     logits_ = nullptr;
     B2_CUDA(cudaMalloc((void **)&logits_, (size_t)n * hp.n_vocab * 4));
     logits_rows_cap_ = n;
+    if (mega_phases_) build_mega(); // the LM-head phase holds the logits pointer
     for (auto &g : decode_graphs_) { // captured graphs hold the old logits pointer
         if (g) cudaGraphExecDestroy(g);
         g = nullptr;
@@ -301,6 +308,59 @@ void Model::run_layer_fused(const LayerW &L, const KVLayout &kv, int n) {
     launch_fused_gemv(w, n, stream);
 }
 
+void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
+    bool realloc = false;
+    if (w_bytes > gemm_w_bytes_) {
+        realloc = true;
+        B2_CUDA(cudaStreamSynchronize(stream));
+        if (gemm_w_) cudaFree(gemm_w_);
+        gemm_w_ = nullptr;
+        B2_CUDA(cudaMalloc(&gemm_w_, w_bytes));
+        gemm_w_bytes_ = w_bytes;
+    }
+    if (x_bytes > gemm_x_bytes_) {
+        B2_CUDA(cudaStreamSynchronize(stream));
+        if (gemm_x_) cudaFree(gemm_x_);
+        gemm_x_ = nullptr;
+        B2_CUDA(cudaMalloc(&gemm_x_, x_bytes));
+        gemm_x_bytes_ = x_bytes;
+        realloc = true;
+    }
+    if (realloc)
+        for (auto &g : decode_graphs_) { // captured graphs hold the old scratch pointers
+            if (g) cudaGraphExecDestroy(g);
+            g = nullptr;
+        }
+}
+
+void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride) {
+    ensure_gemm_scratch(gemm_w_tiles_bytes(W.rows, W.cols), 0);
+    launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, stream);
+}
+
+// Prefill / batched decode: every mat-mul is a tcgen05 tensor-core GEMM on bf16 operands (weights dequantised into
+// operand tiles on the fly); attention, norms and RoPE as in the other paths.
+void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
+    const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hd;
+    ensure_gemm_scratch(0, gemm_x_tiles_bytes(n, std::max(d, ff)));
+    launch_rmsnorm(x_, d, nullptr, (const float *)L.attn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
+    launch_gemm_prepare_x(xn_, d, n, d, gemm_x_, stream);
+    gemm(L.wq, n, q_, d, nullptr, 0);
+    gemm(L.wk, n, k_, kvd, nullptr, 0);
+    gemm(L.wv, n, v_, kvd, nullptr, 0);
+    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+    launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+    launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
+    gemm(L.wo, n, x_, d, x_, d);
+    launch_rmsnorm(x_, d, nullptr, (const float *)L.ffn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
+    launch_gemm_prepare_x(xn_, d, n, d, gemm_x_, stream);
+    gemm(L.gate, n, gate_, ff, nullptr, 0);
+    gemm(L.up, n, up_, ff, nullptr, 0);
+    launch_swiglu(gate_, up_, gate_, (int64_t)n * ff, stream);
+    launch_gemm_prepare_x(gate_, ff, n, ff, gemm_x_, stream);
+    gemm(L.down, n, x_, d, x_, d);
+}
+
 static bool layer_fusable(const LayerW &L) {
     const ActFmt f = act_format_for(L.wq.type);
     return f != ACT_F32 && act_format_for(L.wk.type) == f && act_format_for(L.wv.type) == f && L.gate.type == L.up.type &&
@@ -315,7 +375,8 @@ void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
         const LayerW &L = layers[l];
         KVLayout kv{k_pool_ + (size_t)l * pool_layer_stride_, v_pool_ + (size_t)l * pool_layer_stride_, page_table_, page_size,
                     max_pages, kvd};
-        if (!unfused_ && n <= 4 && layer_fusable(L)) run_layer_fused(L, kv, n); // larger batches: quantise once, not per CTA
+        if (!no_gemm_ && n > gemm_min_tokens_) run_layer_gemm(L, kv, n);
+        else if (!unfused_ && n <= 4 && layer_fusable(L)) run_layer_fused(L, kv, n); // larger batches: quantise once, not per CTA
         else run_layer_unfused(L, kv, n);
         if (dbg_hidden_)
             B2_CUDA(cudaMemcpyAsync(dbg_hidden_ + (size_t)l * d, x_ + (size_t)(n - 1) * d, d * 4, cudaMemcpyDeviceToDevice, stream));
@@ -323,7 +384,13 @@ void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
     if (n_out != 0) {
         const int rows = n_out < 0 ? n : n_out;
         ensure_logits_rows(rows);
-        if (!unfused_ && rows <= 4 && act_format_for(output.type) != ACT_F32) {
+        if (!no_gemm_ && rows > gemm_min_tokens_) {
+            launch_rmsnorm(x_, d, n_out < 0 ? nullptr : out_rows_dev, (const float *)output_norm.data, xn_out_, d, rows, d, hp.rms_eps,
+                           stream);
+            ensure_gemm_scratch(0, gemm_x_tiles_bytes(rows, d));
+            launch_gemm_prepare_x(xn_out_, d, rows, d, gemm_x_, stream);
+            gemm(output, rows, logits_, hp.n_vocab, nullptr, 0);
+        } else if (!unfused_ && rows <= 4 && act_format_for(output.type) != ACT_F32) {
             FusedGemv a;
             a.x = x_; a.x_stride = d; a.x_rows = n_out < 0 ? nullptr : out_rows_dev;
             a.norm_w = (const float *)output_norm.data; a.eps = hp.rms_eps; a.xn_out = xn_out_; a.K = d;
@@ -342,9 +409,84 @@ void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
     }
 }
 
+// Build the phase list of the persistent decode kernel (once): 5 phases per layer + the LM head.
+void Model::build_mega() {
+    mega_ready_ = false;
+    if (no_mega_ || unfused_) return;
+    const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim;
+    std::vector<MegaPhase> ph;
+    for (int l = 0; l < hp.n_layer; l++) {
+        const LayerW &L = layers[l];
+        __half *kp = k_pool_ + (size_t)l * pool_layer_stride_, *vp = v_pool_ + (size_t)l * pool_layer_stride_;
+        if (act_format_for(L.wq.type) != act_format_for(L.wk.type) || act_format_for(L.wq.type) != act_format_for(L.wv.type) ||
+            L.gate.type != L.up.type)
+            return;
+        MegaPhase q;
+        q.kind = PH_QKV; q.K = d; q.fmt = act_format_for(L.wq.type); q.n_jobs = 3;
+        q.job[0] = job_of(L.wq); q.job[1] = job_of(L.wk); q.job[2] = job_of(L.wv);
+        q.x = x_; q.norm_w = (const float *)L.attn_norm.data; q.out = q_; q.k_pool = kp; q.v_pool = vp;
+        q.units = (int)((L.wq.rows + L.wk.rows + L.wv.rows) / 2);
+        ph.push_back(q);
+        MegaPhase at;
+        at.kind = PH_ATT; at.x = q_; at.out = att_; at.k_pool = kp; at.v_pool = vp;
+        ph.push_back(at);
+        MegaPhase o;
+        o.kind = PH_PLAIN; o.K = d; o.fmt = act_format_for(L.wo.type); o.n_jobs = 1; o.job[0] = job_of(L.wo);
+        o.x = att_; o.out = x_; o.residual = x_; o.units = (int)(L.wo.rows / 2);
+        ph.push_back(o);
+        MegaPhase g;
+        g.kind = PH_SWIGLU; g.K = d; g.fmt = act_format_for(L.gate.type); g.n_jobs = 2; g.job[0] = job_of(L.gate); g.job[1] = job_of(L.up);
+        g.x = x_; g.norm_w = (const float *)L.ffn_norm.data; g.out = gate_; g.units = (int)L.gate.rows;
+        ph.push_back(g);
+        MegaPhase w;
+        w.kind = PH_PLAIN; w.K = ff; w.fmt = act_format_for(L.down.type); w.n_jobs = 1; w.job[0] = job_of(L.down);
+        w.x = gate_; w.out = x_; w.residual = x_; w.units = (int)(L.down.rows / 2);
+        ph.push_back(w);
+    }
+    MegaPhase h;
+    h.kind = PH_PLAIN; h.K = d; h.fmt = act_format_for(output.type); h.n_jobs = 1; h.job[0] = job_of(output);
+    h.x = x_; h.norm_w = (const float *)output_norm.data; h.out = logits_; h.xn_out = xn_out_; h.units = (int)(output.rows / 2);
+    ph.push_back(h);
+    for (auto &p : ph)
+        if (!mega_phase_supported(p)) return;
+    if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 32 != 0 || hd > 256) return;
+    if (!mega_phases_) mega_phases_ = (MegaPhase *)dalloc(ph.size() * sizeof(MegaPhase));
+    B2_CUDA(cudaMemcpyAsync(mega_phases_, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice, stream));
+    B2_CUDA(cudaStreamSynchronize(stream));
+    mega_n_phases_ = (int)ph.size();
+    if (!mega_bar_) {
+        mega_bar_ = (unsigned *)dalloc(64);
+        B2_CUDA(cudaMemsetAsync(mega_bar_, 0, 64, stream));
+    }
+    int coop = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
+    cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
+    mega_ready_ = coop != 0;
+    if (getenv("B200LLM_MEGA_DBG") && !mega_dbg_) mega_dbg_ = (long long *)dalloc((size_t)n_sm_ * mega_n_phases_ * 8 * sizeof(long long));
+}
+
+// Batch-1 decode step through the persistent kernel: [embedding gather] [mega] = 2 launches (+ sampling).
+void Model::run_decode_mega() {
+    const int d = hp.n_embd;
+    launch_dequant_rows(tok_embd, tok_, 0, 1, x_, d, stream);
+    MegaArgs a;
+    a.phases = mega_phases_; a.n_phases = mega_n_phases_;
+    a.pos = pos_; a.slot = slot_; a.rope_table = rope_table_; a.page_table = page_table_;
+    a.page_size = page_size; a.max_pages = max_pages; a.kvd = hp.n_head_kv * hp.head_dim;
+    a.n_head = hp.n_head; a.n_head_kv = hp.n_head_kv; a.hd = hp.head_dim;
+    a.eps = hp.rms_eps; a.att_scale = 1.0f / sqrtf((float)hp.head_dim);
+    a.bar = mega_bar_;
+    a.dbg = mega_dbg_;
+    launch_decode_mega(a, n_sm_, stream);
+}
+
 // Decode step for `n` sequences whose inputs are in the device buffers, replayed from a captured CUDA graph
 // (one graph per batch size; ~165 kernel launches collapse into one cudaGraphLaunch).
 void Model::run_decode_graphed(int n) {
+    if (n == 1 && mega_ready_ && !dbg_hidden_) {
+        run_decode_mega();
+        return;
+    }
     if (no_graph_ || dbg_hidden_ || n > (int)decode_graphs_.size() - 1) {
         run_graph(n, nullptr, -1);
         return;

@@ -79,6 +79,25 @@ class Model {
     void run_layer_unfused(const LayerW &L, const KVLayout &kv, int n);
     void run_layer_fused(const LayerW &L, const KVLayout &kv, int n);
     void run_decode_graphed(int n);
+    void run_layer_gemm(const LayerW &L, const KVLayout &kv, int n);
+    void gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride);
+    void ensure_gemm_scratch(size_t w_bytes, size_t x_bytes);
+    void *gemm_w_ = nullptr, *gemm_x_ = nullptr;
+    size_t gemm_w_bytes_ = 0, gemm_x_bytes_ = 0;
+    bool no_gemm_ = false;
+    int gemm_min_tokens_ = 4;
+    void build_mega();
+    void run_decode_mega();
+    MegaPhase *mega_phases_ = nullptr;
+    unsigned *mega_bar_ = nullptr;
+    long long *mega_dbg_ = nullptr;
+  public:
+    long long *mega_dbg() { return mega_dbg_; }
+    int mega_n_phases() const { return mega_n_phases_; }
+    int n_sm() const { return n_sm_; }
+  private:
+    int mega_n_phases_ = 0, n_sm_ = 0;
+    bool mega_ready_ = false, no_mega_ = false;
     bool unfused_ = false, no_graph_ = false;
     std::vector<cudaGraphExec_t> decode_graphs_;
     std::vector<int64_t> decode_graph_launches_;

@@ -1,0 +1,23 @@
+import sys, os, ctypes as C
+os.environ["B200LLM_MEGA_DBG"] = "1"
+sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/tools')
+import numpy as np, bench
+from localai_b200 import capi
+arch, preset = (sys.argv[1], sys.argv[2]) if len(sys.argv) > 2 else ("llama3-8b", "q4_k_m")
+path, info = bench.ensure_model(arch, preset, 0, 0, lambda: None)
+e = capi.Engine(path, n_ctx=1024, n_batch=512, n_parallel=1)
+ms, l = e.bench_decode(1, 128, 8, 3)
+print("ms/step", ms, "launches", l)
+L = capi.lib(); L.b2_mega_debug.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+n = L.b2_mega_debug(e._h, None, 0)
+buf = np.zeros(n, dtype=np.int64); L.b2_mega_debug(e._h, buf.ctypes.data_as(C.c_void_p), n)
+nph = n // 8 // 148; d = buf.reshape(148, nph, 8)
+kinds = ["qkv","att","wo","gateup","down"]
+pro = (d[:,:,1]-d[:,:,0]); stg = (d[:,:,2]-d[:,:,1]); bar = (d[:,:,3]-d[:,:,2])
+print("cycles per phase kind (mean over CTAs and layers; max over CTAs mean over layers) -- clock ~1.9 GHz")
+for k in range(5):
+    idx = np.arange(k, nph-1, 5)
+    print(f"        per-stage: n_stages {d[:,idx,7].mean():.1f} wait_full {d[:,idx,4].sum()/max(1,d[:,idx,7].sum()):.0f} tasks {d[:,idx,5].sum()/max(1,d[:,idx,7].sum()):.0f} arrive+sync+epilogue {d[:,idx,6].sum()/max(1,d[:,idx,7].sum()):.0f}")
+    print(f"{kinds[k]:7s} prologue {pro[:,idx].mean():8.0f}  stages mean {stg[:,idx].mean():8.0f} max-cta {stg[:,idx].max(axis=0).mean():8.0f}  barrier mean {bar[:,idx].mean():8.0f} min-cta {bar[:,idx].min(axis=0).mean():8.0f}")
+print("lm_head  prologue", pro[:,-1].mean(), "stages mean", stg[:,-1].mean(), "max", stg[:,-1].max())
+tot = (d[:,-1,3]-d[:,0,0]); print("total cycles per CTA mean", tot.mean(), "=> ms at 1.9GHz", tot.mean()/1.9e6)

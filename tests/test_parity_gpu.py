@@ -97,6 +97,27 @@ def test_mul_mat_matches_oracle(wtype, rows, cols, n_tok):
     assert np.abs(got - ref).max() <= MATMUL_RTOL * np.abs(ref).max()
 
 
+@pytest.mark.parametrize("path", [3, 4, 5])
+@pytest.mark.parametrize("wtype", [capi.B2_T_Q8_0, capi.B2_T_Q4_K, capi.B2_T_Q5_K, capi.B2_T_Q6_K, capi.B2_T_F16])
+@pytest.mark.parametrize("rows,cols,n_tok", [(64, 256, 1), (258, 1024, 3), (1000, 4096, 1), (96, 5632, 4), (34, 14336, 2),
+                                             (4096, 4096, 1)])
+def test_fused_and_mega_kernels_match_oracle(wtype, rows, cols, n_tok, path):
+    """the decode-path kernels (fused prologue/epilogue kernel, persistent mega-kernel) against the oracle mat-mul"""
+    import make_gguf as mg
+    if path == 4 and (n_tok != 1 or wtype == capi.B2_T_F16):
+        pytest.skip("mega-kernel: one activation row, quantised weights")
+    rng = np.random.default_rng(rows * 3 + cols + n_tok + path)
+    if wtype == capi.B2_T_F16:
+        raw = (rng.standard_normal((rows, cols)) / np.sqrt(cols)).astype(np.float16).view(np.uint8)
+    else:
+        raw = mg.random_blocks(rng, wtype, rows * cols // mg.BLOCK[wtype][0], 1 / np.sqrt(cols))
+    x = rng.standard_normal((n_tok, cols)).astype(np.float32)
+    got = capi.mul_mat(wtype, raw, rows, cols, x, path=path)
+    ref = O.mul_mat(wtype, raw, rows, cols, x)
+    assert np.isfinite(got).all()
+    assert np.abs(got - ref).max() <= MATMUL_RTOL * np.abs(ref).max()
+
+
 def test_mul_mat_linearity_in_rows():
     """size-independent property: rows are independent, so any row subset gives the same values."""
     import make_gguf as mg
@@ -131,7 +152,7 @@ def test_logits_match_oracle_prefill_and_decode(model_files, name):
         # embedding = final-norm hidden state of the last token
         _, embd = e.eval(toks[:8], want_embd=True)
         _, wembd = O.OracleModel(path, n_ctx=128).eval(toks[:8], want_embd=True)
-        assert np.abs(embd - wembd).max() <= 0.05 * wembd.std()
+        assert_logits_close(embd[None], wembd[None], "embedding")  # 8 tokens: tensor-core (bf16 operand) prefill path
 
 
 def test_hidden_states_per_layer(model_files):
