@@ -45,6 +45,12 @@ void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos
 void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv,
                       int hd, const KVLayout &kv, float *out, int max_ctx, cudaStream_t s);
 
+// flash-style prefill attention (kernels_fattn.cu): tokens [t0, t0 + n_q) are one sequence (`slot`), token t0 + i at
+// position pos0 + i; their K/V must already be in the cache
+bool fattn_supported(int hd);
+void launch_fattn_prefill(const float *q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, int hd,
+                          const KVLayout &kv, float *out, cudaStream_t s);
+
 // --- fused decode mat-vec (kernels_fused.cu) -----------------------------------------------------------------
 enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_QKV = 2 };
 struct FusedJob {

@@ -1,0 +1,193 @@
+// kernels_fattn.cu -- prefill attention: flash-style tiled kernel over the paged F16 KV cache.
+//
+// One CTA = 64 consecutive query tokens of one sequence x one head; 4 warps x 16 queries.  K/V tiles of 64 positions
+// are gathered from the KV pages into shared memory with cp.async (double buffered); S = Q.K^T and O += P.V run on
+// the tensor cores through mma.sync.m16n8k16 (f16 inputs, fp32 accumulate) with the online soft-max between them in
+// registers (S accumulator fragment == P operand fragment, so P never leaves the register file).  q is rounded to
+// f16 and P to f16 exactly where ggml's CPU path rounds them (mul_mat on an F16 cache); the only difference to the
+// per-token kernel is that P is rounded before the final 1/sum normalisation.
+// Attention is ~4 % of the prefill flops (2 x n^2/2 x head_dim x 2 per head); the dense mat-muls, which are the rest,
+// run on tcgen05 (kernels_gemm.cu).  L2-bound on K/V re-reads across the query tiles of a head.
+#include "kernels.h"
+#include "quant.cuh"
+
+namespace b2 {
+
+constexpr int FA_BQ = 64, FA_BK = 64, FA_THREADS = 128;
+
+__device__ __forceinline__ void fa_cp16(void *smem, const void *gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void fa_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N> __device__ __forceinline__ void fa_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
+__device__ __forceinline__ void fa_mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t fa_pack(float lo, float hi) {
+    const __half2 h = __floats2half2_rn(lo, hi);
+    return *(const uint32_t *)&h;
+}
+
+// q: [n_tok][n_head*HD] fp32 (rotated); tokens [t0, t0 + n_q) belong to `slot`, token t0 + i sits at position pos0 + i
+template <int HD>
+__global__ void __launch_bounds__(FA_THREADS)
+fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, KVLayout kv,
+                     float *__restrict__ out, float scale) {
+    constexpr int LD = HD + 8; // padded row (halves): conflict-free fragment loads
+    extern __shared__ __align__(16) __half fsm[];
+    __half *sK = fsm;                       // [2][FA_BK][LD]
+    __half *sV = fsm + 2 * FA_BK * LD;      // [2][FA_BK][LD]
+    const int h = blockIdx.y, qt = blockIdx.x;
+    const int hk = h / (n_head / n_head_kv);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tq = lane & 3;
+    const int q_lo = qt * FA_BQ;                       // first query of this CTA (relative to t0)
+    const int n_kv = pos0 + min(q_lo + FA_BQ, n_q);    // keys this CTA may need: positions [0, n_kv)
+    const int32_t *pt = kv.page_table + (int64_t)slot * kv.max_pages;
+
+    auto load_tile = [&](int buf, int j0) {
+        // 64 keys x HD halves = 64 x HD/8 16-byte chunks for K and the same for V
+        constexpr int CH = HD / 8;
+        for (int i = threadIdx.x; i < FA_BK * CH; i += FA_THREADS) {
+            const int r = i / CH, c = i % CH;
+            const int j = min(j0 + r, n_kv - 1); // clamp: rows past the end are masked anyway
+            const int64_t cell = ((int64_t)pt[j / kv.page_size] * kv.page_size + j % kv.page_size) * kv.kvd + hk * HD + c * 8;
+            fa_cp16(sK + ((size_t)buf * FA_BK + r) * LD + c * 8, kv.k_pool + cell);
+            fa_cp16(sV + ((size_t)buf * FA_BK + r) * LD + c * 8, kv.v_pool + cell);
+        }
+        fa_commit();
+    };
+
+    // Q fragments for this warp's 16 queries: rows (g, g+8), k-chunks of 16 dims
+    const int r0 = q_lo + warp * 16 + g, r1 = r0 + 8;
+    uint32_t qa[HD / 16][4];
+    {
+        const float *q0 = q + ((int64_t)(t0 + min(r0, n_q - 1)) * n_head + h) * HD;
+        const float *q1 = q + ((int64_t)(t0 + min(r1, n_q - 1)) * n_head + h) * HD;
+#pragma unroll
+        for (int kc = 0; kc < HD / 16; kc++) {
+            const int c = kc * 16 + tq * 2;
+            qa[kc][0] = fa_pack(q0[c], q0[c + 1]);
+            qa[kc][1] = fa_pack(q1[c], q1[c + 1]);
+            qa[kc][2] = fa_pack(q0[c + 8], q0[c + 9]);
+            qa[kc][3] = fa_pack(q1[c + 8], q1[c + 9]);
+        }
+    }
+    float o[HD / 8][4];
+#pragma unroll
+    for (int i = 0; i < HD / 8; i++) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const int p_r0 = pos0 + r0, p_r1 = pos0 + r1; // absolute positions of this thread's two query rows
+
+    const int n_tiles = (n_kv + FA_BK - 1) / FA_BK;
+    load_tile(0, 0);
+    for (int it = 0; it < n_tiles; it++) {
+        const int buf = it & 1, j0 = it * FA_BK;
+        if (it + 1 < n_tiles) { load_tile(buf ^ 1, j0 + FA_BK); fa_wait<1>(); } else { fa_wait<0>(); }
+        __syncthreads();
+        const __half *K = sK + (size_t)buf * FA_BK * LD, *V = sV + (size_t)buf * FA_BK * LD;
+        // ---- S = Q K^T : 8 n-tiles of 8 keys
+        float s[FA_BK / 8][4];
+#pragma unroll
+        for (int nt = 0; nt < FA_BK / 8; nt++) {
+            s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+            const __half *kr = K + (size_t)(nt * 8 + g) * LD + tq * 2; // B fragment: key (nt*8+g), dims k*16 + tq*2 (+8)
+#pragma unroll
+            for (int kc = 0; kc < HD / 16; kc++)
+                fa_mma(s[nt], qa[kc], *(const uint32_t *)(kr + kc * 16), *(const uint32_t *)(kr + kc * 16 + 8));
+        }
+        // ---- scale, causal mask, online soft-max (rows r0: regs 0,1 ; r1: regs 2,3)
+        float mx0 = m0, mx1 = m1;
+#pragma unroll
+        for (int nt = 0; nt < FA_BK / 8; nt++) {
+            const int j = j0 + nt * 8 + tq * 2;
+            s[nt][0] = (j <= p_r0) ? s[nt][0] * scale : -INFINITY;
+            s[nt][1] = (j + 1 <= p_r0) ? s[nt][1] * scale : -INFINITY;
+            s[nt][2] = (j <= p_r1) ? s[nt][2] * scale : -INFINITY;
+            s[nt][3] = (j + 1 <= p_r1) ? s[nt][3] * scale : -INFINITY;
+            mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
+            mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float c0 = (m0 == -INFINITY) ? 0.f : expf(m0 - mx0), c1 = (m1 == -INFINITY) ? 0.f : expf(m1 - mx1);
+        m0 = mx0;
+        m1 = mx1;
+        l0 *= c0;
+        l1 *= c1;
+#pragma unroll
+        for (int i = 0; i < HD / 8; i++) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+        uint32_t pa[FA_BK / 16][4];
+#pragma unroll
+        for (int nt = 0; nt < FA_BK / 8; nt++) {
+            const float e0 = (mx0 == -INFINITY) ? 0.f : expf(s[nt][0] - mx0), e1 = (mx0 == -INFINITY) ? 0.f : expf(s[nt][1] - mx0);
+            const float e2 = (mx1 == -INFINITY) ? 0.f : expf(s[nt][2] - mx1), e3 = (mx1 == -INFINITY) ? 0.f : expf(s[nt][3] - mx1);
+            const __half2 h01 = __floats2half2_rn(e0, e1), h23 = __floats2half2_rn(e2, e3);
+            // the row sums use the f16-rounded probabilities, i.e. exactly what multiplies V
+            const float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
+            l0 += f01.x + f01.y;
+            l1 += f23.x + f23.y;
+            pa[nt >> 1][(nt & 1) * 2 + 0] = *(const uint32_t *)&h01;
+            pa[nt >> 1][(nt & 1) * 2 + 1] = *(const uint32_t *)&h23;
+        }
+        // ---- O += P V : B fragments straight from the row-major V tile with ldmatrix.trans
+#pragma unroll
+        for (int kc = 0; kc < FA_BK / 16; kc++) {
+            const __half *vr = V + (size_t)(kc * 16 + (lane & 15)) * LD;
+#pragma unroll
+            for (int dt = 0; dt < HD / 8; dt++) {
+                uint32_t b0, b1;
+                asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];"
+                             : "=r"(b0), "=r"(b1)
+                             : "r"((uint32_t)__cvta_generic_to_shared(vr + dt * 8)));
+                fa_mma(o[dt], pa[kc], b0, b1);
+            }
+        }
+        __syncthreads(); // the other buffer is refilled at the top of the next iteration
+    }
+    // ---- normalise and write: rows r0 / r1, dims dt*8 + tq*2 (+1)
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.f / l0, i1 = 1.f / l1;
+    if (r0 < n_q) {
+        float *orow = out + ((int64_t)(t0 + r0) * n_head + h) * HD + tq * 2;
+#pragma unroll
+        for (int dt = 0; dt < HD / 8; dt++) *(float2 *)(orow + dt * 8) = make_float2(o[dt][0] * i0, o[dt][1] * i0);
+    }
+    if (r1 < n_q) {
+        float *orow = out + ((int64_t)(t0 + r1) * n_head + h) * HD + tq * 2;
+#pragma unroll
+        for (int dt = 0; dt < HD / 8; dt++) *(float2 *)(orow + dt * 8) = make_float2(o[dt][2] * i1, o[dt][3] * i1);
+    }
+}
+
+bool fattn_supported(int hd) { return hd == 64 || hd == 128; }
+
+void launch_fattn_prefill(const float *q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, int hd,
+                          const KVLayout &kv, float *out, cudaStream_t s) {
+    if (n_q <= 0) return;
+    const float scale = 1.0f / sqrtf((float)hd);
+    const dim3 grid((n_q + FA_BQ - 1) / FA_BQ, n_head);
+    const size_t smem = (size_t)4 * FA_BK * (hd + 8) * sizeof(__half);
+    if (hd == 128) {
+        static thread_local bool cfg = false;
+        if (!cfg) {
+            B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            cfg = true;
+        }
+        fattn_prefill_kernel<128><<<grid, FA_THREADS, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+    } else if (hd == 64) {
+        fattn_prefill_kernel<64><<<grid, FA_THREADS, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+    } else {
+        throw Error(B2_EUNSUPPORTED, "flash prefill attention: head_dim must be 64 or 128");
+    }
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+} // namespace b2

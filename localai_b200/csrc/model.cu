@@ -257,6 +257,23 @@ void Model::matmul(const DTensor &W, const float *x, int64_t x_stride, int n, fl
 static inline void invalidate(bool (&v)[4]) { v[0] = v[1] = v[2] = v[3] = false; }
 void Model::invalidate_acts() { invalidate(actq_valid_); }
 
+// attention over a batch: consecutive tokens of one sequence (a prompt chunk) go through the flash kernel, single decode
+// tokens through the per-token kernel
+void Model::attention(const KVLayout &kv, int n) {
+    const int hd = hp.head_dim, d = hp.n_embd;
+    if (runs_.empty()) {
+        launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+        return;
+    }
+    for (const Run &r : runs_) {
+        if (r.n >= 16 && fattn_supported(hd))
+            launch_fattn_prefill(q_, r.t0, r.n, r.pos0, r.slot, hp.n_head, hp.n_head_kv, hd, kv, att_, stream);
+        else
+            launch_attention(q_ + (size_t)r.t0 * d, pos_ + r.t0, slot_ + r.t0, r.n, hp.n_head, hp.n_head_kv, hd, kv,
+                             att_ + (size_t)r.t0 * d, n_ctx_slot, stream);
+    }
+}
+
 static FusedJob job_of(const DTensor &W) { return FusedJob{W.data, W.type, W.rows, W.row_stride}; }
 
 // The original, one-op-per-kernel path.  Kept for layers whose matrices need different activation formats (the
@@ -270,7 +287,7 @@ void Model::run_layer_unfused(const LayerW &L, const KVLayout &kv, int n) {
     matmul(L.wk, xn_, d, n, k_, kvd, nullptr, 0);
     matmul(L.wv, xn_, d, n, v_, kvd, nullptr, 0);
     launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
-    launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+    attention(kv, n);
     invalidate(actq_valid_);
     matmul(L.wo, att_, d, n, x_, d, x_, d); // x = x + wo.att
     launch_rmsnorm(x_, d, nullptr, (const float *)L.ffn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
@@ -292,7 +309,7 @@ void Model::run_layer_fused(const LayerW &L, const KVLayout &kv, int n) {
     a.n_jobs = 3; a.job[0] = job_of(L.wq); a.job[1] = job_of(L.wk); a.job[2] = job_of(L.wv);
     a.epi = EPI_QKV; a.out = q_; a.out_stride = d; a.pos = pos_; a.slot = slot_; a.rope_table = rope_table_; a.kv = kv; a.hd = hd;
     launch_fused_gemv(a, n, stream);
-    launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+    attention(kv, n);
     FusedGemv o;
     o.x = att_; o.x_stride = d; o.K = d; o.fmt = act_format_for(L.wo.type);
     o.n_jobs = 1; o.job[0] = job_of(L.wo); o.epi = EPI_PLAIN; o.out = x_; o.out_stride = d; o.residual = x_; o.res_stride = d;
@@ -349,7 +366,7 @@ void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     gemm(L.wk, n, k_, kvd, nullptr, 0);
     gemm(L.wv, n, v_, kvd, nullptr, 0);
     launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
-    launch_attention(q_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, kv, att_, n_ctx_slot, stream);
+    attention(kv, n);
     launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
     gemm(L.wo, n, x_, d, x_, d);
     launch_rmsnorm(x_, d, nullptr, (const float *)L.ffn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
@@ -528,10 +545,18 @@ void Model::forward(const Batch &b) {
     if (b.tokens) B2_CUDA(cudaMemcpyAsync(tok_, b.tokens, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaMemcpyAsync(pos_, b.pos, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaMemcpyAsync(slot_, b.slot, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
+    runs_.clear();
+    for (int i = 0; i < b.n;) { // maximal runs of consecutive positions of one slot
+        int j = i + 1;
+        while (j < b.n && b.slot[j] == b.slot[i] && b.pos[j] == b.pos[i] + (j - i)) j++;
+        runs_.push_back(Run{i, j - i, b.pos[i], b.slot[i]});
+        i = j;
+    }
     int n_out = b.n_out;
     bool pure_decode = n_out == b.n && b.n < (int)decode_graphs_.size(); // every row wants logits, in order
     for (int i = 0; pure_decode && i < n_out; i++) pure_decode = b.out_rows[i] == i;
     if (pure_decode) {
+        runs_.clear(); // one per-token attention launch for the whole batch (and what the captured graph holds)
         run_decode_graphed(b.n);
         return;
     }
@@ -548,6 +573,7 @@ void Model::set_device_inputs(const int32_t *tokens, const int32_t *pos, const i
 
 void Model::forward_device_inputs(int n) {
     B2_CUDA(cudaSetDevice(device));
+    runs_.clear();
     run_decode_graphed(n);
 }
 

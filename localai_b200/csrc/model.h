@@ -79,6 +79,9 @@ class Model {
     void run_layer_unfused(const LayerW &L, const KVLayout &kv, int n);
     void run_layer_fused(const LayerW &L, const KVLayout &kv, int n);
     void run_decode_graphed(int n);
+    struct Run { int t0, n, pos0, slot; };
+    std::vector<Run> runs_; // host view of the current batch (empty: inputs only on the device)
+    void attention(const KVLayout &kv, int n);
     void run_layer_gemm(const LayerW &L, const KVLayout &kv, int n);
     void gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride);
     void ensure_gemm_scratch(size_t w_bytes, size_t x_bytes);
