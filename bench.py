@@ -145,8 +145,8 @@ def run_reference(args, rank: int):
 
     from oracle import oracle as O
 
-    n_prompt = 8
-    m = O.OracleModel(path, n_ctx=4096)
+    n_prompt = args.ctx  # the same context the GPU arm decodes at
+    m = O.OracleModel(path, n_ctx=args.ctx + args.steps + 64)
     prompt = (np.arange(n_prompt) * 7919 % 4000 + 3).astype(np.int32)
     lg = m.eval(prompt)
     tok, pos = int(lg[0].argmax()), n_prompt
@@ -168,7 +168,7 @@ def run_reference(args, rank: int):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": max(1, min(args.warmup, 2)), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int8 x q4/q6 block dot, f32 accumulate", "data": "synthetic",
-        "config": {"workload": f"{args.arch} {args.preset} random-init GGUF, batch-1 greedy decode, ctx {n_prompt}+",
+        "config": {"workload": f"{args.arch} {args.preset} random-init GGUF, batch-1 greedy decode at ctx {args.ctx}",
                    "note": "CPU oracle port (reference llama.cpp is not buildable offline); steps bounded by a time budget"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{steps} greedy decode steps after an {n_prompt}-token prompt, OpenMP {cores} threads"},
@@ -232,7 +232,8 @@ def main():
     n_par = max(1, args.batch)
     n_ctx_slot = max(args.prefill, args.ctx + args.steps + warmup) + 128
     t0 = time.time()
-    eng = capi.Engine(path, n_ctx=n_ctx_slot * n_par, n_batch=512, n_parallel=n_par, device=local_rank)
+    n_batch = max(512, args.prefill)  # NBatch (ModelOptions): one chunk per prompt, weights are dequantised once per chunk
+    eng = capi.Engine(path, n_ctx=n_ctx_slot * n_par, n_batch=n_batch, n_parallel=n_par, device=local_rank)
     log(f"[bench r{rank}] loaded in {time.time() - t0:.1f}s: {eng.info.name.decode()} weights {eng.info.weight_bytes_device / 1e9:.3f} GB")
     stream_bytes = eng.info.decode_stream_bytes
     kv_per_pos = eng.info.kv_bytes_per_pos
@@ -308,7 +309,8 @@ def main():
             "dtype": "int8 x q4/q6 block dot (dp4a), f32 accumulate", "data": "synthetic",
             "config": {"workload": f"{args.arch} {args.preset} random-init GGUF, batch-1 greedy decode at ctx {args.ctx}",
                        "replicas": world, "l2": "inputs larger than L2: every step streams %.2f GB of weights (L2 = 126 MB)" % (stream_bytes / 1e9),
-                       "decode_stream_bytes": stream_bytes, "kv_bytes_per_pos": kv_per_pos},
+                       "decode_stream_bytes": stream_bytes, "kv_bytes_per_pos": kv_per_pos, "n_batch": n_batch,
+                       "n_parallel": n_par},
             "e2e": e2e, "gpu_launches": int(launches) * args.steps, "gpu_launches_per_step": int(launches),
             "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "extra": extra,
         }
