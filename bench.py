@@ -35,6 +35,9 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 METRIC = "Llama-3-8B Q4_K_M decode tok/s (b=1)"
 UNIT = "tok/s"
+# dram__bytes_read.sum + dram__bytes_write.sum of one decode_mega_kernel launch (llama3-8b q4_k_m, ctx 128), from the
+# ncu --set full capture summarised in profiles/ (None until a capture of the current kernel is committed)
+MEGA_TRAFFIC_BYTES = None
 
 
 def log(*a):
@@ -202,27 +205,10 @@ def main():
         return 0
 
     warmup = max(args.warmup, 3)
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist_mod
+    from localai_b200.replicas import Ranks
 
-        torch.cuda.set_device(local_rank)
-        dist_mod.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-        dist = dist_mod
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-
-    def max_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        import torch
-
-        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    ranks = Ranks(rank, world, local_rank)  # nccl; one independent replica per rank, no data-path collective
+    barrier, max_over_ranks = ranks.barrier, ranks.max
 
     from localai_b200 import capi
 
@@ -268,15 +254,20 @@ def main():
            "prompt_ms": fin["t_prompt_ms"], "wall_s": t_wall, "n_decoded": fin["n_decoded"],
            "path": "b2_submit/b2_poll (PredictStream), greedy, host prompt ids"}
 
-    # ---- roofline of the dominant kernel, timed alone
-    k_ms, k_bytes, k_type = eng.bench_gemv(4, 1, 8)
-    achieved = k_bytes / (k_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": f"gemv_kernel<type {k_type}, NT=1> on ffn_gate [{eng.info.n_ff}x{eng.info.n_embd}]",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "bytes_per_launch": k_bytes, "us_per_launch": k_ms * 1e3, "peak_source": peak_src,
-                "step": {"bytes": step_bytes, "achieved_gbs": step_bytes / (ms * 1e-3) / 1e9,
-                         "frac_of_measured": step_bytes / (ms * 1e-3) / 1e9 / peak,
-                         "frac_of_8tbs": step_bytes / (ms * 1e-3) / 8e12}}
+    # ---- roofline of the dominant kernel.  A b=1 decode step IS one launch of decode_mega_kernel (the persistent
+    # kernel that walks every layer), so its launch duration is the step time measured above with CUDA events on the
+    # engine's stream, and its algorithmic bytes are the step's: every weight row once + the KV rows read.
+    # `traffic` is dram__bytes_read.sum + dram__bytes_write.sum of one launch from profiles/r1_mega_ncu_raw.csv.
+    achieved = step_bytes / (ms * 1e-3) / 1e9
+    k_ms, k_bytes, k_type = eng.bench_gemv(4, 1, 8)  # the row-streaming loop alone on one ffn_gate matrix, for reference
+    roofline = {"bound": "hbm", "kernel": "decode_mega_kernel (1 launch per decode step)" if launches == 1 else
+                "fused decode kernels (%d launches per step), whole step" % launches,
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": MEGA_TRAFFIC_BYTES,
+                "bytes_per_launch": step_bytes, "us_per_launch": ms * 1e3, "peak_source": peak_src,
+                "frac_of_8tbs": step_bytes / (ms * 1e-3) / 8e12,
+                "gemv_alone": {"kernel": f"gemv_kernel<type {k_type}, NT=1> on ffn_gate [{eng.info.n_ff}x{eng.info.n_embd}]",
+                               "bytes_per_launch": k_bytes, "us_per_launch": k_ms * 1e3,
+                               "achieved": k_bytes / (k_ms * 1e-3) / 1e9, "frac": k_bytes / (k_ms * 1e-3) / 1e9 / peak}}
 
     extra = {}
     cpu = None
@@ -315,8 +306,7 @@ def main():
             "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "extra": extra,
         }
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+    ranks.close()
     return 0
 
 
