@@ -308,16 +308,16 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
         ph.kind = PH_PLAIN; ph.K = cols; ph.fmt = f; ph.n_jobs = 1;
         ph.job[0] = FusedJob{W.data, W.type, W.rows, W.row_stride};
         ph.x = dx.as<float>(); ph.out = dout.as<float>(); ph.units = (int)(rows / 2);
-        B2_CHECK(mega_phase_supported(ph), B2_EUNSUPPORTED, "mega path: shape/type not supported");
-        DevBuf dph(sizeof(MegaPhase)), dbar(64), dps(64);
+        int n_sm = 0;
+        B2_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0));
+        B2_CHECK(mega_phase_prepare(ph, n_sm), B2_EUNSUPPORTED, "mega path: shape/type not supported");
+        DevBuf dph(sizeof(MegaPhase)), dbar(4096), dps(64);
         B2_CUDA(cudaMemcpy(dph.p, &ph, sizeof(ph), cudaMemcpyHostToDevice));
-        B2_CUDA(cudaMemset(dbar.p, 0, 64));
+        B2_CUDA(cudaMemset(dbar.p, 0, 4096));
         B2_CUDA(cudaMemset(dps.p, 0, 64));
         MegaArgs a;
         a.phases = dph.as<MegaPhase>(); a.n_phases = 1; a.pos = dps.as<int32_t>(); a.slot = dps.as<int32_t>() + 4;
-        a.bar = dbar.as<unsigned>(); a.page_size = 32; a.max_pages = 1; a.hd = 64; a.n_head = 1; a.n_head_kv = 1;
-        int n_sm = 0;
-        B2_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0));
+        a.bar = dbar.as<unsigned>(); a.page_size = 32; a.page_shift = 5; a.max_pages = 1; a.hd = 64; a.n_head = 1; a.n_head_kv = 1;
         launch_decode_mega(a, n_sm, 0);
         B2_CUDA(cudaDeviceSynchronize());
     } else {

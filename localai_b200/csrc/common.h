@@ -34,10 +34,10 @@ void set_last_error(const std::string &m);
 // ---- tensor types (ggml ids) and on-device layouts -------------------------------------------------
 // Q4_K / Q5_K / F16 / F32 rows keep the GGUF layout (their blocks are 16-byte multiples).
 // Q8_0 (34 B) and Q6_K (210 B) blocks are only 2-byte aligned on disk, so LoadModel repacks each ROW
-// into a structure-of-arrays form whose sections are all 16-byte aligned (same byte count, rounded up
-// to 16 per row):
-//   Q8_0 row: [qs: cols x int8][d: nb x fp16]                          nb = cols/32
-//   Q6_K row: [ql: nb x 128][qh: nb x 64][scales: nb x 16][d: nb x fp16] nb = cols/256
+// so that everything a kernel reads with 128-bit loads is 16-byte aligned (same byte count, rounded up
+// to 16 per row): the fp16 block scales move to the end of the row.
+//   Q8_0 row: [qs: cols x int8][d: nb x fp16]                             nb = cols/32
+//   Q6_K row: [nb x {ql 128, qh 64, scales 16} = 208 B][d: nb x fp16]     nb = cols/256
 struct DTensor {
     const uint8_t *data = nullptr; // device
     int type = -1;

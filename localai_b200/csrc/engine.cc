@@ -241,7 +241,7 @@ int Engine::bench_decode(int batch, int ctx_len, int n_steps, int n_warmup, doub
 int Engine::mega_debug(long long *out, int cap) {
     Model &m = model();
     std::lock_guard<std::mutex> lk(dev_mu_);
-    const int n = m.n_sm() * m.mega_n_phases() * 8;
+    const int n = m.n_sm() * m.mega_n_phases() * 16;
     if (!m.mega_dbg()) return 0;
     if (!out) return n;
     B2_CHECK(cap >= n, B2_ENOSPC, "mega_debug: buffer too small");

@@ -96,9 +96,9 @@ __device__ __forceinline__ void row_dot_q6_K(const uint8_t *__restrict__ row, in
     const int p = lane & 7, n = p >> 2, c = p & 3; // 16-byte piece p of ql: half n, 16-element column c
     const int sh = 2 * (c >> 1);                    // qh bit position for the low-nibble elements
     for (int ib = lane >> 3; ib < nb; ib += 4) {
-        const int4 lv = ld_stream(w.ql + (size_t)ib * 128 + p * 16);
-        const int4 hv = ld_stream(w.qh + (size_t)ib * 64 + n * 32 + (c & 1) * 16);
-        const int sc_lo = w.sc[ib * 16 + 8 * n + c], sc_hi = w.sc[ib * 16 + 8 * n + 4 + c];
+        const int4 lv = ld_stream(w.ql(ib) + p * 16);
+        const int4 hv = ld_stream(w.qh(ib) + n * 32 + (c & 1) * 16);
+        const int sc_lo = w.sc(ib)[8 * n + c], sc_hi = w.sc(ib)[8 * n + 4 + c];
         const float d = h2f(w.d[ib]);
         const uint32_t l[4] = {(uint32_t)lv.x, (uint32_t)lv.y, (uint32_t)lv.z, (uint32_t)lv.w};
         const uint32_t h[4] = {(uint32_t)hv.x, (uint32_t)hv.y, (uint32_t)hv.z, (uint32_t)hv.w};

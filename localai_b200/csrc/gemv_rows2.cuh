@@ -197,7 +197,7 @@ __device__ __forceinline__ void rows2_q5_K(const uint8_t *r0, const uint8_t *r1,
 }
 
 // ---------------------------------------------------------------------------------------------------- Q6_K
-// Device (SoA) row layout [ql nb*128][qh nb*64][scales nb*16][d nb*2]; nb_row locates the sections.
+// Device row layout: nb blocks of 208 B [ql 128][qh 64][scales 16], then d nb*2 (quant.cuh Q6Row); nb_row locates d.
 // lane = (block slot lane >> 2, half n = (lane >> 1) & 1, column half lh = lane & 1): 64 weights per lane =
 // the four 16-weight sub-blocks {128n + 32c + 16lh + [0,16)} c = 0..3, which share one 16-byte piece of qh.
 template <class LD, int R, int NT>
@@ -212,10 +212,10 @@ __device__ __forceinline__ void rows2_q6_K(const uint8_t *r0, const uint8_t *r1,
     auto load = [&](int b, int4(&a0)[2], int4(&a1)[2], int4(&h)[2], int2(&s)[2], uint32_t(&dd)[2]) {
 #pragma unroll
         for (int r = 0; r < R; r++) {
-            a0[r] = LD::v4(w[r].ql + (size_t)b * 128 + 64 * n + 16 * lh);      // c = 0 (low nibbles), c = 2 (high)
-            a1[r] = LD::v4(w[r].ql + (size_t)b * 128 + 64 * n + 32 + 16 * lh); // c = 1 (low nibbles), c = 3 (high)
-            h[r] = LD::v4(w[r].qh + (size_t)b * 64 + 32 * n + 16 * lh);
-            s[r] = LD::v2(w[r].sc + b * 16 + 8 * n);                           // 8 int8 scales of this half
+            a0[r] = LD::v4(w[r].ql(b) + 64 * n + 16 * lh);      // c = 0 (low nibbles), c = 2 (high)
+            a1[r] = LD::v4(w[r].ql(b) + 64 * n + 32 + 16 * lh); // c = 1 (low nibbles), c = 3 (high)
+            h[r] = LD::v4(w[r].qh(b) + 32 * n + 16 * lh);
+            s[r] = LD::v2(w[r].sc(b) + 8 * n);                  // 8 int8 scales of this half
             dd[r] = LD::u16(w[r].d + b);
         }
     };

@@ -103,6 +103,14 @@ struct MegaPhase {
     float *xn_out = nullptr;       // optional: the normalised row (LM head -> embeddings)
     __half *k_pool = nullptr, *v_pool = nullptr; // this layer's KV pools (QKV, ATT)
     int units = 0;                 // row pairs (PLAIN/QKV) or rows (SWIGLU) split across the CTAs
+    // lane geometry, filled by mega_phase_prepare() so that the kernel's schedule walk needs no integer division:
+    int S = 1, s_log = 0;          // K-splits (power of two <= warps per CTA): a row is spread over S warps
+    int lpr = 32, lpr_log = 5;     // lanes that share one (row, K-split); rpp = 32 / lpr rows per warp pass when lpr < 32
+    int rpp = 1, np = 0;           // np: Q8_0 16-byte pieces per lane
+    int units_q = 0, units_r = 0;  // units / n_cta, units % n_cta: the first units_r CTAs take units_q + 1 units
+    int j0[3] = {0, 0, 0};         // first row of each matrix in the concatenated row space
+    int rb[3] = {0, 0, 0};         // per matrix: bytes of one row's K-split = row pitch inside a staged tile
+    int R[3] = {0, 0, 0};          // per matrix: rows per tile
 };
 struct MegaArgs {
     const MegaPhase *phases = nullptr; // device
@@ -112,10 +120,13 @@ struct MegaArgs {
     const int32_t *page_table = nullptr;
     int page_size = 0, max_pages = 0, kvd = 0, n_head = 0, n_head_kv = 0, hd = 0;
     float eps = 0.f, att_scale = 0.f;
-    unsigned *bar = nullptr; // [count, generation], zero-initialised once
+    int page_shift = 0;      // log2(page_size)
+    unsigned *bar = nullptr; // arrival counter, zero-initialised once; it only ever grows
+    unsigned bar_base = 0;   // counter value when this launch starts; the host adds n_cta * (n_phases - 1) per launch
     long long *dbg = nullptr; // optional [n_cta][n_phases][4] clock64 stamps: start, after prologue, after stages, after barrier
 };
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s);
+bool mega_phase_prepare(MegaPhase &ph, int n_cta); // fills the lane geometry; false = shape/type the kernel has no mapping for
 bool mega_phase_supported(const MegaPhase &ph);
 size_t mega_attention_ctx_limit(int hd);
 

@@ -83,9 +83,9 @@ __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, in
                 const int64_t ib = k0 / 256;
                 const int e = k0 % 256, n = e / 128, c = (e % 128) / 32, l0 = e % 32;
                 const float d = h2f(q.d[ib]);
-                const uint8_t *ql = q.ql + ib * 128 + 64 * n + ((c & 1) ? 32 : 0) + l0;
-                const uint8_t *qh = q.qh + ib * 64 + 32 * n + l0;
-                const float ds = d * (float)q.sc[ib * 16 + 8 * n + 2 * c + l0 / 16];
+                const uint8_t *ql = q.ql(ib) + 64 * n + ((c & 1) ? 32 : 0) + l0;
+                const uint8_t *qh = q.qh(ib) + 32 * n + l0;
+                const float ds = d * (float)q.sc(ib)[8 * n + 2 * c + l0 / 16];
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
                     const int lo = (c < 2) ? (ql[j] & 0xF) : (ql[j] >> 4);

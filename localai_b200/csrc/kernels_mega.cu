@@ -1,297 +1,997 @@
 // kernels_mega.cu -- the whole batch-1 decode step as ONE persistent cooperative kernel (one CTA per SM).
 //
-// Why: a decode step streams every weight byte exactly once (4.6 GB for Llama-3-8B Q4_K_M), so the only way to sit
-// on the HBM roofline is to never let the memory pipeline drain.  With one kernel per operator (~165 launches) each
-// launch pays ramp-up, an activation-quantisation prologue with no loads in flight, and a tail.  Here:
-//   * the 126 MB L2 is the staging buffer.  A PREFETCH warp walks the static schedule of this CTA's weight rows for
-//     every phase of every layer and issues bulk L2 prefetches (cp.async.bulk.prefetch.L2, the TMA engine) a bounded
-//     distance ahead of what the consumers have finished.  Weights do not depend on activations, so it runs ahead
-//     across phase boundaries: while the consumers sit in a grid barrier or re-quantise the activation row, HBM keeps
-//     streaming into L2.
-//   * 31 CONSUMER warps (64 registers each: latency is hidden by thread-level parallelism, and the loads hit L2) take
-//     (row, K-segment) tasks and do the integer block dots against the activation row held in shared memory (same
-//     arithmetic as the stand-alone kernels).  Segment partials are combined in a fixed order (deterministic) by the
-//     phase epilogue (RoPE + KV store | residual | SwiGLU).
-//   * phases are separated by a sense-reversing grid barrier; activations written by other SMs are read with ld.cg.
-// Phases per layer: QKV -> attention -> wo -> gate/up -> down; then the LM head.  HBM-bound by construction;
-// algorithmic bytes per launch = decode_stream_bytes + KV bytes.
+// A decode step streams every weight byte exactly once (4.6 GB for Llama-3-8B Q4_K_M) and does ~2 integer MACs per
+// byte, so it lives or dies by how close HBM stays to 100 % busy.  Three things keep it there:
+//
+//   1. WEIGHTS STREAM THROUGH SHARED MEMORY, AHEAD OF THE MATH, ACROSS PHASE BOUNDARIES.  Every warp owns a private
+//      two-stage ring (2 x 12 KB) that it fills itself with bulk-async copies (cp.async.bulk -> mbarrier
+//      complete_tx, the TMA engine) from a static schedule of its weight tiles that runs over ALL phases of ALL
+//      layers.  Weights do not depend on activations, so while the CTA sits in a grid barrier or re-quantises the
+//      activation row its 16 stages (192 KB per SM, 28 MB per GPU) are already filling with the next phase's rows.
+//      No warp ever waits for another warp's data; the only CTA-wide syncs are the phase boundaries.
+//   2. ACTIVATIONS ARE REGISTER-STATIONARY.  A lane always handles the same K-slice of a row (K-quants: half a
+//      256-weight super-block; Q8_0: every 32nd 16-byte piece), so after the phase prologue has normalised and
+//      quantised the activation row (bit-exact with quantize_row_q8_K / q8_0) each lane keeps its 128 int8
+//      activations, their scale and block sums in registers for the whole phase.  The inner loop is then
+//      5-8 shared-memory loads + the dp4a chain per 72-104 weight bytes: ~1.6 lane-instructions per weight byte
+//      against a budget of ~5.6 at the HBM roofline.  Rows longer than one warp pass are split over 2/4/8 warps
+//      (K-splits); split partials are combined in a fixed order by the phase epilogue.
+//   3. ONE LAUNCH.  Phases (QKV+RoPE+KV store -> attention -> wo+residual -> gate/up+SwiGLU -> down+residual, then
+//      the LM head) are separated by a grid barrier on per-CTA epoch flags (one release store to arrive, no atomics);
+//      activations written by other SMs are read with ld.cg.
+//
+// Arithmetic = ggml_vec_dot_{q4_K,q6_K}_q8_K / q8_0_q8_0 (integer block dots, fp32 scaling); only the fp32 summation
+// order differs from the scalar reference.  Algorithmic bytes per launch = decode_stream_bytes + KV bytes read.
 #include "act_quant.cuh"
-#include "attention.cuh"
-#include "gemv_rows2.cuh"
 #include "kernels.h"
+#include "quant.cuh"
 
 namespace b2 {
 
-constexpr int MEGA_CW = 31;                       // consumer warps
-constexpr int MEGA_CT = MEGA_CW * 32;             // consumer threads
-constexpr int MEGA_THREADS = MEGA_CT + 32;        // + prefetch warp = 1024
-constexpr int MEGA_XS_BYTES = 36 * 1024;          // quantised activation row, or attention scratch
-constexpr int MEGA_MAX_PART = 4096;               // per-phase partial sums (rows of this CTA x K-segments)
-constexpr int MEGA_PB = 2;                        // prologue: 256-element blocks held in registers per warp
-constexpr long long MEGA_PF_AHEAD = 320 * 1024;   // bytes per CTA the prefetcher may run ahead (x148 = 46 MB of L2)
-constexpr int MEGA_PF_CHUNK = 16 * 1024;
+constexpr int MG_WARPS = 8;
+constexpr int MG_THREADS = MG_WARPS * 32;
+constexpr int MG_STAGES = 2;                 // per warp
+constexpr int MG_STAGE_BYTES = 9216;
+constexpr int MG_RING_BYTES = MG_WARPS * MG_STAGES * MG_STAGE_BYTES;
+constexpr int MG_XS_BYTES = 18 * 1024;       // quantised activation row (attention: scratch, together with the partials)
+constexpr int MG_MAX_PART = 2048;            // per-phase partial sums: rows of this CTA x K-splits
+constexpr int MG_PB = 8;                     // prologue: 256-element blocks a warp holds in registers (K <= 16384)
+constexpr int MG_MAX_PASS = 8;               // warp passes per tile
 
-constexpr size_t MEGA_OFF_PART = MEGA_XS_BYTES;                                  // float [MAX_PART]
-constexpr size_t MEGA_OFF_RED = MEGA_OFF_PART + MEGA_MAX_PART * sizeof(float);   // double [32]
-constexpr size_t MEGA_OFF_CNT = MEGA_OFF_RED + 32 * sizeof(double);              // unsigned long long consumed; int stop
-constexpr size_t MEGA_SMEM = MEGA_OFF_CNT + 64;
+constexpr size_t MG_OFF_XS = MG_RING_BYTES;
+constexpr size_t MG_OFF_PART = MG_OFF_XS + MG_XS_BYTES;
+constexpr size_t MG_OFF_RED = MG_OFF_PART + MG_MAX_PART * sizeof(float);
+constexpr size_t MG_OFF_BAR = MG_OFF_RED + 32 * sizeof(double);
+constexpr int MG_MAX_PAGES = 512;            // page-table entries of the sequence kept in shared memory
+constexpr int MG_PH_WIN = 8;                 // phase descriptors kept in shared memory: phases [p, p + 8)
+constexpr size_t MG_OFF_PH = MG_OFF_BAR + MG_WARPS * MG_STAGES * sizeof(uint64_t);
+constexpr size_t MG_OFF_PT = MG_OFF_PH + MG_PH_WIN * ((sizeof(MegaPhase) + 15) / 16 * 16);
+constexpr size_t MG_OFF_CUR = MG_OFF_PT + MG_MAX_PAGES * sizeof(int);   // 2 schedule cursors per warp
+constexpr size_t MG_OFF_TILE = MG_OFF_CUR + MG_WARPS * 96;                // 1 cursor per warp, then 48-byte tile descriptors
+constexpr size_t MG_SMEM = MG_OFF_TILE + MG_WARPS * MG_STAGES * 48;
+static_assert(sizeof(MegaPhase) % 4 == 0, "MegaPhase is copied word by word");
+static_assert(MG_SMEM <= 227 * 1024, "mega-kernel shared memory");
 
-// weights that the prefetcher has already pulled into L2: plain 128-bit loads, no L1 allocation, no register
-// double buffer (L2 latency is hidden by the 31 warps)
-struct LdL2 {
-    static constexpr bool kPrefetch = false;
-    static __device__ __forceinline__ int4 v4(const void *p) { return ld_stream(p); }
-    static __device__ __forceinline__ int2 v2(const void *p) { return *(const int2 *)p; }
-    static __device__ __forceinline__ uint32_t u16(const void *p) { return *(const uint16_t *)p; }
-};
-
-__device__ __forceinline__ int64_t act_row_bytes_dev(int fmt, int64_t K) {
-    const int64_t b = fmt == ACT_Q8_K ? K + K / 256 * 4 + K / 16 * 2 : fmt == ACT_Q8_0 ? K + K / 32 * 4 : fmt == ACT_F16 ? K * 2 : K * 4;
-    return (b + 15) / 16 * 16;
+// ------------------------------------------------------------------------------------------------ geometry
+// How a phase's rows map onto lanes (computed on the host, mega_phase_prepare).  K-quants: item = half a super-block
+// (128 weights); a (row, K-split) takes lpr = 2*nb/S lanes; when that is a power of two below 32, rpp = 32/lpr rows
+// share a warp pass.  Q8_0: lane l takes the 16-byte pieces l, l+32, ... (np of them) of its K-split.
+inline bool mg_split(int fmt, int64_t K, int &S, int &lpr, int &rpp, int &np) {
+    np = 0;
+    if (fmt == ACT_Q8_K) {
+        if (K % 256) return false;
+        const int nb = (int)(K / 256);
+        if (nb > MG_PB * MG_WARPS) return false;
+        for (S = 1; S <= MG_WARPS; S *= 2)
+            if (nb % S == 0 && 2 * nb / S <= 32) {
+                lpr = 2 * nb / S;
+                rpp = (lpr & (lpr - 1)) == 0 ? 32 / lpr : 1;
+                return true;
+            }
+        return false;
+    }
+    if (fmt == ACT_Q8_0) {
+        if (K / 256 > MG_PB * MG_WARPS) return false;
+        for (S = 1; S <= MG_WARPS; S *= 2)
+            if (K % (S * 512) == 0 && K / S <= 8192) {
+                lpr = 32;
+                rpp = 1;
+                np = (int)(K / S / 512);
+                return true;
+            }
+        return false;
+    }
+    return false;
 }
-__device__ __forceinline__ void prefetch_l2(const void *p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+
+// Tile geometry of one matrix: rb = bytes of one row's K-split (= the row pitch inside a tile), R = rows per tile.
+inline bool mg_job_geo(int type, int64_t K, int64_t row_stride, int S, int rpp, int &rb, int &R) {
+    const int64_t nb = K / 256;
+    if (type == B2_T_Q4_K) rb = (int)(S == 1 ? row_stride : 144 * nb / S);
+    else if (type == B2_T_Q6_K) rb = (int)(S == 1 ? row_stride : Q6_BLK * nb / S);
+    else if (type == B2_T_Q8_0) rb = (int)(S == 1 ? row_stride : K / S + K / S / 16);
+    else return false;
+    if (rb <= 0 || rb % 16) return false;
+    R = MG_STAGE_BYTES / rb;
+    if (R > MG_MAX_PASS * rpp) R = MG_MAX_PASS * rpp;
+    if (S > 1 && R > 32) R = 32; // one lane issues one row's copy
+    R = R / rpp * rpp;
+    if (rpp == 1) { // the row loops work on groups of 4 (Q4_K) / 2 (Q6_K) rows with a merged reduction
+        const int grp = type == B2_T_Q4_K ? 4 : type == B2_T_Q6_K ? 2 : 1;
+        if (R >= grp) R = R / grp * grp;
+    }
+    return R >= rpp && R > 0;
 }
-__device__ __forceinline__ void consumer_sync() { asm volatile("bar.sync 2, %0;" ::"n"(MEGA_CT) : "memory"); }
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
+
+// ------------------------------------------------------------------------------------------------ primitives
+__device__ __forceinline__ uint32_t mg_s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mg_mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mg_s32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mg_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mg_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MG_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MG_DONE_%=;\n"
+        "bra MG_WAIT_%=;\n"
+        "MG_DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void mg_bulk(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ int4 mg_lds128(uint32_t a) {
+    int4 r;
+    asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ int2 mg_lds64(uint32_t a) {
+    int2 r;
+    asm volatile("ld.shared.v2.b32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ uint32_t mg_lds_u16(uint32_t a) {
+    uint32_t r;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(r) : "r"(a));
+    return r;
+}
+__device__ __forceinline__ uint32_t mg_ldg_u16(const void *p) {
+    uint32_t r;
+    asm volatile("ld.global.nc.u16 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ int mg_dp4a_us(uint32_t a, int b, int c) { // 4 x (u8 * s8) + c
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ unsigned mg_ld_acquire(const unsigned *p) {
     unsigned v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 
-// sense-reversing grid barrier; called by ONE thread per CTA after a CTA-level barrier.  `gen` is the caller's copy
-// of the generation counter (read once at kernel start).  arrive = acq_rel RMW on the count, the last arriver resets
-// the count and release-increments the generation, everyone else acquire-polls the generation.
-__device__ __forceinline__ void grid_barrier(unsigned *bar, unsigned n_cta, unsigned &gen) {
-    unsigned prev;
-    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(prev) : "l"(bar) : "memory");
-    if (prev == n_cta - 1) {
-        asm volatile("st.relaxed.gpu.global.u32 [%0], 0;" ::"l"(bar) : "memory");
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar + 1) : "memory");
-    } else {
-        while (ld_acquire_u32(bar + 1) == gen) { }
-    }
-    gen++;
+// Grid barrier: ONE monotonically growing arrival counter.  A CTA arrives with a fire-and-forget release reduction
+// and acquire-polls the same word until it reaches base + (k+1) * n_cta; nothing is ever reset, so there is no
+// last-arriver special case and no second word to hand over.  Measured against the alternatives on B200
+// (scratch/ubench/barrier_bench.cu, 148 CTAs): 1.5k cycles, vs 1.8k cooperative-groups grid.sync, 2.7k counter +
+// generation word, 4.7k per-CTA flags.
+__device__ __forceinline__ void mg_grid_barrier(unsigned *cnt, unsigned target) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(cnt) : "memory");
+    while ((int)(mg_ld_acquire(cnt) - target) < 0) { }
+}
+
+inline int64_t mg_act_row_bytes_host(int fmt, int64_t K) {
+    const int64_t b = fmt == ACT_Q8_K ? K + K / 256 * 4 + K / 16 * 2 : K + K / 32 * 4;
+    return (b + 15) / 16 * 16;
 }
 
 // This CTA's share of a phase: a contiguous range of rows (pair-aligned for PLAIN/QKV) in the concatenated row space.
-__device__ __forceinline__ void cta_range(const MegaPhase &ph, int cta, int n_cta, int &u, int &u_end) {
+__device__ __forceinline__ void mg_cta_range(const MegaPhase &ph, int cta, int n_cta, int &u, int &u_end) {
     if (ph.kind == PH_ATT) { u = u_end = 0; return; }
-    const int64_t a = (int64_t)ph.units * cta / n_cta, b = (int64_t)ph.units * (cta + 1) / n_cta;
+    // units_q = units / n_cta and units_r = units % n_cta come from the host: the first units_r CTAs take one more
+    const int a = cta * ph.units_q + min(cta, ph.units_r), b = a + ph.units_q + (cta < ph.units_r ? 1 : 0);
     const int mul = ph.kind == PH_SWIGLU ? 1 : 2;
-    u = (int)a * mul;
-    u_end = (int)b * mul;
+    u = a * mul;
+    u_end = b * mul;
 }
-
 // row `u` of the concatenated row space -> (job, local row)
-__device__ __forceinline__ void locate_row(const MegaPhase &ph, int u, int &jb, int &row) {
+__device__ __forceinline__ void mg_locate_row(const MegaPhase &ph, int u, int &jb, int &row) {
     jb = 0;
     row = u;
     while (jb + 1 < ph.n_jobs && row >= (int)ph.job[jb].rows) { row -= (int)ph.job[jb].rows; jb++; }
 }
 
-// ------------------------------------------------------------------------------------------------ the kernel
-__global__ void __launch_bounds__(MEGA_THREADS, 1)
-decode_mega_kernel(const MegaArgs a) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *xs = smem;
-    float *partial = (float *)(smem + MEGA_OFF_PART);
-    double *s_part = (double *)(smem + MEGA_OFF_RED);
-    volatile unsigned long long *consumed = (volatile unsigned long long *)(smem + MEGA_OFF_CNT);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int cta = blockIdx.x, n_cta = gridDim.x;
+// ------------------------------------------------------------------------------------------------ tile schedule
+// A warp's walk over its weight tiles: phase by phase, matrix by matrix, R rows at a time.  Producer and consumer
+// each keep one cursor over the SAME sequence; the producer's runs MG_STAGES tiles ahead, across phase boundaries.
+// The cursors live in SHARED memory: with ~220 KB of it in use the L1 is a few KB, so a register spill is an L2 round
+// trip, and two 20-register cursors are exactly what the register allocator would spill.
+struct MgCur {
+    int p, j;          // phase, job (matrix) inside the phase
+    int r, r1;         // job-local rows still to do for this warp: [r, r1)
+    int type, S, q, rb, R;
+    int dr_off;        // index of job-local row r in the phase's partial-sum rows = dr_off + r
+    int ks;            // K / S
+    int64_t stride, koff, K;
+    const uint8_t *W;
+    bool ok;
+};
 
-    if (tid == 0) *consumed = 0ull;
+// Position the cursor on the first (phase, job) at or after (c.p, c.j) in which this warp has rows.
+// Phase descriptors: the window [p_cur, p_cur + MG_PH_WIN) is in shared memory (a dependent chain of L2 round trips
+// per seek otherwise); anything further ahead -- only tiny models get there -- is read from global memory.
+__device__ __forceinline__ const MegaPhase &mg_phase(const MegaArgs &a, const MegaPhase *sph, int p_cur, int p) {
+    return (unsigned)(p - p_cur) < (unsigned)MG_PH_WIN ? sph[p & (MG_PH_WIN - 1)] : a.phases[p];
+}
+__device__ __forceinline__ void mg_seek(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *cp, int cta, int n_cta, int warp) {
+    MgCur &c = *cp;
+    c.ok = false;
+    while (c.p < a.n_phases) {
+        const MegaPhase &ph = mg_phase(a, sph, p_cur, c.p);
+        if (ph.kind != PH_ATT) {
+            int u, u_end;
+            mg_cta_range(ph, cta, n_cta, u, u_end);
+            const int S = ph.S, g_log = 3 - ph.s_log, g = warp >> ph.s_log; // MG_WARPS = 8 = S * 2^g_log row groups
+            while (c.j < ph.n_jobs && u < u_end) {
+                const FusedJob &job = ph.job[c.j];
+                int lo, hi, dr_off;
+                if (ph.kind == PH_SWIGLU) {
+                    lo = u; hi = u_end;
+                    dr_off = c.j * (u_end - u) - u;
+                } else {
+                    const int j0 = ph.j0[c.j];
+                    lo = max(u, j0) - j0;
+                    hi = min(u_end, j0 + (int)job.rows) - j0;
+                    dr_off = j0 - u;
+                }
+                if (hi > lo) {
+                    const int n = hi - lo;
+                    c.r = lo + ((n * g) >> g_log);
+                    c.r1 = lo + ((n * (g + 1)) >> g_log);
+                    if (c.r1 > c.r) {
+                        c.type = job.type; c.S = S; c.q = warp & (S - 1); c.rb = ph.rb[c.j]; c.R = ph.R[c.j];
+                        c.dr_off = dr_off; c.K = ph.K; c.ks = (int)(ph.K >> ph.s_log);
+                        c.stride = job.row_stride; c.W = job.W;
+                        const int64_t nbs = (ph.K >> 8) >> ph.s_log;
+                        c.koff = job.type == B2_T_Q4_K ? c.q * nbs * 144 : job.type == B2_T_Q6_K ? c.q * nbs * Q6_BLK : (int64_t)c.q * c.ks;
+                        c.ok = true;
+                        return;
+                    }
+                }
+                c.j++;
+            }
+        }
+        c.p++;
+        c.j = 0;
+    }
+}
+
+// What a ring stage holds, written by the producer side when it issues the copies and read by the consumer side.
+struct MgTile {
+    int p;             // phase the tile belongs to; MG_NO_TILE when the stage is empty
+    int type, n, rb;   // ggml type, rows, row pitch
+    int dr;            // first row's index in the phase's partial-sum rows
+    int pad;
+    int64_t stride;    // Q6_K: row stride and pointer to the fp16 scales of this K-split in the first row
+    const uint8_t *dp;
+};
+constexpr int MG_NO_TILE = 0x7fffffff;
+
+// Issue the bulk copies of the cursor's next tile (n rows) into `stage` and describe it in *t; all lanes call it.
+__device__ __forceinline__ void mg_issue(const MgCur &c, int n, uint32_t stage, uint32_t bar, int lane, MgTile *t) {
+    const uint8_t *src = c.W + (int64_t)c.r * c.stride;
+    t->p = c.p; t->type = c.type; t->n = n; t->rb = c.rb; t->dr = c.dr_off + c.r; t->stride = c.stride;
+    t->dp = src + (c.K >> 8) * Q6_BLK + 2 * (int64_t)c.q * (c.ks >> 8);
+    if (c.S == 1) { // whole rows, contiguous in memory: one copy
+        if (lane == 0) {
+            const uint32_t bytes = (uint32_t)(n * c.stride);
+            mg_expect_tx(bar, bytes);
+            mg_bulk(stage, src, bytes, bar);
+        }
+    } else {        // one K-split of n rows: a copy per row (Q8_0: its int8 range and its scale range)
+        if (lane == 0) mg_expect_tx(bar, (uint32_t)(n * c.rb));
+        __syncwarp();
+        if (lane < n) {
+            const uint8_t *s = src + (int64_t)lane * c.stride;
+            const uint32_t dst = stage + lane * c.rb;
+            if (c.type == B2_T_Q8_0) {
+                mg_bulk(dst, s + c.koff, (uint32_t)c.ks, bar);
+                mg_bulk(dst + c.ks, s + c.K + c.koff / 16, (uint32_t)(c.ks / 16), bar);
+            } else {
+                mg_bulk(dst, s + c.koff, (uint32_t)c.rb, bar);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ int mg_tile_rows(const MgCur &c) { return min(c.R, c.r1 - c.r); }
+__device__ __forceinline__ void mg_advance(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *c, int n, int cta, int n_cta,
+                                           int warp) {
+    const int r = c->r + n;
+    c->r = r;
+    if (r >= c->r1) {
+        c->j++;
+        mg_seek(a, sph, p_cur, c, cta, n_cta, warp);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ block dots
+// A lane's place in a phase (fixed for the whole phase, so its activations stay in registers).
+struct MgLane {
+    int sr;       // which of the rpp rows of a warp pass
+    int kb, h;    // K-quants: super-block inside the K-split, half of it
+    int span;     // lanes that hold one row's partial sums (32, or lpr when rows share a pass)
+    bool on, head; // lane takes part; lane writes the row's sum
+};
+
+// Q4_K, one half super-block (sub-blocks 4h..4h+3 = 64 bytes of nibbles) against the lane's 128 activations.
+//   block: [d f16][dmin f16][12 B packed 6-bit scales/mins][128 B nibbles]; group j (32 B): low nibbles = sub-block
+//   2j, high nibbles = sub-block 2j+1.  xr[8s..8s+7] = int8 activations of the lane's sub-block s, bs32[s] their sum.
+__device__ __forceinline__ float mg_dot_q4k(uint32_t blk, int h, const int (&xr)[32], float dx, const int (&bs32)[4]) {
+    const int4 hdr = mg_lds128(blk);
+    const uint32_t qa = blk + 16 + 64 * h;
+    const int4 q0 = mg_lds128(qa), q1 = mg_lds128(qa + 16), q2 = mg_lds128(qa + 32), q3 = mg_lds128(qa + 48);
+    // the 4 scales / 4 mins of this half, one per byte (ggml's kmask unpacking of the 12 packed bytes)
+    const uint32_t u0 = hdr.y, u1 = hdr.z, u2 = hdr.w;
+    const uint32_t sc_hi = (u2 & 0x0F0F0F0Fu) | ((u0 >> 2) & 0x30303030u);
+    const uint32_t mn_hi = ((u2 >> 4) & 0x0F0F0F0Fu) | ((u1 >> 2) & 0x30303030u);
+    const uint32_t sc4 = h ? sc_hi : (u0 & 0x3F3F3F3Fu), mn4 = h ? mn_hi : (u1 & 0x3F3F3F3Fu);
+    const uint32_t w[16] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y,
+                            (uint32_t)q1.z, (uint32_t)q1.w, (uint32_t)q2.x, (uint32_t)q2.y, (uint32_t)q2.z, (uint32_t)q2.w,
+                            (uint32_t)q3.x, (uint32_t)q3.y, (uint32_t)q3.z, (uint32_t)q3.w};
+    int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        s0 = mg_dp4a_us(w[i] & 0x0F0F0F0Fu, xr[i], s0);
+        s1 = mg_dp4a_us(w[i] & 0xF0F0F0F0u, xr[8 + i], s1); // 16 * (high nibbles . x)
+        s2 = mg_dp4a_us(w[8 + i] & 0x0F0F0F0Fu, xr[16 + i], s2);
+        s3 = mg_dp4a_us(w[8 + i] & 0xF0F0F0F0u, xr[24 + i], s3);
+    }
+    const int isum = (int)(sc4 & 0xFF) * s0 + (int)((sc4 >> 8) & 0xFF) * (s1 >> 4) + (int)((sc4 >> 16) & 0xFF) * s2 +
+                     (int)(sc4 >> 24) * (s3 >> 4);
+    const int imin = (int)(mn4 & 0xFF) * bs32[0] + (int)((mn4 >> 8) & 0xFF) * bs32[1] + (int)((mn4 >> 16) & 0xFF) * bs32[2] +
+                     (int)(mn4 >> 24) * bs32[3];
+    const float2 dd = __half22float2(*(const __half2 *)&hdr.x);
+    return (dd.x * dx) * (float)isum - (dd.y * dx) * (float)imin;
+}
+
+// Q6_K, one half super-block n (weights 128n..128n+127) of a 208-byte device block [ql 128][qh 64][scales 16]:
+//   ql[64n + l] low/high nibble -> weights l / 64+l, ql[64n + 32 + l] -> 32+l / 96+l, qh[32n + l] holds their four
+//   2-bit tops; scale of the 16-weight sub-block (column c = 0..3, half hf = l/16): sc[8n + 2c + hf].
+//   xr[8c + i] = activations of column c, word i; bs16[2c + hf] = their 16-element sums.  d is the fp16 row-tail scale.
+__device__ __forceinline__ float mg_dot_q6k(uint32_t blk, int n, const int (&xr)[32], float dx, const int (&bs16)[8], uint32_t d16) {
+    const uint32_t la = blk + 64 * n;
+    const int4 a0 = mg_lds128(la), a1 = mg_lds128(la + 16), b0 = mg_lds128(la + 32), b1 = mg_lds128(la + 48);
+    const int4 h0 = mg_lds128(blk + 128 + 32 * n), h1 = mg_lds128(blk + 144 + 32 * n);
+    const int2 scw = mg_lds64(blk + 192 + 8 * n);
+    const uint32_t A[8] = {(uint32_t)a0.x, (uint32_t)a0.y, (uint32_t)a0.z, (uint32_t)a0.w, (uint32_t)a1.x, (uint32_t)a1.y, (uint32_t)a1.z, (uint32_t)a1.w};
+    const uint32_t B[8] = {(uint32_t)b0.x, (uint32_t)b0.y, (uint32_t)b0.z, (uint32_t)b0.w, (uint32_t)b1.x, (uint32_t)b1.y, (uint32_t)b1.z, (uint32_t)b1.w};
+    const uint32_t H[8] = {(uint32_t)h0.x, (uint32_t)h0.y, (uint32_t)h0.z, (uint32_t)h0.w, (uint32_t)h1.x, (uint32_t)h1.y, (uint32_t)h1.z, (uint32_t)h1.w};
+    int s[4][2] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int hf = i >> 2;
+        const uint32_t hh = H[i];
+        s[0][hf] = mg_dp4a_us((A[i] & 0x0F0F0F0Fu) | ((hh << 4) & 0x30303030u), xr[i], s[0][hf]);
+        s[1][hf] = mg_dp4a_us((B[i] & 0x0F0F0F0Fu) | ((hh << 2) & 0x30303030u), xr[8 + i], s[1][hf]);
+        s[2][hf] = mg_dp4a_us(((A[i] >> 4) & 0x0F0F0F0Fu) | (hh & 0x30303030u), xr[16 + i], s[2][hf]);
+        s[3][hf] = mg_dp4a_us(((B[i] >> 4) & 0x0F0F0F0Fu) | ((hh >> 2) & 0x30303030u), xr[24 + i], s[3][hf]);
+    }
+    // stored quants are q+32: subtract 32 * sum(x) of each 16-weight sub-block (exact, integer)
+    int isum = 0;
+#pragma unroll
+    for (int c = 0; c < 4; c++)
+#pragma unroll
+        for (int hf = 0; hf < 2; hf++) {
+            const int k = 2 * c + hf;
+            const uint32_t word = k < 4 ? (uint32_t)scw.x : (uint32_t)scw.y;
+            const int scale = (int)(int8_t)((word >> (8 * (k & 3))) & 0xFF);
+            isum += scale * (s[c][hf] - 32 * bs16[k]);
+        }
+    return (h2f((uint16_t)d16) * dx) * (float)isum;
+}
+
+// warp-reduce over the `span` lanes that hold one row (span = 32, or a power of two when rows share a pass)
+__device__ __forceinline__ float mg_row_sum(float v, int span) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+        if (o < span) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Merged butterfly reductions: the sums of 4 (2) per-lane values over the whole warp in 6 (5) shuffles instead of
+// 20 (10).  Result: the lane with (lane & 7) == 0 holds row 2*bit3 + bit4 (lanes 0/16/8/24 = rows 0/1/2/3);
+// mg_reduce2: lanes 0/16 = rows 0/1.
+__device__ __forceinline__ float mg_reduce4(const float (&v)[4], int lane) {
+    const bool b4 = lane & 16, b3 = lane & 8;
+    const float a01 = (b4 ? v[1] : v[0]) + __shfl_xor_sync(0xffffffffu, b4 ? v[0] : v[1], 16);
+    const float a23 = (b4 ? v[3] : v[2]) + __shfl_xor_sync(0xffffffffu, b4 ? v[2] : v[3], 16);
+    float b = (b3 ? a23 : a01) + __shfl_xor_sync(0xffffffffu, b3 ? a01 : a23, 8);
+    b += __shfl_xor_sync(0xffffffffu, b, 4);
+    b += __shfl_xor_sync(0xffffffffu, b, 2);
+    b += __shfl_xor_sync(0xffffffffu, b, 1);
+    return b;
+}
+__device__ __forceinline__ float mg_reduce2(float v0, float v1, int lane) {
+    const bool b4 = lane & 16;
+    float t = (b4 ? v1 : v0) + __shfl_xor_sync(0xffffffffu, b4 ? v0 : v1, 16);
+    t += __shfl_xor_sync(0xffffffffu, t, 8);
+    t += __shfl_xor_sync(0xffffffffu, t, 4);
+    t += __shfl_xor_sync(0xffffffffu, t, 2);
+    t += __shfl_xor_sync(0xffffffffu, t, 1);
+    return t;
+}
+
+
+// ------------------------------------------------------------------------------------------------ attention
+// One (head, query token) per CTA, written for LATENCY: at short context the phase is a chain of dependent global
+// round trips, so everything whose address is known up front is requested up front.  The page table of the sequence
+// is in shared memory since kernel start; the K rows (2 threads per position, half a row each) and the V rows of the
+// first 256 positions (lane owns hd/32 dims, warp w owns positions w, w+8, ...) are loaded into registers BEFORE q is
+// waited for; the QKV phase has already pulled the sequence's K/V rows into L2 (mg_prefetch_kv).
+// Numerics as attention_head (attention.cuh): q and the normalised probabilities rounded to f16, fp32 accumulation.
+// scratch: q[hd] | red[32] | part[8][hd] | scores[n_kv].  hd = 64 or 128.
+__device__ __forceinline__ const __half *mg_kv_row(const __half *pool, const int *pbase, int j, int page_shift, int kvd) {
+    return pool + ((((int64_t)pbase[j >> page_shift]) << page_shift) + (j & ((1 << page_shift) - 1))) * kvd;
+}
+__device__ __noinline__ void mg_attention(const float *__restrict__ qrow, int n_kv, const int *pbase, const __half *k_pool,
+                                             const __half *v_pool, int page_shift, int kvd, int hk, int hd, float scale,
+                                             float *__restrict__ orow, float *scratch, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+    float *qs = scratch, *red = qs + hd, *part = red + 32, *sc = part + MG_WARPS * hd;
+    const int half = tid & 1, hh = hd / 2, nld = hh / 8;  // pass 1: this thread's half row = nld 16-byte loads (<= 8)
+    const int dpl = hd / 32, nw = dpl / 2;                // pass 2: halves / 32-bit words per lane (<= 2 words)
+    constexpr int KR = 2, KP = MG_THREADS / 2;            // K: 2 rounds of 128 positions per sweep
+    constexpr int VP = 32;                                // V: 32 positions per warp per sweep, position = j0 + warp + 8u
+    int4 kq[KR][8];
+    uint32_t vq[VP][2];
+    auto load_k = [&](int j0) {
+#pragma unroll
+        for (int r = 0; r < KR; r++) {
+            const int j = j0 + r * KP + (tid >> 1);
+            if (j < n_kv) {
+                const __half *kr = mg_kv_row(k_pool, pbase, j, page_shift, kvd) + hk * hd + half * hh;
+#pragma unroll
+                for (int i = 0; i < 8; i++)
+                    if (i < nld) kq[r][i] = *(const int4 *)(kr + i * 8);
+            }
+        }
+    };
+    auto load_v = [&](int j0) {
+#pragma unroll
+        for (int u = 0; u < VP; u++) {
+            const int jv = j0 + warp + MG_WARPS * u;
+            if (jv < n_kv) {
+                const __half *vr = mg_kv_row(v_pool, pbase, jv, page_shift, kvd) + hk * hd + lane * dpl;
+                if (nw == 2) { const int2 t = *(const int2 *)vr; vq[u][0] = t.x; vq[u][1] = t.y; }
+                else vq[u][0] = *(const uint32_t *)vr;
+            }
+        }
+    };
+    // ---- everything that needs no activation is requested first: the first 256 positions' K and V
+    load_k(0);
+    load_v(0);
+    for (int i = tid; i < hd; i += MG_THREADS) qs[i] = __half2float(__float2half_rn(__ldcg(qrow + i))); // q comes from other SMs
     __syncthreads();
 
-    if (warp == MEGA_CW) {
-        // ================= PREFETCHER: one lane pulls this CTA's weights into L2, a bounded distance ahead =================
-        if (lane != 0) return;
-        unsigned long long issued = 0;
-        auto pf = [&](const uint8_t *p, long long bytes) {
-            while (bytes > 0) {
-                const uint32_t n = (uint32_t)min((long long)MEGA_PF_CHUNK, bytes);
-                while ((long long)(issued - *consumed) > MEGA_PF_AHEAD) __nanosleep(100);
-                prefetch_l2(p, n);
-                p += n;
-                bytes -= n;
-                issued += n;
+    // ---- pass 1: scores
+    float lmax = -INFINITY;
+    for (int j0 = 0; j0 < n_kv; j0 += KR * KP) {
+        if (j0 > 0) load_k(j0);
+#pragma unroll
+        for (int r = 0; r < KR; r++) {
+            const int j = j0 + r * KP + (tid >> 1);
+            float acc = 0.f;
+            if (j < n_kv) {
+                const float *qh = qs + half * hh;
+#pragma unroll
+                for (int i = 0; i < 8; i++)
+                    if (i < nld) {
+                        const __half2 *kh = (const __half2 *)&kq[r][i];
+                        const float4 qa = *(const float4 *)(qh + i * 8), qb = *(const float4 *)(qh + i * 8 + 4);
+                        const float2 k0 = __half22float2(kh[0]), k1 = __half22float2(kh[1]), k2 = __half22float2(kh[2]), k3 = __half22float2(kh[3]);
+                        acc += k0.x * qa.x; acc += k0.y * qa.y; acc += k1.x * qa.z; acc += k1.y * qa.w;
+                        acc += k2.x * qb.x; acc += k2.y * qb.y; acc += k3.x * qb.z; acc += k3.y * qb.w;
+                    }
             }
-        };
-        for (int p = 0; p < a.n_phases; p++) {
-            const MegaPhase &ph = a.phases[p];
-            int u, u_end;
-            cta_range(ph, cta, n_cta, u, u_end);
-            if (ph.kind == PH_SWIGLU) {
-                const int64_t s0 = ph.job[0].row_stride, s1 = ph.job[1].row_stride;
-                const int step = max(1, (int)(MEGA_PF_CHUNK / s0));
-                for (int r = u; r < u_end; r += step) {
-                    const int n = min(step, u_end - r);
-                    pf(ph.job[0].W + (int64_t)r * s0, (long long)n * s0);
-                    pf(ph.job[1].W + (int64_t)r * s1, (long long)n * s1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            if (j < n_kv) {
+                acc *= scale;
+                if (half == 0) sc[j] = acc;
+                lmax = fmaxf(lmax, acc);
+            }
+        }
+    }
+    lmax = warp_max(lmax);
+    if (lane == 0) red[warp] = lmax;
+    __syncthreads();
+    float mx = red[0];
+#pragma unroll
+    for (int i = 1; i < MG_WARPS; i++) mx = fmaxf(mx, red[i]);
+    float lsum = 0.f;
+    for (int j = tid; j < n_kv; j += MG_THREADS) {
+        const float e = expf(sc[j] - mx);
+        sc[j] = e;
+        lsum += e;
+    }
+    lsum = warp_sum(lsum);
+    if (lane == 0) red[16 + warp] = lsum;
+    __syncthreads();
+    double tot = 0.0;
+#pragma unroll
+    for (int i = 0; i < MG_WARPS; i++) tot += (double)red[16 + i];
+    const float inv = (float)(1.0 / tot);
+    for (int j = tid; j < n_kv; j += MG_THREADS) sc[j] = __half2float(__float2half_rn(__fmul_rn(sc[j], inv)));
+    __syncthreads();
+
+    // ---- pass 2: out = sum_j p_j v_j
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int j0 = 0; j0 < n_kv; j0 += VP * MG_WARPS) {
+        if (j0 > 0) load_v(j0);
+#pragma unroll
+        for (int u = 0; u < VP; u++) {
+            const int jv = j0 + warp + MG_WARPS * u;
+            if (jv < n_kv) {
+                const float pj = sc[jv];
+#pragma unroll
+                for (int k = 0; k < 2; k++)
+                    if (k < nw) {
+                        const float2 vv = __half22float2(*(const __half2 *)&vq[u][k]);
+                        acc[2 * k] += vv.x * pj;
+                        acc[2 * k + 1] += vv.y * pj;
+                    }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (i < dpl) part[warp * hd + lane * dpl + i] = acc[i];
+    __syncthreads();
+    for (int i = tid; i < hd; i += MG_THREADS) {
+        float o = 0.f;
+#pragma unroll
+        for (int w = 0; w < MG_WARPS; w++) o += part[w * hd + i];
+        orow[i] = o;
+    }
+    __syncthreads();
+}
+
+// Pull the K/V rows (positions < n_kv) of one KV head into L2 ahead of the attention phase.
+__device__ __forceinline__ void mg_prefetch_kv(int n_kv, const int *pbase, const __half *k_pool, const __half *v_pool, int page_shift,
+                                               int kvd, int hk, int hd, int tid) {
+    for (int j = tid; j < n_kv; j += MG_THREADS) {
+        const __half *kr = mg_kv_row(k_pool, pbase, j, page_shift, kvd) + hk * hd;
+        const __half *vr = mg_kv_row(v_pool, pbase, j, page_shift, kvd) + hk * hd;
+        for (int b = 0; b < hd * 2; b += 128) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)kr + b));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"((const char *)vr + b));
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ phase prologue
+// 16-byte chunk c of the int8 activation section is stored at chunk c ^ ((c >> 3) & 7): the lanes of a quarter warp
+// then read their register slices (stride 128 B = one bank group) from 8 different bank groups.
+__device__ __forceinline__ int mg_swz(int c) { return c ^ ((c >> 3) & 7); }
+
+// (RMSNorm ->) quantise the activation row into shared memory, redundantly per CTA.  Written for LATENCY: warp w owns
+// the 256-element blocks w, w+8, ... (PBN of them, all in registers), every global load is issued before the first
+// use, invalid blocks are carried as zeros instead of branches so that the PBN dependency chains interleave, and the
+// warp-wide maxima are hardware reductions (redux.sync) instead of shuffle trees.  Results are bit-exact with
+// quantize_row_q8_K_ref / quantize_row_q8_0_ref (act_quant.cuh holds the same arithmetic for the other kernels).
+template <int PBN>
+__device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t *xs, double *s_part, int nb, int k_first, int warp,
+                                         int lane, bool write_xn) {
+    const int64_t K = ph.K;
+    const float *xrow = ph.x;
+    const bool has_norm = ph.norm_w != nullptr;
+    float v[PBN][8], w[PBN <= 2 ? PBN : 1][8];
+    bool valid[PBN];
+#pragma unroll
+    for (int k = 0; k < PBN; k++) {
+        const int b = warp + (k_first + k) * MG_WARPS;
+        valid[k] = b < nb;
+        const float4 *xb = (const float4 *)(xrow + (valid[k] ? b : 0) * 256 + lane * 8);
+        const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1); // the row was written by other SMs: L2
+        v[k][0] = a0.x; v[k][1] = a0.y; v[k][2] = a0.z; v[k][3] = a0.w;
+        v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
+        if (PBN <= 2 && has_norm) { // norm weights ride the same round trip
+            const float4 *wb = (const float4 *)(ph.norm_w + (valid[k] ? b : 0) * 256 + lane * 8);
+            const float4 w0 = wb[0], w1 = wb[1];
+            w[k][0] = w0.x; w[k][1] = w0.y; w[k][2] = w0.z; w[k][3] = w0.w;
+            w[k][4] = w1.x; w[k][5] = w1.y; w[k][6] = w1.z; w[k][7] = w1.w;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < PBN; k++)
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[k][i] = valid[k] ? v[k][i] : 0.f;
+    if (has_norm) {
+        double sum = 0.0;
+#pragma unroll
+        for (int k = 0; k < PBN; k++)
+#pragma unroll
+            for (int i = 0; i < 8; i++) sum += (double)__fmul_rn(v[k][i], v[k][i]);
+        sum = warp_sum_d(sum);
+        if (lane == 0) s_part[warp] = sum;
+        __syncthreads();
+        double tot = 0.0;
+#pragma unroll
+        for (int i = 0; i < MG_WARPS; i++) tot += s_part[i]; // every thread: same order, same result
+        const float mean = (float)(tot / (double)K);
+        const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+#pragma unroll
+        for (int k = 0; k < PBN; k++) {
+            const int b = warp + (k_first + k) * MG_WARPS;
+            if (PBN > 2 && valid[k]) {
+                const float4 *wb = (const float4 *)(ph.norm_w + b * 256 + lane * 8);
+                const float4 w0 = wb[0], w1 = wb[1];
+                const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[k][i] = __fmul_rn(__fmul_rn(v[k][i], scale), wv[i]);
+            } else if (PBN <= 2) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[k][i] = __fmul_rn(__fmul_rn(v[k][i], scale), w[PBN <= 2 ? k : 0][i]);
+            }
+            if (write_xn && valid[k]) { // the normalised row itself (embeddings)
+                float *o = ph.xn_out + b * 256 + lane * 8;
+                *(float4 *)o = make_float4(v[k][0], v[k][1], v[k][2], v[k][3]);
+                *(float4 *)(o + 4) = make_float4(v[k][4], v[k][5], v[k][6], v[k][7]);
+            }
+        }
+    }
+    if (ph.fmt == ACT_Q8_K) {
+        // [qs: K x int8 (chunk-swizzled)][d: K/256 x f32][bsums: K/16 x int16]
+        constexpr int QB = PBN < 4 ? PBN : 4; // blocks quantised together (interleaved dependency chains)
+#pragma unroll
+        for (int k0 = 0; k0 < PBN; k0 += QB) {
+            uint32_t amax[QB], idx[QB];
+#pragma unroll
+            for (int kk = 0; kk < QB; kk++) {
+                const int k = k0 + kk;
+                float m = 0.f;
+#pragma unroll
+                for (int i = 0; i < 8; i++) m = fmaxf(m, fabsf(v[k][i]));
+                amax[kk] = __reduce_max_sync(0xffffffffu, __float_as_uint(m)); // non-negative floats order like their bits
+            }
+#pragma unroll
+            for (int kk = 0; kk < QB; kk++) { // the FIRST element (in index order) with the largest |x|
+                const int k = k0 + kk;
+                uint32_t li = 0x7fffffffu;
+#pragma unroll
+                for (int i = 7; i >= 0; i--)
+                    if (__float_as_uint(fabsf(v[k][i])) == amax[kk]) li = lane * 8 + i;
+                idx[kk] = __reduce_min_sync(0xffffffffu, li);
+            }
+#pragma unroll
+            for (int kk = 0; kk < QB; kk++) {
+                const int k = k0 + kk;
+                float sel = v[k][0];
+#pragma unroll
+                for (int i = 1; i < 8; i++) sel = (idx[kk] & 7) == i ? v[k][i] : sel;
+                const float mx = __shfl_sync(0xffffffffu, sel, idx[kk] >> 3);
+                const bool zero = amax[kk] == 0u;
+                const float iscale = zero ? 0.f : __fdiv_rn(-127.f, mx);
+                int sum = 0;
+                int q[8];
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    int vi = __float2int_rn(__fmul_rn(iscale, v[k][i])); // nearest_int(): round-half-even
+                    vi = min(127, vi);
+                    q[i] = vi;
+                    sum += vi;
                 }
-            } else {
-                while (u < u_end) {
-                    int jb, row;
-                    locate_row(ph, u, jb, row);
-                    const int n = min(u_end - u, (int)ph.job[jb].rows - row);
-                    pf(ph.job[jb].W + (int64_t)row * ph.job[jb].row_stride, (long long)n * ph.job[jb].row_stride);
-                    u += n;
+                sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+                const int b = warp + (k_first + k) * MG_WARPS;
+                if (valid[k]) {
+                    int2 packed;
+                    packed.x = (q[0] & 0xFF) | ((q[1] & 0xFF) << 8) | ((q[2] & 0xFF) << 16) | ((q[3] & 0xFF) << 24);
+                    packed.y = (q[4] & 0xFF) | ((q[5] & 0xFF) << 8) | ((q[6] & 0xFF) << 16) | ((q[7] & 0xFF) << 24);
+                    *(int2 *)(xs + mg_swz(b * 16 + (lane >> 1)) * 16 + (lane & 1) * 8) = packed;
+                    if ((lane & 1) == 0) ((int16_t *)(xs + K + nb * 4))[b * 16 + (lane >> 1)] = (int16_t)sum;
+                    if (lane == 0) ((float *)(xs + K))[b] = zero ? 0.f : __fdiv_rn(1.f, iscale);
                 }
             }
         }
-        return;
+    } else {
+        // ACT_Q8_0: [qs: K x int8 (chunk-swizzled)][d: K/32 x f32 (value of the fp16-rounded scale)]; 32 elements = 4 lanes
+#pragma unroll
+        for (int k = 0; k < PBN; k++) {
+            float amax = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[k][i]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            const float d = __fdiv_rn(amax, 127.f);
+            const float id = d != 0.f ? __fdiv_rn(1.f, d) : 0.f;
+            int q[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) q[i] = (int)roundf(__fmul_rn(v[k][i], id));
+            const int b = warp + (k_first + k) * MG_WARPS;
+            if (valid[k]) {
+                int2 packed;
+                packed.x = (q[0] & 0xFF) | ((q[1] & 0xFF) << 8) | ((q[2] & 0xFF) << 16) | ((q[3] & 0xFF) << 24);
+                packed.y = (q[4] & 0xFF) | ((q[5] & 0xFF) << 8) | ((q[6] & 0xFF) << 16) | ((q[7] & 0xFF) << 24);
+                *(int2 *)(xs + mg_swz(b * 16 + (lane >> 1)) * 16 + (lane & 1) * 8) = packed;
+                if ((lane & 3) == 0) ((float *)(xs + K))[b * 8 + (lane >> 2)] = __half2float(__float2half_rn(d));
+            }
+        }
     }
+    __syncthreads();
+}
 
-    // ================= CONSUMERS =================
+// ------------------------------------------------------------------------------------------------ the kernel
+template <bool DBG>
+__global__ void __launch_bounds__(MG_THREADS, 1)
+decode_mega_kernel(const MegaArgs a) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint8_t *xs = smem + MG_OFF_XS;
+    float *partial = (float *)(smem + MG_OFF_PART);
+    double *s_part = (double *)(smem + MG_OFF_RED);
+    uint64_t *bars = (uint64_t *)(smem + MG_OFF_BAR);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cta = blockIdx.x, n_cta = gridDim.x;
+
+    MegaPhase *sph = (MegaPhase *)(smem + MG_OFF_PH);
+    constexpr int PH_WORDS = (int)(sizeof(MegaPhase) / 4);
+    static_assert(PH_WORDS <= MG_THREADS - 32, "phase descriptor copy");
+    auto stage_phase = [&](int p) { // threads 32.. (thread 0 runs the grid barrier meanwhile); the caller orders it
+        const int t = tid - 32;     // against the readers with __syncthreads
+        if (p < a.n_phases && t >= 0 && t < PH_WORDS) ((uint32_t *)&sph[p & (MG_PH_WIN - 1)])[t] = ((const uint32_t *)&a.phases[p])[t];
+    };
+    for (int p = 0; p < MG_PH_WIN; p++) stage_phase(p);
     const int pos = a.pos[0], sl = a.slot[0];
-    unsigned bar_gen = tid == 0 ? ld_acquire_u32(a.bar + 1) : 0;
-    for (int p = 0; p < a.n_phases; p++) {
-        const MegaPhase &ph = a.phases[p];
-        long long t0 = 0, t1 = 0, t2 = 0;
-        if (a.dbg && tid == 0) t0 = clock64();
-        if (ph.kind == PH_ATT) {
-            KVLayout kv{ph.k_pool, ph.v_pool, a.page_table, a.page_size, a.max_pages, a.kvd};
-            for (int h = cta; h < a.n_head; h += n_cta)
-                attention_head(ph.x + (int64_t)h * a.hd, pos + 1, a.page_table + (int64_t)sl * a.max_pages, kv,
-                               h / (a.n_head / a.n_head_kv), a.hd, a.att_scale, ph.out + (int64_t)h * a.hd, (float *)xs, tid, MEGA_CT);
+    int *pbase = (int *)(smem + MG_OFF_PT); // page of every 32-position block of this sequence (static during the step)
+    for (int i = tid; a.page_table && i < (pos + a.page_size) / a.page_size && i < MG_MAX_PAGES; i += MG_THREADS) pbase[i] = a.page_table[(int64_t)sl * a.max_pages + i];
+    if (tid == 0) {
+        for (int i = 0; i < MG_WARPS * MG_STAGES; i++) mg_mbar_init(bars + i, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    // ---- this warp's ring and its two cursors over the tile schedule
+    const uint32_t ring = mg_s32(smem) + warp * (MG_STAGES * MG_STAGE_BYTES);
+    const uint32_t bar0 = mg_s32(bars + warp * MG_STAGES);
+    static_assert(sizeof(MgCur) <= 96 && sizeof(MgTile) <= 48, "cursor / tile slots");
+    MgCur *pc = (MgCur *)(smem + MG_OFF_CUR + (size_t)warp * 96);
+    MgTile *tiles = (MgTile *)(smem + MG_OFF_TILE + (size_t)warp * MG_STAGES * 48);
+    pc->p = 0; pc->j = 0;
+    mg_seek(a, sph, 0, pc, cta, n_cta, warp);
+    uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
+    for (int s = 0; s < MG_STAGES; s++) {
+        MgTile *t = (MgTile *)((uint8_t *)tiles + s * 48);
+        if (pc->ok) {
+            const int n = mg_tile_rows(*pc);
+            mg_issue(*pc, n, ring + s * MG_STAGE_BYTES, bar0 + s * 8, lane, t);
+            mg_advance(a, sph, 0, pc, n, cta, n_cta, warp);
         } else {
+            t->p = MG_NO_TILE;
+        }
+    }
+    __syncwarp();
+
+    for (int p = 0; p < a.n_phases; p++) {
+        const MegaPhase &ph = sph[p & (MG_PH_WIN - 1)];
+        long long t0 = 0, t1 = 0, t2 = 0, t_wait = 0, t_comp = 0, t_epi = 0, n_tiles = 0, tp0 = 0, tp3 = 0, tl_end = 0, t_advc = 0, t_iss = 0, t_advp = 0;
+        if (DBG && tid == 0) t0 = clock64();
+        int u = 0, u_end = 0;
+        if (ph.kind == PH_ATT) {
+            for (int h = cta; h < a.n_head; h += n_cta)
+                mg_attention(ph.x + (int64_t)h * a.hd, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift, a.kvd,
+                             h / (a.n_head / a.n_head_kv), a.hd, a.att_scale, ph.out + (int64_t)h * a.hd, (float *)xs, tid);
+        } else {
+            mg_cta_range(ph, cta, n_cta, u, u_end);
+        }
+        if (u < u_end) {
             const int64_t K = ph.K;
-            const int nb = (int)(K / 256);
-            const int64_t xrb = act_row_bytes_dev(ph.fmt, K);
-            int u, u_end;
-            cta_range(ph, cta, n_cta, u, u_end);
-            if (u < u_end) {
-                // ---- prologue: (RMSNorm ->) quantise the activation row into shared memory (redundantly per CTA).
-                // One L2 round trip: every warp pulls its (<= MEGA_PB) 256-element blocks into registers with all
-                // loads in flight, the sum of squares is reduced from those registers, then they are quantised.
-                const float *xr = ph.x;
-                float v[MEGA_PB][8];
+            const int nb = (int)(K >> 8);
+            const int S = ph.S, rpp = ph.rpp, np = ph.np;
+            // ---- prologue: (RMSNorm ->) quantise the activation row into shared memory
+            if (DBG && tid == 0) tp0 = clock64();
+            {
+                const bool wx = ph.xn_out && cta == 0;
+                if (nb <= MG_WARPS) mg_prologue<1>(ph, a.eps, xs, s_part, nb, 0, warp, lane, wx);
+                else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, a.eps, xs, s_part, nb, 0, warp, lane, wx);
+                else // 4 blocks per warp at a time; rows longer than 32 blocks have no norm (mega_phase_prepare)
+                    for (int k0 = 0; k0 * MG_WARPS < nb; k0 += 4) mg_prologue<4>(ph, a.eps, xs, s_part, nb, k0, warp, lane, wx);
+            }
+            if (DBG && tid == 0) tp3 = clock64();
+            if (ph.kind == PH_QKV) // the attention phase comes next: start its K/V rows on their way into L2
+                for (int h = cta; h < a.n_head; h += n_cta)
+                    mg_prefetch_kv(pos, pbase, ph.k_pool, ph.v_pool, a.page_shift, a.kvd, h / (a.n_head / a.n_head_kv), a.hd, tid);
+            // ---- this lane's slice of the quantised row -> registers, for the whole phase
+            const int q = warp & (S - 1);
+            const uint32_t xs_a = mg_s32(xs);
+            int xr[32];
+            float dx = 0.f;
+            int bs[8];
+            MgLane L;
+            if (ph.fmt == ACT_Q8_K) {
+                const int lpr = ph.lpr;
+                L.sr = rpp > 1 ? lane >> ph.lpr_log : 0;
+                const int it = lane - L.sr * lpr;
+                L.on = it < lpr && L.sr < rpp;
+                L.kb = L.on ? it >> 1 : 0;
+                L.h = it & 1;
+                L.head = L.on && it == 0;
+                L.span = rpp > 1 ? lpr : 32;
+                const int blk = q * (nb >> ph.s_log) + L.kb;
+                const int c0 = blk * 16 + 8 * L.h; // first 16-byte chunk of this lane's 128 activations
 #pragma unroll
-                for (int k = 0; k < MEGA_PB; k++) {
-                    const int b = warp + k * MEGA_CW;
-                    if (b < nb) {
-                        const float4 *xb = (const float4 *)(xr + b * 256 + lane * 8);
-                        const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1);
-                        v[k][0] = a0.x; v[k][1] = a0.y; v[k][2] = a0.z; v[k][3] = a0.w;
-                        v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
-                    }
+                for (int i = 0; i < 8; i++) {
+                    const int4 t = mg_lds128(xs_a + mg_swz(c0 + i) * 16);
+                    xr[4 * i] = t.x; xr[4 * i + 1] = t.y; xr[4 * i + 2] = t.z; xr[4 * i + 3] = t.w;
                 }
-                float scale = 1.f;
-                if (ph.norm_w) {
-                    double sum = 0.0;
+                dx = ((const float *)(xs + K))[blk];
+                const int *bsp = (const int *)(xs + K + nb * 4 + (blk * 16 + 8 * L.h) * 2); // 8 x int16
 #pragma unroll
-                    for (int k = 0; k < MEGA_PB; k++)
-                        if (warp + k * MEGA_CW < nb) {
-#pragma unroll
-                            for (int i = 0; i < 8; i++) sum += (double)__fmul_rn(v[k][i], v[k][i]);
-                        }
-                    sum = warp_sum_d(sum);
-                    if (lane == 0) s_part[warp] = sum;
-                    consumer_sync();
-                    double tot = 0.0;
-                    for (int i = 0; i < MEGA_CW; i++) tot += s_part[i]; // every thread: same order, same result
-                    const float mean = (float)(tot / (double)K);
-                    scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, a.eps)));
+                for (int i = 0; i < 4; i++) {
+                    const int w2 = bsp[i];
+                    bs[2 * i] = (int)(int16_t)(w2 & 0xFFFF);
+                    bs[2 * i + 1] = w2 >> 16;
                 }
+            } else { // ACT_Q8_0 (1 byte per weight): the activations are read from shared memory next to the weights
+                L.sr = 0; L.kb = 0; L.h = 0; L.on = true; L.head = lane == 0; L.span = 32;
+            }
+            const int bs32[4] = {bs[0] + bs[1], bs[2] + bs[3], bs[4] + bs[5], bs[6] + bs[7]};
+            if (DBG && tid == 0) t1 = clock64();
+
+            // ---- this warp's tiles of the phase
+            while (true) {
+                MgTile *tile = (MgTile *)((uint8_t *)tiles + stg * 48);
+                if (tile->p != p) break;
+                const int n = tile->n, rb = tile->rb, type = tile->type;
+                const uint32_t st = ring + stg * MG_STAGE_BYTES, bar = bar0 + stg * 8;
+                float *pout = partial + (size_t)tile->dr * S + q;
+                long long tw0 = 0, tw1 = 0;
+                if (DBG && tid == 0) tw0 = clock64();
+                if (type == B2_T_Q4_K) {
+                    mg_wait(bar, parity);
+                    if (DBG && tid == 0) tw1 = clock64();
+                    if (rpp == 1) { // 4 rows at a time: independent dp4a chains, one merged reduction
+                        const uint32_t base = st + L.kb * 144;
+#pragma unroll 1
+                        for (int r0 = 0; r0 < n; r0 += 4) {
+                            float v[4];
 #pragma unroll
-                for (int k = 0; k < MEGA_PB; k++) {
-                    const int b = warp + k * MEGA_CW;
-                    if (b < nb) {
-                        if (ph.norm_w) {
-                            const float4 *wb = (const float4 *)(ph.norm_w + b * 256 + lane * 8);
-                            const float4 w0 = wb[0], w1 = wb[1];
-                            const float wv[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-#pragma unroll
-                            for (int i = 0; i < 8; i++) v[k][i] = __fmul_rn(__fmul_rn(v[k][i], scale), wv[i]);
-                            if (ph.xn_out && cta == 0) {
-                                float *o = ph.xn_out + b * 256 + lane * 8;
-                                *(float4 *)o = make_float4(v[k][0], v[k][1], v[k][2], v[k][3]);
-                                *(float4 *)(o + 4) = make_float4(v[k][4], v[k][5], v[k][6], v[k][7]);
+                            for (int k = 0; k < 4; k++) {
+                                v[k] = mg_dot_q4k(base + min(r0 + k, n - 1) * rb, L.h, xr, dx, bs32);
+                                if (!L.on) v[k] = 0.f;
                             }
+                            const float tot = mg_reduce4(v, lane);
+                            const int k = ((lane >> 4) & 1) | ((lane >> 2) & 2);
+                            if ((lane & 7) == 0 && r0 + k < n) pout[(size_t)(r0 + k) * S] = tot;
                         }
-                        quant_block<true>(ph.fmt, v[k], lane, xs, K, b);
-                    }
-                }
-                consumer_sync();
-                if (a.dbg && tid == 0) t1 = clock64();
-                // ---- tasks: (dot row, K-segment); dot rows = this CTA's rows (SwiGLU: its gate rows, then its up rows)
-                const int n_r = u_end - u;
-                const int n_dot = ph.kind == PH_SWIGLU ? 2 * n_r : n_r;
-                int sh = 0;
-                while ((n_dot << sh) < 2 * MEGA_CW && (nb >> (sh + 1)) >= 8 && (n_dot << (sh + 1)) <= MEGA_MAX_PART) sh++;
-                const int n_tasks = n_dot << sh;
-                for (int task = warp; task < n_tasks; task += MEGA_CW) {
-                    const int dr = task >> sh, seg = task & ((1 << sh) - 1);
-                    int jb, row;
-                    if (ph.kind == PH_SWIGLU) {
-                        jb = dr >= n_r;
-                        row = u + (jb ? dr - n_r : dr);
                     } else {
-                        locate_row(ph, u + dr, jb, row);
+#pragma unroll 1
+                        for (int rr = 0; rr < n; rr += rpp) {
+                            const int row = rr + L.sr;
+                            const bool on = L.on && row < n;
+                            float v = mg_dot_q4k(st + (on ? row : 0) * rb + L.kb * 144, L.h, xr, dx, bs32);
+                            v = mg_row_sum(on ? v : 0.f, L.span);
+                            if (on && L.head) pout[(size_t)row * S] = v;
+                        }
                     }
-                    const FusedJob &j = ph.job[jb];
-                    const uint8_t *r0 = j.W + (int64_t)row * j.row_stride;
-                    float acc[1][1] = {{0.f}};
-                    rows2_dot<LdL2, 1, 1>(j.type, r0, r0, K, seg, 1 << sh, xs, xrb, lane, acc);
-                    const float s0 = warp_sum(acc[0][0]);
-                    if (lane == 0) {
-                        partial[task] = s0;
-                        const unsigned long long by = (unsigned long long)((((int64_t)(seg + 1) * j.row_stride) >> sh) -
-                                                                           (((int64_t)seg * j.row_stride) >> sh));
-                        atomicAdd((unsigned long long *)consumed, by);
+                } else if (type == B2_T_Q6_K) {
+                    // the fp16 super-block scales sit at the end of the row, outside the staged K-split: they come
+                    // straight from global memory (L2), requested one row group ahead of their use
+                    const int64_t stride = tile->stride;
+                    const uint8_t *dp = tile->dp + 2 * L.kb;
+                    if (rpp == 1) { // 2 rows at a time
+                        uint32_t d0 = mg_ldg_u16(dp), d1 = mg_ldg_u16(dp + (n > 1 ? stride : 0));
+                        mg_wait(bar, parity);
+                        if (DBG && tid == 0) tw1 = clock64();
+                        const uint32_t base = st + L.kb * Q6_BLK;
+#pragma unroll 1
+                        for (int k = 0; k < n; k += 2) {
+                            const int k2 = min(k + 2, n - 1), k3 = min(k + 3, n - 1);
+                            const uint32_t e0 = mg_ldg_u16(dp + k2 * stride), e1 = mg_ldg_u16(dp + k3 * stride);
+                            float v0 = mg_dot_q6k(base + k * rb, L.h, xr, dx, bs, d0);
+                            float v1 = mg_dot_q6k(base + min(k + 1, n - 1) * rb, L.h, xr, dx, bs, d1);
+                            if (!L.on) { v0 = 0.f; v1 = 0.f; }
+                            const float tot = mg_reduce2(v0, v1, lane);
+                            const int kk = k + ((lane >> 4) & 1);
+                            if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
+                            d0 = e0; d1 = e1;
+                        }
+                    } else {
+                        mg_wait(bar, parity);
+                        if (DBG && tid == 0) tw1 = clock64();
+#pragma unroll 1
+                        for (int rr = 0; rr < n; rr += rpp) {
+                            const int row = rr + L.sr;
+                            const bool on = L.on && row < n;
+                            const uint32_t d16 = mg_ldg_u16(dp + (on ? row : 0) * stride);
+                            float v = mg_dot_q6k(st + (on ? row : 0) * rb + L.kb * Q6_BLK, L.h, xr, dx, bs, d16);
+                            v = mg_row_sum(on ? v : 0.f, L.span);
+                            if (on && L.head) pout[(size_t)row * S] = v;
+                        }
+                    }
+                } else { // Q8_0: tile row = [int8 K/S][fp16 scales K/S/32]
+                    mg_wait(bar, parity);
+                    if (DBG && tid == 0) tw1 = clock64();
+                    const int ks = (int)(K >> ph.s_log);
+                    const int xc = (q * ks) >> 4;                               // first 16-byte chunk of this K-split's activations
+                    const float *xdq = (const float *)(xs + K) + (q * ks) / 32; // and their block scales
+#pragma unroll 1
+                    for (int row = 0; row < n; row++) {
+                        const uint32_t rp = st + row * rb;
+                        float acc = 0.f;
+#pragma unroll 4
+                        for (int j = 0; j < np; j++) { // 16-byte pieces lane + 32 j
+                            const int piece = lane + 32 * j;
+                            const int4 wv = mg_lds128(rp + piece * 16), xv = mg_lds128(xs_a + mg_swz(xc + piece) * 16);
+                            const float dw = h2f((uint16_t)mg_lds_u16(rp + ks + (piece >> 1) * 2));
+                            int sdot = __dp4a(wv.x, xv.x, 0);
+                            sdot = __dp4a(wv.y, xv.y, sdot);
+                            sdot = __dp4a(wv.z, xv.z, sdot);
+                            sdot = __dp4a(wv.w, xv.w, sdot);
+                            sdot += __shfl_xor_sync(0xffffffffu, sdot, 1); // whole 32-element block, as on the CPU
+                            if ((lane & 1) == 0) acc += (float)sdot * (dw * xdq[piece >> 1]);
+                        }
+                        acc = mg_row_sum(acc, 32);
+                        if (lane == 0) pout[(size_t)row * S] = acc;
                     }
                 }
-                consumer_sync();
-                // ---- epilogue: combine the segment partials in a fixed order (deterministic), then the phase's tail op
-                const int n_seg = 1 << sh;
-                auto dot_sum = [&](int dr) {
-                    float s = 0.f;
-                    for (int sg = 0; sg < n_seg; sg++) s += partial[(dr << sh) + sg];
-                    return s;
-                };
-                if (ph.kind == PH_SWIGLU) {
-                    for (int r = tid; r < n_r; r += MEGA_CT) {
-                        const float g = dot_sum(r), up = dot_sum(n_r + r);
-                        ph.out[u + r] = __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), up);
-                    }
-                } else if (ph.kind == PH_PLAIN) {
-                    for (int r = tid; r < n_r; r += MEGA_CT) {
-                        float s = dot_sum(r);
-                        if (ph.residual) s += __ldcg(ph.residual + u + r);
-                        ph.out[u + r] = s;
-                    }
-                } else { // PH_QKV: job 0 = q, 1 = k, 2 = v; rows (r, r+1) form a rotary pair inside one head
-                    const int page = a.page_table[(int64_t)sl * a.max_pages + pos / a.page_size];
-                    const int64_t cell = ((int64_t)page * a.page_size + pos % a.page_size) * a.kvd;
-                    for (int pr = tid; pr < n_r / 2; pr += MEGA_CT) {
-                        int jb, r;
-                        locate_row(ph, u + 2 * pr, jb, r);
-                        const float v0 = dot_sum(2 * pr), v1 = dot_sum(2 * pr + 1);
-                        if (jb == 2) {
-                            *(__half2 *)(ph.v_pool + cell + r) = __halves2half2(__float2half_rn(v0), __float2half_rn(v1));
-                        } else {
-                            const float *cs = a.rope_table + (int64_t)pos * a.hd + (r % a.hd);
-                            const float c = cs[0], sn = cs[1];
-                            const float o0 = __fsub_rn(__fmul_rn(v0, c), __fmul_rn(v1, sn));
-                            const float o1 = __fadd_rn(__fmul_rn(v0, sn), __fmul_rn(v1, c));
-                            if (jb == 0) *(float2 *)(ph.out + r) = make_float2(o0, o1);
-                            else *(__half2 *)(ph.k_pool + cell + r) = __halves2half2(__float2half_rn(o0), __float2half_rn(o1));
-                        }
+                long long ta0 = 0, ta2 = 0;
+                if (DBG && tid == 0) { ta0 = clock64(); t_wait += tw1 - tw0; t_comp += ta0 - tw1; n_tiles++; }
+                // the stage is free: refill it with the tile MG_STAGES ahead (possibly a later phase's)
+                __syncwarp();
+                if (pc->ok) {
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    const int m = mg_tile_rows(*pc);
+                    mg_issue(*pc, m, st, bar, lane, tile);
+                    if (DBG && tid == 0) ta2 = clock64();
+                    mg_advance(a, sph, p, pc, m, cta, n_cta, warp);
+                    if (DBG && tid == 0) { t_iss += ta2 - ta0; t_advp += clock64() - ta2; }
+                } else {
+                    tile->p = MG_NO_TILE;
+                }
+                __syncwarp();
+                if (++stg == MG_STAGES) { stg = 0; parity ^= 1; }
+            }
+            if (DBG && tid == 0) tl_end = clock64();
+            __syncthreads();
+            if (DBG && tid == 0) t_epi = clock64();
+
+            // ---- epilogue: combine the K-split partials in a fixed order (deterministic), then the phase's tail op
+            const int n_r = u_end - u;
+            auto dot_sum = [&](int dr) {
+                float s = 0.f;
+                for (int sg = 0; sg < S; sg++) s += partial[dr * S + sg];
+                return s;
+            };
+            if (ph.kind == PH_SWIGLU) {
+                for (int r = tid; r < n_r; r += MG_THREADS) {
+                    const float g = dot_sum(r), up = dot_sum(n_r + r);
+                    ph.out[u + r] = __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), up);
+                }
+            } else if (ph.kind == PH_PLAIN) {
+                for (int r = tid; r < n_r; r += MG_THREADS) {
+                    float s = dot_sum(r);
+                    if (ph.residual) s += __ldcg(ph.residual + u + r);
+                    ph.out[u + r] = s;
+                }
+            } else { // PH_QKV: job 0 = q, 1 = k, 2 = v; rows (r, r+1) form a rotary pair inside one head
+                const int64_t cell = ((((int64_t)pbase[pos >> a.page_shift]) << a.page_shift) + (pos & (a.page_size - 1))) * a.kvd;
+                for (int pr = tid; pr < n_r / 2; pr += MG_THREADS) {
+                    int jb, r;
+                    mg_locate_row(ph, u + 2 * pr, jb, r);
+                    const float v0 = dot_sum(2 * pr), v1 = dot_sum(2 * pr + 1);
+                    if (jb == 2) {
+                        *(__half2 *)(ph.v_pool + cell + r) = __halves2half2(__float2half_rn(v0), __float2half_rn(v1));
+                    } else {
+                        const float *cs = a.rope_table + (int64_t)pos * a.hd + (r % a.hd);
+                        const float c = cs[0], sn = cs[1];
+                        const float o0 = __fsub_rn(__fmul_rn(v0, c), __fmul_rn(v1, sn));
+                        const float o1 = __fadd_rn(__fmul_rn(v0, sn), __fmul_rn(v1, c));
+                        if (jb == 0) *(float2 *)(ph.out + r) = make_float2(o0, o1);
+                        else *(__half2 *)(ph.k_pool + cell + r) = __halves2half2(__float2half_rn(o0), __float2half_rn(o1));
                     }
                 }
             }
         }
         // ---- phase boundary
-        if (a.dbg && tid == 0) t2 = clock64();
+        if (DBG && tid == 0) t2 = clock64();
         if (p + 1 < a.n_phases) {
-            consumer_sync();
-            if (tid == 0) grid_barrier(a.bar, n_cta, bar_gen);
-            consumer_sync();
+            __syncthreads();
+            stage_phase(p + MG_PH_WIN); // phase p's slot is free: everyone is past its epilogue (warps 1.. do the copy)
+            if (tid == 0) mg_grid_barrier(a.bar, a.bar_base + (unsigned)(p + 1) * (unsigned)n_cta);
+            __syncthreads();
         }
-        if (a.dbg && tid == 0) {
-            long long *dd = a.dbg + ((int64_t)cta * a.n_phases + p) * 8;
-            dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64(); dd[4] = 0; dd[5] = 0; dd[6] = 0; dd[7] = 0;
+        if (DBG && tid == 0) {
+            long long *dd = a.dbg + ((int64_t)cta * a.n_phases + p) * 16;
+            dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64(); dd[4] = t_wait; dd[5] = t_comp; dd[6] = t_epi ? t2 - t_epi : 0; dd[7] = n_tiles;
+            dd[8] = tp0 - t0; dd[9] = t_advc; dd[10] = tp3 - tp0; dd[11] = t_iss; dd[12] = t1 - tp3; dd[13] = t_epi - tl_end; dd[14] = tl_end - t1; dd[15] = t_advp;
         }
     }
 }
@@ -299,31 +999,52 @@ decode_mega_kernel(const MegaArgs a) {
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s) {
     static thread_local bool configured = false;
     if (!configured) {
-        B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MEGA_SMEM));
+        B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
+        B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
         configured = true;
     }
     void *args[] = {(void *)&a};
-    B2_CUDA(cudaLaunchCooperativeKernel((const void *)decode_mega_kernel, dim3(n_sm), dim3(MEGA_THREADS), args, MEGA_SMEM, s));
+    const void *fn = a.dbg ? (const void *)decode_mega_kernel<true> : (const void *)decode_mega_kernel<false>;
+    B2_CUDA(cudaLaunchCooperativeKernel(fn, dim3(n_sm), dim3(MG_THREADS), args, MG_SMEM, s));
     g_launch_count++;
 }
 
-bool mega_phase_supported(const MegaPhase &ph) {
+bool mega_phase_prepare(MegaPhase &ph, int n_cta) {
     if (ph.kind == PH_ATT) return true;
-    if (ph.fmt != ACT_Q8_K && ph.fmt != ACT_Q8_0) return false;
-    if (act_row_bytes((ActFmt)ph.fmt, ph.K) > MEGA_XS_BYTES || ph.K / 256 > MEGA_PB * MEGA_CW) return false;
+    if (n_cta < 1) return false;
+    ph.units_q = ph.units / n_cta;
+    ph.units_r = ph.units % n_cta;
+    int S, lpr, rpp, np;
+    if (!mg_split(ph.fmt, ph.K, S, lpr, rpp, np)) return false;
+    if (mg_act_row_bytes_host(ph.fmt, ph.K) > MG_XS_BYTES) return false;
+    if (ph.norm_w && ph.K / 256 > 4 * MG_WARPS) return false; // the prologue norms at most 4 blocks per warp in one go
+    ph.S = S; ph.lpr = lpr; ph.rpp = rpp; ph.np = np;
+    ph.s_log = 0;
+    while ((1 << ph.s_log) < S) ph.s_log++;
+    ph.lpr_log = 0;
+    while ((1 << ph.lpr_log) < lpr) ph.lpr_log++; // only used when lpr is a power of two (rpp > 1)
     int64_t rows = 0;
     for (int j = 0; j < ph.n_jobs; j++) {
-        if (ph.job[j].rows % 2 != 0) return false;
+        ph.j0[j] = (int)rows;
+        if (!mg_job_geo(ph.job[j].type, ph.K, ph.job[j].row_stride, S, rpp, ph.rb[j], ph.R[j])) return false;
+        if (ph.job[j].rows % 2 != 0 || ph.job[j].rows >= (1 << 22)) return false;
         rows += ph.job[j].rows;
     }
-    // the per-CTA share of the rows (x2 K-segments at most when it is small) must fit the partial buffer
-    return rows / 132 + 4 <= MEGA_MAX_PART;
+    // the per-CTA share of the rows x K-splits must fit the partial buffer
+    return (rows / n_cta + 4) * S <= MG_MAX_PART;
+}
+bool mega_phase_supported(const MegaPhase &ph) {
+    MegaPhase t = ph;
+    return mega_phase_prepare(t, 128);
 }
 
 size_t mega_attention_ctx_limit(int hd) {
-    // scores + page table + q + per-warp partials must fit the activation region
-    const size_t fixed = sizeof(float) * ((size_t)hd + 32 + (size_t)MEGA_CW * hd + 16);
-    return fixed >= (size_t)MEGA_XS_BYTES ? 0 : (size_t)((MEGA_XS_BYTES - fixed) / 4.6) - 8;
+    // q + reduction scratch + per-warp partials + scores live in the activation-row and partial regions; the page
+    // table of the sequence has MG_MAX_PAGES entries (page size >= 16 assumed by the caller)
+    const size_t avail = MG_XS_BYTES + MG_MAX_PART * sizeof(float);
+    const size_t fixed = sizeof(float) * ((size_t)hd + 32 + (size_t)MG_WARPS * hd + 16);
+    if (fixed >= avail) return 0;
+    return std::min((size_t)((avail - fixed) / 4) - 8, (size_t)MG_MAX_PAGES * 16);
 }
 
 } // namespace b2

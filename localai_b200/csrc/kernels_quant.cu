@@ -38,10 +38,8 @@ __global__ void repack_q6_k_kernel(const uint16_t *__restrict__ src, uint8_t *__
         const int64_t r = blk / nb, b = blk % nb;
         uint8_t *row = dst + r * dst_stride;
         const uint16_t v = src[u];
-        if (w < 64) ((uint16_t *)(row + b * 128))[w] = v;                          // ql
-        else if (w < 96) ((uint16_t *)(row + nb * 128 + b * 64))[w - 64] = v;       // qh
-        else if (w < 104) ((uint16_t *)(row + nb * 192 + b * 16))[w - 96] = v;      // scales
-        else ((uint16_t *)(row + nb * 208))[b] = v;                                // d
+        if (w < 104) ((uint16_t *)(row + b * Q6_BLK))[w] = v;   // ql | qh | scales keep their order inside the block
+        else ((uint16_t *)(row + nb * Q6_BLK))[b] = v;           // d
     }
 }
 
@@ -122,9 +120,9 @@ __global__ void dequant_rows_kernel(const uint8_t *__restrict__ W, int type, int
             const int64_t ib = grp / 8;
             const int j = (int)(grp % 8), n = j / 4, c = j % 4;
             const float d = h2f(q.d[ib]);
-            const uint8_t *ql = q.ql + ib * 128 + 64 * n + ((c & 1) ? 32 : 0);
-            const uint8_t *qh = q.qh + ib * 64 + 32 * n;
-            const int8_t *sc = q.sc + ib * 16 + 8 * n + 2 * c;
+            const uint8_t *ql = q.ql(ib) + 64 * n + ((c & 1) ? 32 : 0);
+            const uint8_t *qh = q.qh(ib) + 32 * n;
+            const int8_t *sc = q.sc(ib) + 8 * n + 2 * c;
             for (int l = 0; l < 32; l++) {
                 const int lo = (c < 2) ? (ql[l] & 0xF) : (ql[l] >> 4);
                 const int hi = (qh[l] >> (2 * c)) & 3;

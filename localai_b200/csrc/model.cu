@@ -464,22 +464,24 @@ void Model::build_mega() {
     h.kind = PH_PLAIN; h.K = d; h.fmt = act_format_for(output.type); h.n_jobs = 1; h.job[0] = job_of(output);
     h.x = x_; h.norm_w = (const float *)output_norm.data; h.out = logits_; h.xn_out = xn_out_; h.units = (int)(output.rows / 2);
     ph.push_back(h);
+    cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
     for (auto &p : ph)
-        if (!mega_phase_supported(p)) return;
-    if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 32 != 0 || hd > 256) return;
+        if (!mega_phase_prepare(p, n_sm_)) return;
+    if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1))) return;
     if (!mega_phases_) mega_phases_ = (MegaPhase *)dalloc(ph.size() * sizeof(MegaPhase));
     B2_CUDA(cudaMemcpyAsync(mega_phases_, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaStreamSynchronize(stream));
     mega_n_phases_ = (int)ph.size();
     if (!mega_bar_) {
-        mega_bar_ = (unsigned *)dalloc(64);
-        B2_CUDA(cudaMemsetAsync(mega_bar_, 0, 64, stream));
+        mega_bar_ = (unsigned *)dalloc(4096);
+        B2_CUDA(cudaMemsetAsync(mega_bar_, 0, 4096, stream));
+        mega_epoch_ = 0;
     }
     int coop = 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
     cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
     mega_ready_ = coop != 0;
-    if (getenv("B200LLM_MEGA_DBG") && !mega_dbg_) mega_dbg_ = (long long *)dalloc((size_t)n_sm_ * mega_n_phases_ * 8 * sizeof(long long));
+    if (getenv("B200LLM_MEGA_DBG") && !mega_dbg_) mega_dbg_ = (long long *)dalloc((size_t)n_sm_ * mega_n_phases_ * 16 * sizeof(long long));
 }
 
 // Batch-1 decode step through the persistent kernel: [embedding gather] [mega] = 2 launches (+ sampling).
@@ -492,7 +494,11 @@ void Model::run_decode_mega() {
     a.page_size = page_size; a.max_pages = max_pages; a.kvd = hp.n_head_kv * hp.head_dim;
     a.n_head = hp.n_head; a.n_head_kv = hp.n_head_kv; a.hd = hp.head_dim;
     a.eps = hp.rms_eps; a.att_scale = 1.0f / sqrtf((float)hp.head_dim);
+    a.page_shift = 0;
+    while ((1 << a.page_shift) < page_size) a.page_shift++;
     a.bar = mega_bar_;
+    a.bar_base = mega_epoch_;
+    mega_epoch_ += (unsigned)n_sm_ * (unsigned)(mega_n_phases_ - 1);
     a.dbg = mega_dbg_;
     launch_decode_mega(a, n_sm_, stream);
 }

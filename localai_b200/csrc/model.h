@@ -92,6 +92,7 @@ class Model {
     void build_mega();
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;
+    unsigned mega_epoch_ = 0;
     unsigned *mega_bar_ = nullptr;
     long long *mega_dbg_ = nullptr;
   public:

@@ -36,14 +36,17 @@ __device__ __forceinline__ void get_scale_min_k4_w(int j, uint32_t w0, uint32_t 
     }
 }
 
-// pointers to the sections of one Q6_K row in device (SoA) layout
+// one Q6_K row in device layout: nb 208-byte blocks [ql 128][qh 64][scales 16] (16-byte aligned; 13 x 16 B, an odd
+// stride, so lanes that each read a different block of a staged row hit different shared-memory banks), then the nb
+// fp16 super-block scales
+constexpr int Q6_BLK = 208;
 struct Q6Row {
-    const uint8_t *ql, *qh;
-    const int8_t *sc;
+    const uint8_t *base;
     const uint16_t *d;
-    __device__ __forceinline__ Q6Row(const uint8_t *row, int nb)
-        : ql(row), qh(row + (size_t)nb * 128), sc((const int8_t *)(row + (size_t)nb * 192)),
-          d((const uint16_t *)(row + (size_t)nb * 208)) {}
+    __device__ __forceinline__ Q6Row(const uint8_t *row, int nb) : base(row), d((const uint16_t *)(row + (size_t)nb * Q6_BLK)) {}
+    __device__ __forceinline__ const uint8_t *ql(int b) const { return base + (size_t)b * Q6_BLK; }
+    __device__ __forceinline__ const uint8_t *qh(int b) const { return base + (size_t)b * Q6_BLK + 128; }
+    __device__ __forceinline__ const int8_t *sc(int b) const { return (const int8_t *)(base + (size_t)b * Q6_BLK + 192); }
 };
 // Q8_0 row in device (SoA) layout
 struct Q80Row {

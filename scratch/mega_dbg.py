@@ -11,13 +11,14 @@ print("ms/step", ms, "launches", l)
 L = capi.lib(); L.b2_mega_debug.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 n = L.b2_mega_debug(e._h, None, 0)
 buf = np.zeros(n, dtype=np.int64); L.b2_mega_debug(e._h, buf.ctypes.data_as(C.c_void_p), n)
-nph = n // 8 // 148; d = buf.reshape(148, nph, 8)
+nph = n // 16 // 148; d = buf.reshape(148, nph, 16)
 kinds = ["qkv","att","wo","gateup","down"]
 pro = (d[:,:,1]-d[:,:,0]); stg = (d[:,:,2]-d[:,:,1]); bar = (d[:,:,3]-d[:,:,2])
 print("cycles per phase kind (mean over CTAs and layers; max over CTAs mean over layers) -- clock ~1.9 GHz")
 for k in range(5):
     idx = np.arange(k, nph-1, 5)
-    print(f"        per-stage: n_stages {d[:,idx,7].mean():.1f} wait_full {d[:,idx,4].sum()/max(1,d[:,idx,7].sum()):.0f} tasks {d[:,idx,5].sum()/max(1,d[:,idx,7].sum()):.0f} arrive+sync+epilogue {d[:,idx,6].sum()/max(1,d[:,idx,7].sum()):.0f}")
+    print(f"        warp0: tiles/phase {d[:,idx,7].mean():.1f} wait/phase {d[:,idx,4].mean():.0f} compute/phase {d[:,idx,5].mean():.0f} (per tile {d[:,idx,5].sum()/max(1,d[:,idx,7].sum()):.0f}) epilogue {d[:,idx,6].mean():.0f}")
+    print(f"        prologue parts: setup+xload {d[:,idx,8].mean():.0f} prologue-fn {d[:,idx,10].mean():.0f} [tile loop: adv-cons {d[:,idx,9].mean():.0f} fence+issue {d[:,idx,11].mean():.0f} adv-prod {d[:,idx,15].mean():.0f}] slice {d[:,idx,12].mean():.0f} | tile loop w0 {d[:,idx,14].mean():.0f} wait-for-other-warps {d[:,idx,13].mean():.0f}")
     print(f"{kinds[k]:7s} prologue {pro[:,idx].mean():8.0f}  stages mean {stg[:,idx].mean():8.0f} max-cta {stg[:,idx].max(axis=0).mean():8.0f}  barrier mean {bar[:,idx].mean():8.0f} min-cta {bar[:,idx].min(axis=0).mean():8.0f}")
 print("lm_head  prologue", pro[:,-1].mean(), "stages mean", stg[:,-1].mean(), "max", stg[:,-1].max())
 tot = (d[:,-1,3]-d[:,0,0]); print("total cycles per CTA mean", tot.mean(), "=> ms at 1.9GHz", tot.mean()/1.9e6)

@@ -112,7 +112,15 @@ def test_fused_and_mega_kernels_match_oracle(wtype, rows, cols, n_tok, path):
     else:
         raw = mg.random_blocks(rng, wtype, rows * cols // mg.BLOCK[wtype][0], 1 / np.sqrt(cols))
     x = rng.standard_normal((n_tok, cols)).astype(np.float32)
-    got = capi.mul_mat(wtype, raw, rows, cols, x, path=path)
+    try:
+        got = capi.mul_mat(wtype, raw, rows, cols, x, path=path)
+    except capi.B2Error as ex:
+        # the mega-kernel declines what it has no lane mapping for (Q5_K; Q8_0 rows that are not a multiple of 512):
+        # the engine then runs the per-operator kernels (path 3).  Everything else must be supported.
+        mega_ok = wtype in (capi.B2_T_Q4_K, capi.B2_T_Q6_K) or (wtype == capi.B2_T_Q8_0 and cols % 512 == 0)
+        if path == 4 and ex.code == capi.B2_EUNSUPPORTED and not mega_ok:
+            pytest.skip("shape/type outside the mega-kernel's lane mappings")
+        raise
     ref = O.mul_mat(wtype, raw, rows, cols, x)
     assert np.isfinite(got).all()
     assert np.abs(got - ref).max() <= MATMUL_RTOL * np.abs(ref).max()
