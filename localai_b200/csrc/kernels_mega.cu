@@ -420,8 +420,10 @@ __device__ __forceinline__ float mg_reduce2(float v0, float v1, int lane) {
 // waited for; the QKV phase has already pulled the sequence's K/V rows into L2 (mg_prefetch_kv).
 // Numerics as attention_head (attention.cuh): q and the normalised probabilities rounded to f16, fp32 accumulation.
 // scratch: q[hd] | red[32] | part[8][hd] | scores[n_kv].  hd = 64 or 128.
+// row of position j in a layer's K or V pool; 32-bit element index (the host checks that a layer pool has < 2^31 halves)
 __device__ __forceinline__ const __half *mg_kv_row(const __half *pool, const int *pbase, int j, int page_shift, int kvd) {
-    return pool + ((((int64_t)pbase[j >> page_shift]) << page_shift) + (j & ((1 << page_shift) - 1))) * kvd;
+    const uint32_t cell = ((uint32_t)pbase[j >> page_shift] << page_shift) + (uint32_t)(j & ((1 << page_shift) - 1));
+    return pool + cell * (uint32_t)kvd;
 }
 __device__ __noinline__ void mg_attention(const float *__restrict__ qrow, int n_kv, const int *pbase, const __half *k_pool,
                                              const __half *v_pool, int page_shift, int kvd, int hk, int hd, float scale,
@@ -581,7 +583,8 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
         const int b = warp + (k_first + k) * MG_WARPS;
         valid[k] = b < nb;
         const float4 *xb = (const float4 *)(xrow + (valid[k] ? b : 0) * 256 + lane * 8);
-        const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1); // the row was written by other SMs: L2
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0; // blocks past the row's end are carried as zeros
+        if (valid[k]) { a0 = __ldcg(xb); a1 = __ldcg(xb + 1); } // the row was written by other SMs: L2
         v[k][0] = a0.x; v[k][1] = a0.y; v[k][2] = a0.z; v[k][3] = a0.w;
         v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
         if (PBN <= 2 && has_norm) { // norm weights ride the same round trip
@@ -591,10 +594,6 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
             w[k][4] = w1.x; w[k][5] = w1.y; w[k][6] = w1.z; w[k][7] = w1.w;
         }
     }
-#pragma unroll
-    for (int k = 0; k < PBN; k++)
-#pragma unroll
-        for (int i = 0; i < 8; i++) v[k][i] = valid[k] ? v[k][i] : 0.f;
     if (has_norm) {
         double sum = 0.0;
 #pragma unroll
@@ -607,7 +606,8 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
         double tot = 0.0;
 #pragma unroll
         for (int i = 0; i < MG_WARPS; i++) tot += s_part[i]; // every thread: same order, same result
-        const float mean = (float)(tot / (double)K);
+        // K a power of two: tot * 2^-k is the correctly rounded quotient, without the division subroutine
+        const float mean = (K & (K - 1)) == 0 ? (float)(tot * (1.0 / (double)K)) : (float)(tot / (double)K);
         const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
 #pragma unroll
         for (int k = 0; k < PBN; k++) {
@@ -634,7 +634,7 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
         constexpr int QB = PBN < 4 ? PBN : 4; // blocks quantised together (interleaved dependency chains)
 #pragma unroll
         for (int k0 = 0; k0 < PBN; k0 += QB) {
-            uint32_t amax[QB], idx[QB];
+            uint32_t amax[QB], key[QB];
 #pragma unroll
             for (int kk = 0; kk < QB; kk++) {
                 const int k = k0 + kk;
@@ -644,21 +644,18 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
                 amax[kk] = __reduce_max_sync(0xffffffffu, __float_as_uint(m)); // non-negative floats order like their bits
             }
 #pragma unroll
-            for (int kk = 0; kk < QB; kk++) { // the FIRST element (in index order) with the largest |x|
+            for (int kk = 0; kk < QB; kk++) { // the FIRST element (in index order) with the largest |x|: only its sign matters
                 const int k = k0 + kk;
-                uint32_t li = 0x7fffffffu;
+                uint32_t li = 0xffffffffu;
 #pragma unroll
                 for (int i = 7; i >= 0; i--)
-                    if (__float_as_uint(fabsf(v[k][i])) == amax[kk]) li = lane * 8 + i;
-                idx[kk] = __reduce_min_sync(0xffffffffu, li);
+                    if (__float_as_uint(fabsf(v[k][i])) == amax[kk]) li = ((uint32_t)(lane * 8 + i) << 1) | (__float_as_uint(v[k][i]) >> 31);
+                key[kk] = __reduce_min_sync(0xffffffffu, li);
             }
 #pragma unroll
             for (int kk = 0; kk < QB; kk++) {
                 const int k = k0 + kk;
-                float sel = v[k][0];
-#pragma unroll
-                for (int i = 1; i < 8; i++) sel = (idx[kk] & 7) == i ? v[k][i] : sel;
-                const float mx = __shfl_sync(0xffffffffu, sel, idx[kk] >> 3);
+                const float mx = __uint_as_float(amax[kk] | (key[kk] << 31)); // +-amax: the value of that element
                 const bool zero = amax[kk] == 0u;
                 const float iscale = zero ? 0.f : __fdiv_rn(-127.f, mx);
                 int sum = 0;

@@ -467,7 +467,9 @@ void Model::build_mega() {
     cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
     for (auto &p : ph)
         if (!mega_phase_prepare(p, n_sm_)) return;
-    if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1))) return;
+    if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1)) ||
+        (uint64_t)pool_layer_stride_ >= (1ull << 31))
+        return;
     if (!mega_phases_) mega_phases_ = (MegaPhase *)dalloc(ph.size() * sizeof(MegaPhase));
     B2_CUDA(cudaMemcpyAsync(mega_phases_, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaStreamSynchronize(stream));
