@@ -135,9 +135,12 @@ size_t gemm_w_tiles_bytes(int64_t rows, int64_t cols);
 size_t gemm_x_tiles_bytes(int n_tok, int64_t cols);
 // fp32 activations [n_tok][K] -> bf16 operand tiles (do once per activation, shared by several matrices)
 void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
-// out[t][r] = W[r] . x[t] (+ residual): dequantises W into w_tiles (scratch), then tcgen05/TMEM GEMM
+// quantised W -> bf16 operand tiles (gemm_w_tiles_bytes of them)
+void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s);
+// out[t][r] = W[r] . x[t] (+ residual): tcgen05/TMEM GEMM on bf16 operand tiles; W is dequantised into w_tiles first
+// unless w_tiles_ready (the caller keeps W's tiles resident)
 void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
-                    int64_t res_stride, void *w_tiles, cudaStream_t s);
+                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, cudaStream_t s);
 
 // --- sampling -------------------------------------------------------------------------------------------
 // out[r] = first argmax of row r.  If feed_tok/feed_pos are given (device-side decode loop) the sampled id is also

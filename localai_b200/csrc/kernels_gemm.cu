@@ -317,8 +317,18 @@ void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t 
     B2_CUDA(cudaGetLastError());
 }
 
+void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s) {
+    B2_CHECK(W.cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
+    const int64_t rows_pad = align_up(W.rows, GM_BN);
+    const int64_t total = rows_pad * (W.cols / 8);
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+    dequant_tiles_kernel<<<blocks, 256, 0, s>>>(W.data, W.type, W.rows, W.cols, W.row_stride, (__nv_bfloat16 *)w_tiles, rows_pad);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
 void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
-                    int64_t res_stride, void *w_tiles, cudaStream_t s) {
+                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, cudaStream_t s) {
     B2_CHECK(W.cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
     static thread_local bool configured = false;
     static thread_local uint32_t lbo = 128, sbo = 1024;
@@ -328,13 +338,7 @@ void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out
         configured = true;
     }
     const int64_t rows_pad = align_up(W.rows, GM_BN);
-    {   // 1. quantised W -> bf16 tiles
-        const int64_t total = rows_pad * (W.cols / 8);
-        const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
-        dequant_tiles_kernel<<<blocks, 256, 0, s>>>(W.data, W.type, W.rows, W.cols, W.row_stride, (__nv_bfloat16 *)w_tiles, rows_pad);
-        g_launch_count++;
-        B2_CUDA(cudaGetLastError());
-    }
+    if (!w_tiles_ready) launch_gemm_dequant_w(W, w_tiles, s); // 1. quantised W -> bf16 tiles (unless the caller keeps them)
     GemmArgs g;
     g.a_tiles = (const __nv_bfloat16 *)x_tiles;
     g.b_tiles = (const __nv_bfloat16 *)w_tiles;

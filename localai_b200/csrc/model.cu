@@ -66,6 +66,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     no_graph_ = getenv("B200LLM_NO_GRAPH") && atoi(getenv("B200LLM_NO_GRAPH")) != 0;
     no_mega_ = getenv("B200LLM_NO_MEGA") && atoi(getenv("B200LLM_NO_MEGA")) != 0;
     no_gemm_ = getenv("B200LLM_NO_GEMM") && atoi(getenv("B200LLM_NO_GEMM")) != 0;
+    no_shadow_ = getenv("B200LLM_NO_BF16_TILES") && atoi(getenv("B200LLM_NO_BF16_TILES")) != 0;
     if (getenv("B200LLM_GEMM_MIN_TOKENS")) gemm_min_tokens_ = atoi(getenv("B200LLM_GEMM_MIN_TOKENS"));
 
     hp.arch = f.get_s("general.architecture", "");
@@ -201,6 +202,7 @@ Model::~Model() {
         if (g) cudaGraphExecDestroy(g);
     for (void *p : allocs_) cudaFree(p);
     if (logits_) cudaFree(logits_);
+    for (auto &kv : w_tiles_) cudaFree(kv.second);
     if (gemm_w_) cudaFree(gemm_w_);
     if (gemm_x_) cudaFree(gemm_x_);
     if (staging_) cudaFree(staging_);
@@ -330,7 +332,8 @@ void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
     if (w_bytes > gemm_w_bytes_) {
         realloc = true;
         B2_CUDA(cudaStreamSynchronize(stream));
-        if (gemm_w_) cudaFree(gemm_w_);
+        for (auto &kv : w_tiles_) cudaFree(kv.second);
+    if (gemm_w_) cudaFree(gemm_w_);
         gemm_w_ = nullptr;
         B2_CUDA(cudaMalloc(&gemm_w_, w_bytes));
         gemm_w_bytes_ = w_bytes;
@@ -350,9 +353,34 @@ void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
         }
 }
 
+// bf16 operand tiles of W for the tensor-core path.  180 GB of HBM is room to keep them resident (15 GB for an 8B
+// model) next to the quantised weights the decode kernels stream: prefill chunks and batched decode steps then skip
+// the dequantisation pass.  Built on first use (never inside a graph capture: run_decode_graphed warms up first);
+// when memory is short the tiles are rebuilt into a scratch buffer on every call instead.
+void *Model::resident_tiles(const DTensor &W) {
+    if (no_shadow_) return nullptr;
+    auto it = w_tiles_.find(W.data);
+    if (it != w_tiles_.end()) return it->second;
+    const size_t bytes = gemm_w_tiles_bytes(W.rows, W.cols);
+    size_t free_b = 0, total_b = 0;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cs);
+    if (cs != cudaStreamCaptureStatusNone) return nullptr;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < bytes + shadow_reserve_) { no_shadow_ = true; return nullptr; }
+    void *p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); no_shadow_ = true; return nullptr; }
+    launch_gemm_dequant_w(W, p, stream);
+    w_tiles_[W.data] = p;
+    return p;
+}
+
 void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride) {
+    if (void *t = resident_tiles(W)) {
+        launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, t, true, stream);
+        return;
+    }
     ensure_gemm_scratch(gemm_w_tiles_bytes(W.rows, W.cols), 0);
-    launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, stream);
+    launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, false, stream);
 }
 
 // Prefill / batched decode: every mat-mul is a tcgen05 tensor-core GEMM on bf16 operands (weights dequantised into

@@ -4,6 +4,7 @@
 
 #include <memory>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "common.h"
@@ -85,6 +86,10 @@ class Model {
     void run_layer_gemm(const LayerW &L, const KVLayout &kv, int n);
     void gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride);
     void ensure_gemm_scratch(size_t w_bytes, size_t x_bytes);
+    void *resident_tiles(const DTensor &W);
+    std::unordered_map<const uint8_t *, void *> w_tiles_; // resident bf16 operand tiles, keyed by the weight pointer
+    bool no_shadow_ = false;
+    size_t shadow_reserve_ = (size_t)6 << 30;            // leave this much HBM free
     void *gemm_w_ = nullptr, *gemm_x_ = nullptr;
     size_t gemm_w_bytes_ = 0, gemm_x_bytes_ = 0;
     bool no_gemm_ = false;

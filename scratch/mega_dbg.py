@@ -22,3 +22,10 @@ for k in range(5):
     print(f"{kinds[k]:7s} prologue {pro[:,idx].mean():8.0f}  stages mean {stg[:,idx].mean():8.0f} max-cta {stg[:,idx].max(axis=0).mean():8.0f}  barrier mean {bar[:,idx].mean():8.0f} min-cta {bar[:,idx].min(axis=0).mean():8.0f}")
 print("lm_head  prologue", pro[:,-1].mean(), "stages mean", stg[:,-1].mean(), "max", stg[:,-1].max())
 tot = (d[:,-1,3]-d[:,0,0]); print("total cycles per CTA mean", tot.mean(), "=> ms at 1.9GHz", tot.mean()/1.9e6)
+
+idx = np.arange(1, nph-1, 5)
+a = d[:32][:, idx, :]
+print("attention (CTAs 0-31) cumulative cycles: preload-issued %.0f  q-sync %.0f  scores %.0f  max-sync %.0f  softmax-sync %.0f  pass2 %.0f  end %.0f" % tuple(a[:,:,k].mean() for k in (8,9,10,11,12,13,14)))
+print("raw CTA0 layer3 att slot:", d[0, 1+5*3, :].tolist())
+print("raw CTA5 layer7 att slot:", d[5, 1+5*7, :].tolist())
+print("raw CTA100 layer7 att slot:", d[100, 1+5*7, :].tolist())
