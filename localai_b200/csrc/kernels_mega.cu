@@ -834,19 +834,16 @@ decode_mega_kernel(const MegaArgs a) {
                 if (type == B2_T_Q4_K) {
                     mg_wait(bar, parity);
                     if (DBG && tid == 0) tw1 = clock64();
-                    if (rpp == 1) { // 4 rows at a time: independent dp4a chains, one merged reduction
+                    if (rpp == 1) { // 2 rows at a time: independent dp4a chains, one merged reduction
                         const uint32_t base = st + L.kb * 144;
 #pragma unroll 1
-                        for (int r0 = 0; r0 < n; r0 += 4) {
-                            float v[4];
-#pragma unroll
-                            for (int k = 0; k < 4; k++) {
-                                v[k] = mg_dot_q4k(base + min(r0 + k, n - 1) * rb, L.h, xr, dx, bs32);
-                                if (!L.on) v[k] = 0.f;
-                            }
-                            const float tot = mg_reduce4(v, lane);
-                            const int k = ((lane >> 4) & 1) | ((lane >> 2) & 2);
-                            if ((lane & 7) == 0 && r0 + k < n) pout[(size_t)(r0 + k) * S] = tot;
+                        for (int r0 = 0; r0 < n; r0 += 2) {
+                            float v0 = mg_dot_q4k(base + r0 * rb, L.h, xr, dx, bs32);
+                            float v1 = mg_dot_q4k(base + min(r0 + 1, n - 1) * rb, L.h, xr, dx, bs32);
+                            if (!L.on) { v0 = 0.f; v1 = 0.f; }
+                            const float tot = mg_reduce2(v0, v1, lane);
+                            const int kk = r0 + ((lane >> 4) & 1);
+                            if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
                         }
                     } else {
 #pragma unroll 1

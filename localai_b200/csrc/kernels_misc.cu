@@ -136,42 +136,51 @@ void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, i
 }
 
 // ------------------------------------------------------------------------------------------ greedy sampling
-// first maximal element, like std::max_element in llama.cpp's greedy sampler
-__global__ void __launch_bounds__(1024)
+// First maximal element, like std::max_element in llama.cpp's greedy sampler.  A row (128 256 logits for Llama-3) is
+// split over ARGMAX_SPLIT CTAs; each folds its slice into one 64-bit key (order-preserving bits of the value in the
+// high word, ~index in the low word, so a plain max picks the largest value and, among equals, the smallest index)
+// and merges it with atomicMax -- order independent, hence deterministic.  The last CTA of the row to finish writes
+// the token (and the device-side decode loop's next inputs) and re-zeroes the scratch for the next launch.
+constexpr int ARGMAX_SPLIT = 32;
+constexpr int ARGMAX_MAX_ROWS = 4096;
+static __device__ unsigned long long g_argmax_key[ARGMAX_MAX_ROWS];
+static __device__ unsigned int g_argmax_done[ARGMAX_MAX_ROWS];
+
+__device__ __forceinline__ unsigned long long argmax_pack(float v, int i) {
+    uint32_t b = __float_as_uint(v);
+    b = (b & 0x80000000u) ? ~b : (b | 0x80000000u); // monotone float -> unsigned
+    return ((unsigned long long)b << 32) | (uint32_t)(~(uint32_t)i);
+}
+
+__global__ void __launch_bounds__(256)
 argmax_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, int32_t *__restrict__ out,
               int32_t *__restrict__ feed_tok, int32_t *__restrict__ feed_pos) {
-    const float *x = logits + (int64_t)blockIdx.x * stride;
-    float best = -INFINITY;
-    int bi = 0x7fffffff;
-    for (int i = threadIdx.x; i < n_vocab; i += blockDim.x) {
+    const int row = blockIdx.y;
+    const float *x = logits + (int64_t)row * stride;
+    const int per = (n_vocab + ARGMAX_SPLIT - 1) / ARGMAX_SPLIT;
+    const int i0 = blockIdx.x * per, i1 = min(n_vocab, i0 + per);
+    unsigned long long best = 0ull; // below every real key (NaNs aside): a real key has ~i >= 0x80000000 for i < 2^31
+    for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
         const float v = x[i];
-        if (v > best) { best = v; bi = i; }
+        if (v == v) best = max(best, argmax_pack(v, i));
     }
-    __shared__ float sv[32];
-    __shared__ int si[32];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-    }
-    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+    for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+    __shared__ unsigned long long sv[8];
+    if ((threadIdx.x & 31) == 0) sv[threadIdx.x >> 5] = best;
     __syncthreads();
-    if (threadIdx.x < 32) {
-        const int nw = blockDim.x >> 5;
-        best = threadIdx.x < nw ? sv[threadIdx.x] : -INFINITY;
-        bi = threadIdx.x < nw ? si[threadIdx.x] : 0x7fffffff;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-            if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
-        }
-        if (threadIdx.x == 0) {
-            const int tok = bi == 0x7fffffff ? 0 : bi;
-            out[blockIdx.x] = tok;
-            if (feed_tok) feed_tok[blockIdx.x] = tok;
-            if (feed_pos) feed_pos[blockIdx.x] += 1;
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++) best = max(best, sv[w]);
+        atomicMax(&g_argmax_key[row], best);
+        __threadfence();
+        if (atomicAdd(&g_argmax_done[row], 1u) == (unsigned)gridDim.x - 1) { // last CTA of the row
+            __threadfence();
+            const unsigned long long k = atomicExch(&g_argmax_key[row], 0ull);
+            g_argmax_done[row] = 0u;
+            const int tok = k == 0ull ? 0 : (int)(~(uint32_t)(k & 0xFFFFFFFFull));
+            out[row] = tok;
+            if (feed_tok) feed_tok[row] = tok;
+            if (feed_pos) feed_pos[row] += 1;
         }
     }
 }
@@ -179,7 +188,8 @@ argmax_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, int
 void launch_argmax(const float *logits, int64_t stride, int n_rows, int n_vocab, int32_t *out, int32_t *feed_tok,
                    int32_t *feed_pos, cudaStream_t s) {
     if (n_rows <= 0) return;
-    argmax_kernel<<<n_rows, 1024, 0, s>>>(logits, stride, n_vocab, out, feed_tok, feed_pos);
+    B2_CHECK(n_rows <= ARGMAX_MAX_ROWS, B2_EINVAL, "argmax: too many rows");
+    argmax_kernel<<<dim3(ARGMAX_SPLIT, n_rows), 256, 0, s>>>(logits, stride, n_vocab, out, feed_tok, feed_pos);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
