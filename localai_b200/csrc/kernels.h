@@ -123,6 +123,13 @@ struct MegaArgs {
     int page_shift = 0;      // log2(page_size)
     unsigned *bar = nullptr; // arrival counter, zero-initialised once; it only ever grows
     unsigned bar_base = 0;   // counter value when this launch starts; the host adds n_cta * (n_phases - 1) per launch
+    // attention of one head split over att_parts CTAs (power of two, att_parts * n_head <= CTAs; 1 = one CTA per head)
+    int att_parts = 1, att_parts_log = 0;
+    float *att_scores = nullptr;     // [n_head][att_scores_stride] scores of the current layer
+    int64_t att_scores_stride = 0;
+    float *att_part_out = nullptr;   // [n_head][att_parts][hd] partial outputs
+    unsigned *att_cnt = nullptr;     // [n_head][2] counters (scores written, partial outputs written), zero-initialised once
+    unsigned att_base = 0;           // counter value when this launch starts; the host adds n_att_phases * att_parts per launch
     long long *dbg = nullptr; // optional [n_cta][n_phases][4] clock64 stamps: start, after prologue, after stages, after barrier
 };
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s);

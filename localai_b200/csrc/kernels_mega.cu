@@ -547,6 +547,168 @@ __device__ __noinline__ void mg_attention(const float *__restrict__ qrow, int n_
     __syncthreads();
 }
 
+// ---- attention of ONE head split over `parts` CTAs (contiguous position ranges), exact soft-max ------------------
+// With one head per CTA, 116 of the 148 SMs idle through the attention phase while 32 of them each pull 64 KB of K/V
+// through one SM's load path.  Here parts (= 4 for 32 heads) CTAs share a head:
+//   1. each computes the scores of its positions (4 threads per position, 64 contiguous bytes per 4-lane group and
+//      load: fully used sectors) and writes them to a per-head row in global memory;
+//   2. a mini-barrier among the head's CTAs (release-add / acquire-poll on a per-head counter that only grows);
+//   3. each reads ALL the scores of the head and does the soft-max redundantly (a few hundred elements), so the
+//      probabilities -- including their rounding to f16 -- are exactly those of the unsplit computation;
+//   4. each accumulates p.V over its own positions (V rows were requested at phase start) and writes a partial
+//      output row; the CTA that arrives last at a second per-head counter adds the partial rows in part order.
+// scratch: q[hd] | red[32] | part[8][hd] | scores[n_kv]
+__device__ __forceinline__ void mg_attention_split(const float *__restrict__ qrow, int n_kv, const int *pbase, const __half *k_pool,
+                                               const __half *v_pool, int page_shift, int kvd, int hk, int hd, float scale,
+                                               float *__restrict__ orow, float *scratch, int tid, int part, int parts,
+                                               float *g_scores, float *g_part, unsigned *cnt_s, unsigned *cnt_o, unsigned target, long long *dd) {
+    const int lane = tid & 31, warp = tid >> 5;
+    long long ts0 = 0;
+    if (dd && tid == 0) ts0 = clock64();
+    float *qs = scratch, *red = qs + hd, *pw = red + 32, *sc = pw + MG_WARPS * hd;
+    __shared__ int s_last;
+    const int chunk = (n_kv + parts - 1) / parts;
+    const int j_lo = min(n_kv, part * chunk), j_hi = min(n_kv, j_lo + chunk);
+    const int qd = tid & 3;                  // pass 1: 4 threads per position; load i covers bytes [64 i + 16 qd, +16) of the row
+    const int nld = hd / 32;                 // 16-byte loads per thread (hd 128 -> 4, hd 64 -> 2)
+    const int dpl = hd / 32, nw = dpl / 2;   // pass 2: halves / words per lane
+    constexpr int KP = MG_THREADS / 4;       // 64 positions per round
+    constexpr int VP = 8;                    // V: local position = j0 + warp + 8u
+    int4 kq[4];
+    uint32_t vq[VP][2];
+    // NOTE: the loads are UNCONDITIONAL on clamped (always valid) positions.  A load under `if (j < j_hi)` into a
+    // register that keeps its old value otherwise is compiled as load + select, and the select waits for the load:
+    // eight such loads in a row cost eight L2 round trips instead of one.
+    const int j_last = max(j_hi - 1, 0);
+    auto load_k = [&](int j0) {
+        const int j = min(j0 + (tid >> 2), j_last);
+        const __half *kr = mg_kv_row(k_pool, pbase, j, page_shift, kvd) + hk * hd + qd * 8;
+#pragma unroll
+        for (int i = 0; i < 4; i++) kq[i] = *(const int4 *)(kr + (i < nld ? i : 0) * 32); // unconditional, see the note above
+    };
+    auto load_v = [&](int j0) {
+#pragma unroll
+        for (int u = 0; u < VP; u++) {
+            const int jv = min(j0 + warp + MG_WARPS * u, j_last);
+            const __half *vr = mg_kv_row(v_pool, pbase, jv, page_shift, kvd) + hk * hd + lane * dpl;
+            if (nw == 2) { const int2 t = *(const int2 *)vr; vq[u][0] = t.x; vq[u][1] = t.y; }
+            else { vq[u][0] = *(const uint32_t *)vr; vq[u][1] = 0u; }
+        }
+    };
+    if (dd && tid == 0) dd[5] = clock64() - ts0;
+    load_k(j_lo);
+    if (dd && tid == 0) dd[6] = clock64() - ts0;
+    load_v(j_lo);
+    if (dd && tid == 0) dd[8] = clock64() - ts0;
+    for (int i = tid; i < hd; i += MG_THREADS) qs[i] = __half2float(__float2half_rn(__ldcg(qrow + i))); // q comes from other SMs
+    __syncthreads();
+    if (dd && tid == 0) dd[9] = clock64() - ts0;
+
+    // ---- 1. scores of my positions -> global
+    for (int j0 = j_lo; j0 < j_hi; j0 += KP) {
+        if (j0 > j_lo) load_k(j0);
+        const int j = j0 + (tid >> 2);
+        float acc = 0.f;
+        if (j < j_hi) {
+            float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (i < nld) {
+                    const __half2 *kh = (const __half2 *)&kq[i];
+                    const float *qh = qs + i * 32 + qd * 8;
+                    const float4 qa = *(const float4 *)qh, qb = *(const float4 *)(qh + 4);
+                    const float2 k0 = __half22float2(kh[0]), k1 = __half22float2(kh[1]), k2 = __half22float2(kh[2]), k3 = __half22float2(kh[3]);
+                    a0 += k0.x * qa.x; a1 += k0.y * qa.y; a0 += k1.x * qa.z; a1 += k1.y * qa.w;
+                    a0 += k2.x * qb.x; a1 += k2.y * qb.y; a0 += k3.x * qb.z; a1 += k3.y * qb.w;
+                }
+            acc = a0 + a1;
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        if (j < j_hi && qd == 0) g_scores[j] = acc * scale;
+    }
+    // ---- 2. the head's CTAs meet
+    if (dd && tid == 0) dd[10] = clock64() - ts0;
+    __syncthreads();
+    if (tid == 0) mg_grid_barrier(cnt_s, target);
+    __syncthreads();
+    if (dd && tid == 0) dd[11] = clock64() - ts0;
+    // ---- 3. soft-max over ALL positions of the head (redundantly in every part)
+    float lmax = -INFINITY;
+    for (int j = tid; j < n_kv; j += MG_THREADS) {
+        const float v = __ldcg(g_scores + j);
+        sc[j] = v;
+        lmax = fmaxf(lmax, v);
+    }
+    lmax = warp_max(lmax);
+    if (lane == 0) red[warp] = lmax;
+    __syncthreads();
+    float mx = red[0];
+#pragma unroll
+    for (int i = 1; i < MG_WARPS; i++) mx = fmaxf(mx, red[i]);
+    float lsum = 0.f;
+    for (int j = tid; j < n_kv; j += MG_THREADS) {
+        const float e = expf(sc[j] - mx);
+        sc[j] = e;
+        lsum += e;
+    }
+    lsum = warp_sum(lsum);
+    if (lane == 0) red[16 + warp] = lsum;
+    __syncthreads();
+    double tot = 0.0;
+#pragma unroll
+    for (int i = 0; i < MG_WARPS; i++) tot += (double)red[16 + i];
+    const float inv = (float)(1.0 / tot);
+    for (int j = j_lo + tid; j < j_hi; j += MG_THREADS) sc[j] = __half2float(__float2half_rn(__fmul_rn(sc[j], inv)));
+    __syncthreads();
+    if (dd && tid == 0) dd[12] = clock64() - ts0;
+    // ---- 4. partial output over my positions
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int j0 = j_lo; j0 < j_hi; j0 += VP * MG_WARPS) {
+        if (j0 > j_lo) load_v(j0);
+#pragma unroll
+        for (int u = 0; u < VP; u++) {
+            const int jv = j0 + warp + MG_WARPS * u;
+            if (jv < j_hi) {
+                const float pj = sc[jv];
+#pragma unroll
+                for (int k = 0; k < 2; k++)
+                    if (k < nw) {
+                        const float2 vv = __half22float2(*(const __half2 *)&vq[u][k]);
+                        acc[2 * k] += vv.x * pj;
+                        acc[2 * k + 1] += vv.y * pj;
+                    }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+        if (i < dpl) pw[warp * hd + lane * dpl + i] = acc[i];
+    __syncthreads();
+    for (int i = tid; i < hd; i += MG_THREADS) {
+        float o = 0.f;
+#pragma unroll
+        for (int w = 0; w < MG_WARPS; w++) o += pw[w * hd + i];
+        g_part[part * hd + i] = o;
+    }
+    __syncthreads();
+    if (dd && tid == 0) dd[13] = clock64() - ts0;
+    if (tid == 0) {
+        unsigned prev;
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(prev) : "l"(cnt_o) : "memory");
+        s_last = (prev + 1 == target);
+    }
+    __syncthreads();
+    if (s_last)
+        for (int i = tid; i < hd; i += MG_THREADS) {
+            float o = 0.f;
+            for (int pp = 0; pp < parts; pp++) o += __ldcg(g_part + pp * hd + i);
+            orow[i] = o;
+        }
+    __syncthreads();
+    if (dd && tid == 0) dd[14] = clock64() - ts0;
+}
+
 // Pull the K/V rows (positions < n_kv) of one KV head into L2 ahead of the attention phase.
 __device__ __forceinline__ void mg_prefetch_kv(int n_kv, const int *pbase, const __half *k_pool, const __half *v_pool, int page_shift,
                                                int kvd, int hk, int hd, int tid) {
@@ -583,17 +745,22 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
         const int b = warp + (k_first + k) * MG_WARPS;
         valid[k] = b < nb;
         const float4 *xb = (const float4 *)(xrow + (valid[k] ? b : 0) * 256 + lane * 8);
-        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0; // blocks past the row's end are carried as zeros
-        if (valid[k]) { a0 = __ldcg(xb); a1 = __ldcg(xb + 1); } // the row was written by other SMs: L2
+        // Loads are unconditional (block index clamped): a load under a condition into a register that otherwise keeps
+        // its value becomes load + select, and the select waits for the load -- the PBN round trips would serialise.
+        const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1); // the row was written by other SMs: L2
         v[k][0] = a0.x; v[k][1] = a0.y; v[k][2] = a0.z; v[k][3] = a0.w;
         v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
-        if (PBN <= 2 && has_norm) { // norm weights ride the same round trip
-            const float4 *wb = (const float4 *)(ph.norm_w + (valid[k] ? b : 0) * 256 + lane * 8);
+        if (PBN <= 2) { // norm weights ride the same round trip (without a norm: a dummy read of the row itself)
+            const float4 *wb = (const float4 *)((has_norm ? ph.norm_w : xrow) + (valid[k] ? b : 0) * 256 + lane * 8);
             const float4 w0 = wb[0], w1 = wb[1];
             w[k][0] = w0.x; w[k][1] = w0.y; w[k][2] = w0.z; w[k][3] = w0.w;
             w[k][4] = w1.x; w[k][5] = w1.y; w[k][6] = w1.z; w[k][7] = w1.w;
         }
     }
+#pragma unroll
+    for (int k = 0; k < PBN; k++) // blocks past the row's end are carried as zeros
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[k][i] = valid[k] ? v[k][i] : 0.f;
     if (has_norm) {
         double sum = 0.0;
 #pragma unroll
@@ -744,6 +911,7 @@ decode_mega_kernel(const MegaArgs a) {
     pc->p = 0; pc->j = 0;
     mg_seek(a, sph, 0, pc, cta, n_cta, warp);
     uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
+    unsigned att_seq = 0;         // attention phases so far (per-head counters only grow)
     for (int s = 0; s < MG_STAGES; s++) {
         MgTile *t = (MgTile *)((uint8_t *)tiles + s * 48);
         if (pc->ok) {
@@ -762,9 +930,22 @@ decode_mega_kernel(const MegaArgs a) {
         if (DBG && tid == 0) t0 = clock64();
         int u = 0, u_end = 0;
         if (ph.kind == PH_ATT) {
-            for (int h = cta; h < a.n_head; h += n_cta)
-                mg_attention(ph.x + (int64_t)h * a.hd, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift, a.kvd,
-                             h / (a.n_head / a.n_head_kv), a.hd, a.att_scale, ph.out + (int64_t)h * a.hd, (float *)xs, tid);
+            if (a.att_parts > 1) {
+                // a head is shared by att_parts CTAs (att_parts * n_head <= n_cta, so a CTA has at most one share)
+                att_seq++;
+                if (cta < a.n_head * a.att_parts) {
+                    const int h = cta >> a.att_parts_log, part = cta & (a.att_parts - 1);
+                    mg_attention_split(ph.x + (int64_t)h * a.hd, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift, a.kvd,
+                                       h / (a.n_head / a.n_head_kv), a.hd, a.att_scale, ph.out + (int64_t)h * a.hd, (float *)xs, tid, part,
+                                       a.att_parts, a.att_scores + (int64_t)h * a.att_scores_stride, a.att_part_out + (int64_t)h * a.att_parts * a.hd,
+                                       a.att_cnt + 2 * h, a.att_cnt + 2 * h + 1, a.att_base + att_seq * (unsigned)a.att_parts,
+                                       DBG ? a.dbg + ((int64_t)cta * a.n_phases + p) * 16 : nullptr);
+                }
+            } else {
+                for (int h = cta; h < a.n_head; h += n_cta)
+                    mg_attention(ph.x + (int64_t)h * a.hd, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift, a.kvd,
+                                 h / (a.n_head / a.n_head_kv), a.hd, a.att_scale, ph.out + (int64_t)h * a.hd, (float *)xs, tid);
+            }
         } else {
             mg_cta_range(ph, cta, n_cta, u, u_end);
         }
@@ -984,8 +1165,8 @@ decode_mega_kernel(const MegaArgs a) {
         }
         if (DBG && tid == 0) {
             long long *dd = a.dbg + ((int64_t)cta * a.n_phases + p) * 16;
-            dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64(); dd[4] = t_wait; dd[5] = t_comp; dd[6] = t_epi ? t2 - t_epi : 0; dd[7] = n_tiles;
-            dd[8] = tp0 - t0; dd[9] = t_advc; dd[10] = tp3 - tp0; dd[11] = t_iss; dd[12] = t1 - tp3; dd[13] = t_epi - tl_end; dd[14] = tl_end - t1; dd[15] = t_advp;
+            dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64(); if (u < u_end) { dd[4] = t_wait; dd[5] = t_comp; dd[6] = t_epi ? t2 - t_epi : 0; dd[7] = n_tiles; }
+            if (u < u_end) { dd[8] = tp0 - t0; dd[9] = t_advc; dd[10] = tp3 - tp0; dd[11] = t_iss; dd[12] = t1 - tp3; dd[13] = t_epi - tl_end; dd[14] = tl_end - t1; dd[15] = t_advp; }
         }
     }
 }

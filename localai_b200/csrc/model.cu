@@ -503,6 +503,16 @@ void Model::build_mega() {
     B2_CUDA(cudaStreamSynchronize(stream));
     mega_n_phases_ = (int)ph.size();
     if (!mega_bar_) {
+        // attention of one head is shared by up to 4 CTAs (B200LLM_ATT_PARTS overrides; 1 = one CTA per head)
+        mega_att_parts_ = 1;
+        while (mega_att_parts_ < 4 && hp.n_head * mega_att_parts_ * 2 <= n_sm_) mega_att_parts_ *= 2;
+        if (getenv("B200LLM_ATT_PARTS")) mega_att_parts_ = std::max(1, atoi(getenv("B200LLM_ATT_PARTS")));
+        while (mega_att_parts_ > 1 && (hp.n_head * mega_att_parts_ > n_sm_ || (mega_att_parts_ & (mega_att_parts_ - 1)))) mega_att_parts_--;
+        mega_att_scores_ = (float *)dalloc((size_t)hp.n_head * n_ctx_slot * sizeof(float));
+        mega_att_part_ = (float *)dalloc((size_t)hp.n_head * mega_att_parts_ * hp.head_dim * sizeof(float));
+        mega_att_cnt_ = (unsigned *)dalloc((size_t)hp.n_head * 2 * sizeof(unsigned));
+        B2_CUDA(cudaMemsetAsync(mega_att_cnt_, 0, (size_t)hp.n_head * 2 * sizeof(unsigned), stream));
+        mega_att_base_ = 0;
         mega_bar_ = (unsigned *)dalloc(4096);
         B2_CUDA(cudaMemsetAsync(mega_bar_, 0, 4096, stream));
         mega_epoch_ = 0;
@@ -526,6 +536,13 @@ void Model::run_decode_mega() {
     a.eps = hp.rms_eps; a.att_scale = 1.0f / sqrtf((float)hp.head_dim);
     a.page_shift = 0;
     while ((1 << a.page_shift) < page_size) a.page_shift++;
+    a.att_parts = mega_att_parts_;
+    a.att_parts_log = 0;
+    while ((1 << a.att_parts_log) < a.att_parts) a.att_parts_log++;
+    a.att_scores = mega_att_scores_; a.att_scores_stride = n_ctx_slot;
+    a.att_part_out = mega_att_part_; a.att_cnt = mega_att_cnt_;
+    a.att_base = mega_att_base_;
+    mega_att_base_ += (unsigned)hp.n_layer * (unsigned)mega_att_parts_;
     a.bar = mega_bar_;
     a.bar_base = mega_epoch_;
     mega_epoch_ += (unsigned)n_sm_ * (unsigned)(mega_n_phases_ - 1);

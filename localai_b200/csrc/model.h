@@ -97,7 +97,10 @@ class Model {
     void build_mega();
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;
-    unsigned mega_epoch_ = 0;
+    unsigned mega_epoch_ = 0, mega_att_base_ = 0;
+    int mega_att_parts_ = 1;
+    float *mega_att_scores_ = nullptr, *mega_att_part_ = nullptr;
+    unsigned *mega_att_cnt_ = nullptr;
     unsigned *mega_bar_ = nullptr;
     long long *mega_dbg_ = nullptr;
   public:

@@ -24,8 +24,8 @@ print("lm_head  prologue", pro[:,-1].mean(), "stages mean", stg[:,-1].mean(), "m
 tot = (d[:,-1,3]-d[:,0,0]); print("total cycles per CTA mean", tot.mean(), "=> ms at 1.9GHz", tot.mean()/1.9e6)
 
 idx = np.arange(1, nph-1, 5)
-a = d[:32][:, idx, :]
-print("attention (CTAs 0-31) cumulative cycles: preload-issued %.0f  q-sync %.0f  scores %.0f  max-sync %.0f  softmax-sync %.0f  pass2 %.0f  end %.0f" % tuple(a[:,:,k].mean() for k in (8,9,10,11,12,13,14)))
-print("raw CTA0 layer3 att slot:", d[0, 1+5*3, :].tolist())
-print("raw CTA5 layer7 att slot:", d[5, 1+5*7, :].tolist())
-print("raw CTA100 layer7 att slot:", d[100, 1+5*7, :].tolist())
+a = d[:128][:, idx, :]
+print("split attention (CTAs 0-127) cumulative cycles: loads-issued %.0f  q-sync %.0f  scores-written %.0f  mini-barrier %.0f  softmax %.0f  partial-out %.0f  end %.0f" % tuple(a[:,:,k].mean() for k in (8,9,10,11,12,13,14)))
+print("split attention: entry->before loads %.0f, after K loads %.0f, after V loads %.0f" % tuple(a[:,:,k].mean() for k in (5,6,8)))
+print("raw CTA0 layer3:", d[0, 1+5*3, :].tolist())
+print("raw CTA77 layer9:", d[77, 1+5*9, :].tolist())
