@@ -140,7 +140,7 @@ def cpu_sample(path: str, n_prompt: int, n_decode: int):
     return n_decode / (t2 - t1), n_prompt / (t1 - t0), O.num_threads()
 
 
-def run_reference(args, rank: int):
+def run_reference(args, rank: int, emit):
     if rank != 0:
         return
     path, info = ensure_model(args.arch, args.preset, args.seed, 0, lambda: None)
@@ -178,7 +178,7 @@ def run_reference(args, rank: int):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -199,9 +199,16 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # stdout carries exactly ONE JSON line: libraries that print there (NCCL's version banner) go to stderr instead
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line: dict):
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
 
     if args.impl == "reference":
-        run_reference(args, rank)
+        run_reference(args, rank, emit)
         return 0
 
     warmup = max(args.warmup, 3)
@@ -305,7 +312,7 @@ def main():
             "e2e": e2e, "gpu_launches": int(launches) * args.steps, "gpu_launches_per_step": int(launches),
             "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "extra": extra,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     ranks.close()
     return 0
 
