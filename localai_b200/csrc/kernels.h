@@ -146,8 +146,10 @@ void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t 
 void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s);
 // out[t][r] = W[r] . x[t] (+ residual): tcgen05/TMEM GEMM on bf16 operand tiles; W is dequantised into w_tiles first
 // unless w_tiles_ready (the caller keeps W's tiles resident)
+// splitk_scratch (optional, fp32): with <= 128 tokens and fewer output tiles than SMs the K range is split over the
+// idle SMs; the slices' partial tiles go through this buffer and are summed in slice order
 void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
-                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, cudaStream_t s);
+                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, float *splitk_scratch, size_t splitk_bytes, cudaStream_t s);
 
 // --- sampling -------------------------------------------------------------------------------------------
 // out[r] = first argmax of row r.  If feed_tok/feed_pos are given (device-side decode loop) the sampled id is also

@@ -192,7 +192,31 @@ struct GemmArgs {
     int64_t res_stride;
     int M, N, k_tiles, m_tiles, n_tiles;
     uint32_t lbo, sbo;
+    // split-K for small M (batched decode): with one m-tile and few n-tiles most SMs would have no work item, and the
+    // weight tiles are the bytes that have to stream.  A work item is (m-tile, n-tile, k-slice); slices write fp32
+    // partial tiles to `partial` [ksplit][M][N], summed in slice order by gemm_splitk_reduce_kernel.
+    int ksplit, k_per_split;
+    float *partial;
 };
+
+__global__ void gemm_splitk_reduce_kernel(const float *__restrict__ partial, int ksplit, int M, int N, float *__restrict__ out,
+                                          int64_t out_stride, const float *__restrict__ residual, int64_t res_stride) {
+    const int64_t total = (int64_t)M * N / 4;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t e = i * 4;
+        const int row = (int)(e / N), col = (int)(e % N);
+        float4 acc = *(const float4 *)(partial + e);
+        for (int k = 1; k < ksplit; k++) {
+            const float4 p = *(const float4 *)(partial + (int64_t)k * M * N + e);
+            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        }
+        if (residual) {
+            const float4 r = *(const float4 *)(residual + (int64_t)row * res_stride + col);
+            acc.x += r.x; acc.y += r.y; acc.z += r.z; acc.w += r.w;
+        }
+        *(float4 *)(out + (int64_t)row * out_stride + col) = acc;
+    }
+}
 
 // ------------------------------------------------------------------------------------------------ the GEMM
 __global__ void __launch_bounds__(GM_THREADS, 1)
@@ -219,7 +243,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
-    const int n_tiles_total = g.m_tiles * g.n_tiles;
+    const int n_tiles_total = g.m_tiles * g.n_tiles * g.ksplit; // work items
     // kind::f16, D = f32, A = B = bf16, both K-major, N = 256, M = 128
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(GM_BN >> 3) << 17) | ((uint32_t)(GM_BM >> 4) << 24);
 
@@ -227,8 +251,9 @@ gemm_tcgen05_kernel(const GemmArgs g) {
         if (lane == 0) { // ===== producer: one bulk copy per operand tile
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-                const int mt = tile % g.m_tiles, nt = tile / g.m_tiles;
-                for (int kt = 0; kt < g.k_tiles; kt++, it++) {
+                const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
+                const int kt0 = ks * g.k_per_split, kt1 = min(g.k_tiles, kt0 + g.k_per_split);
+                for (int kt = kt0; kt < kt1; kt++, it++) {
                     const int s = it % GM_STAGES;
                     gm_mbar_wait(empty + s, ((it / GM_STAGES) & 1) ^ 1);
                     uint8_t *sa = stages + (size_t)s * GM_STAGE_BYTES;
@@ -246,7 +271,9 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                 gm_mbar_wait(tempty + acc, ((acc_it >> 1) & 1) ^ 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t d_tmem = tmem_base + acc * GM_BN;
-                for (int kt = 0; kt < g.k_tiles; kt++, it++) {
+                const int ks = tile / (g.m_tiles * g.n_tiles);
+                const int kt0 = ks * g.k_per_split, kt1 = min(g.k_tiles, kt0 + g.k_per_split);
+                for (int kt = kt0; kt < kt1; kt++, it++) {
                     const int s = it % GM_STAGES;
                     gm_mbar_wait(full + s, (it / GM_STAGES) & 1);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -254,7 +281,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
 #pragma unroll
                     for (int k4 = 0; k4 < GM_BK / 16; k4++) { // one MMA = K 16 = two core matrices = 256 B
                         gm_mma(d_tmem, gm_desc(sa + k4 * 256, g.lbo, g.sbo), gm_desc(sb + k4 * 256, g.lbo, g.sbo), idesc,
-                               (kt | k4) != 0);
+                               ((kt - kt0) | k4) != 0);
                     }
                     gm_commit(empty + s); // frees the smem stage when these MMAs have read it
                 }
@@ -265,7 +292,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
         const int q = warp & 3; // TMEM lane quarter this warp may access
         uint32_t acc_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
-            const int mt = tile % g.m_tiles, nt = tile / g.m_tiles;
+            const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
             const int acc = acc_it & 1;
             gm_mbar_wait(tfull + acc, (acc_it >> 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -275,8 +302,8 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                 gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
                 const int col = nt * GM_BN + c0;
                 if (row < g.M && col < g.N) {
-                    float *o = g.out + (int64_t)row * g.out_stride + col;
-                    const float *res = g.residual ? g.residual + (int64_t)row * g.res_stride + col : nullptr;
+                    float *o = g.ksplit > 1 ? g.partial + ((int64_t)ks * g.M + row) * g.N + col : g.out + (int64_t)row * g.out_stride + col;
+                    const float *res = (g.residual && g.ksplit == 1) ? g.residual + (int64_t)row * g.res_stride + col : nullptr;
                     if (col + 32 <= g.N) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 4) {
@@ -328,7 +355,7 @@ void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s) {
 }
 
 void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
-                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, cudaStream_t s) {
+                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, float *splitk_scratch, size_t splitk_bytes, cudaStream_t s) {
     B2_CHECK(W.cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
     static thread_local bool configured = false;
     static thread_local uint32_t lbo = 128, sbo = 1024;
@@ -346,10 +373,28 @@ void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out
     g.M = n_tok; g.N = (int)W.rows; g.k_tiles = (int)(W.cols / GM_BK);
     g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = (int)(rows_pad / GM_BN);
     g.lbo = lbo; g.sbo = sbo;
-    const int grid = std::min(g.m_tiles * g.n_tiles, 148);
+    g.ksplit = 1; g.k_per_split = g.k_tiles; g.partial = nullptr;
+    const int tiles = g.m_tiles * g.n_tiles;
+    if (splitk_scratch && g.m_tiles == 1 && tiles < 148 && W.rows % 4 == 0) {
+        int ks = std::min(148 / tiles, g.k_tiles / 4);
+        while (ks > 1 && (size_t)ks * n_tok * W.rows * sizeof(float) > splitk_bytes) ks--;
+        if (ks > 1) {
+            g.k_per_split = (g.k_tiles + ks - 1) / ks;
+            g.ksplit = (g.k_tiles + g.k_per_split - 1) / g.k_per_split;
+            g.partial = splitk_scratch;
+        }
+    }
+    const int grid = std::min(tiles * g.ksplit, 148);
     gemm_tcgen05_kernel<<<grid, GM_THREADS, GM_SMEM, s>>>(g);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
+    if (g.ksplit > 1) {
+        const int64_t total = (int64_t)n_tok * W.rows / 4;
+        const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+        gemm_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(g.partial, g.ksplit, n_tok, (int)W.rows, out, out_stride, residual, res_stride);
+        g_launch_count++;
+        B2_CUDA(cudaGetLastError());
+    }
 }
 
 } // namespace b2

@@ -375,12 +375,16 @@ void *Model::resident_tiles(const DTensor &W) {
 }
 
 void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride) {
+    if (!gemm_part_) { // split-K partial tiles for batched decode (<= 128 tokens): 148 slices x 128 tokens x 256 rows at most
+        gemm_part_bytes_ = (size_t)32 << 20;
+        gemm_part_ = (float *)dalloc(gemm_part_bytes_);
+    }
     if (void *t = resident_tiles(W)) {
-        launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, t, true, stream);
+        launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, t, true, gemm_part_, gemm_part_bytes_, stream);
         return;
     }
     ensure_gemm_scratch(gemm_w_tiles_bytes(W.rows, W.cols), 0);
-    launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, false, stream);
+    launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, false, gemm_part_, gemm_part_bytes_, stream);
 }
 
 // Prefill / batched decode: every mat-mul is a tcgen05 tensor-core GEMM on bf16 operands (weights dequantised into

@@ -91,6 +91,8 @@ class Model {
     bool no_shadow_ = false;
     size_t shadow_reserve_ = (size_t)6 << 30;            // leave this much HBM free
     void *gemm_w_ = nullptr, *gemm_x_ = nullptr;
+    float *gemm_part_ = nullptr;
+    size_t gemm_part_bytes_ = 0;
     size_t gemm_w_bytes_ = 0, gemm_x_bytes_ = 0;
     bool no_gemm_ = false;
     int gemm_min_tokens_ = 4;

@@ -126,6 +126,31 @@ def test_fused_and_mega_kernels_match_oracle(wtype, rows, cols, n_tok, path):
     assert np.abs(got - ref).max() <= MATMUL_RTOL * np.abs(ref).max()
 
 
+# bf16 operands, fp32 accumulation: the error of one output is a sum of K products each off by <= 2^-8 relative
+GEMM_TC_RTOL = 1.5e-2
+
+
+@pytest.mark.parametrize("wtype,rows,cols,n_tok", [
+    (capi.B2_T_Q4_K, 256, 256, 128), (capi.B2_T_Q4_K, 512, 1024, 70), (capi.B2_T_Q6_K, 300, 512, 130),
+    (capi.B2_T_Q8_0, 256, 2048, 5), (capi.B2_T_Q5_K, 1024, 4096, 512), (capi.B2_T_F16, 256, 512, 33),
+    # batched-decode shapes: one token tile, fewer output tiles than SMs -> the K range is split over the SMs
+    (capi.B2_T_Q4_K, 4096, 4096, 64), (capi.B2_T_Q6_K, 1024, 14336, 64), (capi.B2_T_Q4_K, 512, 8192, 17)])
+def test_gemm_tcgen05_matches_float_reference(wtype, rows, cols, n_tok):
+    """the tensor-core path (prefill, batched decode): tcgen05 GEMM on bf16 tiles vs dequantised weights in float64"""
+    import make_gguf as mg
+    rng = np.random.default_rng(rows + cols + n_tok)
+    if wtype == capi.B2_T_F16:
+        raw = (rng.standard_normal((rows, cols)) / np.sqrt(cols)).astype(np.float16).view(np.uint8).reshape(-1)
+    else:
+        raw = mg.random_blocks(rng, wtype, rows * cols // mg.BLOCK[wtype][0], 1 / np.sqrt(cols)).reshape(-1)
+    w = O.dequantize(wtype, raw, rows * cols).reshape(rows, cols).astype(np.float64)
+    x = rng.standard_normal((n_tok, cols)).astype(np.float32)
+    ref = x.astype(np.float64) @ w.T
+    got = capi.mul_mat(wtype, raw, rows, cols, x, path=2)
+    assert np.isfinite(got).all()
+    assert np.abs(got - ref).max() <= GEMM_TC_RTOL * np.abs(ref).max()
+
+
 def test_mul_mat_linearity_in_rows():
     """size-independent property: rows are independent, so any row subset gives the same values."""
     import make_gguf as mg
