@@ -102,6 +102,7 @@ struct MegaPhase {
     const float *residual = nullptr;
     float *xn_out = nullptr;       // optional: the normalised row (LM head -> embeddings)
     __half *k_pool = nullptr, *v_pool = nullptr; // this layer's KV pools (QKV, ATT)
+    uint8_t *xq_global = nullptr;  // if set: the row is quantised once per GPU into this buffer (one more grid barrier)
     int units = 0;                 // row pairs (PLAIN/QKV) or rows (SWIGLU) split across the CTAs
     // lane geometry, filled by mega_phase_prepare() so that the kernel's schedule walk needs no integer division:
     int S = 1, s_log = 0;          // K-splits (power of two <= warps per CTA): a row is spread over S warps
@@ -122,7 +123,8 @@ struct MegaArgs {
     float eps = 0.f, att_scale = 0.f;
     int page_shift = 0;      // log2(page_size)
     unsigned *bar = nullptr; // arrival counter, zero-initialised once; it only ever grows
-    unsigned bar_base = 0;   // counter value when this launch starts; the host adds n_cta * (n_phases - 1) per launch
+    unsigned bar_base = 0;   // counter value when this launch starts; the host adds n_cta * (barriers per launch) per launch:
+                             // n_phases - 1, plus one per phase with xq_global
     // attention of one head split over att_parts CTAs (power of two, att_parts * n_head <= CTAs; 1 = one CTA per head)
     int att_parts = 1, att_parts_log = 0;
     float *att_scores = nullptr;     // [n_head][att_scores_stride] scores of the current layer

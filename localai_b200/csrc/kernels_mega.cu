@@ -727,6 +727,43 @@ __device__ __forceinline__ void mg_prefetch_kv(int n_kv, const int *pbase, const
 // then read their register slices (stride 128 B = one bank group) from 8 different bank groups.
 __device__ __forceinline__ int mg_swz(int c) { return c ^ ((c >> 3) & 7); }
 
+// One warp quantises ONE 256-element block of an fp32 row to Q8_K and writes it, in the shared-memory layout of the
+// phase prologue (chunk-swizzled int8 | d | bsums), to a row in GLOBAL memory.  Used for activation rows so long
+// (ffn_down: 56 blocks) that re-quantising them redundantly in every CTA costs more than a second grid barrier: the
+// blocks are spread over the CTAs, then every CTA just copies the 16 KB result.  Arithmetic = mg_prologue's.
+__device__ __forceinline__ void mg_quant_block_global(const float *xrow, int b, int64_t K, int nb, int lane, uint8_t *out) {
+    const float4 *xb = (const float4 *)(xrow + b * 256 + lane * 8);
+    const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1);
+    const float v[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    float m = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) m = fmaxf(m, fabsf(v[i]));
+    const uint32_t amax = __reduce_max_sync(0xffffffffu, __float_as_uint(m));
+    uint32_t li = 0xffffffffu;
+#pragma unroll
+    for (int i = 7; i >= 0; i--)
+        if (__float_as_uint(fabsf(v[i])) == amax) li = ((uint32_t)(lane * 8 + i) << 1) | (__float_as_uint(v[i]) >> 31);
+    const uint32_t key = __reduce_min_sync(0xffffffffu, li);
+    const float mx = __uint_as_float(amax | (key << 31));
+    const bool zero = amax == 0u;
+    const float iscale = zero ? 0.f : __fdiv_rn(-127.f, mx);
+    int sum = 0, qv[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        int vi = __float2int_rn(__fmul_rn(iscale, v[i]));
+        vi = min(127, vi);
+        qv[i] = vi;
+        sum += vi;
+    }
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+    int2 packed;
+    packed.x = (qv[0] & 0xFF) | ((qv[1] & 0xFF) << 8) | ((qv[2] & 0xFF) << 16) | ((qv[3] & 0xFF) << 24);
+    packed.y = (qv[4] & 0xFF) | ((qv[5] & 0xFF) << 8) | ((qv[6] & 0xFF) << 16) | ((qv[7] & 0xFF) << 24);
+    *(int2 *)(out + mg_swz(b * 16 + (lane >> 1)) * 16 + (lane & 1) * 8) = packed;
+    if ((lane & 1) == 0) ((int16_t *)(out + K + nb * 4))[b * 16 + (lane >> 1)] = (int16_t)sum;
+    if (lane == 0) ((float *)(out + K))[b] = zero ? 0.f : __fdiv_rn(1.f, iscale);
+}
+
 // (RMSNorm ->) quantise the activation row into shared memory, redundantly per CTA.  Written for LATENCY: warp w owns
 // the 256-element blocks w, w+8, ... (PBN of them, all in registers), every global load is issued before the first
 // use, invalid blocks are carried as zeros instead of branches so that the PBN dependency chains interleave, and the
@@ -912,6 +949,7 @@ decode_mega_kernel(const MegaArgs a) {
     mg_seek(a, sph, 0, pc, cta, n_cta, warp);
     uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
     unsigned att_seq = 0;         // attention phases so far (per-head counters only grow)
+    unsigned bar_i = 0;           // grid barriers so far in this launch
     for (int s = 0; s < MG_STAGES; s++) {
         MgTile *t = (MgTile *)((uint8_t *)tiles + s * 48);
         if (pc->ok) {
@@ -949,13 +987,28 @@ decode_mega_kernel(const MegaArgs a) {
         } else {
             mg_cta_range(ph, cta, n_cta, u, u_end);
         }
+        if (ph.kind != PH_ATT && ph.xq_global) {
+            // A long activation row is quantised ONCE per GPU (block b by CTA b), not once per CTA: one more grid
+            // barrier, then the prologue below is a 16 KB copy.
+            const int nbq = (int)(ph.K >> 8);
+            if (warp == 0)
+                for (int b = cta; b < nbq; b += n_cta) mg_quant_block_global(ph.x, b, ph.K, nbq, lane, ph.xq_global);
+            __syncthreads();
+            bar_i++;
+            if (tid == 0) mg_grid_barrier(a.bar, a.bar_base + bar_i * (unsigned)n_cta);
+            __syncthreads();
+        }
         if (u < u_end) {
             const int64_t K = ph.K;
             const int nb = (int)(K >> 8);
             const int S = ph.S, rpp = ph.rpp, np = ph.np;
             // ---- prologue: (RMSNorm ->) quantise the activation row into shared memory
             if (DBG && tid == 0) tp0 = clock64();
-            {
+            if (ph.xq_global) { // already quantised (above): copy
+                const int n16 = (int)((K + nb * 4 + K / 8 + 15) / 16);
+                for (int i = tid; i < n16; i += MG_THREADS) ((int4 *)xs)[i] = __ldcg((const int4 *)ph.xq_global + i);
+                __syncthreads();
+            } else {
                 const bool wx = ph.xn_out && cta == 0;
                 if (nb <= MG_WARPS) mg_prologue<1>(ph, a.eps, xs, s_part, nb, 0, warp, lane, wx);
                 else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, a.eps, xs, s_part, nb, 0, warp, lane, wx);
@@ -1160,7 +1213,8 @@ decode_mega_kernel(const MegaArgs a) {
         if (p + 1 < a.n_phases) {
             __syncthreads();
             stage_phase(p + MG_PH_WIN); // phase p's slot is free: everyone is past its epilogue (warps 1.. do the copy)
-            if (tid == 0) mg_grid_barrier(a.bar, a.bar_base + (unsigned)(p + 1) * (unsigned)n_cta);
+            bar_i++;
+            if (tid == 0) mg_grid_barrier(a.bar, a.bar_base + bar_i * (unsigned)n_cta);
             __syncthreads();
         }
         if (DBG && tid == 0) {

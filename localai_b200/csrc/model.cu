@@ -497,8 +497,17 @@ void Model::build_mega() {
     h.x = x_; h.norm_w = (const float *)output_norm.data; h.out = logits_; h.xn_out = xn_out_; h.units = (int)(output.rows / 2);
     ph.push_back(h);
     cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
-    for (auto &p : ph)
+    // ffn_down's input (n_ff >= 8192) is quantised once per GPU, not once per CTA (B200LLM_NO_DIST_QUANT=1: per CTA)
+    const bool dist_quant = !(getenv("B200LLM_NO_DIST_QUANT") && atoi(getenv("B200LLM_NO_DIST_QUANT")));
+    if (!mega_xq_) mega_xq_ = (uint8_t *)dalloc(64 * 1024);
+    mega_n_bar_ = (int)ph.size() - 1;
+    for (auto &p : ph) {
+        if (dist_quant && p.kind == PH_PLAIN && !p.norm_w && p.fmt == ACT_Q8_K && p.K / 256 > 32 && p.K <= 32768) {
+            p.xq_global = mega_xq_;
+            mega_n_bar_++;
+        }
         if (!mega_phase_prepare(p, n_sm_)) return;
+    }
     if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1)) ||
         (uint64_t)pool_layer_stride_ >= (1ull << 31))
         return;
@@ -549,7 +558,7 @@ void Model::run_decode_mega() {
     mega_att_base_ += (unsigned)hp.n_layer * (unsigned)mega_att_parts_;
     a.bar = mega_bar_;
     a.bar_base = mega_epoch_;
-    mega_epoch_ += (unsigned)n_sm_ * (unsigned)(mega_n_phases_ - 1);
+    mega_epoch_ += (unsigned)n_sm_ * (unsigned)mega_n_bar_;
     a.dbg = mega_dbg_;
     launch_decode_mega(a, n_sm_, stream);
 }

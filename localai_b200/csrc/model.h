@@ -100,6 +100,8 @@ class Model {
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;
     unsigned mega_epoch_ = 0, mega_att_base_ = 0;
+    int mega_n_bar_ = 0;
+    uint8_t *mega_xq_ = nullptr;
     int mega_att_parts_ = 1;
     float *mega_att_scores_ = nullptr, *mega_att_part_ = nullptr;
     unsigned *mega_att_cnt_ = nullptr;
