@@ -197,13 +197,16 @@ __device__ __forceinline__ void mg_locate_row(const MegaPhase &ph, int u, int &j
 // trip, and two 20-register cursors are exactly what the register allocator would spill.
 struct MgCur {
     int p, j;          // phase, job (matrix) inside the phase
-    int r, r1;         // job-local rows still to do for this warp: [r, r1)
-    int type, S, q, rb, R;
-    int dr_off;        // index of job-local row r in the phase's partial-sum rows = dr_off + r
+    int left;          // rows of the job still to issue for this warp
+    int dr;            // index of the next row in the phase's partial-sum rows
+    int type, S, rb, R;
     int ks;            // K / S
-    int64_t stride, koff, K;
-    const uint8_t *W;
-    bool ok;
+    int stride;        // row stride in bytes
+    int ok;
+    int pad;
+    const uint8_t *src; // next row (start of the row, not of the K-split)
+    int64_t koff;       // byte offset of this warp's K-split inside a row (Q8_0: of its int8 range)
+    int64_t doff;       // Q6_K: offset of the K-split's fp16 scales inside a row; Q8_0: of its scale range
 };
 
 // Position the cursor on the first (phase, job) at or after (c.p, c.j) in which this warp has rows.
@@ -212,9 +215,9 @@ struct MgCur {
 __device__ __forceinline__ const MegaPhase &mg_phase(const MegaArgs &a, const MegaPhase *sph, int p_cur, int p) {
     return (unsigned)(p - p_cur) < (unsigned)MG_PH_WIN ? sph[p & (MG_PH_WIN - 1)] : a.phases[p];
 }
-__device__ __forceinline__ void mg_seek(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *cp, int cta, int n_cta, int warp) {
+__device__ __noinline__ void mg_seek(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *cp, int cta, int n_cta, int warp) {
     MgCur &c = *cp;
-    c.ok = false;
+    c.ok = 0;
     while (c.p < a.n_phases) {
         const MegaPhase &ph = mg_phase(a, sph, p_cur, c.p);
         if (ph.kind != PH_ATT) {
@@ -235,15 +238,20 @@ __device__ __forceinline__ void mg_seek(const MegaArgs &a, const MegaPhase *sph,
                 }
                 if (hi > lo) {
                     const int n = hi - lo;
-                    c.r = lo + ((n * g) >> g_log);
-                    c.r1 = lo + ((n * (g + 1)) >> g_log);
-                    if (c.r1 > c.r) {
-                        c.type = job.type; c.S = S; c.q = warp & (S - 1); c.rb = ph.rb[c.j]; c.R = ph.R[c.j];
-                        c.dr_off = dr_off; c.K = ph.K; c.ks = (int)(ph.K >> ph.s_log);
-                        c.stride = job.row_stride; c.W = job.W;
-                        const int64_t nbs = (ph.K >> 8) >> ph.s_log;
-                        c.koff = job.type == B2_T_Q4_K ? c.q * nbs * 144 : job.type == B2_T_Q6_K ? c.q * nbs * Q6_BLK : (int64_t)c.q * c.ks;
-                        c.ok = true;
+                    const int r0 = lo + ((n * g) >> g_log), r1 = lo + ((n * (g + 1)) >> g_log);
+                    if (r1 > r0) {
+                        const int q = warp & (S - 1);
+                        const int64_t nbs = (ph.K >> 8) >> ph.s_log, nb = ph.K >> 8;
+                        c.left = r1 - r0;
+                        c.dr = dr_off + r0;
+                        c.type = job.type; c.S = S; c.rb = ph.rb[c.j]; c.R = ph.R[c.j];
+                        c.ks = (int)(ph.K >> ph.s_log);
+                        c.stride = (int)job.row_stride;
+                        c.src = job.W + (int64_t)r0 * job.row_stride;
+                        if (job.type == B2_T_Q4_K) { c.koff = q * nbs * 144; c.doff = 0; }
+                        else if (job.type == B2_T_Q6_K) { c.koff = q * nbs * Q6_BLK; c.doff = nb * Q6_BLK + 2 * q * nbs; }
+                        else { c.koff = (int64_t)q * c.ks; c.doff = ph.K + (int64_t)q * (c.ks >> 4); }
+                        c.ok = 1;
                         return;
                     }
                 }
@@ -255,52 +263,58 @@ __device__ __forceinline__ void mg_seek(const MegaArgs &a, const MegaPhase *sph,
     }
 }
 
-// What a ring stage holds, written by the producer side when it issues the copies and read by the consumer side.
+// What a ring stage holds, written by the producer side when it issues the copies and read by the consumer side:
+// two 16-byte words.
 struct MgTile {
     int p;             // phase the tile belongs to; MG_NO_TILE when the stage is empty
-    int type, n, rb;   // ggml type, rows, row pitch
+    int tnr;           // ggml type | rows << 8 | row pitch << 16
     int dr;            // first row's index in the phase's partial-sum rows
-    int pad;
-    int64_t stride;    // Q6_K: row stride and pointer to the fp16 scales of this K-split in the first row
+    int stride;        // Q6_K: row stride, and pointer to the fp16 scales of this K-split in the first row
     const uint8_t *dp;
+    int64_t pad;
 };
 constexpr int MG_NO_TILE = 0x7fffffff;
 
-// Issue the bulk copies of the cursor's next tile (n rows) into `stage` and describe it in *t; all lanes call it.
-__device__ __forceinline__ void mg_issue(const MgCur &c, int n, uint32_t stage, uint32_t bar, int lane, MgTile *t) {
-    const uint8_t *src = c.W + (int64_t)c.r * c.stride;
-    t->p = c.p; t->type = c.type; t->n = n; t->rb = c.rb; t->dr = c.dr_off + c.r; t->stride = c.stride;
-    t->dp = src + (c.K >> 8) * Q6_BLK + 2 * (int64_t)c.q * (c.ks >> 8);
+// Issue the bulk copies of the cursor's next tile into `stage`, describe it in *t, and step the cursor (a seek only when
+// the matrix is exhausted).  All lanes call it; ~40 instructions on the common path.
+__device__ __forceinline__ void mg_issue_next(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *cp, uint32_t stage, uint32_t bar,
+                                              int lane, MgTile *t, int cta, int n_cta, int warp) {
+    MgCur &c = *cp;
+    const int left = c.left, n = min(c.R, left), rb = c.rb, stride = c.stride, type = c.type;
+    const uint8_t *src = c.src;
+    {
+        int4 w0;
+        w0.x = c.p; w0.y = type | (n << 8) | (rb << 16); w0.z = c.dr; w0.w = stride;
+        *(int4 *)t = w0;
+        t->dp = src + c.doff;
+    }
     if (c.S == 1) { // whole rows, contiguous in memory: one copy
         if (lane == 0) {
-            const uint32_t bytes = (uint32_t)(n * c.stride);
+            const uint32_t bytes = (uint32_t)(n * stride);
             mg_expect_tx(bar, bytes);
             mg_bulk(stage, src, bytes, bar);
         }
     } else {        // one K-split of n rows: a copy per row (Q8_0: its int8 range and its scale range)
-        if (lane == 0) mg_expect_tx(bar, (uint32_t)(n * c.rb));
+        if (lane == 0) mg_expect_tx(bar, (uint32_t)(n * rb));
         __syncwarp();
         if (lane < n) {
-            const uint8_t *s = src + (int64_t)lane * c.stride;
-            const uint32_t dst = stage + lane * c.rb;
-            if (c.type == B2_T_Q8_0) {
-                mg_bulk(dst, s + c.koff, (uint32_t)c.ks, bar);
-                mg_bulk(dst + c.ks, s + c.K + c.koff / 16, (uint32_t)(c.ks / 16), bar);
+            const uint8_t *sr = src + (int64_t)lane * stride;
+            const uint32_t dst = stage + lane * rb;
+            if (type == B2_T_Q8_0) {
+                mg_bulk(dst, sr + c.koff, (uint32_t)c.ks, bar);
+                mg_bulk(dst + c.ks, sr + c.doff, (uint32_t)(c.ks / 16), bar);
             } else {
-                mg_bulk(dst, s + c.koff, (uint32_t)c.rb, bar);
+                mg_bulk(dst, sr + c.koff, (uint32_t)rb, bar);
             }
         }
     }
-}
-
-__device__ __forceinline__ int mg_tile_rows(const MgCur &c) { return min(c.R, c.r1 - c.r); }
-__device__ __forceinline__ void mg_advance(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *c, int n, int cta, int n_cta,
-                                           int warp) {
-    const int r = c->r + n;
-    c->r = r;
-    if (r >= c->r1) {
-        c->j++;
-        mg_seek(a, sph, p_cur, c, cta, n_cta, warp);
+    if (left > n) {
+        c.left = left - n;
+        c.dr += n;
+        c.src = src + (int64_t)n * stride;
+    } else {
+        c.j++;
+        mg_seek(a, sph, p_cur, cp, cta, n_cta, warp);
     }
 }
 
@@ -953,9 +967,7 @@ decode_mega_kernel(const MegaArgs a) {
     for (int s = 0; s < MG_STAGES; s++) {
         MgTile *t = (MgTile *)((uint8_t *)tiles + s * 48);
         if (pc->ok) {
-            const int n = mg_tile_rows(*pc);
-            mg_issue(*pc, n, ring + s * MG_STAGE_BYTES, bar0 + s * 8, lane, t);
-            mg_advance(a, sph, 0, pc, n, cta, n_cta, warp);
+            mg_issue_next(a, sph, 0, pc, ring + s * MG_STAGE_BYTES, bar0 + s * 8, lane, t, cta, n_cta, warp);
         } else {
             t->p = MG_NO_TILE;
         }
@@ -1059,10 +1071,11 @@ decode_mega_kernel(const MegaArgs a) {
             // ---- this warp's tiles of the phase
             while (true) {
                 MgTile *tile = (MgTile *)((uint8_t *)tiles + stg * 48);
-                if (tile->p != p) break;
-                const int n = tile->n, rb = tile->rb, type = tile->type;
+                const int4 tw = *(const int4 *)tile;
+                if (tw.x != p) break;
+                const int type = tw.y & 0xFF, n = (tw.y >> 8) & 0xFF, rb = (int)((uint32_t)tw.y >> 16);
                 const uint32_t st = ring + stg * MG_STAGE_BYTES, bar = bar0 + stg * 8;
-                float *pout = partial + (size_t)tile->dr * S + q;
+                float *pout = partial + (size_t)tw.z * S + q;
                 long long tw0 = 0, tw1 = 0;
                 if (DBG && tid == 0) tw0 = clock64();
                 if (type == B2_T_Q4_K) {
@@ -1092,7 +1105,7 @@ decode_mega_kernel(const MegaArgs a) {
                 } else if (type == B2_T_Q6_K) {
                     // the fp16 super-block scales sit at the end of the row, outside the staged K-split: they come
                     // straight from global memory (L2), requested one row group ahead of their use
-                    const int64_t stride = tile->stride;
+                    const int64_t stride = tw.w;
                     const uint8_t *dp = tile->dp + 2 * L.kb;
                     if (rpp == 1) { // 2 rows at a time
                         uint32_t d0 = mg_ldg_u16(dp), d1 = mg_ldg_u16(dp + (n > 1 ? stride : 0));
@@ -1156,11 +1169,8 @@ decode_mega_kernel(const MegaArgs a) {
                 __syncwarp();
                 if (pc->ok) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    const int m = mg_tile_rows(*pc);
-                    mg_issue(*pc, m, st, bar, lane, tile);
-                    if (DBG && tid == 0) ta2 = clock64();
-                    mg_advance(a, sph, p, pc, m, cta, n_cta, warp);
-                    if (DBG && tid == 0) { t_iss += ta2 - ta0; t_advp += clock64() - ta2; }
+                    mg_issue_next(a, sph, p, pc, st, bar, lane, tile, cta, n_cta, warp);
+                    if (DBG && tid == 0) { ta2 = clock64(); t_iss += ta2 - ta0; }
                 } else {
                     tile->p = MG_NO_TILE;
                 }
