@@ -215,6 +215,22 @@ def test_greedy_64_tokens_identical(model_files, name):
     assert got.tolist() == want.tolist()
 
 
+@pytest.mark.parametrize("n_prompt", [300, 700])
+def test_greedy_long_context(model_files, n_prompt, monkeypatch):
+    """decode at a context where the mega-kernel's attention runs several rounds per CTA (each of the 4 CTAs that share
+    a head owns > 64 positions) -- greedy tokens identical to the oracle.  The prompt goes through the integer kernels
+    (B200LLM_GEMM_MIN_TOKENS) so that the KV cache holds the oracle's numerics, not the bf16 tensor-core path's."""
+    monkeypatch.setenv("B200LLM_GEMM_MIN_TOKENS", "1000000")
+    path = model_files["mini_q4_k_m"]
+    ref = O.OracleModel(path, n_ctx=n_prompt + 40)
+    prompt = np.random.default_rng(n_prompt).integers(0, ref.n_vocab, n_prompt).astype(np.int32)
+    want, _, margins = ref.generate_greedy(prompt, 24)
+    with capi.Engine(path, n_ctx=n_prompt + 40, n_batch=64) as e:
+        got, _, _ = e.decode_greedy(prompt, 24)
+    print(f"ctx {n_prompt}: min top-1 margin {margins.min():.4f}")
+    assert got.tolist() == want.tolist()
+
+
 def test_batched_decode_equals_single(model_files):
     """4 sequences decoded in one batch give the logits each gives alone (slots are independent)."""
     path = model_files["mini_q4_k_m"]
