@@ -35,18 +35,20 @@ __device__ __forceinline__ void attention_head(const float *__restrict__ qrow, i
     for (int j = tid; j < n_kv; j += nthreads) {
         const __half *kr = kv.k_pool + ((int64_t)pbase[j / kv.page_size] * kv.page_size + j % kv.page_size) * kv.kvd + hk * hd;
         float a = 0.f;
-        for (int i0 = 0; i0 < hd; i0 += 32) { // 4 x 16-byte loads in flight
-            int4 kq[4];
+        for (int i0 = 0; i0 < hd; i0 += 128) { // up to 16 x 16-byte loads in flight: one round trip per 128 dims
+            int4 kq[16];
 #pragma unroll
-            for (int u = 0; u < 4; u++) kq[u] = *(const int4 *)(kr + i0 + u * 8);
+            for (int u = 0; u < 16; u++) kq[u] = *(const int4 *)(kr + min(i0 + u * 8, hd - 8)); // clamped, unconditional
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const __half2 *kh = (const __half2 *)&kq[u];
+            for (int u = 0; u < 16; u++) {
+                if (i0 + u * 8 < hd) {
+                    const __half2 *kh = (const __half2 *)&kq[u];
 #pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    const float2 kk = __half22float2(kh[k]);
-                    a += kk.x * qs[i0 + u * 8 + 2 * k];
-                    a += kk.y * qs[i0 + u * 8 + 2 * k + 1];
+                    for (int k = 0; k < 4; k++) {
+                        const float2 kk = __half22float2(kh[k]);
+                        a += kk.x * qs[i0 + u * 8 + 2 * k];
+                        a += kk.y * qs[i0 + u * 8 + 2 * k + 1];
+                    }
                 }
             }
         }

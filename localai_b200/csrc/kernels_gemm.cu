@@ -124,6 +124,83 @@ __global__ void convert_x_tiles_kernel(const float *__restrict__ x, int64_t x_st
     }
 }
 
+// RMSNorm (ggml arithmetic: double-precision sum, (x * scale) * w) fused with the bf16 tile conversion: one CTA per
+// token row; rows m >= n_tok of the last tile are zeroed by the CTAs of the same tile index range.
+__global__ void __launch_bounds__(256)
+rmsnorm_x_tiles_kernel(const float *__restrict__ x, int64_t x_stride, const float *__restrict__ w, int n_tok, int64_t cols, float eps,
+                       __nv_bfloat16 *__restrict__ out, float *__restrict__ xn_out) {
+    const int r = blockIdx.x; // < m_pad
+    const int64_t k_tiles = cols / GM_BK;
+    const int64_t mt = r / GM_BM;
+    __nv_bfloat16 *tile0 = out + mt * k_tiles * (int64_t)(GM_BM * GM_BK);
+    __shared__ double part[8];
+    __shared__ float s_scale;
+    float scale = 0.f;
+    const float *xr = x + (int64_t)r * x_stride;
+    if (r < n_tok) {
+        double sum = 0.0;
+        for (int64_t i = threadIdx.x; i < cols; i += blockDim.x) {
+            const float v = xr[i];
+            sum += (double)__fmul_rn(v, v);
+        }
+        sum = warp_sum_d(sum);
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = sum;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double tot = 0.0;
+            for (int i = 0; i < 8; i++) tot += part[i];
+            const float mean = (float)(tot / (double)cols);
+            s_scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+        }
+        __syncthreads();
+        scale = s_scale;
+    }
+    for (int64_t k0 = (int64_t)threadIdx.x * 8; k0 < cols; k0 += (int64_t)blockDim.x * 8) {
+        float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (r < n_tok) {
+            const float4 a = *(const float4 *)(xr + k0), b = *(const float4 *)(xr + k0 + 4);
+            const float4 wa = *(const float4 *)(w + k0), wb = *(const float4 *)(w + k0 + 4);
+            v[0] = __fmul_rn(__fmul_rn(a.x, scale), wa.x); v[1] = __fmul_rn(__fmul_rn(a.y, scale), wa.y);
+            v[2] = __fmul_rn(__fmul_rn(a.z, scale), wa.z); v[3] = __fmul_rn(__fmul_rn(a.w, scale), wa.w);
+            v[4] = __fmul_rn(__fmul_rn(b.x, scale), wb.x); v[5] = __fmul_rn(__fmul_rn(b.y, scale), wb.y);
+            v[6] = __fmul_rn(__fmul_rn(b.z, scale), wb.z); v[7] = __fmul_rn(__fmul_rn(b.w, scale), wb.w);
+            if (xn_out) {
+                *(float4 *)(xn_out + (int64_t)r * cols + k0) = make_float4(v[0], v[1], v[2], v[3]);
+                *(float4 *)(xn_out + (int64_t)r * cols + k0 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+            }
+        }
+        __nv_bfloat16 *dst = tile0 + (k0 / GM_BK) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset(r % GM_BM, (int)(k0 % GM_BK));
+        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
+                                __floats2bfloat162_rn(v[6], v[7])};
+        *(int4 *)dst = *(const int4 *)p4;
+    }
+}
+
+// silu(gate) * up (ggml arithmetic) fused with the bf16 tile conversion
+__global__ void swiglu_x_tiles_kernel(const float *__restrict__ g, const float *__restrict__ u, int n_tok, int64_t cols,
+                                      __nv_bfloat16 *__restrict__ out, int64_t m_pad) {
+    const int64_t kc_per_row = cols / 8;
+    const int64_t total = m_pad * kc_per_row;
+    const int64_t k_tiles = cols / GM_BK;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / kc_per_row;
+        const int k0 = (int)(i % kc_per_row) * 8;
+        float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (r < n_tok) {
+            const float4 ga = *(const float4 *)(g + r * cols + k0), gb = *(const float4 *)(g + r * cols + k0 + 4);
+            const float4 ua = *(const float4 *)(u + r * cols + k0), ub = *(const float4 *)(u + r * cols + k0 + 4);
+            const float gg[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w}, uu[8] = {ua.x, ua.y, ua.z, ua.w, ub.x, ub.y, ub.z, ub.w};
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = __fmul_rn(__fdiv_rn(gg[j], __fadd_rn(1.0f, expf(-gg[j]))), uu[j]);
+        }
+        const int64_t mt = r / GM_BM, kt = k0 / GM_BK;
+        __nv_bfloat16 *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
+        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
+                                __floats2bfloat162_rn(v[6], v[7])};
+        *(int4 *)dst = *(const int4 *)p4;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ PTX helpers
 __device__ __forceinline__ uint32_t gm_s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void gm_mbar_init(uint64_t *bar, uint32_t count) {
@@ -340,6 +417,25 @@ void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t 
     const int64_t total = m_pad * (K / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
     convert_x_tiles_kernel<<<blocks, 256, 0, s>>>(x, x_stride, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_gemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const float *w, int n_tok, int64_t K, float eps, void *x_tiles,
+                                   float *xn_out, cudaStream_t s) {
+    B2_CHECK(K % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
+    const int m_pad = (int)align_up(n_tok, GM_BM);
+    rmsnorm_x_tiles_kernel<<<m_pad, 256, 0, s>>>(x, x_stride, w, n_tok, K, eps, (__nv_bfloat16 *)x_tiles, xn_out);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_gemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok, int64_t K, void *x_tiles, cudaStream_t s) {
+    B2_CHECK(K % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
+    const int64_t m_pad = align_up(n_tok, GM_BM);
+    const int64_t total = m_pad * (K / 8);
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+    swiglu_x_tiles_kernel<<<blocks, 256, 0, s>>>(gate, up, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }

@@ -392,8 +392,7 @@ void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const 
 void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hd;
     ensure_gemm_scratch(0, gemm_x_tiles_bytes(n, std::max(d, ff)));
-    launch_rmsnorm(x_, d, nullptr, (const float *)L.attn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
-    launch_gemm_prepare_x(xn_, d, n, d, gemm_x_, stream);
+    launch_gemm_prepare_x_rmsnorm(x_, d, (const float *)L.attn_norm.data, n, d, hp.rms_eps, gemm_x_, nullptr, stream);
     gemm(L.wq, n, q_, d, nullptr, 0);
     gemm(L.wk, n, k_, kvd, nullptr, 0);
     gemm(L.wv, n, v_, kvd, nullptr, 0);
@@ -401,12 +400,10 @@ void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     attention(kv, n);
     launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
     gemm(L.wo, n, x_, d, x_, d);
-    launch_rmsnorm(x_, d, nullptr, (const float *)L.ffn_norm.data, xn_, d, n, d, hp.rms_eps, stream);
-    launch_gemm_prepare_x(xn_, d, n, d, gemm_x_, stream);
+    launch_gemm_prepare_x_rmsnorm(x_, d, (const float *)L.ffn_norm.data, n, d, hp.rms_eps, gemm_x_, nullptr, stream);
     gemm(L.gate, n, gate_, ff, nullptr, 0);
     gemm(L.up, n, up_, ff, nullptr, 0);
-    launch_swiglu(gate_, up_, gate_, (int64_t)n * ff, stream);
-    launch_gemm_prepare_x(gate_, ff, n, ff, gemm_x_, stream);
+    launch_gemm_prepare_x_swiglu(gate_, up_, n, ff, gemm_x_, stream);
     gemm(L.down, n, x_, d, x_, d);
 }
 
