@@ -402,19 +402,8 @@ __device__ __forceinline__ float mg_row_sum(float v, int span) {
     return v;
 }
 
-// Merged butterfly reductions: the sums of 4 (2) per-lane values over the whole warp in 6 (5) shuffles instead of
-// 20 (10).  Result: the lane with (lane & 7) == 0 holds row 2*bit3 + bit4 (lanes 0/16/8/24 = rows 0/1/2/3);
-// mg_reduce2: lanes 0/16 = rows 0/1.
-__device__ __forceinline__ float mg_reduce4(const float (&v)[4], int lane) {
-    const bool b4 = lane & 16, b3 = lane & 8;
-    const float a01 = (b4 ? v[1] : v[0]) + __shfl_xor_sync(0xffffffffu, b4 ? v[0] : v[1], 16);
-    const float a23 = (b4 ? v[3] : v[2]) + __shfl_xor_sync(0xffffffffu, b4 ? v[2] : v[3], 16);
-    float b = (b3 ? a23 : a01) + __shfl_xor_sync(0xffffffffu, b3 ? a01 : a23, 8);
-    b += __shfl_xor_sync(0xffffffffu, b, 4);
-    b += __shfl_xor_sync(0xffffffffu, b, 2);
-    b += __shfl_xor_sync(0xffffffffu, b, 1);
-    return b;
-}
+// Merged butterfly reduction: the sums of 2 per-lane values over the whole warp in 5 shuffles instead of 10.
+// Result: lanes 0 / 16 hold rows 0 / 1.
 __device__ __forceinline__ float mg_reduce2(float v0, float v1, int lane) {
     const bool b4 = lane & 16;
     float t = (b4 ? v1 : v0) + __shfl_xor_sync(0xffffffffu, b4 ? v0 : v1, 16);
