@@ -87,6 +87,9 @@ func (l *LLM) request(opts *pb.PredictOptions, stream bool, embedding bool) (C.i
 	r.top_k, r.top_p = C.int32_t(opts.TopK), C.float(opts.TopP)
 	r.repeat_penalty, r.repeat_last_n = C.float(opts.Penalty), C.int32_t(opts.Repeat)
 	r.frequency_penalty, r.presence_penalty = C.float(opts.FrequencyPenalty), C.float(opts.PresencePenalty)
+	// LocalAI's default config sends mirostat 2, tau 5, eta 0.1 (core/config/backend_config.go:286-289)
+	r.mirostat, r.mirostat_tau, r.mirostat_eta = C.int32_t(opts.Mirostat), C.float(opts.MirostatTAU), C.float(opts.MirostatETA)
+	r.typical_p, r.tfs_z = C.float(opts.TypicalP), C.float(opts.TailFreeSamplingZ)
 	r.seed = C.int32_t(opts.Seed)
 	if opts.IgnoreEOS {
 		r.ignore_eos = 1

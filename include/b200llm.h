@@ -124,7 +124,13 @@ typedef struct {
     const size_t *stop_len;    /* optional lengths; NULL => NUL-terminated */
     int32_t n_stop;
     int32_t stream;            /* 1: an event per emitted piece; 0: one final event with the whole text */
-    int32_t reserved[8];
+    int32_t mirostat;          /* Mirostat: 0 off, 2 = v2 (what LocalAI's default config sends, core/config/backend_config.go:286-289);
+                                  1 (v1) is refused with B2_EUNSUPPORTED */
+    float mirostat_tau;        /* MirostatTAU (<= 0 => 5.0) */
+    float mirostat_eta;        /* MirostatETA (<= 0 => 0.1) */
+    float typical_p;           /* TypicalP: 0 or >= 1 = off; other values are refused with B2_EUNSUPPORTED */
+    float tfs_z;               /* TailFreeSamplingZ: as typical_p */
+    int32_t reserved[3];
 } b2_request;
 
 enum {
@@ -186,6 +192,24 @@ int b2_decode_greedy(b2_engine *e, int slot, const int32_t *prompt, int n_prompt
                      double *prefill_ms, double *decode_ms);
 /* hidden state of the last evaluated token after each layer: host [n_layer+1][n_embd] (parity bisecting) */
 int b2_debug_hidden(b2_engine *e, float *out, int cap_floats);
+
+/* The sampler alone (gpt_sampler_sample, grpc-server.cpp:1946) on host logits: `n_draws` successive draws from the same
+ * row, the random state and the mirostat mu carried from draw to draw; penalties are applied to a fresh copy of the
+ * row for every draw.  out_mu (optional): mu after each draw.  Test hook. */
+typedef struct {
+    uint32_t struct_size;
+    float temperature;
+    int32_t top_k;
+    float top_p, min_p;
+    float repeat_penalty, frequency_penalty, presence_penalty;
+    int32_t mirostat;
+    float mirostat_tau, mirostat_eta, mirostat_mu;
+    int32_t ban_token, nl_token;
+    int64_t seed;
+    const int32_t *prev; /* penalty window (the last n_prev tokens) */
+    int32_t n_prev;
+} b2_sample_params;
+int b2_sample(int device, const float *logits, int n_vocab, const b2_sample_params *p, int n_draws, int32_t *out_tokens, float *out_mu);
 
 /* Device-resident benchmark legs (inputs already in HBM, timed with CUDA events on the engine's stream).
  * b2_bench_decode: `n_steps` single-token decode steps for `batch` concurrent sequences whose KV already

@@ -24,7 +24,7 @@ EXPORTS = [
     "b2_abi_version", "b2_last_error", "b2_device_count", "b2_create", "b2_destroy", "b2_model_info", "b2_tokenize",
     "b2_token_to_piece", "b2_submit", "b2_poll", "b2_cancel", "b2_embed_result", "b2_release", "b2_metrics", "b2_eval",
     "b2_decode_greedy", "b2_debug_hidden", "b2_bench_decode", "b2_bench_prefill", "b2_bench_gemv", "b2_dequantize", "b2_quantize_act",
-    "b2_mul_mat", "b2_mul_mat_noalloc",
+    "b2_mul_mat", "b2_mul_mat_noalloc", "b2_sample",
 ]
 
 
@@ -60,7 +60,19 @@ class Request(C.Structure):
         ("repeat_penalty", C.c_float), ("repeat_last_n", C.c_int32), ("frequency_penalty", C.c_float),
         ("presence_penalty", C.c_float), ("seed", C.c_int32), ("ignore_eos", C.c_int32), ("cache_prompt", C.c_int32),
         ("n_keep", C.c_int32), ("embedding_mode", C.c_int32), ("stop", C.POINTER(C.c_char_p)),
-        ("stop_len", C.POINTER(C.c_size_t)), ("n_stop", C.c_int32), ("stream", C.c_int32), ("reserved", C.c_int32 * 8),
+        ("stop_len", C.POINTER(C.c_size_t)), ("n_stop", C.c_int32), ("stream", C.c_int32),
+        ("mirostat", C.c_int32), ("mirostat_tau", C.c_float), ("mirostat_eta", C.c_float), ("typical_p", C.c_float),
+        ("tfs_z", C.c_float), ("reserved", C.c_int32 * 3),
+    ]
+
+
+class SampleParams(C.Structure):
+    _fields_ = [
+        ("struct_size", C.c_uint32), ("temperature", C.c_float), ("top_k", C.c_int32), ("top_p", C.c_float), ("min_p", C.c_float),
+        ("repeat_penalty", C.c_float), ("frequency_penalty", C.c_float), ("presence_penalty", C.c_float),
+        ("mirostat", C.c_int32), ("mirostat_tau", C.c_float), ("mirostat_eta", C.c_float), ("mirostat_mu", C.c_float),
+        ("ban_token", C.c_int32), ("nl_token", C.c_int32), ("seed", C.c_int64), ("prev", C.POINTER(C.c_int32)),
+        ("n_prev", C.c_int32),
     ]
 
 
@@ -119,6 +131,7 @@ def lib() -> C.CDLL:
     L.b2_quantize_act.argtypes = [i32, vp, i64, vp, C.c_size_t]
     L.b2_mul_mat.argtypes = [i32, vp, i64, i64, vp, i32, vp, i32]
     L.b2_mul_mat_noalloc.argtypes = [i32, vp, i64, i64, vp, i32, vp, vp]
+    L.b2_sample.argtypes = [i32, vp, i32, C.POINTER(SampleParams), i32, vp, vp]
     _lib = L
     return L
 
@@ -158,6 +171,29 @@ def mul_mat(wtype: int, w_raw: np.ndarray, rows: int, cols: int, x: np.ndarray, 
     out = np.empty((x.shape[0], rows), dtype=np.float32)
     _check(lib().b2_mul_mat(wtype, _ptr(w_raw), rows, cols, _ptr(x), x.shape[0], _ptr(out), path))
     return out
+
+
+def sample(logits: np.ndarray, n_draws: int = 1, temperature: float = 0.0, top_k: int = 0, top_p: float = 1.0, min_p: float = 0.0,
+           repeat_penalty: float = 1.0, frequency_penalty: float = 0.0, presence_penalty: float = 0.0, prev: Sequence[int] = (),
+           mirostat: int = 0, mirostat_tau: float = 5.0, mirostat_eta: float = 0.1, mirostat_mu: Optional[float] = None,
+           ban_token: int = -1, nl_token: int = -1, seed: int = 0, device: int = 0):
+    """b2_sample: the device sampler alone on one row of host logits -> (tokens[n_draws], mu_after_each_draw[n_draws])."""
+    lg = np.ascontiguousarray(logits, dtype=np.float32).reshape(-1)
+    pv = np.ascontiguousarray(prev, dtype=np.int32)
+    p = SampleParams()
+    p.struct_size = C.sizeof(SampleParams)
+    p.temperature, p.top_k, p.top_p, p.min_p = temperature, top_k, top_p, min_p
+    p.repeat_penalty, p.frequency_penalty, p.presence_penalty = repeat_penalty, frequency_penalty, presence_penalty
+    p.mirostat, p.mirostat_tau, p.mirostat_eta = mirostat, mirostat_tau, mirostat_eta
+    p.mirostat_mu = 2.0 * mirostat_tau if mirostat_mu is None else mirostat_mu
+    p.ban_token, p.nl_token, p.seed = ban_token, nl_token, seed
+    p.prev = pv.ctypes.data_as(C.POINTER(C.c_int32))
+    p.n_prev = pv.size
+    toks = np.empty(n_draws, dtype=np.int32)
+    mus = np.empty(n_draws, dtype=np.float32)
+    _check(lib().b2_sample(device, lg.ctypes.data_as(C.POINTER(C.c_float)), lg.size, C.byref(p), n_draws,
+                           toks.ctypes.data_as(C.POINTER(C.c_int32)), mus.ctypes.data_as(C.POINTER(C.c_float))))
+    return toks, mus
 
 
 def mul_mat_noalloc(wtype: int, w_dev: int, rows: int, cols: int, x_dev: int, n_tok: int, out_dev: int, stream: int = 0):
@@ -263,7 +299,9 @@ class Engine:
     def submit(self, prompt: str | bytes | None = None, prompt_ids: Optional[Sequence[int]] = None, n_predict: int = 0,
                temperature: float = 0.0, top_k: int = 40, top_p: float = 0.95, min_p: float = 0.0, seed: int = -1,
                ignore_eos: bool = False, cache_prompt: bool = False, n_keep: int = 0, embedding_mode: bool = False,
-               stop: Sequence[str | bytes] = (), stream: bool = True) -> int:
+               stop: Sequence[str | bytes] = (), stream: bool = True, repeat_penalty: float = 1.0, repeat_last_n: int = 64,
+               frequency_penalty: float = 0.0, presence_penalty: float = 0.0, mirostat: int = 0, mirostat_tau: float = 5.0,
+               mirostat_eta: float = 0.1, typical_p: float = 1.0, tfs_z: float = 1.0) -> int:
         r = Request()
         r.struct_size = C.sizeof(Request)
         keep = []
@@ -277,7 +315,9 @@ class Engine:
             r.n_prompt_ids = ids.size
             keep.append(ids)
         r.n_predict, r.temperature, r.top_k, r.top_p, r.min_p, r.seed = n_predict, temperature, top_k, top_p, min_p, seed
-        r.repeat_penalty = 1.0
+        r.repeat_penalty, r.repeat_last_n = repeat_penalty, repeat_last_n
+        r.frequency_penalty, r.presence_penalty = frequency_penalty, presence_penalty
+        r.mirostat, r.mirostat_tau, r.mirostat_eta, r.typical_p, r.tfs_z = mirostat, mirostat_tau, mirostat_eta, typical_p, tfs_z
         r.ignore_eos, r.cache_prompt, r.n_keep = int(ignore_eos), int(cache_prompt), n_keep
         r.embedding_mode, r.stream = int(embedding_mode), int(stream)
         if stop:

@@ -8,6 +8,7 @@
 
 #include "engine.h"
 #include "kernels.h"
+#include "sampling.h"
 #include "model.h"
 
 namespace b2 {
@@ -324,6 +325,37 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
         launch_gemv(W, xq, f, n_tok, dout.as<float>(), rows, nullptr, 0, 0);
     }
     B2_CUDA(cudaMemcpy(out, dout.p, (size_t)n_tok * rows * 4, cudaMemcpyDeviceToHost));
+    return 0;
+    B2_API_END(0)
+}
+
+int b2_sample(int device, const float *logits, int n_vocab, const b2_sample_params *p, int n_draws, int32_t *out_tokens, float *out_mu) {
+    B2_API_BEGIN
+    B2_CHECK(logits && p && out_tokens && n_vocab > 0 && n_draws > 0, B2_EINVAL, "b2_sample: bad arguments");
+    B2_CHECK(p->struct_size == sizeof(b2_sample_params), B2_EINVAL, "b2_sample: struct_size mismatch");
+    B2_CHECK(device >= 0 && sm100_device_count() > device, B2_ENODEV, "b2_sample: no such sm_100 device");
+    B2_CUDA(cudaSetDevice(device));
+    DevBuf src((size_t)n_vocab * 4), row((size_t)n_vocab * 4), spec(sizeof(SampleSpec)), tok(4), mu(4);
+    B2_CUDA(cudaMemcpy(src.p, logits, (size_t)n_vocab * 4, cudaMemcpyHostToDevice));
+    SampleSpec sp;
+    sp.temperature = p->temperature; sp.top_k = p->top_k; sp.top_p = p->top_p > 0 ? p->top_p : 1.f; sp.min_p = p->min_p;
+    sp.ban_token = p->ban_token; sp.nl_token = p->nl_token;
+    sp.repeat_penalty = p->repeat_penalty > 0 ? p->repeat_penalty : 1.f;
+    sp.frequency_penalty = p->frequency_penalty; sp.presence_penalty = p->presence_penalty;
+    sp.n_prev = std::min(std::max(p->n_prev, 0), SAMPLE_MAX_PREV);
+    for (int k = 0; k < sp.n_prev; k++) sp.prev[k] = p->prev[p->n_prev - sp.n_prev + k];
+    sp.mirostat = p->mirostat; sp.mirostat_tau = p->mirostat_tau; sp.mirostat_eta = p->mirostat_eta; sp.mirostat_mu = p->mirostat_mu;
+    uint64_t rng = (uint64_t)p->seed;
+    for (int i = 0; i < n_draws; i++) {
+        sp.rng = rng;
+        rng = rng * 6364136223846793005ULL + 1442695040888963407ULL; // the scheduler's per-token advance
+        B2_CUDA(cudaMemcpy(row.p, src.p, (size_t)n_vocab * 4, cudaMemcpyDeviceToDevice));
+        B2_CUDA(cudaMemcpy(spec.p, &sp, sizeof(sp), cudaMemcpyHostToDevice));
+        launch_sample(row.as<float>(), n_vocab, 1, n_vocab, spec.as<SampleSpec>(), sp.has_penalties(), tok.as<int32_t>(), mu.as<float>(), 0);
+        B2_CUDA(cudaMemcpy(&out_tokens[i], tok.p, 4, cudaMemcpyDeviceToHost));
+        B2_CUDA(cudaMemcpy(&sp.mirostat_mu, mu.p, 4, cudaMemcpyDeviceToHost));
+        if (out_mu) out_mu[i] = sp.mirostat_mu;
+    }
     return 0;
     B2_API_END(0)
 }

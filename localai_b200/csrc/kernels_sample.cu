@@ -1,6 +1,7 @@
-// kernels_sample.cu -- on-device sampling: greedy, temperature, top-k, top-p, min-p.
-// Chain order follows llama.cpp's default sampler chain (top_k -> top_p -> min_p -> temperature -> softmax ->
-// draw); one CTA per logits row; the vocabulary row (<= 513 KB) is read from L2 a handful of times.
+// kernels_sample.cu -- on-device sampling: penalties, then greedy | top-k, top-p, min-p, temperature, draw | mirostat v2.
+// Chain order follows llama.cpp's sampler chain as gpt_sampler_init builds it (penalties -> temp <= 0 ? greedy :
+// mirostat == 2 ? temperature -> mirostat_v2 : top_k -> top_p -> min_p -> temperature -> softmax -> draw); one CTA
+// per logits row; the vocabulary row (<= 513 KB) is read from L2 a handful of times.
 #include "kernels.h"
 #include "model.h"
 #include "quant.cuh"
@@ -26,19 +27,45 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
     return x ^ (x >> 31);
 }
 
+// llama_sampler_penalties_apply (llama.cpp src/llama-sampling.cpp @ d5cb868, un-vendored): for every distinct token
+// of the window with count c: logit <= 0 ? logit * repeat : logit / repeat, then logit -= c * freq + presence.
+// In place on the logits row; one thread per window entry, the first occurrence of a token does the update.
+__global__ void __launch_bounds__(SAMPLE_MAX_PREV)
+penalty_kernel(float *__restrict__ logits, int64_t stride, int n_vocab, const SampleSpec *__restrict__ specs) {
+    const SampleSpec &sp = specs[blockIdx.x];
+    if (!(sp.n_prev > 0 && (sp.repeat_penalty != 1.f || sp.frequency_penalty != 0.f || sp.presence_penalty != 0.f))) return;
+    const int n = min(sp.n_prev, SAMPLE_MAX_PREV), j = threadIdx.x;
+    if (j >= n) return;
+    const int tok = sp.prev[j];
+    if (tok < 0 || tok >= n_vocab || tok == sp.nl_token) return;
+    int count = 0;
+    for (int k = 0; k < n; k++) {
+        if (sp.prev[k] == tok) {
+            if (k < j) return; // not the first occurrence
+            count++;
+        }
+    }
+    float *x = logits + (int64_t)blockIdx.x * stride + tok;
+    float v = *x;
+    v = v <= 0.f ? v * sp.repeat_penalty : v / sp.repeat_penalty;
+    v -= (float)count * sp.frequency_penalty + sp.presence_penalty;
+    *x = v;
+}
+
 __global__ void __launch_bounds__(SAMPLE_THREADS)
 sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, const SampleSpec *__restrict__ specs,
-              int32_t *__restrict__ out) {
+              int32_t *__restrict__ out, float *__restrict__ mu_out) {
     __shared__ uint32_t hist[256];
     __shared__ uint32_t s_prefix, s_remaining, s_count;
     __shared__ unsigned long long cand[CAND_CAP]; // (key << 32) | (~idx): sorting descending gives key desc, idx asc
     __shared__ float s_red[32];
     __shared__ int s_redi[32];
     __shared__ float s_scan[SAMPLE_THREADS];
-    const SampleSpec sp = specs[blockIdx.x];
+    const SampleSpec &sp = specs[blockIdx.x];
     const float *x = logits + (int64_t)blockIdx.x * stride;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     auto key_at = [&](int i) -> uint32_t { return i == sp.ban_token ? 0u : float_key(x[i]); };
+    if (mu_out && tid == 0) mu_out[blockIdx.x] = sp.mirostat_mu;
 
     // ---------------- greedy: first maximal element
     if (sp.temperature <= 0.f) {
@@ -74,6 +101,73 @@ sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, con
     const float inv_t = 1.0f / sp.temperature;
     int K = sp.top_k <= 0 ? n_vocab : min(sp.top_k, n_vocab);
     const bool full = (K == n_vocab) && sp.top_p >= 1.0f && sp.min_p <= 0.0f;
+
+    // ---------------- mirostat v2 (llama_sampler_mirostat_v2_apply): soft-max of the temperature-scaled logits, drop
+    // every token whose surprise -log2(p) exceeds mu (the most probable one always stays), renormalise, draw,
+    // mu -= eta * (surprise of the drawn token - tau)
+    if (sp.mirostat == 2) {
+        float mx = -INFINITY;
+        for (int i = tid; i < n_vocab; i += SAMPLE_THREADS)
+            if (i != sp.ban_token) mx = fmaxf(mx, x[i]);
+        mx = warp_max(mx);
+        if (lane == 0) s_red[warp] = mx;
+        __syncthreads();
+        mx = s_red[0];
+        for (int i = 1; i < SAMPLE_THREADS / 32; i++) mx = fmaxf(mx, s_red[i]);
+        __syncthreads();
+        const int per = (n_vocab + SAMPLE_THREADS - 1) / SAMPLE_THREADS;
+        const int i0 = tid * per, i1 = min(n_vocab, i0 + per);
+        float part = 0.f;
+        for (int i = i0; i < i1; i++)
+            if (i != sp.ban_token) part += expf((x[i] - mx) * inv_t);
+        s_scan[tid] = part;
+        __syncthreads();
+        float tot = 0.f;
+        for (int i = 0; i < SAMPLE_THREADS; i++) tot += s_scan[i]; // every thread: same order, same value
+        __syncthreads();
+        // keep token i iff -log2(e_i / tot) <= mu  <=>  (x_i - mx) / T >= ln(tot) - mu ln 2; e_max = 1 always stays
+        const float thr = fminf(logf(tot) - sp.mirostat_mu * 0.69314718056f, 0.f);
+        part = 0.f;
+        for (int i = i0; i < i1; i++) {
+            const float z = (x[i] - mx) * inv_t;
+            if (i != sp.ban_token && z >= thr) part += expf(z);
+        }
+        s_scan[tid] = part;
+        __syncthreads();
+        if (tid == 0) {
+            float tot2 = 0.f;
+            for (int i = 0; i < SAMPLE_THREADS; i++) tot2 += s_scan[i];
+            const float target = u01 * tot2;
+            float acc = 0.f;
+            int t = 0;
+            for (; t < SAMPLE_THREADS - 1; t++) {
+                if (acc + s_scan[t] > target) break;
+                acc += s_scan[t];
+            }
+            int pick = -1;
+            float e_pick = 1.f;
+            const int j0 = t * per, j1 = min(n_vocab, j0 + per);
+            for (int i = j0; i < j1; i++) {
+                const float z = (x[i] - mx) * inv_t;
+                if (i == sp.ban_token || z < thr) continue;
+                const float e = expf(z);
+                acc += e;
+                pick = i;
+                e_pick = e;
+                if (acc > target) break;
+            }
+            if (pick < 0) { // rounding left the target past the last kept token of this chunk: take the global maximum
+                for (int i = 0; i < n_vocab; i++)
+                    if (i != sp.ban_token && x[i] == mx) { pick = i; break; }
+                if (pick < 0) pick = 0;
+                e_pick = 1.f;
+            }
+            out[blockIdx.x] = pick;
+            const float surprise = -log2f(e_pick / tot2);
+            if (mu_out) mu_out[blockIdx.x] = sp.mirostat_mu - sp.mirostat_eta * (surprise - sp.mirostat_tau);
+        }
+        return;
+    }
 
     // ---------------- no truncation at all: inverse-CDF over the whole vocabulary, no sort needed
     if (full) {
@@ -210,21 +304,30 @@ sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, con
     }
 }
 
-void launch_sample(const float *logits, int64_t stride, int n_rows, int n_vocab, const SampleSpec *specs_dev, int32_t *out,
-                   cudaStream_t s) {
+void launch_sample(float *logits, int64_t stride, int n_rows, int n_vocab, const SampleSpec *specs_dev, bool any_penalties,
+                   int32_t *out, float *mu_out, cudaStream_t s) {
     if (n_rows <= 0) return;
-    sample_kernel<<<n_rows, SAMPLE_THREADS, 0, s>>>(logits, stride, n_vocab, specs_dev, out);
+    if (any_penalties) {
+        penalty_kernel<<<n_rows, SAMPLE_MAX_PREV, 0, s>>>(logits, stride, n_vocab, specs_dev);
+        g_launch_count++;
+        B2_CUDA(cudaGetLastError());
+    }
+    sample_kernel<<<n_rows, SAMPLE_THREADS, 0, s>>>(logits, stride, n_vocab, specs_dev, out, mu_out);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
 
-void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_host) {
+void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_host, float *mu_out_host) {
     const int n = (int)specs.size();
     if (n == 0) return;
+    bool any_pen = false;
+    for (const auto &sp : specs) any_pen |= sp.has_penalties();
     SampleSpec *dev = m.sample_specs_dev(n);
     B2_CUDA(cudaMemcpyAsync(dev, specs.data(), sizeof(SampleSpec) * n, cudaMemcpyHostToDevice, m.stream));
-    launch_sample(m.logits_dev(), m.hp.n_vocab, n, m.hp.n_vocab, dev, const_cast<int32_t *>(m.next_tok_dev()), m.stream);
+    launch_sample(m.logits_dev_mut(), m.hp.n_vocab, n, m.hp.n_vocab, dev, any_pen, const_cast<int32_t *>(m.next_tok_dev()),
+                  m.sample_mu_dev(), m.stream);
     B2_CUDA(cudaMemcpyAsync(out_host, m.next_tok_dev(), sizeof(int32_t) * n, cudaMemcpyDeviceToHost, m.stream));
+    if (mu_out_host) B2_CUDA(cudaMemcpyAsync(mu_out_host, m.sample_mu_dev(), sizeof(float) * n, cudaMemcpyDeviceToHost, m.stream));
 }
 
 } // namespace b2

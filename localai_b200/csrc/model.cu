@@ -189,6 +189,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     next_tok_ = (int32_t *)dalloc(nb * 4);
     xn_out_ = (float *)dalloc(nb * d * 4);
     sample_specs_ = (SampleSpec *)dalloc(nb * sizeof(SampleSpec));
+    sample_mu_ = (float *)dalloc(nb * sizeof(float));
     ensure_logits_rows(std::max(n_parallel, 1));
     build_mega();
     decode_graphs_.assign((size_t)std::min(n_parallel, 64) + 1, nullptr);

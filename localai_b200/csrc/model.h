@@ -55,6 +55,8 @@ class Model {
     void sync() { B2_CUDA(cudaStreamSynchronize(stream)); }
 
     const float *logits_dev() const { return logits_; }
+    float *logits_dev_mut() { return logits_; } // the sampler applies penalties in place
+    float *sample_mu_dev() { return sample_mu_; }
     const float *embd_dev() const { return xn_out_; }
     const int32_t *next_tok_dev() const { return next_tok_; }
     float *debug_hidden_dev() { return dbg_hidden_; }
@@ -137,6 +139,7 @@ class Model {
     int32_t *tok_ = nullptr, *pos_ = nullptr, *slot_ = nullptr, *out_rows_ = nullptr, *next_tok_ = nullptr;
     int logits_rows_cap_ = 0;
     SampleSpec *sample_specs_ = nullptr;
+    float *sample_mu_ = nullptr;
     void ensure_logits_rows(int n);
     void invalidate_acts();
 };

@@ -62,6 +62,12 @@ int64_t Scheduler::submit(const b2_request &r) {
     q->presence_penalty = r.presence_penalty;
     q->seed = r.seed;
     q->n_keep = r.n_keep;
+    B2_CHECK(r.mirostat == 0 || r.mirostat == 2, B2_EUNSUPPORTED, "mirostat v1 is not implemented (0 = off, 2 = v2)");
+    B2_CHECK(!(r.typical_p > 0.f && r.typical_p < 1.f) && !(r.tfs_z > 0.f && r.tfs_z < 1.f), B2_EUNSUPPORTED,
+             "typical_p / tfs_z sampling is not implemented (leave them at 0 or 1)");
+    q->mirostat = r.mirostat;
+    q->mirostat_tau = r.mirostat_tau > 0.f ? r.mirostat_tau : 5.f;
+    q->mirostat_eta = r.mirostat_eta > 0.f ? r.mirostat_eta : 0.1f;
     q->ignore_eos = r.ignore_eos != 0;
     q->cache_prompt = r.cache_prompt != 0;
     q->embedding_mode = r.embedding_mode != 0;
@@ -209,6 +215,7 @@ void Scheduler::launch_slot(Slot &s, std::shared_ptr<Request> r) {
     s.stopped_eos = s.stopped_word = s.stopped_limit = s.truncated = false;
     s.t_start_prompt = clk::now();
     s.t_prompt_ms = s.t_gen_ms = 0;
+    s.mirostat_mu = 2.f * r->mirostat_tau; // llama_sampler_init_mirostat_v2: mu = 2 * tau
     s.rng_state = r->seed < 0 ? (uint64_t)std::chrono::high_resolution_clock::now().time_since_epoch().count() : (uint64_t)(uint32_t)r->seed;
     // tokenize (BOS iff the vocabulary asks for it; special tokens parsed: grpc-server.cpp:564,1689)
     std::vector<int32_t> toks;
@@ -439,6 +446,23 @@ bool Scheduler::step() {
                 sp.ban_token = s.req->ignore_eos ? eng_->tokenizer()->eos_id() : -1;
                 sp.rng = s.rng_state;
                 s.rng_state = s.rng_state * 6364136223846793005ULL + 1442695040888963407ULL;
+                // penalties over the last repeat_last_n tokens of prompt + generation (gpt_sampler_accept is fed both,
+                // grpc-server.cpp:1737,1948); -1 = the whole context, clamped to the window the kernel keeps
+                sp.repeat_penalty = s.req->repeat_penalty;
+                sp.frequency_penalty = s.req->frequency_penalty;
+                sp.presence_penalty = s.req->presence_penalty;
+                sp.nl_token = eng_->tokenizer()->nl_id();
+                {
+                    const int hist = (int)s.cache_tokens.size();
+                    int last_n = s.req->repeat_last_n < 0 ? hist : s.req->repeat_last_n;
+                    last_n = std::min(std::min(last_n, hist), SAMPLE_MAX_PREV);
+                    sp.n_prev = last_n;
+                    for (int k = 0; k < last_n; k++) sp.prev[k] = s.cache_tokens[hist - last_n + k];
+                }
+                sp.mirostat = s.req->mirostat;
+                sp.mirostat_tau = s.req->mirostat_tau;
+                sp.mirostat_eta = s.req->mirostat_eta;
+                sp.mirostat_mu = s.mirostat_mu;
                 specs.push_back(sp);
             }
         }
@@ -460,7 +484,8 @@ bool Scheduler::step() {
             embd.resize((size_t)n_out * m.hp.n_embd);
             B2_CUDA(cudaMemcpyAsync(embd.data(), m.embd_dev(), embd.size() * 4, cudaMemcpyDeviceToHost, m.stream));
         }
-        sample_rows(m, specs, sampled.data());
+        std::vector<float> mu_new(specs.size());
+        sample_rows(m, specs, sampled.data(), mu_new.data());
         m.sync();
         {
             std::lock_guard<std::mutex> lk(metrics_mu_);
@@ -493,6 +518,7 @@ bool Scheduler::step() {
                 continue;
             }
             const int32_t id = sampled[k];
+            s.mirostat_mu = mu_new[k];
             if (s.state == PROMPT) s.state = GENERATING;
             s.n_decoded += 1;
             if (s.n_decoded == 1) {

@@ -37,6 +37,8 @@ struct Request {
     int n_predict = -1;
     float temperature = 0.f, top_p = 1.f, min_p = 0.f, repeat_penalty = 1.f, frequency_penalty = 0.f, presence_penalty = 0.f;
     int top_k = 0, repeat_last_n = 0, seed = -1, n_keep = 0;
+    int mirostat = 0;
+    float mirostat_tau = 5.f, mirostat_eta = 0.1f;
     bool ignore_eos = false, cache_prompt = false, embedding_mode = false, stream = true;
     std::vector<std::string> stop;
     // results
@@ -77,6 +79,7 @@ class Scheduler {
         std::chrono::steady_clock::time_point t_last_used, t_start_prompt, t_start_gen;
         double t_prompt_ms = 0, t_gen_ms = 0;
         uint64_t rng_state = 0;
+        float mirostat_mu = 10.f; // mirostat state of the request in the slot (2 * tau at launch)
     };
 
     void loop();

@@ -203,6 +203,8 @@ Tokenizer::Tokenizer(const GGUFFile &f) {
         auto it = token_to_id_.find("<|eot_id|>");
         if (it != token_to_id_.end()) eot_ = it->second;
     }
+    nl_ = byte_to_token((uint8_t)'\n');
+    if (nl_ == unk_) nl_ = -1;
     add_bos_ = f.get_b("tokenizer.ggml.add_bos_token", add_bos_);
     add_eos_ = f.get_b("tokenizer.ggml.add_eos_token", false);
     add_space_prefix_ = f.get_b("tokenizer.ggml.add_space_prefix", true);

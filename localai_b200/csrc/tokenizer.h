@@ -29,6 +29,7 @@ class Tokenizer {
     int32_t bos_id() const { return bos_; }
     int32_t eos_id() const { return eos_; }
     int32_t eot_id() const { return eot_; }
+    int32_t nl_id() const { return nl_; } // llama_token_nl: the byte / byte-level token of '\n'
     bool add_bos() const { return add_bos_; }
     bool is_eog(int32_t id) const { return id >= 0 && (id == eos_ || id == eot_); }
     const std::string &model_name() const { return model_; }
@@ -48,7 +49,7 @@ class Tokenizer {
     std::unordered_map<std::string, int32_t> token_to_id_;
     std::unordered_map<std::string, int> bpe_ranks_; // "left right" -> rank
     std::vector<int32_t> special_;                   // ids matched verbatim in text, longest first
-    int32_t bos_ = -1, eos_ = -1, eot_ = -1, unk_ = -1;
+    int32_t bos_ = -1, eos_ = -1, eot_ = -1, unk_ = -1, nl_ = -1;
     bool add_bos_ = true, add_eos_ = false, add_space_prefix_ = true, ignore_merges_ = false;
 };
 

@@ -196,3 +196,38 @@ class OracleModel:
 
 def num_threads() -> int:
     return lib().ref_num_threads()
+
+
+# ---------------------------------------------------------------------------------------------- sampler chain
+# Restatement of the two llama.cpp samplers the engine runs on the device beyond top-k/top-p/min-p (llama.cpp
+# src/llama-sampling.cpp @ d5cb868, un-vendored: llama_sampler_penalties_apply, llama_sampler_mirostat_v2_apply;
+# called through gpt_sampler_sample at backend/cpp/llama/grpc-server.cpp:1946).  Test infrastructure only.
+def penalties_ref(logits, prev, repeat_penalty=1.0, frequency_penalty=0.0, presence_penalty=0.0, nl_token=-1):
+    """logits after the repeat / frequency / presence penalties over the window `prev` (penalize_nl = false)."""
+    x = np.array(logits, dtype=np.float32, copy=True)
+    counts = {}
+    for t in prev:
+        counts[int(t)] = counts.get(int(t), 0) + 1
+    rp, fp, pp = np.float32(repeat_penalty), np.float32(frequency_penalty), np.float32(presence_penalty)
+    for t, c in counts.items():
+        if t < 0 or t >= x.size or t == nl_token:
+            continue
+        v = x[t]
+        v = v * rp if v <= 0 else v / rp
+        x[t] = np.float32(v - (np.float32(c) * fp + pp))
+    return x
+
+
+def mirostat_v2_ref(logits, temperature, mu, tau, eta, token):
+    """One mirostat-v2 step given WHICH token was drawn: returns (kept mask, p of `token` after truncation and
+    renormalisation, mu after the update).  The draw itself depends on the random stream and is not restated."""
+    z = (np.asarray(logits, dtype=np.float64) - np.max(logits)) / temperature
+    p = np.exp(z)
+    p /= p.sum()
+    surprise = -np.log2(p)
+    kept = surprise <= mu
+    kept[int(np.argmax(p))] = True  # the most probable token always stays
+    p2 = np.where(kept, p, 0.0)
+    p2 /= p2.sum()
+    obs = -np.log2(p2[token]) if p2[token] > 0 else np.inf
+    return kept, p2[token], mu - eta * (obs - tau)

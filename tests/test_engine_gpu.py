@@ -192,3 +192,70 @@ def test_sampling_distribution_matches_softmax(model_files):
             counts[match[0]] += 1
         freq = np.array([counts[t] for t in top.tolist()]) / N
         assert np.abs(freq - p).max() < 0.08
+
+
+# ---------------------------------------------------------------------------------------------- sampler chain (§8 f1)
+def _zipf_logits(n_vocab, seed):
+    rng = np.random.default_rng(seed)
+    p = 1.0 / np.arange(1, n_vocab + 1) ** 1.1
+    return np.log(p / p.sum())[rng.permutation(n_vocab)].astype(np.float32)
+
+
+@pytest.mark.gpu
+def test_penalties_match_reference_greedy():
+    """repeat / frequency / presence penalties, then greedy: the token is the argmax of the reference's penalised row"""
+    from oracle import oracle as O
+    rng = np.random.default_rng(5)
+    for trial in range(8):
+        n_vocab = 4000 + 17 * trial
+        x = rng.standard_normal(n_vocab).astype(np.float32) * 2
+        top = np.argsort(-x)[:6]
+        prev = np.concatenate([top[:3], top[:2], top[:1], rng.integers(0, n_vocab, 20)]).astype(np.int32)
+        kw = dict(repeat_penalty=1.3 + 0.1 * trial, frequency_penalty=0.2, presence_penalty=0.1, nl_token=int(top[1]))
+        want = int(np.argmax(O.penalties_ref(x, prev, **kw)))
+        got, _ = capi.sample(x, 1, temperature=0.0, prev=prev, **kw)
+        assert int(got[0]) == want
+        assert want != int(top[0])  # the penalties did change the decision
+
+
+@pytest.mark.gpu
+def test_mirostat_v2_follows_reference_update_and_converges():
+    """every draw comes from the truncated set, mu follows mu -= eta (surprise - tau) exactly, and the average
+    surprise of the drawn tokens settles at tau (what mirostat is for)"""
+    from oracle import oracle as O
+    x = _zipf_logits(32000, 1)
+    tau, eta, temp = 3.0, 0.1, 0.9
+    toks, mus = capi.sample(x, 600, temperature=temp, mirostat=2, mirostat_tau=tau, mirostat_eta=eta, seed=123)
+    mu = 2 * tau
+    surprises = []
+    for t, mu_after in zip(toks, mus):
+        kept, p, mu_ref = O.mirostat_v2_ref(x, temp, mu, tau, eta, int(t))
+        assert kept[int(t)], "token drawn from outside the mirostat-truncated set"
+        assert abs(mu_ref - float(mu_after)) <= 2e-3 * max(1.0, abs(mu_ref))
+        surprises.append(-np.log2(p))
+        mu = float(mu_after)
+    assert abs(np.mean(surprises[100:]) - tau) < 0.5
+    # same seed -> same tokens; another seed -> another sequence
+    toks2, _ = capi.sample(x, 600, temperature=temp, mirostat=2, mirostat_tau=tau, mirostat_eta=eta, seed=123)
+    toks3, _ = capi.sample(x, 600, temperature=temp, mirostat=2, mirostat_tau=tau, mirostat_eta=eta, seed=124)
+    assert toks.tolist() == toks2.tolist() and toks.tolist() != toks3.tolist()
+
+
+@pytest.mark.gpu
+def test_requests_with_localai_default_sampling(eng):
+    """LocalAI's default config (temperature 0.9, top-k 40, top-p 0.95, mirostat 2, repeat penalty) runs through
+    b2_submit; mirostat v1 and typical-p are refused, not silently ignored"""
+    rid = eng.submit(prompt="The quick brown fox", n_predict=24, temperature=0.9, top_k=40, top_p=0.95, seed=7, mirostat=2,
+                     mirostat_tau=5.0, mirostat_eta=0.1, repeat_penalty=1.1, repeat_last_n=64, stream=False)
+    ev = list(eng.events(rid))[-1]
+    eng.release(rid)
+    assert ev["flags"] & capi.EV_FINAL and ev["n_decoded"] == 24 and not (ev["flags"] & capi.EV_ERROR)
+    rid2 = eng.submit(prompt="The quick brown fox", n_predict=24, temperature=0.9, top_k=40, top_p=0.95, seed=7, mirostat=2,
+                      mirostat_tau=5.0, mirostat_eta=0.1, repeat_penalty=1.1, repeat_last_n=64, stream=False)
+    ev2 = list(eng.events(rid2))[-1]
+    eng.release(rid2)
+    assert ev2["text"] == ev["text"]  # seeded: reproducible
+    with pytest.raises(capi.B2Error):
+        eng.submit(prompt="x", n_predict=4, temperature=0.9, mirostat=1)
+    with pytest.raises(capi.B2Error):
+        eng.submit(prompt="x", n_predict=4, temperature=0.9, typical_p=0.5)

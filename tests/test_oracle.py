@@ -131,3 +131,17 @@ def test_greedy_is_argmax_chain(model_files):
         seq.append(int(t))
         lg = m2.eval([int(t)], n_past=len(seq) - 1)[0]
     assert (margins >= 0).all()
+
+
+def test_sampler_reference_functions():
+    """the restated penalties / mirostat-v2 arithmetic on a hand-checked case"""
+    x = np.array([2.0, -1.0, 0.5, 3.0], dtype=np.float32)
+    y = O.penalties_ref(x, [0, 0, 1, 3], repeat_penalty=2.0, frequency_penalty=0.5, presence_penalty=0.25, nl_token=3)
+    assert np.allclose(y, [2.0 / 2 - (2 * 0.5 + 0.25), -1.0 * 2 - (0.5 + 0.25), 0.5, 3.0])
+    kept, p, mu = O.mirostat_v2_ref(np.log(np.array([0.5, 0.25, 0.125, 0.125])), 1.0, mu=1.5, tau=1.0, eta=0.1, token=1)
+    assert kept.tolist() == [True, False, False, False] or kept.tolist() == [True, True, False, False]
+    # surprise of p=0.5 is 1 bit, of 0.25 is 2 bits: with mu = 1.5 only the first survives
+    kept, p, mu = O.mirostat_v2_ref(np.log(np.array([0.5, 0.25, 0.125, 0.125])), 1.0, mu=1.5, tau=1.0, eta=0.1, token=0)
+    assert kept.tolist() == [True, False, False, False] and abs(p - 1.0) < 1e-12 and abs(mu - (1.5 - 0.1 * (0.0 - 1.0))) < 1e-12
+    kept, p, mu = O.mirostat_v2_ref(np.log(np.array([0.5, 0.25, 0.125, 0.125])), 1.0, mu=2.5, tau=1.0, eta=0.1, token=1)
+    assert kept.tolist() == [True, True, False, False] and abs(p - 1 / 3) < 1e-12
