@@ -37,7 +37,7 @@ METRIC = "Llama-3-8B Q4_K_M decode tok/s (b=1)"
 UNIT = "tok/s"
 # dram__bytes_read.sum + dram__bytes_write.sum of one decode_mega_kernel launch (llama3-8b q4_k_m, ctx 128), from the
 # ncu --set full capture summarised in profiles/ (None until a capture of the current kernel is committed)
-MEGA_TRAFFIC_BYTES = 4.7264e9  # profiles/r1_mega_v5_ncu_summary.txt: 4.6717 GB read + 54.7 MB written
+MEGA_TRAFFIC_BYTES = 4.6731e9  # profiles/r1_mega_v6_ncu_summary.txt: 4.6391 GB read + 34.1 MB written
 
 
 def log(*a):
