@@ -1133,23 +1133,28 @@ decode_mega_kernel(const MegaArgs a) {
                     const int xc = (q * ks) >> 4;                               // first 16-byte chunk of this K-split's activations
                     const float *xdq = (const float *)(xs + K) + (q * ks) / 32; // and their block scales
 #pragma unroll 1
-                    for (int row = 0; row < n; row++) {
-                        const uint32_t rp = st + row * rb;
-                        float acc = 0.f;
+                    for (int row = 0; row < n; row += 2) { // 2 rows at a time: independent chains, one merged reduction
+                        const uint32_t rp0 = st + row * rb, rp1 = st + min(row + 1, n - 1) * rb;
+                        float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll 4
-                        for (int j = 0; j < np; j++) { // 16-byte pieces lane + 32 j
+                        for (int j = 0; j < np; j++) { // 16-byte pieces lane + 32 j: half a 32-element block each
                             const int piece = lane + 32 * j;
-                            const int4 wv = mg_lds128(rp + piece * 16), xv = mg_lds128(xs_a + mg_swz(xc + piece) * 16);
-                            const float dw = h2f((uint16_t)mg_lds_u16(rp + ks + (piece >> 1) * 2));
-                            int sdot = __dp4a(wv.x, xv.x, 0);
-                            sdot = __dp4a(wv.y, xv.y, sdot);
-                            sdot = __dp4a(wv.z, xv.z, sdot);
-                            sdot = __dp4a(wv.w, xv.w, sdot);
-                            sdot += __shfl_xor_sync(0xffffffffu, sdot, 1); // whole 32-element block, as on the CPU
-                            if ((lane & 1) == 0) acc += (float)sdot * (dw * xdq[piece >> 1]);
+                            const int4 xv = mg_lds128(xs_a + mg_swz(xc + piece) * 16);
+                            const int4 w0 = mg_lds128(rp0 + piece * 16), w1 = mg_lds128(rp1 + piece * 16);
+                            const float dxj = xdq[piece >> 1];
+                            const float d0 = h2f((uint16_t)mg_lds_u16(rp0 + ks + (piece >> 1) * 2)) * dxj;
+                            const float d1 = h2f((uint16_t)mg_lds_u16(rp1 + ks + (piece >> 1) * 2)) * dxj;
+                            int s0 = __dp4a(w0.x, xv.x, 0), s1 = __dp4a(w1.x, xv.x, 0);
+                            s0 = __dp4a(w0.y, xv.y, s0); s1 = __dp4a(w1.y, xv.y, s1);
+                            s0 = __dp4a(w0.z, xv.z, s0); s1 = __dp4a(w1.z, xv.z, s1);
+                            s0 = __dp4a(w0.w, xv.w, s0); s1 = __dp4a(w1.w, xv.w, s1);
+                            // the two halves of a block are scaled separately ((a + b) d = a d + b d up to one rounding)
+                            acc0 += (float)s0 * d0;
+                            acc1 += (float)s1 * d1;
                         }
-                        acc = mg_row_sum(acc, 32);
-                        if (lane == 0) pout[(size_t)row * S] = acc;
+                        const float tot = mg_reduce2(acc0, acc1, lane);
+                        const int kk = row + ((lane >> 4) & 1);
+                        if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
                     }
                 }
                 long long ta0 = 0, ta2 = 0;
