@@ -157,6 +157,16 @@ void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s);
 // idle SMs; the slices' partial tiles go through this buffer and are summed in slice order
 void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
                     int64_t res_stride, void *w_tiles, bool w_tiles_ready, float *splitk_scratch, size_t splitk_bytes, cudaStream_t s);
+// up to three matrices that share the activation (wq|wk|wv, gate|up) in ONE launch; residual only with one matrix
+struct GemmJob {
+    const DTensor *W;
+    void *w_tiles;
+    bool w_tiles_ready;
+    float *out;
+    int64_t out_stride;
+};
+void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,
+                          float *splitk_scratch, size_t splitk_bytes, cudaStream_t s);
 
 // --- sampling -------------------------------------------------------------------------------------------
 // out[r] = first argmax of row r.  If feed_tok/feed_pos are given (device-side decode loop) the sampled id is also

@@ -260,31 +260,38 @@ __device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) 
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-struct GemmArgs {
-    const __nv_bfloat16 *a_tiles; // [m_tiles][k_tiles][128 x 64]
-    const __nv_bfloat16 *b_tiles; // [n_tiles][k_tiles][256 x 64]
+struct GemmJobDev {             // one weight matrix of a launch: several matrices that share the activation
+    const __nv_bfloat16 *b_tiles; // [n_tiles][k_tiles][256 x 64]   (wq|wk|wv, gate|up) run as ONE launch
     float *out;
     int64_t out_stride;
-    const float *residual;
+    int N, n_tiles, nt0;          // nt0: first n-tile of this matrix in the launch's concatenated n-tile space
+    int col0;                     // first column of this matrix in the split-K partial rows
+};
+struct GemmArgs {
+    const __nv_bfloat16 *a_tiles; // [m_tiles][k_tiles][128 x 64]
+    GemmJobDev job[3];
+    int n_jobs;
+    const float *residual;        // single-matrix launches only
     int64_t res_stride;
-    int M, N, k_tiles, m_tiles, n_tiles;
+    int M, N_total, k_tiles, m_tiles, n_tiles; // n_tiles: over all matrices
     uint32_t lbo, sbo;
     // split-K for small M (batched decode): with one m-tile and few n-tiles most SMs would have no work item, and the
     // weight tiles are the bytes that have to stream.  A work item is (m-tile, n-tile, k-slice); slices write fp32
-    // partial tiles to `partial` [ksplit][M][N], summed in slice order by gemm_splitk_reduce_kernel.
+    // partial tiles to `partial` [ksplit][M][N_total], summed in slice order by gemm_splitk_reduce_kernel.
     int ksplit, k_per_split;
     float *partial;
 };
 
-__global__ void gemm_splitk_reduce_kernel(const float *__restrict__ partial, int ksplit, int M, int N, float *__restrict__ out,
-                                          int64_t out_stride, const float *__restrict__ residual, int64_t res_stride) {
+__global__ void gemm_splitk_reduce_kernel(const float *__restrict__ partial, int ksplit, int M, int N, int N_total, int col0,
+                                          float *__restrict__ out, int64_t out_stride, const float *__restrict__ residual,
+                                          int64_t res_stride) {
     const int64_t total = (int64_t)M * N / 4;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t e = i * 4;
-        const int row = (int)(e / N), col = (int)(e % N);
+        const int row = (int)(i * 4 / N), col = (int)(i * 4 % N);
+        const int64_t e = (int64_t)row * N_total + col0 + col;
         float4 acc = *(const float4 *)(partial + e);
         for (int k = 1; k < ksplit; k++) {
-            const float4 p = *(const float4 *)(partial + (int64_t)k * M * N + e);
+            const float4 p = *(const float4 *)(partial + (int64_t)k * M * N_total + e);
             acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
         }
         if (residual) {
@@ -329,6 +336,8 @@ gemm_tcgen05_kernel(const GemmArgs g) {
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
                 const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
+                const int jb = (g.n_jobs > 2 && nt >= g.job[2].nt0) ? 2 : (g.n_jobs > 1 && nt >= g.job[1].nt0) ? 1 : 0;
+                const __nv_bfloat16 *bt = g.job[jb].b_tiles + (int64_t)(nt - g.job[jb].nt0) * g.k_tiles * (GM_BN * GM_BK);
                 const int kt0 = ks * g.k_per_split, kt1 = min(g.k_tiles, kt0 + g.k_per_split);
                 for (int kt = kt0; kt < kt1; kt++, it++) {
                     const int s = it % GM_STAGES;
@@ -336,7 +345,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                     uint8_t *sa = stages + (size_t)s * GM_STAGE_BYTES;
                     gm_mbar_expect_tx(full + s, GM_STAGE_BYTES);
                     gm_bulk_g2s(sa, g.a_tiles + ((int64_t)mt * g.k_tiles + kt) * (GM_BM * GM_BK), GM_A_BYTES, full + s);
-                    gm_bulk_g2s(sa + GM_A_BYTES, g.b_tiles + ((int64_t)nt * g.k_tiles + kt) * (GM_BN * GM_BK), GM_B_BYTES, full + s);
+                    gm_bulk_g2s(sa + GM_A_BYTES, bt + (int64_t)kt * (GM_BN * GM_BK), GM_B_BYTES, full + s);
                 }
             }
         }
@@ -371,17 +380,18 @@ gemm_tcgen05_kernel(const GemmArgs g) {
         for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
             const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
             const int acc = acc_it & 1;
+            const GemmJobDev &J = g.job[(g.n_jobs > 2 && nt >= g.job[2].nt0) ? 2 : (g.n_jobs > 1 && nt >= g.job[1].nt0) ? 1 : 0];
             gm_mbar_wait(tfull + acc, (acc_it >> 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const int row = mt * GM_BM + q * 32 + lane;
             for (int c0 = 0; c0 < GM_BN; c0 += 32) {
                 uint32_t r[32];
                 gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
-                const int col = nt * GM_BN + c0;
-                if (row < g.M && col < g.N) {
-                    float *o = g.ksplit > 1 ? g.partial + ((int64_t)ks * g.M + row) * g.N + col : g.out + (int64_t)row * g.out_stride + col;
+                const int col = (nt - J.nt0) * GM_BN + c0; // column inside this matrix
+                if (row < g.M && col < J.N) {
+                    float *o = g.ksplit > 1 ? g.partial + ((int64_t)ks * g.M + row) * g.N_total + J.col0 + col : J.out + (int64_t)row * J.out_stride + col;
                     const float *res = (g.residual && g.ksplit == 1) ? g.residual + (int64_t)row * g.res_stride + col : nullptr;
-                    if (col + 32 <= g.N) {
+                    if (col + 32 <= J.N) {
 #pragma unroll
                         for (int j = 0; j < 32; j += 4) {
                             float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
@@ -393,7 +403,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                             *(float4 *)(o + j) = v;
                         }
                     } else {
-                        for (int j = 0; j < 32 && col + j < g.N; j++) o[j] = __uint_as_float(r[j]) + (res ? res[j] : 0.f);
+                        for (int j = 0; j < 32 && col + j < J.N; j++) o[j] = __uint_as_float(r[j]) + (res ? res[j] : 0.f);
                     }
                 }
             }
@@ -450,9 +460,12 @@ void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s) {
     B2_CUDA(cudaGetLastError());
 }
 
-void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
-                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, float *splitk_scratch, size_t splitk_bytes, cudaStream_t s) {
-    B2_CHECK(W.cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
+void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,
+                          float *splitk_scratch, size_t splitk_bytes, cudaStream_t s) {
+    B2_CHECK(n_jobs >= 1 && n_jobs <= 3, B2_EINVAL, "gemm: 1 to 3 matrices per launch");
+    B2_CHECK(!residual || n_jobs == 1, B2_EINVAL, "gemm: the residual add needs a single matrix");
+    const int64_t cols = jobs[0].W->cols;
+    B2_CHECK(cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
     static thread_local bool configured = false;
     static thread_local uint32_t lbo = 128, sbo = 1024;
     if (!configured) {
@@ -460,20 +473,31 @@ void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out
         if (getenv("B200LLM_UMMA_SWAP") && atoi(getenv("B200LLM_UMMA_SWAP"))) { lbo = 1024; sbo = 128; }
         configured = true;
     }
-    const int64_t rows_pad = align_up(W.rows, GM_BN);
-    if (!w_tiles_ready) launch_gemm_dequant_w(W, w_tiles, s); // 1. quantised W -> bf16 tiles (unless the caller keeps them)
     GemmArgs g;
     g.a_tiles = (const __nv_bfloat16 *)x_tiles;
-    g.b_tiles = (const __nv_bfloat16 *)w_tiles;
-    g.out = out; g.out_stride = out_stride; g.residual = residual; g.res_stride = res_stride;
-    g.M = n_tok; g.N = (int)W.rows; g.k_tiles = (int)(W.cols / GM_BK);
-    g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = (int)(rows_pad / GM_BN);
+    g.n_jobs = n_jobs;
+    int nt = 0, col = 0;
+    bool rows4 = true;
+    for (int j = 0; j < n_jobs; j++) {
+        const DTensor &W = *jobs[j].W;
+        B2_CHECK(W.cols == cols, B2_EINVAL, "gemm: matrices of one launch share K");
+        if (!jobs[j].w_tiles_ready) launch_gemm_dequant_w(W, jobs[j].w_tiles, s); // quantised W -> bf16 tiles (unless kept resident)
+        g.job[j].b_tiles = (const __nv_bfloat16 *)jobs[j].w_tiles;
+        g.job[j].out = jobs[j].out; g.job[j].out_stride = jobs[j].out_stride;
+        g.job[j].N = (int)W.rows; g.job[j].n_tiles = (int)(align_up(W.rows, GM_BN) / GM_BN);
+        g.job[j].nt0 = nt; g.job[j].col0 = col;
+        nt += g.job[j].n_tiles; col += (int)W.rows;
+        rows4 = rows4 && W.rows % 4 == 0;
+    }
+    g.residual = residual; g.res_stride = res_stride;
+    g.M = n_tok; g.N_total = col; g.k_tiles = (int)(cols / GM_BK);
+    g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = nt;
     g.lbo = lbo; g.sbo = sbo;
     g.ksplit = 1; g.k_per_split = g.k_tiles; g.partial = nullptr;
     const int tiles = g.m_tiles * g.n_tiles;
-    if (splitk_scratch && g.m_tiles == 1 && tiles < 148 && W.rows % 4 == 0) {
+    if (splitk_scratch && g.m_tiles == 1 && tiles <= 148 / 2 && rows4) { // at least 2 slices per tile or not worth a reduce pass
         int ks = std::min(148 / tiles, g.k_tiles / 4);
-        while (ks > 1 && (size_t)ks * n_tok * W.rows * sizeof(float) > splitk_bytes) ks--;
+        while (ks > 1 && (size_t)ks * n_tok * g.N_total * sizeof(float) > splitk_bytes) ks--;
         if (ks > 1) {
             g.k_per_split = (g.k_tiles + ks - 1) / ks;
             g.ksplit = (g.k_tiles + g.k_per_split - 1) / g.k_per_split;
@@ -485,12 +509,21 @@ void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
     if (g.ksplit > 1) {
-        const int64_t total = (int64_t)n_tok * W.rows / 4;
-        const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
-        gemm_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(g.partial, g.ksplit, n_tok, (int)W.rows, out, out_stride, residual, res_stride);
-        g_launch_count++;
-        B2_CUDA(cudaGetLastError());
+        for (int j = 0; j < n_jobs; j++) {
+            const int64_t total = (int64_t)n_tok * g.job[j].N / 4;
+            const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 8);
+            gemm_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(g.partial, g.ksplit, n_tok, g.job[j].N, g.N_total, g.job[j].col0, g.job[j].out,
+                                                             g.job[j].out_stride, residual, res_stride);
+            g_launch_count++;
+            B2_CUDA(cudaGetLastError());
+        }
     }
+}
+
+void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
+                    int64_t res_stride, void *w_tiles, bool w_tiles_ready, float *splitk_scratch, size_t splitk_bytes, cudaStream_t s) {
+    GemmJob j{&W, w_tiles, w_tiles_ready, out, out_stride};
+    launch_gemm_tc_multi(&j, 1, x_tiles, n_tok, residual, res_stride, splitk_scratch, splitk_bytes, s);
 }
 
 } // namespace b2

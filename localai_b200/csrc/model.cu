@@ -388,22 +388,50 @@ void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const 
     launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, false, gemm_part_, gemm_part_bytes_, stream);
 }
 
+// Several matrices that share the activation tiles in ONE launch (wq|wk|wv, gate|up) when their bf16 tiles are
+// resident; otherwise one launch each through the scratch tile buffer.
+void Model::gemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n) {
+    if (!gemm_part_) {
+        gemm_part_bytes_ = (size_t)32 << 20;
+        gemm_part_ = (float *)dalloc(gemm_part_bytes_);
+    }
+    GemmJob jobs[3];
+    bool all = n_jobs <= 3;
+    for (int j = 0; j < n_jobs && all; j++) {
+        void *t = resident_tiles(*Ws[j]);
+        if (!t) all = false;
+        else jobs[j] = GemmJob{Ws[j], t, true, outs[j], strides[j]};
+    }
+    if (all) {
+        launch_gemm_tc_multi(jobs, n_jobs, gemm_x_, n, nullptr, 0, gemm_part_, gemm_part_bytes_, stream);
+        return;
+    }
+    for (int j = 0; j < n_jobs; j++) gemm(*Ws[j], n, outs[j], strides[j], nullptr, 0);
+}
+
 // Prefill / batched decode: every mat-mul is a tcgen05 tensor-core GEMM on bf16 operands (weights dequantised into
 // operand tiles on the fly); attention, norms and RoPE as in the other paths.
 void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hd;
     ensure_gemm_scratch(0, gemm_x_tiles_bytes(n, std::max(d, ff)));
     launch_gemm_prepare_x_rmsnorm(x_, d, (const float *)L.attn_norm.data, n, d, hp.rms_eps, gemm_x_, nullptr, stream);
-    gemm(L.wq, n, q_, d, nullptr, 0);
-    gemm(L.wk, n, k_, kvd, nullptr, 0);
-    gemm(L.wv, n, v_, kvd, nullptr, 0);
+    {
+        const DTensor *Ws[3] = {&L.wq, &L.wk, &L.wv};
+        float *outs[3] = {q_, k_, v_};
+        const int64_t strides[3] = {d, kvd, kvd};
+        gemm_multi(Ws, outs, strides, 3, n);
+    }
     launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
     attention(kv, n);
     launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
     gemm(L.wo, n, x_, d, x_, d);
     launch_gemm_prepare_x_rmsnorm(x_, d, (const float *)L.ffn_norm.data, n, d, hp.rms_eps, gemm_x_, nullptr, stream);
-    gemm(L.gate, n, gate_, ff, nullptr, 0);
-    gemm(L.up, n, up_, ff, nullptr, 0);
+    {
+        const DTensor *Ws[2] = {&L.gate, &L.up};
+        float *outs[2] = {gate_, up_};
+        const int64_t strides[2] = {ff, ff};
+        gemm_multi(Ws, outs, strides, 2, n);
+    }
     launch_gemm_prepare_x_swiglu(gate_, up_, n, ff, gemm_x_, stream);
     gemm(L.down, n, x_, d, x_, d);
 }

@@ -87,6 +87,7 @@ class Model {
     void attention(const KVLayout &kv, int n);
     void run_layer_gemm(const LayerW &L, const KVLayout &kv, int n);
     void gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride);
+    void gemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n);
     void ensure_gemm_scratch(size_t w_bytes, size_t x_bytes);
     void *resident_tiles(const DTensor &W);
     std::unordered_map<const uint8_t *, void *> w_tiles_; // resident bf16 operand tiles, keyed by the weight pointer
