@@ -257,7 +257,7 @@ def main():
     eng.release(rid)
     fin = evs[-1]
     e2e_ms = max_over_ranks(fin["t_gen_ms"] / max(1, fin["n_decoded"] - 1))
-    e2e = {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": 48, "d2h_bytes_per_step": 4,
+    e2e = {"value": world * 1e3 / e2e_ms, "unit": UNIT, "h2d_bytes_per_step": 12 + 584, "d2h_bytes_per_step": 8,  # token/pos/slot + SampleSpec up; token id + mirostat mu down
            "prompt_ms": fin["t_prompt_ms"], "wall_s": t_wall, "n_decoded": fin["n_decoded"],
            "path": "b2_submit/b2_poll (PredictStream), greedy, host prompt ids"}
 
