@@ -550,11 +550,22 @@ void Model::build_mega() {
         mega_att_scores_ = (float *)dalloc((size_t)hp.n_head * n_ctx_slot * sizeof(float));
         mega_att_part_ = (float *)dalloc((size_t)hp.n_head * mega_att_parts_ * hp.head_dim * sizeof(float));
         mega_att_cnt_ = (unsigned *)dalloc((size_t)hp.n_head * 2 * sizeof(unsigned));
-        B2_CUDA(cudaMemsetAsync(mega_att_cnt_, 0, (size_t)hp.n_head * 2 * sizeof(unsigned), stream));
-        mega_att_base_ = 0;
+        // The barrier counters only ever grow and are compared modulo 2^32; B200LLM_MEGA_COUNTER0 starts them at an
+        // arbitrary value so that a test can drive them across the wrap-around.
+        const unsigned c0 = getenv("B200LLM_MEGA_COUNTER0") ? (unsigned)strtoul(getenv("B200LLM_MEGA_COUNTER0"), nullptr, 0) : 0u;
+        {
+            std::vector<unsigned> init((size_t)hp.n_head * 2, c0);
+            B2_CUDA(cudaMemcpyAsync(mega_att_cnt_, init.data(), init.size() * sizeof(unsigned), cudaMemcpyHostToDevice, stream));
+            B2_CUDA(cudaStreamSynchronize(stream));
+        }
+        mega_att_base_ = c0; // (advances by n_layer * parts per launch, the grid counter by CTAs * barriers)
         mega_bar_ = (unsigned *)dalloc(4096);
-        B2_CUDA(cudaMemsetAsync(mega_bar_, 0, 4096, stream));
-        mega_epoch_ = 0;
+        {
+            std::vector<unsigned> init(1024, c0);
+            B2_CUDA(cudaMemcpyAsync(mega_bar_, init.data(), 4096, cudaMemcpyHostToDevice, stream));
+            B2_CUDA(cudaStreamSynchronize(stream));
+        }
+        mega_epoch_ = c0;
     }
     int coop = 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);

@@ -231,6 +231,21 @@ def test_greedy_long_context(model_files, n_prompt, monkeypatch):
     assert got.tolist() == want.tolist()
 
 
+def test_mega_barrier_counters_wrap_around(model_files, monkeypatch):
+    """the persistent kernel's grid-barrier and per-head counters only grow and are compared modulo 2^32: start them
+    just below the wrap and decode across it"""
+    path = model_files["mini_q4_k_m"]
+    ref = O.OracleModel(path, n_ctx=160)
+    prompt = np.random.default_rng(21).integers(0, ref.n_vocab, 40).astype(np.int32)
+    want, _, _ = ref.generate_greedy(prompt, 48)
+    # the grid counter advances by CTAs x barriers (~2800) per step, the per-head counters by layers x parts (12)
+    for below in (3000, 100):
+        monkeypatch.setenv("B200LLM_MEGA_COUNTER0", str(2 ** 32 - below))
+        with capi.Engine(path, n_ctx=160, n_batch=32) as e:
+            got, _, _ = e.decode_greedy(prompt, 48)
+        assert got.tolist() == want.tolist(), f"counters started {below} below the wrap"
+
+
 def test_batched_decode_equals_single(model_files):
     """4 sequences decoded in one batch give the logits each gives alone (slots are independent)."""
     path = model_files["mini_q4_k_m"]
