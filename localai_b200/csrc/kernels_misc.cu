@@ -118,10 +118,45 @@ attention_kernel(const float *__restrict__ q, const int32_t *__restrict__ pos, c
                    h / (n_head / n_head_kv), hd, scale, out + ((int64_t)t * n_head + h) * hd, smem, threadIdx.x, ATT_THREADS);
 }
 
+// grouped-query variant: one CTA per (KV head, token) serves the G query heads of the group (attention.cuh)
+template <int G>
+__global__ void __launch_bounds__(ATT_THREADS)
+attention_group_kernel(const float *__restrict__ q, const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head,
+                       int hd, KVLayout kv, float *__restrict__ out, float scale) {
+    extern __shared__ __align__(16) float smem[];
+    const int hk = blockIdx.x, t = blockIdx.y;
+    const int64_t row0 = ((int64_t)t * n_head + (int64_t)hk * G) * hd; // heads hk*G .. hk*G+G-1 are consecutive
+    attention_group<G>(q + row0, pos[t] + 1, kv.page_table + (int64_t)slot[t] * kv.max_pages, kv, hk, hd, scale, out + row0, smem,
+                       threadIdx.x, ATT_THREADS);
+}
+
+template <int G>
+static bool try_launch_attention_group(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv,
+                                       int hd, const KVLayout &kv, float *out, int max_ctx, cudaStream_t s) {
+    const size_t smem = attention_group_smem_bytes(G, hd, max_ctx, ATT_THREADS);
+    if (smem > 96 * 1024) return false; // keep at least two CTAs per SM; longer contexts use the per-head kernel
+    static thread_local bool configured = false;
+    if (!configured) {
+        B2_CUDA(cudaFuncSetAttribute(attention_group_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+        configured = true;
+    }
+    const float scale = 1.0f / sqrtf((float)hd);
+    attention_group_kernel<G><<<dim3(n_head_kv, n_tok), ATT_THREADS, smem, s>>>(q, pos, slot, n_head, hd, kv, out, scale);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+    return true;
+}
+
 void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv, int hd,
                       const KVLayout &kv, float *out, int max_ctx, cudaStream_t s) {
     if (n_tok <= 0) return;
     B2_CHECK(hd % 32 == 0 && hd <= 256, B2_EUNSUPPORTED, "attention: head_dim must be a multiple of 32, at most 256");
+    if (n_head % n_head_kv == 0 && hd <= 128 && !(getenv("B200LLM_NO_GQA_ATT") && atoi(getenv("B200LLM_NO_GQA_ATT")))) {
+        const int G = n_head / n_head_kv;
+        if (G == 2 && try_launch_attention_group<2>(q, pos, slot, n_tok, n_head, n_head_kv, hd, kv, out, max_ctx, s)) return;
+        if (G == 4 && try_launch_attention_group<4>(q, pos, slot, n_tok, n_head, n_head_kv, hd, kv, out, max_ctx, s)) return;
+        if (G == 8 && try_launch_attention_group<8>(q, pos, slot, n_tok, n_head, n_head_kv, hd, kv, out, max_ctx, s)) return;
+    }
     const size_t smem = attention_smem_bytes(hd, max_ctx, ATT_THREADS);
     B2_CHECK(smem <= 220 * 1024, B2_EUNSUPPORTED, "attention: context too long for the two-pass kernel");
     static thread_local size_t configured = 0;

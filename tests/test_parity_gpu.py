@@ -246,6 +246,24 @@ def test_mega_barrier_counters_wrap_around(model_files, monkeypatch):
         assert got.tolist() == want.tolist(), f"counters started {below} below the wrap"
 
 
+@pytest.mark.parametrize("name", ["mini_q4_k_m", "micro_q8_0"])
+def test_grouped_query_attention_is_bit_identical(model_files, name, monkeypatch):
+    """the decode attention that serves all query heads of a KV group from one CTA gives exactly the per-head kernel's
+    numbers (same arithmetic, same order per head)"""
+    monkeypatch.setenv("B200LLM_NO_MEGA", "1")   # batch-1 decode through the per-operator path, i.e. launch_attention
+    monkeypatch.setenv("B200LLM_NO_GRAPH", "1")
+    path = model_files[name]
+    prompt = np.random.default_rng(3).integers(0, 4000, 150).astype(np.int32)
+    outs = []
+    for no_gqa in ("0", "1"):
+        monkeypatch.setenv("B200LLM_NO_GQA_ATT", no_gqa)
+        with capi.Engine(path, n_ctx=256, n_batch=64) as e:
+            e.eval(prompt[:-3])
+            outs.append([e.eval(prompt[-3 + i:len(prompt) - 2 + i], n_past=len(prompt) - 3 + i) for i in range(3)])
+    for a, b in zip(*outs):
+        assert np.array_equal(a, b)
+
+
 def test_batched_decode_equals_single(model_files):
     """4 sequences decoded in one batch give the logits each gives alone (slots are independent)."""
     path = model_files["mini_q4_k_m"]
