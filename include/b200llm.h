@@ -124,12 +124,12 @@ typedef struct {
     const size_t *stop_len;    /* optional lengths; NULL => NUL-terminated */
     int32_t n_stop;
     int32_t stream;            /* 1: an event per emitted piece; 0: one final event with the whole text */
-    int32_t mirostat;          /* Mirostat: 0 off, 2 = v2 (what LocalAI's default config sends, core/config/backend_config.go:286-289);
-                                  1 (v1) is refused with B2_EUNSUPPORTED */
+    int32_t mirostat;          /* Mirostat: 0 off, 1 = v1, 2 = v2 (what LocalAI's default config sends,
+                                  core/config/backend_config.go:286-289) */
     float mirostat_tau;        /* MirostatTAU (<= 0 => 5.0) */
     float mirostat_eta;        /* MirostatETA (<= 0 => 0.1) */
-    float typical_p;           /* TypicalP: 0 or >= 1 = off; other values are refused with B2_EUNSUPPORTED */
-    float tfs_z;               /* TailFreeSamplingZ: as typical_p */
+    float typical_p;           /* TypicalP: 0 or >= 1 = off (with typical-p on, at most the 256 most probable tokens are considered) */
+    float tfs_z;               /* TailFreeSamplingZ: 0 or >= 1 = off */
     int32_t reserved[3];
 } b2_request;
 
@@ -208,6 +208,7 @@ typedef struct {
     int64_t seed;
     const int32_t *prev; /* penalty window (the last n_prev tokens) */
     int32_t n_prev;
+    float tfs_z, typical_p; /* 0 or >= 1 = off */
 } b2_sample_params;
 int b2_sample(int device, const float *logits, int n_vocab, const b2_sample_params *p, int n_draws, int32_t *out_tokens, float *out_mu);
 

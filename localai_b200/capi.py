@@ -72,7 +72,7 @@ class SampleParams(C.Structure):
         ("repeat_penalty", C.c_float), ("frequency_penalty", C.c_float), ("presence_penalty", C.c_float),
         ("mirostat", C.c_int32), ("mirostat_tau", C.c_float), ("mirostat_eta", C.c_float), ("mirostat_mu", C.c_float),
         ("ban_token", C.c_int32), ("nl_token", C.c_int32), ("seed", C.c_int64), ("prev", C.POINTER(C.c_int32)),
-        ("n_prev", C.c_int32),
+        ("n_prev", C.c_int32), ("tfs_z", C.c_float), ("typical_p", C.c_float),
     ]
 
 
@@ -176,7 +176,7 @@ def mul_mat(wtype: int, w_raw: np.ndarray, rows: int, cols: int, x: np.ndarray, 
 def sample(logits: np.ndarray, n_draws: int = 1, temperature: float = 0.0, top_k: int = 0, top_p: float = 1.0, min_p: float = 0.0,
            repeat_penalty: float = 1.0, frequency_penalty: float = 0.0, presence_penalty: float = 0.0, prev: Sequence[int] = (),
            mirostat: int = 0, mirostat_tau: float = 5.0, mirostat_eta: float = 0.1, mirostat_mu: Optional[float] = None,
-           ban_token: int = -1, nl_token: int = -1, seed: int = 0, device: int = 0):
+           ban_token: int = -1, nl_token: int = -1, seed: int = 0, device: int = 0, tfs_z: float = 1.0, typical_p: float = 1.0):
     """b2_sample: the device sampler alone on one row of host logits -> (tokens[n_draws], mu_after_each_draw[n_draws])."""
     lg = np.ascontiguousarray(logits, dtype=np.float32).reshape(-1)
     pv = np.ascontiguousarray(prev, dtype=np.int32)
@@ -187,6 +187,7 @@ def sample(logits: np.ndarray, n_draws: int = 1, temperature: float = 0.0, top_k
     p.mirostat, p.mirostat_tau, p.mirostat_eta = mirostat, mirostat_tau, mirostat_eta
     p.mirostat_mu = 2.0 * mirostat_tau if mirostat_mu is None else mirostat_mu
     p.ban_token, p.nl_token, p.seed = ban_token, nl_token, seed
+    p.tfs_z, p.typical_p = tfs_z, typical_p
     p.prev = pv.ctypes.data_as(C.POINTER(C.c_int32))
     p.n_prev = pv.size
     toks = np.empty(n_draws, dtype=np.int32)

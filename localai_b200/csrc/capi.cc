@@ -344,6 +344,8 @@ int b2_sample(int device, const float *logits, int n_vocab, const b2_sample_para
     sp.frequency_penalty = p->frequency_penalty; sp.presence_penalty = p->presence_penalty;
     sp.n_prev = std::min(std::max(p->n_prev, 0), SAMPLE_MAX_PREV);
     for (int k = 0; k < sp.n_prev; k++) sp.prev[k] = p->prev[p->n_prev - sp.n_prev + k];
+    sp.tfs_z = (p->tfs_z > 0.f && p->tfs_z < 1.f) ? p->tfs_z : 1.f;
+    sp.typical_p = (p->typical_p > 0.f && p->typical_p < 1.f) ? p->typical_p : 1.f;
     sp.mirostat = p->mirostat; sp.mirostat_tau = p->mirostat_tau; sp.mirostat_eta = p->mirostat_eta; sp.mirostat_mu = p->mirostat_mu;
     uint64_t rng = (uint64_t)p->seed;
     for (int i = 0; i < n_draws; i++) {

@@ -100,7 +100,10 @@ sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, con
     const float u01 = (float)(splitmix64(sp.rng) >> 40) * (1.0f / 16777216.0f);
     const float inv_t = 1.0f / sp.temperature;
     int K = sp.top_k <= 0 ? n_vocab : min(sp.top_k, n_vocab);
-    const bool full = (K == n_vocab) && sp.top_p >= 1.0f && sp.min_p <= 0.0f;
+    const bool chain = sp.mirostat != 1; // mirostat v1 replaces top-k .. min-p (gpt_sampler_init: temp -> mirostat)
+    if (!chain) K = n_vocab;
+    if (chain && sp.typical_p < 1.0f) K = min(K, 256); // the typicality selection below is O(n * kept) on one thread
+    const bool full = chain && (K == n_vocab) && sp.top_p >= 1.0f && sp.min_p <= 0.0f && sp.tfs_z >= 1.0f && sp.typical_p >= 1.0f;
 
     // ---------------- mirostat v2 (llama_sampler_mirostat_v2_apply): soft-max of the temperature-scaled logits, drop
     // every token whose surprise -log2(p) exceeds mu (the most probable one always stays), renormalise, draw,
@@ -271,21 +274,107 @@ sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, con
         int n = min(n_cand, K);
         if (n <= 0) { out[blockIdx.x] = 0; return; }
         const float l0 = key_float((uint32_t)(cand[0] >> 32));
+        auto logit = [&](int i) { return key_float((uint32_t)(cand[i] >> 32)); };
+        if (!chain) {
+            // ---- mirostat v1 (llama_sampler_mirostat_apply): estimate the Zipf exponent s_hat from the m = 100 most
+            // probable tokens, turn mu into a top-k cut, draw, mu -= eta (surprise - tau).  Candidates beyond the
+            // SAMPLE_MAX_CANDIDATES most probable are not considered (k is clamped to that).
+            float tot = 0.f;
+            for (int i = 0; i < n; i++) tot += expf((logit(i) - l0) * inv_t);
+            const int m = min(100, n);
+            float sum_ti_bi = 0.f, sum_ti_sq = 0.f;
+            for (int i = 0; i < m - 1; i++) {
+                const float t_i = logf((float)(i + 2) / (float)(i + 1));
+                const float b_i = (logit(i) - logit(i + 1)) * inv_t; // log(p_i / p_{i+1})
+                sum_ti_bi += t_i * b_i;
+                sum_ti_sq += t_i * t_i;
+            }
+            const float s_hat = sum_ti_sq > 0.f ? sum_ti_bi / sum_ti_sq : 1.f;
+            const float eps_hat = s_hat - 1.f;
+            const float kf = powf((eps_hat * powf(2.f, sp.mirostat_mu)) / (1.f - powf((float)n_vocab, -eps_hat)), 1.f / s_hat);
+            int k = (kf == kf && kf < (float)n) ? max((int)kf, 1) : n; // NaN / huge -> no cut
+            k = min(k, n);
+            float tot_k = 0.f;
+            for (int i = 0; i < k; i++) tot_k += expf((logit(i) - l0) * inv_t);
+            const float target = u01 * tot_k;
+            float acc = 0.f, e_pick = 1.f;
+            int pick = k - 1;
+            for (int i = 0; i < k; i++) {
+                const float e = expf((logit(i) - l0) * inv_t);
+                acc += e;
+                if (acc > target) { pick = i; e_pick = e; break; }
+                e_pick = e;
+            }
+            out[blockIdx.x] = (int32_t)(~(uint32_t)(cand[pick] & 0xFFFFFFFFu));
+            const float surprise = -log2f(e_pick / tot_k);
+            if (mu_out) mu_out[blockIdx.x] = sp.mirostat_mu - sp.mirostat_eta * (surprise - sp.mirostat_tau);
+            return;
+        }
+        // tail-free sampling (llama_sampler_tail_free_apply) on the T=1 softmax: cut where the cumulated, normalised
+        // |second derivative| of the sorted probabilities exceeds z
+        if (sp.tfs_z < 1.0f && n > 2) {
+            float tot = 0.f;
+            for (int i = 0; i < n; i++) { s_scan[i] = expf(logit(i) - l0); tot += s_scan[i]; }
+            float sum2 = 0.f;
+            for (int i = 0; i < n - 2; i++) sum2 += fabsf(((s_scan[i] - s_scan[i + 1]) - (s_scan[i + 1] - s_scan[i + 2])) / tot);
+            float cum = 0.f;
+            int last = n;
+            for (int i = 0; i < n - 2; i++) {
+                const float d2 = fabsf(((s_scan[i] - s_scan[i + 1]) - (s_scan[i + 1] - s_scan[i + 2])) / tot);
+                cum += sum2 > 1e-6f ? d2 / sum2 : 1.0f / (float)(n - 2);
+                if (cum > sp.tfs_z && i >= 1) { last = i; break; }
+            }
+            n = last;
+        }
+        // locally typical sampling (llama_sampler_typical_apply): keep the tokens whose surprise is closest to the
+        // entropy until their mass exceeds p; the survivors stay in logit order for the samplers that follow
+        if (sp.typical_p < 1.0f && n > 1) {
+            float tot = 0.f;
+            for (int i = 0; i < n; i++) { s_scan[i] = expf(logit(i) - l0); tot += s_scan[i]; }
+            float entropy = 0.f;
+            for (int i = 0; i < n; i++) {
+                const float pi = s_scan[i] / tot;
+                s_scan[i] = pi;
+                entropy += -pi * logf(pi);
+            }
+            // s_scan[i] < 0 marks "taken" (probabilities are > 0)
+            float cum = 0.f;
+            int kept = 0;
+            while (kept < n) {
+                int best = -1;
+                float best_s = INFINITY;
+                for (int i = 0; i < n; i++) {
+                    if (s_scan[i] < 0.f) continue;
+                    const float sh = fabsf(-logf(s_scan[i]) - entropy);
+                    if (sh < best_s) { best_s = sh; best = i; }
+                }
+                if (best < 0) break;
+                cum += s_scan[best];
+                s_scan[best] = -s_scan[best];
+                kept++;
+                if (cum > sp.typical_p) break;
+            }
+            int w = 0;
+            for (int i = 0; i < n; i++)
+                if (s_scan[i] < 0.f) cand[w++] = cand[i];
+            n = max(w, 1);
+        }
         // top-p on the T=1 softmax of the surviving candidates
+        const float l0p = logit(0);
         if (sp.top_p < 1.0f) {
             float tot = 0.f;
-            for (int i = 0; i < n; i++) tot += expf(key_float((uint32_t)(cand[i] >> 32)) - l0);
+            for (int i = 0; i < n; i++) tot += expf(key_float((uint32_t)(cand[i] >> 32)) - l0p);
             float cum = 0.f;
             int keep = n;
             for (int i = 0; i < n; i++) {
-                cum += expf(key_float((uint32_t)(cand[i] >> 32)) - l0) / tot;
+                cum += expf(key_float((uint32_t)(cand[i] >> 32)) - l0p) / tot;
                 if (cum >= sp.top_p) { keep = i + 1; break; }
             }
             n = keep;
         }
         // min-p: p_i >= min_p * p_max  <=>  logit_i >= logit_max + log(min_p)
         if (sp.min_p > 0.0f) {
-            const float thr = l0 + logf(sp.min_p);
+            const float thr = l0p + logf(sp.min_p);
             int keep = 1;
             while (keep < n && key_float((uint32_t)(cand[keep] >> 32)) >= thr) keep++;
             n = keep;

@@ -25,7 +25,8 @@ struct SampleSpec {
     float repeat_penalty = 1.f, frequency_penalty = 0.f, presence_penalty = 0.f;
     int32_t n_prev = 0;
     int32_t nl_token = -1;
-    // mirostat (0 = off, 2 = v2; LocalAI's default config sends 2, core/config/backend_config.go:286-289)
+    float tfs_z = 1.f, typical_p = 1.f; // tail-free / locally typical sampling; >= 1 = off
+    // mirostat (0 = off, 1 = v1, 2 = v2; LocalAI's default config sends 2, core/config/backend_config.go:286-289)
     int32_t mirostat = 0;
     float mirostat_tau = 5.f, mirostat_eta = 0.1f;
     float mirostat_mu = 10.f; // state carried by the caller from draw to draw (starts at 2 * tau)

@@ -62,9 +62,9 @@ int64_t Scheduler::submit(const b2_request &r) {
     q->presence_penalty = r.presence_penalty;
     q->seed = r.seed;
     q->n_keep = r.n_keep;
-    B2_CHECK(r.mirostat == 0 || r.mirostat == 2, B2_EUNSUPPORTED, "mirostat v1 is not implemented (0 = off, 2 = v2)");
-    B2_CHECK(!(r.typical_p > 0.f && r.typical_p < 1.f) && !(r.tfs_z > 0.f && r.tfs_z < 1.f), B2_EUNSUPPORTED,
-             "typical_p / tfs_z sampling is not implemented (leave them at 0 or 1)");
+    B2_CHECK(r.mirostat >= 0 && r.mirostat <= 2, B2_EINVAL, "mirostat must be 0 (off), 1 or 2");
+    q->typical_p = (r.typical_p > 0.f && r.typical_p < 1.f) ? r.typical_p : 1.f;
+    q->tfs_z = (r.tfs_z > 0.f && r.tfs_z < 1.f) ? r.tfs_z : 1.f;
     q->mirostat = r.mirostat;
     q->mirostat_tau = r.mirostat_tau > 0.f ? r.mirostat_tau : 5.f;
     q->mirostat_eta = r.mirostat_eta > 0.f ? r.mirostat_eta : 0.1f;
@@ -459,6 +459,8 @@ bool Scheduler::step() {
                     sp.n_prev = last_n;
                     for (int k = 0; k < last_n; k++) sp.prev[k] = s.cache_tokens[hist - last_n + k];
                 }
+                sp.tfs_z = s.req->tfs_z;
+                sp.typical_p = s.req->typical_p;
                 sp.mirostat = s.req->mirostat;
                 sp.mirostat_tau = s.req->mirostat_tau;
                 sp.mirostat_eta = s.req->mirostat_eta;

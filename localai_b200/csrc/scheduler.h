@@ -38,7 +38,7 @@ struct Request {
     float temperature = 0.f, top_p = 1.f, min_p = 0.f, repeat_penalty = 1.f, frequency_penalty = 0.f, presence_penalty = 0.f;
     int top_k = 0, repeat_last_n = 0, seed = -1, n_keep = 0;
     int mirostat = 0;
-    float mirostat_tau = 5.f, mirostat_eta = 0.1f;
+    float mirostat_tau = 5.f, mirostat_eta = 0.1f, typical_p = 1.f, tfs_z = 1.f;
     bool ignore_eos = false, cache_prompt = false, embedding_mode = false, stream = true;
     std::vector<std::string> stop;
     // results

@@ -231,3 +231,64 @@ def mirostat_v2_ref(logits, temperature, mu, tau, eta, token):
     p2 /= p2.sum()
     obs = -np.log2(p2[token]) if p2[token] > 0 else np.inf
     return kept, p2[token], mu - eta * (obs - tau)
+
+
+def _softmax_sorted(logits):
+    order = np.argsort(-np.asarray(logits, dtype=np.float64), kind="stable")
+    z = np.asarray(logits, dtype=np.float64)[order]
+    p = np.exp(z - z[0])
+    return order, p / p.sum()
+
+
+def tail_free_ref(logits, z):
+    """token ids kept by llama_sampler_tail_free_apply (min_keep = 1) on the given candidates"""
+    order, p = _softmax_sorted(logits)
+    n = p.size
+    if z >= 1.0 or n <= 2:
+        return set(order.tolist())
+    d2 = np.abs(np.diff(np.diff(-p)))  # |(p_i - p_{i+1}) - (p_{i+1} - p_{i+2})|
+    d2 = d2 / d2.sum() if d2.sum() > 1e-6 else np.full(n - 2, 1.0 / (n - 2))
+    last, cum = n, 0.0
+    for i in range(n - 2):
+        cum += d2[i]
+        if cum > z and i >= 1:
+            last = i
+            break
+    return set(order[:last].tolist())
+
+
+def typical_ref(logits, p_keep):
+    """token ids kept by llama_sampler_typical_apply (min_keep = 1)"""
+    order, p = _softmax_sorted(logits)
+    if p_keep >= 1.0:
+        return set(order.tolist())
+    entropy = -(p * np.log(p)).sum()
+    shifted = np.abs(-np.log(p) - entropy)
+    idx = np.argsort(shifted, kind="stable")
+    cum, last = 0.0, p.size
+    for i, k in enumerate(idx):
+        cum += p[k]
+        if cum > p_keep:
+            last = i + 1
+            break
+    return set(order[idx[:last]].tolist())
+
+
+def mirostat_v1_ref(logits, temperature, mu, tau, eta, token, m=100):
+    """One mirostat-v1 step given WHICH token was drawn (llama_sampler_mirostat_apply): returns (k, p of `token` among
+    the k most probable, mu after the update)."""
+    order, p = _softmax_sorted(np.asarray(logits, dtype=np.float64) / temperature)
+    n = p.size
+    mm = min(m, n)
+    i = np.arange(mm - 1)
+    t = np.log((i + 2) / (i + 1))
+    b = np.log(p[:mm - 1] / p[1:mm])
+    s_hat = (t * b).sum() / (t * t).sum()
+    eps = s_hat - 1.0
+    k = ((eps * 2.0 ** mu) / (1.0 - float(n) ** (-eps))) ** (1.0 / s_hat)
+    k = n if not np.isfinite(k) or k >= n else max(int(k), 1)
+    pk = p[:k] / p[:k].sum()
+    where = np.nonzero(order[:k] == token)[0]
+    pt = pk[where[0]] if where.size else 0.0
+    obs = -np.log2(pt) if pt > 0 else np.inf
+    return k, pt, mu - eta * (obs - tau)

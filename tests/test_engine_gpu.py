@@ -255,7 +255,42 @@ def test_requests_with_localai_default_sampling(eng):
     ev2 = list(eng.events(rid2))[-1]
     eng.release(rid2)
     assert ev2["text"] == ev["text"]  # seeded: reproducible
+    for kw in (dict(mirostat=1), dict(typical_p=0.5), dict(tfs_z=0.9)):  # the rest of the chain runs too
+        rid3 = eng.submit(prompt="The quick brown fox", n_predict=8, temperature=0.9, top_k=40, seed=3, stream=False, **kw)
+        ev3 = list(eng.events(rid3))[-1]
+        eng.release(rid3)
+        assert ev3["n_decoded"] == 8 and not (ev3["flags"] & capi.EV_ERROR)
     with pytest.raises(capi.B2Error):
-        eng.submit(prompt="x", n_predict=4, temperature=0.9, mirostat=1)
-    with pytest.raises(capi.B2Error):
-        eng.submit(prompt="x", n_predict=4, temperature=0.9, typical_p=0.5)
+        eng.submit(prompt="x", n_predict=4, temperature=0.9, mirostat=3)
+
+
+@pytest.mark.gpu
+def test_tail_free_and_typical_keep_the_reference_sets():
+    """every draw lies in the set the restated llama.cpp sampler keeps, and every kept token with real mass is drawn"""
+    from oracle import oracle as O
+    rng = np.random.default_rng(11)
+    for trial in range(3):
+        x = (rng.standard_normal(96) * 2.5).astype(np.float32)
+        for kw, keep in ((dict(tfs_z=0.8), O.tail_free_ref(x, 0.8)), (dict(typical_p=0.6), O.typical_ref(x, 0.6))):
+            toks, _ = capi.sample(x, 1500, temperature=1.0, seed=trial, **kw)
+            drawn = set(int(t) for t in toks)
+            assert drawn <= keep, f"{kw}: drew {sorted(drawn - keep)} outside the kept set"
+            p = np.exp(x - x.max()); p /= p.sum()
+            heavy = {t for t in keep if p[t] / sum(p[k] for k in keep) > 0.02}
+            assert heavy <= drawn, f"{kw}: kept tokens never drawn: {sorted(heavy - drawn)}"
+        assert len(O.tail_free_ref(x, 0.8)) < 96 and len(O.typical_ref(x, 0.6)) < 96
+
+
+@pytest.mark.gpu
+def test_mirostat_v1_follows_reference_update():
+    from oracle import oracle as O
+    x = _zipf_logits(8000, 2)
+    tau, eta, temp = 4.0, 0.1, 0.8
+    toks, mus = capi.sample(x, 300, temperature=temp, mirostat=1, mirostat_tau=tau, mirostat_eta=eta, seed=5)
+    mu = 2 * tau
+    for t, mu_after in zip(toks, mus):
+        k, p, mu_ref = O.mirostat_v1_ref(x, temp, mu, tau, eta, int(t))
+        if k <= 1024:  # the device considers the 1024 most probable candidates
+            assert p > 0, "token drawn from outside the top-k mirostat v1 computed"
+            assert abs(mu_ref - float(mu_after)) <= 5e-3 * max(1.0, abs(mu_ref))
+        mu = float(mu_after)
