@@ -98,7 +98,8 @@ class Model {
     size_t gemm_part_bytes_ = 0;
     size_t gemm_w_bytes_ = 0, gemm_x_bytes_ = 0;
     bool no_gemm_ = false;
-    int gemm_min_tokens_ = 4;
+    int gemm_min_tokens_ = -1; // B200LLM_GEMM_MIN_TOKENS; -1 = automatic
+    int gemm_threshold() const;
     void build_mega();
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;
