@@ -61,6 +61,10 @@ __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, in
                 const float d = h2f(q.d[k0 / 32]);
 #pragma unroll
                 for (int j = 0; j < 8; j++) v[j] = (float)q.qs[k0 + j] * d;
+            } else if (is_legacy_type(type)) {
+                const uint8_t *blk = row + (size_t)(k0 / 32) * legacy_block_bytes(type);
+#pragma unroll
+                for (int j = 0; j < 8; j++) v[j] = dequant_legacy_elem(type, blk, k0 % 32 + j);
             } else if (type == B2_T_Q4_K || type == B2_T_Q5_K) {
                 const int bb = type == B2_T_Q4_K ? 144 : 176;
                 const uint8_t *blk = row + (size_t)(k0 / 256) * bb;

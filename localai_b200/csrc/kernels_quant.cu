@@ -98,6 +98,9 @@ __global__ void dequant_rows_kernel(const uint8_t *__restrict__ W, int type, int
             const float d = h2f(q.d[grp]);
             const int8_t *qs = q.qs + grp * 32;
             for (int l = 0; l < 32; l++) y[l] = __fmul_rn((float)qs[l], d);
+        } else if (is_legacy_type(type)) {
+            const uint8_t *blk = row + grp * legacy_block_bytes(type);
+            for (int l = 0; l < 32; l++) y[l] = dequant_legacy_elem(type, blk, l);
         } else if (type == B2_T_Q4_K || type == B2_T_Q5_K) {
             const int bb = type == B2_T_Q4_K ? 144 : 176;
             const int64_t ib = grp / 8;

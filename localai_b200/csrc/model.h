@@ -100,6 +100,7 @@ class Model {
     bool no_gemm_ = false;
     int gemm_min_tokens_ = -1; // B200LLM_GEMM_MIN_TOKENS; -1 = automatic
     int gemm_threshold() const;
+    bool tiles_only_ = false; // some weight is in a format only the tensor-core path reads
     void build_mega();
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;

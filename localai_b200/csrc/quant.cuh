@@ -36,6 +36,30 @@ __device__ __forceinline__ void get_scale_min_k4_w(int j, uint32_t w0, uint32_t 
     }
 }
 
+__device__ __forceinline__ bool is_legacy_type(int t) { return t == 2 || t == 3 || t == 6 || t == 7; } // Q4_0 Q4_1 Q5_0 Q5_1
+__device__ __forceinline__ int legacy_block_bytes(int t) { return t == 2 ? 18 : t == 3 ? 20 : t == 6 ? 22 : 24; }
+// element l (0..31) of a legacy block (GGUF layout, 2-byte aligned), with dequantize_row_q4_0 / q4_1 / q5_0 / q5_1's
+// arithmetic and rounding (unfused multiply / add)
+__device__ __forceinline__ float dequant_legacy_elem(int type, const uint8_t *blk, int l) {
+    const float d = h2f(*(const uint16_t *)blk);
+    const int j = l & 15, hi = l >> 4;
+    if (type == 2 /* Q4_0 */) {
+        const uint8_t b = blk[2 + j];
+        return __fmul_rn((float)((hi ? (b >> 4) : (b & 0x0F)) - 8), d);
+    }
+    if (type == 3 /* Q4_1 */) {
+        const float m = h2f(*(const uint16_t *)(blk + 2));
+        const uint8_t b = blk[4 + j];
+        return __fadd_rn(__fmul_rn((float)(hi ? (b >> 4) : (b & 0x0F)), d), m);
+    }
+    const int off = type == 6 /* Q5_0 */ ? 2 : 4; // qh[4] then qs[16]
+    const uint32_t qh = (uint32_t)blk[off] | ((uint32_t)blk[off + 1] << 8) | ((uint32_t)blk[off + 2] << 16) | ((uint32_t)blk[off + 3] << 24);
+    const uint8_t b = blk[off + 4 + j];
+    const int q = (hi ? (b >> 4) : (b & 0x0F)) | (((qh >> l) & 1) << 4);
+    if (type == 6) return __fmul_rn((float)(q - 16), d);
+    return __fadd_rn(__fmul_rn((float)q, d), h2f(*(const uint16_t *)(blk + 2)));
+}
+
 // one Q6_K row in device layout: nb 208-byte blocks [ql 128][qh 64][scales 16] (16-byte aligned; 13 x 16 B, an odd
 // stride, so lanes that each read a different block of a staged row hit different shared-memory banks), then the nb
 // fp16 super-block scales

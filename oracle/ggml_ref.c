@@ -33,7 +33,8 @@
 #define QK_K 256
 #define K_SCALE_SIZE 12
 
-enum { T_F32 = 0, T_F16 = 1, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14, T_Q8_K = 15 };
+enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13,
+       T_Q6_K = 14, T_Q8_K = 15 };
 
 typedef uint16_t fp16_t;
 
@@ -51,15 +52,24 @@ static inline fp16_t fp32_to_fp16(float x) {
 
 #pragma pack(push, 1)
 typedef struct { fp16_t d; int8_t qs[QK8_0]; } block_q8_0;                                   /* 34 B  */
+typedef struct { fp16_t d, s; int8_t qs[QK8_0]; } block_q8_1;                                /* 36 B: s = d * sum(qs) */
+typedef struct { fp16_t d; uint8_t qs[16]; } block_q4_0;                                     /* 18 B  */
+typedef struct { fp16_t d, m; uint8_t qs[16]; } block_q4_1;                                  /* 20 B  */
+typedef struct { fp16_t d; uint8_t qh[4]; uint8_t qs[16]; } block_q5_0;                      /* 22 B  */
+typedef struct { fp16_t d, m; uint8_t qh[4]; uint8_t qs[16]; } block_q5_1;                   /* 24 B  */
 typedef struct { fp16_t d, dmin; uint8_t scales[K_SCALE_SIZE]; uint8_t qs[QK_K / 2]; } block_q4_K; /* 144 B */
 typedef struct { fp16_t d, dmin; uint8_t scales[K_SCALE_SIZE]; uint8_t qh[QK_K / 8]; uint8_t qs[QK_K / 2]; } block_q5_K; /* 176 B */
 typedef struct { uint8_t ql[QK_K / 2]; uint8_t qh[QK_K / 4]; int8_t scales[QK_K / 16]; fp16_t d; } block_q6_K; /* 210 B */
 typedef struct { float d; int8_t qs[QK_K]; int16_t bsums[QK_K / 16]; } block_q8_K;             /* 292 B */
 #pragma pack(pop)
 
-static int64_t type_block(int t) { return t == T_F32 || t == T_F16 ? 1 : (t == T_Q8_0 ? 32 : 256); }
+static int64_t type_block(int t) {
+    if (t == T_F32 || t == T_F16) return 1;
+    return (t == T_Q8_0 || t == T_Q8_1 || t == T_Q4_0 || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1) ? 32 : 256;
+}
 static int64_t type_bytes(int t) {
     switch (t) {
+        case T_Q4_0: return 18; case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24; case T_Q8_1: return 36;
         case T_F32: return 4; case T_F16: return 2; case T_Q8_0: return 34; case T_Q4_K: return 144;
         case T_Q5_K: return 176; case T_Q6_K: return 210; case T_Q8_K: return 292;
     }
@@ -82,6 +92,52 @@ static void dequantize_row_q8_0(const block_q8_0 *x, float *y, int64_t k) {
     for (int64_t i = 0; i < k / QK8_0; i++) {
         const float d = fp16_to_fp32(x[i].d);
         for (int j = 0; j < QK8_0; ++j) y[i * QK8_0 + j] = x[i].qs[j] * d;
+    }
+}
+
+/* legacy 32-element blocks (ggml-quants.c dequantize_row_q4_0 / q4_1 / q5_0 / q5_1) */
+static void dequantize_row_q4_0(const block_q4_0 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const float d = fp16_to_fp32(x[i].d);
+        for (int j = 0; j < 16; ++j) {
+            y[i * 32 + j] = ((x[i].qs[j] & 0x0F) - 8) * d;
+            y[i * 32 + j + 16] = ((x[i].qs[j] >> 4) - 8) * d;
+        }
+    }
+}
+static void dequantize_row_q4_1(const block_q4_1 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const float d = fp16_to_fp32(x[i].d), m = fp16_to_fp32(x[i].m);
+        for (int j = 0; j < 16; ++j) {
+            y[i * 32 + j] = (x[i].qs[j] & 0x0F) * d + m;
+            y[i * 32 + j + 16] = (x[i].qs[j] >> 4) * d + m;
+        }
+    }
+}
+static void dequantize_row_q5_0(const block_q5_0 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const float d = fp16_to_fp32(x[i].d);
+        uint32_t qh;
+        memcpy(&qh, x[i].qh, sizeof(qh));
+        for (int j = 0; j < 16; ++j) {
+            const uint8_t xh_0 = ((qh >> (j + 0)) << 4) & 0x10;
+            const uint8_t xh_1 = ((qh >> (j + 12))) & 0x10;
+            y[i * 32 + j] = (((x[i].qs[j] & 0x0F) | xh_0) - 16) * d;
+            y[i * 32 + j + 16] = (((x[i].qs[j] >> 4) | xh_1) - 16) * d;
+        }
+    }
+}
+static void dequantize_row_q5_1(const block_q5_1 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / 32; i++) {
+        const float d = fp16_to_fp32(x[i].d), m = fp16_to_fp32(x[i].m);
+        uint32_t qh;
+        memcpy(&qh, x[i].qh, sizeof(qh));
+        for (int j = 0; j < 16; ++j) {
+            const uint8_t xh_0 = ((qh >> (j + 0)) << 4) & 0x10;
+            const uint8_t xh_1 = ((qh >> (j + 12))) & 0x10;
+            y[i * 32 + j] = ((x[i].qs[j] & 0x0F) | xh_0) * d + m;
+            y[i * 32 + j + 16] = ((x[i].qs[j] >> 4) | xh_1) * d + m;
+        }
     }
 }
 
@@ -157,6 +213,10 @@ void ref_dequantize_row(int type, const void *x, float *y, int64_t k) {
         case T_F32: memcpy(y, x, k * sizeof(float)); break;
         case T_F16: for (int64_t i = 0; i < k; i++) y[i] = fp16_to_fp32(((const fp16_t *)x)[i]); break;
         case T_Q8_0: dequantize_row_q8_0((const block_q8_0 *)x, y, k); break;
+        case T_Q4_0: dequantize_row_q4_0((const block_q4_0 *)x, y, k); break;
+        case T_Q4_1: dequantize_row_q4_1((const block_q4_1 *)x, y, k); break;
+        case T_Q5_0: dequantize_row_q5_0((const block_q5_0 *)x, y, k); break;
+        case T_Q5_1: dequantize_row_q5_1((const block_q5_1 *)x, y, k); break;
         case T_Q4_K: dequantize_row_q4_K((const block_q4_K *)x, y, k); break;
         case T_Q5_K: dequantize_row_q5_K((const block_q5_K *)x, y, k); break;
         case T_Q6_K: dequantize_row_q6_K((const block_q6_K *)x, y, k); break;
@@ -184,6 +244,29 @@ void ref_quantize_row_q8_0(const float *x, void *vy, int64_t k) {
         const float id = d ? 1.0f / d : 0.0f;
         y[i].d = fp32_to_fp16(d);
         for (int j = 0; j < QK8_0; ++j) y[i].qs[j] = (int8_t)roundf(x[i * QK8_0 + j] * id);
+    }
+}
+
+/* quantize_row_q8_1_ref: like q8_0 plus s = d * sum(qs), both stored as fp16 */
+void ref_quantize_row_q8_1(const float *x, void *vy, int64_t k) {
+    block_q8_1 *y = (block_q8_1 *)vy;
+    for (int64_t i = 0; i < k / 32; i++) {
+        float amax = 0.0f;
+        for (int j = 0; j < 32; j++) {
+            const float v = fabsf(x[i * 32 + j]);
+            if (v > amax) amax = v;
+        }
+        const float d = amax / ((1 << 7) - 1);
+        const float id = d ? 1.0f / d : 0.0f;
+        y[i].d = fp32_to_fp16(d);
+        int sum = 0;
+        for (int j = 0; j < 16; ++j) {
+            const float v0 = x[i * 32 + j] * id, v1 = x[i * 32 + 16 + j] * id;
+            y[i].qs[j] = (int8_t)roundf(v0);
+            y[i].qs[16 + j] = (int8_t)roundf(v1);
+            sum += y[i].qs[j] + y[i].qs[16 + j];
+        }
+        y[i].s = fp32_to_fp16(sum * d);
     }
 }
 
@@ -224,6 +307,66 @@ static float vec_dot_q8_0_q8_0(int n, const block_q8_0 *x, const block_q8_0 *y) 
         int sumi = 0;
         for (int j = 0; j < QK8_0; j++) sumi += x[i].qs[j] * y[i].qs[j];
         sumf += sumi * (fp16_to_fp32(x[i].d) * fp16_to_fp32(y[i].d));
+    }
+    return sumf;
+}
+
+/* ggml_vec_dot_q4_0_q8_0 / q4_1_q8_1 / q5_0_q8_0 / q5_1_q8_1, generic paths */
+static float vec_dot_q4_0_q8_0(int n, const block_q4_0 *x, const block_q8_0 *y) {
+    float sumf = 0;
+    for (int i = 0; i < n / 32; i++) {
+        int sumi = 0;
+        for (int j = 0; j < 16; ++j) {
+            const int v0 = (x[i].qs[j] & 0x0F) - 8, v1 = (x[i].qs[j] >> 4) - 8;
+            sumi += (v0 * y[i].qs[j]) + (v1 * y[i].qs[j + 16]);
+        }
+        sumf += sumi * fp16_to_fp32(x[i].d) * fp16_to_fp32(y[i].d);
+    }
+    return sumf;
+}
+static float vec_dot_q4_1_q8_1(int n, const block_q4_1 *x, const block_q8_1 *y) {
+    float sumf = 0;
+    for (int i = 0; i < n / 32; i++) {
+        int sumi = 0;
+        for (int j = 0; j < 16; ++j) {
+            const int v0 = (x[i].qs[j] & 0x0F), v1 = (x[i].qs[j] >> 4);
+            sumi += (v0 * y[i].qs[j]) + (v1 * y[i].qs[j + 16]);
+        }
+        sumf += (fp16_to_fp32(x[i].d) * fp16_to_fp32(y[i].d)) * sumi + fp16_to_fp32(x[i].m) * fp16_to_fp32(y[i].s);
+    }
+    return sumf;
+}
+static float vec_dot_q5_0_q8_0(int n, const block_q5_0 *x, const block_q8_0 *y) {
+    float sumf = 0;
+    for (int i = 0; i < n / 32; i++) {
+        uint32_t qh;
+        memcpy(&qh, x[i].qh, sizeof(qh));
+        int sumi = 0;
+        for (int j = 0; j < 16; ++j) {
+            const uint8_t xh_0 = ((qh & (1u << (j + 0))) >> (j + 0)) << 4;
+            const uint8_t xh_1 = ((qh & (1u << (j + 16))) >> (j + 12));
+            const int32_t x0 = (int8_t)(((x[i].qs[j] & 0x0F) | xh_0) - 16);
+            const int32_t x1 = (int8_t)(((x[i].qs[j] >> 4) | xh_1) - 16);
+            sumi += (x0 * y[i].qs[j]) + (x1 * y[i].qs[j + 16]);
+        }
+        sumf += (fp16_to_fp32(x[i].d) * fp16_to_fp32(y[i].d)) * sumi;
+    }
+    return sumf;
+}
+static float vec_dot_q5_1_q8_1(int n, const block_q5_1 *x, const block_q8_1 *y) {
+    float sumf = 0;
+    for (int i = 0; i < n / 32; i++) {
+        uint32_t qh;
+        memcpy(&qh, x[i].qh, sizeof(qh));
+        int sumi = 0;
+        for (int j = 0; j < 16; ++j) {
+            const uint8_t xh_0 = ((qh >> (j + 0)) << 4) & 0x10;
+            const uint8_t xh_1 = ((qh >> (j + 12))) & 0x10;
+            const int32_t x0 = (x[i].qs[j] & 0xF) | xh_0;
+            const int32_t x1 = (x[i].qs[j] >> 4) | xh_1;
+            sumi += (x0 * y[i].qs[j]) + (x1 * y[i].qs[j + 16]);
+        }
+        sumf += (fp16_to_fp32(x[i].d) * fp16_to_fp32(y[i].d)) * sumi + fp16_to_fp32(x[i].m) * fp16_to_fp32(y[i].s);
     }
     return sumf;
 }
@@ -371,7 +514,8 @@ int ref_vec_dot_type(int wtype) {
     switch (wtype) {
         case T_F32: return T_F32;
         case T_F16: return T_F16;
-        case T_Q8_0: return T_Q8_0;
+        case T_Q8_0: case T_Q4_0: case T_Q5_0: return T_Q8_0;
+        case T_Q4_1: case T_Q5_1: return T_Q8_1;
         default: return T_Q8_K;
     }
 }
@@ -381,6 +525,7 @@ void ref_quantize_activations(int wtype, const float *x, void *y, int64_t k) {
         case T_F32: memcpy(y, x, k * 4); break;
         case T_F16: for (int64_t i = 0; i < k; i++) ((fp16_t *)y)[i] = fp32_to_fp16(x[i]); break;
         case T_Q8_0: ref_quantize_row_q8_0(x, y, k); break;
+        case T_Q8_1: ref_quantize_row_q8_1(x, y, k); break;
         default: ref_quantize_row_q8_K(x, y, k); break;
     }
 }
@@ -390,6 +535,10 @@ float ref_vec_dot(int wtype, int n, const void *w, const void *yq) {
         case T_F32: return vec_dot_f32(n, (const float *)w, (const float *)yq);
         case T_F16: return vec_dot_f16(n, (const fp16_t *)w, (const fp16_t *)yq);
         case T_Q8_0: return vec_dot_q8_0_q8_0(n, (const block_q8_0 *)w, (const block_q8_0 *)yq);
+        case T_Q4_0: return vec_dot_q4_0_q8_0(n, (const block_q4_0 *)w, (const block_q8_0 *)yq);
+        case T_Q4_1: return vec_dot_q4_1_q8_1(n, (const block_q4_1 *)w, (const block_q8_1 *)yq);
+        case T_Q5_0: return vec_dot_q5_0_q8_0(n, (const block_q5_0 *)w, (const block_q8_0 *)yq);
+        case T_Q5_1: return vec_dot_q5_1_q8_1(n, (const block_q5_1 *)w, (const block_q8_1 *)yq);
         case T_Q4_K: return vec_dot_q4_K_q8_K(n, (const block_q4_K *)w, (const block_q8_K *)yq);
         case T_Q5_K: return vec_dot_q5_K_q8_K(n, (const block_q5_K *)w, (const block_q8_K *)yq);
         case T_Q6_K: return vec_dot_q6_K_q8_K(n, (const block_q6_K *)w, (const block_q8_K *)yq);

@@ -37,6 +37,8 @@ def model_files(gguf_dir):
         "mini_q4_k_m": ("mini", "q4_k_m"),
         "mini_q5_k": ("mini", "q5_k"),
         "mini_f16": ("mini", "f16"),
+        "mini_q4_0": ("mini", "q4_0"),
+        "mini_q5_1": ("mini", "q5_1"),
     }
     out = {}
     for name, (arch, preset) in specs.items():

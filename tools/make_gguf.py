@@ -32,8 +32,12 @@ ALIGN = 32
 
 # ggml type ids
 F32, F16, Q8_0, Q4_K, Q5_K, Q6_K = 0, 1, 8, 12, 13, 14
-TYPE_NAMES = {F32: "F32", F16: "F16", Q8_0: "Q8_0", Q4_K: "Q4_K", Q5_K: "Q5_K", Q6_K: "Q6_K"}
-BLOCK = {F32: (1, 4), F16: (1, 2), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210)}
+Q4_0, Q4_1, Q5_0, Q5_1 = 2, 3, 6, 7  # legacy 32-element blocks (tensor-core path only on the device)
+LEGACY = (Q4_0, Q4_1, Q5_0, Q5_1)
+TYPE_NAMES = {F32: "F32", F16: "F16", Q8_0: "Q8_0", Q4_K: "Q4_K", Q5_K: "Q5_K", Q6_K: "Q6_K", Q4_0: "Q4_0", Q4_1: "Q4_1",
+              Q5_0: "Q5_0", Q5_1: "Q5_1"}
+BLOCK = {F32: (1, 4), F16: (1, 2), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), Q4_0: (32, 18),
+         Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24)}
 
 # gguf metadata value types
 T_U8, T_I8, T_U16, T_I16, T_U32, T_I32, T_F32, T_BOOL, T_STR, T_ARR, T_U64, T_I64, T_F64 = range(13)
@@ -84,6 +88,8 @@ def tensor_type(preset: str, arch: Arch, name: str, layer: int) -> int:
         return F16
     if preset == "q8_0":
         return Q8_0
+    if preset in ("q4_0", "q4_1", "q5_0", "q5_1"):  # as llama-quantize: the output matrix gets Q6_K
+        return Q6_K if name == "output.weight" else {"q4_0": Q4_0, "q4_1": Q4_1, "q5_0": Q5_0, "q5_1": Q5_1}[preset]
     if preset in ("q4_k", "q5_k", "q6_k"):
         return {"q4_k": Q4_K, "q5_k": Q5_K, "q6_k": Q6_K}[preset]
     if preset == "q4_k_m":
@@ -132,6 +138,9 @@ def _pack_k_scales(sc: np.ndarray, mn: np.ndarray) -> np.ndarray:
 def random_blocks(rng: np.random.Generator, gtype: int, n_blocks: int, sigma: float) -> np.ndarray:
     """Return uint8 [n_blocks, block_bytes] of random blocks with dequantised std ~ sigma."""
     jitter = rng.uniform(0.8, 1.25, size=n_blocks).astype(np.float32)
+    if gtype in LEGACY:  # quantise Gaussian data with llama.cpp's own Python quantiser (gguf-py)
+        x = (rng.standard_normal((n_blocks, 32)).astype(np.float32) * (sigma * jitter)[:, None])
+        return quantize_rows(x, gtype)
     if gtype == Q8_0:
         qs = rng.integers(-127, 128, size=(n_blocks, 32), dtype=np.int8)
         d = (sigma / 73.3) * jitter
@@ -191,6 +200,9 @@ def quantize_rows(x: np.ndarray, gtype: int) -> np.ndarray:
         return x.astype(np.float32).view(np.uint8).reshape(rows, -1)
     if gtype == F16:
         return x.astype(np.float16).view(np.uint8).reshape(rows, -1)
+    if gtype in LEGACY:
+        import gguf
+        return np.ascontiguousarray(gguf.quants.quantize(np.ascontiguousarray(x, dtype=np.float32), gguf.GGMLQuantizationType(gtype)))
     if gtype == Q8_0:
         b = x.reshape(-1, 32)
         d = np.abs(b).max(axis=1, keepdims=True) / 127.0
@@ -406,7 +418,8 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     vocab = load_vocab(arch.tokenizer, arch.n_vocab, vocab_dir)
     plan = tensor_plan(arch, preset, gain_out)
 
-    ftype = {"f32": 0, "f16": 1, "q8_0": 7, "q4_k_m": 15, "q4_k": 14, "q5_k": 16, "q6_k": 18, "mixed": 15}[preset]
+    ftype = {"f32": 0, "f16": 1, "q8_0": 7, "q4_k_m": 15, "q4_k": 14, "q5_k": 16, "q6_k": 18, "mixed": 15,
+             "q4_0": 2, "q4_1": 3, "q5_0": 8, "q5_1": 9}[preset]  # llama_ftype
     kvs = [
         kv_bytes("general.architecture", T_STR, "llama"),
         kv_bytes("general.name", T_STR, f"{arch.name}-{preset}-random-seed{seed}"),
@@ -493,7 +506,7 @@ def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--arch", required=True, choices=sorted(ARCHS))
     ap.add_argument("--preset", required=True,
-                    choices=["f32", "f16", "q8_0", "q4_k_m", "q4_k", "q5_k", "q6_k", "mixed"])
+                    choices=["f32", "f16", "q8_0", "q4_k_m", "q4_k", "q5_k", "q6_k", "mixed", "q4_0", "q4_1", "q5_0", "q5_1"])
     ap.add_argument("--out", required=True)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--gain-out", type=float, default=4.0, help="output.weight std multiplier (argmax margin)")

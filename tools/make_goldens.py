@@ -80,7 +80,37 @@ def main():
     q = gguf.quants.quantize(x, QT.Q8_0).reshape(-1)
     np.savez_compressed(os.path.join(GOLD, "quant_q8_0.npz"), x=x, blocks=q)
     print("quant_q8_0", x.shape, q.shape)
+    mint_legacy()
+
+
+LEGACY = {"q4_0": (mg.Q4_0, QT.Q4_0), "q4_1": (mg.Q4_1, QT.Q4_1), "q5_0": (mg.Q5_0, QT.Q5_0), "q5_1": (mg.Q5_1, QT.Q5_1)}
+
+
+def mint_legacy():
+    """dequant_{q4_0,q4_1,q5_0,q5_1}.npz: quantised Gaussian data plus raw random bytes (every bit pattern of the
+    quants and high bits) under edge-case scales.  Own random stream, so the files above never change."""
+    rng = np.random.default_rng(4321)
+    f16 = lambda v: np.frombuffer(np.float16(v).tobytes(), dtype=np.uint8)  # noqa: E731
+    for name, (gt, qt) in LEGACY.items():
+        bb = mg.BLOCK[gt][1]
+        blocks = [mg.random_blocks(rng, gt, 48, 0.02)]
+        raw = rng.integers(0, 256, size=(16, bb), dtype=np.uint8)
+        for i, d in enumerate([0.0, -0.0, 6.1e-5, -3.0e-3, 5.96e-8, 1.0, -2.5, 15.99, 0.25, -0.125, 3e-4, 7.0, -1e-2, 0.5, 2.0, -4.0]):
+            raw[i, 0:2] = f16(d)
+            if gt in (mg.Q4_1, mg.Q5_1):
+                raw[i, 2:4] = f16(-d * 3 if i % 2 else d * 0.5)
+            if i == 2:
+                raw[i, -16:] = 0xFF
+            if i == 3:
+                raw[i, -16:] = 0x00
+        blocks.append(raw)
+        blocks = np.concatenate(blocks, axis=0)
+        vals = gguf.quants.dequantize(blocks.reshape(-1), qt).astype(np.float32).reshape(-1)
+        np.savez_compressed(os.path.join(GOLD, f"dequant_{name}.npz"), blocks=blocks, values=vals, ggml_type=gt)
+        print(name, blocks.shape, vals.shape, "finite:", bool(np.isfinite(vals).all()))
 
 
 if __name__ == "__main__":
+    if "--legacy-only" in sys.argv:
+        sys.exit(mint_legacy())
     sys.exit(main())
