@@ -127,6 +127,7 @@ def cpu_sample(path: str, n_prompt: int, n_decode: int):
 
     from oracle import oracle as O
 
+    O.set_num_threads(os.cpu_count() or 1)
     m = O.OracleModel(path, n_ctx=n_prompt + n_decode + 8)
     prompt = (np.arange(n_prompt) * 7919 % 4000 + 3).astype(np.int32)
     t0 = time.time()
@@ -148,6 +149,7 @@ def run_reference(args, rank: int, emit):
 
     from oracle import oracle as O
 
+    O.set_num_threads(os.cpu_count() or 1)  # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1)
     n_prompt = args.ctx  # the same context the GPU arm decodes at
     m = O.OracleModel(path, n_ctx=args.ctx + args.steps + 64)
     prompt = (np.arange(n_prompt) * 7919 % 4000 + 3).astype(np.int32)

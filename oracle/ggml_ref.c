@@ -773,6 +773,15 @@ int ref_generate_greedy(ref_ctx *c, const int32_t *prompt, int n_prompt, int n_g
     return n;
 }
 
+/* launchers such as torchrun export OMP_NUM_THREADS=1; the CPU baseline is meant to use every host core */
+void ref_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int ref_num_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

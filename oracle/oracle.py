@@ -199,6 +199,11 @@ def num_threads() -> int:
     return lib().ref_num_threads()
 
 
+def set_num_threads(n: int) -> None:
+    """Use n OpenMP threads regardless of OMP_NUM_THREADS (torchrun exports OMP_NUM_THREADS=1)."""
+    lib().ref_set_num_threads(int(n))
+
+
 # ---------------------------------------------------------------------------------------------- sampler chain
 # Restatement of the two llama.cpp samplers the engine runs on the device beyond top-k/top-p/min-p (llama.cpp
 # src/llama-sampling.cpp @ d5cb868, un-vendored: llama_sampler_penalties_apply, llama_sampler_mirostat_v2_apply;
