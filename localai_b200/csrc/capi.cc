@@ -355,7 +355,8 @@ int b2_sample(int device, const float *logits, int n_vocab, const b2_sample_para
         rng = rng * 6364136223846793005ULL + 1442695040888963407ULL; // the scheduler's per-token advance
         B2_CUDA(cudaMemcpy(row.p, src.p, (size_t)n_vocab * 4, cudaMemcpyDeviceToDevice));
         B2_CUDA(cudaMemcpy(spec.p, &sp, sizeof(sp), cudaMemcpyHostToDevice));
-        launch_sample(row.as<float>(), n_vocab, 1, n_vocab, spec.as<SampleSpec>(), sp.has_penalties(), tok.as<int32_t>(), mu.as<float>(), 0);
+        launch_sample(row.as<float>(), n_vocab, 1, n_vocab, spec.as<SampleSpec>(), sp.has_penalties(), tok.as<int32_t>(), mu.as<float>(), 0,
+                      sp.temperature <= 0.f);
         B2_CUDA(cudaMemcpy(&out_tokens[i], tok.p, 4, cudaMemcpyDeviceToHost));
         B2_CUDA(cudaMemcpy(&sp.mirostat_mu, mu.p, 4, cudaMemcpyDeviceToHost));
         if (out_mu) out_mu[i] = sp.mirostat_mu;

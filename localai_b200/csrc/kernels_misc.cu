@@ -151,7 +151,9 @@ void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, i
                       const KVLayout &kv, float *out, int max_ctx, cudaStream_t s) {
     if (n_tok <= 0) return;
     B2_CHECK(hd % 32 == 0 && hd <= 256, B2_EUNSUPPORTED, "attention: head_dim must be a multiple of 32, at most 256");
-    if (n_head % n_head_kv == 0 && hd <= 128 && !(getenv("B200LLM_NO_GQA_ATT") && atoi(getenv("B200LLM_NO_GQA_ATT")))) {
+    // B200LLM_NO_GQA_ATT=1 (A/B tests) is read at every call on purpose: the bit-identity test flips it inside one process
+    const char *no_gqa = getenv("B200LLM_NO_GQA_ATT");
+    if (n_head % n_head_kv == 0 && hd <= 128 && !(no_gqa && no_gqa[0] == '1')) {
         const int G = n_head / n_head_kv;
         if (G == 2 && try_launch_attention_group<2>(q, pos, slot, n_tok, n_head, n_head_kv, hd, kv, out, max_ctx, s)) return;
         if (G == 4 && try_launch_attention_group<4>(q, pos, slot, n_tok, n_head, n_head_kv, hd, kv, out, max_ctx, s)) return;

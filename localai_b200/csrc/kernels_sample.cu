@@ -393,15 +393,58 @@ sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, con
     }
 }
 
+// Greedy rows (temperature <= 0) without the single-CTA scan: the row is split over GREEDY_SPLIT CTAs that fold their
+// slice into one 64-bit key (monotone value bits | ~index: max = largest value, smallest index among equals) and merge
+// with atomicMax; the last CTA of the row writes the token and re-zeroes the scratch.  Same result as the greedy
+// branch of sample_kernel (first maximal element, the banned token excluded).
+constexpr int GREEDY_SPLIT = 32;
+constexpr int GREEDY_MAX_ROWS = 4096;
+static __device__ unsigned long long g_greedy_key[GREEDY_MAX_ROWS];
+static __device__ unsigned int g_greedy_done[GREEDY_MAX_ROWS];
+
+__global__ void __launch_bounds__(256)
+greedy_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, const SampleSpec *__restrict__ specs,
+              int32_t *__restrict__ out, float *__restrict__ mu_out) {
+    const int row = blockIdx.y;
+    const SampleSpec &sp = specs[row];
+    const float *x = logits + (int64_t)row * stride;
+    const int per = (n_vocab + GREEDY_SPLIT - 1) / GREEDY_SPLIT;
+    const int i0 = blockIdx.x * per, i1 = min(n_vocab, i0 + per);
+    unsigned long long best = 0ull;
+    for (int i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+        if (i == sp.ban_token) continue;
+        const uint32_t k = float_key(x[i]);
+        if (k != 0u) best = max(best, ((unsigned long long)k << 32) | (uint32_t)(~(uint32_t)i));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+    __shared__ unsigned long long sv[8];
+    if ((threadIdx.x & 31) == 0) sv[threadIdx.x >> 5] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++) best = max(best, sv[w]);
+        atomicMax(&g_greedy_key[row], best);
+        __threadfence();
+        if (atomicAdd(&g_greedy_done[row], 1u) == (unsigned)gridDim.x - 1) {
+            __threadfence();
+            const unsigned long long k = atomicExch(&g_greedy_key[row], 0ull);
+            g_greedy_done[row] = 0u;
+            out[row] = k == 0ull ? 0 : (int)(~(uint32_t)(k & 0xFFFFFFFFull));
+            if (mu_out) mu_out[row] = sp.mirostat_mu;
+        }
+    }
+}
+
 void launch_sample(float *logits, int64_t stride, int n_rows, int n_vocab, const SampleSpec *specs_dev, bool any_penalties,
-                   int32_t *out, float *mu_out, cudaStream_t s) {
+                   int32_t *out, float *mu_out, cudaStream_t s, bool all_greedy) {
     if (n_rows <= 0) return;
     if (any_penalties) {
         penalty_kernel<<<n_rows, SAMPLE_MAX_PREV, 0, s>>>(logits, stride, n_vocab, specs_dev);
         g_launch_count++;
         B2_CUDA(cudaGetLastError());
     }
-    sample_kernel<<<n_rows, SAMPLE_THREADS, 0, s>>>(logits, stride, n_vocab, specs_dev, out, mu_out);
+    if (all_greedy && n_rows <= GREEDY_MAX_ROWS) greedy_kernel<<<dim3(GREEDY_SPLIT, n_rows), 256, 0, s>>>(logits, stride, n_vocab, specs_dev, out, mu_out);
+    else sample_kernel<<<n_rows, SAMPLE_THREADS, 0, s>>>(logits, stride, n_vocab, specs_dev, out, mu_out);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -409,12 +452,15 @@ void launch_sample(float *logits, int64_t stride, int n_rows, int n_vocab, const
 void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_host, float *mu_out_host) {
     const int n = (int)specs.size();
     if (n == 0) return;
-    bool any_pen = false;
-    for (const auto &sp : specs) any_pen |= sp.has_penalties();
+    bool any_pen = false, all_greedy = true;
+    for (const auto &sp : specs) {
+        any_pen |= sp.has_penalties();
+        all_greedy &= sp.temperature <= 0.f;
+    }
     SampleSpec *dev = m.sample_specs_dev(n);
     B2_CUDA(cudaMemcpyAsync(dev, specs.data(), sizeof(SampleSpec) * n, cudaMemcpyHostToDevice, m.stream));
     launch_sample(m.logits_dev_mut(), m.hp.n_vocab, n, m.hp.n_vocab, dev, any_pen, const_cast<int32_t *>(m.next_tok_dev()),
-                  m.sample_mu_dev(), m.stream);
+                  m.sample_mu_dev(), m.stream, all_greedy);
     B2_CUDA(cudaMemcpyAsync(out_host, m.next_tok_dev(), sizeof(int32_t) * n, cudaMemcpyDeviceToHost, m.stream));
     if (mu_out_host) B2_CUDA(cudaMemcpyAsync(mu_out_host, m.sample_mu_dev(), sizeof(float) * n, cudaMemcpyDeviceToHost, m.stream));
 }

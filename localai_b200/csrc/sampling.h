@@ -45,6 +45,6 @@ constexpr int SAMPLE_MAX_CANDIDATES = 1024; // top-k / nucleus candidates kept o
 void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_host, float *mu_out_host = nullptr);
 
 void launch_sample(float *logits, int64_t stride, int n_rows, int n_vocab, const SampleSpec *specs_dev, bool any_penalties,
-                   int32_t *out, float *mu_out, cudaStream_t s);
+                   int32_t *out, float *mu_out, cudaStream_t s, bool all_greedy = false);
 
 } // namespace b2
