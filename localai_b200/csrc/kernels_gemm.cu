@@ -61,6 +61,10 @@ __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, in
                 const float d = h2f(q.d[k0 / 32]);
 #pragma unroll
                 for (int j = 0; j < 8; j++) v[j] = (float)q.qs[k0 + j] * d;
+            } else if (is_small_k_type(type)) {
+                const uint8_t *blk = row + (size_t)(k0 / 256) * (type == 10 ? 84 : 110);
+#pragma unroll
+                for (int j = 0; j < 8; j++) v[j] = dequant_small_k_elem(type, blk, k0 % 256 + j);
             } else if (is_legacy_type(type)) {
                 const uint8_t *blk = row + (size_t)(k0 / 32) * legacy_block_bytes(type);
 #pragma unroll

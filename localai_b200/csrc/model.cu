@@ -31,8 +31,9 @@ DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_r
              "gguf: tensor " + name + " has shape [" + std::to_string(rows) + "," + std::to_string(cols) + "], expected [" +
                  std::to_string(want_rows) + "," + std::to_string(want_cols) + "]");
     if (type_tiles_only(ti->type)) {
-        B2_CHECK(cols % 64 == 0, B2_EUNSUPPORTED, "tensor " + name + ": row length must be a multiple of 64");
-        tiles_only_ = true; // legacy block formats have no integer decode kernel: everything goes through the bf16 tiles
+        B2_CHECK(cols % std::max(64, type_block_elems(ti->type)) == 0, B2_EUNSUPPORTED,
+                 "tensor " + name + ": row length must be a multiple of 64 and of the block size");
+        tiles_only_ = true; // these formats have no integer decode kernel: everything goes through the bf16 tiles
     } else if (ti->type != B2_T_F32 && ti->type != B2_T_F16) {
         B2_CHECK(cols % 256 == 0, B2_EUNSUPPORTED, "tensor " + name + ": quantised row length must be a multiple of 256");
     }
@@ -128,7 +129,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     }
     output_norm = upload(f, "output_norm.weight", 1, d, true);
     B2_CHECK(output_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
-    B2_CHECK(!(tiles_only_ && no_gemm_), B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 weights need the tensor-core path (B200LLM_NO_GEMM is set)");
+    B2_CHECK(!(tiles_only_ && no_gemm_), B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K weights need the tensor-core path (B200LLM_NO_GEMM is set)");
     output = upload(f, "output.weight", hp.n_vocab, d, false);
     if (!output.data) { // tied embeddings
         output = tok_embd;
@@ -368,7 +369,7 @@ void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
 // (measured on Llama-3-8B: 4.3 ms per step for 2..16 streams against 5.4 / 6.9 / 8.5 ms of the integer kernels at 2 / 3 / 4);
 // when the tiles have to be rebuilt on every call the integer kernels keep the small batches.
 int Model::gemm_threshold() const {
-    if (tiles_only_) return 0; // Q4_0 / Q4_1 / Q5_0 / Q5_1 weights: the tensor-core path is the only one, from 1 token on
+    if (tiles_only_) return 0; // Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K weights: the tensor-core path is the only one, from 1 token on
     return gemm_min_tokens_ >= 0 ? gemm_min_tokens_ : (no_shadow_ ? 4 : 1);
 }
 

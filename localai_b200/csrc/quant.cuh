@@ -60,6 +60,29 @@ __device__ __forceinline__ float dequant_legacy_elem(int type, const uint8_t *bl
     return __fadd_rn(__fmul_rn((float)q, d), h2f(*(const uint16_t *)(blk + 2)));
 }
 
+// element e (0..255) of a Q2_K (84 B: scales[16] qs[64] d dmin) or Q3_K (110 B: hmask[32] qs[64] scales[12] d) block in
+// GGUF layout, with dequantize_row_q2_K / q3_K's arithmetic and rounding
+__device__ __forceinline__ bool is_small_k_type(int t) { return t == 10 || t == 11; }
+__device__ __forceinline__ float dequant_small_k_elem(int type, const uint8_t *blk, int e) {
+    const int n = e >> 7, j = (e & 127) >> 5, half = (e & 31) >> 4, l = (e & 15) + 16 * half;
+    const int is = n * 8 + 2 * j + half;
+    if (type == 10) {
+        const uint8_t sc = blk[is];
+        const float d = h2f(*(const uint16_t *)(blk + 80)), mn = h2f(*(const uint16_t *)(blk + 82));
+        const float dl = __fmul_rn(d, (float)(sc & 0xF)), ml = __fmul_rn(mn, (float)(sc >> 4));
+        const int q = (blk[16 + 32 * n + l] >> (2 * j)) & 3;
+        return __fsub_rn(__fmul_rn(dl, (float)q), ml);
+    }
+    // Q3_K: 6-bit scale `is` = 4 low bits from scales[0..7] nibbles, 2 high bits from scales[8..11]
+    const uint8_t *sp = blk + 96;
+    const int lo = is < 8 ? (sp[is] & 0xF) : (sp[is - 8] >> 4);
+    const int hi = (sp[8 + (is & 3)] >> (2 * (is >> 2))) & 3;
+    const int scale = (int)(int8_t)(lo | (hi << 4)) - 32;
+    const float dl = __fmul_rn(h2f(*(const uint16_t *)(blk + 108)), (float)scale);
+    const int q = ((blk[32 + 32 * n + l] >> (2 * j)) & 3) - ((blk[l] & (1 << (4 * n + j))) ? 0 : 4);
+    return __fmul_rn(dl, (float)q);
+}
+
 // one Q6_K row in device layout: nb 208-byte blocks [ql 128][qh 64][scales 16] (16-byte aligned; 13 x 16 B, an odd
 // stride, so lanes that each read a different block of a staged row hit different shared-memory banks), then the nb
 // fp16 super-block scales

@@ -33,7 +33,8 @@
 #define QK_K 256
 #define K_SCALE_SIZE 12
 
-enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q4_K = 12, T_Q5_K = 13,
+enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q2_K = 10, T_Q3_K = 11,
+       T_Q4_K = 12, T_Q5_K = 13,
        T_Q6_K = 14, T_Q8_K = 15 };
 
 typedef uint16_t fp16_t;
@@ -57,6 +58,8 @@ typedef struct { fp16_t d; uint8_t qs[16]; } block_q4_0;                        
 typedef struct { fp16_t d, m; uint8_t qs[16]; } block_q4_1;                                  /* 20 B  */
 typedef struct { fp16_t d; uint8_t qh[4]; uint8_t qs[16]; } block_q5_0;                      /* 22 B  */
 typedef struct { fp16_t d, m; uint8_t qh[4]; uint8_t qs[16]; } block_q5_1;                   /* 24 B  */
+typedef struct { uint8_t scales[QK_K / 16]; uint8_t qs[QK_K / 4]; fp16_t d, dmin; } block_q2_K;     /* 84 B  */
+typedef struct { uint8_t hmask[QK_K / 8]; uint8_t qs[QK_K / 4]; uint8_t scales[12]; fp16_t d; } block_q3_K; /* 110 B */
 typedef struct { fp16_t d, dmin; uint8_t scales[K_SCALE_SIZE]; uint8_t qs[QK_K / 2]; } block_q4_K; /* 144 B */
 typedef struct { fp16_t d, dmin; uint8_t scales[K_SCALE_SIZE]; uint8_t qh[QK_K / 8]; uint8_t qs[QK_K / 2]; } block_q5_K; /* 176 B */
 typedef struct { uint8_t ql[QK_K / 2]; uint8_t qh[QK_K / 4]; int8_t scales[QK_K / 16]; fp16_t d; } block_q6_K; /* 210 B */
@@ -69,6 +72,7 @@ static int64_t type_block(int t) {
 }
 static int64_t type_bytes(int t) {
     switch (t) {
+        case T_Q2_K: return 84; case T_Q3_K: return 110;
         case T_Q4_0: return 18; case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24; case T_Q8_1: return 36;
         case T_F32: return 4; case T_F16: return 2; case T_Q8_0: return 34; case T_Q4_K: return 144;
         case T_Q5_K: return 176; case T_Q6_K: return 210; case T_Q8_K: return 292;
@@ -137,6 +141,62 @@ static void dequantize_row_q5_1(const block_q5_1 *x, float *y, int64_t k) {
             const uint8_t xh_1 = ((qh >> (j + 12))) & 0x10;
             y[i * 32 + j] = ((x[i].qs[j] & 0x0F) | xh_0) * d + m;
             y[i * 32 + j + 16] = ((x[i].qs[j] >> 4) | xh_1) * d + m;
+        }
+    }
+}
+
+/* ggml-quants.c dequantize_row_q2_K / dequantize_row_q3_K */
+static void dequantize_row_q2_K(const block_q2_K *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d = fp16_to_fp32(x[i].d), min = fp16_to_fp32(x[i].dmin);
+        const uint8_t *q = x[i].qs;
+        int is = 0;
+        for (int n = 0; n < QK_K; n += 128) {
+            int shift = 0;
+            for (int j = 0; j < 4; ++j) {
+                uint8_t sc = x[i].scales[is++];
+                float dl = d * (sc & 0xF), ml = min * (sc >> 4);
+                for (int l = 0; l < 16; ++l) *y++ = dl * ((int8_t)((q[l] >> shift) & 3)) - ml;
+                sc = x[i].scales[is++];
+                dl = d * (sc & 0xF);
+                ml = min * (sc >> 4);
+                for (int l = 0; l < 16; ++l) *y++ = dl * ((int8_t)((q[l + 16] >> shift) & 3)) - ml;
+                shift += 2;
+            }
+            q += 32;
+        }
+    }
+}
+static void q3_K_scales(const uint8_t *packed, int8_t scales[16]) {
+    const uint32_t km1 = 0x03030303, km2 = 0x0f0f0f0f;
+    uint32_t aux[4];
+    memcpy(aux, packed, 12);
+    const uint32_t tmp = aux[2];
+    aux[2] = ((aux[0] >> 4) & km2) | (((tmp >> 4) & km1) << 4);
+    aux[3] = ((aux[1] >> 4) & km2) | (((tmp >> 6) & km1) << 4);
+    aux[0] = (aux[0] & km2) | (((tmp >> 0) & km1) << 4);
+    aux[1] = (aux[1] & km2) | (((tmp >> 2) & km1) << 4);
+    memcpy(scales, aux, 16);
+}
+static void dequantize_row_q3_K(const block_q3_K *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d_all = fp16_to_fp32(x[i].d);
+        const uint8_t *q = x[i].qs, *hm = x[i].hmask;
+        uint8_t m = 1;
+        int8_t scales[16];
+        q3_K_scales(x[i].scales, scales);
+        int is = 0;
+        for (int n = 0; n < QK_K; n += 128) {
+            int shift = 0;
+            for (int j = 0; j < 4; ++j) {
+                float dl = d_all * (scales[is++] - 32);
+                for (int l = 0; l < 16; ++l) *y++ = dl * ((int8_t)((q[l + 0] >> shift) & 3) - ((hm[l + 0] & m) ? 0 : 4));
+                dl = d_all * (scales[is++] - 32);
+                for (int l = 0; l < 16; ++l) *y++ = dl * ((int8_t)((q[l + 16] >> shift) & 3) - ((hm[l + 16] & m) ? 0 : 4));
+                shift += 2;
+                m <<= 1;
+            }
+            q += 32;
         }
     }
 }
@@ -217,6 +277,8 @@ void ref_dequantize_row(int type, const void *x, float *y, int64_t k) {
         case T_Q4_1: dequantize_row_q4_1((const block_q4_1 *)x, y, k); break;
         case T_Q5_0: dequantize_row_q5_0((const block_q5_0 *)x, y, k); break;
         case T_Q5_1: dequantize_row_q5_1((const block_q5_1 *)x, y, k); break;
+        case T_Q2_K: dequantize_row_q2_K((const block_q2_K *)x, y, k); break;
+        case T_Q3_K: dequantize_row_q3_K((const block_q3_K *)x, y, k); break;
         case T_Q4_K: dequantize_row_q4_K((const block_q4_K *)x, y, k); break;
         case T_Q5_K: dequantize_row_q5_K((const block_q5_K *)x, y, k); break;
         case T_Q6_K: dequantize_row_q6_K((const block_q6_K *)x, y, k); break;
@@ -412,6 +474,66 @@ static float k4_accumulate(const int8_t *aux8, const uint8_t *packed_scales, con
     return 0;
 }
 
+/* ggml_vec_dot_q2_K_q8_K (generic path) */
+static float vec_dot_q2_K_q8_K(int n, const block_q2_K *x, const block_q8_K *y) {
+    float sumf = 0;
+    for (int i = 0; i < n / QK_K; ++i) {
+        const uint8_t *q2 = x[i].qs, *sc = x[i].scales;
+        const int8_t *q8 = y[i].qs;
+        int summs = 0;
+        for (int j = 0; j < 16; ++j) summs += y[i].bsums[j] * (sc[j] >> 4);
+        const float dall = y[i].d * fp16_to_fp32(x[i].d), dmin = y[i].d * fp16_to_fp32(x[i].dmin);
+        int isum = 0, is = 0;
+        for (int k = 0; k < QK_K / 128; ++k) {
+            int shift = 0;
+            for (int j = 0; j < 4; ++j) {
+                int d = sc[is++] & 0xF, isuml = 0;
+                for (int l = 0; l < 16; ++l) isuml += q8[l] * ((q2[l] >> shift) & 3);
+                isum += d * isuml;
+                d = sc[is++] & 0xF;
+                isuml = 0;
+                for (int l = 16; l < 32; ++l) isuml += q8[l] * ((q2[l] >> shift) & 3);
+                isum += d * isuml;
+                shift += 2;
+                q8 += 32;
+            }
+            q2 += 32;
+        }
+        sumf += dall * isum - dmin * summs;
+    }
+    return sumf;
+}
+/* ggml_vec_dot_q3_K_q8_K: the same integer sums as the generic path; the generic path accumulates them in eight fp32
+ * lanes, here one fp32 product per super-block (this type runs on the bf16 tensor-core path on the device, whose
+ * tolerance is far wider than that re-association) */
+static float vec_dot_q3_K_q8_K(int n, const block_q3_K *x, const block_q8_K *y) {
+    float sumf = 0;
+    for (int i = 0; i < n / QK_K; ++i) {
+        const uint8_t *q = x[i].qs, *hm = x[i].hmask;
+        const int8_t *q8 = y[i].qs;
+        int8_t scales[16];
+        q3_K_scales(x[i].scales, scales);
+        uint8_t m = 1;
+        int isum = 0, is = 0;
+        for (int k = 0; k < QK_K / 128; ++k) {
+            int shift = 0;
+            for (int j = 0; j < 4; ++j) {
+                int s0 = 0, s1 = 0;
+                for (int l = 0; l < 16; ++l) s0 += q8[l] * ((int)((q[l] >> shift) & 3) - ((hm[l] & m) ? 0 : 4));
+                for (int l = 16; l < 32; ++l) s1 += q8[l] * ((int)((q[l] >> shift) & 3) - ((hm[l] & m) ? 0 : 4));
+                isum += (scales[is] - 32) * s0 + (scales[is + 1] - 32) * s1;
+                is += 2;
+                shift += 2;
+                m <<= 1;
+                q8 += 32;
+            }
+            q += 32;
+        }
+        sumf += (fp16_to_fp32(x[i].d) * y[i].d) * isum;
+    }
+    return sumf;
+}
+
 static float vec_dot_q4_K_q8_K(int n, const block_q4_K *x, const block_q8_K *y) {
     int8_t aux8[QK_K];
     float sums[8] = {0};
@@ -539,6 +661,8 @@ float ref_vec_dot(int wtype, int n, const void *w, const void *yq) {
         case T_Q4_1: return vec_dot_q4_1_q8_1(n, (const block_q4_1 *)w, (const block_q8_1 *)yq);
         case T_Q5_0: return vec_dot_q5_0_q8_0(n, (const block_q5_0 *)w, (const block_q8_0 *)yq);
         case T_Q5_1: return vec_dot_q5_1_q8_1(n, (const block_q5_1 *)w, (const block_q8_1 *)yq);
+        case T_Q2_K: return vec_dot_q2_K_q8_K(n, (const block_q2_K *)w, (const block_q8_K *)yq);
+        case T_Q3_K: return vec_dot_q3_K_q8_K(n, (const block_q3_K *)w, (const block_q8_K *)yq);
         case T_Q4_K: return vec_dot_q4_K_q8_K(n, (const block_q4_K *)w, (const block_q8_K *)yq);
         case T_Q5_K: return vec_dot_q5_K_q8_K(n, (const block_q5_K *)w, (const block_q8_K *)yq);
         case T_Q6_K: return vec_dot_q6_K_q8_K(n, (const block_q6_K *)w, (const block_q8_K *)yq);

@@ -39,6 +39,8 @@ def model_files(gguf_dir):
         "mini_f16": ("mini", "f16"),
         "mini_q4_0": ("mini", "q4_0"),
         "mini_q5_1": ("mini", "q5_1"),
+        "mini_q2_k": ("mini", "q2_k"),
+        "mini_q3_k": ("mini", "q3_k"),
     }
     out = {}
     for name, (arch, preset) in specs.items():

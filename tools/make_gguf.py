@@ -34,10 +34,11 @@ ALIGN = 32
 F32, F16, Q8_0, Q4_K, Q5_K, Q6_K = 0, 1, 8, 12, 13, 14
 Q4_0, Q4_1, Q5_0, Q5_1 = 2, 3, 6, 7  # legacy 32-element blocks (tensor-core path only on the device)
 LEGACY = (Q4_0, Q4_1, Q5_0, Q5_1)
+Q2_K, Q3_K = 10, 11  # K-quants without an integer decode kernel on the device (tensor-core path only)
 TYPE_NAMES = {F32: "F32", F16: "F16", Q8_0: "Q8_0", Q4_K: "Q4_K", Q5_K: "Q5_K", Q6_K: "Q6_K", Q4_0: "Q4_0", Q4_1: "Q4_1",
-              Q5_0: "Q5_0", Q5_1: "Q5_1"}
+              Q5_0: "Q5_0", Q5_1: "Q5_1", Q2_K: "Q2_K", Q3_K: "Q3_K"}
 BLOCK = {F32: (1, 4), F16: (1, 2), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), Q4_0: (32, 18),
-         Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24)}
+         Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q2_K: (256, 84), Q3_K: (256, 110)}
 
 # gguf metadata value types
 T_U8, T_I8, T_U16, T_I16, T_U32, T_I32, T_F32, T_BOOL, T_STR, T_ARR, T_U64, T_I64, T_F64 = range(13)
@@ -90,6 +91,12 @@ def tensor_type(preset: str, arch: Arch, name: str, layer: int) -> int:
         return Q8_0
     if preset in ("q4_0", "q4_1", "q5_0", "q5_1"):  # as llama-quantize: the output matrix gets Q6_K
         return Q6_K if name == "output.weight" else {"q4_0": Q4_0, "q4_1": Q4_1, "q5_0": Q5_0, "q5_1": Q5_1}[preset]
+    if preset in ("q2_k", "q3_k"):  # token embeddings and the output matrix keep more bits, as llama-quantize does
+        if name == "output.weight":
+            return Q6_K
+        if name == "token_embd.weight":
+            return Q4_K
+        return Q2_K if preset == "q2_k" else Q3_K
     if preset in ("q4_k", "q5_k", "q6_k"):
         return {"q4_k": Q4_K, "q5_k": Q5_K, "q6_k": Q6_K}[preset]
     if preset == "q4_k_m":
@@ -141,6 +148,15 @@ def random_blocks(rng: np.random.Generator, gtype: int, n_blocks: int, sigma: fl
     if gtype in LEGACY:  # quantise Gaussian data with llama.cpp's own Python quantiser (gguf-py)
         x = (rng.standard_normal((n_blocks, 32)).astype(np.float32) * (sigma * jitter)[:, None])
         return quantize_rows(x, gtype)
+    if gtype == Q2_K:  # scales[16] (scale | min << 4), qs[64], d, dmin: value = d*sc*q - dmin*m, q in 0..3
+        scales = rng.integers(0, 256, size=(n_blocks, 16), dtype=np.uint8)
+        qs = rng.integers(0, 256, size=(n_blocks, 64), dtype=np.uint8)
+        d = (sigma / 11.5) * jitter
+        return np.concatenate([scales, qs, _f16_bytes(d), _f16_bytes(d * 1.5)], axis=1)
+    if gtype == Q3_K:  # hmask[32], qs[64], scales[12] (6-bit, -32), d: value = d*(sc-32)*q, q in -4..3
+        body = rng.integers(0, 256, size=(n_blocks, 108), dtype=np.uint8)
+        d = (sigma / 43.0) * jitter
+        return np.concatenate([body, _f16_bytes(d)], axis=1)
     if gtype == Q8_0:
         qs = rng.integers(-127, 128, size=(n_blocks, 32), dtype=np.int8)
         d = (sigma / 73.3) * jitter
@@ -419,7 +435,7 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     plan = tensor_plan(arch, preset, gain_out)
 
     ftype = {"f32": 0, "f16": 1, "q8_0": 7, "q4_k_m": 15, "q4_k": 14, "q5_k": 16, "q6_k": 18, "mixed": 15,
-             "q4_0": 2, "q4_1": 3, "q5_0": 8, "q5_1": 9}[preset]  # llama_ftype
+             "q4_0": 2, "q4_1": 3, "q5_0": 8, "q5_1": 9, "q2_k": 10, "q3_k": 12}[preset]  # llama_ftype
     kvs = [
         kv_bytes("general.architecture", T_STR, "llama"),
         kv_bytes("general.name", T_STR, f"{arch.name}-{preset}-random-seed{seed}"),
@@ -506,7 +522,7 @@ def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--arch", required=True, choices=sorted(ARCHS))
     ap.add_argument("--preset", required=True,
-                    choices=["f32", "f16", "q8_0", "q4_k_m", "q4_k", "q5_k", "q6_k", "mixed", "q4_0", "q4_1", "q5_0", "q5_1"])
+                    choices=["f32", "f16", "q8_0", "q4_k_m", "q4_k", "q5_k", "q6_k", "mixed", "q4_0", "q4_1", "q5_0", "q5_1", "q2_k", "q3_k"])
     ap.add_argument("--out", required=True)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--gain-out", type=float, default=4.0, help="output.weight std multiplier (argmax margin)")

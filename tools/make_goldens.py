@@ -81,6 +81,7 @@ def main():
     np.savez_compressed(os.path.join(GOLD, "quant_q8_0.npz"), x=x, blocks=q)
     print("quant_q8_0", x.shape, q.shape)
     mint_legacy()
+    mint_small_k()
 
 
 LEGACY = {"q4_0": (mg.Q4_0, QT.Q4_0), "q4_1": (mg.Q4_1, QT.Q4_1), "q5_0": (mg.Q5_0, QT.Q5_0), "q5_1": (mg.Q5_1, QT.Q5_1)}
@@ -110,7 +111,36 @@ def mint_legacy():
         print(name, blocks.shape, vals.shape, "finite:", bool(np.isfinite(vals).all()))
 
 
+def mint_small_k():
+    """dequant_{q2_k,q3_k}.npz: random blocks plus raw random bytes under edge-case super-block scales."""
+    rng = np.random.default_rng(987)
+    f16 = lambda v: np.frombuffer(np.float16(v).tobytes(), dtype=np.uint8)  # noqa: E731
+    for name, gt, qt in (("q2_k", mg.Q2_K, QT.Q2_K), ("q3_k", mg.Q3_K, QT.Q3_K)):
+        bb = mg.BLOCK[gt][1]
+        raw = rng.integers(0, 256, size=(8, bb), dtype=np.uint8)
+        for i, d in enumerate([0.0, -0.0, 6.1e-5, -3.0e-3, 5.96e-8, 1.0, -2.5, 0.25]):
+            if gt == mg.Q2_K:
+                raw[i, 80:82] = f16(d)
+                raw[i, 82:84] = f16(-d * 3 if i % 2 else d * 0.5)
+                if i == 2:
+                    raw[i, 0:80] = 0xFF
+                if i == 3:
+                    raw[i, 0:80] = 0x00
+            else:
+                raw[i, 108:110] = f16(d)
+                if i == 2:
+                    raw[i, 0:108] = 0xFF
+                if i == 3:
+                    raw[i, 0:108] = 0x00
+        blocks = np.concatenate([mg.random_blocks(rng, gt, 24, 0.02), raw], axis=0)
+        vals = gguf.quants.dequantize(blocks.reshape(-1), qt).astype(np.float32).reshape(-1)
+        np.savez_compressed(os.path.join(GOLD, f"dequant_{name}.npz"), blocks=blocks, values=vals, ggml_type=gt)
+        print(name, blocks.shape, vals.shape, "finite:", bool(np.isfinite(vals).all()))
+
+
 if __name__ == "__main__":
+    if "--small-k-only" in sys.argv:
+        sys.exit(mint_small_k())
     if "--legacy-only" in sys.argv:
         sys.exit(mint_legacy())
     sys.exit(main())
