@@ -135,6 +135,9 @@ typedef struct {
     float typical_p;           /* TypicalP: 0 or >= 1 = off (with typical-p on, at most the 256 most probable tokens are considered) */
     float tfs_z;               /* TailFreeSamplingZ: 0 or >= 1 = off */
     int32_t reserved[3];
+    const char *grammar;       /* Grammar: GBNF text, NUL-terminated (NULL or "" = none).  The sampled token is checked
+                                  against it; when it does not fit, the row is re-sampled under a vocabulary mask
+                                  (grpc-server.cpp:655,2114).  A text that does not parse fails b2_submit (B2_EINVAL). */
 } b2_request;
 
 enum {
@@ -214,6 +217,15 @@ typedef struct {
     int32_t n_prev;
     float tfs_z, typical_p; /* 0 or >= 1 = off */
 } b2_sample_params;
+/* Grammar matcher alone (host only, no device needed).  b2_grammar_match parses `gbnf` and feeds `text` one code point
+ * at a time: *n_accepted = bytes taken before the first code point that does not fit, *can_stop = 1 if the accepted
+ * text is a complete sentence of the grammar.  b2_grammar_token_mask: after `accepted`, bit t of mask_bits
+ * ((n_vocab + 31) / 32 words) = piece t may come next (end-of-generation pieces only where the grammar may stop).
+ * A grammar that does not parse: B2_EINVAL, reason in b2_last_error.  Replaces llama_grammar_parse / _apply / _accept
+ * behind gpt_sampler_init / _sample / _accept (grpc-server.cpp:890,1946,1948). */
+int b2_grammar_match(const char *gbnf, const char *text, size_t text_len, size_t *n_accepted, int *can_stop);
+int b2_grammar_token_mask(const char *gbnf, const char *accepted, size_t accepted_len, const char *const *pieces, const size_t *piece_len,
+                          const uint8_t *is_eog, int n_vocab, uint32_t *mask_bits);
 int b2_sample(int device, const float *logits, int n_vocab, const b2_sample_params *p, int n_draws, int32_t *out_tokens, float *out_mu);
 
 /* Device-resident benchmark legs (inputs already in HBM, timed with CUDA events on the engine's stream).

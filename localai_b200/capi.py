@@ -25,7 +25,7 @@ EXPORTS = [
     "b2_abi_version", "b2_last_error", "b2_device_count", "b2_create", "b2_destroy", "b2_model_info", "b2_tokenize",
     "b2_token_to_piece", "b2_submit", "b2_poll", "b2_cancel", "b2_embed_result", "b2_release", "b2_metrics", "b2_eval",
     "b2_decode_greedy", "b2_debug_hidden", "b2_bench_decode", "b2_bench_prefill", "b2_bench_gemv", "b2_dequantize", "b2_quantize_act",
-    "b2_mul_mat", "b2_mul_mat_noalloc", "b2_sample",
+    "b2_mul_mat", "b2_mul_mat_noalloc", "b2_sample", "b2_grammar_match", "b2_grammar_token_mask",
 ]
 
 
@@ -63,7 +63,7 @@ class Request(C.Structure):
         ("n_keep", C.c_int32), ("embedding_mode", C.c_int32), ("stop", C.POINTER(C.c_char_p)),
         ("stop_len", C.POINTER(C.c_size_t)), ("n_stop", C.c_int32), ("stream", C.c_int32),
         ("mirostat", C.c_int32), ("mirostat_tau", C.c_float), ("mirostat_eta", C.c_float), ("typical_p", C.c_float),
-        ("tfs_z", C.c_float), ("reserved", C.c_int32 * 3),
+        ("tfs_z", C.c_float), ("reserved", C.c_int32 * 3), ("grammar", C.c_char_p),
     ]
 
 
@@ -133,8 +133,32 @@ def lib() -> C.CDLL:
     L.b2_mul_mat.argtypes = [i32, vp, i64, i64, vp, i32, vp, i32]
     L.b2_mul_mat_noalloc.argtypes = [i32, vp, i64, i64, vp, i32, vp, vp]
     L.b2_sample.argtypes = [i32, vp, i32, C.POINTER(SampleParams), i32, vp, vp]
+    L.b2_grammar_match.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_int)]
+    L.b2_grammar_token_mask.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), vp, i32, vp]
     _lib = L
     return L
+
+
+def grammar_match(gbnf: str | bytes, text: str | bytes):
+    """b2_grammar_match -> (bytes of `text` accepted, grammar may stop there).  Raises on a grammar that does not parse."""
+    g = gbnf.encode("utf-8") if isinstance(gbnf, str) else bytes(gbnf)
+    t = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+    n, stop = C.c_size_t(0), C.c_int(0)
+    _check(lib().b2_grammar_match(g, t, len(t), C.byref(n), C.byref(stop)))
+    return int(n.value), bool(stop.value)
+
+
+def grammar_token_mask(gbnf: str | bytes, accepted: str | bytes, pieces: Sequence[bytes], is_eog: Sequence[bool] | None = None):
+    """b2_grammar_token_mask -> bool[n_vocab]: which pieces may follow `accepted`."""
+    g = gbnf.encode("utf-8") if isinstance(gbnf, str) else bytes(gbnf)
+    a = accepted.encode("utf-8") if isinstance(accepted, str) else bytes(accepted)
+    n = len(pieces)
+    arr = (C.c_char_p * n)(*[bytes(p) for p in pieces])
+    lens = (C.c_size_t * n)(*[len(p) for p in pieces])
+    eog = np.ascontiguousarray(is_eog if is_eog is not None else np.zeros(n), dtype=np.uint8)
+    bits = np.zeros((n + 31) // 32, dtype=np.uint32)
+    _check(lib().b2_grammar_token_mask(g, a, len(a), arr, lens, eog.ctypes.data, n, bits.ctypes.data))
+    return ((bits[np.arange(n) >> 5] >> (np.arange(n) & 31).astype(np.uint32)) & 1).astype(bool)
 
 
 def _check(rc: int) -> int:
@@ -303,7 +327,7 @@ class Engine:
                ignore_eos: bool = False, cache_prompt: bool = False, n_keep: int = 0, embedding_mode: bool = False,
                stop: Sequence[str | bytes] = (), stream: bool = True, repeat_penalty: float = 1.0, repeat_last_n: int = 64,
                frequency_penalty: float = 0.0, presence_penalty: float = 0.0, mirostat: int = 0, mirostat_tau: float = 5.0,
-               mirostat_eta: float = 0.1, typical_p: float = 1.0, tfs_z: float = 1.0) -> int:
+               mirostat_eta: float = 0.1, typical_p: float = 1.0, tfs_z: float = 1.0, grammar: str | bytes | None = None) -> int:
         r = Request()
         r.struct_size = C.sizeof(Request)
         keep = []
@@ -322,6 +346,10 @@ class Engine:
         r.mirostat, r.mirostat_tau, r.mirostat_eta, r.typical_p, r.tfs_z = mirostat, mirostat_tau, mirostat_eta, typical_p, tfs_z
         r.ignore_eos, r.cache_prompt, r.n_keep = int(ignore_eos), int(cache_prompt), n_keep
         r.embedding_mode, r.stream = int(embedding_mode), int(stream)
+        if grammar:
+            g = grammar.encode("utf-8") if isinstance(grammar, str) else bytes(grammar)
+            r.grammar = g
+            keep.append(g)
         if stop:
             bs = [s.encode("utf-8") if isinstance(s, str) else bytes(s) for s in stop]
             arr = (C.c_char_p * len(bs))(*bs)

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "engine.h"
+#include "grammar.h"
 #include "kernels.h"
 #include "sampling.h"
 #include "model.h"
@@ -328,6 +329,47 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     }
     B2_CUDA(cudaMemcpy(out, dout.p, (size_t)n_tok * rows * 4, cudaMemcpyDeviceToHost));
     return 0;
+    B2_API_END(0)
+}
+
+int b2_grammar_match(const char *gbnf, const char *text, size_t text_len, size_t *n_accepted, int *can_stop) {
+    B2_API_BEGIN
+    B2_CHECK(gbnf && (text || text_len == 0), B2_EINVAL, "b2_grammar_match: bad arguments");
+    Grammar g(grammar_parse(gbnf));
+    size_t i = 0;
+    while (i < text_len) { // one code point at a time, so that the count stops at the first one that does not fit
+        size_t n = 1;
+        while (i + n < text_len && ((uint8_t)text[i + n] >> 6) == 2) n++;
+        if (!g.accept_bytes(std::string(text + i, n))) break;
+        i += n;
+    }
+    if (n_accepted) *n_accepted = i;
+    if (can_stop) *can_stop = g.can_stop() ? 1 : 0;
+    return B2_OK;
+    B2_API_END(0)
+}
+
+int b2_grammar_token_mask(const char *gbnf, const char *accepted, size_t accepted_len, const char *const *pieces, const size_t *piece_len,
+                          const uint8_t *is_eog, int n_vocab, uint32_t *mask_bits) {
+    B2_API_BEGIN
+    B2_CHECK(gbnf && pieces && piece_len && mask_bits && n_vocab > 0, B2_EINVAL, "b2_grammar_token_mask: bad arguments");
+    Grammar g(grammar_parse(gbnf));
+    B2_CHECK(accepted_len == 0 || g.accept_bytes(std::string(accepted, accepted_len)), B2_EINVAL,
+             "b2_grammar_token_mask: the accepted text does not fit the grammar");
+    GrammarVocab v;
+    v.cps.resize(n_vocab); v.tails.resize(n_vocab); v.is_eog.resize(n_vocab); v.is_empty.resize(n_vocab); v.pieces.resize(n_vocab);
+    for (int t = 0; t < n_vocab; t++) {
+        v.pieces[t].assign(pieces[t] ? pieces[t] : "", pieces[t] ? piece_len[t] : 0);
+        v.is_eog[t] = is_eog ? is_eog[t] : 0;
+        v.is_empty[t] = v.pieces[t].empty() || v.pieces[t][0] == '\0';
+        Utf8Tail tail;
+        utf8_decode_piece(v.pieces[t], tail, v.cps[t]);
+        v.tails[t] = tail;
+    }
+    g.token_mask(v, mask_bits);
+    for (int t = 0; t < n_vocab; t++) // the single-candidate check must agree with the mask
+        B2_CHECK(g.token_fits(v, t) == (bool)((mask_bits[t >> 5] >> (t & 31)) & 1u), B2_ESTATE, "b2_grammar_token_mask: mask and check disagree");
+    return B2_OK;
     B2_API_END(0)
 }
 

@@ -449,6 +449,33 @@ void launch_sample(float *logits, int64_t stride, int n_rows, int n_vocab, const
     B2_CUDA(cudaGetLastError());
 }
 
+// logits of the tokens whose bit is clear go to -inf (the grammar leg of the resample, see grammar.h)
+__global__ void token_mask_kernel(float *__restrict__ logits, int n_vocab, const uint32_t *__restrict__ bits) {
+    const int w = blockIdx.x * blockDim.x + threadIdx.x; // one 32-token word per thread
+    if (w * 32 >= n_vocab) return;
+    const uint32_t b = bits[w];
+    if (b == 0xFFFFFFFFu) return;
+    const int n = min(32, n_vocab - w * 32);
+    for (int i = 0; i < n; i++)
+        if (!((b >> i) & 1u)) logits[w * 32 + i] = -INFINITY;
+}
+
+void resample_row_masked(Model &m, int row, const SampleSpec &spec, const uint32_t *mask_host, int32_t *out_host, float *mu_out_host) {
+    const int n_vocab = m.hp.n_vocab, n_words = (n_vocab + 31) / 32;
+    uint32_t *bits = m.token_mask_dev();
+    B2_CUDA(cudaMemcpyAsync(bits, mask_host, sizeof(uint32_t) * n_words, cudaMemcpyHostToDevice, m.stream));
+    float *logits = m.logits_dev_mut() + (size_t)row * n_vocab;
+    token_mask_kernel<<<(n_words + 255) / 256, 256, 0, m.stream>>>(logits, n_vocab, bits);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+    SampleSpec *dev = m.sample_specs_dev(row + 1) + row;
+    B2_CUDA(cudaMemcpyAsync(dev, &spec, sizeof(SampleSpec), cudaMemcpyHostToDevice, m.stream));
+    int32_t *out = const_cast<int32_t *>(m.next_tok_dev()) + row;
+    launch_sample(logits, n_vocab, 1, n_vocab, dev, false, out, m.sample_mu_dev() + row, m.stream, spec.temperature <= 0.f);
+    B2_CUDA(cudaMemcpyAsync(out_host, out, sizeof(int32_t), cudaMemcpyDeviceToHost, m.stream));
+    if (mu_out_host) B2_CUDA(cudaMemcpyAsync(mu_out_host, m.sample_mu_dev() + row, sizeof(float), cudaMemcpyDeviceToHost, m.stream));
+}
+
 void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_host, float *mu_out_host) {
     const int n = (int)specs.size();
     if (n == 0) return;

@@ -236,6 +236,11 @@ SampleSpec *Model::sample_specs_dev(int n) {
     return sample_specs_;
 }
 
+uint32_t *Model::token_mask_dev() {
+    if (!token_mask_) token_mask_ = (uint32_t *)dalloc((size_t)((hp.n_vocab + 31) / 32) * 4);
+    return token_mask_;
+}
+
 void Model::enable_debug_hidden() {
     if (!dbg_hidden_) dbg_hidden_ = (float *)dalloc((size_t)(hp.n_layer + 1) * hp.n_embd * 4);
 }

@@ -61,6 +61,7 @@ class Model {
     const int32_t *next_tok_dev() const { return next_tok_; }
     float *debug_hidden_dev() { return dbg_hidden_; }
     SampleSpec *sample_specs_dev(int n);
+    uint32_t *token_mask_dev(); // (n_vocab + 31) / 32 words, allocated on first use (grammar resample)
     void enable_debug_hidden();
     int bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type);
 
@@ -143,6 +144,7 @@ class Model {
     int logits_rows_cap_ = 0;
     SampleSpec *sample_specs_ = nullptr;
     float *sample_mu_ = nullptr;
+    uint32_t *token_mask_ = nullptr;
     void ensure_logits_rows(int n);
     void invalidate_acts();
 };

@@ -44,6 +44,12 @@ constexpr int SAMPLE_MAX_CANDIDATES = 1024; // top-k / nucleus candidates kept o
 // NOTE: rows with penalties have their logits modified in place.
 void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_host, float *mu_out_host = nullptr);
 
+// Grammar resample of ONE row of the same logits: tokens whose bit in `mask_host` ((n_vocab + 31) / 32 words) is clear
+// are set to -inf in place, then the row is sampled again with `spec` (penalties are NOT applied a second time: the
+// first draw already modified the row).  Asynchronous on m.stream like sample_rows.
+void resample_row_masked(Model &m, int row, const SampleSpec &spec, const uint32_t *mask_host, int32_t *out_host,
+                         float *mu_out_host = nullptr);
+
 void launch_sample(float *logits, int64_t stride, int n_rows, int n_vocab, const SampleSpec *specs_dev, bool any_penalties,
                    int32_t *out, float *mu_out, cudaStream_t s, bool all_greedy = false);
 

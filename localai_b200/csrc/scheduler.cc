@@ -73,6 +73,8 @@ int64_t Scheduler::submit(const b2_request &r) {
     q->embedding_mode = r.embedding_mode != 0;
     q->stream = r.stream != 0;
     if (q->embedding_mode) q->n_predict = 0;
+    if (r.struct_size >= offsetof(b2_request, grammar) + sizeof(r.grammar) && r.grammar && r.grammar[0] && !q->embedding_mode)
+        q->grammar = grammar_parse(r.grammar); // throws B2_EINVAL: the caller gets the parse error, nothing is queued
     for (int i = 0; i < r.n_stop; i++) {
         if (!r.stop || !r.stop[i]) continue;
         const size_t n = r.stop_len ? r.stop_len[i] : strlen(r.stop[i]);
@@ -198,6 +200,29 @@ Scheduler::Slot *Scheduler::get_free_slot() {
     return best;
 }
 
+const GrammarVocab &Scheduler::grammar_vocab() {
+    if (!grammar_vocab_) { // pieces as llama_grammar_apply sees them: special tokens rendered, end-of-generation apart
+        const Tokenizer &tk = *eng_->tokenizer();
+        auto v = std::make_unique<GrammarVocab>();
+        const int n = tk.n_vocab();
+        v->cps.resize(n);
+        v->tails.resize(n);
+        v->is_eog.resize(n);
+        v->is_empty.resize(n);
+        v->pieces.resize(n);
+        for (int t = 0; t < n; t++) {
+            v->pieces[t] = tk.token_to_piece(t, true);
+            v->is_eog[t] = tk.is_eog(t);
+            v->is_empty[t] = v->pieces[t].empty() || v->pieces[t][0] == '\0';
+            Utf8Tail tail;
+            utf8_decode_piece(v->pieces[t], tail, v->cps[t]);
+            v->tails[t] = tail;
+        }
+        grammar_vocab_ = std::move(v);
+    }
+    return *grammar_vocab_;
+}
+
 bool Scheduler::has_budget(const Slot &s) const { // grpc-server.cpp:260-278
     if (s.req->n_predict == -1) return true;
     return s.req->n_predict - s.n_decoded > 0;
@@ -216,6 +241,8 @@ void Scheduler::launch_slot(Slot &s, std::shared_ptr<Request> r) {
     s.t_start_prompt = clk::now();
     s.t_prompt_ms = s.t_gen_ms = 0;
     s.mirostat_mu = 2.f * r->mirostat_tau; // llama_sampler_init_mirostat_v2: mu = 2 * tau
+    s.grammar.reset(r->grammar ? new Grammar(r->grammar) : nullptr); // the prompt is not run through it (grpc-server.cpp:1734)
+    s.mask_cache.clear();
     s.rng_state = r->seed < 0 ? (uint64_t)std::chrono::high_resolution_clock::now().time_since_epoch().count() : (uint64_t)(uint32_t)r->seed;
     // tokenize (BOS iff the vocabulary asks for it; special tokens parsed: grpc-server.cpp:564,1689)
     std::vector<int32_t> toks;
@@ -489,6 +516,30 @@ bool Scheduler::step() {
         std::vector<float> mu_new(specs.size());
         sample_rows(m, specs, sampled.data(), mu_new.data());
         m.sync();
+        // grammar: keep the draw if it fits, else mask the vocabulary and draw again from the same logits -- the order
+        // gpt_sampler_sample uses (grpc-server.cpp:1946), so an unconstrained step costs one host-side check
+        for (int k = 0; k < n_out; k++) {
+            Slot &s = slots_[out_slot[k]];
+            if (s.state == IDLE || !s.grammar || s.req->embedding_mode) continue;
+            const GrammarVocab &gv = grammar_vocab();
+            if (s.grammar->token_fits(gv, sampled[k])) continue;
+            if (s.mask_cache.size() >= 256) s.mask_cache.clear();
+            auto ins = s.mask_cache.try_emplace(s.grammar->state_key());
+            std::vector<uint32_t> &mask = ins.first->second;
+            if (ins.second) {
+                mask.resize((gv.cps.size() + 31) / 32);
+                s.grammar->token_mask(gv, mask.data());
+            }
+            SampleSpec sp = specs[k];
+            sp.n_prev = 0; // the row already carries the penalties of the first draw
+            sp.mirostat_mu = mu_new[k];
+            sp.rng = s.rng_state;
+            s.rng_state = s.rng_state * 6364136223846793005ULL + 1442695040888963407ULL;
+            resample_row_masked(m, k, sp, mask.data(), &sampled[k], &mu_new[k]);
+            m.sync();
+            if (!s.grammar->token_fits(gv, sampled[k])) // nothing fits (dead end, or only EOS fits and it is banned): stop
+                sampled[k] = eng_->tokenizer()->eos_id();
+        }
         {
             std::lock_guard<std::mutex> lk(metrics_mu_);
             metrics_.n_decode_steps++;
@@ -528,6 +579,7 @@ bool Scheduler::step() {
                 s.t_prompt_ms = ms_since(s.t_start_prompt);
             }
             s.cache_tokens.push_back(id);
+            if (s.grammar && s.grammar->token_fits(grammar_vocab(), id)) s.grammar->accept_token(grammar_vocab(), id);
             if (!process_token(s, id)) finish_slot(s);
         }
     }

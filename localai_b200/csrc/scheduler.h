@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "common.h"
+#include "grammar.h"
 
 namespace b2 {
 
@@ -41,6 +42,7 @@ struct Request {
     float mirostat_tau = 5.f, mirostat_eta = 0.1f, typical_p = 1.f, tfs_z = 1.f;
     bool ignore_eos = false, cache_prompt = false, embedding_mode = false, stream = true;
     std::vector<std::string> stop;
+    std::shared_ptr<const GrammarRules> grammar; // parsed at submit; null = unconstrained
     // results
     std::mutex mu;
     std::condition_variable cv;
@@ -80,6 +82,10 @@ class Scheduler {
         double t_prompt_ms = 0, t_gen_ms = 0;
         uint64_t rng_state = 0;
         float mirostat_mu = 10.f; // mirostat state of the request in the slot (2 * tau at launch)
+        std::unique_ptr<Grammar> grammar; // matcher state of the request in the slot
+        // token masks by matcher state: inside a JSON string, between digits ... the same state comes back token after
+        // token, and a mask costs one pass over the vocabulary
+        std::map<std::string, std::vector<uint32_t>> mask_cache;
     };
 
     void loop();
@@ -90,6 +96,7 @@ class Scheduler {
     void finish_slot(Slot &s, bool error = false, const std::string &msg = "");
     void push_event(Request &r, EventData &&ev);
     bool has_budget(const Slot &s) const;
+    const GrammarVocab &grammar_vocab();
 
     Engine *eng_;
     std::thread thread_;
@@ -100,6 +107,7 @@ class Scheduler {
     std::vector<Slot> slots_;
     bool stop_ = false;
     int64_t next_id_ = 1;
+    std::unique_ptr<GrammarVocab> grammar_vocab_; // built on the first grammar request (engine thread only)
     // metrics
     std::mutex metrics_mu_;
     b2_metrics_t metrics_{};
