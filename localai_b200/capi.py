@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("B200LLM_LIB", os.path.join(_HERE, "lib", "libb200llm.
 
 B2_T_F32, B2_T_F16, B2_T_Q8_0, B2_T_Q4_K, B2_T_Q5_K, B2_T_Q6_K = 0, 1, 8, 12, 13, 14
 B2_T_Q4_0, B2_T_Q4_1, B2_T_Q5_0, B2_T_Q5_1, B2_T_Q2_K, B2_T_Q3_K = 2, 3, 6, 7, 10, 11  # tensor-core path only
+B2_T_IQ4_NL, B2_T_IQ4_XS = 20, 23  # likewise
 B2_ETIMEOUT = -8
 B2_EUNSUPPORTED = -9
 EV_FINAL, EV_STOP_EOS, EV_STOP_WORD, EV_STOP_LIMIT, EV_ERROR, EV_EMBEDDING = 1, 2, 4, 8, 16, 32

@@ -282,7 +282,7 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     B2_CHECK(type_block_elems(wtype) > 0, B2_EUNSUPPORTED, "unsupported ggml type");
     B2_CHECK(rows > 0 && cols > 0 && n_tok > 0 && cols % (type_tiles_only(wtype) ? std::max(64, type_block_elems(wtype)) : 256) == 0, B2_EINVAL,
              "bad shape (cols must be a multiple of 256; 64 for the legacy 32-element block types)");
-    B2_CHECK(!type_tiles_only(wtype) || path == 2, B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K run on the tensor-core path (2) only");
+    B2_CHECK(!type_tiles_only(wtype) || path == 2, B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K / IQ4_NL / IQ4_XS run on the tensor-core path (2) only");
     B2_CHECK(path >= 0 && path <= 5, B2_EUNSUPPORTED, "unknown mat-mul path");
     DevBuf staging((size_t)(rows * gguf_row_bytes(wtype, cols))), dst((size_t)(rows * device_row_stride(wtype, cols)));
     DTensor W = upload_matrix(wtype, blocks, rows, cols, staging, dst);

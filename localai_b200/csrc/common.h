@@ -51,8 +51,8 @@ inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 inline int type_block_elems(int t) {
     switch (t) {
         case B2_T_F32: case B2_T_F16: return 1;
-        case B2_T_Q8_0: case B2_T_Q4_0: case B2_T_Q4_1: case B2_T_Q5_0: case B2_T_Q5_1: return 32;
-        case B2_T_Q4_K: case B2_T_Q5_K: case B2_T_Q6_K: case B2_T_Q2_K: case B2_T_Q3_K: return 256;
+        case B2_T_Q8_0: case B2_T_Q4_0: case B2_T_Q4_1: case B2_T_Q5_0: case B2_T_Q5_1: case B2_T_IQ4_NL: return 32;
+        case B2_T_Q4_K: case B2_T_Q5_K: case B2_T_Q6_K: case B2_T_Q2_K: case B2_T_Q3_K: case B2_T_IQ4_XS: return 256;
     }
     return 0;
 }
@@ -60,7 +60,7 @@ inline int type_block_bytes(int t) {
     switch (t) {
         case B2_T_F32: return 4; case B2_T_F16: return 2; case B2_T_Q8_0: return 34;
         case B2_T_Q4_0: return 18; case B2_T_Q4_1: return 20; case B2_T_Q5_0: return 22; case B2_T_Q5_1: return 24;
-        case B2_T_Q2_K: return 84; case B2_T_Q3_K: return 110;
+        case B2_T_Q2_K: return 84; case B2_T_Q3_K: return 110; case B2_T_IQ4_NL: return 18; case B2_T_IQ4_XS: return 136;
         case B2_T_Q4_K: return 144; case B2_T_Q5_K: return 176; case B2_T_Q6_K: return 210;
     }
     return 0;
@@ -72,7 +72,8 @@ inline int64_t device_row_stride(int t, int64_t cols) { return align_up(gguf_row
 
 // formats without an integer decode kernel: tensor-core path (bf16 tiles) only
 inline bool type_tiles_only(int t) {
-    return t == B2_T_Q4_0 || t == B2_T_Q4_1 || t == B2_T_Q5_0 || t == B2_T_Q5_1 || t == B2_T_Q2_K || t == B2_T_Q3_K;
+    return t == B2_T_Q4_0 || t == B2_T_Q4_1 || t == B2_T_Q5_0 || t == B2_T_Q5_1 || t == B2_T_Q2_K || t == B2_T_Q3_K ||
+           t == B2_T_IQ4_NL || t == B2_T_IQ4_XS;
 }
 
 // activation formats (what llama.cpp converts src1 to before the dot: ggml type_traits.vec_dot_type)

@@ -62,7 +62,7 @@ __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, in
 #pragma unroll
                 for (int j = 0; j < 8; j++) v[j] = (float)q.qs[k0 + j] * d;
             } else if (is_small_k_type(type)) {
-                const uint8_t *blk = row + (size_t)(k0 / 256) * (type == 10 ? 84 : 110);
+                const uint8_t *blk = row + (size_t)(k0 / 256) * small_k_block_bytes(type);
 #pragma unroll
                 for (int j = 0; j < 8; j++) v[j] = dequant_small_k_elem(type, blk, k0 % 256 + j);
             } else if (is_legacy_type(type)) {

@@ -99,7 +99,7 @@ __global__ void dequant_rows_kernel(const uint8_t *__restrict__ W, int type, int
             const int8_t *qs = q.qs + grp * 32;
             for (int l = 0; l < 32; l++) y[l] = __fmul_rn((float)qs[l], d);
         } else if (is_small_k_type(type)) {
-            const uint8_t *blk = row + (grp / 8) * (type == 10 ? 84 : 110);
+            const uint8_t *blk = row + (grp / 8) * small_k_block_bytes(type);
             for (int l = 0; l < 32; l++) y[l] = dequant_small_k_elem(type, blk, (int)(grp % 8) * 32 + l);
         } else if (is_legacy_type(type)) {
             const uint8_t *blk = row + grp * legacy_block_bytes(type);

@@ -129,7 +129,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     }
     output_norm = upload(f, "output_norm.weight", 1, d, true);
     B2_CHECK(output_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
-    B2_CHECK(!(tiles_only_ && no_gemm_), B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K weights need the tensor-core path (B200LLM_NO_GEMM is set)");
+    B2_CHECK(!(tiles_only_ && no_gemm_), B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K / IQ4 weights need the tensor-core path (B200LLM_NO_GEMM is set)");
     output = upload(f, "output.weight", hp.n_vocab, d, false);
     if (!output.data) { // tied embeddings
         output = tok_embd;
@@ -374,7 +374,7 @@ void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
 // (measured on Llama-3-8B: 4.3 ms per step for 2..16 streams against 5.4 / 6.9 / 8.5 ms of the integer kernels at 2 / 3 / 4);
 // when the tiles have to be rebuilt on every call the integer kernels keep the small batches.
 int Model::gemm_threshold() const {
-    if (tiles_only_) return 0; // Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K weights: the tensor-core path is the only one, from 1 token on
+    if (tiles_only_) return 0; // Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K / IQ4 weights: the tensor-core path is the only one, from 1 token on
     return gemm_min_tokens_ >= 0 ? gemm_min_tokens_ : (no_shadow_ ? 4 : 1);
 }
 

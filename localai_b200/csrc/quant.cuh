@@ -36,8 +36,14 @@ __device__ __forceinline__ void get_scale_min_k4_w(int j, uint32_t w0, uint32_t 
     }
 }
 
-__device__ __forceinline__ bool is_legacy_type(int t) { return t == 2 || t == 3 || t == 6 || t == 7; } // Q4_0 Q4_1 Q5_0 Q5_1
-__device__ __forceinline__ int legacy_block_bytes(int t) { return t == 2 ? 18 : t == 3 ? 20 : t == 6 ? 22 : 24; }
+// the 16 levels of IQ4_NL / IQ4_XS (ggml-quants.c kvalues_iq4nl), packed one per byte
+__device__ __forceinline__ int iq4nl_value(int idx) {
+    const unsigned long long t = idx < 8 ? 0xF6EADDCFBFAD9881ull : 0x7159453526190D01ull;
+    return (int)(int8_t)(t >> (8 * (idx & 7)));
+}
+// 32-element blocks: Q4_0 Q4_1 Q5_0 Q5_1 IQ4_NL
+__device__ __forceinline__ bool is_legacy_type(int t) { return t == 2 || t == 3 || t == 6 || t == 7 || t == 20; }
+__device__ __forceinline__ int legacy_block_bytes(int t) { return (t == 2 || t == 20) ? 18 : t == 3 ? 20 : t == 6 ? 22 : 24; }
 // element l (0..31) of a legacy block (GGUF layout, 2-byte aligned), with dequantize_row_q4_0 / q4_1 / q5_0 / q5_1's
 // arithmetic and rounding (unfused multiply / add)
 __device__ __forceinline__ float dequant_legacy_elem(int type, const uint8_t *blk, int l) {
@@ -46,6 +52,10 @@ __device__ __forceinline__ float dequant_legacy_elem(int type, const uint8_t *bl
     if (type == 2 /* Q4_0 */) {
         const uint8_t b = blk[2 + j];
         return __fmul_rn((float)((hi ? (b >> 4) : (b & 0x0F)) - 8), d);
+    }
+    if (type == 20 /* IQ4_NL: d * level[nibble] */) {
+        const uint8_t b = blk[2 + j];
+        return __fmul_rn(d, (float)iq4nl_value(hi ? (b >> 4) : (b & 0x0F)));
     }
     if (type == 3 /* Q4_1 */) {
         const float m = h2f(*(const uint16_t *)(blk + 2));
@@ -62,8 +72,18 @@ __device__ __forceinline__ float dequant_legacy_elem(int type, const uint8_t *bl
 
 // element e (0..255) of a Q2_K (84 B: scales[16] qs[64] d dmin) or Q3_K (110 B: hmask[32] qs[64] scales[12] d) block in
 // GGUF layout, with dequantize_row_q2_K / q3_K's arithmetic and rounding
-__device__ __forceinline__ bool is_small_k_type(int t) { return t == 10 || t == 11; }
+// (also IQ4_XS, 136 B: d, scales_h, scales_l[4], qs[128] -- dequantize_row_iq4_xs)
+__device__ __forceinline__ bool is_small_k_type(int t) { return t == 10 || t == 11 || t == 23; }
+__device__ __forceinline__ int small_k_block_bytes(int t) { return t == 10 ? 84 : t == 11 ? 110 : 136; }
 __device__ __forceinline__ float dequant_small_k_elem(int type, const uint8_t *blk, int e) {
+    if (type == 23) {
+        const int ib = e >> 5, l = e & 31;
+        const uint32_t scales_h = *(const uint16_t *)(blk + 2);
+        const int ls = ((blk[4 + ib / 2] >> (4 * (ib & 1))) & 0xF) | (((scales_h >> (2 * ib)) & 3) << 4);
+        const float dl = __fmul_rn(h2f(*(const uint16_t *)blk), (float)(ls - 32));
+        const uint8_t b = blk[8 + 16 * ib + (l & 15)];
+        return __fmul_rn(dl, (float)iq4nl_value(l < 16 ? (b & 0x0F) : (b >> 4)));
+    }
     const int n = e >> 7, j = (e & 127) >> 5, half = (e & 31) >> 4, l = (e & 15) + 16 * half;
     const int is = n * 8 + 2 * j + half;
     if (type == 10) {

@@ -35,7 +35,7 @@
 
 enum { T_F32 = 0, T_F16 = 1, T_Q4_0 = 2, T_Q4_1 = 3, T_Q5_0 = 6, T_Q5_1 = 7, T_Q8_0 = 8, T_Q8_1 = 9, T_Q2_K = 10, T_Q3_K = 11,
        T_Q4_K = 12, T_Q5_K = 13,
-       T_Q6_K = 14, T_Q8_K = 15 };
+       T_Q6_K = 14, T_Q8_K = 15, T_IQ4_NL = 20, T_IQ4_XS = 23 };
 
 typedef uint16_t fp16_t;
 
@@ -64,15 +64,17 @@ typedef struct { fp16_t d, dmin; uint8_t scales[K_SCALE_SIZE]; uint8_t qs[QK_K /
 typedef struct { fp16_t d, dmin; uint8_t scales[K_SCALE_SIZE]; uint8_t qh[QK_K / 8]; uint8_t qs[QK_K / 2]; } block_q5_K; /* 176 B */
 typedef struct { uint8_t ql[QK_K / 2]; uint8_t qh[QK_K / 4]; int8_t scales[QK_K / 16]; fp16_t d; } block_q6_K; /* 210 B */
 typedef struct { float d; int8_t qs[QK_K]; int16_t bsums[QK_K / 16]; } block_q8_K;             /* 292 B */
+typedef struct { fp16_t d; uint8_t qs[16]; } block_iq4_nl;                                   /* 18 B: 4-bit indices into a fixed non-linear table */
+typedef struct { fp16_t d; uint16_t scales_h; uint8_t scales_l[QK_K / 64]; uint8_t qs[QK_K / 2]; } block_iq4_xs; /* 136 B */
 #pragma pack(pop)
 
 static int64_t type_block(int t) {
     if (t == T_F32 || t == T_F16) return 1;
-    return (t == T_Q8_0 || t == T_Q8_1 || t == T_Q4_0 || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1) ? 32 : 256;
+    return (t == T_Q8_0 || t == T_Q8_1 || t == T_Q4_0 || t == T_Q4_1 || t == T_Q5_0 || t == T_Q5_1 || t == T_IQ4_NL) ? 32 : 256;
 }
 static int64_t type_bytes(int t) {
     switch (t) {
-        case T_Q2_K: return 84; case T_Q3_K: return 110;
+        case T_Q2_K: return 84; case T_Q3_K: return 110; case T_IQ4_NL: return 18; case T_IQ4_XS: return 136;
         case T_Q4_0: return 18; case T_Q4_1: return 20; case T_Q5_0: return 22; case T_Q5_1: return 24; case T_Q8_1: return 36;
         case T_F32: return 4; case T_F16: return 2; case T_Q8_0: return 34; case T_Q4_K: return 144;
         case T_Q5_K: return 176; case T_Q6_K: return 210; case T_Q8_K: return 292;
@@ -267,6 +269,39 @@ static void dequantize_row_q6_K(const block_q6_K *x, float *y, int64_t k) {
     }
 }
 
+/* ggml-quants.c kvalues_iq4nl, dequantize_row_iq4_nl / dequantize_row_iq4_xs */
+static const int8_t kvalues_iq4nl[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
+
+static void dequantize_row_iq4_nl(const block_iq4_nl *x, float *y, int64_t k) {
+    const int64_t nb = k / 32;
+    for (int64_t i = 0; i < nb; i++) {
+        const float d = fp16_to_fp32(x[i].d);
+        for (int j = 0; j < 16; ++j) {
+            y[j] = d * kvalues_iq4nl[x[i].qs[j] & 0xf];
+            y[j + 16] = d * kvalues_iq4nl[x[i].qs[j] >> 4];
+        }
+        y += 32;
+    }
+}
+
+static void dequantize_row_iq4_xs(const block_iq4_xs *x, float *y, int64_t k) {
+    const int64_t nb = k / QK_K;
+    for (int64_t i = 0; i < nb; i++) {
+        const uint8_t *qs = x[i].qs;
+        const float d = fp16_to_fp32(x[i].d);
+        for (int ib = 0; ib < QK_K / 32; ++ib) {
+            const int ls = ((x[i].scales_l[ib / 2] >> 4 * (ib % 2)) & 0xf) | (((x[i].scales_h >> 2 * ib) & 3) << 4);
+            const float dl = d * (ls - 32);
+            for (int j = 0; j < 16; ++j) {
+                y[j] = dl * kvalues_iq4nl[qs[j] & 0xf];
+                y[j + 16] = dl * kvalues_iq4nl[qs[j] >> 4];
+            }
+            y += 32;
+            qs += 16;
+        }
+    }
+}
+
 /* one row of `k` elements of type `type` -> f32 */
 void ref_dequantize_row(int type, const void *x, float *y, int64_t k) {
     switch (type) {
@@ -282,6 +317,8 @@ void ref_dequantize_row(int type, const void *x, float *y, int64_t k) {
         case T_Q4_K: dequantize_row_q4_K((const block_q4_K *)x, y, k); break;
         case T_Q5_K: dequantize_row_q5_K((const block_q5_K *)x, y, k); break;
         case T_Q6_K: dequantize_row_q6_K((const block_q6_K *)x, y, k); break;
+        case T_IQ4_NL: dequantize_row_iq4_nl((const block_iq4_nl *)x, y, k); break;
+        case T_IQ4_XS: dequantize_row_iq4_xs((const block_iq4_xs *)x, y, k); break;
         default: break;
     }
 }
@@ -619,6 +656,58 @@ static float vec_dot_q6_K_q8_K(int n, const block_q6_K *x, const block_q8_K *y) 
     return sumf;
 }
 
+/* ggml_vec_dot_iq4_nl_q8_0 (generic path): one float product per 32-element block */
+static float vec_dot_iq4_nl_q8_0(int n, const block_iq4_nl *x, const block_q8_0 *y) {
+    const int nb = n / 32;
+    float sumf = 0;
+    for (int ib = 0; ib < nb; ++ib) {
+        const float d = fp16_to_fp32(y[ib].d) * fp16_to_fp32(x[ib].d);
+        int sumi1 = 0, sumi2 = 0;
+        for (int j = 0; j < 16; ++j) {
+            sumi1 += y[ib].qs[j] * kvalues_iq4nl[x[ib].qs[j] & 0xf];
+            sumi2 += y[ib].qs[j + 16] * kvalues_iq4nl[x[ib].qs[j] >> 4];
+        }
+        sumf += d * (sumi1 + sumi2);
+    }
+    return sumf;
+}
+
+/* ggml_vec_dot_iq4_xs_q8_K (generic path): sub-block scales applied in float, two sub-blocks per turn */
+static float vec_dot_iq4_xs_q8_K(int n, const block_iq4_xs *x, const block_q8_K *y) {
+    const int nb = n / QK_K;
+    float sumf = 0;
+    for (int ibl = 0; ibl < nb; ++ibl) {
+        const float d4d8 = fp16_to_fp32(x[ibl].d) * y[ibl].d;
+        uint16_t h = x[ibl].scales_h;
+        const uint8_t *qs = x[ibl].qs;
+        const int8_t *q8 = y[ibl].qs;
+        for (int ib = 0; ib < QK_K / 32; ib += 2) {
+            const uint8_t ls1 = (uint8_t)((x[ibl].scales_l[ib / 2] & 0xf) | ((h << 4) & 0x30));
+            const uint8_t ls2 = (uint8_t)((x[ibl].scales_l[ib / 2] >> 4) | ((h << 2) & 0x30));
+            h >>= 4;
+            const float d1 = d4d8 * (ls1 - 32);
+            const float d2 = d4d8 * (ls2 - 32);
+            int sumi1 = 0, sumi2 = 0;
+            for (int j = 0; j < 16; ++j) {
+                sumi1 += q8[j + 0] * kvalues_iq4nl[qs[j] & 0xf];
+                sumi2 += q8[j + 16] * kvalues_iq4nl[qs[j] >> 4];
+            }
+            sumf += d1 * (sumi1 + sumi2);
+            qs += 16;
+            q8 += 32;
+            sumi1 = sumi2 = 0;
+            for (int j = 0; j < 16; ++j) {
+                sumi1 += q8[j + 0] * kvalues_iq4nl[qs[j] & 0xf];
+                sumi2 += q8[j + 16] * kvalues_iq4nl[qs[j] >> 4];
+            }
+            sumf += d2 * (sumi1 + sumi2);
+            qs += 16;
+            q8 += 32;
+        }
+    }
+    return sumf;
+}
+
 /* generic ggml_vec_dot_f16 / ggml_vec_dot_f32: double accumulator over f32 products */
 static float vec_dot_f16(int n, const fp16_t *x, const fp16_t *y) {
     double sumf = 0.0;
@@ -636,7 +725,7 @@ int ref_vec_dot_type(int wtype) {
     switch (wtype) {
         case T_F32: return T_F32;
         case T_F16: return T_F16;
-        case T_Q8_0: case T_Q4_0: case T_Q5_0: return T_Q8_0;
+        case T_Q8_0: case T_Q4_0: case T_Q5_0: case T_IQ4_NL: return T_Q8_0;
         case T_Q4_1: case T_Q5_1: return T_Q8_1;
         default: return T_Q8_K;
     }
@@ -666,6 +755,8 @@ float ref_vec_dot(int wtype, int n, const void *w, const void *yq) {
         case T_Q4_K: return vec_dot_q4_K_q8_K(n, (const block_q4_K *)w, (const block_q8_K *)yq);
         case T_Q5_K: return vec_dot_q5_K_q8_K(n, (const block_q5_K *)w, (const block_q8_K *)yq);
         case T_Q6_K: return vec_dot_q6_K_q8_K(n, (const block_q6_K *)w, (const block_q8_K *)yq);
+        case T_IQ4_NL: return vec_dot_iq4_nl_q8_0(n, (const block_iq4_nl *)w, (const block_q8_0 *)yq);
+        case T_IQ4_XS: return vec_dot_iq4_xs_q8_K(n, (const block_iq4_xs *)w, (const block_q8_K *)yq);
     }
     return NAN;
 }

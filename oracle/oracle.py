@@ -20,6 +20,7 @@ _LIB_PATH = os.path.join(_HERE, "_build", "libggml_ref.so")
 T_F32, T_F16, T_Q8_0, T_Q4_K, T_Q5_K, T_Q6_K, T_Q8_K = 0, 1, 8, 12, 13, 14, 15
 T_Q4_0, T_Q4_1, T_Q5_0, T_Q5_1 = 2, 3, 6, 7
 T_Q2_K, T_Q3_K = 10, 11
+T_IQ4_NL, T_IQ4_XS = 20, 23
 (TK_TOK_EMBD, TK_OUTPUT_NORM, TK_OUTPUT, TK_ATTN_NORM, TK_WQ, TK_WK, TK_WV, TK_WO, TK_FFN_NORM, TK_GATE, TK_UP,
  TK_DOWN) = range(12)
 

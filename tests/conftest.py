@@ -41,6 +41,8 @@ def model_files(gguf_dir):
         "mini_q5_1": ("mini", "q5_1"),
         "mini_q2_k": ("mini", "q2_k"),
         "mini_q3_k": ("mini", "q3_k"),
+        "mini_iq4_nl": ("mini", "iq4_nl"),
+        "mini_iq4_xs": ("mini", "iq4_xs"),
     }
     out = {}
     for name, (arch, preset) in specs.items():

@@ -10,7 +10,7 @@ from oracle import oracle as O
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 
 
-@pytest.mark.parametrize("name", ["q8_0", "q4_k", "q5_k", "q6_k", "f16", "q4_0", "q4_1", "q5_0", "q5_1", "q2_k", "q3_k"])
+@pytest.mark.parametrize("name", ["q8_0", "q4_k", "q5_k", "q6_k", "f16", "q4_0", "q4_1", "q5_0", "q5_1", "q2_k", "q3_k", "iq4_nl", "iq4_xs"])
 def test_dequant_bit_exact_vs_gguf_py(name):
     g = np.load(os.path.join(GOLD, f"dequant_{name}.npz"))
     got = O.dequantize(int(g["ggml_type"]), g["blocks"], g["values"].size)

@@ -37,7 +37,7 @@ def assert_logits_close(got, want, what=""):
     assert np.median(err) <= LOGITS_MEDIAN_SIGMA * sigma, f"{what}: median err {np.median(err):.3e} vs sigma {sigma:.3e}"
 
 
-@pytest.mark.parametrize("name", ["q8_0", "q4_k", "q5_k", "q6_k", "f16", "q4_0", "q4_1", "q5_0", "q5_1", "q2_k", "q3_k"])
+@pytest.mark.parametrize("name", ["q8_0", "q4_k", "q5_k", "q6_k", "f16", "q4_0", "q4_1", "q5_0", "q5_1", "q2_k", "q3_k", "iq4_nl", "iq4_xs"])
 def test_dequant_bit_exact_vs_golden_and_oracle(name):
     g = np.load(os.path.join(GOLD, f"dequant_{name}.npz"))
     n = g["values"].size // 256 * 256
@@ -48,7 +48,8 @@ def test_dequant_bit_exact_vs_golden_and_oracle(name):
 
 
 @pytest.mark.parametrize("wtype", [capi.B2_T_Q4_K, capi.B2_T_Q5_K, capi.B2_T_Q6_K, capi.B2_T_Q8_0, capi.B2_T_Q4_0, capi.B2_T_Q4_1,
-                                   capi.B2_T_Q5_0, capi.B2_T_Q5_1, capi.B2_T_Q2_K, capi.B2_T_Q3_K])
+                                   capi.B2_T_Q5_0, capi.B2_T_Q5_1, capi.B2_T_Q2_K, capi.B2_T_Q3_K, capi.B2_T_IQ4_NL,
+                                   capi.B2_T_IQ4_XS])
 def test_dequant_bit_exact_large_random(wtype):
     import make_gguf as mg
     rng = np.random.default_rng(wtype)
@@ -138,7 +139,7 @@ GEMM_TC_RTOL = 1.5e-2
     (capi.B2_T_Q4_K, 4096, 4096, 64), (capi.B2_T_Q6_K, 1024, 14336, 64), (capi.B2_T_Q4_K, 512, 8192, 17),
     # legacy 32-element blocks: this path is the only one they have, from one token on
     (capi.B2_T_Q4_0, 512, 1024, 1), (capi.B2_T_Q4_1, 300, 576, 9), (capi.B2_T_Q5_0, 1024, 4096, 64), (capi.B2_T_Q5_1, 256, 2048, 130),
-    (capi.B2_T_Q2_K, 512, 1024, 3), (capi.B2_T_Q3_K, 300, 2048, 70)])
+    (capi.B2_T_Q2_K, 512, 1024, 3), (capi.B2_T_Q3_K, 300, 2048, 70), (capi.B2_T_IQ4_NL, 300, 576, 5), (capi.B2_T_IQ4_XS, 512, 2048, 40)])
 def test_gemm_tcgen05_matches_float_reference(wtype, rows, cols, n_tok):
     """the tensor-core path (prefill, batched decode): tcgen05 GEMM on bf16 tiles vs dequantised weights in float64"""
     import make_gguf as mg
@@ -167,7 +168,7 @@ def test_mul_mat_linearity_in_rows():
     assert np.array_equal(full[:, 512:1024], part)
 
 
-MODELS = ["micro_mixed", "micro_q8_0", "mini_q4_k_m", "mini_q5_k", "mini_f16", "mini_q4_0", "mini_q5_1", "mini_q2_k", "mini_q3_k"]
+MODELS = ["micro_mixed", "micro_q8_0", "mini_q4_k_m", "mini_q5_k", "mini_f16", "mini_q4_0", "mini_q5_1", "mini_q2_k", "mini_q3_k", "mini_iq4_nl", "mini_iq4_xs"]
 
 
 @pytest.mark.parametrize("name", MODELS)

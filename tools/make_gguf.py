@@ -35,10 +35,12 @@ F32, F16, Q8_0, Q4_K, Q5_K, Q6_K = 0, 1, 8, 12, 13, 14
 Q4_0, Q4_1, Q5_0, Q5_1 = 2, 3, 6, 7  # legacy 32-element blocks (tensor-core path only on the device)
 LEGACY = (Q4_0, Q4_1, Q5_0, Q5_1)
 Q2_K, Q3_K = 10, 11  # K-quants without an integer decode kernel on the device (tensor-core path only)
+IQ4_NL, IQ4_XS = 20, 23  # 4-bit indices into a fixed non-linear table (tensor-core path only)
 TYPE_NAMES = {F32: "F32", F16: "F16", Q8_0: "Q8_0", Q4_K: "Q4_K", Q5_K: "Q5_K", Q6_K: "Q6_K", Q4_0: "Q4_0", Q4_1: "Q4_1",
-              Q5_0: "Q5_0", Q5_1: "Q5_1", Q2_K: "Q2_K", Q3_K: "Q3_K"}
+              Q5_0: "Q5_0", Q5_1: "Q5_1", Q2_K: "Q2_K", Q3_K: "Q3_K", IQ4_NL: "IQ4_NL", IQ4_XS: "IQ4_XS"}
 BLOCK = {F32: (1, 4), F16: (1, 2), Q8_0: (32, 34), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), Q4_0: (32, 18),
-         Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q2_K: (256, 84), Q3_K: (256, 110)}
+         Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q2_K: (256, 84), Q3_K: (256, 110),
+         IQ4_NL: (32, 18), IQ4_XS: (256, 136)}
 
 # gguf metadata value types
 T_U8, T_I8, T_U16, T_I16, T_U32, T_I32, T_F32, T_BOOL, T_STR, T_ARR, T_U64, T_I64, T_F64 = range(13)
@@ -97,6 +99,12 @@ def tensor_type(preset: str, arch: Arch, name: str, layer: int) -> int:
         if name == "token_embd.weight":
             return Q4_K
         return Q2_K if preset == "q2_k" else Q3_K
+    if preset in ("iq4_nl", "iq4_xs"):  # output Q6_K as llama-quantize does; token embeddings Q4_K (needs a quantiser here)
+        if name == "output.weight":
+            return Q6_K
+        if name == "token_embd.weight":
+            return Q4_K
+        return IQ4_NL if preset == "iq4_nl" else IQ4_XS
     if preset in ("q4_k", "q5_k", "q6_k"):
         return {"q4_k": Q4_K, "q5_k": Q5_K, "q6_k": Q6_K}[preset]
     if preset == "q4_k_m":
@@ -157,6 +165,13 @@ def random_blocks(rng: np.random.Generator, gtype: int, n_blocks: int, sigma: fl
         body = rng.integers(0, 256, size=(n_blocks, 108), dtype=np.uint8)
         d = (sigma / 43.0) * jitter
         return np.concatenate([body, _f16_bytes(d)], axis=1)
+    if gtype == IQ4_NL:  # d, qs[16]: value = d * level[nibble]; the 16 levels have rms ~ 68
+        qs = rng.integers(0, 256, size=(n_blocks, 16), dtype=np.uint8)
+        sign = rng.integers(0, 2, size=n_blocks).astype(np.float32) * 2 - 1  # the levels are not centred: mix both signs of d
+        return np.concatenate([_f16_bytes((sigma / 68.0) * jitter * sign), qs], axis=1)
+    if gtype == IQ4_XS:  # d, scales_h, scales_l[4], qs[128]: value = d * (ls - 32) * level[nibble], ls 6-bit
+        body = rng.integers(0, 256, size=(n_blocks, 134), dtype=np.uint8)
+        return np.concatenate([_f16_bytes((sigma / (68.0 * 18.5)) * jitter), body], axis=1)
     if gtype == Q8_0:
         qs = rng.integers(-127, 128, size=(n_blocks, 32), dtype=np.int8)
         d = (sigma / 73.3) * jitter
@@ -435,7 +450,7 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     plan = tensor_plan(arch, preset, gain_out)
 
     ftype = {"f32": 0, "f16": 1, "q8_0": 7, "q4_k_m": 15, "q4_k": 14, "q5_k": 16, "q6_k": 18, "mixed": 15,
-             "q4_0": 2, "q4_1": 3, "q5_0": 8, "q5_1": 9, "q2_k": 10, "q3_k": 12}[preset]  # llama_ftype
+             "q4_0": 2, "q4_1": 3, "q5_0": 8, "q5_1": 9, "q2_k": 10, "q3_k": 12, "iq4_nl": 25, "iq4_xs": 30}[preset]  # llama_ftype
     kvs = [
         kv_bytes("general.architecture", T_STR, "llama"),
         kv_bytes("general.name", T_STR, f"{arch.name}-{preset}-random-seed{seed}"),
@@ -522,7 +537,7 @@ def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--arch", required=True, choices=sorted(ARCHS))
     ap.add_argument("--preset", required=True,
-                    choices=["f32", "f16", "q8_0", "q4_k_m", "q4_k", "q5_k", "q6_k", "mixed", "q4_0", "q4_1", "q5_0", "q5_1", "q2_k", "q3_k"])
+                    choices=["f32", "f16", "q8_0", "q4_k_m", "q4_k", "q5_k", "q6_k", "mixed", "q4_0", "q4_1", "q5_0", "q5_1", "q2_k", "q3_k", "iq4_nl", "iq4_xs"])
     ap.add_argument("--out", required=True)
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--gain-out", type=float, default=4.0, help="output.weight std multiplier (argmax margin)")

@@ -138,7 +138,28 @@ def mint_small_k():
         print(name, blocks.shape, vals.shape, "finite:", bool(np.isfinite(vals).all()))
 
 
+def mint_iq4():
+    """dequant_{iq4_nl,iq4_xs}.npz: random blocks plus raw random bytes under edge-case scales (gguf-py dequantiser)."""
+    rng = np.random.default_rng(4321)
+    f16 = lambda v: np.frombuffer(np.float16(v).tobytes(), dtype=np.uint8)  # noqa: E731
+    for name, gt, qt in (("iq4_nl", mg.IQ4_NL, QT.IQ4_NL), ("iq4_xs", mg.IQ4_XS, QT.IQ4_XS)):
+        bb = mg.BLOCK[gt][1]
+        raw = rng.integers(0, 256, size=(8, bb), dtype=np.uint8)
+        for i, d in enumerate([0.0, -0.0, 6.1e-5, -3.0e-3, 5.96e-8, 1.0, -2.5, 0.25]):
+            raw[i, 0:2] = f16(d)
+            if i == 2:
+                raw[i, 2:] = 0xFF
+            if i == 3:
+                raw[i, 2:] = 0x00
+        blocks = np.concatenate([mg.random_blocks(rng, gt, 24, 0.02), raw], axis=0)
+        vals = gguf.quants.dequantize(blocks.reshape(-1), qt).astype(np.float32).reshape(-1)
+        np.savez_compressed(os.path.join(GOLD, f"dequant_{name}.npz"), blocks=blocks, values=vals, ggml_type=gt)
+        print(name, blocks.shape, vals.shape, "finite:", bool(np.isfinite(vals).all()))
+
+
 if __name__ == "__main__":
+    if "--iq4-only" in sys.argv:
+        sys.exit(mint_iq4())
     if "--small-k-only" in sys.argv:
         sys.exit(mint_small_k())
     if "--legacy-only" in sys.argv:
