@@ -217,6 +217,32 @@ typedef struct {
     int32_t n_prev;
     float tfs_z, typical_p; /* 0 or >= 1 = off */
 } b2_sample_params;
+/* ------------------------------------------------------------------------------------------------
+ * BERT embeddings: the `bert-embeddings` backend.  Replaces bert.New / Embeddings / TokenEmbeddings of go-bert.cpp as
+ * bound by backend/go/llm/bert/bert.go:18,30,33 (Load, Embeddings with PredictOptions.Embeddings or .EmbeddingTokens),
+ * for a BERT encoder stored as GGUF (general.architecture = "bert", WordPiece vocabulary).  One text -> one vector of
+ * n_embd floats: mean over the tokens' last hidden states, L2-normalised (bert.cpp bert_eval).  Calls on one handle
+ * are serialised (the reference backend is base.SingleThread).  vocab_only != 0 loads the tokenizer alone (no device).
+ */
+typedef struct b2_bert b2_bert;
+typedef struct {
+    int32_t n_layer, n_embd, n_head, n_ff, n_ctx, n_vocab;
+    int64_t weight_bytes_device;
+} b2_bert_info_t;
+b2_bert *b2_bert_load(const char *model_path, int device, int vocab_only); /* NULL on failure: b2_last_error() */
+void b2_bert_free(b2_bert *b);
+int b2_bert_info(b2_bert *b, b2_bert_info_t *out);
+/* [CLS] pieces... [SEP], cut to the model's context; returns the count, or -(count needed) if cap is too small */
+int b2_bert_tokenize(b2_bert *b, const char *text, size_t text_len, int32_t *out, int cap);
+/* Embeddings(text) / TokenEmbeddings(ids): writes n_embd floats, returns n_embd */
+int b2_bert_embed_text(b2_bert *b, const char *text, size_t text_len, float *out, int cap);
+int b2_bert_embed_tokens(b2_bert *b, const int32_t *ids, int n_ids, float *out, int cap);
+/* several token sequences in one forward (no counterpart in the reference, whose API carries one text per call):
+ * ids back to back, offsets[n_seq + 1]; out [n_seq][n_embd]; at most 8192 tokens per call */
+int b2_bert_embed_batch(b2_bert *b, const int32_t *ids, const int32_t *offsets, int n_seq, float *out);
+/* test hook: last hidden states [n_ids][n_embd] of one sequence */
+int b2_bert_hidden(b2_bert *b, const int32_t *ids, int n_ids, float *out);
+
 /* Grammar matcher alone (host only, no device needed).  b2_grammar_match parses `gbnf` and feeds `text` one code point
  * at a time: *n_accepted = bytes taken before the first code point that does not fit, *can_stop = 1 if the accepted
  * text is a complete sentence of the grammar.  b2_grammar_token_mask: after `accepted`, bit t of mask_bits

@@ -27,6 +27,8 @@ EXPORTS = [
     "b2_token_to_piece", "b2_submit", "b2_poll", "b2_cancel", "b2_embed_result", "b2_release", "b2_metrics", "b2_eval",
     "b2_decode_greedy", "b2_debug_hidden", "b2_bench_decode", "b2_bench_prefill", "b2_bench_gemv", "b2_dequantize", "b2_quantize_act",
     "b2_mul_mat", "b2_mul_mat_noalloc", "b2_sample", "b2_grammar_match", "b2_grammar_token_mask",
+    "b2_bert_load", "b2_bert_free", "b2_bert_info", "b2_bert_tokenize", "b2_bert_embed_text", "b2_bert_embed_tokens",
+    "b2_bert_embed_batch", "b2_bert_hidden",
 ]
 
 
@@ -86,6 +88,11 @@ class Event(C.Structure):
     ]
 
 
+class BertInfo(C.Structure):
+    _fields_ = [("n_layer", C.c_int32), ("n_embd", C.c_int32), ("n_head", C.c_int32), ("n_ff", C.c_int32), ("n_ctx", C.c_int32),
+                ("n_vocab", C.c_int32), ("weight_bytes_device", C.c_int64)]
+
+
 class Metrics(C.Structure):
     _fields_ = [
         ("slot_id", C.c_int32), ("tokens_per_second", C.c_float), ("tokens_generated", C.c_int32),
@@ -134,6 +141,16 @@ def lib() -> C.CDLL:
     L.b2_mul_mat.argtypes = [i32, vp, i64, i64, vp, i32, vp, i32]
     L.b2_mul_mat_noalloc.argtypes = [i32, vp, i64, i64, vp, i32, vp, vp]
     L.b2_sample.argtypes = [i32, vp, i32, C.POINTER(SampleParams), i32, vp, vp]
+    L.b2_bert_load.restype = vp
+    L.b2_bert_load.argtypes = [C.c_char_p, i32, i32]
+    L.b2_bert_free.restype = None
+    L.b2_bert_free.argtypes = [vp]
+    L.b2_bert_info.argtypes = [vp, C.POINTER(BertInfo)]
+    L.b2_bert_tokenize.argtypes = [vp, C.c_char_p, C.c_size_t, vp, i32]
+    L.b2_bert_embed_text.argtypes = [vp, C.c_char_p, C.c_size_t, vp, i32]
+    L.b2_bert_embed_tokens.argtypes = [vp, vp, i32, vp, i32]
+    L.b2_bert_embed_batch.argtypes = [vp, vp, vp, i32, vp]
+    L.b2_bert_hidden.argtypes = [vp, vp, i32, vp]
     L.b2_grammar_match.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_int)]
     L.b2_grammar_token_mask.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), vp, i32, vp]
     _lib = L
@@ -395,3 +412,59 @@ class Engine:
         m = Metrics()
         _check(lib().b2_metrics(self._h, C.byref(m)))
         return {k: getattr(m, k) for k, _ in Metrics._fields_}
+
+
+class Bert:
+    """The `bert-embeddings` backend over the C ABI: Load / Embeddings / TokenEmbeddings (backend/go/llm/bert/bert.go)."""
+
+    def __init__(self, model_path: str, device: int = 0, vocab_only: bool = False):
+        self._h = lib().b2_bert_load(model_path.encode(), device, int(vocab_only))
+        if not self._h:
+            raise B2Error(-1, (lib().b2_last_error() or b"").decode("utf-8", "replace"))
+        info = BertInfo()
+        _check(lib().b2_bert_info(self._h, C.byref(info)))
+        self.info = {k: getattr(info, k) for k, _ in BertInfo._fields_}
+        self.n_embd = info.n_embd
+
+    def close(self):
+        if self._h:
+            lib().b2_bert_free(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def tokenize(self, text: str | bytes) -> list[int]:
+        t = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+        buf = np.empty(max(16, self.info["n_ctx"]), dtype=np.int32)
+        n = _check(lib().b2_bert_tokenize(self._h, t, len(t), buf.ctypes.data, buf.size))
+        return buf[:n].tolist()
+
+    def embed(self, text: str | bytes) -> np.ndarray:
+        t = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+        out = np.empty(self.n_embd, dtype=np.float32)
+        _check(lib().b2_bert_embed_text(self._h, t, len(t), out.ctypes.data, out.size))
+        return out
+
+    def embed_tokens(self, ids: Sequence[int]) -> np.ndarray:
+        a = np.ascontiguousarray(ids, dtype=np.int32)
+        out = np.empty(self.n_embd, dtype=np.float32)
+        _check(lib().b2_bert_embed_tokens(self._h, a.ctypes.data, a.size, out.ctypes.data, out.size))
+        return out
+
+    def embed_batch(self, seqs: Sequence[Sequence[int]]) -> np.ndarray:
+        offs = np.zeros(len(seqs) + 1, dtype=np.int32)
+        offs[1:] = np.cumsum([len(s) for s in seqs])
+        ids = np.ascontiguousarray(np.concatenate([np.asarray(s, dtype=np.int32) for s in seqs]), dtype=np.int32)
+        out = np.empty((len(seqs), self.n_embd), dtype=np.float32)
+        _check(lib().b2_bert_embed_batch(self._h, ids.ctypes.data, offs.ctypes.data, len(seqs), out.ctypes.data))
+        return out
+
+    def hidden(self, ids: Sequence[int]) -> np.ndarray:
+        a = np.ascontiguousarray(ids, dtype=np.int32)
+        out = np.empty((a.size, self.n_embd), dtype=np.float32)
+        _check(lib().b2_bert_hidden(self._h, a.ctypes.data, a.size, out.ctypes.data))
+        return out

@@ -6,6 +6,7 @@
 #include <mutex>
 #include <vector>
 
+#include "bert.h"
 #include "engine.h"
 #include "grammar.h"
 #include "kernels.h"
@@ -329,6 +330,81 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     }
     B2_CUDA(cudaMemcpy(out, dout.p, (size_t)n_tok * rows * 4, cudaMemcpyDeviceToHost));
     return 0;
+    B2_API_END(0)
+}
+
+struct b2_bert {
+    std::unique_ptr<BertModel> m;
+};
+
+b2_bert *b2_bert_load(const char *model_path, int device, int vocab_only) {
+    try {
+        B2_CHECK(model_path, B2_EINVAL, "b2_bert_load: no model path");
+        B2_CHECK(vocab_only || sm100_device_count() > 0, B2_ENODEV, "no sm_100 CUDA device (this library has no CPU fallback)");
+        auto h = std::make_unique<b2_bert>();
+        h->m.reset(new BertModel(model_path, device, vocab_only != 0));
+        return h.release();
+    } catch (const std::exception &e) {
+        b2::set_last_error(e.what());
+        return nullptr;
+    }
+}
+
+void b2_bert_free(b2_bert *b) { delete b; }
+
+int b2_bert_info(b2_bert *b, b2_bert_info_t *out) {
+    B2_API_BEGIN
+    B2_CHECK(b && out, B2_EINVAL, "b2_bert_info: bad arguments");
+    const BertModel &m = *b->m;
+    *out = b2_bert_info_t{m.n_layer, m.n_embd, m.n_head, m.n_ff, m.n_ctx, m.n_vocab, m.weight_bytes};
+    return B2_OK;
+    B2_API_END(0)
+}
+
+int b2_bert_tokenize(b2_bert *b, const char *text, size_t text_len, int32_t *out, int cap) {
+    B2_API_BEGIN
+    B2_CHECK(b && (text || text_len == 0), B2_EINVAL, "b2_bert_tokenize: bad arguments");
+    const std::vector<int32_t> ids = b->m->tokenize(std::string(text ? text : "", text_len));
+    if ((int)ids.size() > cap || !out) return -(int)ids.size();
+    memcpy(out, ids.data(), ids.size() * 4);
+    return (int)ids.size();
+    B2_API_END(0)
+}
+
+int b2_bert_embed_tokens(b2_bert *b, const int32_t *ids, int n_ids, float *out, int cap) {
+    B2_API_BEGIN
+    B2_CHECK(b && ids && out && n_ids > 0, B2_EINVAL, "b2_bert_embed_tokens: bad arguments");
+    B2_CHECK(cap >= b->m->n_embd, B2_ENOSPC, "b2_bert_embed_tokens: the output needs n_embd floats");
+    const int32_t offs[2] = {0, n_ids};
+    b->m->embed(ids, offs, 1, out);
+    return b->m->n_embd;
+    B2_API_END(0)
+}
+
+int b2_bert_embed_text(b2_bert *b, const char *text, size_t text_len, float *out, int cap) {
+    B2_API_BEGIN
+    B2_CHECK(b && out && (text || text_len == 0), B2_EINVAL, "b2_bert_embed_text: bad arguments");
+    B2_CHECK(cap >= b->m->n_embd, B2_ENOSPC, "b2_bert_embed_text: the output needs n_embd floats");
+    const std::vector<int32_t> ids = b->m->tokenize(std::string(text ? text : "", text_len));
+    const int32_t offs[2] = {0, (int32_t)ids.size()};
+    b->m->embed(ids.data(), offs, 1, out);
+    return b->m->n_embd;
+    B2_API_END(0)
+}
+
+int b2_bert_embed_batch(b2_bert *b, const int32_t *ids, const int32_t *offsets, int n_seq, float *out) {
+    B2_API_BEGIN
+    B2_CHECK(b && ids && offsets && out && n_seq > 0, B2_EINVAL, "b2_bert_embed_batch: bad arguments");
+    b->m->embed(ids, offsets, n_seq, out);
+    return n_seq;
+    B2_API_END(0)
+}
+
+int b2_bert_hidden(b2_bert *b, const int32_t *ids, int n_ids, float *out) {
+    B2_API_BEGIN
+    B2_CHECK(b && ids && out && n_ids > 0, B2_EINVAL, "b2_bert_hidden: bad arguments");
+    b->m->hidden(ids, n_ids, out);
+    return n_ids;
     B2_API_END(0)
 }
 

@@ -149,6 +149,8 @@ void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t 
 void launch_gemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const float *w, int n_tok, int64_t K, float eps, void *x_tiles,
                                    float *xn_out, cudaStream_t s);
 void launch_gemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
+// gelu(x + bias): the BERT feed-forward activation (bert.cu)
+void launch_gemm_prepare_x_bias_gelu(const float *x, const float *bias, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
 // quantised W -> bf16 operand tiles (gemm_w_tiles_bytes of them)
 void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s);
 // out[t][r] = W[r] . x[t] (+ residual): tcgen05/TMEM GEMM on bf16 operand tiles; W is dequantised into w_tiles first

@@ -1,0 +1,352 @@
+// kernels_bert.cu -- the element-wise, normalisation, attention and pooling kernels of the BERT encoder (bert.h).
+// The mat-muls are the tcgen05 GEMM of kernels_gemm.cu; everything here is HBM/L2-bound fp32 row work.
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <math_constants.h>
+
+#include <cstdlib>
+
+#include "bert.h"
+
+namespace b2 {
+
+namespace {
+
+constexpr int LN_THREADS = 256;
+
+__device__ __forceinline__ float block_sum(float v, float *red) { // red: 32 floats of shared memory
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    __syncthreads(); // red may still be read from the previous reduction
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float t = lane < nw ? red[lane] : 0.f;
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    return t;
+}
+
+// ggml_norm: mean, then the variance of the centred values, y = (x - mean) / sqrt(var + eps); then * w + b
+__device__ __forceinline__ void layernorm_row(float *row, const float *w, const float *b, int d, float eps, float *red) {
+    float s = 0.f;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) s += row[i];
+    const float mean = block_sum(s, red) / (float)d;
+    float s2 = 0.f;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+        const float c = row[i] - mean;
+        s2 += c * c;
+    }
+    const float inv = rsqrtf(block_sum(s2, red) / (float)d + eps);
+    for (int i = threadIdx.x; i < d; i += blockDim.x) row[i] = (row[i] - mean) * inv * w[i] + b[i];
+}
+
+__global__ void __launch_bounds__(LN_THREADS) bert_embed_ln_kernel(float *x, const float *pos_embd, const float *type0, const int32_t *pos,
+                                                                   const float *w, const float *b, int d, float eps) {
+    __shared__ float red[32];
+    float *row = x + (size_t)blockIdx.x * d;
+    const float *pe = pos_embd + (size_t)pos[blockIdx.x] * d;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) row[i] = row[i] + type0[i] + pe[i];
+    __syncthreads();
+    layernorm_row(row, w, b, d, eps, red);
+}
+
+__global__ void __launch_bounds__(LN_THREADS) bert_bias_residual_ln_kernel(float *x, const float *h, const float *bias, const float *w,
+                                                                           const float *b, int d, float eps) {
+    __shared__ float red[32];
+    float *row = x + (size_t)blockIdx.x * d;
+    const float *hr = h + (size_t)blockIdx.x * d;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) row[i] = row[i] + (hr[i] + bias[i]);
+    __syncthreads();
+    layernorm_row(row, w, b, d, eps, red);
+}
+
+// ggml_gelu: 0.5 x (1 + tanh(sqrt(2/pi) x (1 + 0.044715 x^2)))
+__global__ void bert_bias_gelu_kernel(float *x, const float *bias, int64_t total, int n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const float v = x[i] + bias[i % n];
+    x[i] = 0.5f * v * (1.f + tanhf(0.7978845608028654f * v * (1.f + 0.044715f * v * v)));
+}
+
+// One CTA = one head of one sequence x QB queries; K/V go through shared memory in tiles of KT keys, the softmax is
+// the running (flash) form, exact in fp32.  Lane l owns keys l, l + 32 of a tile for the scores and features
+// l, l + 32 of the output.
+constexpr int ATT_QB = 32, ATT_KT = 64, ATT_WARPS = 4;
+
+template <int HD>
+__global__ void __launch_bounds__(ATT_WARPS * 32) bert_attention_kernel(const float *__restrict__ q, const float *__restrict__ k,
+                                                                        const float *__restrict__ v, const float *__restrict__ bq,
+                                                                        const float *__restrict__ bk, const float *__restrict__ bv,
+                                                                        const int32_t *__restrict__ offs, int n_head, float *__restrict__ out) {
+    constexpr int NC = HD / 32, QW = ATT_QB / ATT_WARPS;
+    __shared__ float Qs[ATT_QB][HD];
+    __shared__ float Ks[ATT_KT][HD + 1];
+    __shared__ float Vs[ATT_KT][HD];
+    const int seq = blockIdx.z, head = blockIdx.y, t0 = offs[seq], len = offs[seq + 1] - t0;
+    const int q0 = blockIdx.x * ATT_QB;
+    if (q0 >= len) return;
+    const int d = n_head * HD, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float scale = rsqrtf((float)HD);
+    for (int i = tid; i < ATT_QB * HD; i += ATT_WARPS * 32) {
+        const int r = i / HD, c = i % HD;
+        Qs[r][c] = q0 + r < len ? (q[(size_t)(t0 + q0 + r) * d + head * HD + c] + bq[head * HD + c]) * scale : 0.f;
+    }
+    float m[QW], l[QW], acc[QW][NC];
+#pragma unroll
+    for (int i = 0; i < QW; i++) {
+        m[i] = -CUDART_INF_F;
+        l[i] = 0.f;
+#pragma unroll
+        for (int c = 0; c < NC; c++) acc[i][c] = 0.f;
+    }
+    for (int k0 = 0; k0 < len; k0 += ATT_KT) {
+        __syncthreads(); // the previous tile is consumed (and Qs is written, first time round)
+        for (int i = tid; i < ATT_KT * HD; i += ATT_WARPS * 32) {
+            const int r = i / HD, c = i % HD;
+            const bool ok = k0 + r < len;
+            const size_t g = (size_t)(t0 + k0 + (ok ? r : 0)) * d + head * HD + c;
+            Ks[r][c] = ok ? k[g] + bk[head * HD + c] : 0.f;
+            Vs[r][c] = ok ? v[g] + bv[head * HD + c] : 0.f;
+        }
+        __syncthreads();
+        const bool ok0 = k0 + lane < len, ok1 = k0 + lane + 32 < len;
+#pragma unroll
+        for (int i = 0; i < QW; i++) {
+            const int qi = warp * QW + i;
+            if (q0 + qi >= len) continue; // warp-uniform
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll 8
+            for (int c = 0; c < HD; c++) {
+                const float qv = Qs[qi][c];
+                s0 += qv * Ks[lane][c];
+                s1 += qv * Ks[lane + 32][c];
+            }
+            s0 = ok0 ? s0 : -CUDART_INF_F;
+            s1 = ok1 ? s1 : -CUDART_INF_F;
+            float mt = fmaxf(s0, s1);
+            for (int o = 16; o > 0; o >>= 1) mt = fmaxf(mt, __shfl_xor_sync(0xffffffffu, mt, o));
+            const float mn = fmaxf(m[i], mt); // finite: key k0 of every tile exists
+            const float sc = __expf(m[i] - mn);
+            const float p0 = __expf(s0 - mn), p1 = __expf(s1 - mn);
+            m[i] = mn;
+            l[i] = l[i] * sc + (p0 + p1);
+#pragma unroll
+            for (int c = 0; c < NC; c++) acc[i][c] *= sc;
+#pragma unroll 8
+            for (int j = 0; j < 32; j++) {
+                const float pa = __shfl_sync(0xffffffffu, p0, j), pb = __shfl_sync(0xffffffffu, p1, j);
+#pragma unroll
+                for (int c = 0; c < NC; c++) acc[i][c] += pa * Vs[j][lane + 32 * c] + pb * Vs[j + 32][lane + 32 * c];
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < QW; i++) {
+        const int qi = warp * QW + i;
+        if (q0 + qi >= len) continue;
+        float lt = l[i];
+        for (int o = 16; o > 0; o >>= 1) lt += __shfl_xor_sync(0xffffffffu, lt, o);
+        const float inv = 1.f / lt;
+#pragma unroll
+        for (int c = 0; c < NC; c++) out[(size_t)(t0 + q0 + qi) * d + head * HD + lane + 32 * c] = acc[i][c] * inv;
+    }
+}
+
+// The same attention on the warp-level tensor-core path: S = Q K^T and O = P V as m16n8k16 bf16 MMAs with fp32
+// accumulators, the running softmax in fp32 registers in between (the accumulator fragment of S is the A fragment of
+// the next product, so P never leaves registers).  One warp = 16 queries, one CTA = 4 warps = 64 queries of one head.
+// K is staged as bf16 [key][dim], V transposed as bf16 [dim][key]; both rows padded by 8 elements so that the 32 lanes of a
+// fragment load (8 rows x 4 words) fall into 32 different banks.
+constexpr int MMA_QB = 64, MMA_KT = 64;
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&v);
+}
+__device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+template <int HD>
+__global__ void __launch_bounds__(128) bert_attention_mma_kernel(const float *__restrict__ q, const float *__restrict__ k,
+                                                                 const float *__restrict__ v, const float *__restrict__ bq,
+                                                                 const float *__restrict__ bk, const float *__restrict__ bv,
+                                                                 const int32_t *__restrict__ offs, int n_head, float *__restrict__ out) {
+    constexpr int KS = HD / 16, ND = HD / 8, NB = MMA_KT / 8, PAD = 8;
+    __shared__ __align__(16) __nv_bfloat16 Kb[MMA_KT][HD + PAD];
+    __shared__ __align__(16) __nv_bfloat16 Vt[HD][MMA_KT + PAD];
+    const int seq = blockIdx.z, head = blockIdx.y, t0 = offs[seq], len = offs[seq + 1] - t0;
+    const int q0 = blockIdx.x * MMA_QB;
+    if (q0 >= len) return;
+    const int d = n_head * HD, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, tq = lane & 3; // row inside the fragment, position inside the quad
+    const float scale = rsqrtf((float)HD);
+    const int r0 = q0 + warp * 16 + g, r1 = r0 + 8; // the two query rows this thread holds parts of
+    uint32_t qa[KS][4];
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) { // h: columns +0 / +8 of the k-step
+            const int c = ks * 16 + h * 8 + tq * 2;
+            const float b0 = bq[head * HD + c], b1 = bq[head * HD + c + 1];
+            const float *p0 = q + (size_t)(t0 + r0) * d + head * HD + c, *p1 = q + (size_t)(t0 + r1) * d + head * HD + c;
+            qa[ks][2 * h + 0] = r0 < len ? pack_bf16((p0[0] + b0) * scale, (p0[1] + b1) * scale) : 0u;
+            qa[ks][2 * h + 1] = r1 < len ? pack_bf16((p1[0] + b0) * scale, (p1[1] + b1) * scale) : 0u;
+        }
+    }
+    float o[ND][4];
+#pragma unroll
+    for (int i = 0; i < ND; i++) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
+    for (int k0 = 0; k0 < len; k0 += MMA_KT) {
+        __syncthreads();
+        for (int i = tid; i < MMA_KT * HD; i += 128) {
+            const int r = i / HD, c = i % HD;
+            const bool ok = k0 + r < len;
+            const size_t gi = (size_t)(t0 + k0 + (ok ? r : 0)) * d + head * HD + c;
+            Kb[r][c] = __float2bfloat16_rn(ok ? k[gi] + bk[head * HD + c] : 0.f);
+            Vt[c][r] = __float2bfloat16_rn(ok ? v[gi] + bv[head * HD + c] : 0.f);
+        }
+        __syncthreads();
+        float s[NB][4];
+#pragma unroll
+        for (int nb = 0; nb < NB; nb++) {
+            s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < KS; ks++) {
+                const uint32_t b0 = *reinterpret_cast<const uint32_t *>(&Kb[nb * 8 + g][ks * 16 + tq * 2]);
+                const uint32_t b1 = *reinterpret_cast<const uint32_t *>(&Kb[nb * 8 + g][ks * 16 + 8 + tq * 2]);
+                mma_16816(s[nb], qa[ks], b0, b1);
+            }
+        }
+        float mt0 = -CUDART_INF_F, mt1 = -CUDART_INF_F;
+#pragma unroll
+        for (int nb = 0; nb < NB; nb++) {
+            const int key = k0 + nb * 8 + tq * 2;
+            if (key >= len) s[nb][0] = s[nb][2] = -CUDART_INF_F;
+            if (key + 1 >= len) s[nb][1] = s[nb][3] = -CUDART_INF_F;
+            mt0 = fmaxf(mt0, fmaxf(s[nb][0], s[nb][1]));
+            mt1 = fmaxf(mt1, fmaxf(s[nb][2], s[nb][3]));
+        }
+        mt0 = fmaxf(mt0, __shfl_xor_sync(0xffffffffu, mt0, 1));
+        mt0 = fmaxf(mt0, __shfl_xor_sync(0xffffffffu, mt0, 2));
+        mt1 = fmaxf(mt1, __shfl_xor_sync(0xffffffffu, mt1, 1));
+        mt1 = fmaxf(mt1, __shfl_xor_sync(0xffffffffu, mt1, 2));
+        const float mn0 = fmaxf(m0, mt0), mn1 = fmaxf(m1, mt1); // finite: key k0 of every tile exists
+        const float sc0 = __expf(m0 - mn0), sc1 = __expf(m1 - mn1);
+        m0 = mn0;
+        m1 = mn1;
+        float ps0 = 0.f, ps1 = 0.f;
+#pragma unroll
+        for (int nb = 0; nb < NB; nb++) {
+            s[nb][0] = __expf(s[nb][0] - mn0);
+            s[nb][1] = __expf(s[nb][1] - mn0);
+            s[nb][2] = __expf(s[nb][2] - mn1);
+            s[nb][3] = __expf(s[nb][3] - mn1);
+            ps0 += s[nb][0] + s[nb][1];
+            ps1 += s[nb][2] + s[nb][3];
+        }
+        l0 = l0 * sc0 + ps0; // per-thread part of the row sum; the quad is summed at the end
+        l1 = l1 * sc1 + ps1;
+#pragma unroll
+        for (int nd = 0; nd < ND; nd++) {
+            o[nd][0] *= sc0;
+            o[nd][1] *= sc0;
+            o[nd][2] *= sc1;
+            o[nd][3] *= sc1;
+        }
+#pragma unroll
+        for (int kk = 0; kk < MMA_KT / 16; kk++) {
+            uint32_t pa[4];
+            pa[0] = pack_bf16(s[2 * kk][0], s[2 * kk][1]);
+            pa[1] = pack_bf16(s[2 * kk][2], s[2 * kk][3]);
+            pa[2] = pack_bf16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+            pa[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+            for (int nd = 0; nd < ND; nd++) {
+                const uint32_t b0 = *reinterpret_cast<const uint32_t *>(&Vt[nd * 8 + g][kk * 16 + tq * 2]);
+                const uint32_t b1 = *reinterpret_cast<const uint32_t *>(&Vt[nd * 8 + g][kk * 16 + 8 + tq * 2]);
+                mma_16816(o[nd], pa, b0, b1);
+            }
+        }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.f / l0, i1 = 1.f / l1;
+#pragma unroll
+    for (int nd = 0; nd < ND; nd++) {
+        const int c = head * HD + nd * 8 + tq * 2;
+        if (r0 < len) *reinterpret_cast<float2 *>(out + (size_t)(t0 + r0) * d + c) = make_float2(o[nd][0] * i0, o[nd][1] * i0);
+        if (r1 < len) *reinterpret_cast<float2 *>(out + (size_t)(t0 + r1) * d + c) = make_float2(o[nd][2] * i1, o[nd][3] * i1);
+    }
+}
+
+// mean over the tokens of a sequence (bert.cpp: mul_mat with a vector of 1/N), then x / sqrt(sum x^2)
+__global__ void __launch_bounds__(LN_THREADS) bert_mean_pool_l2_kernel(const float *x, const int32_t *offs, int d, float *out) {
+    __shared__ float red[32];
+    const int t0 = offs[blockIdx.x], n = offs[blockIdx.x + 1] - t0;
+    float ss = 0.f;
+    float *o = out + (size_t)blockIdx.x * d;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) {
+        float s = 0.f;
+        for (int t = 0; t < n; t++) s += x[(size_t)(t0 + t) * d + i];
+        s /= (float)n;
+        o[i] = s;
+        ss += s * s;
+    }
+    const float inv = rsqrtf(block_sum(ss, red));
+    for (int i = threadIdx.x; i < d; i += blockDim.x) o[i] *= inv;
+}
+
+} // namespace
+
+void launch_bert_embed_ln(float *x, const float *pos_embd, const float *type0, const int32_t *pos, const float *w, const float *b,
+                          int n_tok, int d, float eps, cudaStream_t s) {
+    bert_embed_ln_kernel<<<n_tok, LN_THREADS, 0, s>>>(x, pos_embd, type0, pos, w, b, d, eps);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_bert_bias_gelu(float *x, const float *bias, int n_tok, int n, cudaStream_t s) {
+    const int64_t total = (int64_t)n_tok * n;
+    bert_bias_gelu_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(x, bias, total, n);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_bert_bias_residual_ln(float *x, const float *h, const float *bias, const float *w, const float *b, int n_tok, int d,
+                                  float eps, cudaStream_t s) {
+    bert_bias_residual_ln_kernel<<<n_tok, LN_THREADS, 0, s>>>(x, h, bias, w, b, d, eps);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_bert_attention(const float *q, const float *k, const float *v, const float *bq, const float *bk, const float *bv,
+                           const int32_t *offs, int n_seq, int max_len, int n_head, int hd, float *out, cudaStream_t s) {
+    const bool simple = getenv("B200LLM_BERT_ATT_SIMPLE") && atoi(getenv("B200LLM_BERT_ATT_SIMPLE")) != 0;
+    if (!simple && (hd == 64 || hd == 32)) { // tensor-core attention; the fp32 CUDA-core kernel below is kept for A/B checks
+        const dim3 grid((max_len + MMA_QB - 1) / MMA_QB, n_head, n_seq);
+        if (hd == 64) bert_attention_mma_kernel<64><<<grid, 128, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
+        else bert_attention_mma_kernel<32><<<grid, 128, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
+        g_launch_count++;
+        B2_CUDA(cudaGetLastError());
+        return;
+    }
+    const dim3 grid((max_len + ATT_QB - 1) / ATT_QB, n_head, n_seq);
+    if (hd == 64) bert_attention_kernel<64><<<grid, ATT_WARPS * 32, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
+    else if (hd == 32) bert_attention_kernel<32><<<grid, ATT_WARPS * 32, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
+    else throw Error(B2_EUNSUPPORTED, "bert: head size must be 32 or 64");
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_bert_mean_pool_l2(const float *x, const int32_t *offs, int n_seq, int d, float *out, cudaStream_t s) {
+    bert_mean_pool_l2_kernel<<<n_seq, LN_THREADS, 0, s>>>(x, offs, d, out);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+} // namespace b2

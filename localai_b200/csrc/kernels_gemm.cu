@@ -209,6 +209,31 @@ __global__ void swiglu_x_tiles_kernel(const float *__restrict__ g, const float *
     }
 }
 
+// gelu(x + bias) (ggml_gelu's tanh form) fused with the bf16 tile conversion: the BERT feed-forward activation
+__global__ void bias_gelu_x_tiles_kernel(const float *__restrict__ x, const float *__restrict__ bias, int n_tok, int64_t cols,
+                                         __nv_bfloat16 *__restrict__ out, int64_t m_pad) {
+    const int64_t kc_per_row = cols / 8;
+    const int64_t total = m_pad * kc_per_row;
+    const int64_t k_tiles = cols / GM_BK;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / kc_per_row;
+        const int k0 = (int)(i % kc_per_row) * 8;
+        float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (r < n_tok) {
+            const float4 xa = *(const float4 *)(x + r * cols + k0), xb = *(const float4 *)(x + r * cols + k0 + 4);
+            const float4 ba = *(const float4 *)(bias + k0), bb = *(const float4 *)(bias + k0 + 4);
+            const float t[8] = {xa.x + ba.x, xa.y + ba.y, xa.z + ba.z, xa.w + ba.w, xb.x + bb.x, xb.y + bb.y, xb.z + bb.z, xb.w + bb.w};
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[j] = 0.5f * t[j] * (1.f + tanhf(0.7978845608028654f * t[j] * (1.f + 0.044715f * t[j] * t[j])));
+        }
+        const int64_t mt = r / GM_BM, kt = k0 / GM_BK;
+        __nv_bfloat16 *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
+        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
+                                __floats2bfloat162_rn(v[6], v[7])};
+        *(int4 *)dst = *(const int4 *)p4;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ PTX helpers
 __device__ __forceinline__ uint32_t gm_s32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void gm_mbar_init(uint64_t *bar, uint32_t count) {
@@ -454,6 +479,16 @@ void launch_gemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok,
     const int64_t total = m_pad * (K / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
     swiglu_x_tiles_kernel<<<blocks, 256, 0, s>>>(gate, up, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_gemm_prepare_x_bias_gelu(const float *x, const float *bias, int n_tok, int64_t K, void *x_tiles, cudaStream_t s) {
+    B2_CHECK(K % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
+    const int64_t m_pad = align_up(n_tok, GM_BM);
+    const int64_t total = m_pad * (K / 8);
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+    bias_gelu_x_tiles_kernel<<<blocks, 256, 0, s>>>(x, bias, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }

@@ -1,0 +1,98 @@
+"""BERT embeddings backend (csrc/bert.cu; reference: backend/go/llm/bert/bert.go -> go-bert.cpp -> bert.cpp bert_eval).
+
+CPU part: the WordPiece tokeniser through the C ABI vs the restatement in oracle/bert_ref.py, and error behaviour.
+GPU part: hidden states and embeddings vs the float32 numpy restatement, plus the behaviour the reference's own test
+pins (core/http/app_test.go:856-881: vector length, same input -> same vector).
+
+Tolerance: the mat-muls run on bf16 operand tiles with fp32 accumulation (weights are F16 in the file), everything else
+is fp32: after every layer the rows are re-normalised, so the bf16 rounding (2^-8 relative per operand) shows as an
+absolute error on unit-variance values: max <= 8 % of the standard deviation, median <= 1.2 %, cosine(embedding) >= 0.9995.
+The default attention kernel also rounds Q, K, P and V to bf16 for its MMAs (the usual flash-attention numerics); the
+scores are exponentiated, so its worst element may be off by up to 15 % of the standard deviation -- the median bound
+and the cosine bound are the same for both kernels."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from localai_b200 import capi
+from oracle.bert_ref import BertRef
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "tools"))
+
+TEXTS = ["The quick brown fox, jumping over 2 lazy dogs! 日本語 xyzzy café", "", "   ", "Hello,World!!", "ÀB ünïcode ß", "a" * 700,
+         "tokenization embeddings unusedword \x7f ", "LocalAI is a drop-in replacement REST API", "[CLS] is just text here"]
+
+
+@pytest.fixture(scope="module")
+def bert_files(tmp_path_factory):
+    import make_bert_gguf as mb
+
+    d = tmp_path_factory.mktemp("bert")
+    return {n: mb.write_bert_gguf(str(d / f"{n}.gguf"), mb.BERT_ARCHS[n], seed=3) for n in ("bert-mini", "minilm-l3")}
+
+
+def test_wordpiece_matches_restatement(bert_files):
+    ref = BertRef(bert_files["bert-mini"])
+    with capi.Bert(bert_files["bert-mini"], vocab_only=True) as b:
+        assert b.info["n_embd"] == 256 and b.info["n_ctx"] == 512
+        for t in TEXTS:
+            got = b.tokenize(t)
+            assert got == ref.tokenize(t), t
+            assert got[0] == ref.cls and got[-1] == ref.sep and len(got) <= 512
+        assert b.tokenize("the fox") == [ref.cls, ref.tok_id["▁the"], ref.tok_id["▁fox"], ref.sep]
+        assert b.tokenize("foxes") == [ref.cls, ref.tok_id["▁fox"], ref.tok_id["e"], ref.tok_id["s"], ref.sep]
+        assert b.tokenize("\x7f") == [ref.cls, ref.unk, ref.sep]  # no piece: the whole word is [UNK]
+        with pytest.raises(RuntimeError, match="vocab_only"):
+            b.embed("x")
+
+
+def test_load_errors(model_files):
+    with pytest.raises(RuntimeError, match="bert"):
+        capi.Bert(model_files["micro_q8_0"], vocab_only=True)  # a llama GGUF is not a BERT encoder
+    with pytest.raises(RuntimeError):
+        capi.Bert("/nonexistent.gguf", vocab_only=True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("att", ["mma", "fp32"])
+@pytest.mark.parametrize("name", ["bert-mini", "minilm-l3"])
+def test_hidden_states_and_embedding_match_restatement(bert_files, name, att, monkeypatch):
+    """att: the tensor-core attention kernel (default) and the fp32 CUDA-core one kept beside it for A/B checks"""
+    monkeypatch.setenv("B200LLM_BERT_ATT_SIMPLE", "1" if att == "fp32" else "0")
+    ref = BertRef(bert_files[name])
+    with capi.Bert(bert_files[name]) as b:
+        for text in (TEXTS[0], TEXTS[7], "a" * 700, "x"):
+            ids = ref.tokenize(text)
+            want = ref.embed_tokens(ids, return_hidden=True)
+            got = b.hidden(ids)
+            err = np.abs(got - want)
+            print(f"{name} {att} n={len(ids)}: max err {err.max():.4f}, median {np.median(err):.5f}, std {want.std():.3f}")
+            max_tol = 0.15 if att == "mma" else 0.08
+            assert err.max() <= max_tol * want.std() and np.median(err) <= 0.012 * want.std(), (name, len(ids), err.max(), want.std())
+            e, we = b.embed_tokens(ids), ref.embed_tokens(ids)
+            assert e.shape == (ref.n_embd,) and abs(np.linalg.norm(e) - 1.0) < 1e-5
+            assert float(e @ we) >= 0.9995, float(e @ we)
+            assert np.array_equal(e, b.embed(text))  # Embeddings(text) = TokenEmbeddings(tokenize(text))
+
+
+@pytest.mark.gpu
+def test_same_input_same_vector_and_batch_equals_single(bert_files):
+    ref = BertRef(bert_files["minilm-l3"])
+    with capi.Bert(bert_files["minilm-l3"]) as b:
+        a1, a2 = b.embed("doc one"), b.embed("doc one")
+        assert a1.shape == (384,) and np.array_equal(a1, a2)  # app_test.go:856-881
+        assert not np.allclose(a1, b.embed("another document"), atol=1e-3)
+        seqs = [ref.tokenize(t) for t in TEXTS]
+        batch = b.embed_batch(seqs)  # ragged lengths 2..512 packed into one forward
+        for s, row in zip(seqs, batch):
+            single = b.embed_tokens(s)
+            # same kernels, but the GEMM sees another row count, so its split-K slices and with them the fp32 summation
+            # order differ; a last-bit difference can flip the bf16 rounding of an activation before the next GEMM
+            # (2^-8 relative on that element), which is what remains: 1e-3 on unit vectors, cosine 1 - 1e-5
+            assert np.abs(row - single).max() <= 1e-3 and float(row @ single) >= 1.0 - 1e-5
+        with pytest.raises(RuntimeError, match="tokens"):
+            b.embed_tokens(list(range(5)) * 200)  # 1000 tokens > context
+        with pytest.raises(RuntimeError, match="out of range"):
+            b.embed_tokens([1, 999999])
