@@ -153,10 +153,10 @@ __global__ void __launch_bounds__(ATT_WARPS * 32) bert_attention_kernel(const fl
 
 // The same attention on the warp-level tensor-core path: S = Q K^T and O = P V as m16n8k16 bf16 MMAs with fp32
 // accumulators, the running softmax in fp32 registers in between (the accumulator fragment of S is the A fragment of
-// the next product, so P never leaves registers).  One warp = 16 queries, one CTA = 4 warps = 64 queries of one head.
-// K is staged as bf16 [key][dim], V transposed as bf16 [dim][key]; both rows padded by 8 elements so that the 32 lanes of a
-// fragment load (8 rows x 4 words) fall into 32 different banks.
-constexpr int MMA_QB = 64, MMA_KT = 64;
+// the next product, so P never leaves registers).  One warp = 16 queries, one CTA = 8 warps = 128 queries of one head.
+// K and V are staged as bf16 [key][dim] rows padded by 8 elements, so that the 32 lanes of a K fragment load (8 rows x
+// 4 words) and the 16 row addresses of a transposing ldmatrix on V fall into different banks.
+constexpr int MMA_WARPS = 8, MMA_QB = 16 * MMA_WARPS, MMA_KT = 64, MMA_THREADS = 32 * MMA_WARPS;
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -169,13 +169,13 @@ __device__ __forceinline__ void mma_16816(float (&c)[4], const uint32_t (&a)[4],
 }
 
 template <int HD>
-__global__ void __launch_bounds__(128) bert_attention_mma_kernel(const float *__restrict__ q, const float *__restrict__ k,
+__global__ void __launch_bounds__(MMA_THREADS) bert_attention_mma_kernel(const float *__restrict__ q, const float *__restrict__ k,
                                                                  const float *__restrict__ v, const float *__restrict__ bq,
                                                                  const float *__restrict__ bk, const float *__restrict__ bv,
                                                                  const int32_t *__restrict__ offs, int n_head, float *__restrict__ out) {
     constexpr int KS = HD / 16, ND = HD / 8, NB = MMA_KT / 8, PAD = 8;
     __shared__ __align__(16) __nv_bfloat16 Kb[MMA_KT][HD + PAD];
-    __shared__ __align__(16) __nv_bfloat16 Vt[HD][MMA_KT + PAD];
+    __shared__ __align__(16) __nv_bfloat16 Vb[MMA_KT][HD + PAD];
     const int seq = blockIdx.z, head = blockIdx.y, t0 = offs[seq], len = offs[seq + 1] - t0;
     const int q0 = blockIdx.x * MMA_QB;
     if (q0 >= len) return;
@@ -201,12 +201,19 @@ __global__ void __launch_bounds__(128) bert_attention_mma_kernel(const float *__
     float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
     for (int k0 = 0; k0 < len; k0 += MMA_KT) {
         __syncthreads();
-        for (int i = tid; i < MMA_KT * HD; i += 128) {
-            const int r = i / HD, c = i % HD;
+        for (int i = tid; i < MMA_KT * (HD / 4); i += MMA_THREADS) { // four features per thread: 16-byte loads, 8-byte stores
+            const int r = i / (HD / 4), c = (i % (HD / 4)) * 4;
             const bool ok = k0 + r < len;
             const size_t gi = (size_t)(t0 + k0 + (ok ? r : 0)) * d + head * HD + c;
-            Kb[r][c] = __float2bfloat16_rn(ok ? k[gi] + bk[head * HD + c] : 0.f);
-            Vt[c][r] = __float2bfloat16_rn(ok ? v[gi] + bv[head * HD + c] : 0.f);
+            const float4 kv = *reinterpret_cast<const float4 *>(k + gi), vv = *reinterpret_cast<const float4 *>(v + gi);
+            const float4 kb = *reinterpret_cast<const float4 *>(bk + head * HD + c), vb = *reinterpret_cast<const float4 *>(bv + head * HD + c);
+            uint2 pk, pv;
+            pk.x = ok ? pack_bf16(kv.x + kb.x, kv.y + kb.y) : 0u;
+            pk.y = ok ? pack_bf16(kv.z + kb.z, kv.w + kb.w) : 0u;
+            pv.x = ok ? pack_bf16(vv.x + vb.x, vv.y + vb.y) : 0u;
+            pv.y = ok ? pack_bf16(vv.z + vb.z, vv.w + vb.w) : 0u;
+            *reinterpret_cast<uint2 *>(&Kb[r][c]) = pk;
+            *reinterpret_cast<uint2 *>(&Vb[r][c]) = pv;
         }
         __syncthreads();
         float s[NB][4];
@@ -265,8 +272,10 @@ __global__ void __launch_bounds__(128) bert_attention_mma_kernel(const float *__
             pa[3] = pack_bf16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
 #pragma unroll
             for (int nd = 0; nd < ND; nd++) {
-                const uint32_t b0 = *reinterpret_cast<const uint32_t *>(&Vt[nd * 8 + g][kk * 16 + tq * 2]);
-                const uint32_t b1 = *reinterpret_cast<const uint32_t *>(&Vt[nd * 8 + g][kk * 16 + 8 + tq * 2]);
+                // B fragment = V[16 keys][8 features] read transposed: lanes 0-15 name the 16 key rows
+                uint32_t b0, b1;
+                const uint32_t addr = (uint32_t)__cvta_generic_to_shared(&Vb[kk * 16 + (lane & 15)][nd * 8]);
+                asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0, %1}, [%2];" : "=r"(b0), "=r"(b1) : "r"(addr));
                 mma_16816(o[nd], pa, b0, b1);
             }
         }
@@ -284,19 +293,30 @@ __global__ void __launch_bounds__(128) bert_attention_mma_kernel(const float *__
     }
 }
 
-// mean over the tokens of a sequence (bert.cpp: mul_mat with a vector of 1/N), then x / sqrt(sum x^2)
-__global__ void __launch_bounds__(LN_THREADS) bert_mean_pool_l2_kernel(const float *x, const int32_t *offs, int d, float *out) {
-    __shared__ float red[32];
+// mean over the tokens of a sequence (bert.cpp: mul_mat with a vector of 1/N): one CTA per (sequence, 32 features),
+// 8 warps stride over the tokens; then x / sqrt(sum x^2) per sequence
+__global__ void __launch_bounds__(256) bert_mean_pool_kernel(const float *x, const int32_t *offs, int d, float *out) {
+    __shared__ float part[8][32];
     const int t0 = offs[blockIdx.x], n = offs[blockIdx.x + 1] - t0;
-    float ss = 0.f;
-    float *o = out + (size_t)blockIdx.x * d;
-    for (int i = threadIdx.x; i < d; i += blockDim.x) {
-        float s = 0.f;
-        for (int t = 0; t < n; t++) s += x[(size_t)(t0 + t) * d + i];
-        s /= (float)n;
-        o[i] = s;
-        ss += s * s;
+    const int f = blockIdx.y * 32 + (threadIdx.x & 31), w = threadIdx.x >> 5;
+    float s = 0.f;
+    if (f < d)
+        for (int t = w; t < n; t += 8) s += x[(size_t)(t0 + t) * d + f];
+    part[w][threadIdx.x & 31] = s;
+    __syncthreads();
+    if (w == 0 && f < d) {
+        float tot = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) tot += part[i][threadIdx.x];
+        out[(size_t)blockIdx.x * d + f] = tot / (float)n;
     }
+}
+
+__global__ void __launch_bounds__(LN_THREADS) bert_l2_normalize_kernel(float *out, int d) {
+    __shared__ float red[32];
+    float *o = out + (size_t)blockIdx.x * d;
+    float ss = 0.f;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) ss += o[i] * o[i];
     const float inv = rsqrtf(block_sum(ss, red));
     for (int i = threadIdx.x; i < d; i += blockDim.x) o[i] *= inv;
 }
@@ -329,8 +349,8 @@ void launch_bert_attention(const float *q, const float *k, const float *v, const
     const bool simple = getenv("B200LLM_BERT_ATT_SIMPLE") && atoi(getenv("B200LLM_BERT_ATT_SIMPLE")) != 0;
     if (!simple && (hd == 64 || hd == 32)) { // tensor-core attention; the fp32 CUDA-core kernel below is kept for A/B checks
         const dim3 grid((max_len + MMA_QB - 1) / MMA_QB, n_head, n_seq);
-        if (hd == 64) bert_attention_mma_kernel<64><<<grid, 128, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
-        else bert_attention_mma_kernel<32><<<grid, 128, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
+        if (hd == 64) bert_attention_mma_kernel<64><<<grid, MMA_THREADS, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
+        else bert_attention_mma_kernel<32><<<grid, MMA_THREADS, 0, s>>>(q, k, v, bq, bk, bv, offs, n_head, out);
         g_launch_count++;
         B2_CUDA(cudaGetLastError());
         return;
@@ -344,8 +364,9 @@ void launch_bert_attention(const float *q, const float *k, const float *v, const
 }
 
 void launch_bert_mean_pool_l2(const float *x, const int32_t *offs, int n_seq, int d, float *out, cudaStream_t s) {
-    bert_mean_pool_l2_kernel<<<n_seq, LN_THREADS, 0, s>>>(x, offs, d, out);
-    g_launch_count++;
+    bert_mean_pool_kernel<<<dim3(n_seq, (d + 31) / 32), 256, 0, s>>>(x, offs, d, out);
+    bert_l2_normalize_kernel<<<n_seq, LN_THREADS, 0, s>>>(out, d);
+    g_launch_count += 2;
     B2_CUDA(cudaGetLastError());
 }
 
