@@ -183,6 +183,86 @@ def run_reference(args, rank: int, emit):
     emit(line)
 
 
+def run_bert(args, rank, local_rank, world, ranks, emit, warmup):
+    """BASELINE config 4: BERT-base F16, texts of 512 WordPiece tokens, through b2_bert_embed_batch (host ids in, host
+    vectors out -- the call is synchronous, so every timed step holds its own H2D and D2H copies).  A step = one call
+    with 16 sequences (8192 tokens, larger than nothing L2 could keep: activations of a step are 25-100 MB per tensor)."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import make_bert_gguf as mb
+    from localai_b200 import capi
+
+    d = os.environ.get("B200LLM_BENCH_DIR", "/dev/shm/b200llm_bench" if os.path.isdir("/dev/shm") else "/tmp/b200llm_bench")
+    os.makedirs(d, exist_ok=True)
+    path = os.path.join(d, "bert_base_f16_seed0.gguf")
+    if rank == 0 and not os.path.exists(path):
+        mb.write_bert_gguf(path + ".tmp", mb.BERT_ARCHS["bert-base"], seed=0)
+        os.replace(path + ".tmp", path)
+    ranks.barrier()
+    per_call, n_tok = 16, 512
+    rng = np.random.default_rng(rank)
+    b = capi.Bert(path, device=local_rank)
+    ids = np.ascontiguousarray(np.concatenate([np.concatenate([[2], rng.integers(5, 300, n_tok - 2), [3]]) for _ in range(per_call)]), dtype=np.int32)
+    offs = (np.arange(per_call + 1) * n_tok).astype(np.int32)
+    out = np.empty((per_call, b.n_embd), dtype=np.float32)
+    L = capi.lib()
+
+    def step():
+        rc = L.b2_bert_embed_batch(b._h, ids.ctypes.data, offs.ctypes.data, per_call, out.ctypes.data)
+        assert rc == per_call, rc
+
+    for _ in range(warmup):
+        step()
+    ranks.barrier()
+    with ClockSampler(local_rank) as clk:
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step()
+        dt = time.perf_counter() - t0
+    ranks.barrier()
+    dt = ranks.max(dt)
+    seqs = ranks.sum(float(per_call * args.steps))
+    if rank != 0:
+        b.close()
+        return 0
+    a = mb.BERT_ARCHS["bert-base"]
+    lin = 2.0 * a.n_layer * (4 * a.n_embd * a.n_embd + 2 * a.n_embd * a.n_ff) * n_tok
+    att = 4.0 * n_tok * n_tok * a.n_embd * a.n_layer
+    flops_seq = lin + att
+    with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+        tf_peak = float(json.load(f).get("bf16_tflops_sustained", 1392.2))
+    achieved = flops_seq * per_call * args.steps / dt / 1e12  # per GPU: every rank runs the same number of texts
+    cpu = None
+    try:  # the numpy restatement on ONE 512-token text (about 2 s per text on a few cores)
+        from oracle.bert_ref import BertRef
+
+        ref = BertRef(path)
+        t1 = time.perf_counter()
+        ref.embed_tokens(ids[:n_tok])
+        cpu_dt = time.perf_counter() - t1
+        cpu = {"value": 1.0 / cpu_dt, "unit": "seq/s", "cores": os.cpu_count(), "kind": "port",
+               "sample": "1 text of 512 tokens through oracle/bert_ref.py (numpy float32, BLAS threads)"}
+    except Exception as e:  # noqa: BLE001
+        log(f"[bench] cpu baseline skipped: {e}")
+    v = seqs / dt
+    launches_per_step = 2 + a.n_layer * 10 + 2
+    emit({"metric": "BERT-base F16 embeddings seq/s (512-token texts)", "value": v, "unit": "seq/s", "n_gpus": world, "steps": args.steps,
+          "warmup": warmup, "ms_per_step": dt * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+          "dtype": "bf16 operands, f32 accumulate (weights F16 in the file)", "data": "synthetic",
+          "config": {"workload": "bert-base f16 random-init GGUF, 16 texts x 512 tokens per b2_bert_embed_batch call", "replicas": world,
+                     "l2": "inputs larger than L2: a step moves 25-100 MB per activation tensor, 24 tensors per layer pass"},
+          "e2e": {"value": v, "unit": "seq/s", "h2d_bytes_per_step": int(ids.nbytes + offs.nbytes), "d2h_bytes_per_step": int(out.nbytes),
+                  "path": "b2_bert_embed_batch (host ids -> host vectors, synchronous); value is this same measurement"},
+          "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step,
+          "roofline": {"bound": "tensor", "kernel": "whole step (gemm_tcgen05_kernel x 4 + attention per layer)", "achieved": achieved,
+                       "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak, "traffic": None,
+                       "flops_per_seq": flops_seq, "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"},
+          "cpu_baseline": cpu, "clocks": clk.summary()})
+    b.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -196,6 +276,8 @@ def main():
     ap.add_argument("--prefill", type=int, default=2048)
     ap.add_argument("--batch", type=int, default=64, help="concurrent streams for the batched-decode extra")
     ap.add_argument("--no-extras", action="store_true", help="skip the b=64 / prefill / cpu legs")
+    ap.add_argument("--workload", default="decode", choices=["decode", "bert"],
+                    help="decode: the headline (Llama-3-8B Q4_K_M b=1 decode); bert: BASELINE config 4, BERT-base F16 embeddings of 512-token texts")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -223,6 +305,8 @@ def main():
 
     if capi.device_count() < 1:
         raise SystemExit("bench.py: no sm_100 device visible; there is no CPU fallback for the b200 arm")
+    if args.workload == "bert":
+        return run_bert(args, rank, local_rank, world, ranks, emit, warmup)
     path, info = ensure_model(args.arch, args.preset, args.seed, rank, barrier)
     n_par = max(1, args.batch)
     n_ctx_slot = max(args.prefill, args.ctx + args.steps + warmup) + 128
