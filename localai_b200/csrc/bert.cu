@@ -246,19 +246,28 @@ void BertModel::forward(const int32_t *ids, const int32_t *offs, int n_seq) {
     const int d = n_embd, ff = n_ff;
     launch_dequant_rows(tok_embd_, ids_dev_, 0, T, x_, d, s);
     launch_bert_embed_ln(x_, pos_embd_, type0_, pos_dev_, ln0_w_, ln0_b_, T, d, eps, s);
-    for (const BertLayer &L : layers_) {
-        launch_gemm_prepare_x(x_, d, T, d, x_tiles_, s);
+    // LayerNorm rows of up to 2048 features are produced together with their operand tiles (one pass over the row)
+    const bool fused_ln = d <= 2048;
+    auto ln = [&](const float *bias, const float *w, const float *b) {
+        if (fused_ln) {
+            launch_gemm_prepare_x_bias_residual_ln(x_, h_, bias, w, b, T, d, eps, x_tiles_, s);
+        } else {
+            launch_bert_bias_residual_ln(x_, h_, bias, w, b, T, d, eps, s);
+            launch_gemm_prepare_x(x_, d, T, d, x_tiles_, s);
+        }
+    };
+    launch_gemm_prepare_x(x_, d, T, d, x_tiles_, s);
+    for (const BertLayer &L : layers_) { // on entry x_tiles_ holds x_
         const GemmJob qkv[3] = {{&L.wq, L.tq, true, q_, d}, {&L.wk, L.tk, true, k_, d}, {&L.wv, L.tv, true, v_, d}};
         launch_gemm_tc_multi(qkv, 3, x_tiles_, T, nullptr, 0, splitk_, splitk_bytes_, s);
         launch_bert_attention(q_, k_, v_, L.bq, L.bk, L.bv, offs_dev_, n_seq, max_len, n_head, head_dim, att_, s);
         launch_gemm_prepare_x(att_, d, T, d, x_tiles_, s);
         launch_gemm_tc(L.wo, x_tiles_, T, h_, d, nullptr, 0, L.to, true, splitk_, splitk_bytes_, s);
-        launch_bert_bias_residual_ln(x_, h_, L.bo, L.ln1_w, L.ln1_b, T, d, eps, s);
-        launch_gemm_prepare_x(x_, d, T, d, x_tiles_, s);
+        ln(L.bo, L.ln1_w, L.ln1_b);
         launch_gemm_tc(L.up, x_tiles_, T, u_, ff, nullptr, 0, L.tup, true, splitk_, splitk_bytes_, s);
         launch_gemm_prepare_x_bias_gelu(u_, L.bup, T, ff, x_tiles_, s); // gelu(u + b) straight into the operand tiles
         launch_gemm_tc(L.down, x_tiles_, T, h_, d, nullptr, 0, L.tdown, true, splitk_, splitk_bytes_, s);
-        launch_bert_bias_residual_ln(x_, h_, L.bdown, L.ln2_w, L.ln2_b, T, d, eps, s);
+        ln(L.bdown, L.ln2_w, L.ln2_b);
     }
 }
 

@@ -149,6 +149,9 @@ void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t 
 void launch_gemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const float *w, int n_tok, int64_t K, float eps, void *x_tiles,
                                    float *xn_out, cudaStream_t s);
 void launch_gemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
+// x = LayerNorm(x + h + bias) * w + b, written back as fp32 rows and as operand tiles (BERT; K <= 2048)
+void launch_gemm_prepare_x_bias_residual_ln(float *x, const float *h, const float *bias, const float *w, const float *b, int n_tok,
+                                            int64_t K, float eps, void *x_tiles, cudaStream_t s);
 // gelu(x + bias): the BERT feed-forward activation (bert.cu)
 void launch_gemm_prepare_x_bias_gelu(const float *x, const float *bias, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
 // quantised W -> bf16 operand tiles (gemm_w_tiles_bytes of them)

@@ -184,6 +184,72 @@ rmsnorm_x_tiles_kernel(const float *__restrict__ x, int64_t x_stride, const floa
     }
 }
 
+// BERT: x = LayerNorm(x + h + bias) * w + b (ggml_norm: mean, variance of the centred values), the row written back as
+// fp32 (it is the next residual) AND as bf16 operand tiles of the next GEMM.  One CTA per token row, the row lives in
+// registers (8 features per thread, cols <= 2048); rows >= n_tok of the last tile get zero tiles.
+__global__ void __launch_bounds__(256)
+bias_residual_ln_x_tiles_kernel(float *__restrict__ x, const float *__restrict__ h, const float *__restrict__ bias,
+                                const float *__restrict__ w, const float *__restrict__ b, int n_tok, int64_t cols, float eps,
+                                __nv_bfloat16 *__restrict__ out) {
+    const int r = blockIdx.x; // < m_pad
+    const int64_t k_tiles = cols / GM_BK;
+    __nv_bfloat16 *tile0 = out + (int64_t)(r / GM_BM) * k_tiles * (int64_t)(GM_BM * GM_BK);
+    __shared__ float red[2][8];
+    const int64_t k0 = (int64_t)threadIdx.x * 8;
+    const bool mine = k0 < cols;
+    float v[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (r < n_tok) { // block-uniform
+        float s = 0.f;
+        if (mine) {
+            float *xr = x + (int64_t)r * cols + k0;
+            const float *hr = h + (int64_t)r * cols + k0;
+            const float4 xa = *(const float4 *)xr, xb = *(const float4 *)(xr + 4), ha = *(const float4 *)hr, hb = *(const float4 *)(hr + 4);
+            const float4 ba = *(const float4 *)(bias + k0), bb = *(const float4 *)(bias + k0 + 4);
+            v[0] = xa.x + (ha.x + ba.x); v[1] = xa.y + (ha.y + ba.y); v[2] = xa.z + (ha.z + ba.z); v[3] = xa.w + (ha.w + ba.w);
+            v[4] = xb.x + (hb.x + bb.x); v[5] = xb.y + (hb.y + bb.y); v[6] = xb.z + (hb.z + bb.z); v[7] = xb.w + (hb.w + bb.w);
+#pragma unroll
+            for (int j = 0; j < 8; j++) s += v[j];
+        }
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if ((threadIdx.x & 31) == 0) red[0][threadIdx.x >> 5] = s;
+        __syncthreads();
+        float tot = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) tot += red[0][i];
+        const float mean = tot / (float)cols;
+        float s2 = 0.f;
+        if (mine) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                v[j] -= mean;
+                s2 += v[j] * v[j];
+            }
+        }
+        for (int o = 16; o > 0; o >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+        if ((threadIdx.x & 31) == 0) red[1][threadIdx.x >> 5] = s2;
+        __syncthreads();
+        float tot2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) tot2 += red[1][i];
+        const float inv = rsqrtf(tot2 / (float)cols + eps);
+        if (mine) {
+            const float4 wa = *(const float4 *)(w + k0), wb = *(const float4 *)(w + k0 + 4);
+            const float4 ca = *(const float4 *)(b + k0), cb = *(const float4 *)(b + k0 + 4);
+            v[0] = v[0] * inv * wa.x + ca.x; v[1] = v[1] * inv * wa.y + ca.y; v[2] = v[2] * inv * wa.z + ca.z; v[3] = v[3] * inv * wa.w + ca.w;
+            v[4] = v[4] * inv * wb.x + cb.x; v[5] = v[5] * inv * wb.y + cb.y; v[6] = v[6] * inv * wb.z + cb.z; v[7] = v[7] * inv * wb.w + cb.w;
+            float *xr = x + (int64_t)r * cols + k0;
+            *(float4 *)xr = make_float4(v[0], v[1], v[2], v[3]);
+            *(float4 *)(xr + 4) = make_float4(v[4], v[5], v[6], v[7]);
+        }
+    }
+    if (mine) {
+        __nv_bfloat16 *dst = tile0 + (k0 / GM_BK) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset(r % GM_BM, (int)(k0 % GM_BK));
+        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
+                                __floats2bfloat162_rn(v[6], v[7])};
+        *(int4 *)dst = *(const int4 *)p4;
+    }
+}
+
 // silu(gate) * up (ggml arithmetic) fused with the bf16 tile conversion
 __global__ void swiglu_x_tiles_kernel(const float *__restrict__ g, const float *__restrict__ u, int n_tok, int64_t cols,
                                       __nv_bfloat16 *__restrict__ out, int64_t m_pad) {
@@ -479,6 +545,15 @@ void launch_gemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok,
     const int64_t total = m_pad * (K / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
     swiglu_x_tiles_kernel<<<blocks, 256, 0, s>>>(gate, up, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_gemm_prepare_x_bias_residual_ln(float *x, const float *h, const float *bias, const float *w, const float *b, int n_tok,
+                                            int64_t K, float eps, void *x_tiles, cudaStream_t s) {
+    B2_CHECK(K % GM_BK == 0 && K <= 2048, B2_EINVAL, "gemm: LayerNorm rows must be a multiple of 64 and at most 2048 wide");
+    const int m_pad = (int)align_up(n_tok, GM_BM);
+    bias_residual_ln_x_tiles_kernel<<<m_pad, 256, 0, s>>>(x, h, bias, w, b, n_tok, K, eps, (__nv_bfloat16 *)x_tiles);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
