@@ -25,6 +25,7 @@ class WpmTokenizer {
     explicit WpmTokenizer(const GGUFFile &f);
     std::vector<int32_t> tokenize(const std::string &text, int max_tokens) const; // [CLS] pieces... [SEP]
     int n_vocab() const { return (int)tokens_.size(); }
+    const std::string &text(int32_t id) const { return tokens_.at((size_t)id); }
     int32_t cls = 2, sep = 3, unk = 1;
 
   private:
@@ -46,6 +47,9 @@ class BertModel {
     BertModel(const BertModel &) = delete;
 
     std::vector<int32_t> tokenize(const std::string &text) const { return tok_.tokenize(text, n_ctx); }
+    int32_t cls_id() const { return tok_.cls; }
+    int32_t sep_id() const { return tok_.sep; }
+    std::string token_text(int32_t id) const { return id >= 0 && id < n_vocab ? tok_.text(id) : std::string(); }
     // ids: the sequences back to back; offs[n_seq + 1]: where each starts; out_host: [n_seq][n_embd]
     void embed(const int32_t *ids, const int32_t *offs, int n_seq, float *out_host);
     // the last hidden states [n_tokens][n_embd] of one sequence (parity tests)

@@ -5,6 +5,9 @@
 #include <algorithm>
 #include <cstring>
 
+#include <chrono>
+
+#include "bert.h"
 #include "scheduler.h"
 #include "tokenizer.h"
 
@@ -12,6 +15,16 @@ namespace b2 {
 
 Engine::Engine(const b2_load_opts &o) : opts_(o) {
     GGUFFile f(o.model_path);
+    if (f.get_s("general.architecture", "") == "bert") { // encoder: its own loader, tokeniser and forward (bert.cu)
+        bert_.reset(new BertModel(o.model_path, o.device, o.vocab_only != 0));
+        read_hparams_only(f);
+        vocab_hp_.n_vocab = bert_->n_vocab;
+        vocab_hp_.n_ctx_train = bert_->n_ctx;
+        tok_model_ = "bert";
+        bos_ = bert_->cls_id();
+        eos_ = bert_->sep_id();
+        return;
+    }
     if (!o.vocab_only) model_.reset(new Model(f, o));
     else read_hparams_only(f);
     tok_.reset(new Tokenizer(f));
@@ -40,11 +53,13 @@ void Engine::read_hparams_only(const GGUFFile &f) {
 }
 
 Model &Engine::model() {
+    B2_CHECK(!bert_, B2_EUNSUPPORTED, "this entry point needs a decoder model; a BERT encoder serves Embedding requests only");
     B2_CHECK(model_ != nullptr, B2_ESTATE, "engine was created with vocab_only: no model is loaded");
     return *model_;
 }
 
 Engine::~Engine() {
+    bert_.reset();
     sched_.reset(); // joins the engine thread before the model goes away
     tok_.reset();
     model_.reset();
@@ -62,6 +77,7 @@ void Engine::model_info(b2_model_info_t *o) {
         o->decode_stream_bytes = model_->decode_stream_bytes;
         o->kv_bytes_per_pos = model_->kv_bytes_per_pos;
     }
+    if (bert_) o->weight_bytes_device = bert_->weight_bytes;
     o->bos_id = bos_; o->eos_id = eos_; o->eot_id = eot_; o->add_bos = add_bos_ ? 1 : 0;
     o->rms_eps = h.rms_eps; o->rope_freq_base = h.rope_base; o->rope_freq_scale = h.rope_scale;
     snprintf(o->arch, sizeof(o->arch), "%s", h.arch.c_str());
@@ -70,17 +86,88 @@ void Engine::model_info(b2_model_info_t *o) {
 }
 
 std::vector<int32_t> Engine::tokenize(const std::string &text, bool add_bos, bool parse_special) {
+    if (bert_) return bert_->tokenize(text); // [CLS] ... [SEP] always, as bert.cpp and llama.cpp's WordPiece do
     return tok_->tokenize(text, add_bos, parse_special);
 }
 // special = true, like common's llama_token_to_piece(ctx, token) default used at grpc-server.cpp:1012
-std::string Engine::token_to_piece(int32_t t) { return tok_->token_to_piece(t, true); }
+std::string Engine::token_to_piece(int32_t t) { return bert_ ? bert_->token_text(t) : tok_->token_to_piece(t, true); }
 
-int64_t Engine::submit(const b2_request &r) { return sched().submit(r); }
-int Engine::poll(int64_t id, b2_event *ev, int timeout_ms) { return sched().poll(id, ev, timeout_ms); }
-int Engine::cancel(int64_t id) { return sched().cancel(id); }
-int Engine::embed_result(int64_t id, float *out, int cap) { return sched().embed_result(id, out, cap); }
-int Engine::release(int64_t id) { return sched().release(id); }
-void Engine::metrics(b2_metrics_t *out) { sched().metrics(out); }
+int64_t Engine::submit(const b2_request &r) {
+    if (!bert_) return sched().submit(r);
+    B2_CHECK(r.embedding_mode, B2_EUNSUPPORTED, "a BERT encoder serves Embedding requests only");
+    std::vector<int32_t> ids;
+    if (r.prompt_ids && r.n_prompt_ids > 0) ids.assign(r.prompt_ids, r.prompt_ids + r.n_prompt_ids);
+    else ids = bert_->tokenize(std::string(r.prompt ? r.prompt : "", r.prompt ? r.prompt_len : 0));
+    BertResult res;
+    res.n_prompt = (int)ids.size();
+    const auto t0 = std::chrono::steady_clock::now();
+    if (opts_.embeddings) { // embeddings disabled -> zeros, as send_embedding does (grpc-server.cpp:1301-1310)
+        res.embedding.resize(bert_->n_embd);
+        const int32_t offs[2] = {0, (int32_t)ids.size()};
+        bert_->embed(ids.data(), offs, 1, res.embedding.data());
+    } else {
+        res.embedding.assign(bert_->n_embd, 0.f);
+    }
+    res.ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    std::lock_guard<std::mutex> lk(bert_mu_);
+    const int64_t id = bert_next_id_++;
+    bert_results_.emplace(id, std::move(res));
+    return id;
+}
+
+int Engine::poll(int64_t id, b2_event *ev, int timeout_ms) {
+    if (!bert_) return sched().poll(id, ev, timeout_ms);
+    std::lock_guard<std::mutex> lk(bert_mu_);
+    auto it = bert_results_.find(id);
+    B2_CHECK(it != bert_results_.end(), B2_ESTATE, "unknown request id");
+    if (it->second.polled) return B2_ETIMEOUT; // the one (final) event was handed out already
+    it->second.polled = true;
+    const uint32_t sz = ev->struct_size ? std::min<uint32_t>(ev->struct_size, sizeof(b2_event)) : (uint32_t)sizeof(b2_event);
+    b2_event out;
+    memset(&out, 0, sizeof(out));
+    out.struct_size = sz;
+    out.flags = B2_EV_FINAL | B2_EV_EMBEDDING;
+    out.text = "";
+    out.n_prompt_tokens = it->second.n_prompt;
+    out.n_embd = (int)it->second.embedding.size();
+    out.t_prompt_ms = it->second.ms;
+    memcpy(ev, &out, sz);
+    return 0;
+}
+
+int Engine::cancel(int64_t id) {
+    if (!bert_) return sched().cancel(id);
+    std::lock_guard<std::mutex> lk(bert_mu_);
+    B2_CHECK(bert_results_.count(id), B2_ESTATE, "unknown request id");
+    return 0;
+}
+
+int Engine::embed_result(int64_t id, float *out, int cap) {
+    if (!bert_) return sched().embed_result(id, out, cap);
+    std::lock_guard<std::mutex> lk(bert_mu_);
+    auto it = bert_results_.find(id);
+    B2_CHECK(it != bert_results_.end(), B2_ESTATE, "unknown request id");
+    const int n = (int)it->second.embedding.size();
+    if (n > cap) return -n;
+    memcpy(out, it->second.embedding.data(), (size_t)n * 4);
+    return n;
+}
+
+int Engine::release(int64_t id) {
+    if (!bert_) return sched().release(id);
+    std::lock_guard<std::mutex> lk(bert_mu_);
+    B2_CHECK(bert_results_.erase(id) == 1, B2_ESTATE, "unknown request id");
+    return 0;
+}
+
+void Engine::metrics(b2_metrics_t *out) {
+    if (bert_) {
+        memset(out, 0, sizeof(*out));
+        return;
+    }
+    sched().metrics(out);
+}
+
 Scheduler &Engine::sched() {
     B2_CHECK(sched_ != nullptr, B2_ESTATE, "engine was created with vocab_only: no model is loaded");
     return *sched_;

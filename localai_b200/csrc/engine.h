@@ -2,6 +2,7 @@
 // Replaces llama_server_context (backend/cpp/llama/grpc-server.cpp:394-2036) and the task/result queues
 // (backend/cpp/llama/utils.hpp:192-409).
 #pragma once
+#include <map>
 #include <memory>
 #include <mutex>
 #include <string>
@@ -14,6 +15,7 @@ namespace b2 {
 
 class Tokenizer;
 class Scheduler;
+class BertModel;
 
 class Engine {
   public:
@@ -53,6 +55,13 @@ class Engine {
     void prefill_chunks(int slot, const int32_t *tokens, int n, int n_past, bool want_logits);
 
     std::unique_ptr<Model> model_;
+    // general.architecture = "bert": the engine serves Embedding requests only (what the reference's llama-cpp backend does
+    // with a BERT GGUF and `embeddings: true`, grpc-server.cpp:2410-2432); requests are computed inside b2_submit
+    std::unique_ptr<BertModel> bert_;
+    struct BertResult { std::vector<float> embedding; int n_prompt = 0; double ms = 0; bool polled = false; };
+    std::map<int64_t, BertResult> bert_results_;
+    std::mutex bert_mu_;
+    int64_t bert_next_id_ = 1;
     std::unique_ptr<Tokenizer> tok_;
     std::unique_ptr<Scheduler> sched_;
     std::mutex dev_mu_; // serialises users of the device-side scratch buffers

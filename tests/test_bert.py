@@ -96,3 +96,39 @@ def test_same_input_same_vector_and_batch_equals_single(bert_files):
             b.embed_tokens(list(range(5)) * 200)  # 1000 tokens > context
         with pytest.raises(RuntimeError, match="out of range"):
             b.embed_tokens([1, 999999])
+
+
+def test_engine_face_on_a_bert_gguf_vocab_only(bert_files):
+    """b2_create on a BERT GGUF (what the llama-cpp backend is given with `embeddings: true`): metadata + WordPiece"""
+    ref = BertRef(bert_files["bert-mini"])
+    with capi.Engine(bert_files["bert-mini"], vocab_only=True) as e:
+        assert e.info.arch == b"bert" and e.info.n_embd == 256 and e.info.tokenizer_model == b"bert"
+        assert e.tokenize("The quick brown fox!") == ref.tokenize("The quick brown fox!")
+        assert e.token_to_piece(ref.tok_id["▁fox"]) == "▁fox".encode()
+
+
+@pytest.mark.gpu
+def test_engine_embedding_request_on_a_bert_gguf(bert_files):
+    """Embedding through b2_submit / b2_poll / b2_embed_result (grpc-server.cpp:2410-2432) = the bert backend's vector;
+    anything but an Embedding request is refused"""
+    text = "LocalAI serves embeddings"
+    with capi.Bert(bert_files["minilm-l3"]) as b:
+        want = b.embed(text)
+    with capi.Engine(bert_files["minilm-l3"], embeddings=True) as e:
+        rid = e.submit(prompt=text, embedding_mode=True)
+        evs = list(e.events(rid))
+        assert len(evs) == 1 and evs[0]["flags"] & capi.EV_FINAL and evs[0]["flags"] & capi.EV_EMBEDDING and evs[0]["n_embd"] == 384
+        vec = e.embed_result(rid)
+        e.release(rid)
+        assert np.array_equal(vec, want)
+        rid = e.submit(prompt_ids=e.tokenize(text), embedding_mode=True)
+        list(e.events(rid))
+        assert np.array_equal(e.embed_result(rid), want)
+        with pytest.raises(RuntimeError, match="Embedding requests only"):
+            e.submit(prompt=text, n_predict=4)
+        with pytest.raises(RuntimeError, match="decoder"):
+            e.eval([1, 2, 3])
+    with capi.Engine(bert_files["minilm-l3"], embeddings=False) as e:
+        rid = e.submit(prompt=text, embedding_mode=True)
+        list(e.events(rid))
+        assert not e.embed_result(rid).any()  # embeddings disabled -> zeros (grpc-server.cpp:1301-1310)
