@@ -2,6 +2,7 @@
 #include "bert.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace b2 {
@@ -247,7 +248,7 @@ void BertModel::forward(const int32_t *ids, const int32_t *offs, int n_seq) {
     launch_dequant_rows(tok_embd_, ids_dev_, 0, T, x_, d, s);
     launch_bert_embed_ln(x_, pos_embd_, type0_, pos_dev_, ln0_w_, ln0_b_, T, d, eps, s);
     // LayerNorm rows of up to 2048 features are produced together with their operand tiles (one pass over the row)
-    const bool fused_ln = d <= 2048;
+    const bool fused_ln = d <= 2048 && !(getenv("B200LLM_BERT_UNFUSED_LN") && atoi(getenv("B200LLM_BERT_UNFUSED_LN")) != 0);
     auto ln = [&](const float *bias, const float *w, const float *b) {
         if (fused_ln) {
             launch_gemm_prepare_x_bias_residual_ln(x_, h_, bias, w, b, T, d, eps, x_tiles_, s);

@@ -86,8 +86,7 @@ class BertModel {
 
 void launch_bert_embed_ln(float *x, const float *pos_embd, const float *type0, const int32_t *pos, const float *w, const float *b,
                           int n_tok, int d, float eps, cudaStream_t s);
-void launch_bert_bias_gelu(float *x, const float *bias, int n_tok, int n, cudaStream_t s);
-// x = LayerNorm(x + h + bias) * w + b
+// x = LayerNorm(x + h + bias) * w + b (rows wider than 2048 features; narrower rows take the fused kernel of kernels_gemm.cu)
 void launch_bert_bias_residual_ln(float *x, const float *h, const float *bias, const float *w, const float *b, int n_tok, int d,
                                   float eps, cudaStream_t s);
 // bidirectional attention inside each sequence; q/k/v: [n_tok][n_head * hd] without their biases (added on load)

@@ -59,14 +59,6 @@ __global__ void __launch_bounds__(LN_THREADS) bert_bias_residual_ln_kernel(float
     layernorm_row(row, w, b, d, eps, red);
 }
 
-// ggml_gelu: 0.5 x (1 + tanh(sqrt(2/pi) x (1 + 0.044715 x^2)))
-__global__ void bert_bias_gelu_kernel(float *x, const float *bias, int64_t total, int n) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    const float v = x[i] + bias[i % n];
-    x[i] = 0.5f * v * (1.f + tanhf(0.7978845608028654f * v * (1.f + 0.044715f * v * v)));
-}
-
 // One CTA = one head of one sequence x QB queries; K/V go through shared memory in tiles of KT keys, the softmax is
 // the running (flash) form, exact in fp32.  Lane l owns keys l, l + 32 of a tile for the scores and features
 // l, l + 32 of the output.
@@ -326,13 +318,6 @@ __global__ void __launch_bounds__(LN_THREADS) bert_l2_normalize_kernel(float *ou
 void launch_bert_embed_ln(float *x, const float *pos_embd, const float *type0, const int32_t *pos, const float *w, const float *b,
                           int n_tok, int d, float eps, cudaStream_t s) {
     bert_embed_ln_kernel<<<n_tok, LN_THREADS, 0, s>>>(x, pos_embd, type0, pos, w, b, d, eps);
-    g_launch_count++;
-    B2_CUDA(cudaGetLastError());
-}
-
-void launch_bert_bias_gelu(float *x, const float *bias, int n_tok, int n, cudaStream_t s) {
-    const int64_t total = (int64_t)n_tok * n;
-    bert_bias_gelu_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(x, bias, total, n);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }

@@ -61,6 +61,7 @@ def test_load_errors(model_files):
 def test_hidden_states_and_embedding_match_restatement(bert_files, name, att, monkeypatch):
     """att: the tensor-core attention kernel (default) and the fp32 CUDA-core one kept beside it for A/B checks"""
     monkeypatch.setenv("B200LLM_BERT_ATT_SIMPLE", "1" if att == "fp32" else "0")
+    monkeypatch.setenv("B200LLM_BERT_UNFUSED_LN", "1" if att == "fp32" else "0")  # and the LayerNorm kernel for wide rows
     ref = BertRef(bert_files[name])
     with capi.Bert(bert_files[name]) as b:
         for text in (TEXTS[0], TEXTS[7], "a" * 700, "x"):
