@@ -221,6 +221,8 @@ BertModel::~BertModel() {
     if (vocab_only_) return;
     cudaSetDevice(device_);
     if (stream_) cudaStreamSynchronize(stream_);
+    for (cudaGraphExec_t g : graphs_)
+        if (g) cudaGraphExecDestroy(g);
     for (void *p : allocs_) cudaFree(p);
     if (stream_) cudaStreamDestroy(stream_);
 }
@@ -230,20 +232,72 @@ void BertModel::forward(const int32_t *ids, const int32_t *offs, int n_seq) {
     B2_CHECK(n_seq > 0 && offs[0] == 0, B2_EINVAL, "bert: bad sequence offsets");
     const int T = offs[n_seq];
     B2_CHECK(T > 0 && T <= MAX_TOKENS, B2_EINVAL, "bert: between 1 and " + std::to_string(MAX_TOKENS) + " tokens per call");
-    std::vector<int32_t> pos(T);
     int max_len = 0;
     for (int s = 0; s < n_seq; s++) {
         const int len = offs[s + 1] - offs[s];
         B2_CHECK(len > 0 && len <= n_ctx, B2_EINVAL, "bert: a sequence has " + std::to_string(len) + " tokens; the model takes 1.." + std::to_string(n_ctx));
         max_len = std::max(max_len, len);
-        for (int i = 0; i < len; i++) pos[offs[s] + i] = i;
     }
     for (int i = 0; i < T; i++) B2_CHECK(ids[i] >= 0 && ids[i] < n_vocab, B2_EINVAL, "bert: token id out of range");
     B2_CUDA(cudaSetDevice(device_));
+    // One text per call (the reference API's shape) is launch-bound below ~128 tokens: its ~110 kernels are replayed from
+    // a CUDA graph captured per length bucket of 32 tokens.  The rows between the text's end and the bucket's are
+    // padding: token 0 at the following positions, computed and ignored (attention and pooling read the true length).
+    const bool debug_env = (getenv("B200LLM_BERT_UNFUSED_LN") && atoi(getenv("B200LLM_BERT_UNFUSED_LN"))) ||
+                           (getenv("B200LLM_BERT_ATT_SIMPLE") && atoi(getenv("B200LLM_BERT_ATT_SIMPLE"))) ||
+                           (getenv("B200LLM_BERT_NO_GRAPH") && atoi(getenv("B200LLM_BERT_NO_GRAPH")));
+    const bool bucketed = n_seq == 1 && !debug_env;
+    const int Tp = bucketed ? std::min((T + 31) / 32 * 32, n_ctx) : T;
+    std::vector<int32_t> pos(Tp), idp(Tp, 0);
+    memcpy(idp.data(), ids, (size_t)T * 4);
+    for (int s = 0; s < n_seq; s++)
+        for (int i = offs[s]; i < offs[s + 1]; i++) pos[i] = i - offs[s];
+    for (int i = T; i < Tp; i++) pos[i] = i;
     cudaStream_t s = stream_;
-    B2_CUDA(cudaMemcpyAsync(ids_dev_, ids, (size_t)T * 4, cudaMemcpyHostToDevice, s));
-    B2_CUDA(cudaMemcpyAsync(pos_dev_, pos.data(), (size_t)T * 4, cudaMemcpyHostToDevice, s));
+    B2_CUDA(cudaMemcpyAsync(ids_dev_, idp.data(), (size_t)Tp * 4, cudaMemcpyHostToDevice, s));
+    B2_CUDA(cudaMemcpyAsync(pos_dev_, pos.data(), (size_t)Tp * 4, cudaMemcpyHostToDevice, s));
     B2_CUDA(cudaMemcpyAsync(offs_dev_, offs, (size_t)(n_seq + 1) * 4, cudaMemcpyHostToDevice, s));
+    if (!bucketed) {
+        run_kernels(T, n_seq, max_len);
+        return;
+    }
+    B2_CUDA(cudaStreamSynchronize(s)); // the host vectors above go out of scope; also keeps the copies out of the capture
+    const int bi = Tp / 32;
+    if ((int)graphs_.size() <= bi) { graphs_.resize(bi + 1, nullptr); graph_seen_.resize(bi + 1, 0); }
+    if (graphs_[bi]) {
+        B2_CUDA(cudaGraphLaunch(graphs_[bi], s));
+    } else if (!graph_seen_[bi]) { // first time: eagerly (one-time kernel attributes are set outside any capture)
+        graph_seen_[bi] = 1;
+        run_kernels(Tp, 1, Tp);
+    } else if (graph_seen_[bi] == 2) { // capture failed once for this bucket: stay eager
+        run_kernels(Tp, 1, Tp);
+    } else {
+        cudaGraph_t gr = nullptr;
+        bool ok = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+        if (ok) {
+            try {
+                run_kernels(Tp, 1, Tp);
+            } catch (...) {
+                ok = false;
+            }
+            ok = (cudaStreamEndCapture(s, &gr) == cudaSuccess) && ok && gr;
+        }
+        if (ok) ok = cudaGraphInstantiate(&graphs_[bi], gr, 0) == cudaSuccess;
+        if (gr) cudaGraphDestroy(gr);
+        if (!ok) { // nothing ran: forget the error state and do this call the plain way
+            graphs_[bi] = nullptr;
+            graph_seen_[bi] = 2;
+            cudaGetLastError();
+            run_kernels(Tp, 1, Tp);
+        } else {
+            B2_CUDA(cudaGraphLaunch(graphs_[bi], s));
+        }
+    }
+}
+
+// the kernels of one forward; every input (ids, positions, offsets) is already in its device buffer
+void BertModel::run_kernels(int T, int n_seq, int max_len) {
+    cudaStream_t s = stream_;
     const int d = n_embd, ff = n_ff;
     launch_dequant_rows(tok_embd_, ids_dev_, 0, T, x_, d, s);
     launch_bert_embed_ln(x_, pos_embd_, type0_, pos_dev_, ln0_w_, ln0_b_, T, d, eps, s);

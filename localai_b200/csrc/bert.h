@@ -66,6 +66,9 @@ class BertModel {
     float *upload_f32(const GGUFFile &f, const std::string &name, int64_t rows, int64_t cols); // any type -> fp32 rows
     void *make_tiles(const DTensor &W);
     void forward(const int32_t *ids, const int32_t *offs, int n_seq);
+    void run_kernels(int T, int n_seq, int max_len);
+    std::vector<cudaGraphExec_t> graphs_; // one text per call: the forward per 32-token length bucket
+    std::vector<uint8_t> graph_seen_;
 
     WpmTokenizer tok_;
     bool vocab_only_ = false;
