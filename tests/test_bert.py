@@ -133,3 +133,20 @@ def test_engine_embedding_request_on_a_bert_gguf(bert_files):
         rid = e.submit(prompt=text, embedding_mode=True)
         list(e.events(rid))
         assert not e.embed_result(rid).any()  # embeddings disabled -> zeros (grpc-server.cpp:1301-1310)
+
+
+@pytest.mark.gpu
+def test_single_text_graph_replay_equals_plain_launches(bert_files, monkeypatch):
+    """one text per call: first call plain, second captures a CUDA graph for the 32-token length bucket, later ones
+    replay it; padding rows must not leak into the vector"""
+    rng = np.random.default_rng(4)
+    seqs = [[2] + rng.integers(5, 200, n - 2).tolist() + [3] for n in (3, 31, 32, 33, 100, 512)]
+    with capi.Bert(bert_files["bert-mini"]) as b:
+        first = [b.embed_tokens(s) for s in seqs]      # plain launches (lengths 31 and 32 share a bucket: 32 captures)
+        second = [b.embed_tokens(s) for s in seqs]     # capture + launch
+        third = [b.embed_tokens(s) for s in reversed(seqs)][::-1]  # replay, other order
+        for a, c, d in zip(first, second, third):
+            assert np.array_equal(a, c) and np.array_equal(a, d)
+        monkeypatch.setenv("B200LLM_BERT_NO_GRAPH", "1")  # no padding, no graph
+        for s, a in zip(seqs, first):
+            assert np.abs(b.embed_tokens(s) - a).max() <= 1e-6
