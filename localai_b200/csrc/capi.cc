@@ -203,6 +203,36 @@ int b2_mega_debug(b2_engine *e, long long *out, int cap) {
     B2_API_END(0)
 }
 
+// undocumented test hook (not part of the ABI header; needs no device): plan the decode kernel's weight streams for a
+// phase list given as 9 int64 per phase {kind, K, n_jobs, type0, rows0, type1, rows1, type2, rows2} and replay every
+// warp's walk over them.  Returns the stream bytes, or a negative error code when the planner is inconsistent.
+int64_t b2_mega_plan_check(const int64_t *desc, int n_phases, int n_cta, int64_t *n_tiles) {
+    B2_API_BEGIN
+    B2_CHECK(desc && n_phases > 0 && n_cta > 0, B2_EINVAL, "b2_mega_plan_check: bad arguments");
+    std::vector<MegaPhase> ph((size_t)n_phases);
+    for (int p = 0; p < n_phases; p++) {
+        const int64_t *d = desc + 9 * p;
+        MegaPhase &m = ph[(size_t)p];
+        m.kind = (int)d[0];
+        if (m.kind == PH_ATT) continue;
+        m.K = d[1];
+        m.n_jobs = (int)d[2];
+        B2_CHECK(m.n_jobs >= 1 && m.n_jobs <= 3, B2_EINVAL, "b2_mega_plan_check: 1..3 matrices per phase");
+        int64_t rows = 0;
+        for (int j = 0; j < m.n_jobs; j++) {
+            const int type = (int)d[3 + 2 * j];
+            m.job[j] = FusedJob{(const uint8_t *)(uintptr_t)(((uint64_t)p * 3 + j + 1) << 36), type, d[4 + 2 * j], device_row_stride(type, m.K)};
+            rows += d[4 + 2 * j];
+        }
+        m.fmt = act_format_for(m.job[0].type);
+        m.units = (int)(m.kind == PH_SWIGLU ? m.job[0].rows : rows / 2);
+        if (m.kind == PH_PLAIN && m.K / 256 > 32 && m.K <= 32768) m.xq_global = (uint8_t *)16; // as Model::build_mega: quantised once per GPU
+        B2_CHECK(mega_phase_prepare(m, n_cta), B2_EUNSUPPORTED, "phase " + std::to_string(p) + ": no lane mapping for this shape/type");
+    }
+    return mega_plan_check(ph.data(), n_phases, n_cta, n_tiles);
+    B2_API_END(0)
+}
+
 int b2_bench_gemv(b2_engine *e, int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch,
                   int *ggml_type) {
     B2_API_BEGIN
@@ -316,12 +346,15 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
         int n_sm = 0;
         B2_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0));
         B2_CHECK(mega_phase_prepare(ph, n_sm), B2_EUNSUPPORTED, "mega path: shape/type not supported");
+        MegaStreams ms;
+        ms.build(&ph, 1, n_sm, 0);
+        struct Guard { MegaStreams &m; ~Guard() { m.free(); } } guard{ms};
         DevBuf dph(sizeof(MegaPhase)), dbar(4096), dps(64);
         B2_CUDA(cudaMemcpy(dph.p, &ph, sizeof(ph), cudaMemcpyHostToDevice));
         B2_CUDA(cudaMemset(dbar.p, 0, 4096));
         B2_CUDA(cudaMemset(dps.p, 0, 64));
         MegaArgs a;
-        a.phases = dph.as<MegaPhase>(); a.n_phases = 1; a.pos = dps.as<int32_t>(); a.slot = dps.as<int32_t>() + 4;
+        a.phases = dph.as<MegaPhase>(); a.n_phases = 1; a.starts = ms.starts; a.pos = dps.as<int32_t>(); a.slot = dps.as<int32_t>() + 4;
         a.bar = dbar.as<unsigned>(); a.page_size = 32; a.page_shift = 5; a.max_pages = 1; a.hd = 64; a.n_head = 1; a.n_head_kv = 1;
         launch_decode_mega(a, n_sm, 0);
         B2_CUDA(cudaDeviceSynchronize());

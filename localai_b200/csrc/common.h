@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 
@@ -30,6 +31,22 @@ void set_last_error(const std::string &m);
     do {                                                           \
         if (!(cond)) throw ::b2::Error((code), std::string(msg));  \
     } while (0)
+
+// cudaFuncSetAttribute (opt-in shared memory above 48 KB) is PER DEVICE: one `static PerDeviceOnce` per launch site runs
+// its set-up the first time the site is reached with each device current, whichever host thread that is.
+struct PerDeviceOnce {
+    std::mutex mu;
+    uint64_t done = 0;
+    template <class F>
+    void run(F &&f) {
+        int dev = 0;
+        B2_CUDA(cudaGetDevice(&dev));
+        std::lock_guard<std::mutex> lk(mu);
+        if (dev < 64 && ((done >> dev) & 1)) return;
+        f();
+        if (dev < 64) done |= 1ull << dev;
+    }
+};
 
 // ---- tensor types (ggml ids) and on-device layouts -------------------------------------------------
 // Q4_K / Q5_K / F16 / F32 rows keep the GGUF layout (their blocks are 16-byte multiples).

@@ -113,9 +113,17 @@ struct MegaPhase {
     int rb[3] = {0, 0, 0};         // per matrix: bytes of one row's K-split = row pitch inside a staged tile
     int R[3] = {0, 0, 0};          // per matrix: rows per tile
 };
+// Where a warp's weight stream starts (one entry per (CTA, warp), built by MegaStreams).
+struct MegaStreamStart {
+    const uint8_t *src = nullptr; // first tile of the stream (16-byte aligned)
+    uint32_t size0 = 0, size1 = 0; // bytes of the first two tiles (0: the stream has no such tile)
+    int32_t first_p = 0;           // first phase in which this warp has tiles (n_phases: never)
+    int32_t pad[3] = {0, 0, 0};
+};
 struct MegaArgs {
     const MegaPhase *phases = nullptr; // device
     int n_phases = 0;
+    const MegaStreamStart *starts = nullptr; // device, [n_cta][warps per CTA]
     const int32_t *pos = nullptr, *slot = nullptr; // device, one sequence
     const float *rope_table = nullptr;
     const int32_t *page_table = nullptr;
@@ -132,11 +140,26 @@ struct MegaArgs {
     float *att_part_out = nullptr;   // [n_head][att_parts][hd] partial outputs
     unsigned *att_cnt = nullptr;     // [n_head][2] counters (scores written, partial outputs written), zero-initialised once
     unsigned att_base = 0;           // counter value when this launch starts; the host adds n_att_phases * att_parts per launch
-    long long *dbg = nullptr; // optional [n_cta][n_phases][4] clock64 stamps: start, after prologue, after stages, after barrier
+    long long *dbg = nullptr; // optional [n_cta][n_phases][16] clock64 stamps and per-phase cycle counts (scratch/mega_dbg.py)
 };
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s);
 bool mega_phase_prepare(MegaPhase &ph, int n_cta); // fills the lane geometry; false = shape/type the kernel has no mapping for
 bool mega_phase_supported(const MegaPhase &ph);
+// The weights of a phase list, repacked into one contiguous byte stream per (CTA, warp) in the order that warp
+// consumes them: tile = [16-byte header][n row-splits x rb bytes].  Built once per model (device-side scatter from the
+// GGUF-layout rows); the decode kernel then needs no schedule arithmetic, only "copy the next tile of my stream".
+struct MegaStreams {
+    uint8_t *data = nullptr;           // device, all streams
+    size_t bytes = 0;                  // of data
+    MegaStreamStart *starts = nullptr; // device
+    int64_t n_tiles = 0;
+    // phases: prepared (mega_phase_prepare) host copies.  Allocates with cudaMalloc; free() releases.
+    void build(const MegaPhase *phases, int n_phases, int n_cta, cudaStream_t s);
+    void free();
+};
+// host-only: plan the streams of a phase list and replay every warp's walk (throws b2::Error on an inconsistency);
+// returns the stream bytes.  Needs no device: the unit test of the planner (tests/test_capi_cpu.py).
+int64_t mega_plan_check(const MegaPhase *phases, int n_phases, int n_cta, int64_t *n_tiles);
 size_t mega_attention_ctx_limit(int hd);
 
 // --- tensor-core GEMM for prefill / batched decode (kernels_gemm.cu) ----------------------------------------------

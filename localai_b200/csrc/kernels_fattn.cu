@@ -175,11 +175,8 @@ void launch_fattn_prefill(const float *q, int t0, int n_q, int pos0, int slot, i
     const dim3 grid((n_q + FA_BQ - 1) / FA_BQ, n_head);
     const size_t smem = (size_t)4 * FA_BK * (hd + 8) * sizeof(__half);
     if (hd == 128) {
-        static thread_local bool cfg = false;
-        if (!cfg) {
-            B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            cfg = true;
-        }
+        static PerDeviceOnce cfg;
+        cfg.run([&] { B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); });
         fattn_prefill_kernel<128><<<grid, FA_THREADS, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
     } else if (hd == 64) {
         fattn_prefill_kernel<64><<<grid, FA_THREADS, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);

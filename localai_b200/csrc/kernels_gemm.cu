@@ -584,13 +584,10 @@ void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, 
     B2_CHECK(!residual || n_jobs == 1, B2_EINVAL, "gemm: the residual add needs a single matrix");
     const int64_t cols = jobs[0].W->cols;
     B2_CHECK(cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
-    static thread_local bool configured = false;
-    static thread_local uint32_t lbo = 128, sbo = 1024;
-    if (!configured) {
-        B2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GM_SMEM));
-        if (getenv("B200LLM_UMMA_SWAP") && atoi(getenv("B200LLM_UMMA_SWAP"))) { lbo = 1024; sbo = 128; }
-        configured = true;
-    }
+    static PerDeviceOnce configured;
+    configured.run([&] { B2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GM_SMEM)); });
+    static const bool umma_swap = getenv("B200LLM_UMMA_SWAP") && atoi(getenv("B200LLM_UMMA_SWAP"));
+    const uint32_t lbo = umma_swap ? 1024 : 128, sbo = umma_swap ? 128 : 1024;
     GemmArgs g;
     g.a_tiles = (const __nv_bfloat16 *)x_tiles;
     g.n_jobs = n_jobs;

@@ -1,27 +1,33 @@
 // kernels_mega.cu -- the whole batch-1 decode step as ONE persistent cooperative kernel (one CTA per SM).
 //
 // A decode step streams every weight byte exactly once (4.6 GB for Llama-3-8B Q4_K_M) and does ~2 integer MACs per
-// byte, so it lives or dies by how close HBM stays to 100 % busy.  Three things keep it there:
+// byte, so it lives or dies by how close HBM stays to 100 % busy.  Four things keep it there:
 //
-//   1. WEIGHTS STREAM THROUGH SHARED MEMORY, AHEAD OF THE MATH, ACROSS PHASE BOUNDARIES.  Every warp owns a private
-//      two-stage ring (2 x 12 KB) that it fills itself with bulk-async copies (cp.async.bulk -> mbarrier
-//      complete_tx, the TMA engine) from a static schedule of its weight tiles that runs over ALL phases of ALL
-//      layers.  Weights do not depend on activations, so while the CTA sits in a grid barrier or re-quantises the
-//      activation row its 16 stages (192 KB per SM, 28 MB per GPU) are already filling with the next phase's rows.
-//      No warp ever waits for another warp's data; the only CTA-wide syncs are the phase boundaries.
-//   2. ACTIVATIONS ARE REGISTER-STATIONARY.  A lane always handles the same K-slice of a row (K-quants: half a
+//   1. THE WEIGHTS ARE LAID OUT FOR THIS KERNEL.  At LoadModel the rows of every matrix are scattered (MegaStreams)
+//      into ONE CONTIGUOUS BYTE STREAM PER (CTA, WARP), in exactly the order that warp consumes them across all phases
+//      of all layers: tile = [16-byte header][n row-splits].  The header says what the tile is (type, rows, pitch,
+//      where the partial sums go), how many bytes the tile two ahead has, and whether it is the warp's last tile of
+//      its phase.  The kernel therefore holds no schedule at all: "copy the next tile of my stream" is one
+//      cp.async.bulk of a size read from shared memory.  (Same bytes as the GGUF rows + 16 B per ~9 KB tile.)
+//   2. WEIGHTS STREAM THROUGH SHARED MEMORY, AHEAD OF THE MATH, ACROSS PHASE BOUNDARIES.  Every warp owns a private
+//      two-stage ring (2 x 9 KB) that it fills itself (cp.async.bulk -> mbarrier complete_tx, the TMA engine).
+//      Weights do not depend on activations, so while the CTA sits in a grid barrier or re-quantises the activation
+//      row its 16 stages (144 KB per SM, 21 MB per GPU) are already filling with the next phase's rows.  No warp ever
+//      waits for another warp's data; the only CTA-wide syncs are the phase boundaries.
+//   3. ACTIVATIONS ARE REGISTER-STATIONARY.  A lane always handles the same K-slice of a row (K-quants: half a
 //      256-weight super-block; Q8_0: every 32nd 16-byte piece), so after the phase prologue has normalised and
 //      quantised the activation row (bit-exact with quantize_row_q8_K / q8_0) each lane keeps its 128 int8
-//      activations, their scale and block sums in registers for the whole phase.  The inner loop is then
-//      5-8 shared-memory loads + the dp4a chain per 72-104 weight bytes: ~1.6 lane-instructions per weight byte
-//      against a budget of ~5.6 at the HBM roofline.  Rows longer than one warp pass are split over 2/4/8 warps
-//      (K-splits); split partials are combined in a fixed order by the phase epilogue.
-//   3. ONE LAUNCH.  Phases (QKV+RoPE+KV store -> attention -> wo+residual -> gate/up+SwiGLU -> down+residual, then
-//      the LM head) are separated by a grid barrier on per-CTA epoch flags (one release store to arrive, no atomics);
-//      activations written by other SMs are read with ld.cg.
+//      activations, their scale and block sums in registers for the whole phase.  Rows longer than one warp pass are
+//      split over 2/4/8 warps (K-splits); split partials are combined in a fixed order by the phase epilogue.
+//   4. ONE LAUNCH.  Phases (QKV+RoPE+KV store -> attention -> wo+residual -> gate/up+SwiGLU -> down+residual, then
+//      the LM head) are separated by a grid barrier on one monotonically growing counter; activations written by
+//      other SMs are read with ld.cg.
 //
-// Arithmetic = ggml_vec_dot_{q4_K,q6_K}_q8_K / q8_0_q8_0 (integer block dots, fp32 scaling); only the fp32 summation
-// order differs from the scalar reference.  Algorithmic bytes per launch = decode_stream_bytes + KV bytes read.
+// Arithmetic = ggml_vec_dot_{q4_K,q5_K,q6_K}_q8_K / q8_0_q8_0 (integer block dots, fp32 scaling); only the fp32
+// summation order differs from the scalar reference.  Algorithmic bytes per launch = decode_stream_bytes + KV bytes read.
+#include <algorithm>
+#include <vector>
+
 #include "act_quant.cuh"
 #include "kernels.h"
 #include "quant.cuh"
@@ -31,9 +37,11 @@ namespace b2 {
 constexpr int MG_WARPS = 8;
 constexpr int MG_THREADS = MG_WARPS * 32;
 constexpr int MG_STAGES = 2;                 // per warp
-constexpr int MG_STAGE_BYTES = 9216;
+constexpr int MG_TILE_HDR = 16;              // tile header, in-band
+constexpr int MG_TILE_DATA = 9216;           // weight bytes of a tile, at most
+constexpr int MG_STAGE_BYTES = MG_TILE_HDR + MG_TILE_DATA;
 constexpr int MG_RING_BYTES = MG_WARPS * MG_STAGES * MG_STAGE_BYTES;
-constexpr int MG_XS_BYTES = 18 * 1024;       // quantised activation row (attention: scratch, together with the partials)
+constexpr int MG_XS_BYTES = 34 * 1024;       // quantised activation row, K <= 28672 (attention: scratch, together with the partials)
 constexpr int MG_MAX_PART = 2048;            // per-phase partial sums: rows of this CTA x K-splits
 constexpr int MG_PB = 8;                     // prologue: 256-element blocks a warp holds in registers (K <= 16384)
 constexpr int MG_MAX_PASS = 8;               // warp passes per tile
@@ -43,25 +51,25 @@ constexpr size_t MG_OFF_PART = MG_OFF_XS + MG_XS_BYTES;
 constexpr size_t MG_OFF_RED = MG_OFF_PART + MG_MAX_PART * sizeof(float);
 constexpr size_t MG_OFF_BAR = MG_OFF_RED + 32 * sizeof(double);
 constexpr int MG_MAX_PAGES = 512;            // page-table entries of the sequence kept in shared memory
-constexpr int MG_PH_WIN = 8;                 // phase descriptors kept in shared memory: phases [p, p + 8)
+constexpr int MG_PH_WIN = 2;                 // phase descriptors kept in shared memory: phases [p, p + 2)
 constexpr size_t MG_OFF_PH = MG_OFF_BAR + MG_WARPS * MG_STAGES * sizeof(uint64_t);
 constexpr size_t MG_OFF_PT = MG_OFF_PH + MG_PH_WIN * ((sizeof(MegaPhase) + 15) / 16 * 16);
-constexpr size_t MG_OFF_CUR = MG_OFF_PT + MG_MAX_PAGES * sizeof(int);   // 2 schedule cursors per warp
-constexpr size_t MG_OFF_TILE = MG_OFF_CUR + MG_WARPS * 96;                // 1 cursor per warp, then 48-byte tile descriptors
-constexpr size_t MG_SMEM = MG_OFF_TILE + MG_WARPS * MG_STAGES * 48;
+constexpr size_t MG_SMEM = MG_OFF_PT + MG_MAX_PAGES * sizeof(int);
 static_assert(sizeof(MegaPhase) % 4 == 0, "MegaPhase is copied word by word");
 static_assert(MG_SMEM <= 227 * 1024, "mega-kernel shared memory");
+static_assert(MG_STAGE_BYTES % 16 == 0 && MG_OFF_XS % 16 == 0, "bulk copies need 16-byte aligned stages");
+constexpr long long MG_WATCHDOG = 40000000000ll; // cycles (~20 s) after which a wait gives up and traps instead of hanging the GPU
 
 // ------------------------------------------------------------------------------------------------ geometry
 // How a phase's rows map onto lanes (computed on the host, mega_phase_prepare).  K-quants: item = half a super-block
 // (128 weights); a (row, K-split) takes lpr = 2*nb/S lanes; when that is a power of two below 32, rpp = 32/lpr rows
 // share a warp pass.  Q8_0: lane l takes the 16-byte pieces l, l+32, ... (np of them) of its K-split.
-inline bool mg_split(int fmt, int64_t K, int &S, int &lpr, int &rpp, int &np) {
+inline bool mg_split(int fmt, int64_t K, bool pre_quantised, int &S, int &lpr, int &rpp, int &np) {
     np = 0;
     if (fmt == ACT_Q8_K) {
         if (K % 256) return false;
         const int nb = (int)(K / 256);
-        if (nb > MG_PB * MG_WARPS) return false;
+        if (nb > (pre_quantised ? 16 * MG_WARPS : MG_PB * MG_WARPS)) return false; // the register prologue holds MG_PB blocks per warp
         for (S = 1; S <= MG_WARPS; S *= 2)
             if (nb % S == 0 && 2 * nb / S <= 32) {
                 lpr = 2 * nb / S;
@@ -84,23 +92,24 @@ inline bool mg_split(int fmt, int64_t K, int &S, int &lpr, int &rpp, int &np) {
     return false;
 }
 
-// Tile geometry of one matrix: rb = bytes of one row's K-split (= the row pitch inside a tile), R = rows per tile.
-inline bool mg_job_geo(int type, int64_t K, int64_t row_stride, int S, int rpp, int &rb, int &R) {
-    const int64_t nb = K / 256;
-    if (type == B2_T_Q4_K) rb = (int)(S == 1 ? row_stride : 144 * nb / S);
-    else if (type == B2_T_Q6_K) rb = (int)(S == 1 ? row_stride : Q6_BLK * nb / S);
-    else if (type == B2_T_Q8_0) rb = (int)(S == 1 ? row_stride : K / S + K / S / 16);
+// Tile geometry of one matrix: rb = bytes of one row's K-split inside a tile (= the row pitch), R = rows per tile.
+//   Q4_K / Q5_K: the K-split's blocks.  Q6_K: its 208-byte blocks, then its fp16 super-block scales (padded to 16).
+//   Q8_0: its int8 range, then its fp16 block scales.
+inline bool mg_job_geo(int type, int64_t K, int S, int rpp, int &rb, int &R) {
+    const int64_t nbs = K / 256 / S;
+    if (type == B2_T_Q4_K) rb = (int)(144 * nbs);
+    else if (type == B2_T_Q5_K) rb = (int)(176 * nbs);
+    else if (type == B2_T_Q6_K) rb = (int)(Q6_BLK * nbs + (2 * nbs + 15) / 16 * 16);
+    else if (type == B2_T_Q8_0) rb = (int)(K / S + K / S / 16);
     else return false;
-    if (rb <= 0 || rb % 16) return false;
-    R = MG_STAGE_BYTES / rb;
+    if (rb <= 0 || rb % 16 || rb > MG_TILE_DATA) return false;
+    R = MG_TILE_DATA / rb;
     if (R > MG_MAX_PASS * rpp) R = MG_MAX_PASS * rpp;
-    if (S > 1 && R > 32) R = 32; // one lane issues one row's copy
     R = R / rpp * rpp;
-    if (rpp == 1) { // the row loops work on groups of 4 (Q4_K) / 2 (Q6_K) rows with a merged reduction
-        const int grp = type == B2_T_Q4_K ? 4 : type == B2_T_Q6_K ? 2 : 1;
-        if (R >= grp) R = R / grp * grp;
+    if (rpp == 1) { // the row loops work on groups of 2 rows with a merged reduction
+        if (R >= 2) R = R / 2 * 2;
     }
-    return R >= rpp && R > 0;
+    return R >= rpp && R > 0 && R < 256;
 }
 
 // ------------------------------------------------------------------------------------------------ primitives
@@ -111,17 +120,26 @@ __device__ __forceinline__ void mg_mbar_init(uint64_t *bar, uint32_t count) {
 __device__ __forceinline__ void mg_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void mg_wait(uint32_t bar, uint32_t parity) {
+__device__ __forceinline__ bool mg_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "MG_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra MG_DONE_%=;\n"
-        "bra MG_WAIT_%=;\n"
-        "MG_DONE_%=:\n"
-        "}\n" ::"r"(bar), "r"(parity)
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
         : "memory");
+    return ok != 0;
+}
+// Wait for a stage to fill.  A wait that lasts MG_WATCHDOG cycles (a bug, never a slow copy) traps: the launch fails
+// with an error instead of occupying the GPU for ever.
+__device__ __forceinline__ void mg_wait(uint32_t bar, uint32_t parity) {
+    if (mg_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mg_try_wait(bar, parity))
+        if (clock64() - t0 > MG_WATCHDOG) __trap();
 }
 __device__ __forceinline__ void mg_bulk(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
@@ -166,7 +184,10 @@ __device__ __forceinline__ unsigned mg_ld_acquire(const unsigned *p) {
 // generation word, 4.7k per-CTA flags.
 __device__ __forceinline__ void mg_grid_barrier(unsigned *cnt, unsigned target) {
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(cnt) : "memory");
-    while ((int)(mg_ld_acquire(cnt) - target) < 0) { }
+    if ((int)(mg_ld_acquire(cnt) - target) >= 0) return;
+    const long long t0 = clock64();
+    while ((int)(mg_ld_acquire(cnt) - target) < 0)
+        if (clock64() - t0 > MG_WATCHDOG) __trap(); // see mg_wait
 }
 
 inline int64_t mg_act_row_bytes_host(int fmt, int64_t K) {
@@ -175,10 +196,10 @@ inline int64_t mg_act_row_bytes_host(int fmt, int64_t K) {
 }
 
 // This CTA's share of a phase: a contiguous range of rows (pair-aligned for PLAIN/QKV) in the concatenated row space.
-__device__ __forceinline__ void mg_cta_range(const MegaPhase &ph, int cta, int n_cta, int &u, int &u_end) {
+__host__ __device__ __forceinline__ void mg_cta_range(const MegaPhase &ph, int cta, int n_cta, int &u, int &u_end) {
     if (ph.kind == PH_ATT) { u = u_end = 0; return; }
     // units_q = units / n_cta and units_r = units % n_cta come from the host: the first units_r CTAs take one more
-    const int a = cta * ph.units_q + min(cta, ph.units_r), b = a + ph.units_q + (cta < ph.units_r ? 1 : 0);
+    const int a = cta * ph.units_q + (cta < ph.units_r ? cta : ph.units_r), b = a + ph.units_q + (cta < ph.units_r ? 1 : 0);
     const int mul = ph.kind == PH_SWIGLU ? 1 : 2;
     u = a * mul;
     u_end = b * mul;
@@ -190,133 +211,6 @@ __device__ __forceinline__ void mg_locate_row(const MegaPhase &ph, int u, int &j
     while (jb + 1 < ph.n_jobs && row >= (int)ph.job[jb].rows) { row -= (int)ph.job[jb].rows; jb++; }
 }
 
-// ------------------------------------------------------------------------------------------------ tile schedule
-// A warp's walk over its weight tiles: phase by phase, matrix by matrix, R rows at a time.  Producer and consumer
-// each keep one cursor over the SAME sequence; the producer's runs MG_STAGES tiles ahead, across phase boundaries.
-// The cursors live in SHARED memory: with ~220 KB of it in use the L1 is a few KB, so a register spill is an L2 round
-// trip, and two 20-register cursors are exactly what the register allocator would spill.
-struct MgCur {
-    int p, j;          // phase, job (matrix) inside the phase
-    int left;          // rows of the job still to issue for this warp
-    int dr;            // index of the next row in the phase's partial-sum rows
-    int type, S, rb, R;
-    int ks;            // K / S
-    int stride;        // row stride in bytes
-    int ok;
-    int pad;
-    const uint8_t *src; // next row (start of the row, not of the K-split)
-    int64_t koff;       // byte offset of this warp's K-split inside a row (Q8_0: of its int8 range)
-    int64_t doff;       // Q6_K: offset of the K-split's fp16 scales inside a row; Q8_0: of its scale range
-};
-
-// Position the cursor on the first (phase, job) at or after (c.p, c.j) in which this warp has rows.
-// Phase descriptors: the window [p_cur, p_cur + MG_PH_WIN) is in shared memory (a dependent chain of L2 round trips
-// per seek otherwise); anything further ahead -- only tiny models get there -- is read from global memory.
-__device__ __forceinline__ const MegaPhase &mg_phase(const MegaArgs &a, const MegaPhase *sph, int p_cur, int p) {
-    return (unsigned)(p - p_cur) < (unsigned)MG_PH_WIN ? sph[p & (MG_PH_WIN - 1)] : a.phases[p];
-}
-__device__ __noinline__ void mg_seek(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *cp, int cta, int n_cta, int warp) {
-    MgCur &c = *cp;
-    c.ok = 0;
-    while (c.p < a.n_phases) {
-        const MegaPhase &ph = mg_phase(a, sph, p_cur, c.p);
-        if (ph.kind != PH_ATT) {
-            int u, u_end;
-            mg_cta_range(ph, cta, n_cta, u, u_end);
-            const int S = ph.S, g_log = 3 - ph.s_log, g = warp >> ph.s_log; // MG_WARPS = 8 = S * 2^g_log row groups
-            while (c.j < ph.n_jobs && u < u_end) {
-                const FusedJob &job = ph.job[c.j];
-                int lo, hi, dr_off;
-                if (ph.kind == PH_SWIGLU) {
-                    lo = u; hi = u_end;
-                    dr_off = c.j * (u_end - u) - u;
-                } else {
-                    const int j0 = ph.j0[c.j];
-                    lo = max(u, j0) - j0;
-                    hi = min(u_end, j0 + (int)job.rows) - j0;
-                    dr_off = j0 - u;
-                }
-                if (hi > lo) {
-                    const int n = hi - lo;
-                    const int r0 = lo + ((n * g) >> g_log), r1 = lo + ((n * (g + 1)) >> g_log);
-                    if (r1 > r0) {
-                        const int q = warp & (S - 1);
-                        const int64_t nbs = (ph.K >> 8) >> ph.s_log, nb = ph.K >> 8;
-                        c.left = r1 - r0;
-                        c.dr = dr_off + r0;
-                        c.type = job.type; c.S = S; c.rb = ph.rb[c.j]; c.R = ph.R[c.j];
-                        c.ks = (int)(ph.K >> ph.s_log);
-                        c.stride = (int)job.row_stride;
-                        c.src = job.W + (int64_t)r0 * job.row_stride;
-                        if (job.type == B2_T_Q4_K) { c.koff = q * nbs * 144; c.doff = 0; }
-                        else if (job.type == B2_T_Q6_K) { c.koff = q * nbs * Q6_BLK; c.doff = nb * Q6_BLK + 2 * q * nbs; }
-                        else { c.koff = (int64_t)q * c.ks; c.doff = ph.K + (int64_t)q * (c.ks >> 4); }
-                        c.ok = 1;
-                        return;
-                    }
-                }
-                c.j++;
-            }
-        }
-        c.p++;
-        c.j = 0;
-    }
-}
-
-// What a ring stage holds, written by the producer side when it issues the copies and read by the consumer side:
-// two 16-byte words.
-struct MgTile {
-    int p;             // phase the tile belongs to; MG_NO_TILE when the stage is empty
-    int tnr;           // ggml type | rows << 8 | row pitch << 16
-    int dr;            // first row's index in the phase's partial-sum rows
-    int stride;        // Q6_K: row stride, and pointer to the fp16 scales of this K-split in the first row
-    const uint8_t *dp;
-    int64_t pad;
-};
-constexpr int MG_NO_TILE = 0x7fffffff;
-
-// Issue the bulk copies of the cursor's next tile into `stage`, describe it in *t, and step the cursor (a seek only when
-// the matrix is exhausted).  All lanes call it; ~40 instructions on the common path.
-__device__ __forceinline__ void mg_issue_next(const MegaArgs &a, const MegaPhase *sph, int p_cur, MgCur *cp, uint32_t stage, uint32_t bar,
-                                              int lane, MgTile *t, int cta, int n_cta, int warp) {
-    MgCur &c = *cp;
-    const int left = c.left, n = min(c.R, left), rb = c.rb, stride = c.stride, type = c.type;
-    const uint8_t *src = c.src;
-    {
-        int4 w0;
-        w0.x = c.p; w0.y = type | (n << 8) | (rb << 16); w0.z = c.dr; w0.w = stride;
-        *(int4 *)t = w0;
-        t->dp = src + c.doff;
-    }
-    if (c.S == 1) { // whole rows, contiguous in memory: one copy
-        if (lane == 0) {
-            const uint32_t bytes = (uint32_t)(n * stride);
-            mg_expect_tx(bar, bytes);
-            mg_bulk(stage, src, bytes, bar);
-        }
-    } else {        // one K-split of n rows: a copy per row (Q8_0: its int8 range and its scale range)
-        if (lane == 0) mg_expect_tx(bar, (uint32_t)(n * rb));
-        __syncwarp();
-        if (lane < n) {
-            const uint8_t *sr = src + (int64_t)lane * stride;
-            const uint32_t dst = stage + lane * rb;
-            if (type == B2_T_Q8_0) {
-                mg_bulk(dst, sr + c.koff, (uint32_t)c.ks, bar);
-                mg_bulk(dst + c.ks, sr + c.doff, (uint32_t)(c.ks / 16), bar);
-            } else {
-                mg_bulk(dst, sr + c.koff, (uint32_t)rb, bar);
-            }
-        }
-    }
-    if (left > n) {
-        c.left = left - n;
-        c.dr += n;
-        c.src = src + (int64_t)n * stride;
-    } else {
-        c.j++;
-        mg_seek(a, sph, p_cur, cp, cta, n_cta, warp);
-    }
-}
 
 // ------------------------------------------------------------------------------------------------ block dots
 // A lane's place in a phase (fixed for the whole phase, so its activations stay in registers).
@@ -352,6 +246,37 @@ __device__ __forceinline__ float mg_dot_q4k(uint32_t blk, int h, const int (&xr)
     }
     const int isum = (int)(sc4 & 0xFF) * s0 + (int)((sc4 >> 8) & 0xFF) * (s1 >> 4) + (int)((sc4 >> 16) & 0xFF) * s2 +
                      (int)(sc4 >> 24) * (s3 >> 4);
+    const int imin = (int)(mn4 & 0xFF) * bs32[0] + (int)((mn4 >> 8) & 0xFF) * bs32[1] + (int)((mn4 >> 16) & 0xFF) * bs32[2] +
+                     (int)(mn4 >> 24) * bs32[3];
+    const float2 dd = __half22float2(*(const __half2 *)&hdr.x);
+    return (dd.x * dx) * (float)isum - (dd.y * dx) * (float)imin;
+}
+
+// Q5_K, one half super-block of a 176-byte block [d f16][dmin f16][12 B scales/mins][qh 32 B][qs 128 B]: as Q4_K, and bit s
+// of qh[l] is the fifth bit of weight l of sub-block s (dequantize_row_q5_K).  Only the 70B-class attn_v rows use it.
+__device__ __forceinline__ float mg_dot_q5k(uint32_t blk, int h, const int (&xr)[32], float dx, const int (&bs32)[4]) {
+    const int4 hdr = mg_lds128(blk);
+    const int4 h0 = mg_lds128(blk + 16), h1 = mg_lds128(blk + 32);
+    const uint32_t qa = blk + 48 + 64 * h;
+    const int4 q0 = mg_lds128(qa), q1 = mg_lds128(qa + 16), q2 = mg_lds128(qa + 32), q3 = mg_lds128(qa + 48);
+    const uint32_t u0 = hdr.y, u1 = hdr.z, u2 = hdr.w;
+    const uint32_t sc_hi = (u2 & 0x0F0F0F0Fu) | ((u0 >> 2) & 0x30303030u);
+    const uint32_t mn_hi = ((u2 >> 4) & 0x0F0F0F0Fu) | ((u1 >> 2) & 0x30303030u);
+    const uint32_t sc4 = h ? sc_hi : (u0 & 0x3F3F3F3Fu), mn4 = h ? mn_hi : (u1 & 0x3F3F3F3Fu);
+    const uint32_t w[16] = {(uint32_t)q0.x, (uint32_t)q0.y, (uint32_t)q0.z, (uint32_t)q0.w, (uint32_t)q1.x, (uint32_t)q1.y,
+                            (uint32_t)q1.z, (uint32_t)q1.w, (uint32_t)q2.x, (uint32_t)q2.y, (uint32_t)q2.z, (uint32_t)q2.w,
+                            (uint32_t)q3.x, (uint32_t)q3.y, (uint32_t)q3.z, (uint32_t)q3.w};
+    const uint32_t H[8] = {(uint32_t)h0.x, (uint32_t)h0.y, (uint32_t)h0.z, (uint32_t)h0.w, (uint32_t)h1.x, (uint32_t)h1.y, (uint32_t)h1.z, (uint32_t)h1.w};
+    int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const uint32_t hb = H[i] >> (4 * h); // bits 0..3 of every byte: the fifth bits of this half's four sub-blocks
+        s0 = mg_dp4a_us((w[i] & 0x0F0F0F0Fu) | ((hb << 4) & 0x10101010u), xr[i], s0);
+        s1 = mg_dp4a_us(((w[i] >> 4) & 0x0F0F0F0Fu) | ((hb << 3) & 0x10101010u), xr[8 + i], s1);
+        s2 = mg_dp4a_us((w[8 + i] & 0x0F0F0F0Fu) | ((hb << 2) & 0x10101010u), xr[16 + i], s2);
+        s3 = mg_dp4a_us(((w[8 + i] >> 4) & 0x0F0F0F0Fu) | ((hb << 1) & 0x10101010u), xr[24 + i], s3);
+    }
+    const int isum = (int)(sc4 & 0xFF) * s0 + (int)((sc4 >> 8) & 0xFF) * s1 + (int)((sc4 >> 16) & 0xFF) * s2 + (int)(sc4 >> 24) * s3;
     const int imin = (int)(mn4 & 0xFF) * bs32[0] + (int)((mn4 >> 8) & 0xFF) * bs32[1] + (int)((mn4 >> 16) & 0xFF) * bs32[2] +
                      (int)(mn4 >> 24) * bs32[3];
     const float2 dd = __half22float2(*(const __half2 *)&hdr.x);
@@ -439,27 +364,24 @@ __device__ __noinline__ void mg_attention(const float *__restrict__ qrow, int n_
     constexpr int VP = 32;                                // V: 32 positions per warp per sweep, position = j0 + warp + 8u
     int4 kq[KR][8];
     uint32_t vq[VP][2];
+    // loads are UNCONDITIONAL on clamped (always valid) positions: see the note in mg_attention_split
+    const int j_last = n_kv - 1;
     auto load_k = [&](int j0) {
 #pragma unroll
         for (int r = 0; r < KR; r++) {
-            const int j = j0 + r * KP + (tid >> 1);
-            if (j < n_kv) {
-                const __half *kr = mg_kv_row(k_pool, pbase, j, page_shift, kvd) + hk * hd + half * hh;
+            const int j = min(j0 + r * KP + (tid >> 1), j_last);
+            const __half *kr = mg_kv_row(k_pool, pbase, j, page_shift, kvd) + hk * hd + half * hh;
 #pragma unroll
-                for (int i = 0; i < 8; i++)
-                    if (i < nld) kq[r][i] = *(const int4 *)(kr + i * 8);
-            }
+            for (int i = 0; i < 8; i++) kq[r][i] = *(const int4 *)(kr + (i < nld ? i : 0) * 8);
         }
     };
     auto load_v = [&](int j0) {
 #pragma unroll
         for (int u = 0; u < VP; u++) {
-            const int jv = j0 + warp + MG_WARPS * u;
-            if (jv < n_kv) {
-                const __half *vr = mg_kv_row(v_pool, pbase, jv, page_shift, kvd) + hk * hd + lane * dpl;
-                if (nw == 2) { const int2 t = *(const int2 *)vr; vq[u][0] = t.x; vq[u][1] = t.y; }
-                else vq[u][0] = *(const uint32_t *)vr;
-            }
+            const int jv = min(j0 + warp + MG_WARPS * u, j_last);
+            const __half *vr = mg_kv_row(v_pool, pbase, jv, page_shift, kvd) + hk * hd + lane * dpl;
+            if (nw == 2) { const int2 t = *(const int2 *)vr; vq[u][0] = t.x; vq[u][1] = t.y; }
+            else { vq[u][0] = *(const uint32_t *)vr; vq[u][1] = 0u; }
         }
     };
     // ---- everything that needs no activation is requested first: the first 256 positions' K and V
@@ -914,6 +836,10 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
 }
 
 // ------------------------------------------------------------------------------------------------ the kernel
+// Tile header, the first 16 bytes of every tile of a warp's stream (written by MegaStreams::build):
+//   w0: ggml type | rows << 8 | row pitch << 16        w1: first row's index in the phase's partial-sum rows
+//   w2: bytes of the tile TWO ahead in this stream (0: none) -- what the freed stage is refilled with
+//   w3: bit 0: the warp's last tile of this phase; bits 8..: the next phase in which the warp has tiles
 template <bool DBG>
 __global__ void __launch_bounds__(MG_THREADS, 1)
 decode_mega_kernel(const MegaArgs a) {
@@ -942,30 +868,28 @@ decode_mega_kernel(const MegaArgs a) {
     }
     __syncthreads();
 
-    // ---- this warp's ring and its two cursors over the tile schedule
+    // ---- this warp's ring and its weight stream: the first two tiles are requested right away
     const uint32_t ring = mg_s32(smem) + warp * (MG_STAGES * MG_STAGE_BYTES);
     const uint32_t bar0 = mg_s32(bars + warp * MG_STAGES);
-    static_assert(sizeof(MgCur) <= 96 && sizeof(MgTile) <= 48, "cursor / tile slots");
-    MgCur *pc = (MgCur *)(smem + MG_OFF_CUR + (size_t)warp * 96);
-    MgTile *tiles = (MgTile *)(smem + MG_OFF_TILE + (size_t)warp * MG_STAGES * 48);
-    pc->p = 0; pc->j = 0;
-    mg_seek(a, sph, 0, pc, cta, n_cta, warp);
+    const uint8_t *src;
+    int next_p; // the next phase in which this warp has tiles
+    {
+        const MegaStreamStart st = a.starts[cta * MG_WARPS + warp];
+        src = st.src;
+        next_p = st.first_p;
+        if (lane == 0) {
+            if (st.size0) { mg_expect_tx(bar0, st.size0); mg_bulk(ring, src, st.size0, bar0); }
+            if (st.size1) { mg_expect_tx(bar0 + 8, st.size1); mg_bulk(ring + MG_STAGE_BYTES, src + st.size0, st.size1, bar0 + 8); }
+        }
+        src += st.size0 + st.size1;
+    }
     uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
     unsigned att_seq = 0;         // attention phases so far (per-head counters only grow)
     unsigned bar_i = 0;           // grid barriers so far in this launch
-    for (int s = 0; s < MG_STAGES; s++) {
-        MgTile *t = (MgTile *)((uint8_t *)tiles + s * 48);
-        if (pc->ok) {
-            mg_issue_next(a, sph, 0, pc, ring + s * MG_STAGE_BYTES, bar0 + s * 8, lane, t, cta, n_cta, warp);
-        } else {
-            t->p = MG_NO_TILE;
-        }
-    }
-    __syncwarp();
 
     for (int p = 0; p < a.n_phases; p++) {
         const MegaPhase &ph = sph[p & (MG_PH_WIN - 1)];
-        long long t0 = 0, t1 = 0, t2 = 0, t_wait = 0, t_comp = 0, t_epi = 0, n_tiles = 0, tp0 = 0, tp3 = 0, tl_end = 0, t_advc = 0, t_iss = 0, t_advp = 0;
+        long long t0 = 0, t1 = 0, t2 = 0, t_wait = 0, t_comp = 0, t_epi = 0, n_tiles = 0, tp0 = 0, tp3 = 0, tl_end = 0;
         if (DBG && tid == 0) t0 = clock64();
         int u = 0, u_end = 0;
         if (ph.kind == PH_ATT) {
@@ -1055,121 +979,122 @@ decode_mega_kernel(const MegaArgs a) {
                 L.sr = 0; L.kb = 0; L.h = 0; L.on = true; L.head = lane == 0; L.span = 32;
             }
             const int bs32[4] = {bs[0] + bs[1], bs[2] + bs[3], bs[4] + bs[5], bs[6] + bs[7]};
+            const uint32_t q6d = (uint32_t)((nb >> ph.s_log) * Q6_BLK + 2 * L.kb); // Q6_K: this lane's fp16 scale inside a row-split
             if (DBG && tid == 0) t1 = clock64();
 
             // ---- this warp's tiles of the phase
-            while (true) {
-                MgTile *tile = (MgTile *)((uint8_t *)tiles + stg * 48);
-                const int4 tw = *(const int4 *)tile;
-                if (tw.x != p) break;
-                const int type = tw.y & 0xFF, n = (tw.y >> 8) & 0xFF, rb = (int)((uint32_t)tw.y >> 16);
-                const uint32_t st = ring + stg * MG_STAGE_BYTES, bar = bar0 + stg * 8;
-                float *pout = partial + (size_t)tw.z * S + q;
-                long long tw0 = 0, tw1 = 0;
-                if (DBG && tid == 0) tw0 = clock64();
-                if (type == B2_T_Q4_K) {
+            if (next_p == p) {
+                while (true) {
+                    const uint32_t st = ring + stg * MG_STAGE_BYTES, bar = bar0 + stg * 8;
+                    long long tw0 = 0, tw1 = 0;
+                    if (DBG && tid == 0) tw0 = clock64();
                     mg_wait(bar, parity);
                     if (DBG && tid == 0) tw1 = clock64();
-                    if (rpp == 1) { // 2 rows at a time: independent dp4a chains, one merged reduction
-                        const uint32_t base = st + L.kb * 144;
+                    const int4 th = mg_lds128(st);
+                    const int type = th.x & 0xFF, n = (th.x >> 8) & 0xFF, rb = (int)((uint32_t)th.x >> 16);
+                    const uint32_t td = st + MG_TILE_HDR;
+                    float *pout = partial + (size_t)th.y * S + q;
+                    if (type == B2_T_Q4_K) {
+                        if (rpp == 1) { // 2 rows at a time: independent dp4a chains, one merged reduction
+                            const uint32_t base = td + L.kb * 144;
 #pragma unroll 1
-                        for (int r0 = 0; r0 < n; r0 += 2) {
-                            float v0 = mg_dot_q4k(base + r0 * rb, L.h, xr, dx, bs32);
-                            float v1 = mg_dot_q4k(base + min(r0 + 1, n - 1) * rb, L.h, xr, dx, bs32);
-                            if (!L.on) { v0 = 0.f; v1 = 0.f; }
-                            const float tot = mg_reduce2(v0, v1, lane);
-                            const int kk = r0 + ((lane >> 4) & 1);
-                            if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
+                            for (int r0 = 0; r0 < n; r0 += 2) {
+                                float v0 = mg_dot_q4k(base + r0 * rb, L.h, xr, dx, bs32);
+                                float v1 = mg_dot_q4k(base + min(r0 + 1, n - 1) * rb, L.h, xr, dx, bs32);
+                                if (!L.on) { v0 = 0.f; v1 = 0.f; }
+                                const float tot = mg_reduce2(v0, v1, lane);
+                                const int kk = r0 + ((lane >> 4) & 1);
+                                if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
+                            }
+                        } else {
+#pragma unroll 1
+                            for (int rr = 0; rr < n; rr += rpp) {
+                                const int row = rr + L.sr;
+                                const bool on = L.on && row < n;
+                                float v = mg_dot_q4k(td + (on ? row : 0) * rb + L.kb * 144, L.h, xr, dx, bs32);
+                                v = mg_row_sum(on ? v : 0.f, L.span);
+                                if (on && L.head) pout[(size_t)row * S] = v;
+                            }
                         }
-                    } else {
+                    } else if (type == B2_T_Q6_K) {
+                        // row-split = [208-byte blocks][their fp16 super-block scales]
+                        if (rpp == 1) { // 2 rows at a time
+                            const uint32_t base = td + L.kb * Q6_BLK;
+#pragma unroll 1
+                            for (int k = 0; k < n; k += 2) {
+                                const uint32_t o0 = k * rb, o1 = min(k + 1, n - 1) * rb;
+                                const uint32_t d0 = mg_lds_u16(td + o0 + q6d), d1 = mg_lds_u16(td + o1 + q6d);
+                                float v0 = mg_dot_q6k(base + o0, L.h, xr, dx, bs, d0);
+                                float v1 = mg_dot_q6k(base + o1, L.h, xr, dx, bs, d1);
+                                if (!L.on) { v0 = 0.f; v1 = 0.f; }
+                                const float tot = mg_reduce2(v0, v1, lane);
+                                const int kk = k + ((lane >> 4) & 1);
+                                if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
+                            }
+                        } else {
+#pragma unroll 1
+                            for (int rr = 0; rr < n; rr += rpp) {
+                                const int row = rr + L.sr;
+                                const bool on = L.on && row < n;
+                                const uint32_t o = (on ? row : 0) * rb;
+                                const uint32_t d16 = mg_lds_u16(td + o + q6d);
+                                float v = mg_dot_q6k(td + o + L.kb * Q6_BLK, L.h, xr, dx, bs, d16);
+                                v = mg_row_sum(on ? v : 0.f, L.span);
+                                if (on && L.head) pout[(size_t)row * S] = v;
+                            }
+                        }
+                    } else if (type == B2_T_Q5_K) {
 #pragma unroll 1
                         for (int rr = 0; rr < n; rr += rpp) {
                             const int row = rr + L.sr;
                             const bool on = L.on && row < n;
-                            float v = mg_dot_q4k(st + (on ? row : 0) * rb + L.kb * 144, L.h, xr, dx, bs32);
+                            float v = mg_dot_q5k(td + (on ? row : 0) * rb + L.kb * 176, L.h, xr, dx, bs32);
                             v = mg_row_sum(on ? v : 0.f, L.span);
                             if (on && L.head) pout[(size_t)row * S] = v;
                         }
-                    }
-                } else if (type == B2_T_Q6_K) {
-                    // the fp16 super-block scales sit at the end of the row, outside the staged K-split: they come
-                    // straight from global memory (L2), requested one row group ahead of their use
-                    const int64_t stride = tw.w;
-                    const uint8_t *dp = tile->dp + 2 * L.kb;
-                    if (rpp == 1) { // 2 rows at a time
-                        uint32_t d0 = mg_ldg_u16(dp), d1 = mg_ldg_u16(dp + (n > 1 ? stride : 0));
-                        mg_wait(bar, parity);
-                        if (DBG && tid == 0) tw1 = clock64();
-                        const uint32_t base = st + L.kb * Q6_BLK;
+                    } else { // Q8_0: row-split = [int8 K/S][fp16 scales K/S/32]
+                        const int ks = (int)(K >> ph.s_log);
+                        const int xc = (q * ks) >> 4;                               // first 16-byte chunk of this K-split's activations
+                        const float *xdq = (const float *)(xs + K) + (q * ks) / 32; // and their block scales
 #pragma unroll 1
-                        for (int k = 0; k < n; k += 2) {
-                            const int k2 = min(k + 2, n - 1), k3 = min(k + 3, n - 1);
-                            const uint32_t e0 = mg_ldg_u16(dp + k2 * stride), e1 = mg_ldg_u16(dp + k3 * stride);
-                            float v0 = mg_dot_q6k(base + k * rb, L.h, xr, dx, bs, d0);
-                            float v1 = mg_dot_q6k(base + min(k + 1, n - 1) * rb, L.h, xr, dx, bs, d1);
-                            if (!L.on) { v0 = 0.f; v1 = 0.f; }
-                            const float tot = mg_reduce2(v0, v1, lane);
-                            const int kk = k + ((lane >> 4) & 1);
-                            if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
-                            d0 = e0; d1 = e1;
-                        }
-                    } else {
-                        mg_wait(bar, parity);
-                        if (DBG && tid == 0) tw1 = clock64();
-#pragma unroll 1
-                        for (int rr = 0; rr < n; rr += rpp) {
-                            const int row = rr + L.sr;
-                            const bool on = L.on && row < n;
-                            const uint32_t d16 = mg_ldg_u16(dp + (on ? row : 0) * stride);
-                            float v = mg_dot_q6k(st + (on ? row : 0) * rb + L.kb * Q6_BLK, L.h, xr, dx, bs, d16);
-                            v = mg_row_sum(on ? v : 0.f, L.span);
-                            if (on && L.head) pout[(size_t)row * S] = v;
-                        }
-                    }
-                } else { // Q8_0: tile row = [int8 K/S][fp16 scales K/S/32]
-                    mg_wait(bar, parity);
-                    if (DBG && tid == 0) tw1 = clock64();
-                    const int ks = (int)(K >> ph.s_log);
-                    const int xc = (q * ks) >> 4;                               // first 16-byte chunk of this K-split's activations
-                    const float *xdq = (const float *)(xs + K) + (q * ks) / 32; // and their block scales
-#pragma unroll 1
-                    for (int row = 0; row < n; row += 2) { // 2 rows at a time: independent chains, one merged reduction
-                        const uint32_t rp0 = st + row * rb, rp1 = st + min(row + 1, n - 1) * rb;
-                        float acc0 = 0.f, acc1 = 0.f;
+                        for (int row = 0; row < n; row += 2) { // 2 rows at a time: independent chains, one merged reduction
+                            const uint32_t rp0 = td + row * rb, rp1 = td + min(row + 1, n - 1) * rb;
+                            float acc0 = 0.f, acc1 = 0.f;
 #pragma unroll 4
-                        for (int j = 0; j < np; j++) { // 16-byte pieces lane + 32 j: half a 32-element block each
-                            const int piece = lane + 32 * j;
-                            const int4 xv = mg_lds128(xs_a + mg_swz(xc + piece) * 16);
-                            const int4 w0 = mg_lds128(rp0 + piece * 16), w1 = mg_lds128(rp1 + piece * 16);
-                            const float dxj = xdq[piece >> 1];
-                            const float d0 = h2f((uint16_t)mg_lds_u16(rp0 + ks + (piece >> 1) * 2)) * dxj;
-                            const float d1 = h2f((uint16_t)mg_lds_u16(rp1 + ks + (piece >> 1) * 2)) * dxj;
-                            int s0 = __dp4a(w0.x, xv.x, 0), s1 = __dp4a(w1.x, xv.x, 0);
-                            s0 = __dp4a(w0.y, xv.y, s0); s1 = __dp4a(w1.y, xv.y, s1);
-                            s0 = __dp4a(w0.z, xv.z, s0); s1 = __dp4a(w1.z, xv.z, s1);
-                            s0 = __dp4a(w0.w, xv.w, s0); s1 = __dp4a(w1.w, xv.w, s1);
-                            // the two halves of a block are scaled separately ((a + b) d = a d + b d up to one rounding)
-                            acc0 += (float)s0 * d0;
-                            acc1 += (float)s1 * d1;
+                            for (int j = 0; j < np; j++) { // 16-byte pieces lane + 32 j: half a 32-element block each
+                                const int piece = lane + 32 * j;
+                                const int4 xv = mg_lds128(xs_a + mg_swz(xc + piece) * 16);
+                                const int4 w0 = mg_lds128(rp0 + piece * 16), w1 = mg_lds128(rp1 + piece * 16);
+                                const float dxj = xdq[piece >> 1];
+                                const float d0 = h2f((uint16_t)mg_lds_u16(rp0 + ks + (piece >> 1) * 2)) * dxj;
+                                const float d1 = h2f((uint16_t)mg_lds_u16(rp1 + ks + (piece >> 1) * 2)) * dxj;
+                                int s0 = __dp4a(w0.x, xv.x, 0), s1 = __dp4a(w1.x, xv.x, 0);
+                                s0 = __dp4a(w0.y, xv.y, s0); s1 = __dp4a(w1.y, xv.y, s1);
+                                s0 = __dp4a(w0.z, xv.z, s0); s1 = __dp4a(w1.z, xv.z, s1);
+                                s0 = __dp4a(w0.w, xv.w, s0); s1 = __dp4a(w1.w, xv.w, s1);
+                                // the two halves of a block are scaled separately ((a + b) d = a d + b d up to one rounding)
+                                acc0 += (float)s0 * d0;
+                                acc1 += (float)s1 * d1;
+                            }
+                            const float tot = mg_reduce2(acc0, acc1, lane);
+                            const int kk = row + ((lane >> 4) & 1);
+                            if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
                         }
-                        const float tot = mg_reduce2(acc0, acc1, lane);
-                        const int kk = row + ((lane >> 4) & 1);
-                        if ((lane & 15) == 0 && kk < n) pout[(size_t)kk * S] = tot;
                     }
+                    if (DBG && tid == 0) { t_wait += tw1 - tw0; t_comp += clock64() - tw1; n_tiles++; }
+                    // the stage is free: refill it with the tile MG_STAGES ahead in the stream (possibly a later phase's)
+                    __syncwarp();
+                    if (th.z) {
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        if (lane == 0) {
+                            mg_expect_tx(bar, (uint32_t)th.z);
+                            mg_bulk(st, src, (uint32_t)th.z, bar);
+                        }
+                        src += (uint32_t)th.z;
+                    }
+                    if (++stg == MG_STAGES) { stg = 0; parity ^= 1; }
+                    if (th.w & 1) { next_p = (int)((uint32_t)th.w >> 8); break; }
                 }
-                long long ta0 = 0, ta2 = 0;
-                if (DBG && tid == 0) { ta0 = clock64(); t_wait += tw1 - tw0; t_comp += ta0 - tw1; n_tiles++; }
-                // the stage is free: refill it with the tile MG_STAGES ahead (possibly a later phase's)
-                __syncwarp();
-                if (pc->ok) {
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    mg_issue_next(a, sph, p, pc, st, bar, lane, tile, cta, n_cta, warp);
-                    if (DBG && tid == 0) { ta2 = clock64(); t_iss += ta2 - ta0; }
-                } else {
-                    tile->p = MG_NO_TILE;
-                }
-                __syncwarp();
-                if (++stg == MG_STAGES) { stg = 0; parity ^= 1; }
             }
             if (DBG && tid == 0) tl_end = clock64();
             __syncthreads();
@@ -1223,19 +1148,21 @@ decode_mega_kernel(const MegaArgs a) {
         }
         if (DBG && tid == 0) {
             long long *dd = a.dbg + ((int64_t)cta * a.n_phases + p) * 16;
-            dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64(); if (u < u_end) { dd[4] = t_wait; dd[5] = t_comp; dd[6] = t_epi ? t2 - t_epi : 0; dd[7] = n_tiles; }
-            if (u < u_end) { dd[8] = tp0 - t0; dd[9] = t_advc; dd[10] = tp3 - tp0; dd[11] = t_iss; dd[12] = t1 - tp3; dd[13] = t_epi - tl_end; dd[14] = tl_end - t1; dd[15] = t_advp; }
+            dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64();
+            if (u < u_end) {
+                dd[4] = t_wait; dd[5] = t_comp; dd[6] = t_epi ? t2 - t_epi : 0; dd[7] = n_tiles;
+                dd[8] = tp0 - t0; dd[9] = 0; dd[10] = tp3 - tp0; dd[11] = 0; dd[12] = t1 - tp3; dd[13] = t_epi - tl_end; dd[14] = tl_end - t1; dd[15] = 0;
+            }
         }
     }
 }
 
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s) {
-    static thread_local bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    configured.run([&] {
         B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
         B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
-        configured = true;
-    }
+    });
     void *args[] = {(void *)&a};
     const void *fn = a.dbg ? (const void *)decode_mega_kernel<true> : (const void *)decode_mega_kernel<false>;
     B2_CUDA(cudaLaunchCooperativeKernel(fn, dim3(n_sm), dim3(MG_THREADS), args, MG_SMEM, s));
@@ -1248,7 +1175,7 @@ bool mega_phase_prepare(MegaPhase &ph, int n_cta) {
     ph.units_q = ph.units / n_cta;
     ph.units_r = ph.units % n_cta;
     int S, lpr, rpp, np;
-    if (!mg_split(ph.fmt, ph.K, S, lpr, rpp, np)) return false;
+    if (!mg_split(ph.fmt, ph.K, ph.xq_global != nullptr, S, lpr, rpp, np)) return false;
     if (mg_act_row_bytes_host(ph.fmt, ph.K) > MG_XS_BYTES) return false;
     if (ph.norm_w && ph.K / 256 > 4 * MG_WARPS) return false; // the prologue norms at most 4 blocks per warp in one go
     ph.S = S; ph.lpr = lpr; ph.rpp = rpp; ph.np = np;
@@ -1259,7 +1186,8 @@ bool mega_phase_prepare(MegaPhase &ph, int n_cta) {
     int64_t rows = 0;
     for (int j = 0; j < ph.n_jobs; j++) {
         ph.j0[j] = (int)rows;
-        if (!mg_job_geo(ph.job[j].type, ph.K, ph.job[j].row_stride, S, rpp, ph.rb[j], ph.R[j])) return false;
+        if (act_format_for(ph.job[j].type) != ph.fmt) return false;
+        if (!mg_job_geo(ph.job[j].type, ph.K, S, rpp, ph.rb[j], ph.R[j])) return false;
         if (ph.job[j].rows % 2 != 0 || ph.job[j].rows >= (1 << 22)) return false;
         rows += ph.job[j].rows;
     }
@@ -1278,6 +1206,244 @@ size_t mega_attention_ctx_limit(int hd) {
     const size_t fixed = sizeof(float) * ((size_t)hd + 32 + (size_t)MG_WARPS * hd + 16);
     if (fixed >= avail) return 0;
     return std::min((size_t)((avail - fixed) / 4) - 8, (size_t)MG_MAX_PAGES * 16);
+}
+
+// ------------------------------------------------------------------------------------------------ weight streams
+// One entry per tile: where its row-splits come from (GGUF-layout rows on the device) and where the tile goes.
+struct MgTileSrc {
+    const uint8_t *src0, *src1; // first row's two pieces (piece 1: Q6_K fp16 super-block scales / Q8_0 block scales)
+    uint64_t dst;               // byte offset of the tile in the stream buffer
+    uint32_t hdr[4];
+    int32_t stride;             // source row stride
+    int32_t len0, len1;         // bytes of the pieces (len0 a multiple of 16, len1 of 2)
+    int32_t rb, n, pad;
+};
+static_assert(sizeof(MgTileSrc) == 64, "tile table entry");
+
+__global__ void __launch_bounds__(256) mega_scatter_kernel(const MgTileSrc *__restrict__ tab, uint8_t *__restrict__ data) {
+    const MgTileSrc t = tab[blockIdx.x];
+    uint8_t *dst = data + t.dst;
+    if (threadIdx.x == 0) *(uint4 *)dst = make_uint4(t.hdr[0], t.hdr[1], t.hdr[2], t.hdr[3]);
+    dst += MG_TILE_HDR;
+    const int c0 = t.len0 >> 4;
+    for (int i = threadIdx.x; i < t.n * c0; i += blockDim.x) {
+        const int r = i / c0, k = i - r * c0;
+        ((int4 *)(dst + (size_t)r * t.rb))[k] = ld_stream((const int4 *)(t.src0 + (size_t)r * t.stride) + k);
+    }
+    const int c1 = t.len1 >> 1;
+    for (int i = threadIdx.x; i < t.n * c1; i += blockDim.x) {
+        const int r = i / c1, k = i - r * c1;
+        ((uint16_t *)(dst + (size_t)r * t.rb + t.len0))[k] = ((const uint16_t *)(t.src1 + (size_t)r * t.stride))[k];
+    }
+}
+
+void MegaStreams::free() {
+    if (data) cudaFree(data);
+    if (starts) cudaFree(starts);
+    data = nullptr;
+    starts = nullptr;
+    bytes = 0;
+    n_tiles = 0;
+}
+
+// Plan the streams (pure host arithmetic): the tile table in stream order, the per-warp starts, the first tile's offset
+// of every stream; returns the bytes of the stream buffer.
+static uint64_t mega_plan_streams(const MegaPhase *phases, int n_phases, int n_cta, std::vector<MgTileSrc> &tab,
+                                  std::vector<MegaStreamStart> &st, std::vector<uint64_t> &first_off) {
+    tab.clear();
+    st.assign((size_t)n_cta * MG_WARPS, MegaStreamStart{});
+    first_off.assign(st.size(), 0);
+    uint64_t off = 0;
+    for (int cta = 0; cta < n_cta; cta++)
+        for (int warp = 0; warp < MG_WARPS; warp++) {
+            off = (off + 127) / 128 * 128;
+            const size_t first = tab.size();
+            long last_prev = -1;
+            int first_p = n_phases;
+            for (int p = 0; p < n_phases; p++) {
+                const MegaPhase &ph = phases[p];
+                if (ph.kind == PH_ATT) continue;
+                const size_t before = tab.size();
+                int u, u_end;
+                mg_cta_range(ph, cta, n_cta, u, u_end);
+                // MG_WARPS = S K-splits x 2^g_log row groups: warp = (row group g, K-split q)
+                const int S = ph.S, g_log = 3 - ph.s_log, g = warp >> ph.s_log, q = warp & (S - 1);
+                const int64_t nb = ph.K >> 8, nbs = nb >> ph.s_log, ks = ph.K >> ph.s_log;
+                for (int j = 0; j < ph.n_jobs && u < u_end; j++) {
+                    const FusedJob &job = ph.job[j];
+                    int lo, hi, dr_off;
+                    if (ph.kind == PH_SWIGLU) { // gate rows [u, u_end) and the same rows of up
+                        lo = u; hi = u_end;
+                        dr_off = j * (u_end - u) - u;
+                    } else {
+                        const int j0 = ph.j0[j];
+                        lo = std::max(u, j0) - j0;
+                        hi = std::min(u_end, j0 + (int)job.rows) - j0;
+                        dr_off = j0 - u;
+                    }
+                    if (hi <= lo) continue;
+                    const int n = hi - lo;
+                    const int r0 = lo + ((n * g) >> g_log), r1 = lo + ((n * (g + 1)) >> g_log);
+                    if (r1 <= r0) continue;
+                    int64_t off0 = 0, len0 = 0, off1 = 0, len1 = 0;
+                    if (job.type == B2_T_Q4_K) { off0 = q * nbs * 144; len0 = nbs * 144; }
+                    else if (job.type == B2_T_Q5_K) { off0 = q * nbs * 176; len0 = nbs * 176; }
+                    else if (job.type == B2_T_Q6_K) { off0 = q * nbs * Q6_BLK; len0 = nbs * Q6_BLK; off1 = nb * Q6_BLK + 2 * q * nbs; len1 = 2 * nbs; }
+                    else { off0 = q * ks; len0 = ks; off1 = ph.K + q * (ks / 16); len1 = ks / 16; }
+                    const int rb = ph.rb[j], R = ph.R[j];
+                    B2_CHECK(len0 % 16 == 0 && len0 + len1 <= rb && MG_TILE_HDR + (int64_t)R * rb <= MG_STAGE_BYTES, B2_EINVAL, "mega streams: tile geometry");
+                    for (int r = r0; r < r1; r += R) {
+                        const int nr = std::min(R, r1 - r);
+                        MgTileSrc t;
+                        const uint8_t *row = job.W + (int64_t)r * job.row_stride;
+                        t.src0 = row + off0;
+                        t.src1 = row + off1;
+                        t.dst = 0;
+                        t.hdr[0] = (uint32_t)job.type | ((uint32_t)nr << 8) | ((uint32_t)rb << 16);
+                        t.hdr[1] = (uint32_t)(dr_off + r);
+                        t.hdr[2] = 0;
+                        t.hdr[3] = 0;
+                        t.stride = (int32_t)job.row_stride;
+                        t.len0 = (int32_t)len0; t.len1 = (int32_t)len1;
+                        t.rb = rb; t.n = nr; t.pad = p;
+                        tab.push_back(t);
+                    }
+                }
+                if (tab.size() > before) {
+                    if (first_p == n_phases) first_p = p;
+                    if (last_prev >= 0) tab[(size_t)last_prev].hdr[3] |= (uint32_t)p << 8;
+                    tab.back().hdr[3] |= 1u;
+                    last_prev = (long)tab.size() - 1;
+                }
+            }
+            if (last_prev >= 0) tab[(size_t)last_prev].hdr[3] |= (uint32_t)n_phases << 8;
+            const size_t n_t = tab.size() - first;
+            for (size_t i = first; i < tab.size(); i++) {
+                tab[i].dst = off;
+                off += MG_TILE_HDR + (uint64_t)tab[i].n * tab[i].rb;
+            }
+            auto tile_bytes = [&](size_t i) { return (uint32_t)(MG_TILE_HDR + tab[i].n * tab[i].rb); };
+            for (size_t i = first; i + 2 < tab.size(); i++) tab[i].hdr[2] = tile_bytes(i + 2);
+            MegaStreamStart &ss = st[(size_t)cta * MG_WARPS + warp];
+            ss.first_p = first_p;
+            ss.size0 = n_t > 0 ? tile_bytes(first) : 0;
+            ss.size1 = n_t > 1 ? tile_bytes(first + 1) : 0;
+            first_off[(size_t)cta * MG_WARPS + warp] = n_t > 0 ? tab[first].dst : 0;
+        }
+    return off + 128;
+}
+
+// Replay every warp's walk over its stream the way the kernel does it (sizes from the start entry and the headers'
+// look-ahead field, phase hand-over from the last-tile flag) and check that each (row, K-split) of each phase is
+// produced exactly once, from the right source bytes.  Throws on the first inconsistency.
+static void mega_plan_verify(const MegaPhase *phases, int n_phases, int n_cta, const std::vector<MgTileSrc> &tab,
+                             const std::vector<MegaStreamStart> &st, const std::vector<uint64_t> &first_off, uint64_t total) {
+    auto fail = [](const std::string &m) { throw Error(B2_EINVAL, "mega stream plan: " + m); };
+    std::vector<std::vector<uint8_t>> cover((size_t)n_phases * n_cta);
+    for (int p = 0; p < n_phases; p++)
+        for (int cta = 0; cta < n_cta; cta++) {
+            if (phases[p].kind == PH_ATT) continue;
+            int u, u_end;
+            mg_cta_range(phases[p], cta, n_cta, u, u_end);
+            const int n_r = (u_end - u) * (phases[p].kind == PH_SWIGLU ? 2 : 1);
+            if ((int64_t)n_r * phases[p].S > MG_MAX_PART) fail("partial sums do not fit");
+            cover[(size_t)p * n_cta + cta].assign((size_t)n_r * phases[p].S, 0);
+        }
+    size_t idx = 0;
+    for (int cta = 0; cta < n_cta; cta++)
+        for (int warp = 0; warp < MG_WARPS; warp++) {
+            const MegaStreamStart &ss = st[(size_t)cta * MG_WARPS + warp];
+            uint32_t pend[2] = {ss.size0, ss.size1};
+            uint64_t src = first_off[(size_t)cta * MG_WARPS + warp];
+            uint64_t issued = src + ss.size0 + ss.size1; // where the next refill reads
+            int next_p = ss.first_p;
+            for (int p = 0; p < n_phases; p++) {
+                const MegaPhase &ph = phases[p];
+                if (ph.kind == PH_ATT || next_p != p) continue;
+                int u, u_end;
+                mg_cta_range(ph, cta, n_cta, u, u_end);
+                if (u >= u_end) fail("tiles in a phase without rows");
+                const int q = warp & (ph.S - 1);
+                while (true) {
+                    if (idx >= tab.size()) fail("stream runs past the table");
+                    const MgTileSrc &t = tab[idx];
+                    const uint32_t sz = (uint32_t)(MG_TILE_HDR + t.n * t.rb);
+                    if (t.pad != p) fail("tile of another phase");
+                    if (pend[0] != sz || t.dst != src) fail("tile size / offset chain broken");
+                    if (sz > (uint32_t)MG_STAGE_BYTES || sz % 16 || t.dst % 16 || t.dst + sz > total) fail("tile does not fit");
+                    const int type = t.hdr[0] & 0xFF, n = (t.hdr[0] >> 8) & 0xFF, rb = (int)(t.hdr[0] >> 16);
+                    if (n != t.n || rb != t.rb || n <= 0) fail("header fields");
+                    auto &cv = cover[(size_t)p * n_cta + cta];
+                    for (int r = 0; r < n; r++) {
+                        const size_t c = ((size_t)t.hdr[1] + r) * ph.S + q;
+                        if (c >= cv.size()) fail("partial index out of range");
+                        if (cv[c]++) fail("row-split produced twice");
+                        // the source row this partial index stands for
+                        int dr = (int)t.hdr[1] + r, jb = 0, row;
+                        if (ph.kind == PH_SWIGLU) { jb = dr / (u_end - u); row = u + dr % (u_end - u); }
+                        else { row = u + dr; while (jb + 1 < ph.n_jobs && row >= (int)ph.job[jb].rows) { row -= (int)ph.job[jb].rows; jb++; } }
+                        if (ph.job[jb].type != type) fail("tile type");
+                        const int64_t nb = ph.K >> 8, nbs = nb >> ph.s_log, ks = ph.K >> ph.s_log;
+                        const int64_t off0 = type == B2_T_Q4_K ? q * nbs * 144 : type == B2_T_Q5_K ? q * nbs * 176 : type == B2_T_Q6_K ? q * nbs * Q6_BLK : q * ks;
+                        if (t.src0 + (int64_t)r * t.stride != ph.job[jb].W + (int64_t)row * ph.job[jb].row_stride + off0) fail("source row");
+                    }
+                    src += sz;
+                    pend[0] = pend[1];
+                    pend[1] = t.hdr[2];
+                    if (t.hdr[2]) {
+                        if (issued != src + pend[0]) fail("refill source pointer");
+                        issued += t.hdr[2];
+                    }
+                    idx++;
+                    if (t.hdr[3] & 1u) { next_p = (int)(t.hdr[3] >> 8); break; }
+                }
+            }
+            if (next_p != n_phases || pend[0] || pend[1]) fail("stream does not end cleanly");
+        }
+    if (idx != tab.size()) fail("tiles left over");
+    for (auto &cv : cover)
+        for (uint8_t c : cv)
+            if (c != 1) fail("row-split not produced");
+}
+
+int64_t mega_plan_check(const MegaPhase *phases, int n_phases, int n_cta, int64_t *n_tiles) {
+    std::vector<MgTileSrc> tab;
+    std::vector<MegaStreamStart> st;
+    std::vector<uint64_t> first_off;
+    const uint64_t total = mega_plan_streams(phases, n_phases, n_cta, tab, st, first_off);
+    mega_plan_verify(phases, n_phases, n_cta, tab, st, first_off, total);
+    if (n_tiles) *n_tiles = (int64_t)tab.size();
+    return (int64_t)total;
+}
+
+void MegaStreams::build(const MegaPhase *phases, int n_phases, int n_cta, cudaStream_t s) {
+    free();
+    std::vector<MgTileSrc> tab;
+    std::vector<MegaStreamStart> st;
+    std::vector<uint64_t> first_off;
+    const uint64_t off = mega_plan_streams(phases, n_phases, n_cta, tab, st, first_off) - 128;
+    bytes = (size_t)off + 128;
+    n_tiles = (int64_t)tab.size();
+    B2_CUDA(cudaMalloc((void **)&data, bytes));
+    B2_CUDA(cudaMalloc((void **)&starts, st.size() * sizeof(MegaStreamStart)));
+    for (size_t i = 0; i < st.size(); i++) st[i].src = data + first_off[i];
+    B2_CUDA(cudaMemsetAsync(data, 0, bytes, s));
+    B2_CUDA(cudaMemcpyAsync(starts, st.data(), st.size() * sizeof(MegaStreamStart), cudaMemcpyHostToDevice, s));
+    // scatter in slices of the table, so that the staging copy of the table stays small
+    const size_t SLICE = (size_t)1 << 18;
+    MgTileSrc *dtab = nullptr;
+    if (!tab.empty()) {
+        B2_CUDA(cudaMalloc((void **)&dtab, std::min(SLICE, tab.size()) * sizeof(MgTileSrc)));
+        for (size_t i0 = 0; i0 < tab.size(); i0 += SLICE) {
+            const size_t cnt = std::min(SLICE, tab.size() - i0);
+            B2_CUDA(cudaMemcpyAsync(dtab, tab.data() + i0, cnt * sizeof(MgTileSrc), cudaMemcpyHostToDevice, s));
+            mega_scatter_kernel<<<(unsigned)cnt, 256, 0, s>>>(dtab, data);
+            B2_CUDA(cudaGetLastError());
+            B2_CUDA(cudaStreamSynchronize(s)); // tab slice is pageable host memory and dtab is reused
+        }
+    }
+    B2_CUDA(cudaStreamSynchronize(s));
+    if (dtab) cudaFree(dtab);
 }
 
 } // namespace b2

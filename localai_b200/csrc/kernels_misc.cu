@@ -135,11 +135,8 @@ static bool try_launch_attention_group(const float *q, const int32_t *pos, const
                                        int hd, const KVLayout &kv, float *out, int max_ctx, cudaStream_t s) {
     const size_t smem = attention_group_smem_bytes(G, hd, max_ctx, ATT_THREADS);
     if (smem > 96 * 1024) return false; // keep at least two CTAs per SM; longer contexts use the per-head kernel
-    static thread_local bool configured = false;
-    if (!configured) {
-        B2_CUDA(cudaFuncSetAttribute(attention_group_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-        configured = true;
-    }
+    static PerDeviceOnce configured;
+    configured.run([&] { B2_CUDA(cudaFuncSetAttribute(attention_group_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); });
     const float scale = 1.0f / sqrtf((float)hd);
     attention_group_kernel<G><<<dim3(n_head_kv, n_tok), ATT_THREADS, smem, s>>>(q, pos, slot, n_head, hd, kv, out, scale);
     g_launch_count++;
@@ -161,11 +158,9 @@ void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, i
     }
     const size_t smem = attention_smem_bytes(hd, max_ctx, ATT_THREADS);
     B2_CHECK(smem <= 220 * 1024, B2_EUNSUPPORTED, "attention: context too long for the two-pass kernel");
-    static thread_local size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        B2_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        configured = 220 * 1024;
-    }
+    static PerDeviceOnce configured;
+    if (smem > 48 * 1024)
+        configured.run([&] { B2_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024)); });
     const float scale = 1.0f / sqrtf((float)hd);
     attention_kernel<<<dim3(n_head, n_tok), ATT_THREADS, smem, s>>>(q, pos, slot, n_head, n_head_kv, hd, kv, out, scale);
     g_launch_count++;

@@ -64,7 +64,11 @@ sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, con
     const SampleSpec &sp = specs[blockIdx.x];
     const float *x = logits + (int64_t)blockIdx.x * stride;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    auto key_at = [&](int i) -> uint32_t { return i == sp.ban_token ? 0u : float_key(x[i]); };
+    // key 0 = "not a candidate": the banned token and every masked (-inf) logit (token_mask_kernel)
+    auto key_at = [&](int i) -> uint32_t {
+        const float v = x[i];
+        return (i == sp.ban_token || v == -INFINITY) ? 0u : float_key(v);
+    };
     if (mu_out && tid == 0) mu_out[blockIdx.x] = sp.mirostat_mu;
 
     // ---------------- greedy: first maximal element
@@ -242,15 +246,49 @@ sample_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, con
         }
         __syncthreads();
     }
-    const uint32_t kth = s_prefix; // key of the K-th largest element
+    const uint32_t kth = s_prefix; // key of the K-th largest element (0: fewer than K tokens are allowed at all)
     if (tid == 0) s_count = 0;
     __syncthreads();
+    // candidates = every key above the K-th (fewer than K of them, any order: they are sorted below) ...
     for (int i = tid; i < n_vocab; i += SAMPLE_THREADS) {
         const uint32_t k = key_at(i);
-        if (k >= kth && k != 0u) {
+        if (k > kth) {
             const uint32_t slot = atomicAdd(&s_count, 1u);
             if (slot < CAND_CAP) cand[slot] = ((unsigned long long)k << 32) | (uint32_t)(~(uint32_t)i);
         }
+    }
+    __syncthreads();
+    // ... plus as many of the tokens tied AT the K-th key as still fit into K, lowest ids first.  A plain ">= kth"
+    // gather overflows the candidate buffer when the tie is large (a grammar mask leaves fewer than K finite logits,
+    // or many equal logits) and then keeps whichever tokens happened to arrive first.
+    const int n_gt = min((int)s_count, CAND_CAP);
+    const int need = K - n_gt;
+    if (kth != 0u && need > 0) {
+        int *s_cnt = (int *)s_scan;
+        const int per = (n_vocab + SAMPLE_THREADS - 1) / SAMPLE_THREADS;
+        const int i0 = tid * per, i1 = min(n_vocab, i0 + per);
+        int c = 0;
+        for (int i = i0; i < i1; i++) c += key_at(i) == kth;
+        // exclusive prefix over the threads: warp scan, then the warp totals
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_redi[warp] = incl;
+        __syncthreads();
+        int base = 0;
+        for (int w = 0; w < warp; w++) base += s_redi[w];
+        int rank = base + incl - c;
+        for (int i = i0; i < i1 && rank < need; i++)
+            if (key_at(i) == kth) {
+                cand[n_gt + rank] = ((unsigned long long)kth << 32) | (uint32_t)(~(uint32_t)i);
+                rank++;
+            }
+        if (tid == SAMPLE_THREADS - 1) s_cnt[0] = min(need, base + incl); // ties taken
+        __syncthreads();
+        if (tid == 0) s_count = (uint32_t)(n_gt + s_cnt[0]);
     }
     __syncthreads();
     const int n_cand = min((int)s_count, CAND_CAP);

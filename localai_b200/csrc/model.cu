@@ -209,6 +209,7 @@ Model::~Model() {
     for (auto g : decode_graphs_)
         if (g) cudaGraphExecDestroy(g);
     for (void *p : allocs_) cudaFree(p);
+    mega_streams_.free();
     if (logits_) cudaFree(logits_);
     for (auto &kv : w_tiles_) cudaFree(kv.second);
     if (gemm_w_) cudaFree(gemm_w_);
@@ -345,8 +346,9 @@ void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
     if (w_bytes > gemm_w_bytes_) {
         realloc = true;
         B2_CUDA(cudaStreamSynchronize(stream));
-        for (auto &kv : w_tiles_) cudaFree(kv.second);
-    if (gemm_w_) cudaFree(gemm_w_);
+        for (auto &kv : w_tiles_) cudaFree(kv.second); // memory is short (no_shadow_): give the resident tiles back too
+        w_tiles_.clear();
+        if (gemm_w_) cudaFree(gemm_w_);
         gemm_w_ = nullptr;
         B2_CUDA(cudaMalloc(&gemm_w_, w_bytes));
         gemm_w_bytes_ = w_bytes;
@@ -557,6 +559,15 @@ void Model::build_mega() {
     if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1)) ||
         (uint64_t)pool_layer_stride_ >= (1ull << 31))
         return;
+    if (!mega_streams_.data) {
+        // The decode kernel reads its own copy of the weights (MegaStreams): same bytes, laid out per (CTA, warp) in
+        // consumption order.  180 GB of HBM is room for it next to the GGUF-layout rows the other paths read; when it
+        // is not (B200LLM_NO_MEGA_STREAMS=1 forces that), batch-1 decode takes the fused per-layer kernels instead.
+        size_t free_b = 0, total_b = 0;
+        const bool off = getenv("B200LLM_NO_MEGA_STREAMS") && atoi(getenv("B200LLM_NO_MEGA_STREAMS"));
+        if (off || cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < (size_t)decode_stream_bytes + shadow_reserve_) return;
+        mega_streams_.build(ph.data(), (int)ph.size(), n_sm_, stream);
+    }
     if (!mega_phases_) mega_phases_ = (MegaPhase *)dalloc(ph.size() * sizeof(MegaPhase));
     B2_CUDA(cudaMemcpyAsync(mega_phases_, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaStreamSynchronize(stream));
@@ -599,7 +610,7 @@ void Model::run_decode_mega() {
     const int d = hp.n_embd;
     launch_dequant_rows(tok_embd, tok_, 0, 1, x_, d, stream);
     MegaArgs a;
-    a.phases = mega_phases_; a.n_phases = mega_n_phases_;
+    a.phases = mega_phases_; a.n_phases = mega_n_phases_; a.starts = mega_streams_.starts;
     a.pos = pos_; a.slot = slot_; a.rope_table = rope_table_; a.page_table = page_table_;
     a.page_size = page_size; a.max_pages = max_pages; a.kvd = hp.n_head_kv * hp.head_dim;
     a.n_head = hp.n_head; a.n_head_kv = hp.n_head_kv; a.hd = hp.head_dim;

@@ -105,6 +105,7 @@ class Model {
     void build_mega();
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;
+    MegaStreams mega_streams_; // the decode kernel's copy of the weights: one contiguous stream per (CTA, warp)
     unsigned mega_epoch_ = 0, mega_att_base_ = 0;
     int mega_n_bar_ = 0;
     uint8_t *mega_xq_ = nullptr;
