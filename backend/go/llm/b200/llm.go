@@ -4,6 +4,11 @@ package main
 // It embeds base.Base, not base.SingleThread: Locking() is false, so concurrent RPCs reach the engine, whose own
 // thread batches them (continuous batching); LocalAI must be started with --parallel-requests for the client side
 // not to serialise (pkg/grpc/client.go:103-106).
+//
+// One backend process serves one model (pkg/model/loader.go:117-141), so models that fit one GPU are replicated
+// INSIDE this process: Load creates one engine per visible sm_100 device (B200_REPLICAS / MainGPU narrow that) and
+// every request goes to the replica with the fewest requests in flight -- the policy of get_slot's LRU pick
+// (grpc-server.cpp:609-628) one level up.  No data crosses GPUs.
 
 /*
 #cgo CFLAGS: -I${SRCDIR}/../../../../include
@@ -17,21 +22,39 @@ import "C"
 import (
 	"fmt"
 	"os"
+	"runtime"
 	"strconv"
+	"sync"
 	"unsafe"
 
 	"github.com/mudler/LocalAI/pkg/grpc/base"
 	pb "github.com/mudler/LocalAI/pkg/grpc/proto"
 )
 
-type LLM struct {
-	base.Base
-	eng *C.b2_engine
+type replica struct {
+	eng      *C.b2_engine
+	inflight int
 }
 
-func lastError() error { return fmt.Errorf("b200llm: %s", C.GoString(C.b2_last_error())) }
+type LLM struct {
+	base.Base
+	mu       sync.Mutex
+	replicas []*replica
+	weights  uint64 // device bytes of one replica's weights (Status)
+}
 
-// Load <- ModelOptions (backend.proto:162-235); replaces grpc-server.cpp:2312-2332.
+// b2_last_error() is thread-local in C, and a goroutine may move to another OS thread between a failing call and the
+// read of its message: every call whose failure is reported pins the goroutine first (callPinned).
+func callPinned(f func() bool) error {
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	if f() {
+		return nil
+	}
+	return fmt.Errorf("b200llm: %s", C.GoString(C.b2_last_error()))
+}
+
+// Load <- ModelOptions (backend.proto:126-203); replaces grpc-server.cpp:2312-2332.
 func (l *LLM) Load(opts *pb.ModelOptions) error {
 	var o C.b2_load_opts
 	o.struct_size = C.uint32_t(unsafe.Sizeof(o))
@@ -44,9 +67,6 @@ func (l *LLM) Load(opts *pb.ModelOptions) error {
 	if v, err := strconv.Atoi(os.Getenv("LLAMACPP_PARALLEL")); err == nil && v > 0 { // grpc-server.cpp:2225-2231
 		o.n_parallel = C.int32_t(v)
 	}
-	if v, err := strconv.Atoi(opts.MainGPU); err == nil {
-		o.device = C.int32_t(v)
-	}
 	if opts.Embeddings {
 		o.embeddings = 1
 	}
@@ -55,24 +75,84 @@ func (l *LLM) Load(opts *pb.ModelOptions) error {
 	}
 	o.rope_freq_base = C.float(opts.RopeFreqBase)
 	o.rope_freq_scale = C.float(opts.RopeFreqScale)
-	l.eng = C.b2_create(&o)
-	if l.eng == nil {
-		return lastError()
+
+	// which devices: MainGPU set => that one; else every sm_100 device, capped by B200_REPLICAS
+	devices := []int{}
+	if v, err := strconv.Atoi(opts.MainGPU); err == nil && opts.MainGPU != "" {
+		devices = append(devices, v)
+	} else {
+		n := int(C.b2_device_count())
+		if v, err := strconv.Atoi(os.Getenv("B200_REPLICAS")); err == nil && v > 0 && v < n {
+			n = v
+		}
+		if n < 1 || opts.VocabOnly {
+			n = 1 // vocab_only needs no device; without a device b2_create reports B2_ENODEV below
+		}
+		for d := 0; d < n; d++ {
+			devices = append(devices, d)
+		}
+	}
+	for _, d := range devices {
+		o.device = C.int32_t(d)
+		var eng *C.b2_engine
+		if err := callPinned(func() bool { eng = C.b2_create(&o); return eng != nil }); err != nil {
+			l.free()
+			return err
+		}
+		l.replicas = append(l.replicas, &replica{eng: eng})
+	}
+	var info C.b2_model_info_t
+	if C.b2_model_info(l.replicas[0].eng, &info) == 0 {
+		l.weights = uint64(info.weight_bytes_device)
 	}
 	return nil
 }
 
-func (l *LLM) request(opts *pb.PredictOptions, stream bool, embedding bool) (C.int64_t, func(), error) {
+func (l *LLM) free() {
+	for _, r := range l.replicas {
+		C.b2_destroy(r.eng)
+	}
+	l.replicas = nil
+}
+
+// pick the replica with the fewest requests in flight; done() gives the slot back
+func (l *LLM) pick() (*replica, func(), error) {
+	l.mu.Lock()
+	defer l.mu.Unlock()
+	if len(l.replicas) == 0 {
+		return nil, nil, fmt.Errorf("b200llm: no model loaded")
+	}
+	best := l.replicas[0]
+	for _, r := range l.replicas[1:] {
+		if r.inflight < best.inflight {
+			best = r
+		}
+	}
+	best.inflight++
+	return best, func() { l.mu.Lock(); best.inflight--; l.mu.Unlock() }, nil
+}
+
+// request <- parse_options (grpc-server.cpp:2068-2137): PredictOptions -> b2_request.  The returned release() frees
+// the C copies, releases the request id and gives the replica slot back; call it on every path.
+func (l *LLM) request(opts *pb.PredictOptions, stream bool, embedding bool) (*replica, C.int64_t, func(), error) {
+	rep, done, err := l.pick()
+	if err != nil {
+		return nil, 0, nil, err
+	}
 	var r C.b2_request
 	r.struct_size = C.uint32_t(unsafe.Sizeof(r))
 	text := opts.Prompt
 	if embedding {
 		text = opts.Embeddings
 	}
-	cprompt := C.CString(text)
-	r.prompt = cprompt
+	frees := []unsafe.Pointer{}
+	cstr := func(s string) *C.char {
+		p := C.CString(s)
+		frees = append(frees, unsafe.Pointer(p))
+		return p
+	}
+	r.prompt = cstr(text)
 	r.prompt_len = C.size_t(len(text))
-	frees := []unsafe.Pointer{unsafe.Pointer(cprompt)}
 	if embedding && len(opts.EmbeddingTokens) > 0 {
 		ids := (*C.int32_t)(C.malloc(C.size_t(4 * len(opts.EmbeddingTokens))))
 		frees = append(frees, unsafe.Pointer(ids))
@@ -85,6 +165,7 @@ func (l *LLM) request(opts *pb.PredictOptions, stream bool, embedding bool) (C.i
 	r.n_predict = C.int32_t(opts.Tokens) // 0 => until EOS/context, as grpc-server.cpp:2098
 	r.temperature = C.float(opts.Temperature)
 	r.top_k, r.top_p = C.int32_t(opts.TopK), C.float(opts.TopP)
+	r.min_p = 0.05 // PredictOptions has no MinP: the reference runs with llama.cpp's default (grpc-server.cpp:639)
 	r.repeat_penalty, r.repeat_last_n = C.float(opts.Penalty), C.int32_t(opts.Repeat)
 	r.frequency_penalty, r.presence_penalty = C.float(opts.FrequencyPenalty), C.float(opts.PresencePenalty)
 	// LocalAI's default config sends mirostat 2, tau 5, eta 0.1 (core/config/backend_config.go:286-289)
@@ -93,6 +174,9 @@ func (l *LLM) request(opts *pb.PredictOptions, stream bool, embedding bool) (C.i
 	r.seed = C.int32_t(opts.Seed)
 	if opts.IgnoreEOS {
 		r.ignore_eos = 1
+	}
+	if opts.PenalizeNL { // grpc-server.cpp:2111
+		r.penalize_nl = 1
 	}
 	if opts.PromptCacheAll {
 		r.cache_prompt = 1
@@ -104,42 +188,46 @@ func (l *LLM) request(opts *pb.PredictOptions, stream bool, embedding bool) (C.i
 	if stream {
 		r.stream = 1
 	}
+	if opts.Grammar != "" && !embedding { // grpc-server.cpp:2114; every tools / function-call request carries one
+		r.grammar = cstr(opts.Grammar)
+	}
 	if n := len(opts.StopPrompts); n > 0 {
 		arr := (**C.char)(C.malloc(C.size_t(n) * C.size_t(unsafe.Sizeof(uintptr(0)))))
 		frees = append(frees, unsafe.Pointer(arr))
 		s := unsafe.Slice(arr, n)
 		for i, w := range opts.StopPrompts {
-			s[i] = C.CString(w)
-			frees = append(frees, unsafe.Pointer(s[i]))
+			s[i] = cstr(w)
 		}
 		r.stop, r.n_stop = arr, C.int32_t(n)
 	}
-	id := C.b2_submit(l.eng, &r)
+	var id C.int64_t
+	err = callPinned(func() bool { id = C.b2_submit(rep.eng, &r); return id >= 0 })
+	for _, p := range frees { // b2_submit deep-copies the request
+		C.free(p)
+	}
+	if err != nil {
+		done()
+		return nil, 0, nil, err
+	}
 	release := func() {
-		for _, p := range frees {
-			C.free(p)
-		}
+		C.b2_release(rep.eng, id)
+		done()
 	}
-	if id < 0 {
-		release()
-		return 0, nil, lastError()
-	}
-	return id, release, nil
+	return rep, id, release, nil
 }
 
 // drain polls events until the final one; f receives every text piece.
-func (l *LLM) drain(id C.int64_t, f func(string)) error {
-	defer C.b2_release(l.eng, id)
+func drain(rep *replica, id C.int64_t, f func(string)) error {
 	for {
 		var ev C.b2_event
 		ev.struct_size = C.uint32_t(unsafe.Sizeof(ev))
-		if rc := C.b2_poll(l.eng, id, &ev, -1); rc != 0 {
-			return lastError()
+		if err := callPinned(func() bool { return C.b2_poll(rep.eng, id, &ev, -1) == 0 }); err != nil {
+			return err
 		}
 		if ev.flags&C.B2_EV_ERROR != 0 {
 			return fmt.Errorf("b200llm: %s", C.GoStringN(ev.text, C.int(ev.text_len)))
 		}
-		if ev.text_len > 0 {
+		if ev.text_len > 0 && f != nil {
 			f(C.GoStringN(ev.text, C.int(ev.text_len)))
 		}
 		if ev.flags&C.B2_EV_FINAL != 0 {
@@ -150,19 +238,19 @@ func (l *LLM) drain(id C.int64_t, f func(string)) error {
 
 // Predict <- grpc-server.cpp:2380-2407
 func (l *LLM) Predict(opts *pb.PredictOptions) (string, error) {
-	id, release, err := l.request(opts, false, false)
+	rep, id, release, err := l.request(opts, false, false)
 	if err != nil {
 		return "", err
 	}
 	defer release()
 	out := ""
-	err = l.drain(id, func(s string) { out += s })
+	err = drain(rep, id, func(s string) { out += s })
 	return out, err
 }
 
 // PredictStream <- grpc-server.cpp:2333-2377; the callee closes the channel (pkg/grpc/base/base.go:43-46).
 func (l *LLM) PredictStream(opts *pb.PredictOptions, results chan string) error {
-	id, release, err := l.request(opts, true, false)
+	rep, id, release, err := l.request(opts, true, false)
 	if err != nil {
 		close(results)
 		return err
@@ -170,45 +258,101 @@ func (l *LLM) PredictStream(opts *pb.PredictOptions, results chan string) error 
 	go func() {
 		defer release()
 		defer close(results)
-		_ = l.drain(id, func(s string) { results <- s })
+		_ = drain(rep, id, func(s string) { results <- s })
 	}()
 	return nil
 }
 
 // Embeddings <- grpc-server.cpp:2410-2432
 func (l *LLM) Embeddings(opts *pb.PredictOptions) ([]float32, error) {
-	id, release, err := l.request(opts, false, true)
+	rep, id, release, err := l.request(opts, false, true)
 	if err != nil {
 		return nil, err
 	}
-	defer release()
-	var ev C.b2_event
-	ev.struct_size = C.uint32_t(unsafe.Sizeof(ev))
-	for ev.flags&C.B2_EV_FINAL == 0 {
-		if rc := C.b2_poll(l.eng, id, &ev, -1); rc != 0 {
-			return nil, lastError()
-		}
+	defer release() // every return path below gives the request back
+	if err := drain(rep, id, nil); err != nil {
+		return nil, err // includes B2_EV_ERROR events
 	}
-	defer C.b2_release(l.eng, id)
-	out := make([]float32, int(ev.n_embd))
+	var info C.b2_model_info_t
+	if err := callPinned(func() bool { return C.b2_model_info(rep.eng, &info) == 0 }); err != nil {
+		return nil, err
+	}
+	out := make([]float32, int(info.n_embd))
 	if len(out) == 0 {
 		return out, nil
 	}
-	if n := C.b2_embed_result(l.eng, id, (*C.float)(unsafe.Pointer(&out[0])), C.int(len(out))); n < 0 {
-		return nil, lastError()
+	var n C.int
+	if err := callPinned(func() bool {
+		n = C.b2_embed_result(rep.eng, id, (*C.float)(unsafe.Pointer(&out[0])), C.int(len(out)))
+		return n >= 0
+	}); err != nil {
+		return nil, err
 	}
-	return out, nil
+	return out[:int(n)], nil
 }
 
 // TokenizeString: the reference C++ backend does not implement it (SURVEY.md 3.5); this one does.
 func (l *LLM) TokenizeString(opts *pb.PredictOptions) (pb.TokenizationResponse, error) {
+	l.mu.Lock()
+	if len(l.replicas) == 0 {
+		l.mu.Unlock()
+		return pb.TokenizationResponse{}, fmt.Errorf("b200llm: no model loaded")
+	}
+	eng := l.replicas[0].eng // the tokenizer is host code, identical in every replica
+	l.mu.Unlock()
 	text := C.CString(opts.Prompt)
 	defer C.free(unsafe.Pointer(text))
 	cap := len(opts.Prompt) + 16
 	buf := make([]int32, cap)
-	n := C.b2_tokenize(l.eng, text, C.size_t(len(opts.Prompt)), 1, 1, (*C.int32_t)(unsafe.Pointer(&buf[0])), C.int(cap))
-	if n < 0 {
-		return pb.TokenizationResponse{}, lastError()
+	var n C.int
+	if err := callPinned(func() bool {
+		n = C.b2_tokenize(eng, text, C.size_t(len(opts.Prompt)), 1, 1, (*C.int32_t)(unsafe.Pointer(&buf[0])), C.int(cap))
+		return n >= 0
+	}); err != nil {
+		return pb.TokenizationResponse{}, err
 	}
 	return pb.TokenizationResponse{Length: int32(n), Tokens: buf[:n]}, nil
+}
+
+// Busy / Status <- pkg/grpc/server.go:173-180, base.Base.Status (pkg/grpc/base/base.go): state + memory of the backend.
+func (l *LLM) Busy() bool {
+	l.mu.Lock()
+	defer l.mu.Unlock()
+	for _, r := range l.replicas {
+		if r.inflight > 0 {
+			return true
+		}
+	}
+	return false
+}
+
+func (l *LLM) Status() (pb.StatusResponse, error) {
+	state := pb.StatusResponse_READY
+	if len(l.replicas) == 0 {
+		state = pb.StatusResponse_UNINITIALIZED
+	} else if l.Busy() {
+		state = pb.StatusResponse_BUSY
+	}
+	total := l.weights * uint64(len(l.replicas))
+	return pb.StatusResponse{State: state, Memory: &pb.MemoryUsageData{Total: total, Breakdown: map[string]uint64{"gpu_weights": total}}}, nil
+}
+
+// Metrics sums b2_metrics over the replicas: what GetMetrics (grpc-server.cpp:2434-2457) reports.  pkg/grpc's Go
+// server has no GetMetrics hook in the LLM interface (interface.go:7-27); INTEGRATION.md shows the three lines a
+// maintainer adds to pkg/grpc/server.go to serve it from here.
+func (l *LLM) Metrics() *pb.MetricsResponse {
+	out := &pb.MetricsResponse{}
+	l.mu.Lock()
+	reps := append([]*replica(nil), l.replicas...)
+	l.mu.Unlock()
+	for _, r := range reps {
+		var m C.b2_metrics_t
+		if C.b2_metrics(r.eng, &m) != 0 {
+			continue
+		}
+		out.TokensPerSecond += float32(m.tokens_per_second)
+		out.TokensGenerated += int32(m.tokens_generated)
+		out.PromptTokensProcessed += int32(m.prompt_tokens_processed)
+	}
+	return out
 }

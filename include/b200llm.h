@@ -134,7 +134,9 @@ typedef struct {
     float mirostat_eta;        /* MirostatETA (<= 0 => 0.1) */
     float typical_p;           /* TypicalP: 0 or >= 1 = off (with typical-p on, at most the 256 most probable tokens are considered) */
     float tfs_z;               /* TailFreeSamplingZ: 0 or >= 1 = off */
-    int32_t reserved[3];
+    int32_t penalize_nl;       /* PenalizeNL (grpc-server.cpp:2111): 1 = the newline token takes the repeat / frequency /
+                                  presence penalties like any other; 0 (the proto default) = it is exempt */
+    int32_t reserved[2];
     const char *grammar;       /* Grammar: GBNF text, NUL-terminated (NULL or "" = none).  The sampled token is checked
                                   against it; when it does not fit, the row is re-sampled under a vocabulary mask
                                   (grpc-server.cpp:655,2114).  A text that does not parse fails b2_submit (B2_EINVAL). */

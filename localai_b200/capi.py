@@ -66,7 +66,7 @@ class Request(C.Structure):
         ("n_keep", C.c_int32), ("embedding_mode", C.c_int32), ("stop", C.POINTER(C.c_char_p)),
         ("stop_len", C.POINTER(C.c_size_t)), ("n_stop", C.c_int32), ("stream", C.c_int32),
         ("mirostat", C.c_int32), ("mirostat_tau", C.c_float), ("mirostat_eta", C.c_float), ("typical_p", C.c_float),
-        ("tfs_z", C.c_float), ("reserved", C.c_int32 * 3), ("grammar", C.c_char_p),
+        ("tfs_z", C.c_float), ("penalize_nl", C.c_int32), ("reserved", C.c_int32 * 2), ("grammar", C.c_char_p),
     ]
 
 
@@ -345,7 +345,8 @@ class Engine:
                ignore_eos: bool = False, cache_prompt: bool = False, n_keep: int = 0, embedding_mode: bool = False,
                stop: Sequence[str | bytes] = (), stream: bool = True, repeat_penalty: float = 1.0, repeat_last_n: int = 64,
                frequency_penalty: float = 0.0, presence_penalty: float = 0.0, mirostat: int = 0, mirostat_tau: float = 5.0,
-               mirostat_eta: float = 0.1, typical_p: float = 1.0, tfs_z: float = 1.0, grammar: str | bytes | None = None) -> int:
+               mirostat_eta: float = 0.1, typical_p: float = 1.0, tfs_z: float = 1.0, grammar: str | bytes | None = None,
+               penalize_nl: bool = False) -> int:
         r = Request()
         r.struct_size = C.sizeof(Request)
         keep = []
@@ -364,6 +365,7 @@ class Engine:
         r.mirostat, r.mirostat_tau, r.mirostat_eta, r.typical_p, r.tfs_z = mirostat, mirostat_tau, mirostat_eta, typical_p, tfs_z
         r.ignore_eos, r.cache_prompt, r.n_keep = int(ignore_eos), int(cache_prompt), n_keep
         r.embedding_mode, r.stream = int(embedding_mode), int(stream)
+        r.penalize_nl = int(penalize_nl)
         if grammar:
             g = grammar.encode("utf-8") if isinstance(grammar, str) else bytes(grammar)
             r.grammar = g

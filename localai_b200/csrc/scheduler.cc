@@ -72,6 +72,7 @@ int64_t Scheduler::submit(const b2_request &r) {
     q->cache_prompt = r.cache_prompt != 0;
     q->embedding_mode = r.embedding_mode != 0;
     q->stream = r.stream != 0;
+    q->penalize_nl = r.penalize_nl != 0; // grpc-server.cpp:2111
     if (q->embedding_mode) q->n_predict = 0;
     if (r.struct_size >= offsetof(b2_request, grammar) + sizeof(r.grammar) && r.grammar && r.grammar[0] && !q->embedding_mode)
         q->grammar = grammar_parse(r.grammar); // throws B2_EINVAL: the caller gets the parse error, nothing is queued
@@ -478,7 +479,7 @@ bool Scheduler::step() {
                 sp.repeat_penalty = s.req->repeat_penalty;
                 sp.frequency_penalty = s.req->frequency_penalty;
                 sp.presence_penalty = s.req->presence_penalty;
-                sp.nl_token = eng_->tokenizer()->nl_id();
+                sp.nl_token = s.req->penalize_nl ? -1 : eng_->tokenizer()->nl_id(); // the newline is exempt unless PenalizeNL
                 {
                     const int hist = (int)s.cache_tokens.size();
                     int last_n = s.req->repeat_last_n < 0 ? hist : s.req->repeat_last_n;

@@ -40,7 +40,7 @@ struct Request {
     int top_k = 0, repeat_last_n = 0, seed = -1, n_keep = 0;
     int mirostat = 0;
     float mirostat_tau = 5.f, mirostat_eta = 0.1f, typical_p = 1.f, tfs_z = 1.f;
-    bool ignore_eos = false, cache_prompt = false, embedding_mode = false, stream = true;
+    bool ignore_eos = false, cache_prompt = false, embedding_mode = false, stream = true, penalize_nl = false;
     std::vector<std::string> stop;
     std::shared_ptr<const GrammarRules> grammar; // parsed at submit; null = unconstrained
     // results

@@ -1,0 +1,6 @@
+#!/bin/bash
+# ncu --set full capture of one decode_mega_kernel launch (after the same command ran clean without ncu)
+mkdir -p gpurun_out
+timeout 600 python scratch/prof_mega.py > gpurun_out/r2_prof_plain.log 2>&1 &&
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:decode_mega -s 4 -c 1 -f -o gpurun_out/r2_mega_v8 python scratch/prof_mega.py > gpurun_out/r2_ncu_mega.log 2>&1
+echo "rc=$?"; tail -3 gpurun_out/r2_prof_plain.log; tail -5 gpurun_out/r2_ncu_mega.log; ls -la gpurun_out/*.ncu-rep
