@@ -2,16 +2,22 @@
 """bench.py -- BASELINE.json's metric on BASELINE.json's config, one JSON line on stdout.
 
 Workload (config.workload): configs[1] = Llama-3-8B-arch GGUF Q4_K_M, random-init, batch-1 greedy decode
-(the north-star number) at a short context; the same run also reports batch-64 decode and the 2048-token
-prefill as `extra`.  A "step" is one decode step (one token for every active sequence).
+(the north-star number) at a short context.  A "step" is one decode step (one token for every active sequence).
 
   value     decode tok/s with everything resident in HBM (b2_bench_decode: CUDA events on the engine's stream)
   e2e       the same metric through the request path a LocalAI backend uses (b2_submit / b2_poll, i.e.
             PredictStream): host prompt ids in, token text out, per-step H2D/D2H inside the timed region;
             tok/s = n_decoded / t_generation as the reference defines it (grpc-server.cpp:305-318)
-  roofline  the dominant kernel (streaming dequant-GEMV on the Q4_K ffn_gate matrices) timed alone with CUDA
-            events; achieved = rows x row_bytes / time against MEASURED_PEAKS.json hbm_gbs
-  cpu_baseline  the oracle (C restatement of the llama.cpp CPU path, OpenMP) on a bounded sample, same GGUF
+  roofline  the dominant kernel IS the step: one launch of decode_mega_kernel per token.  achieved = (every weight
+            byte once + the KV rows read) / the mean duration of that kernel's launches, measured live with CUDA events
+            recorded around every launch on the engine's stream; peak = MEASURED_PEAKS.json hbm_gbs; traffic = the
+            dram bytes of one launch from the committed ncu capture (profiles/r2_mega_traffic.json)
+  cpu_baseline  the oracle (C restatement of the llama.cpp CPU path, scalar loops under OpenMP -- NOT llama.cpp's
+            AVX2 / AVX-512 build, which cannot be built offline) on a bounded sample of the same workload, same GGUF
+  parity_checked  the first 16 tokens of the e2e request equal the oracle's greedy continuation of the same prompt
+  extra     the other BASELINE configs on the same box, each with its own roofline: TinyLlama Q8_0 b=1 (configs[0]),
+            64 concurrent streams (configs[2]), 2048-token prefill, BERT-base F16 embeddings (configs[3]); at N > 1
+            also `pool`: ONE process driving a ReplicaPool over the N devices (the deployment shape)
 
 N > 1 (torchrun): independent per-GPU replicas, no data-path collective ("replicas only", SURVEY.md 8e);
 value = tokens of all ranks / max-over-ranks time.
@@ -35,9 +41,18 @@ sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 METRIC = "Llama-3-8B Q4_K_M decode tok/s (b=1)"
 UNIT = "tok/s"
-# dram__bytes_read.sum + dram__bytes_write.sum of one decode_mega_kernel launch (llama3-8b q4_k_m, ctx 128), from the
-# ncu --set full capture summarised in profiles/ (None until a capture of the current kernel is committed)
-MEGA_TRAFFIC_BYTES = 4.6731e9  # profiles/r1_mega_v6_ncu_summary.txt: 4.6391 GB read + 34.1 MB written
+
+
+def mega_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE decode_mega_kernel launch (llama3-8b q4_k_m, ctx ~128), as
+    tools/ncu_traffic.py extracted it from the committed ncu --set full capture; None if no capture is committed."""
+    p = os.path.join(ROOT, "profiles", "r2_mega_traffic.json")
+    try:
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["dram_bytes_read"]) + float(d["dram_bytes_write"]), d.get("source")
+    except Exception:
+        return None, None
 
 
 def log(*a):
@@ -181,6 +196,135 @@ def run_reference(args, rank: int, emit):
         "gpu_launches": 0,
     }
     emit(line)
+
+
+def eng_pieces(path: str, ids):
+    """token ids -> the bytes the engine would stream for them (host tokenizer only)."""
+    from localai_b200 import capi
+
+    with capi.Engine(path, vocab_only=True) as e:
+        return [e.token_to_piece(int(t)) for t in ids]
+
+
+def bench_tinyllama(args, rank, local_rank, world, ranks, peak):
+    """BASELINE configs[0]: TinyLlama-1.1B-arch Q8_0, batch-1 greedy decode after a 128-token prompt."""
+    import numpy as np
+
+    from localai_b200 import capi
+
+    path, _ = ensure_model("tinyllama-1.1b", "q8_0", 0, rank, ranks.barrier)
+    with capi.Engine(path, n_ctx=512, n_batch=128, n_parallel=1, device=local_rank) as e:
+        ms, launches = e.bench_decode(1, 128, 64, 5)
+        k_ms = ranks.max(e.last_mega_ms())
+        ms = ranks.max(ms)
+        step_bytes = e.info.decode_stream_bytes + e.info.kv_bytes_per_pos * 128
+        prompt = (np.arange(128) * 7919 % 4000 + 3).astype(np.int32)
+        got, _, _ = e.decode_greedy(prompt, 16)
+    out = {"metric": "TinyLlama-1.1B Q8_0 decode tok/s (b=1)", "tok_s": world * 1e3 / ms, "ms_per_step": ms, "launches_per_step": launches,
+           "roofline": {"bound": "hbm", "kernel": "decode_mega_kernel", "achieved": step_bytes / ((k_ms or ms) * 1e-3) / 1e9, "peak": peak,
+                        "unit": "GB/s", "frac": step_bytes / ((k_ms or ms) * 1e-3) / 1e9 / peak, "bytes_per_launch": step_bytes,
+                        "us_per_launch": (k_ms or ms) * 1e3}}
+    if rank == 0 and world == 1:
+        try:
+            from oracle import oracle as O
+
+            O.set_num_threads(os.cpu_count() or 1)
+            t0 = time.time()
+            want, _, _ = O.OracleModel(path, n_ctx=256).generate_greedy(prompt, 16)
+            out["cpu_tok_s"] = (128 + 16) / (time.time() - t0)
+            out["parity_checked"] = bool(got.tolist() == want.tolist())
+        except Exception as ex:  # noqa: BLE001
+            out["parity_checked"] = False
+            out["parity_error"] = str(ex)
+    return out
+
+
+def bench_bert_extra(rank, local_rank, world, ranks):
+    """BASELINE configs[3]: BERT-base F16 embeddings of 512-token texts: 16 texts per call, and one text per call (the
+    shape of the reference API, backend.proto:141)."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import make_bert_gguf as mb
+    from localai_b200 import capi
+
+    d = os.environ.get("B200LLM_BENCH_DIR", "/dev/shm/b200llm_bench" if os.path.isdir("/dev/shm") else "/tmp/b200llm_bench")
+    os.makedirs(d, exist_ok=True)
+    path = os.path.join(d, "bert_base_f16_seed0.gguf")
+    if rank == 0 and not os.path.exists(path):
+        mb.write_bert_gguf(path + ".tmp", mb.BERT_ARCHS["bert-base"], seed=0)
+        os.replace(path + ".tmp", path)
+    ranks.barrier()
+    a = mb.BERT_ARCHS["bert-base"]
+    n_tok = 512
+    flops_seq = 2.0 * a.n_layer * (4 * a.n_embd * a.n_embd + 2 * a.n_embd * a.n_ff) * n_tok + 4.0 * n_tok * n_tok * a.n_embd * a.n_layer
+    with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+        tf_peak = float(json.load(f).get("bf16_tflops_sustained", 1400.0))
+    rng = np.random.default_rng(rank)
+    out = {"metric": "BERT-base F16 embeddings seq/s (512-token texts)"}
+    with capi.Bert(path, device=local_rank) as b:
+        L = capi.lib()
+        for per_call, n_calls in ((16, 16), (1, 64)):
+            ids = np.ascontiguousarray(np.concatenate([np.concatenate([[2], rng.integers(5, 30000, n_tok - 2), [3]]) for _ in range(per_call)]), dtype=np.int32)
+            offs = (np.arange(per_call + 1) * n_tok).astype(np.int32)
+            vec = np.empty((per_call, b.n_embd), dtype=np.float32)
+            for _ in range(3):
+                assert L.b2_bert_embed_batch(b._h, ids.ctypes.data, offs.ctypes.data, per_call, vec.ctypes.data) == per_call
+            ranks.barrier()
+            t0 = time.perf_counter()
+            for _ in range(n_calls):
+                L.b2_bert_embed_batch(b._h, ids.ctypes.data, offs.ctypes.data, per_call, vec.ctypes.data)
+            dt = ranks.max(time.perf_counter() - t0)
+            tf = flops_seq * per_call * n_calls / dt / 1e12
+            out["per_call_%d" % per_call] = {"seq_s": world * per_call * n_calls / dt, "ms_per_call": dt * 1e3 / n_calls,
+                                             "roofline": {"bound": "tensor", "achieved": tf, "peak": tf_peak, "unit": "TFLOP/s", "frac": tf / tf_peak}}
+        if rank == 0 and world == 1:
+            try:
+                from oracle.bert_ref import BertRef
+
+                want = BertRef(path).embed_tokens(ids[:n_tok])
+                got = b.embed_tokens(ids[:n_tok])
+                cos = float((got * want).sum() / np.sqrt((got * got).sum() * (want * want).sum()))
+                out["parity_checked"] = bool(cos >= 0.9995)
+                out["cosine_vs_oracle"] = cos
+            except Exception as ex:  # noqa: BLE001
+                out["parity_checked"] = False
+                out["parity_error"] = str(ex)
+    return out
+
+
+def bench_pool(path, rank, world, ranks):
+    """N > 1: ONE process (rank 0) drives a ReplicaPool over all N devices -- one engine per GPU, least-loaded dispatch --
+    with 64 x N concurrent greedy streams submitted from the host; the other ranks wait at the barrier."""
+    import numpy as np
+
+    out = None
+    ranks.barrier()
+    if rank == 0:
+        from localai_b200.replicas import ReplicaPool
+
+        n_streams, n_predict = 64 * world, 32
+        pool = ReplicaPool(path, devices=list(range(world)), n_ctx=64 * 256, n_batch=512, n_parallel=64)
+        try:
+            rng = np.random.default_rng(5)
+            prompts = [rng.integers(3, 4000, 16).astype(np.int32) for _ in range(n_streams)]
+            warm = [pool.submit(prompt_ids=p, n_predict=4, temperature=0.0, ignore_eos=True, stream=False) for p in prompts[:world]]
+            for h in warm:
+                list(pool.events(h))
+            pool.assigned = [0] * len(pool.devices)
+            t0 = time.perf_counter()
+            hs = [pool.submit(prompt_ids=p, n_predict=n_predict, temperature=0.0, ignore_eos=True, stream=False) for p in prompts]
+            n_tok = 0
+            for h in hs:
+                n_tok += list(pool.events(h))[-1]["n_decoded"]
+            dt = time.perf_counter() - t0
+            out = {"tok_s": n_tok / dt, "streams": n_streams, "n_predict": n_predict, "wall_s": dt, "assigned_per_replica": list(pool.assigned),
+                   "path": "one process, ReplicaPool over %d devices, b2_submit / b2_poll with host buffers (prompt + decode inside the timed region)" % world}
+        finally:
+            pool.close()
+    ranks.barrier()
+    return out
+
 
 
 def run_bert(args, rank, local_rank, world, ranks, emit, warmup):
@@ -348,44 +492,96 @@ def main():
            "path": "b2_submit/b2_poll (PredictStream), greedy, host prompt ids"}
 
     # ---- roofline of the dominant kernel.  A b=1 decode step IS one launch of decode_mega_kernel (the persistent
-    # kernel that walks every layer), so its launch duration is the step time measured above with CUDA events on the
-    # engine's stream, and its algorithmic bytes are the step's: every weight row once + the KV rows read.
-    # `traffic` is dram__bytes_read.sum + dram__bytes_write.sum of one launch from profiles/r1_mega_ncu_raw.csv.
-    achieved = step_bytes / (ms * 1e-3) / 1e9
-    k_ms, k_bytes, k_type = eng.bench_gemv(4, 1, 8)  # the row-streaming loop alone on one ffn_gate matrix, for reference
-    roofline = {"bound": "hbm", "kernel": "decode_mega_kernel (1 launch per decode step)" if launches == 1 else
+    # kernel that walks every layer): its launches were timed one by one with CUDA events on the engine's stream
+    # during the timed region above; its algorithmic bytes are the step's: every weight byte once + the KV rows read.
+    mega_ms = max_over_ranks(eng.last_mega_ms())
+    k_ms = mega_ms if mega_ms > 0 else ms  # (the fused per-layer kernels took the step: whole-step time)
+    achieved = step_bytes / (k_ms * 1e-3) / 1e9
+    traffic, traffic_src = mega_traffic()
+    roofline = {"bound": "hbm", "kernel": "decode_mega_kernel (one launch per decode step; CUDA events around every launch)" if mega_ms > 0 else
                 "fused decode kernels (%d launches per step), whole step" % launches,
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": MEGA_TRAFFIC_BYTES,
-                "bytes_per_launch": step_bytes, "us_per_launch": ms * 1e3, "peak_source": peak_src,
-                "frac_of_8tbs": step_bytes / (ms * 1e-3) / 8e12,
-                "gemv_alone": {"kernel": f"gemv_kernel<type {k_type}, NT=1> on ffn_gate [{eng.info.n_ff}x{eng.info.n_embd}]",
-                               "bytes_per_launch": k_bytes, "us_per_launch": k_ms * 1e3,
-                               "achieved": k_bytes / (k_ms * 1e-3) / 1e9, "frac": k_bytes / (k_ms * 1e-3) / 1e9 / peak}}
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                "bytes_per_launch": step_bytes, "us_per_launch": k_ms * 1e3, "step_us": ms * 1e3, "kernel_share_of_step": k_ms / ms,
+                "peak_source": peak_src, "frac_of_8tbs": step_bytes / (k_ms * 1e-3) / 8e12}
 
     extra = {}
     cpu = None
+    parity_checked = None
     if not args.no_extras:
-        try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            tf_peak = float(json.load(f).get("bf16_tflops_sustained", 1400.0))
+        i = eng.info
+        kvd = i.n_head_kv * i.head_dim
+        lin_params = i.n_layer * (2 * i.n_embd * i.n_embd + 2 * i.n_embd * kvd + 3 * i.n_embd * i.n_ff)  # mat-mul weights of the layers
+        head_params = i.n_vocab * i.n_embd
+        try:  # configs[2]: 64 concurrent streams, one step = one token for each
             bms, bl = eng.bench_decode(n_par, args.ctx, max(8, args.steps // 8), 3)
             bms = max_over_ranks(bms)
-            extra["decode_b%d" % n_par] = {"tok_s": world * n_par * 1e3 / bms, "ms_per_step": bms, "launches_per_step": bl,
-                                           "hbm_frac_of_measured": (stream_bytes + n_par * kv_per_pos * args.ctx) / (bms * 1e-3) / 1e9 / peak}
+            b_bytes = stream_bytes + n_par * kv_per_pos * args.ctx
+            b_flops = 2.0 * (lin_params + head_params) * n_par
+            extra["decode_b%d" % n_par] = {
+                "tok_s": world * n_par * 1e3 / bms, "ms_per_step": bms, "launches_per_step": bl,
+                "hbm": {"bound": "hbm", "achieved": b_bytes / (bms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": b_bytes / (bms * 1e-3) / 1e9 / peak},
+                "tensor": {"bound": "tensor", "achieved": b_flops / (bms * 1e-3) / 1e12, "peak": tf_peak, "unit": "TFLOP/s",
+                           "frac": b_flops / (bms * 1e-3) / 1e12 / tf_peak}}
         except capi.B2Error as ex:
             extra["decode_b%d" % n_par] = {"error": str(ex)}
-        try:
+        try:  # 2048-token prefill
             pms, pl = eng.bench_prefill(args.prefill, 2, 1)
             pms = max_over_ranks(pms)
-            extra["prefill_%d" % args.prefill] = {"tok_s": world * args.prefill * 1e3 / pms, "ms": pms, "launches": pl}
+            n = args.prefill
+            p_flops = 2.0 * lin_params * n + 2.0 * n * n * i.n_embd * i.n_layer + 2.0 * head_params  # causal attention: half of 4 n^2 d
+            extra["prefill_%d" % n] = {"tok_s": world * n * 1e3 / pms, "ms": pms, "launches": pl,
+                                       "roofline": {"bound": "tensor", "achieved": p_flops / (pms * 1e-3) / 1e12, "peak": tf_peak,
+                                                    "unit": "TFLOP/s", "frac": p_flops / (pms * 1e-3) / 1e12 / tf_peak}}
         except capi.B2Error as ex:
             extra["prefill_%d" % args.prefill] = {"error": str(ex)}
         if rank == 0 and world == 1:
+            # ---- the checker, after every timed region: the oracle continues the e2e request's prompt greedily; its
+            # first 16 tokens must be the text the engine streamed.  The same run is the CPU baseline sample.
             try:
-                dv, pv, cores = cpu_sample(path, 8, 8)
-                cpu = {"value": dv, "unit": UNIT, "cores": cores, "kind": "port", "prompt_tok_s": pv,
-                       "sample": "oracle (C restatement of the llama.cpp CPU path, OpenMP): 8-token prompt + 8 greedy decode steps on the same GGUF"}
+                from oracle import oracle as O
+
+                O.set_num_threads(os.cpu_count() or 1)
+                n_chk = max(1, min(16, fin["n_decoded"]))
+                n_dec = max(n_chk, min(args.steps, 20))
+                m = O.OracleModel(path, n_ctx=args.ctx + n_dec + 8)
+                t1 = time.time()
+                lg = m.eval(prompt)
+                t2 = time.time()
+                ids = []
+                for k in range(n_dec):
+                    ids.append(int(lg[0].argmax()))
+                    lg = m.eval([ids[-1]], n_past=args.ctx + k)
+                t3 = time.time()
+                want_text = b"".join(eng_pieces(path, ids[:n_chk]))
+                got_text = b"".join(ev["text"] for ev in evs)
+                parity_checked = bool(got_text[:len(want_text)] == want_text and len(want_text) > 0)
+                cores = O.num_threads()
+                cpu = {"value": n_dec / (t3 - t2), "unit": UNIT, "cores": cores, "kind": "port", "prompt_tok_s": args.ctx / (t2 - t1),
+                       "sample": f"oracle (C restatement of the llama.cpp CPU path: scalar block dots under OpenMP, {cores} threads; NOT "
+                                 f"llama.cpp's AVX2/AVX-512 build, which cannot be built offline): {args.ctx}-token prompt + {n_dec} greedy "
+                                 f"decode steps at ctx {args.ctx} on the same GGUF"}
+                del m
             except Exception as ex:  # the checker failing must not void the GPU measurement
                 cpu = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {ex}"}
+                parity_checked = False
     eng.close()
+    if not args.no_extras:
+        try:
+            extra["tinyllama_q8_0_b1"] = bench_tinyllama(args, rank, local_rank, world, ranks, peak)
+        except Exception as ex:  # noqa: BLE001
+            extra["tinyllama_q8_0_b1"] = {"error": str(ex)}
+        try:
+            extra["bert_base_256x512"] = bench_bert_extra(rank, local_rank, world, ranks)
+        except Exception as ex:  # noqa: BLE001
+            extra["bert_base_256x512"] = {"error": str(ex)}
+        if world > 1:
+            try:
+                extra["pool"] = bench_pool(path, rank, world, ranks)
+            except Exception as ex:  # noqa: BLE001
+                extra["pool"] = {"error": str(ex)}
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
@@ -396,7 +592,7 @@ def main():
                        "decode_stream_bytes": stream_bytes, "kv_bytes_per_pos": kv_per_pos, "n_batch": n_batch,
                        "n_parallel": n_par},
             "e2e": e2e, "gpu_launches": int(launches) * args.steps, "gpu_launches_per_step": int(launches),
-            "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "extra": extra,
+            "roofline": roofline, "cpu_baseline": cpu, "parity_checked": parity_checked, "clocks": clocks, "extra": extra,
         }
         emit(line)
     ranks.close()

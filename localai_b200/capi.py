@@ -329,6 +329,12 @@ class Engine:
         _check(lib().b2_bench_decode(self._h, batch, ctx_len, n_steps, n_warmup, C.byref(ms), C.byref(l)))
         return ms.value, l.value
 
+    def last_mega_ms(self) -> float:
+        """mean decode_mega_kernel launch (ms) of the last bench_decode(1, ...): CUDA events around every launch"""
+        f = lib().b2_bench_last_mega_ms
+        f.restype, f.argtypes = C.c_double, [C.c_void_p]
+        return float(f(self._h))
+
     def bench_prefill(self, n_tokens: int, n_iters: int, n_warmup: int = 1):
         ms, l = C.c_double(0), C.c_int64(0)
         _check(lib().b2_bench_prefill(self._h, n_tokens, n_iters, n_warmup, C.byref(ms), C.byref(l)))
@@ -392,9 +398,12 @@ class Engine:
         return dict(flags=ev.flags, text=text, n_prompt_tokens=ev.n_prompt_tokens, n_decoded=ev.n_decoded,
                     slot_id=ev.slot_id, n_embd=ev.n_embd, t_prompt_ms=ev.t_prompt_ms, t_gen_ms=ev.t_gen_ms)
 
-    def events(self, rid: int) -> Iterator[dict]:
+    def events(self, rid: int, timeout_ms: int = -1) -> Iterator[dict]:
+        """every event of the request up to the final one; timeout_ms bounds the wait for each (-1: none)"""
         while True:
-            ev = self.poll(rid, -1)
+            ev = self.poll(rid, timeout_ms)
+            if ev is None:
+                raise TimeoutError(f"request {rid}: no event within {timeout_ms} ms")
             yield ev
             if ev["flags"] & EV_FINAL:
                 return

@@ -196,6 +196,16 @@ int b2_bench_decode(b2_engine *e, int batch, int ctx_len, int n_steps, int n_war
     B2_API_END(0)
 }
 
+// undocumented bench hook (not part of the ABI header): mean duration in ms of one decode_mega_kernel launch during the
+// last b2_bench_decode with batch 1 (CUDA events on the engine's stream around every launch); 0 if that kernel did not run
+double b2_bench_last_mega_ms(b2_engine *e) {
+    try {
+        return e ? E(e)->last_mega_ms() : 0.0;
+    } catch (...) {
+        return 0.0;
+    }
+}
+
 // undocumented profiling hook (not part of the ABI header): per-CTA, per-phase clock64 stamps of the decode mega-kernel
 int b2_mega_debug(b2_engine *e, long long *out, int cap) {
     B2_API_BEGIN
@@ -226,7 +236,7 @@ int64_t b2_mega_plan_check(const int64_t *desc, int n_phases, int n_cta, int64_t
         }
         m.fmt = act_format_for(m.job[0].type);
         m.units = (int)(m.kind == PH_SWIGLU ? m.job[0].rows : rows / 2);
-        if (m.kind == PH_PLAIN && m.K / 256 > 32 && m.K <= 32768) m.xq_global = (uint8_t *)16; // as Model::build_mega: quantised once per GPU
+        if (m.kind == PH_PLAIN && m.K / 256 > 32 && m.K <= 32768) m.xq_ll = (uint2 *)16; // as Model::build_mega: quantised once per GPU
         B2_CHECK(mega_phase_prepare(m, n_cta), B2_EUNSUPPORTED, "phase " + std::to_string(p) + ": no lane mapping for this shape/type");
     }
     return mega_plan_check(ph.data(), n_phases, n_cta, n_tiles);
@@ -349,13 +359,12 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
         MegaStreams ms;
         ms.build(&ph, 1, n_sm, 0);
         struct Guard { MegaStreams &m; ~Guard() { m.free(); } } guard{ms};
-        DevBuf dph(sizeof(MegaPhase)), dbar(4096), dps(64);
+        DevBuf dph(sizeof(MegaPhase)), dps(64);
         B2_CUDA(cudaMemcpy(dph.p, &ph, sizeof(ph), cudaMemcpyHostToDevice));
-        B2_CUDA(cudaMemset(dbar.p, 0, 4096));
         B2_CUDA(cudaMemset(dps.p, 0, 64));
         MegaArgs a;
         a.phases = dph.as<MegaPhase>(); a.n_phases = 1; a.starts = ms.starts; a.pos = dps.as<int32_t>(); a.slot = dps.as<int32_t>() + 4;
-        a.bar = dbar.as<unsigned>(); a.page_size = 32; a.page_shift = 5; a.max_pages = 1; a.hd = 64; a.n_head = 1; a.n_head_kv = 1;
+        a.page_size = 32; a.page_shift = 5; a.max_pages = 1; a.hd = 64; a.n_head = 1; a.n_head_kv = 1;
         launch_decode_mega(a, n_sm, 0);
         B2_CUDA(cudaDeviceSynchronize());
     } else {

@@ -40,6 +40,8 @@ class Engine {
     int debug_hidden(float *out, int cap_floats);
     int bench_decode(int batch, int ctx_len, int n_steps, int n_warmup, double *ms_per_step, int64_t *launches);
     int mega_debug(long long *out, int cap);
+    double last_mega_ms() const { return last_mega_ms_; } // mean decode_mega_kernel launch of the last bench_decode(batch 1)
+    double last_mega_ms_ = 0.0;
     int bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type);
     int bench_prefill(int n_tokens, int n_iters, int n_warmup, double *ms_per_iter, int64_t *launches);
 

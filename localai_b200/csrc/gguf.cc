@@ -79,6 +79,9 @@ GGUFFile::GGUFFile(const std::string &path) {
             if (v.type == GT_ARR) {
                 v.elem_type = (GGUFType)c.rd<uint32_t>();
                 const uint64_t n = c.rd<uint64_t>();
+                // an array element takes at least one byte of the file (strings: 8): a count beyond what is left of
+                // the file is a corrupt header, not something to reserve memory for
+                if (n > (uint64_t)(c.end - c.p)) throw Error(B2_EIO, "gguf: array length exceeds the file size (key " + key + ")");
                 if (v.elem_type == GT_STR) {
                     v.arr_s.reserve(n);
                     for (uint64_t k = 0; k < n; k++) v.arr_s.push_back(c.str());
@@ -102,6 +105,7 @@ GGUFFile::GGUFFile(const std::string &path) {
             }
             kv.emplace(std::move(key), std::move(v));
         }
+        if (n_tensors > (uint64_t)(c.end - c.p) / 24) throw Error(B2_EIO, "gguf: tensor count exceeds the file size"); // >= 24 bytes per info
         tensors.resize(n_tensors);
         for (uint64_t i = 0; i < n_tensors; i++) {
             GGUFTensorInfo &t = tensors[i];
@@ -113,19 +117,26 @@ GGUFFile::GGUFFile(const std::string &path) {
             t.offset = c.rd<uint64_t>();
         }
         const uint64_t align = get_u("general.alignment", 32);
+        if (align == 0 || (align & (align - 1)) != 0 || align > (1u << 20)) throw Error(B2_EIO, "gguf: general.alignment must be a power of two");
         const size_t meta = (size_t)(c.p - map_);
         const size_t data_off = (meta + align - 1) / align * align;
+        if (data_off > file_size) throw Error(B2_EIO, "gguf: header exceeds file size");
         for (size_t i = 0; i < tensors.size(); i++) {
             GGUFTensorInfo &t = tensors[i];
             int64_t n = 1;
-            for (auto e : t.ne) n *= e;
+            for (auto e : t.ne) { // the element count must not overflow
+                if (e <= 0 || n > (int64_t)(INT64_MAX / 4) / e) throw Error(B2_EIO, "gguf: tensor " + t.name + " has an invalid shape");
+                n *= e;
+            }
             const int be = type_block_elems(t.type), bb = type_block_bytes(t.type);
             if (be == 0) {
                 t.n_bytes = -1; // unsupported type: only an error if the model needs this tensor
             } else {
                 if (t.ne.empty() || t.ne[0] % be != 0) throw Error(B2_EIO, "gguf: tensor " + t.name + " row not a block multiple");
                 t.n_bytes = n / be * bb;
-                if (data_off + t.offset + (uint64_t)t.n_bytes > file_size)
+                // overflow-safe: offset <= file_size - data_off - n_bytes
+                const uint64_t room = (uint64_t)(file_size - data_off);
+                if ((uint64_t)t.n_bytes > room || t.offset > room - (uint64_t)t.n_bytes)
                     throw Error(B2_EIO, "gguf: tensor " + t.name + " exceeds file size");
             }
             t.data = map_ + data_off + t.offset;

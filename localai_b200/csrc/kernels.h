@@ -90,21 +90,32 @@ void launch_fused_gemv(FusedGemv a, int n_tok, cudaStream_t s);
 
 // --- persistent decode mega-kernel (kernels_mega.cu) ------------------------------------------------------------
 enum { PH_QKV = 0, PH_ATT = 1, PH_PLAIN = 2, PH_SWIGLU = 3 };
+// Activations that one phase hands to the next travel as 8-byte {fp32 value, 32-bit tag} words ("LL" words, the idea
+// of NCCL's low-latency protocol): the producer stores value and tag with ONE 64-bit store, the consumer polls the
+// word itself until it carries the tag of the producing phase.  Data and "ready" flag cannot be seen out of order,
+// so there is no fence, no atomic and no separate barrier round trip between two phases.
 struct MegaPhase {
     int kind = PH_PLAIN;
     int64_t K = 0;
     int fmt = 0;
     int n_jobs = 0;
     FusedJob job[3];
-    const float *x = nullptr;      // fp32 activation row (PH_ATT: q)
+    // input row: either plain fp32 written before the launch (x, src_p = -1) or LL words written by phase src_p
+    const float *x = nullptr;
+    const uint2 *x_ll = nullptr;   // PH_ATT: q
+    int src_p = -1;
     const float *norm_w = nullptr; // RMSNorm weights applied before quantisation (optional)
-    float *out = nullptr;          // PLAIN/SWIGLU: output row; QKV: q; ATT: attention output
-    const float *residual = nullptr;
+    // output row: LL words (consumed by a later phase) or plain fp32 (logits); QKV: q; ATT: attention output
+    float *out = nullptr;
+    uint2 *out_ll = nullptr;
+    const float *residual = nullptr; // plain fp32 residual (written before the launch)
+    const uint2 *res_ll = nullptr;   // residual in LL words (written by an earlier phase; no tag check needed)
     float *xn_out = nullptr;       // optional: the normalised row (LM head -> embeddings)
     __half *k_pool = nullptr, *v_pool = nullptr; // this layer's KV pools (QKV, ATT)
-    uint8_t *xq_global = nullptr;  // if set: the row is quantised once per GPU into this buffer (one more grid barrier)
+    uint2 *xq_ll = nullptr;        // if set: the row is quantised once per GPU (block b by CTA b) into this buffer of
+                                   // LL words holding the image of the shared-memory activation row, then copied
     int units = 0;                 // row pairs (PLAIN/QKV) or rows (SWIGLU) split across the CTAs
-    // lane geometry, filled by mega_phase_prepare() so that the kernel's schedule walk needs no integer division:
+    // lane geometry, filled by mega_phase_prepare() so that the kernel needs no integer division:
     int S = 1, s_log = 0;          // K-splits (power of two <= warps per CTA): a row is spread over S warps
     int lpr = 32, lpr_log = 5;     // lanes that share one (row, K-split); rpp = 32 / lpr rows per warp pass when lpr < 32
     int rpp = 1, np = 0;           // np: Q8_0 16-byte pieces per lane
@@ -130,16 +141,13 @@ struct MegaArgs {
     int page_size = 0, max_pages = 0, kvd = 0, n_head = 0, n_head_kv = 0, hd = 0;
     float eps = 0.f, att_scale = 0.f;
     int page_shift = 0;      // log2(page_size)
-    unsigned *bar = nullptr; // arrival counter, zero-initialised once; it only ever grows
-    unsigned bar_base = 0;   // counter value when this launch starts; the host adds n_cta * (barriers per launch) per launch:
-                             // n_phases - 1, plus one per phase with xq_global
+    unsigned tag_base = 0;   // LL tag of phase p's outputs = tag_base + p + 1; the host adds n_phases per launch
+    uint2 *kcur_ll = nullptr, *vcur_ll = nullptr; // [kvd] the current token's K / V row (f16-rounded values) as LL words
     // attention of one head split over att_parts CTAs (power of two, att_parts * n_head <= CTAs; 1 = one CTA per head)
     int att_parts = 1, att_parts_log = 0;
-    float *att_scores = nullptr;     // [n_head][att_scores_stride] scores of the current layer
+    uint2 *att_scores = nullptr;     // [n_head][att_scores_stride] scores of the current layer (LL words)
     int64_t att_scores_stride = 0;
-    float *att_part_out = nullptr;   // [n_head][att_parts][hd] partial outputs
-    unsigned *att_cnt = nullptr;     // [n_head][2] counters (scores written, partial outputs written), zero-initialised once
-    unsigned att_base = 0;           // counter value when this launch starts; the host adds n_att_phases * att_parts per launch
+    uint2 *att_part_out = nullptr;   // [n_head][att_parts][hd] partial outputs (LL words)
     long long *dbg = nullptr; // optional [n_cta][n_phases][16] clock64 stamps and per-phase cycle counts (scratch/mega_dbg.py)
 };
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s);

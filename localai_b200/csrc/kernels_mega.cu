@@ -51,7 +51,7 @@ constexpr size_t MG_OFF_PART = MG_OFF_XS + MG_XS_BYTES;
 constexpr size_t MG_OFF_RED = MG_OFF_PART + MG_MAX_PART * sizeof(float);
 constexpr size_t MG_OFF_BAR = MG_OFF_RED + 32 * sizeof(double);
 constexpr int MG_MAX_PAGES = 512;            // page-table entries of the sequence kept in shared memory
-constexpr int MG_PH_WIN = 2;                 // phase descriptors kept in shared memory: phases [p, p + 2)
+constexpr int MG_PH_WIN = 3;                 // phase descriptors kept in shared memory: phases p - 1, p, p + 1
 constexpr size_t MG_OFF_PH = MG_OFF_BAR + MG_WARPS * MG_STAGES * sizeof(uint64_t);
 constexpr size_t MG_OFF_PT = MG_OFF_PH + MG_PH_WIN * ((sizeof(MegaPhase) + 15) / 16 * 16);
 constexpr size_t MG_SMEM = MG_OFF_PT + MG_MAX_PAGES * sizeof(int);
@@ -171,23 +171,59 @@ __device__ __forceinline__ int mg_dp4a_us(uint32_t a, int b, int c) { // 4 x (u8
     asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
     return d;
 }
-__device__ __forceinline__ unsigned mg_ld_acquire(const unsigned *p) {
-    unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
+// ---- LL words: {fp32 value, 32-bit tag} moved as ONE 64-bit access, so value and "ready" flag travel together ----
+__device__ __forceinline__ void ll_st(uint2 *p, float v, uint32_t tag) {
+    const unsigned long long w = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+    asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
 }
-
-// Grid barrier: ONE monotonically growing arrival counter.  A CTA arrives with a fire-and-forget release reduction
-// and acquire-polls the same word until it reaches base + (k+1) * n_cta; nothing is ever reset, so there is no
-// last-arriver special case and no second word to hand over.  Measured against the alternatives on B200
-// (scratch/ubench/barrier_bench.cu, 148 CTAs): 1.5k cycles, vs 1.8k cooperative-groups grid.sync, 2.7k counter +
-// generation word, 4.7k per-CTA flags.
-__device__ __forceinline__ void mg_grid_barrier(unsigned *cnt, unsigned target) {
-    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(cnt) : "memory");
-    if ((int)(mg_ld_acquire(cnt) - target) >= 0) return;
-    const long long t0 = clock64();
-    while ((int)(mg_ld_acquire(cnt) - target) < 0)
-        if (clock64() - t0 > MG_WATCHDOG) __trap(); // see mg_wait
+__device__ __forceinline__ void ll_st2(uint2 *p, float v0, float v1, uint32_t tag) { // p 16-byte aligned
+    const unsigned long long w0 = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v0);
+    const unsigned long long w1 = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v1);
+    asm volatile("st.relaxed.gpu.global.v2.b64 [%0], {%1, %2};" ::"l"(p), "l"(w0), "l"(w1) : "memory");
+}
+__device__ __forceinline__ unsigned long long ll_ld(const uint2 *p) {
+    unsigned long long w;
+    asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    return w;
+}
+__device__ __forceinline__ void ll_ld2(const uint2 *p, unsigned long long &w0, unsigned long long &w1) { // p 16-byte aligned
+    asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+}
+__device__ __forceinline__ uint32_t ll_tag(unsigned long long w) { return (uint32_t)(w >> 32); }
+__device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((uint32_t)w); }
+// Spin budget of every LL wait: a wait that long is a bug (a producer that never ran), and traps instead of hanging.
+constexpr unsigned MG_SPIN_LIMIT = 1u << 27;
+__device__ unsigned g_ll_probe = 1;   // B200LLM_LL_PROBE=0: no light probe before the full-slice poll
+__device__ unsigned g_ll_poll_ns = 32; // B200LLM_LL_POLL_NS (tuning knob): sleep between two polls of an LL word
+__device__ __forceinline__ void ll_backoff(unsigned &spins) {
+    const unsigned ns = g_ll_poll_ns;
+    if (ns) __nanosleep(ns);
+    if (++spins > MG_SPIN_LIMIT) __trap();
+}
+// one word, polled by one thread until it carries `tag`
+__device__ __forceinline__ float ll_wait(const uint2 *p, uint32_t tag) {
+    unsigned long long w = ll_ld(p);
+    unsigned spins = 0;
+    while (ll_tag(w) != tag) {
+        ll_backoff(spins);
+        w = ll_ld(p);
+    }
+    return ll_val(w);
+}
+// 8 consecutive words (64 bytes, 16-byte aligned) -> v; false when some word does not carry `tag` yet
+__device__ __forceinline__ bool ll_ld8(const uint2 *p, uint32_t tag, float (&v)[8]) {
+    unsigned long long w[8];
+    ll_ld2(p, w[0], w[1]);
+    ll_ld2(p + 2, w[2], w[3]);
+    ll_ld2(p + 4, w[4], w[5]);
+    ll_ld2(p + 6, w[6], w[7]);
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        ok = ok && ll_tag(w[i]) == tag;
+        v[i] = ll_val(w[i]);
+    }
+    return ok;
 }
 
 inline int64_t mg_act_row_bytes_host(int fmt, int64_t K) {
@@ -341,157 +377,33 @@ __device__ __forceinline__ float mg_reduce2(float v0, float v1, int lane) {
 
 
 // ------------------------------------------------------------------------------------------------ attention
-// One (head, query token) per CTA, written for LATENCY: at short context the phase is a chain of dependent global
-// round trips, so everything whose address is known up front is requested up front.  The page table of the sequence
-// is in shared memory since kernel start; the K rows (2 threads per position, half a row each) and the V rows of the
-// first 256 positions (lane owns hd/32 dims, warp w owns positions w, w+8, ...) are loaded into registers BEFORE q is
-// waited for; the QKV phase has already pulled the sequence's K/V rows into L2 (mg_prefetch_kv).
-// Numerics as attention_head (attention.cuh): q and the normalised probabilities rounded to f16, fp32 accumulation.
-// scratch: q[hd] | red[32] | part[8][hd] | scores[n_kv].  hd = 64 or 128.
 // row of position j in a layer's K or V pool; 32-bit element index (the host checks that a layer pool has < 2^31 halves)
 __device__ __forceinline__ const __half *mg_kv_row(const __half *pool, const int *pbase, int j, int page_shift, int kvd) {
     const uint32_t cell = ((uint32_t)pbase[j >> page_shift] << page_shift) + (uint32_t)(j & ((1 << page_shift) - 1));
     return pool + cell * (uint32_t)kvd;
 }
-__device__ __noinline__ void mg_attention(const float *__restrict__ qrow, int n_kv, const int *pbase, const __half *k_pool,
-                                             const __half *v_pool, int page_shift, int kvd, int hk, int hd, float scale,
-                                             float *__restrict__ orow, float *scratch, int tid) {
-    const int lane = tid & 31, warp = tid >> 5;
-    float *qs = scratch, *red = qs + hd, *part = red + 32, *sc = part + MG_WARPS * hd;
-    const int half = tid & 1, hh = hd / 2, nld = hh / 8;  // pass 1: this thread's half row = nld 16-byte loads (<= 8)
-    const int dpl = hd / 32, nw = dpl / 2;                // pass 2: halves / 32-bit words per lane (<= 2 words)
-    constexpr int KR = 2, KP = MG_THREADS / 2;            // K: 2 rounds of 128 positions per sweep
-    constexpr int VP = 32;                                // V: 32 positions per warp per sweep, position = j0 + warp + 8u
-    int4 kq[KR][8];
-    uint32_t vq[VP][2];
-    // loads are UNCONDITIONAL on clamped (always valid) positions: see the note in mg_attention_split
-    const int j_last = n_kv - 1;
-    auto load_k = [&](int j0) {
-#pragma unroll
-        for (int r = 0; r < KR; r++) {
-            const int j = min(j0 + r * KP + (tid >> 1), j_last);
-            const __half *kr = mg_kv_row(k_pool, pbase, j, page_shift, kvd) + hk * hd + half * hh;
-#pragma unroll
-            for (int i = 0; i < 8; i++) kq[r][i] = *(const int4 *)(kr + (i < nld ? i : 0) * 8);
-        }
-    };
-    auto load_v = [&](int j0) {
-#pragma unroll
-        for (int u = 0; u < VP; u++) {
-            const int jv = min(j0 + warp + MG_WARPS * u, j_last);
-            const __half *vr = mg_kv_row(v_pool, pbase, jv, page_shift, kvd) + hk * hd + lane * dpl;
-            if (nw == 2) { const int2 t = *(const int2 *)vr; vq[u][0] = t.x; vq[u][1] = t.y; }
-            else { vq[u][0] = *(const uint32_t *)vr; vq[u][1] = 0u; }
-        }
-    };
-    // ---- everything that needs no activation is requested first: the first 256 positions' K and V
-    load_k(0);
-    load_v(0);
-    for (int i = tid; i < hd; i += MG_THREADS) qs[i] = __half2float(__float2half_rn(__ldcg(qrow + i))); // q comes from other SMs
-    __syncthreads();
 
-    // ---- pass 1: scores
-    float lmax = -INFINITY;
-    for (int j0 = 0; j0 < n_kv; j0 += KR * KP) {
-        if (j0 > 0) load_k(j0);
-#pragma unroll
-        for (int r = 0; r < KR; r++) {
-            const int j = j0 + r * KP + (tid >> 1);
-            float acc = 0.f;
-            if (j < n_kv) {
-                const float *qh = qs + half * hh;
-#pragma unroll
-                for (int i = 0; i < 8; i++)
-                    if (i < nld) {
-                        const __half2 *kh = (const __half2 *)&kq[r][i];
-                        const float4 qa = *(const float4 *)(qh + i * 8), qb = *(const float4 *)(qh + i * 8 + 4);
-                        const float2 k0 = __half22float2(kh[0]), k1 = __half22float2(kh[1]), k2 = __half22float2(kh[2]), k3 = __half22float2(kh[3]);
-                        acc += k0.x * qa.x; acc += k0.y * qa.y; acc += k1.x * qa.z; acc += k1.y * qa.w;
-                        acc += k2.x * qb.x; acc += k2.y * qb.y; acc += k3.x * qb.z; acc += k3.y * qb.w;
-                    }
-            }
-            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-            if (j < n_kv) {
-                acc *= scale;
-                if (half == 0) sc[j] = acc;
-                lmax = fmaxf(lmax, acc);
-            }
-        }
-    }
-    lmax = warp_max(lmax);
-    if (lane == 0) red[warp] = lmax;
-    __syncthreads();
-    float mx = red[0];
-#pragma unroll
-    for (int i = 1; i < MG_WARPS; i++) mx = fmaxf(mx, red[i]);
-    float lsum = 0.f;
-    for (int j = tid; j < n_kv; j += MG_THREADS) {
-        const float e = expf(sc[j] - mx);
-        sc[j] = e;
-        lsum += e;
-    }
-    lsum = warp_sum(lsum);
-    if (lane == 0) red[16 + warp] = lsum;
-    __syncthreads();
-    double tot = 0.0;
-#pragma unroll
-    for (int i = 0; i < MG_WARPS; i++) tot += (double)red[16 + i];
-    const float inv = (float)(1.0 / tot);
-    for (int j = tid; j < n_kv; j += MG_THREADS) sc[j] = __half2float(__float2half_rn(__fmul_rn(sc[j], inv)));
-    __syncthreads();
-
-    // ---- pass 2: out = sum_j p_j v_j
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int j0 = 0; j0 < n_kv; j0 += VP * MG_WARPS) {
-        if (j0 > 0) load_v(j0);
-#pragma unroll
-        for (int u = 0; u < VP; u++) {
-            const int jv = j0 + warp + MG_WARPS * u;
-            if (jv < n_kv) {
-                const float pj = sc[jv];
-#pragma unroll
-                for (int k = 0; k < 2; k++)
-                    if (k < nw) {
-                        const float2 vv = __half22float2(*(const __half2 *)&vq[u][k]);
-                        acc[2 * k] += vv.x * pj;
-                        acc[2 * k + 1] += vv.y * pj;
-                    }
-            }
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < 4; i++)
-        if (i < dpl) part[warp * hd + lane * dpl + i] = acc[i];
-    __syncthreads();
-    for (int i = tid; i < hd; i += MG_THREADS) {
-        float o = 0.f;
-#pragma unroll
-        for (int w = 0; w < MG_WARPS; w++) o += part[w * hd + i];
-        orow[i] = o;
-    }
-    __syncthreads();
-}
-
-// ---- attention of ONE head split over `parts` CTAs (contiguous position ranges), exact soft-max ------------------
-// With one head per CTA, 116 of the 148 SMs idle through the attention phase while 32 of them each pull 64 KB of K/V
-// through one SM's load path.  Here parts (= 4 for 32 heads) CTAs share a head:
-//   1. each computes the scores of its positions (4 threads per position, 64 contiguous bytes per 4-lane group and
-//      load: fully used sectors) and writes them to a per-head row in global memory;
-//   2. a mini-barrier among the head's CTAs (release-add / acquire-poll on a per-head counter that only grows);
-//   3. each reads ALL the scores of the head and does the soft-max redundantly (a few hundred elements), so the
+// Attention of ONE (head, query token), shared by `parts` CTAs (contiguous position ranges; parts = 1: one CTA), written
+// for LATENCY: at short context the phase is a chain of dependent round trips, so everything whose address is known up
+// front is requested up front, and the CTAs of a head talk through LL words -- no barrier, no atomic:
+//   0. the K rows (4 threads per position, 64 contiguous bytes per 4-lane group and load) and V rows of my first
+//      positions are requested from the cache BEFORE q is waited for (the QKV phase prefetched them into L2);
+//   1. q arrives (LL, from the QKV phase); the row of the CURRENT position is not in the cache yet as far as this SM can
+//      know, so its K and V values come as LL words too (kcur / vcur) and replace the cache row in registers;
+//   2. scores of my positions -> the head's score row (LL);
+//   3. every part reads ALL the scores of the head and does the soft-max redundantly (a few hundred elements), so the
 //      probabilities -- including their rounding to f16 -- are exactly those of the unsplit computation;
-//   4. each accumulates p.V over its own positions (V rows were requested at phase start) and writes a partial
-//      output row; the CTA that arrives last at a second per-head counter adds the partial rows in part order.
-// scratch: q[hd] | red[32] | part[8][hd] | scores[n_kv]
-__device__ __forceinline__ void mg_attention_split(const float *__restrict__ qrow, int n_kv, const int *pbase, const __half *k_pool,
-                                               const __half *v_pool, int page_shift, int kvd, int hk, int hd, float scale,
-                                               float *__restrict__ orow, float *scratch, int tid, int part, int parts,
-                                               float *g_scores, float *g_part, unsigned *cnt_s, unsigned *cnt_o, unsigned target, long long *dd) {
+//   4. p.V over my positions -> a partial output row (LL); part 0 adds the partial rows in part order and publishes
+//      the head's output (LL) for the wo phase.
+// Numerics as attention_head (attention.cuh): q and the normalised probabilities rounded to f16, fp32 accumulation.
+// scratch: q[hd] | red[32] | part[8][hd] | scores[n_kv].  hd = 64 or 128.
+__device__ __noinline__ void mg_attention_ll(const uint2 *__restrict__ q_ll, const uint2 *__restrict__ kcur_ll, const uint2 *__restrict__ vcur_ll,
+                                             uint32_t tag_in, int n_kv, const int *pbase, const __half *k_pool, const __half *v_pool,
+                                             int page_shift, int kvd, int hk, int hd, float scale, uint2 *__restrict__ out_ll, float *scratch,
+                                             int tid, int part, int parts, uint2 *g_scores, uint2 *g_part, uint32_t tag) {
     const int lane = tid & 31, warp = tid >> 5;
-    long long ts0 = 0;
-    if (dd && tid == 0) ts0 = clock64();
     float *qs = scratch, *red = qs + hd, *pw = red + 32, *sc = pw + MG_WARPS * hd;
-    __shared__ int s_last;
+    const int pos = n_kv - 1;                // the current token's position
     const int chunk = (n_kv + parts - 1) / parts;
     const int j_lo = min(n_kv, part * chunk), j_hi = min(n_kv, j_lo + chunk);
     const int qd = tid & 3;                  // pass 1: 4 threads per position; load i covers bytes [64 i + 16 qd, +16) of the row
@@ -520,19 +432,35 @@ __device__ __forceinline__ void mg_attention_split(const float *__restrict__ qro
             else { vq[u][0] = *(const uint32_t *)vr; vq[u][1] = 0u; }
         }
     };
-    if (dd && tid == 0) dd[5] = clock64() - ts0;
     load_k(j_lo);
-    if (dd && tid == 0) dd[6] = clock64() - ts0;
     load_v(j_lo);
-    if (dd && tid == 0) dd[8] = clock64() - ts0;
-    for (int i = tid; i < hd; i += MG_THREADS) qs[i] = __half2float(__float2half_rn(__ldcg(qrow + i))); // q comes from other SMs
+    for (int i = tid; i < hd; i += MG_THREADS) qs[i] = __half2float(__float2half_rn(ll_wait(q_ll + i, tag_in)));
     __syncthreads();
-    if (dd && tid == 0) dd[9] = clock64() - ts0;
 
-    // ---- 1. scores of my positions -> global
+    // ---- 1./2. scores of my positions -> the head's score row
     for (int j0 = j_lo; j0 < j_hi; j0 += KP) {
         if (j0 > j_lo) load_k(j0);
         const int j = j0 + (tid >> 2);
+        if (j == pos && j < j_hi) { // the current token: its K row comes as LL words (values already rounded to f16)
+            float kc[4][8];
+            unsigned spins = 0;
+            while (true) { // all loads of a round are in flight together; a round trip per missing word would serialise
+                bool ok = true;
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+                    if (i < nld) ok = ll_ld8(kcur_ll + hk * hd + i * 32 + qd * 8, tag_in, kc[i]) && ok;
+                if (ok) break;
+                ll_backoff(spins);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (i < nld) {
+                    __half2 h2[4];
+#pragma unroll
+                    for (int e = 0; e < 4; e++) h2[e] = __halves2half2(__float2half_rn(kc[i][2 * e]), __float2half_rn(kc[i][2 * e + 1]));
+                    kq[i] = *(const int4 *)h2;
+                }
+        }
         float acc = 0.f;
         if (j < j_hi) {
             float a0 = 0.f, a1 = 0.f;
@@ -550,21 +478,25 @@ __device__ __forceinline__ void mg_attention_split(const float *__restrict__ qro
         }
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-        if (j < j_hi && qd == 0) g_scores[j] = acc * scale;
+        if (j < j_hi && qd == 0) ll_st(g_scores + j, acc * scale, tag);
     }
-    // ---- 2. the head's CTAs meet
-    if (dd && tid == 0) dd[10] = clock64() - ts0;
-    __syncthreads();
-    if (tid == 0) mg_grid_barrier(cnt_s, target);
-    __syncthreads();
-    if (dd && tid == 0) dd[11] = clock64() - ts0;
-    // ---- 3. soft-max over ALL positions of the head (redundantly in every part)
+    // ---- 3. soft-max over ALL positions of the head (redundantly in every part); the scores of the other parts arrive as LL words
+    {
+        unsigned spins = 0;
+        while (true) { // every round requests all of this thread's words at once
+            bool ok = true;
+#pragma unroll 4
+            for (int j = tid; j < n_kv; j += MG_THREADS) {
+                const unsigned long long w = ll_ld(g_scores + j);
+                if (ll_tag(w) == tag) sc[j] = ll_val(w);
+                else ok = false;
+            }
+            if (ok) break;
+            ll_backoff(spins);
+        }
+    }
     float lmax = -INFINITY;
-    for (int j = tid; j < n_kv; j += MG_THREADS) {
-        const float v = __ldcg(g_scores + j);
-        sc[j] = v;
-        lmax = fmaxf(lmax, v);
-    }
+    for (int j = tid; j < n_kv; j += MG_THREADS) lmax = fmaxf(lmax, sc[j]);
     lmax = warp_max(lmax);
     if (lane == 0) red[warp] = lmax;
     __syncthreads();
@@ -586,7 +518,6 @@ __device__ __forceinline__ void mg_attention_split(const float *__restrict__ qro
     const float inv = (float)(1.0 / tot);
     for (int j = j_lo + tid; j < j_hi; j += MG_THREADS) sc[j] = __half2float(__float2half_rn(__fmul_rn(sc[j], inv)));
     __syncthreads();
-    if (dd && tid == 0) dd[12] = clock64() - ts0;
     // ---- 4. partial output over my positions
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     for (int j0 = j_lo; j0 < j_hi; j0 += VP * MG_WARPS) {
@@ -594,6 +525,23 @@ __device__ __forceinline__ void mg_attention_split(const float *__restrict__ qro
 #pragma unroll
         for (int u = 0; u < VP; u++) {
             const int jv = j0 + warp + MG_WARPS * u;
+            if (jv == pos && jv < j_hi) { // the current token's V row: LL words
+                const uint2 *vp = vcur_ll + hk * hd + lane * dpl;
+                unsigned long long w0, w1, w2 = 0, w3 = 0;
+                unsigned spins = 0;
+                while (true) {
+                    ll_ld2(vp, w0, w1);
+                    if (nw == 2) ll_ld2(vp + 2, w2, w3);
+                    if (ll_tag(w0) == tag_in && ll_tag(w1) == tag_in && (nw != 2 || (ll_tag(w2) == tag_in && ll_tag(w3) == tag_in))) break;
+                    ll_backoff(spins);
+                }
+                const __half2 h0 = __halves2half2(__float2half_rn(ll_val(w0)), __float2half_rn(ll_val(w1)));
+                vq[u][0] = *(const uint32_t *)&h0;
+                if (nw == 2) {
+                    const __half2 h1 = __halves2half2(__float2half_rn(ll_val(w2)), __float2half_rn(ll_val(w3)));
+                    vq[u][1] = *(const uint32_t *)&h1;
+                }
+            }
             if (jv < j_hi) {
                 const float pj = sc[jv];
 #pragma unroll
@@ -614,24 +562,30 @@ __device__ __forceinline__ void mg_attention_split(const float *__restrict__ qro
         float o = 0.f;
 #pragma unroll
         for (int w = 0; w < MG_WARPS; w++) o += pw[w * hd + i];
-        g_part[part * hd + i] = o;
-    }
-    __syncthreads();
-    if (dd && tid == 0) dd[13] = clock64() - ts0;
-    if (tid == 0) {
-        unsigned prev;
-        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(prev) : "l"(cnt_o) : "memory");
-        s_last = (prev + 1 == target);
-    }
-    __syncthreads();
-    if (s_last)
-        for (int i = tid; i < hd; i += MG_THREADS) {
-            float o = 0.f;
-            for (int pp = 0; pp < parts; pp++) o += __ldcg(g_part + pp * hd + i);
-            orow[i] = o;
+        if (part != 0) {
+            ll_st(g_part + part * hd + i, o, tag);
+        } else { // part 0 adds the partial rows in part order (fixed order: deterministic) and publishes the head's output
+            float pv[3] = {0.f, 0.f, 0.f}; // parts <= 4
+            unsigned spins = 0;
+            while (true) {
+                bool ok = true;
+#pragma unroll
+                for (int pp = 1; pp < 4; pp++)
+                    if (pp < parts) {
+                        const unsigned long long w = ll_ld(g_part + pp * hd + i);
+                        ok = ok && ll_tag(w) == tag;
+                        pv[pp - 1] = ll_val(w);
+                    }
+                if (ok) break;
+                ll_backoff(spins);
+            }
+#pragma unroll
+            for (int pp = 1; pp < 4; pp++)
+                if (pp < parts) o += pv[pp - 1];
+            ll_st(out_ll + i, o, tag);
         }
-    __syncthreads();
-    if (dd && tid == 0) dd[14] = clock64() - ts0;
+    }
+    __syncthreads(); // the scratch is reused by the next phase's prologue
 }
 
 // Pull the K/V rows (positions < n_kv) of one KV head into L2 ahead of the attention phase.
@@ -652,14 +606,16 @@ __device__ __forceinline__ void mg_prefetch_kv(int n_kv, const int *pbase, const
 // then read their register slices (stride 128 B = one bank group) from 8 different bank groups.
 __device__ __forceinline__ int mg_swz(int c) { return c ^ ((c >> 3) & 7); }
 
-// One warp quantises ONE 256-element block of an fp32 row to Q8_K and writes it, in the shared-memory layout of the
-// phase prologue (chunk-swizzled int8 | d | bsums), to a row in GLOBAL memory.  Used for activation rows so long
-// (ffn_down: 56 blocks) that re-quantising them redundantly in every CTA costs more than a second grid barrier: the
-// blocks are spread over the CTAs, then every CTA just copies the 16 KB result.  Arithmetic = mg_prologue's.
-__device__ __forceinline__ void mg_quant_block_global(const float *xrow, int b, int64_t K, int nb, int lane, uint8_t *out) {
-    const float4 *xb = (const float4 *)(xrow + b * 256 + lane * 8);
-    const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1);
-    const float v[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+// One warp quantises ONE 256-element block of a row to Q8_K and publishes it as LL words that hold the 32-bit words of
+// the shared-memory activation row image (chunk-swizzled int8 | d | bsums): word w of the image -> out[w].  Used for
+// activation rows so long (ffn_down: 56 blocks) that re-quantising them redundantly in every CTA costs more than one
+// more hop: block b is quantised by CTA b as soon as its 256 inputs have arrived, then every CTA copies the 16 KB
+// image.  Arithmetic = mg_prologue's.
+__device__ __forceinline__ void mg_quant_block_ll(const uint2 *x_ll, uint32_t tag_in, int b, int64_t K, int nb, int lane, uint2 *out,
+                                                   uint32_t tag_out) {
+    float v[8];
+    unsigned spins = 0;
+    while (!__all_sync(0xffffffffu, ll_ld8(x_ll + b * 256 + lane * 8, tag_in, v))) ll_backoff(spins);
     float m = 0.f;
 #pragma unroll
     for (int i = 0; i < 8; i++) m = fmaxf(m, fabsf(v[i]));
@@ -680,13 +636,53 @@ __device__ __forceinline__ void mg_quant_block_global(const float *xrow, int b, 
         qv[i] = vi;
         sum += vi;
     }
-    sum += __shfl_xor_sync(0xffffffffu, sum, 1);
-    int2 packed;
-    packed.x = (qv[0] & 0xFF) | ((qv[1] & 0xFF) << 8) | ((qv[2] & 0xFF) << 16) | ((qv[3] & 0xFF) << 24);
-    packed.y = (qv[4] & 0xFF) | ((qv[5] & 0xFF) << 8) | ((qv[6] & 0xFF) << 16) | ((qv[7] & 0xFF) << 24);
-    *(int2 *)(out + mg_swz(b * 16 + (lane >> 1)) * 16 + (lane & 1) * 8) = packed;
-    if ((lane & 1) == 0) ((int16_t *)(out + K + nb * 4))[b * 16 + (lane >> 1)] = (int16_t)sum;
-    if (lane == 0) ((float *)(out + K))[b] = zero ? 0.f : __fdiv_rn(1.f, iscale);
+    sum += __shfl_xor_sync(0xffffffffu, sum, 1); // 16-element sums, in both lanes of a pair
+    const uint32_t p0 = (qv[0] & 0xFF) | ((qv[1] & 0xFF) << 8) | ((qv[2] & 0xFF) << 16) | ((uint32_t)(qv[3] & 0xFF) << 24);
+    const uint32_t p1 = (qv[4] & 0xFF) | ((qv[5] & 0xFF) << 8) | ((qv[6] & 0xFF) << 16) | ((uint32_t)(qv[7] & 0xFF) << 24);
+    const int w0 = (mg_swz(b * 16 + (lane >> 1)) * 16 + (lane & 1) * 8) >> 2; // image word of this lane's 8 bytes
+    ll_st2(out + w0, __uint_as_float(p0), __uint_as_float(p1), tag_out);
+    // bsums: int16 index b*16 + lane/2; two of them per image word: lanes 4k (low half) and 4k+2 (high half)
+    const int hi = __shfl_down_sync(0xffffffffu, sum, 2);
+    if ((lane & 3) == 0) {
+        const uint32_t wv = ((uint32_t)sum & 0xFFFFu) | ((uint32_t)hi << 16);
+        ll_st(out + ((K + nb * 4) >> 2) + b * 8 + (lane >> 2), __uint_as_float(wv), tag_out);
+    }
+    if (lane == 0) ll_st(out + (K >> 2) + b, zero ? 0.f : __fdiv_rn(1.f, iscale), tag_out);
+}
+
+// Copy the image of a quantised activation row (mg_quant_block_ll: LL words, one per 32-bit word of the image) into
+// shared memory.  A light probe first -- the scale word of every block -- then 8 paired loads per thread in flight.
+__device__ __noinline__ void mg_copy_xq(const uint2 *xq_ll, uint32_t tag, int64_t K, int nb, uint8_t *xs, int tid) {
+    const int n_w = (int)((K + nb * 4 + K / 8) >> 2);
+    unsigned spins = 0;
+    while (true) {
+        bool ok = true;
+        for (int b = tid; b < nb; b += MG_THREADS) ok = ok && ll_tag(ll_ld(xq_ll + (K >> 2) + b)) == tag;
+        if (__syncthreads_and(ok)) break;
+        ll_backoff(spins);
+    }
+    for (int base = 0; base < n_w; base += 16 * MG_THREADS) {
+        unsigned long long w[8][2];
+        bool pending[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int i0 = base + 2 * (tid + k * MG_THREADS);
+            pending[k] = i0 < n_w;
+            if (pending[k]) ll_ld2(xq_ll + i0, w[k][0], w[k][1]);
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int i0 = base + 2 * (tid + k * MG_THREADS);
+            if (!pending[k]) continue;
+            while (ll_tag(w[k][0]) != tag || (i0 + 1 < n_w && ll_tag(w[k][1]) != tag)) {
+                ll_backoff(spins);
+                ll_ld2(xq_ll + i0, w[k][0], w[k][1]);
+            }
+            ((uint32_t *)xs)[i0] = (uint32_t)w[k][0];
+            if (i0 + 1 < n_w) ((uint32_t *)xs)[i0 + 1] = (uint32_t)w[k][1];
+        }
+    }
+    __syncthreads();
 }
 
 // (RMSNorm ->) quantise the activation row into shared memory, redundantly per CTA.  Written for LATENCY: warp w owns
@@ -695,10 +691,9 @@ __device__ __forceinline__ void mg_quant_block_global(const float *xrow, int b, 
 // warp-wide maxima are hardware reductions (redux.sync) instead of shuffle trees.  Results are bit-exact with
 // quantize_row_q8_K_ref / quantize_row_q8_0_ref (act_quant.cuh holds the same arithmetic for the other kernels).
 template <int PBN>
-__device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t *xs, double *s_part, int nb, int k_first, int warp,
-                                         int lane, bool write_xn) {
+__device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, float eps, uint8_t *xs, double *s_part, int nb, int k_first,
+                                         int warp, int lane, bool write_xn) {
     const int64_t K = ph.K;
-    const float *xrow = ph.x;
     const bool has_norm = ph.norm_w != nullptr;
     float v[PBN][8], w[PBN <= 2 ? PBN : 1][8];
     bool valid[PBN];
@@ -706,17 +701,48 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, float eps, uint8_t
     for (int k = 0; k < PBN; k++) {
         const int b = warp + (k_first + k) * MG_WARPS;
         valid[k] = b < nb;
-        const float4 *xb = (const float4 *)(xrow + (valid[k] ? b : 0) * 256 + lane * 8);
-        // Loads are unconditional (block index clamped): a load under a condition into a register that otherwise keeps
-        // its value becomes load + select, and the select waits for the load -- the PBN round trips would serialise.
-        const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1); // the row was written by other SMs: L2
-        v[k][0] = a0.x; v[k][1] = a0.y; v[k][2] = a0.z; v[k][3] = a0.w;
-        v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
-        if (PBN <= 2) { // norm weights ride the same round trip (without a norm: a dummy read of the row itself)
-            const float4 *wb = (const float4 *)((has_norm ? ph.norm_w : xrow) + (valid[k] ? b : 0) * 256 + lane * 8);
+        if (PBN <= 2 && has_norm) { // the norm weights are requested first: they do not depend on anybody
+            const float4 *wb = (const float4 *)(ph.norm_w + (valid[k] ? b : 0) * 256 + lane * 8);
             const float4 w0 = wb[0], w1 = wb[1];
             w[k][0] = w0.x; w[k][1] = w0.y; w[k][2] = w0.z; w[k][3] = w0.w;
             w[k][4] = w1.x; w[k][5] = w1.y; w[k][6] = w1.z; w[k][7] = w1.w;
+        }
+    }
+    if (ph.src_p < 0) { // plain fp32 row written before the launch
+#pragma unroll
+        for (int k = 0; k < PBN; k++) {
+            const int b = warp + (k_first + k) * MG_WARPS;
+            // Loads are unconditional (block index clamped): a load under a condition into a register that otherwise keeps
+            // its value becomes load + select, and the select waits for the load -- the PBN round trips would serialise.
+            const float4 *xb = (const float4 *)(ph.x + (valid[k] ? b : 0) * 256 + lane * 8);
+            const float4 a0 = __ldcg(xb), a1 = __ldcg(xb + 1);
+            v[k][0] = a0.x; v[k][1] = a0.y; v[k][2] = a0.z; v[k][3] = a0.w;
+            v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
+        }
+    } else {
+        // LL words written by phase src_p, possibly still on their way.  First a light probe -- one word per lane and
+        // block, 8 elements apart, so every producer CTA (each owns >= 8 consecutive rows) has a word in the sample --
+        // then the whole slice; the probe keeps the polling traffic of early CTAs off the L2 that streams the weights.
+        unsigned spins = 0;
+        while (g_ll_probe) {
+            bool ok = true;
+#pragma unroll
+            for (int k = 0; k < PBN; k++) {
+                const int b = warp + (k_first + k) * MG_WARPS;
+                ok = ok && ll_tag(ll_ld(ph.x_ll + (valid[k] ? b : 0) * 256 + lane * 8 + 7)) == tag_in;
+            }
+            if (__all_sync(0xffffffffu, ok)) break;
+            ll_backoff(spins);
+        }
+        while (true) {
+            bool ok = true;
+#pragma unroll
+            for (int k = 0; k < PBN; k++) {
+                const int b = warp + (k_first + k) * MG_WARPS;
+                ok = ll_ld8(ph.x_ll + (valid[k] ? b : 0) * 256 + lane * 8, tag_in, v[k]) && ok;
+            }
+            if (__all_sync(0xffffffffu, ok)) break;
+            ll_backoff(spins);
         }
     }
 #pragma unroll
@@ -853,12 +879,15 @@ decode_mega_kernel(const MegaArgs a) {
 
     MegaPhase *sph = (MegaPhase *)(smem + MG_OFF_PH);
     constexpr int PH_WORDS = (int)(sizeof(MegaPhase) / 4);
-    static_assert(PH_WORDS <= MG_THREADS - 32, "phase descriptor copy");
-    auto stage_phase = [&](int p) { // threads 32.. (thread 0 runs the grid barrier meanwhile); the caller orders it
-        const int t = tid - 32;     // against the readers with __syncthreads
-        if (p < a.n_phases && t >= 0 && t < PH_WORDS) ((uint32_t *)&sph[p & (MG_PH_WIN - 1)])[t] = ((const uint32_t *)&a.phases[p])[t];
+    static_assert(PH_WORDS <= MG_THREADS, "phase descriptor copy");
+    // Phase p's descriptor sits in slot p % 3.  It is copied in during phase p - 2, right after that phase's mid-phase
+    // __syncthreads (every thread is then past phase p - 3, the slot's previous tenant), and first read after phase
+    // p - 1's mid-phase __syncthreads.
+    auto stage_phase = [&](int p) {
+        if (p < a.n_phases && tid < PH_WORDS) ((uint32_t *)&sph[p % MG_PH_WIN])[tid] = ((const uint32_t *)&a.phases[p])[tid];
     };
-    for (int p = 0; p < MG_PH_WIN; p++) stage_phase(p);
+    stage_phase(0);
+    stage_phase(1);
     const int pos = a.pos[0], sl = a.slot[0];
     int *pbase = (int *)(smem + MG_OFF_PT); // page of every 32-position block of this sequence (static during the step)
     for (int i = tid; a.page_table && i < (pos + a.page_size) / a.page_size && i < MG_MAX_PAGES; i += MG_THREADS) pbase[i] = a.page_table[(int64_t)sl * a.max_pages + i];
@@ -884,44 +913,36 @@ decode_mega_kernel(const MegaArgs a) {
         src += st.size0 + st.size1;
     }
     uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
-    unsigned att_seq = 0;         // attention phases so far (per-head counters only grow)
-    unsigned bar_i = 0;           // grid barriers so far in this launch
 
     for (int p = 0; p < a.n_phases; p++) {
-        const MegaPhase &ph = sph[p & (MG_PH_WIN - 1)];
+        const MegaPhase &ph = sph[p % MG_PH_WIN];
+        const uint32_t tag_in = a.tag_base + (uint32_t)ph.src_p + 1u, tag_out = a.tag_base + (uint32_t)p + 1u;
         long long t0 = 0, t1 = 0, t2 = 0, t_wait = 0, t_comp = 0, t_epi = 0, n_tiles = 0, tp0 = 0, tp3 = 0, tl_end = 0;
         if (DBG && tid == 0) t0 = clock64();
         int u = 0, u_end = 0;
         if (ph.kind == PH_ATT) {
-            if (a.att_parts > 1) {
-                // a head is shared by att_parts CTAs (att_parts * n_head <= n_cta, so a CTA has at most one share)
-                att_seq++;
-                if (cta < a.n_head * a.att_parts) {
-                    const int h = cta >> a.att_parts_log, part = cta & (a.att_parts - 1);
-                    mg_attention_split(ph.x + (int64_t)h * a.hd, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift, a.kvd,
-                                       h / (a.n_head / a.n_head_kv), a.hd, a.att_scale, ph.out + (int64_t)h * a.hd, (float *)xs, tid, part,
-                                       a.att_parts, a.att_scores + (int64_t)h * a.att_scores_stride, a.att_part_out + (int64_t)h * a.att_parts * a.hd,
-                                       a.att_cnt + 2 * h, a.att_cnt + 2 * h + 1, a.att_base + att_seq * (unsigned)a.att_parts,
-                                       DBG ? a.dbg + ((int64_t)cta * a.n_phases + p) * 16 : nullptr);
-                }
-            } else {
-                for (int h = cta; h < a.n_head; h += n_cta)
-                    mg_attention(ph.x + (int64_t)h * a.hd, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift, a.kvd,
-                                 h / (a.n_head / a.n_head_kv), a.hd, a.att_scale, ph.out + (int64_t)h * a.hd, (float *)xs, tid);
+            // a head is shared by att_parts CTAs (att_parts * n_head <= n_cta whenever att_parts > 1)
+            for (int hp = cta; hp < a.n_head * a.att_parts; hp += n_cta) {
+                const int h = hp >> a.att_parts_log, part = hp & (a.att_parts - 1), hk = h / (a.n_head / a.n_head_kv);
+                mg_attention_ll(ph.x_ll + (int64_t)h * a.hd, a.kcur_ll, a.vcur_ll, tag_in, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift,
+                                a.kvd, hk, a.hd, a.att_scale, ph.out_ll + (int64_t)h * a.hd, (float *)xs, tid, part, a.att_parts,
+                                a.att_scores + (int64_t)h * a.att_scores_stride, a.att_part_out + (int64_t)h * a.att_parts * a.hd, tag_out);
             }
+            __syncthreads(); // the mid-phase sync of a phase without rows
+            stage_phase(p + 2);
         } else {
             mg_cta_range(ph, cta, n_cta, u, u_end);
+            if (u >= u_end) {
+                __syncthreads();
+                stage_phase(p + 2);
+            }
         }
-        if (ph.kind != PH_ATT && ph.xq_global) {
-            // A long activation row is quantised ONCE per GPU (block b by CTA b), not once per CTA: one more grid
-            // barrier, then the prologue below is a 16 KB copy.
+        if (ph.kind != PH_ATT && ph.xq_ll) {
+            // A long activation row is quantised ONCE per GPU (block b by warp 0 of CTA b, as soon as its inputs are
+            // there), not once per CTA; the prologue below then copies the 16 KB image.
             const int nbq = (int)(ph.K >> 8);
             if (warp == 0)
-                for (int b = cta; b < nbq; b += n_cta) mg_quant_block_global(ph.x, b, ph.K, nbq, lane, ph.xq_global);
-            __syncthreads();
-            bar_i++;
-            if (tid == 0) mg_grid_barrier(a.bar, a.bar_base + bar_i * (unsigned)n_cta);
-            __syncthreads();
+                for (int b = cta; b < nbq; b += n_cta) mg_quant_block_ll(ph.x_ll, tag_in, b, ph.K, nbq, lane, ph.xq_ll, tag_out);
         }
         if (u < u_end) {
             const int64_t K = ph.K;
@@ -929,16 +950,14 @@ decode_mega_kernel(const MegaArgs a) {
             const int S = ph.S, rpp = ph.rpp, np = ph.np;
             // ---- prologue: (RMSNorm ->) quantise the activation row into shared memory
             if (DBG && tid == 0) tp0 = clock64();
-            if (ph.xq_global) { // already quantised (above): copy
-                const int n16 = (int)((K + nb * 4 + K / 8 + 15) / 16);
-                for (int i = tid; i < n16; i += MG_THREADS) ((int4 *)xs)[i] = __ldcg((const int4 *)ph.xq_global + i);
-                __syncthreads();
+            if (ph.xq_ll) { // quantised once per GPU (above): copy the image of the activation row
+                mg_copy_xq(ph.xq_ll, tag_out, K, nb, xs, tid);
             } else {
                 const bool wx = ph.xn_out && cta == 0;
-                if (nb <= MG_WARPS) mg_prologue<1>(ph, a.eps, xs, s_part, nb, 0, warp, lane, wx);
-                else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, a.eps, xs, s_part, nb, 0, warp, lane, wx);
+                if (nb <= MG_WARPS) mg_prologue<1>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
+                else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
                 else // 4 blocks per warp at a time; rows longer than 32 blocks have no norm (mega_phase_prepare)
-                    for (int k0 = 0; k0 * MG_WARPS < nb; k0 += 4) mg_prologue<4>(ph, a.eps, xs, s_part, nb, k0, warp, lane, wx);
+                    for (int k0 = 0; k0 * MG_WARPS < nb; k0 += 4) mg_prologue<4>(ph, tag_in, a.eps, xs, s_part, nb, k0, warp, lane, wx);
             }
             if (DBG && tid == 0) tp3 = clock64();
             if (ph.kind == PH_QKV) // the attention phase comes next: start its K/V rows on their way into L2
@@ -980,6 +999,12 @@ decode_mega_kernel(const MegaArgs a) {
             }
             const int bs32[4] = {bs[0] + bs[1], bs[2] + bs[3], bs[4] + bs[5], bs[6] + bs[7]};
             const uint32_t q6d = (uint32_t)((nb >> ph.s_log) * Q6_BLK + 2 * L.kb); // Q6_K: this lane's fp16 scale inside a row-split
+            // the residual of this thread's first output row is requested now, not in the epilogue (a round trip under load)
+            float res_pre = 0.f;
+            if (ph.kind == PH_PLAIN && tid < u_end - u) {
+                if (ph.res_ll) res_pre = ll_val(ll_ld(ph.res_ll + u + tid));
+                else if (ph.residual) res_pre = __ldcg(ph.residual + u + tid);
+            }
             if (DBG && tid == 0) t1 = clock64();
 
             // ---- this warp's tiles of the phase
@@ -1097,10 +1122,12 @@ decode_mega_kernel(const MegaArgs a) {
                 }
             }
             if (DBG && tid == 0) tl_end = clock64();
-            __syncthreads();
+            __syncthreads(); // the mid-phase sync: every warp's partial sums are in shared memory
+            stage_phase(p + 2);
             if (DBG && tid == 0) t_epi = clock64();
 
-            // ---- epilogue: combine the K-split partials in a fixed order (deterministic), then the phase's tail op
+            // ---- epilogue: combine the K-split partials in a fixed order (deterministic), then the phase's tail op.  Outputs
+            // that a later phase consumes leave as LL words tagged with this phase: no fence and no barrier follow.
             const int n_r = u_end - u;
             auto dot_sum = [&](int dr) {
                 float s = 0.f;
@@ -1110,13 +1137,16 @@ decode_mega_kernel(const MegaArgs a) {
             if (ph.kind == PH_SWIGLU) {
                 for (int r = tid; r < n_r; r += MG_THREADS) {
                     const float g = dot_sum(r), up = dot_sum(n_r + r);
-                    ph.out[u + r] = __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), up);
+                    ll_st(ph.out_ll + u + r, __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), up), tag_out);
                 }
             } else if (ph.kind == PH_PLAIN) {
                 for (int r = tid; r < n_r; r += MG_THREADS) {
                     float s = dot_sum(r);
-                    if (ph.residual) s += __ldcg(ph.residual + u + r);
-                    ph.out[u + r] = s;
+                    if (r == tid) s += res_pre; // requested before the tile loop
+                    else if (ph.res_ll) s += ll_val(ll_ld(ph.res_ll + u + r));
+                    else if (ph.residual) s += __ldcg(ph.residual + u + r);
+                    if (ph.out_ll) ll_st(ph.out_ll + u + r, s, tag_out);
+                    else ph.out[u + r] = s;
                 }
             } else { // PH_QKV: job 0 = q, 1 = k, 2 = v; rows (r, r+1) form a rotary pair inside one head
                 const int64_t cell = ((((int64_t)pbase[pos >> a.page_shift]) << a.page_shift) + (pos & (a.page_size - 1))) * a.kvd;
@@ -1124,28 +1154,27 @@ decode_mega_kernel(const MegaArgs a) {
                     int jb, r;
                     mg_locate_row(ph, u + 2 * pr, jb, r);
                     const float v0 = dot_sum(2 * pr), v1 = dot_sum(2 * pr + 1);
-                    if (jb == 2) {
-                        *(__half2 *)(ph.v_pool + cell + r) = __halves2half2(__float2half_rn(v0), __float2half_rn(v1));
+                    if (jb == 2) { // V: into the cache for later tokens, and as LL words for this token's attention
+                        const __half2 hv = __halves2half2(__float2half_rn(v0), __float2half_rn(v1));
+                        *(__half2 *)(ph.v_pool + cell + r) = hv;
+                        ll_st2(a.vcur_ll + r, __low2float(hv), __high2float(hv), tag_out);
                     } else {
                         const float *cs = a.rope_table + (int64_t)pos * a.hd + (r % a.hd);
                         const float c = cs[0], sn = cs[1];
                         const float o0 = __fsub_rn(__fmul_rn(v0, c), __fmul_rn(v1, sn));
                         const float o1 = __fadd_rn(__fmul_rn(v0, sn), __fmul_rn(v1, c));
-                        if (jb == 0) *(float2 *)(ph.out + r) = make_float2(o0, o1);
-                        else *(__half2 *)(ph.k_pool + cell + r) = __halves2half2(__float2half_rn(o0), __float2half_rn(o1));
+                        if (jb == 0) {
+                            ll_st2(ph.out_ll + r, o0, o1, tag_out);
+                        } else {
+                            const __half2 hk2 = __halves2half2(__float2half_rn(o0), __float2half_rn(o1));
+                            *(__half2 *)(ph.k_pool + cell + r) = hk2;
+                            ll_st2(a.kcur_ll + r, __low2float(hk2), __high2float(hk2), tag_out);
+                        }
                     }
                 }
             }
         }
-        // ---- phase boundary
         if (DBG && tid == 0) t2 = clock64();
-        if (p + 1 < a.n_phases) {
-            __syncthreads();
-            stage_phase(p + MG_PH_WIN); // phase p's slot is free: everyone is past its epilogue (warps 1.. do the copy)
-            bar_i++;
-            if (tid == 0) mg_grid_barrier(a.bar, a.bar_base + bar_i * (unsigned)n_cta);
-            __syncthreads();
-        }
         if (DBG && tid == 0) {
             long long *dd = a.dbg + ((int64_t)cta * a.n_phases + p) * 16;
             dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64();
@@ -1163,6 +1192,11 @@ void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s) {
         B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
         B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
     });
+    static PerDeviceOnce knobs;
+    knobs.run([&] {
+        if (getenv("B200LLM_LL_POLL_NS")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_LL_POLL_NS")); B2_CUDA(cudaMemcpyToSymbol(g_ll_poll_ns, &v, sizeof(v))); }
+        if (getenv("B200LLM_LL_PROBE")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_LL_PROBE")); B2_CUDA(cudaMemcpyToSymbol(g_ll_probe, &v, sizeof(v))); }
+    });
     void *args[] = {(void *)&a};
     const void *fn = a.dbg ? (const void *)decode_mega_kernel<true> : (const void *)decode_mega_kernel<false>;
     B2_CUDA(cudaLaunchCooperativeKernel(fn, dim3(n_sm), dim3(MG_THREADS), args, MG_SMEM, s));
@@ -1175,7 +1209,7 @@ bool mega_phase_prepare(MegaPhase &ph, int n_cta) {
     ph.units_q = ph.units / n_cta;
     ph.units_r = ph.units % n_cta;
     int S, lpr, rpp, np;
-    if (!mg_split(ph.fmt, ph.K, ph.xq_global != nullptr, S, lpr, rpp, np)) return false;
+    if (!mg_split(ph.fmt, ph.K, ph.xq_ll != nullptr, S, lpr, rpp, np)) return false;
     if (mg_act_row_bytes_host(ph.fmt, ph.K) > MG_XS_BYTES) return false;
     if (ph.norm_w && ph.K / 256 > 4 * MG_WARPS) return false; // the prologue norms at most 4 blocks per warp in one go
     ph.S = S; ph.lpr = lpr; ph.rpp = rpp; ph.np = np;

@@ -209,6 +209,7 @@ Model::~Model() {
     for (auto g : decode_graphs_)
         if (g) cudaGraphExecDestroy(g);
     for (void *p : allocs_) cudaFree(p);
+    for (auto e : mega_ev_) cudaEventDestroy(e);
     mega_streams_.free();
     if (logits_) cudaFree(logits_);
     for (auto &kv : w_tiles_) cudaFree(kv.second);
@@ -510,8 +511,37 @@ void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
 void Model::build_mega() {
     mega_ready_ = false;
     if (no_mega_ || unfused_) return;
-    const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim;
+    const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hp.head_dim;
+    cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
+    if (!x_ll_) {
+        // attention of one head is shared by up to 4 CTAs (B200LLM_ATT_PARTS overrides; 1 = one CTA per head)
+        mega_att_parts_ = 1;
+        while (mega_att_parts_ < 4 && hp.n_head * mega_att_parts_ * 2 <= n_sm_) mega_att_parts_ *= 2;
+        if (getenv("B200LLM_ATT_PARTS")) mega_att_parts_ = std::min(4, std::max(1, atoi(getenv("B200LLM_ATT_PARTS"))));
+        while (mega_att_parts_ > 1 && (hp.n_head * mega_att_parts_ > n_sm_ || (mega_att_parts_ & (mega_att_parts_ - 1)))) mega_att_parts_--;
+        // The tags only ever grow and are compared for equality modulo 2^32; B200LLM_MEGA_COUNTER0 starts them at an
+        // arbitrary value so that a test can drive them across the wrap-around.  Every word starts with the tag the
+        // first launch can not expect (its base).
+        const unsigned c0 = getenv("B200LLM_MEGA_COUNTER0") ? (unsigned)strtoul(getenv("B200LLM_MEGA_COUNTER0"), nullptr, 0) : 0u;
+        mega_tag_base_ = c0;
+        const size_t kmax = (size_t)std::max(d, ff);
+        const size_t n_xq = kmax / 4 + kmax / 256 + kmax / 32 + 8; // words of the quantised activation row image (+ slack for the paired loads)
+        const size_t sizes[9] = {(size_t)d, (size_t)d, (size_t)d, (size_t)ff, (size_t)kvd, (size_t)kvd, n_xq,
+                                 (size_t)hp.n_head * n_ctx_slot, (size_t)hp.n_head * mega_att_parts_ * hd};
+        uint2 **bufs[9] = {&x_ll_, &q_ll_, &att_ll_, &gate_ll_, &kcur_ll_, &vcur_ll_, &xq_ll_, &mega_att_scores_, &mega_att_part_};
+        size_t most = 0;
+        for (size_t n : sizes) most = std::max(most, n);
+        std::vector<uint2> init(most, make_uint2(0u, c0));
+        for (int i = 0; i < 9; i++) {
+            *bufs[i] = (uint2 *)dalloc(sizes[i] * sizeof(uint2));
+            B2_CUDA(cudaMemcpyAsync(*bufs[i], init.data(), sizes[i] * sizeof(uint2), cudaMemcpyHostToDevice, stream));
+        }
+        B2_CUDA(cudaStreamSynchronize(stream));
+    }
+    // ffn_down's input (n_ff >= 8192) is quantised once per GPU, not once per CTA (B200LLM_NO_DIST_QUANT=1: per CTA)
+    const bool dist_quant = !(getenv("B200LLM_NO_DIST_QUANT") && atoi(getenv("B200LLM_NO_DIST_QUANT")));
     std::vector<MegaPhase> ph;
+    int prev = -1; // the phase that produced x_ll_ (-1: the embedding row, plain fp32 in x_)
     for (int l = 0; l < hp.n_layer; l++) {
         const LayerW &L = layers[l];
         __half *kp = k_pool_ + (size_t)l * pool_layer_stride_, *vp = v_pool_ + (size_t)l * pool_layer_stride_;
@@ -521,43 +551,42 @@ void Model::build_mega() {
         MegaPhase q;
         q.kind = PH_QKV; q.K = d; q.fmt = act_format_for(L.wq.type); q.n_jobs = 3;
         q.job[0] = job_of(L.wq); q.job[1] = job_of(L.wk); q.job[2] = job_of(L.wv);
-        q.x = x_; q.norm_w = (const float *)L.attn_norm.data; q.out = q_; q.k_pool = kp; q.v_pool = vp;
+        q.x = x_; q.x_ll = x_ll_; q.src_p = prev;
+        q.norm_w = (const float *)L.attn_norm.data; q.out_ll = q_ll_; q.k_pool = kp; q.v_pool = vp;
         q.units = (int)((L.wq.rows + L.wk.rows + L.wv.rows) / 2);
+        const int iq = (int)ph.size();
         ph.push_back(q);
         MegaPhase at;
-        at.kind = PH_ATT; at.x = q_; at.out = att_; at.k_pool = kp; at.v_pool = vp;
+        at.kind = PH_ATT; at.x_ll = q_ll_; at.src_p = iq; at.out_ll = att_ll_; at.k_pool = kp; at.v_pool = vp;
+        const int iat = (int)ph.size();
         ph.push_back(at);
         MegaPhase o;
         o.kind = PH_PLAIN; o.K = d; o.fmt = act_format_for(L.wo.type); o.n_jobs = 1; o.job[0] = job_of(L.wo);
-        o.x = att_; o.out = x_; o.residual = x_; o.units = (int)(L.wo.rows / 2);
+        o.x_ll = att_ll_; o.src_p = iat; o.out_ll = x_ll_; o.units = (int)(L.wo.rows / 2);
+        if (prev < 0) o.residual = x_; else o.res_ll = x_ll_;
+        const int io = (int)ph.size();
         ph.push_back(o);
         MegaPhase g;
         g.kind = PH_SWIGLU; g.K = d; g.fmt = act_format_for(L.gate.type); g.n_jobs = 2; g.job[0] = job_of(L.gate); g.job[1] = job_of(L.up);
-        g.x = x_; g.norm_w = (const float *)L.ffn_norm.data; g.out = gate_; g.units = (int)L.gate.rows;
+        g.x_ll = x_ll_; g.src_p = io; g.norm_w = (const float *)L.ffn_norm.data; g.out_ll = gate_ll_; g.units = (int)L.gate.rows;
+        const int ig = (int)ph.size();
         ph.push_back(g);
         MegaPhase w;
         w.kind = PH_PLAIN; w.K = ff; w.fmt = act_format_for(L.down.type); w.n_jobs = 1; w.job[0] = job_of(L.down);
-        w.x = gate_; w.out = x_; w.residual = x_; w.units = (int)(L.down.rows / 2);
+        w.x_ll = gate_ll_; w.src_p = ig; w.res_ll = x_ll_; w.out_ll = x_ll_; w.units = (int)(L.down.rows / 2);
+        if (dist_quant && w.fmt == ACT_Q8_K && w.K / 256 > 32 && w.K <= 32768) w.xq_ll = xq_ll_;
+        prev = (int)ph.size();
         ph.push_back(w);
     }
     MegaPhase h;
     h.kind = PH_PLAIN; h.K = d; h.fmt = act_format_for(output.type); h.n_jobs = 1; h.job[0] = job_of(output);
-    h.x = x_; h.norm_w = (const float *)output_norm.data; h.out = logits_; h.xn_out = xn_out_; h.units = (int)(output.rows / 2);
+    h.x = x_; h.x_ll = x_ll_; h.src_p = prev;
+    h.norm_w = (const float *)output_norm.data; h.out = logits_; h.xn_out = xn_out_; h.units = (int)(output.rows / 2);
     ph.push_back(h);
-    cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
-    // ffn_down's input (n_ff >= 8192) is quantised once per GPU, not once per CTA (B200LLM_NO_DIST_QUANT=1: per CTA)
-    const bool dist_quant = !(getenv("B200LLM_NO_DIST_QUANT") && atoi(getenv("B200LLM_NO_DIST_QUANT")));
-    if (!mega_xq_) mega_xq_ = (uint8_t *)dalloc(64 * 1024);
-    mega_n_bar_ = (int)ph.size() - 1;
-    for (auto &p : ph) {
-        if (dist_quant && p.kind == PH_PLAIN && !p.norm_w && p.fmt == ACT_Q8_K && p.K / 256 > 32 && p.K <= 32768) {
-            p.xq_global = mega_xq_;
-            mega_n_bar_++;
-        }
+    for (auto &p : ph)
         if (!mega_phase_prepare(p, n_sm_)) return;
-    }
     if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1)) ||
-        (uint64_t)pool_layer_stride_ >= (1ull << 31))
+        (uint64_t)pool_layer_stride_ >= (1ull << 31) || kvd % 2 != 0)
         return;
     if (!mega_streams_.data) {
         // The decode kernel reads its own copy of the weights (MegaStreams): same bytes, laid out per (CTA, warp) in
@@ -572,35 +601,8 @@ void Model::build_mega() {
     B2_CUDA(cudaMemcpyAsync(mega_phases_, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaStreamSynchronize(stream));
     mega_n_phases_ = (int)ph.size();
-    if (!mega_bar_) {
-        // attention of one head is shared by up to 4 CTAs (B200LLM_ATT_PARTS overrides; 1 = one CTA per head)
-        mega_att_parts_ = 1;
-        while (mega_att_parts_ < 4 && hp.n_head * mega_att_parts_ * 2 <= n_sm_) mega_att_parts_ *= 2;
-        if (getenv("B200LLM_ATT_PARTS")) mega_att_parts_ = std::max(1, atoi(getenv("B200LLM_ATT_PARTS")));
-        while (mega_att_parts_ > 1 && (hp.n_head * mega_att_parts_ > n_sm_ || (mega_att_parts_ & (mega_att_parts_ - 1)))) mega_att_parts_--;
-        mega_att_scores_ = (float *)dalloc((size_t)hp.n_head * n_ctx_slot * sizeof(float));
-        mega_att_part_ = (float *)dalloc((size_t)hp.n_head * mega_att_parts_ * hp.head_dim * sizeof(float));
-        mega_att_cnt_ = (unsigned *)dalloc((size_t)hp.n_head * 2 * sizeof(unsigned));
-        // The barrier counters only ever grow and are compared modulo 2^32; B200LLM_MEGA_COUNTER0 starts them at an
-        // arbitrary value so that a test can drive them across the wrap-around.
-        const unsigned c0 = getenv("B200LLM_MEGA_COUNTER0") ? (unsigned)strtoul(getenv("B200LLM_MEGA_COUNTER0"), nullptr, 0) : 0u;
-        {
-            std::vector<unsigned> init((size_t)hp.n_head * 2, c0);
-            B2_CUDA(cudaMemcpyAsync(mega_att_cnt_, init.data(), init.size() * sizeof(unsigned), cudaMemcpyHostToDevice, stream));
-            B2_CUDA(cudaStreamSynchronize(stream));
-        }
-        mega_att_base_ = c0; // (advances by n_layer * parts per launch, the grid counter by CTAs * barriers)
-        mega_bar_ = (unsigned *)dalloc(4096);
-        {
-            std::vector<unsigned> init(1024, c0);
-            B2_CUDA(cudaMemcpyAsync(mega_bar_, init.data(), 4096, cudaMemcpyHostToDevice, stream));
-            B2_CUDA(cudaStreamSynchronize(stream));
-        }
-        mega_epoch_ = c0;
-    }
     int coop = 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
-    cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device);
     mega_ready_ = coop != 0;
     if (getenv("B200LLM_MEGA_DBG") && !mega_dbg_) mega_dbg_ = (long long *)dalloc((size_t)n_sm_ * mega_n_phases_ * 16 * sizeof(long long));
 }
@@ -621,14 +623,39 @@ void Model::run_decode_mega() {
     a.att_parts_log = 0;
     while ((1 << a.att_parts_log) < a.att_parts) a.att_parts_log++;
     a.att_scores = mega_att_scores_; a.att_scores_stride = n_ctx_slot;
-    a.att_part_out = mega_att_part_; a.att_cnt = mega_att_cnt_;
-    a.att_base = mega_att_base_;
-    mega_att_base_ += (unsigned)hp.n_layer * (unsigned)mega_att_parts_;
-    a.bar = mega_bar_;
-    a.bar_base = mega_epoch_;
-    mega_epoch_ += (unsigned)n_sm_ * (unsigned)mega_n_bar_;
+    a.att_part_out = mega_att_part_;
+    a.kcur_ll = kcur_ll_; a.vcur_ll = vcur_ll_;
+    a.tag_base = mega_tag_base_;
+    mega_tag_base_ += (unsigned)mega_n_phases_;
     a.dbg = mega_dbg_;
+    const bool timed = mega_timing_ && mega_ev_n_ + 2 <= mega_ev_.size();
+    if (timed) B2_CUDA(cudaEventRecord(mega_ev_[mega_ev_n_++], stream));
     launch_decode_mega(a, n_sm_, stream);
+    if (timed) B2_CUDA(cudaEventRecord(mega_ev_[mega_ev_n_++], stream));
+}
+
+void Model::mega_timing_begin(int max_launches) {
+    while ((int)mega_ev_.size() < 2 * max_launches) {
+        cudaEvent_t e;
+        B2_CUDA(cudaEventCreate(&e));
+        mega_ev_.push_back(e);
+    }
+    mega_ev_n_ = 0;
+    mega_timing_ = true;
+}
+
+double Model::mega_timing_end() {
+    mega_timing_ = false;
+    B2_CUDA(cudaStreamSynchronize(stream));
+    double tot = 0;
+    for (size_t i = 0; i + 1 < mega_ev_n_; i += 2) {
+        float ms = 0;
+        B2_CUDA(cudaEventElapsedTime(&ms, mega_ev_[i], mega_ev_[i + 1]));
+        tot += ms;
+    }
+    const double mean = mega_ev_n_ ? tot / (double)(mega_ev_n_ / 2) : 0.0;
+    mega_ev_n_ = 0;
+    return mean;
 }
 
 // Decode step for `n` sequences whose inputs are in the device buffers, replayed from a captured CUDA graph

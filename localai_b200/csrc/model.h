@@ -106,16 +106,21 @@ class Model {
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;
     MegaStreams mega_streams_; // the decode kernel's copy of the weights: one contiguous stream per (CTA, warp)
-    unsigned mega_epoch_ = 0, mega_att_base_ = 0;
-    int mega_n_bar_ = 0;
-    uint8_t *mega_xq_ = nullptr;
+    unsigned mega_tag_base_ = 0;   // LL tag base of the next launch (advances by the number of phases)
+    // LL-word buffers ({fp32, tag} pairs) through which the phases of the decode kernel hand activations to each other
+    uint2 *x_ll_ = nullptr, *q_ll_ = nullptr, *att_ll_ = nullptr, *gate_ll_ = nullptr, *kcur_ll_ = nullptr, *vcur_ll_ = nullptr,
+          *xq_ll_ = nullptr, *mega_att_scores_ = nullptr, *mega_att_part_ = nullptr;
     int mega_att_parts_ = 1;
-    float *mega_att_scores_ = nullptr, *mega_att_part_ = nullptr;
-    unsigned *mega_att_cnt_ = nullptr;
-    unsigned *mega_bar_ = nullptr;
     long long *mega_dbg_ = nullptr;
+    std::vector<cudaEvent_t> mega_ev_;
+    size_t mega_ev_n_ = 0;
+    bool mega_timing_ = false;
   public:
     long long *mega_dbg() { return mega_dbg_; }
+    // bench hook: CUDA events around every decode_mega_kernel launch (the roofline figure is per launch of that kernel)
+    void mega_timing_begin(int max_launches);
+    double mega_timing_end(); // mean ms per launch since mega_timing_begin (0: the kernel did not run)
+    bool mega_ready() const { return mega_ready_; }
     int mega_n_phases() const { return mega_n_phases_; }
     int n_sm() const { return n_sm_; }
   private:

@@ -120,3 +120,77 @@ def test_q4_k_m_type_mix_reproduces_known_file_sizes():
         plan = mg.tensor_plan(mg.ARCHS[arch], preset, 4.0)
         total = sum(mg.tensor_nbytes(r, c, t) for _, r, c, t, _, _ in plan)
         assert abs(total / 1e9 - gb) < 0.01 * gb + 0.01
+
+
+# ---- the decode kernel's weight-stream planner (host arithmetic, csrc/kernels_mega.cu: mega_plan_streams) ----
+Q4_K, Q5_K, Q6_K, Q8_0 = 12, 13, 14, 8
+
+
+def _llama_phases(n_layer, d, ff, kvd, vocab, t_main, t_v, t_down, t_out):
+    """9 int64 per phase {kind, K, n_jobs, type0, rows0, type1, rows1, type2, rows2}: QKV, attention, wo, gate|up, down per
+    layer, then the LM head -- the list Model::build_mega makes."""
+    ph = []
+    for l in range(n_layer):
+        ph += [[0, d, 3, t_main, d, t_main, kvd, t_v[l % len(t_v)], kvd], [1, 0, 0, 0, 0, 0, 0, 0, 0], [2, d, 1, t_main, d, 0, 0, 0, 0],
+               [3, d, 2, t_main, ff, t_main, ff, 0, 0], [2, ff, 1, t_down[l % len(t_down)], d, 0, 0, 0, 0]]
+    ph.append([2, d, 1, t_out, vocab, 0, 0, 0, 0])
+    return np.array(ph, dtype=np.int64)
+
+
+@pytest.mark.parametrize("name,args,expect_bytes", [
+    ("llama3-8b q4_k_m", (32, 4096, 14336, 1024, 128256, Q4_K, [Q6_K, Q4_K], [Q6_K, Q4_K], Q6_K), 4.6e9),
+    ("tinyllama q8_0", (22, 2048, 5632, 256, 32000, Q8_0, [Q8_0], [Q8_0], Q8_0), 1.1e9),
+    ("llama3-70b q4_k_m, 4 layers", (4, 8192, 28672, 1024, 128256, Q4_K, [Q6_K, Q5_K], [Q6_K, Q4_K], Q6_K), 2.9e9),
+    ("mini", (3, 512, 1024, 128, 4608, Q4_K, [Q6_K], [Q6_K], Q6_K), None),
+])
+@pytest.mark.parametrize("n_cta", [148, 132, 16])
+def test_mega_stream_plan_is_consistent(name, args, expect_bytes, n_cta):
+    """Every (row, K-split) of every phase appears in exactly one tile of exactly one warp's stream, the tiles of a stream
+    chain through their headers (size of the tile two ahead, last-of-phase flag, next phase) the way the kernel walks
+    them, and the streams hold the weights' bytes plus 16 per tile.  The check itself is mega_plan_verify in the library."""
+    L = capi.lib()
+    L.b2_mega_plan_check.restype = ctypes.c_int64
+    L.b2_mega_plan_check.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    d = _llama_phases(*args)
+    n_tiles = ctypes.c_int64(0)
+    r = L.b2_mega_plan_check(d.ctypes.data, len(d), n_cta, ctypes.byref(n_tiles))
+    if r == capi.B2_EUNSUPPORTED:  # e.g. more rows x K-splits per CTA than the partial-sum buffer holds at a small grid
+        pytest.skip((L.b2_last_error() or b"").decode())
+    assert r > 0, (L.b2_last_error() or b"").decode()
+    assert n_tiles.value > 0
+    if expect_bytes and n_cta == 148:
+        assert abs(r - expect_bytes) < 0.02 * expect_bytes
+
+
+def test_corrupt_gguf_headers_are_rejected(tmp_path, model_files):
+    """Header fields are not trusted: a zero / non-power-of-two alignment, tensor offsets that wrap, element counts that
+    overflow and counts beyond the file are parse errors, not divisions by zero, wild reads or huge allocations."""
+    import struct
+    good = open(model_files["mini_q4_k_m"], "rb").read()
+    key = b"general.alignment"
+    k = good.index(key) + len(key)
+    assert struct.unpack("<I", good[k:k + 4])[0] == 4  # GGUF type u32
+    for bad_align in (0, 24):
+        p = tmp_path / f"align{bad_align}.gguf"
+        p.write_bytes(good[:k + 4] + struct.pack("<I", bad_align) + good[k + 8:])
+        with pytest.raises(capi.B2Error, match="alignment"):
+            capi.Engine(str(p), vocab_only=True)
+    # the tensor count: far more tensors than the file has bytes
+    p = tmp_path / "count.gguf"
+    p.write_bytes(good[:8] + struct.pack("<Q", 1 << 60) + good[16:])
+    with pytest.raises(capi.B2Error, match="tensor count|truncated"):
+        capi.Engine(str(p), vocab_only=True)
+    # the offset of the first tensor info pushed to 2^64 - 64: offset + size wraps around
+    name = b"token_embd.weight"
+    t = good.index(name) + len(name)
+    nd = struct.unpack("<I", good[t:t + 4])[0]
+    off_at = t + 4 + 8 * nd + 4
+    p = tmp_path / "offset.gguf"
+    p.write_bytes(good[:off_at] + struct.pack("<Q", (1 << 64) - 64) + good[off_at + 8:])
+    with pytest.raises(capi.B2Error, match="exceeds file size"):
+        capi.Engine(str(p), vocab_only=True)
+    # a dimension so large that the element count overflows
+    p = tmp_path / "dims.gguf"
+    p.write_bytes(good[:t + 4] + struct.pack("<Q", 1 << 62) + good[t + 12:])
+    with pytest.raises(capi.B2Error, match="invalid shape|block multiple|exceeds"):
+        capi.Engine(str(p), vocab_only=True)

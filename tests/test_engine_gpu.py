@@ -381,3 +381,29 @@ def test_grammar_that_does_not_parse_fails_submit(eng):
         eng.submit(prompt=PROMPT, grammar='root ::= missing\n')
     evs = run(eng, prompt=PROMPT, n_predict=4, temperature=0.0, ignore_eos=True)  # the engine is still fine
     assert evs[-1]["n_decoded"] == 4
+
+
+def test_replica_pool_over_real_devices(model_files):
+    """SURVEY 8e row 1 on hardware: ONE process, one engine per GPU, least-loaded dispatch -- the streams of every replica
+    produce the text a single engine produces, and the requests spread over the replicas.  (One host thread drives
+    engines on several devices here, so this also covers the per-device kernel attributes.)"""
+    from localai_b200.replicas import ReplicaPool
+
+    n_dev = capi.device_count()
+    if n_dev < 2:
+        pytest.skip("needs at least 2 sm_100 devices")
+    path = model_files["mini_q4_k_m"]
+    rng = np.random.default_rng(8)
+    prompts = [rng.integers(0, 4000, 12).astype(np.int32) for _ in range(8 * n_dev)]
+    with capi.Engine(path, n_ctx=8 * 128, n_parallel=8, n_batch=64) as e:
+        want = [text_of(run(e, prompt_ids=p, n_predict=16, temperature=0.0, ignore_eos=True, stream=False)) for p in prompts]
+    pool = ReplicaPool(path, n_ctx=8 * 128, n_parallel=8, n_batch=64)
+    try:
+        assert len(pool.engines) == n_dev
+        hs = [pool.submit(prompt_ids=p, n_predict=16, temperature=0.0, ignore_eos=True, stream=False) for p in prompts]
+        got = [b"".join(ev["text"] for ev in pool.events(h)) for h in hs]
+        assert got == want
+        assert min(pool.assigned) >= 4 and sum(pool.assigned) == len(prompts)
+        assert pool.load() == [0] * n_dev
+    finally:
+        pool.close()

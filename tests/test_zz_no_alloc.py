@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 from localai_b200 import capi
+from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
 MATMUL_RTOL = 2e-5  # same tolerance as tests/test_parity_gpu.py
@@ -24,21 +25,30 @@ def _case(torch, wtype, rows, cols, n_tok, seed):
         raw = mg.random_blocks(rng, wtype, rows * cols // 256, 1 / np.sqrt(cols)).reshape(-1)
     x = rng.standard_normal((n_tok, cols)).astype(np.float32)
     want = capi.mul_mat(wtype, raw, rows, cols, x, path=1)  # the existing, allocating entry point
+    ref = O.mul_mat(wtype, raw, rows, cols, x)               # and the CPU oracle
     w_d = torch.from_numpy(raw.copy()).cuda()
     x_d = torch.from_numpy(x).cuda()
     out_d = torch.full((n_tok, rows), float("nan"), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info()[0]
     capi.mul_mat_noalloc(wtype, w_d.data_ptr(), rows, cols, x_d.data_ptr(), n_tok, out_d.data_ptr(), 0)
     torch.cuda.synchronize()
+    # nothing was allocated: the device's free memory is what it was (the first call of the process did its one-time
+    # symbol look-up before this function was entered, see the warm-up in the test)
+    assert torch.cuda.mem_get_info()[0] == free_before
     got = out_d.cpu().numpy()
     assert np.isfinite(got).all()
     assert np.abs(got - want).max() <= MATMUL_RTOL * np.abs(want).max()
+    assert np.abs(got - ref).max() <= MATMUL_RTOL * np.abs(ref).max()
     return got
 
 
 def test_no_alloc_matches_allocating_entry_point_twice_in_a_row():
     torch = pytest.importorskip("torch")
     assert torch.cuda.is_available()
+    warm = torch.zeros(1 << 16, dtype=torch.uint8, device="cuda")  # first call on the device: looks the scratch symbol up
+    capi.mul_mat_noalloc(capi.B2_T_Q4_K, warm.data_ptr(), 2, 256, warm.data_ptr(), 1, warm.data_ptr() + 4096, 0)
+    torch.cuda.synchronize()
     # two calls back to back share the same scratch array: the second (smaller, other type) must not see stale data
     _case(torch, capi.B2_T_Q4_K, 512, 4096, 4, seed=1)
     _case(torch, capi.B2_T_Q5_K, 300, 1024, 1, seed=2)

@@ -71,6 +71,8 @@ ARCHS = {
     # unit-test sized models: every quant type has K % 256 == 0
     "micro": Arch("micro", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm"),
     "mini": Arch("mini", 3, 512, 8, 2, 1024, 4608, 1024, 500000.0, 1e-5, "bpe"),
+    "small": Arch("small", 8, 1024, 16, 4, 2816, 8192, 1024, 500000.0, 1e-5, "bpe"),          # deeper: error growth over 8 layers
+    "mini-70b": Arch("mini-70b", 4, 1024, 16, 8, 3584, 8192, 1024, 500000.0, 1e-5, "bpe", True),  # 70B type mix (Q5_K attn_v), 8 KV heads
     # BASELINE.json configs
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 5632, 32000, 2048, 10000.0, 1e-5, "spm"),
     "llama3-8b": Arch("llama3-8b", 32, 4096, 32, 8, 14336, 128256, 8192, 500000.0, 1e-5, "bpe"),
@@ -442,9 +444,33 @@ def tensor_nbytes(rows, cols, t):
     return rows * (cols // bs) * bb
 
 
+def _write_tensor(job):
+    """Generate one tensor (its own RNG stream) and write it at its offset in the file."""
+    path, off, idx, name, rows, cols, t, sigma, is_norm, seed, structured = job
+    rng = np.random.default_rng([seed, idx])
+    n = 0
+    with open(path, "r+b") as f:
+        f.seek(off)
+        if is_norm:
+            w = (1.0 + 0.1 * rng.standard_normal(cols)).astype(np.float32)
+            f.write(w.tobytes())
+            n = w.nbytes
+        elif structured and name in ("token_embd.weight", "output.weight"):
+            kind = "embd" if name == "token_embd.weight" else "out"
+            for chunk in structured_tensor_bytes(kind, seed, t, rows, cols, sigma):
+                f.write(chunk)
+                n += len(chunk)
+        else:
+            for chunk in random_tensor_bytes(rng, t, rows, cols, sigma):
+                f.write(chunk)
+                n += len(chunk)
+    assert n == tensor_nbytes(rows, cols, t), (name, n)
+    return n
+
+
 def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: float = 4.0,
                vocab_dir: str | None = None, n_ctx_train: int | None = None, quiet: bool = False,
-               structured: bool = True) -> dict:
+               structured: bool = True, workers: int = 0) -> dict:
     vocab_dir = vocab_dir or os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
     vocab = load_vocab(arch.tokenizer, arch.n_vocab, vocab_dir)
     plan = tensor_plan(arch, preset, gain_out)
@@ -496,32 +522,31 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     header = struct.pack("<IIQQ", GGUF_MAGIC, GGUF_VERSION, len(plan), len(kvs))
     meta = header + b"".join(kvs) + b"".join(infos)
     pad = (-len(meta)) % ALIGN
-    total = 0
+    # Every tensor has its own generator (seed, index) and a known offset, so tensors are written independently: big files
+    # (the 8B / 70B configurations) are filled by a pool of worker processes, byte-identical to the serial order.
+    data_off = len(meta) + pad
+    jobs, off = [], data_off
     type_bytes: dict[str, int] = {}
+    for idx, (name, rows, cols, t, sigma, is_norm) in enumerate(plan):
+        nb = tensor_nbytes(rows, cols, t)
+        jobs.append((path, off, idx, name, rows, cols, t, sigma, is_norm, seed, structured))
+        off += (nb + ALIGN - 1) // ALIGN * ALIGN
+        type_bytes[TYPE_NAMES[t]] = type_bytes.get(TYPE_NAMES[t], 0) + nb
+    total = off
     with open(path, "wb") as f:
         f.write(meta + b"\0" * pad)
-        total += len(meta) + pad
-        for idx, (name, rows, cols, t, sigma, is_norm) in enumerate(plan):
-            rng = np.random.default_rng([seed, idx])
-            n = 0
-            if is_norm:
-                w = (1.0 + 0.1 * rng.standard_normal(cols)).astype(np.float32)
-                f.write(w.tobytes())
-                n = w.nbytes
-            elif structured and name in ("token_embd.weight", "output.weight"):
-                kind = "embd" if name == "token_embd.weight" else "out"
-                for chunk in structured_tensor_bytes(kind, seed, t, rows, cols, sigma):
-                    f.write(chunk)
-                    n += len(chunk)
-            else:
-                for chunk in random_tensor_bytes(rng, t, rows, cols, sigma):
-                    f.write(chunk)
-                    n += len(chunk)
-            assert n == tensor_nbytes(rows, cols, t), (name, n)
-            p = (-n) % ALIGN
-            f.write(b"\0" * p)
-            total += n + p
-            type_bytes[TYPE_NAMES[t]] = type_bytes.get(TYPE_NAMES[t], 0) + n
+        f.truncate(total)  # the alignment gaps between tensors read as zeros
+    n_workers = workers if workers > 0 else (min(os.cpu_count() or 1, 32) if total > (1 << 30) else 1)
+    if n_workers > 1:
+        import multiprocessing as mp
+
+        jobs.sort(key=lambda j: -tensor_nbytes(j[4], j[5], j[6]))  # largest first: better balance
+        with mp.get_context("fork").Pool(n_workers) as pool:
+            for _ in pool.imap_unordered(_write_tensor, jobs, chunksize=1):
+                pass
+    else:
+        for j in jobs:
+            _write_tensor(j)
     # bytes streamed per decoded token = every weight except the embedding table
     # (one row gathered) -- SURVEY.md §8(d)
     stream = sum(tensor_nbytes(r, c, t) for (nm, r, c, t, _, _) in plan if nm != "token_embd.weight")
