@@ -69,7 +69,10 @@ typedef struct {
     float rope_freq_scale;  /* 0 = 1.0 */
     int32_t kv_page_size;   /* KV page length in tokens; 0 = 32 */
     int32_t vocab_only;     /* ModelOptions.VocabOnly: load metadata + tokenizer only; needs no GPU; compute calls fail */
-    int32_t reserved[7];
+    int32_t tp_size;        /* tensor-parallel degree (ModelOptions.TensorSplit names that many GPUs; backend.proto:175-176,
+                               grpc-server.cpp:2240-2262): 0 / 1 = one GPU; 2, 4, 8 = the model is sharded over the devices
+                               device .. device + tp_size - 1 of this process (70B-class models) */
+    int32_t reserved[6];
 } b2_load_opts;
 
 b2_engine *b2_create(const b2_load_opts *opts);
@@ -97,6 +100,26 @@ int b2_model_info(b2_engine *e, b2_model_info_t *out);
 int b2_tokenize(b2_engine *e, const char *text, size_t n, int add_bos, int parse_special, int32_t *out, int cap);
 /* llama_token_to_piece (grpc-server.cpp:116,124,1012).  Returns bytes written or -(needed). */
 int b2_token_to_piece(b2_engine *e, int32_t token, char *out, int cap);
+
+/* ------------------------------------------------------------------------------------------------
+ * Tensor parallelism (b2_load_opts.tp_size > 1).  Replaces llama.cpp's tensor_split / main_gpu, the reference's only
+ * multi-GPU knobs (backend/backend.proto:175-176 -> backend/cpp/llama/grpc-server.cpp:2240-2262).  Every entry point of
+ * this header works on such an engine unchanged; the two below select and report the exchange between the shards.
+ *   mode 0 (B2_TP_NCCL)   per-layer kernels + ncclAllReduce after attn_output and ffn_down (BASELINE.json north_star)
+ *   mode 1 (B2_TP_FUSED)  one persistent decode kernel per GPU; partial rows are stored into the peers' memory over
+ *                         NVLink and summed by the consuming phase (the default when the model's shapes allow it)
+ */
+enum { B2_TP_NCCL = 0, B2_TP_FUSED = 1 };
+typedef struct {
+    int32_t tp_size;               /* 1: not tensor-parallel */
+    int32_t mode;                  /* B2_TP_NCCL / B2_TP_FUSED */
+    int32_t n_allreduce_per_step;  /* 2 x n_layer */
+    int32_t reserved;
+    double allreduce_ms_per_step;  /* B2_TP_NCCL: time inside the collectives per step of the last b2_bench_decode (CUDA events, shard 0) */
+    int64_t shard_stream_bytes;    /* weight bytes ONE shard streams per decode step */
+} b2_tp_info_t;
+int b2_tp_set_mode(b2_engine *e, int mode);
+int b2_tp_info(b2_engine *e, b2_tp_info_t *out);
 
 /* ------------------------------------------------------------------------------------------------
  * Predict / PredictStream / Embedding.  Replaces parse_options + request_completion + the result queue

@@ -19,11 +19,12 @@ B2_T_F32, B2_T_F16, B2_T_Q8_0, B2_T_Q4_K, B2_T_Q5_K, B2_T_Q6_K = 0, 1, 8, 12, 13
 B2_T_Q4_0, B2_T_Q4_1, B2_T_Q5_0, B2_T_Q5_1, B2_T_Q2_K, B2_T_Q3_K = 2, 3, 6, 7, 10, 11  # tensor-core path only
 B2_T_IQ4_NL, B2_T_IQ4_XS = 20, 23  # likewise
 B2_ETIMEOUT = -8
+B2_TP_NCCL, B2_TP_FUSED = 0, 1
 B2_EUNSUPPORTED = -9
 EV_FINAL, EV_STOP_EOS, EV_STOP_WORD, EV_STOP_LIMIT, EV_ERROR, EV_EMBEDDING = 1, 2, 4, 8, 16, 32
 
 EXPORTS = [
-    "b2_abi_version", "b2_last_error", "b2_device_count", "b2_create", "b2_destroy", "b2_model_info", "b2_tokenize",
+    "b2_tp_set_mode", "b2_tp_info", "b2_abi_version", "b2_last_error", "b2_device_count", "b2_create", "b2_destroy", "b2_model_info", "b2_tokenize",
     "b2_token_to_piece", "b2_submit", "b2_poll", "b2_cancel", "b2_embed_result", "b2_release", "b2_metrics", "b2_eval",
     "b2_decode_greedy", "b2_debug_hidden", "b2_bench_decode", "b2_bench_prefill", "b2_bench_gemv", "b2_dequantize", "b2_quantize_act",
     "b2_mul_mat", "b2_mul_mat_noalloc", "b2_sample", "b2_grammar_match", "b2_grammar_token_mask",
@@ -43,7 +44,7 @@ class LoadOpts(C.Structure):
         ("struct_size", C.c_uint32), ("model_path", C.c_char_p), ("n_ctx", C.c_int32), ("n_batch", C.c_int32),
         ("n_parallel", C.c_int32), ("device", C.c_int32), ("embeddings", C.c_int32), ("rope_freq_base", C.c_float),
         ("rope_freq_scale", C.c_float), ("kv_page_size", C.c_int32), ("vocab_only", C.c_int32),
-        ("reserved", C.c_int32 * 7),
+        ("tp_size", C.c_int32), ("reserved", C.c_int32 * 6),
     ]
 
 
@@ -93,6 +94,11 @@ class BertInfo(C.Structure):
                 ("n_vocab", C.c_int32), ("weight_bytes_device", C.c_int64)]
 
 
+class TPInfo(C.Structure):
+    _fields_ = [("tp_size", C.c_int32), ("mode", C.c_int32), ("n_allreduce_per_step", C.c_int32), ("reserved", C.c_int32),
+                ("allreduce_ms_per_step", C.c_double), ("shard_stream_bytes", C.c_int64)]
+
+
 class Metrics(C.Structure):
     _fields_ = [
         ("slot_id", C.c_int32), ("tokens_per_second", C.c_float), ("tokens_generated", C.c_int32),
@@ -130,6 +136,8 @@ def lib() -> C.CDLL:
     L.b2_embed_result.argtypes = [vp, i64, vp, i32]
     L.b2_release.argtypes = [vp, i64]
     L.b2_metrics.argtypes = [vp, C.POINTER(Metrics)]
+    L.b2_tp_set_mode.argtypes = [vp, i32]
+    L.b2_tp_info.argtypes = [vp, C.POINTER(TPInfo)]
     L.b2_eval.argtypes = [vp, i32, vp, i32, i32, vp, i32, vp]
     L.b2_decode_greedy.argtypes = [vp, i32, vp, i32, i32, vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.b2_debug_hidden.argtypes = [vp, vp, i32]
@@ -252,13 +260,14 @@ class Engine:
 
     def __init__(self, model_path: str, n_ctx: int = 1024, n_batch: int = 512, n_parallel: int = 1, device: int = 0,
                  embeddings: bool = False, rope_freq_base: float = 0.0, rope_freq_scale: float = 0.0,
-                 kv_page_size: int = 0, vocab_only: bool = False):
+                 kv_page_size: int = 0, vocab_only: bool = False, tp_size: int = 0):
         o = LoadOpts()
         o.struct_size = C.sizeof(LoadOpts)
         o.model_path = os.fsencode(model_path)
         o.n_ctx, o.n_batch, o.n_parallel, o.device = n_ctx, n_batch, n_parallel, device
         o.embeddings = int(embeddings)
         o.vocab_only = int(vocab_only)
+        o.tp_size = int(tp_size)
         o.rope_freq_base, o.rope_freq_scale, o.kv_page_size = rope_freq_base, rope_freq_scale, kv_page_size
         self._h = lib().b2_create(C.byref(o))
         if not self._h:
@@ -328,6 +337,15 @@ class Engine:
         ms, l = C.c_double(0), C.c_int64(0)
         _check(lib().b2_bench_decode(self._h, batch, ctx_len, n_steps, n_warmup, C.byref(ms), C.byref(l)))
         return ms.value, l.value
+
+    def tp_set_mode(self, mode: int):
+        """0 = per-layer kernels + ncclAllReduce, 1 = persistent kernels exchanging partial rows over peer memory"""
+        _check(lib().b2_tp_set_mode(self._h, mode))
+
+    def tp_info(self) -> dict:
+        t = TPInfo()
+        _check(lib().b2_tp_info(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in TPInfo._fields_ if k != "reserved"}
 
     def last_mega_ms(self) -> float:
         """mean decode_mega_kernel launch (ms) of the last bench_decode(1, ...): CUDA events around every launch"""

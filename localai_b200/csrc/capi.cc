@@ -206,6 +206,27 @@ double b2_bench_last_mega_ms(b2_engine *e) {
     }
 }
 
+int b2_tp_set_mode(b2_engine *e, int mode) {
+    B2_API_BEGIN
+    std::lock_guard<std::mutex> lk(E(e)->device_mutex());
+    E(e)->model().tp_set_mode(mode);
+    return 0;
+    B2_API_END(0)
+}
+
+int b2_tp_info(b2_engine *e, b2_tp_info_t *out) {
+    B2_API_BEGIN
+    B2_CHECK(out != nullptr, B2_EINVAL, "b2_tp_info: no output");
+    Model &m = E(e)->model();
+    out->tp_size = m.tp_size;
+    out->mode = m.tp_size > 1 ? m.tp_mode() : 0;
+    out->n_allreduce_per_step = m.tp_size > 1 ? m.tp_n_allreduce : 0;
+    out->allreduce_ms_per_step = E(e)->last_tp_allreduce_ms_;
+    out->shard_stream_bytes = m.decode_stream_bytes;
+    return 0;
+    B2_API_END(0)
+}
+
 // undocumented profiling hook (not part of the ABI header): per-CTA, per-phase clock64 stamps of the decode mega-kernel
 int b2_mega_debug(b2_engine *e, long long *out, int cap) {
     B2_API_BEGIN

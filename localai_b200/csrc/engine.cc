@@ -312,12 +312,18 @@ int Engine::bench_decode(int batch, int ctx_len, int n_steps, int n_warmup, doub
     for (int i = 0; i < n_warmup; i++) step();
     m.sync();
     const int64_t l0 = g_launch_count;
-    if (batch == 1) m.mega_timing_begin(n_steps);
+    if (batch == 1 && m.tp_size == 1) m.mega_timing_begin(n_steps);
+    if (m.tp_size > 1) m.tp_timing(true);
     B2_CUDA(cudaEventRecord(e0, m.stream));
     for (int i = 0; i < n_steps; i++) step();
     B2_CUDA(cudaEventRecord(e1, m.stream));
     m.sync();
-    last_mega_ms_ = batch == 1 ? m.mega_timing_end() : 0.0;
+    last_mega_ms_ = batch == 1 && m.tp_size == 1 ? m.mega_timing_end() : 0.0;
+    if (m.tp_size > 1) {
+        m.tp_sync();
+        last_tp_allreduce_ms_ = m.tp_allreduce_ms() / n_steps;
+        m.tp_timing(false);
+    }
     float ms = 0;
     B2_CUDA(cudaEventElapsedTime(&ms, e0, e1));
     cudaEventDestroy(e0);

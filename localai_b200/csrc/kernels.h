@@ -112,6 +112,18 @@ struct MegaPhase {
     const uint2 *res_ll = nullptr;   // residual in LL words (written by an earlier phase; no tag check needed)
     float *xn_out = nullptr;       // optional: the normalised row (LM head -> embeddings)
     __half *k_pool = nullptr, *v_pool = nullptr; // this layer's KV pools (QKV, ATT)
+    // tensor parallelism (tp.cu): a row-parallel mat-mul's output is a PARTIAL row; it is stored, as LL words, into the
+    // receive buffer of every shard (peer_part[j] = shard j's buffer for this shard's partial, peer memory over NVLink).
+    // The phase that consumes the row first adds the reduce_n partial rows in rank order plus the residual and
+    // publishes the sum in x_ll (each CTA a slice of it), then reads x_ll like any other input.
+    int n_peers = 0;
+    uint2 *peer_part[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int reduce_n = 0;              // > 0: x_ll must first be assembled from part_ll[reduce_n][reduce_len]
+    int reduce_len = 0;
+    const uint2 *part_ll = nullptr;
+    uint2 *x_ll_w = nullptr;       // x_ll, writable (the reducer's output)
+    const uint2 *red_res_ll = nullptr; // the residual the reducer adds: LL words (no tag check) ...
+    const float *red_residual = nullptr; // ... or plain fp32 written before the launch
     uint2 *xq_ll = nullptr;        // if set: the row is quantised once per GPU (block b by CTA b) into this buffer of
                                    // LL words holding the image of the shared-memory activation row, then copied
     int units = 0;                 // row pairs (PLAIN/QKV) or rows (SWIGLU) split across the CTAs
@@ -129,7 +141,8 @@ struct MegaStreamStart {
     const uint8_t *src = nullptr; // first tile of the stream (16-byte aligned)
     uint32_t size0 = 0, size1 = 0; // bytes of the first two tiles (0: the stream has no such tile)
     int32_t first_p = 0;           // first phase in which this warp has tiles (n_phases: never)
-    int32_t pad[3] = {0, 0, 0};
+    uint32_t total = 0;            // bytes of the whole stream
+    int32_t pad[2] = {0, 0};
 };
 struct MegaArgs {
     const MegaPhase *phases = nullptr; // device
@@ -148,6 +161,8 @@ struct MegaArgs {
     uint2 *att_scores = nullptr;     // [n_head][att_scores_stride] scores of the current layer (LL words)
     int64_t att_scores_stride = 0;
     uint2 *att_part_out = nullptr;   // [n_head][att_parts][hd] partial outputs (LL words)
+    float *out_override = nullptr;   // if set: the last phase's plain output row goes here instead of phase.out (tp.cu: logits row of this step)
+    float *xn_override = nullptr;    // likewise for phase.xn_out
     long long *dbg = nullptr; // optional [n_cta][n_phases][16] clock64 stamps and per-phase cycle counts (scratch/mega_dbg.py)
 };
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s);

@@ -36,12 +36,22 @@ namespace b2 {
 
 constexpr int MG_WARPS = 8;
 constexpr int MG_THREADS = MG_WARPS * 32;
-constexpr int MG_STAGES = 2;                 // per warp
+// ring geometry (overridable at build time for A/B measurements: make VARIANT=...)
+#ifndef B2_MG_STAGES
+#define B2_MG_STAGES 2
+#endif
+#ifndef B2_MG_TILE_DATA
+#define B2_MG_TILE_DATA 9216
+#endif
+#ifndef B2_MG_XS_KB
+#define B2_MG_XS_KB 34
+#endif
+constexpr int MG_STAGES = B2_MG_STAGES;      // per warp
 constexpr int MG_TILE_HDR = 16;              // tile header, in-band
-constexpr int MG_TILE_DATA = 9216;           // weight bytes of a tile, at most
+constexpr int MG_TILE_DATA = B2_MG_TILE_DATA; // weight bytes of a tile, at most
 constexpr int MG_STAGE_BYTES = MG_TILE_HDR + MG_TILE_DATA;
 constexpr int MG_RING_BYTES = MG_WARPS * MG_STAGES * MG_STAGE_BYTES;
-constexpr int MG_XS_BYTES = 34 * 1024;       // quantised activation row, K <= 28672 (attention: scratch, together with the partials)
+constexpr int MG_XS_BYTES = B2_MG_XS_KB * 1024; // quantised activation row, K <= 28672 at 34 KB (attention: scratch, together with the partials)
 constexpr int MG_MAX_PART = 2048;            // per-phase partial sums: rows of this CTA x K-splits
 constexpr int MG_PB = 8;                     // prologue: 256-element blocks a warp holds in registers (K <= 16384)
 constexpr int MG_MAX_PASS = 8;               // warp passes per tile
@@ -146,6 +156,10 @@ __device__ __forceinline__ void mg_bulk(uint32_t dst, const void *src, uint32_t 
                  "r"(bytes), "r"(bar)
                  : "memory");
 }
+// ask for [p, p + bytes) to be brought into L2 (fire and forget; 16-byte granularity)
+__device__ __forceinline__ void mg_prefetch_l2(const void *p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ int4 mg_lds128(uint32_t a) {
     int4 r;
     asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
@@ -189,10 +203,21 @@ __device__ __forceinline__ unsigned long long ll_ld(const uint2 *p) {
 __device__ __forceinline__ void ll_ld2(const uint2 *p, unsigned long long &w0, unsigned long long &w1) { // p 16-byte aligned
     asm volatile("ld.relaxed.gpu.global.v2.b64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
 }
+// the same across GPUs (peer memory over NVLink): system scope
+__device__ __forceinline__ void ll_st_sys(uint2 *p, float v, uint32_t tag) {
+    const unsigned long long w = ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(v);
+    asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ unsigned long long ll_ld_sys(const uint2 *p) {
+    unsigned long long w;
+    asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    return w;
+}
 __device__ __forceinline__ uint32_t ll_tag(unsigned long long w) { return (uint32_t)(w >> 32); }
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((uint32_t)w); }
 // Spin budget of every LL wait: a wait that long is a bug (a producer that never ran), and traps instead of hanging.
 constexpr unsigned MG_SPIN_LIMIT = 1u << 27;
+__device__ unsigned g_mega_l2_ahead = 32768; // B200LLM_MEGA_L2_AHEAD: bytes of its weight stream every warp keeps requested into L2 beyond its ring (0: off)
 __device__ unsigned g_ll_probe = 1;   // B200LLM_LL_PROBE=0: no light probe before the full-slice poll
 __device__ unsigned g_ll_poll_ns = 32; // B200LLM_LL_POLL_NS (tuning knob): sleep between two polls of an LL word
 __device__ __forceinline__ void ll_backoff(unsigned &spins) {
@@ -692,7 +717,8 @@ __device__ __noinline__ void mg_copy_xq(const uint2 *xq_ll, uint32_t tag, int64_
 // quantize_row_q8_K_ref / quantize_row_q8_0_ref (act_quant.cuh holds the same arithmetic for the other kernels).
 template <int PBN>
 __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, float eps, uint8_t *xs, double *s_part, int nb, int k_first,
-                                         int warp, int lane, bool write_xn) {
+                                         int warp, int lane, float *xn_out) {
+    const bool write_xn = xn_out != nullptr;
     const int64_t K = ph.K;
     const bool has_norm = ph.norm_w != nullptr;
     float v[PBN][8], w[PBN <= 2 ? PBN : 1][8];
@@ -778,7 +804,7 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, f
                 for (int i = 0; i < 8; i++) v[k][i] = __fmul_rn(__fmul_rn(v[k][i], scale), w[PBN <= 2 ? k : 0][i]);
             }
             if (write_xn && valid[k]) { // the normalised row itself (embeddings)
-                float *o = ph.xn_out + b * 256 + lane * 8;
+                float *o = xn_out + b * 256 + lane * 8;
                 *(float4 *)o = make_float4(v[k][0], v[k][1], v[k][2], v[k][3]);
                 *(float4 *)(o + 4) = make_float4(v[k][4], v[k][5], v[k][6], v[k][7]);
             }
@@ -900,7 +926,8 @@ decode_mega_kernel(const MegaArgs a) {
     // ---- this warp's ring and its weight stream: the first two tiles are requested right away
     const uint32_t ring = mg_s32(smem) + warp * (MG_STAGES * MG_STAGE_BYTES);
     const uint32_t bar0 = mg_s32(bars + warp * MG_STAGES);
-    const uint8_t *src;
+    const uint8_t *src; // next tile to request into the ring
+    uint32_t rem;       // bytes of the stream from src on (the L2 prefetch front runs g_mega_l2_ahead bytes ahead of src)
     int next_p; // the next phase in which this warp has tiles
     {
         const MegaStreamStart st = a.starts[cta * MG_WARPS + warp];
@@ -911,6 +938,12 @@ decode_mega_kernel(const MegaArgs a) {
             if (st.size1) { mg_expect_tx(bar0 + 8, st.size1); mg_bulk(ring + MG_STAGE_BYTES, src + st.size0, st.size1, bar0 + 8); }
         }
         src += st.size0 + st.size1;
+        // Beyond the ring, the stream is kept requested into L2 a fixed distance ahead: while the CTA sits in the latency-bound
+        // phases (QKV, attention, attn_output: a few MB of weights between many hand-overs) HBM keeps working on the rows
+        // of the big phases that follow, and their ring refills then come from L2.
+        rem = st.total - st.size0 - st.size1;
+        const uint32_t ahead = g_mega_l2_ahead;
+        if (ahead && lane == 0 && rem) mg_prefetch_l2(src, min(ahead, rem));
     }
     uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
 
@@ -937,6 +970,36 @@ decode_mega_kernel(const MegaArgs a) {
                 stage_phase(p + 2);
             }
         }
+        if (ph.kind != PH_ATT && ph.reduce_n > 0) {
+            // Tensor parallelism: the input row is the sum of reduce_n partial rows, one from every shard (they arrive in
+            // this GPU's memory as LL words stored by the peers), plus the residual.  Every CTA assembles a slice of it --
+            // the partial rows are added in rank order, so all shards compute the same bits -- and publishes the slice
+            // in x_ll, with the tag the prologue below waits for.
+            const int per = (ph.reduce_len + n_cta - 1) / n_cta;
+            for (int k = tid; k < per; k += MG_THREADS) {
+                const int e = cta * per + k;
+                if (e >= ph.reduce_len) break;
+                float pv[8];
+                unsigned spins = 0;
+                while (true) {
+                    bool ok = true;
+#pragma unroll
+                    for (int j = 0; j < 8; j++)
+                        if (j < ph.reduce_n) {
+                            const unsigned long long w = ll_ld_sys(ph.part_ll + (size_t)j * ph.reduce_len + e);
+                            ok = ok && ll_tag(w) == tag_in;
+                            pv[j] = ll_val(w);
+                        }
+                    if (ok) break;
+                    ll_backoff(spins);
+                }
+                float sum = ph.red_res_ll ? ll_val(ll_ld(ph.red_res_ll + e)) : ph.red_residual ? __ldcg(ph.red_residual + e) : 0.f;
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (j < ph.reduce_n) sum += pv[j];
+                ll_st(ph.x_ll_w + e, sum, tag_in);
+            }
+        }
         if (ph.kind != PH_ATT && ph.xq_ll) {
             // A long activation row is quantised ONCE per GPU (block b by warp 0 of CTA b, as soon as its inputs are
             // there), not once per CTA; the prologue below then copies the 16 KB image.
@@ -953,7 +1016,7 @@ decode_mega_kernel(const MegaArgs a) {
             if (ph.xq_ll) { // quantised once per GPU (above): copy the image of the activation row
                 mg_copy_xq(ph.xq_ll, tag_out, K, nb, xs, tid);
             } else {
-                const bool wx = ph.xn_out && cta == 0;
+                float *wx = ph.xn_out && cta == 0 ? (a.xn_override ? a.xn_override : ph.xn_out) : nullptr;
                 if (nb <= MG_WARPS) mg_prologue<1>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
                 else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
                 else // 4 blocks per warp at a time; rows longer than 32 blocks have no norm (mega_phase_prepare)
@@ -1001,7 +1064,7 @@ decode_mega_kernel(const MegaArgs a) {
             const uint32_t q6d = (uint32_t)((nb >> ph.s_log) * Q6_BLK + 2 * L.kb); // Q6_K: this lane's fp16 scale inside a row-split
             // the residual of this thread's first output row is requested now, not in the epilogue (a round trip under load)
             float res_pre = 0.f;
-            if (ph.kind == PH_PLAIN && tid < u_end - u) {
+            if (ph.kind == PH_PLAIN && ph.n_peers == 0 && tid < u_end - u) {
                 if (ph.res_ll) res_pre = ll_val(ll_ld(ph.res_ll + u + tid));
                 else if (ph.residual) res_pre = __ldcg(ph.residual + u + tid);
             }
@@ -1114,8 +1177,11 @@ decode_mega_kernel(const MegaArgs a) {
                         if (lane == 0) {
                             mg_expect_tx(bar, (uint32_t)th.z);
                             mg_bulk(st, src, (uint32_t)th.z, bar);
+                            const uint32_t ahead = g_mega_l2_ahead;
+                            if (ahead && ahead < rem) mg_prefetch_l2(src + ahead, min((uint32_t)th.z, rem - ahead));
                         }
                         src += (uint32_t)th.z;
+                        rem -= (uint32_t)th.z;
                     }
                     if (++stg == MG_STAGES) { stg = 0; parity ^= 1; }
                     if (th.w & 1) { next_p = (int)((uint32_t)th.w >> 8); break; }
@@ -1139,14 +1205,23 @@ decode_mega_kernel(const MegaArgs a) {
                     const float g = dot_sum(r), up = dot_sum(n_r + r);
                     ll_st(ph.out_ll + u + r, __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), up), tag_out);
                 }
+            } else if (ph.kind == PH_PLAIN && ph.n_peers > 0) {
+                // a partial row of a tensor-parallel model: one plain 64-bit store per shard, this one included
+                for (int r = tid; r < n_r; r += MG_THREADS) {
+                    const float s = dot_sum(r);
+#pragma unroll
+                    for (int j = 0; j < 8; j++)
+                        if (j < ph.n_peers) ll_st_sys(ph.peer_part[j] + u + r, s, tag_out);
+                }
             } else if (ph.kind == PH_PLAIN) {
+                float *outp = a.out_override && !ph.out_ll ? a.out_override : ph.out;
                 for (int r = tid; r < n_r; r += MG_THREADS) {
                     float s = dot_sum(r);
                     if (r == tid) s += res_pre; // requested before the tile loop
                     else if (ph.res_ll) s += ll_val(ll_ld(ph.res_ll + u + r));
                     else if (ph.residual) s += __ldcg(ph.residual + u + r);
                     if (ph.out_ll) ll_st(ph.out_ll + u + r, s, tag_out);
-                    else ph.out[u + r] = s;
+                    else outp[u + r] = s;
                 }
             } else { // PH_QKV: job 0 = q, 1 = k, 2 = v; rows (r, r+1) form a rotary pair inside one head
                 const int64_t cell = ((((int64_t)pbase[pos >> a.page_shift]) << a.page_shift) + (pos & (a.page_size - 1))) * a.kvd;
@@ -1195,6 +1270,7 @@ void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s) {
     static PerDeviceOnce knobs;
     knobs.run([&] {
         if (getenv("B200LLM_LL_POLL_NS")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_LL_POLL_NS")); B2_CUDA(cudaMemcpyToSymbol(g_ll_poll_ns, &v, sizeof(v))); }
+        if (getenv("B200LLM_MEGA_L2_AHEAD")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_MEGA_L2_AHEAD")) / 16 * 16; B2_CUDA(cudaMemcpyToSymbol(g_mega_l2_ahead, &v, sizeof(v))); }
         if (getenv("B200LLM_LL_PROBE")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_LL_PROBE")); B2_CUDA(cudaMemcpyToSymbol(g_ll_probe, &v, sizeof(v))); }
     });
     void *args[] = {(void *)&a};
@@ -1362,6 +1438,7 @@ static uint64_t mega_plan_streams(const MegaPhase *phases, int n_phases, int n_c
             ss.first_p = first_p;
             ss.size0 = n_t > 0 ? tile_bytes(first) : 0;
             ss.size1 = n_t > 1 ? tile_bytes(first + 1) : 0;
+            ss.total = n_t > 0 ? (uint32_t)(off - tab[first].dst) : 0;
             first_off[(size_t)cta * MG_WARPS + warp] = n_t > 0 ? tab[first].dst : 0;
         }
     return off + 128;

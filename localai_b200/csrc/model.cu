@@ -18,21 +18,26 @@ void *Model::dalloc(size_t bytes) {
     return p;
 }
 
-DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required) {
+DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required,
+                      int64_t row0, int64_t nrows, int64_t col0, int64_t ncols) {
     const GGUFTensorInfo *ti = f.tensor(name);
     if (!ti) {
         B2_CHECK(!required, B2_EIO, "gguf: missing tensor " + name);
         return DTensor{};
     }
     B2_CHECK(ti->n_bytes >= 0, B2_EUNSUPPORTED, "gguf: tensor " + name + " has unsupported ggml type " + std::to_string(ti->type));
-    const int64_t cols = ti->ne[0];
-    const int64_t rows = ti->ne.size() > 1 ? ti->ne[1] : 1;
-    B2_CHECK(cols == want_cols && rows == want_rows, B2_EIO,
-             "gguf: tensor " + name + " has shape [" + std::to_string(rows) + "," + std::to_string(cols) + "], expected [" +
+    const int64_t cols_all = ti->ne[0];
+    const int64_t rows_all = ti->ne.size() > 1 ? ti->ne[1] : 1;
+    B2_CHECK(cols_all == want_cols && rows_all == want_rows, B2_EIO,
+             "gguf: tensor " + name + " has shape [" + std::to_string(rows_all) + "," + std::to_string(cols_all) + "], expected [" +
                  std::to_string(want_rows) + "," + std::to_string(want_cols) + "]");
+    // the slice this shard keeps (everything when the model is not tensor-parallel)
+    const int64_t rows = nrows < 0 ? rows_all : nrows, cols = ncols < 0 ? cols_all : ncols;
+    const int be = type_block_elems(ti->type);
+    B2_CHECK(row0 >= 0 && row0 + rows <= rows_all && col0 >= 0 && col0 + cols <= cols_all && col0 % be == 0 && cols % be == 0, B2_EINVAL,
+             "tensor " + name + ": slice outside the tensor or off the block boundaries");
     if (type_tiles_only(ti->type)) {
-        B2_CHECK(cols % std::max(64, type_block_elems(ti->type)) == 0, B2_EUNSUPPORTED,
-                 "tensor " + name + ": row length must be a multiple of 64 and of the block size");
+        B2_CHECK(cols % std::max(64, be) == 0, B2_EUNSUPPORTED, "tensor " + name + ": row length must be a multiple of 64 and of the block size");
         tiles_only_ = true; // these formats have no integer decode kernel: everything goes through the bf16 tiles
     } else if (ti->type != B2_T_F32 && ti->type != B2_T_F16) {
         B2_CHECK(cols % 256 == 0, B2_EUNSUPPORTED, "tensor " + name + ": quantised row length must be a multiple of 256");
@@ -43,12 +48,20 @@ DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_r
     t.cols = cols;
     t.row_stride = device_row_stride(ti->type, cols);
     uint8_t *dst = (uint8_t *)dalloc((size_t)t.bytes());
-    if ((size_t)ti->n_bytes > staging_bytes_) {
+    const int64_t row_bytes_all = gguf_row_bytes(ti->type, cols_all), row_bytes = gguf_row_bytes(ti->type, cols);
+    const size_t n_bytes = (size_t)(rows * row_bytes);
+    if (n_bytes > staging_bytes_) {
         if (staging_) cudaFree(staging_);
-        staging_bytes_ = (size_t)ti->n_bytes;
+        staging_bytes_ = n_bytes;
         B2_CUDA(cudaMalloc((void **)&staging_, staging_bytes_));
     }
-    B2_CUDA(cudaMemcpyAsync(staging_, ti->data, (size_t)ti->n_bytes, cudaMemcpyHostToDevice, stream));
+    const uint8_t *src = ti->data + row0 * row_bytes_all;
+    if (cols == cols_all) { // whole rows: one contiguous range of the file
+        B2_CUDA(cudaMemcpyAsync(staging_, src, n_bytes, cudaMemcpyHostToDevice, stream));
+    } else { // a K-slice: the blocks [col0 / be, (col0 + cols) / be) of every row
+        B2_CUDA(cudaMemcpy2DAsync(staging_, (size_t)row_bytes, src + gguf_row_bytes(ti->type, col0), (size_t)row_bytes_all, (size_t)row_bytes,
+                                  (size_t)rows, cudaMemcpyHostToDevice, stream));
+    }
     launch_repack(t.type, staging_, dst, rows, cols, stream);
     B2_CUDA(cudaStreamSynchronize(stream)); // staging buffer is reused by the next tensor
     t.data = dst;
@@ -56,11 +69,13 @@ DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_r
     return t;
 }
 
-Model::Model(const GGUFFile &f, const b2_load_opts &o) {
+Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_size_arg) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) throw Error(B2_ENODEV, "no CUDA device visible (this library has no CPU fallback)");
-    device = o.device;
-    B2_CHECK(device >= 0 && device < ndev, B2_EINVAL, "device ordinal out of range");
+    tp_size = tp_size_arg > 0 ? tp_size_arg : (o.struct_size >= offsetof(b2_load_opts, tp_size) + sizeof(o.tp_size) && o.tp_size > 1 ? o.tp_size : 1);
+    tp_rank = tp_rank_arg;
+    device = o.device + tp_rank;
+    B2_CHECK(device >= 0 && device < ndev, B2_EINVAL, tp_size > 1 ? "tensor-parallel model: not enough devices" : "device ordinal out of range");
     B2_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop;
     B2_CUDA(cudaGetDeviceProperties(&prop, device));
@@ -108,8 +123,18 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     B2_CHECK(n_ctx_slot > 0, B2_EINVAL, "context size smaller than the number of slots");
     max_pages = (n_ctx_slot + page_size - 1) / page_size;
 
-    const int d = hp.n_embd, ff = hp.n_ff, kvd = hp.n_head_kv * hp.head_dim;
-    // ---- weights, in execution order
+    const int d = hp.n_embd;
+    B2_CHECK(tp_size == 1 || (hp.n_head % tp_size == 0 && hp.n_head_kv % tp_size == 0 && (hp.n_ff / tp_size) % 256 == 0 && hp.n_ff % tp_size == 0 &&
+                              (d / tp_size) % 256 == 0 && hp.n_vocab % (2 * tp_size) == 0),
+             B2_EUNSUPPORTED, "tensor-parallel degree does not divide the heads / KV heads / 256-weight blocks of this model");
+    nh_l = hp.n_head / tp_size;
+    nkv_l = hp.n_head_kv / tp_size;
+    ff_l = hp.n_ff / tp_size;
+    dq_l = nh_l * hp.head_dim;
+    kvd_l = nkv_l * hp.head_dim;
+    vocab_l = hp.n_vocab / tp_size;
+    const int ff = hp.n_ff, kvd = hp.n_head_kv * hp.head_dim, r = tp_rank;
+    // ---- weights, in execution order (a tensor-parallel shard keeps its rows / its K-slice only)
     tok_embd = upload(f, "token_embd.weight", hp.n_vocab, d, true);
     const int64_t embd_bytes = tok_embd.bytes();
     layers.resize(hp.n_layer);
@@ -117,21 +142,23 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
         const std::string p = "blk." + std::to_string(l) + ".";
         LayerW &L = layers[l];
         L.attn_norm = upload(f, p + "attn_norm.weight", 1, d, true);
-        L.wq = upload(f, p + "attn_q.weight", d, d, true);
-        L.wk = upload(f, p + "attn_k.weight", kvd, d, true);
-        L.wv = upload(f, p + "attn_v.weight", kvd, d, true);
-        L.wo = upload(f, p + "attn_output.weight", d, d, true);
+        L.wq = upload(f, p + "attn_q.weight", d, d, true, (int64_t)r * dq_l, dq_l);
+        L.wk = upload(f, p + "attn_k.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
+        L.wv = upload(f, p + "attn_v.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
+        L.wo = upload(f, p + "attn_output.weight", d, d, true, 0, -1, (int64_t)r * dq_l, dq_l);
         L.ffn_norm = upload(f, p + "ffn_norm.weight", 1, d, true);
-        L.gate = upload(f, p + "ffn_gate.weight", ff, d, true);
-        L.up = upload(f, p + "ffn_up.weight", ff, d, true);
-        L.down = upload(f, p + "ffn_down.weight", d, ff, true);
+        L.gate = upload(f, p + "ffn_gate.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
+        L.up = upload(f, p + "ffn_up.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
+        L.down = upload(f, p + "ffn_down.weight", d, ff, true, 0, -1, (int64_t)r * ff_l, ff_l);
         B2_CHECK(L.attn_norm.type == B2_T_F32 && L.ffn_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
     }
     output_norm = upload(f, "output_norm.weight", 1, d, true);
     B2_CHECK(output_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
     B2_CHECK(!(tiles_only_ && no_gemm_), B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K / IQ4 weights need the tensor-core path (B200LLM_NO_GEMM is set)");
-    output = upload(f, "output.weight", hp.n_vocab, d, false);
+    B2_CHECK(!(tiles_only_ && tp_size > 1), B2_EUNSUPPORTED, "tensor-parallel models need weights with an integer decode kernel (Q4_K, Q5_K, Q6_K, Q8_0)");
+    output = upload(f, "output.weight", hp.n_vocab, d, false, (int64_t)r * vocab_l, vocab_l);
     if (!output.data) { // tied embeddings
+        B2_CHECK(tp_size == 1, B2_EUNSUPPORTED, "tensor-parallel models need an output.weight tensor");
         output = tok_embd;
         decode_stream_bytes = weight_bytes;
     } else {
@@ -145,13 +172,13 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
 
     // ---- KV cache (F16, paged; slot s statically owns pages [s*max_pages, (s+1)*max_pages))
     const int64_t n_pages = (int64_t)n_parallel * max_pages;
-    pool_layer_stride_ = n_pages * page_size * kvd;
+    pool_layer_stride_ = n_pages * page_size * kvd_l;
     const size_t pool_bytes = (size_t)pool_layer_stride_ * hp.n_layer * sizeof(__half);
     k_pool_ = (__half *)dalloc(pool_bytes);
     v_pool_ = (__half *)dalloc(pool_bytes);
     B2_CUDA(cudaMemsetAsync(k_pool_, 0, pool_bytes, stream));
     B2_CUDA(cudaMemsetAsync(v_pool_, 0, pool_bytes, stream));
-    kv_bytes_per_pos = (int64_t)2 * hp.n_layer * kvd * sizeof(__half);
+    kv_bytes_per_pos = (int64_t)2 * hp.n_layer * kvd_l * sizeof(__half);
     {
         std::vector<int32_t> pt((size_t)n_parallel * max_pages);
         for (size_t i = 0; i < pt.size(); i++) pt[i] = (int32_t)i;
@@ -181,13 +208,14 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     const size_t nb = (size_t)n_batch;
     x_ = (float *)dalloc(nb * d * 4);
     xn_ = (float *)dalloc(nb * d * 4);
-    q_ = (float *)dalloc(nb * d * 4);
-    k_ = (float *)dalloc(nb * kvd * 4);
-    v_ = (float *)dalloc(nb * kvd * 4);
-    att_ = (float *)dalloc(nb * d * 4);
-    gate_ = (float *)dalloc(nb * ff * 4);
-    up_ = (float *)dalloc(nb * ff * 4);
-    const int64_t kmax = std::max(d, ff);
+    q_ = (float *)dalloc(nb * dq_l * 4);
+    k_ = (float *)dalloc(nb * kvd_l * 4);
+    v_ = (float *)dalloc(nb * kvd_l * 4);
+    att_ = (float *)dalloc(nb * dq_l * 4);
+    gate_ = (float *)dalloc(nb * ff_l * 4);
+    up_ = (float *)dalloc(nb * ff_l * 4);
+    if (tp_size > 1) xp_ = (float *)dalloc(nb * d * 4);
+    const int64_t kmax = std::max(d, ff_l);
     for (int fmt = ACT_F16; fmt <= ACT_Q8_K; fmt++) actq_[fmt] = (uint8_t *)dalloc(nb * (size_t)act_row_bytes((ActFmt)fmt, kmax));
     tok_ = (int32_t *)dalloc(nb * 4);
     pos_ = (int32_t *)dalloc(nb * 4);
@@ -197,10 +225,17 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o) {
     xn_out_ = (float *)dalloc(nb * d * 4);
     sample_specs_ = (SampleSpec *)dalloc(nb * sizeof(SampleSpec));
     sample_mu_ = (float *)dalloc(nb * sizeof(float));
-    ensure_logits_rows(std::max(n_parallel, 1));
-    build_mega();
+    if (tp_size > 1) {
+        B2_CUDA(cudaEventCreateWithFlags(&tp_done_, cudaEventDisableTiming));
+        B2_CUDA(cudaEventCreateWithFlags(&tp_in_, cudaEventDisableTiming));
+    }
+    // a tensor-parallel shard never re-allocates its logits rows (the fused decode kernels' phase lists hold the address):
+    // one row per token of the largest batch, plus a spare one for rows nobody asked for
+    ensure_logits_rows(tp_size > 1 ? n_batch + 1 : std::max(n_parallel, 1));
+    if (tp_size == 1) build_mega();
     decode_graphs_.assign((size_t)std::min(n_parallel, 64) + 1, nullptr);
     decode_graph_launches_.assign(decode_graphs_.size(), 0);
+    if (tp_size > 1 && tp_rank == 0) tp_init(f, o); // creates the other shards, the communicators and the fused decode kernels' phase lists
 }
 
 Model::~Model() {
@@ -208,6 +243,9 @@ Model::~Model() {
     if (stream) cudaStreamSynchronize(stream);
     for (auto g : decode_graphs_)
         if (g) cudaGraphExecDestroy(g);
+    tp_destroy(); // joins the shard threads and frees the other shards first
+    if (tp_done_) cudaEventDestroy(tp_done_);
+    if (tp_in_) cudaEventDestroy(tp_in_);
     for (void *p : allocs_) cudaFree(p);
     for (auto e : mega_ev_) cudaEventDestroy(e);
     mega_streams_.free();
@@ -226,6 +264,7 @@ void Model::ensure_logits_rows(int n) {
     logits_ = nullptr;
     B2_CUDA(cudaMalloc((void **)&logits_, (size_t)n * hp.n_vocab * 4));
     logits_rows_cap_ = n;
+    B2_CHECK(tp_size == 1 || !mega_phases_, B2_ESTATE, "tensor-parallel shard: the logits rows are fixed");
     if (mega_phases_) build_mega(); // the LM-head phase holds the logits pointer
     for (auto &g : decode_graphs_) { // captured graphs hold the old logits pointer
         if (g) cudaGraphExecDestroy(g);
@@ -703,6 +742,10 @@ void Model::forward(const Batch &b) {
         B2_CHECK(b.pos[i] >= 0 && b.pos[i] < n_ctx_slot, B2_EINVAL, "position exceeds the slot's context");
         if (b.tokens) B2_CHECK(b.tokens[i] >= 0 && b.tokens[i] < hp.n_vocab, B2_EINVAL, "token id out of range");
     }
+    if (tp_size > 1) {
+        forward_tp(b);
+        return;
+    }
     if (b.tokens) B2_CUDA(cudaMemcpyAsync(tok_, b.tokens, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaMemcpyAsync(pos_, b.pos, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaMemcpyAsync(slot_, b.slot, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
@@ -726,7 +769,7 @@ void Model::forward(const Batch &b) {
 }
 
 void Model::set_device_inputs(const int32_t *tokens, const int32_t *pos, const int32_t *slot, int n) {
-    B2_CUDA(cudaSetDevice(device));
+    B2_CUDA(cudaSetDevice(device)); // (a tensor-parallel model: shard 0's buffers; forward_device_inputs hands them to the other shards)
     B2_CUDA(cudaMemcpyAsync(tok_, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaMemcpyAsync(pos_, pos, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
     B2_CUDA(cudaMemcpyAsync(slot_, slot, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
@@ -734,6 +777,10 @@ void Model::set_device_inputs(const int32_t *tokens, const int32_t *pos, const i
 
 void Model::forward_device_inputs(int n) {
     B2_CUDA(cudaSetDevice(device));
+    if (tp_size > 1) {
+        forward_device_inputs_tp(n);
+        return;
+    }
     runs_.clear();
     run_decode_graphed(n);
 }

@@ -36,9 +36,15 @@ struct Batch {
     int n_out = 0;
 };
 
+struct TPGroup; // tp.cu: the shards of one tensor-parallel model, their NCCL communicators and worker threads
+
 class Model {
   public:
-    Model(const GGUFFile &f, const b2_load_opts &o);
+    // tp_size > 1: this object is shard `tp_rank` of a tensor-parallel model on device o.device + tp_rank (SURVEY.md 8e
+    // row 2): column-parallel wq|wk|wv|gate|up|output (rows tp_rank * R/tp .. of each), row-parallel wo|down (the
+    // K-slice that multiplies this shard's heads / ffn rows), n_head_kv / tp KV heads, everything else replicated.
+    // Shard 0, created with o.tp_size, creates and drives the others.
+    Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank = 0, int tp_size = 0);
     ~Model();
     Model(const Model &) = delete;
 
@@ -65,7 +71,9 @@ class Model {
     void enable_debug_hidden();
     int bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type);
 
-    HParams hp;
+    HParams hp;          // of the whole model (global head counts and widths, also in a tensor-parallel shard)
+    int tp_size = 1, tp_rank = 0;
+    int nh_l = 0, nkv_l = 0, ff_l = 0, dq_l = 0, kvd_l = 0, vocab_l = 0; // this shard's heads, KV heads, ffn rows, q width, KV width, LM-head rows
     int n_ctx = 0, n_ctx_slot = 0, n_parallel = 1, n_batch = 512, page_size = 32, max_pages = 0;
     int device = 0;
     int64_t weight_bytes = 0, decode_stream_bytes = 0, kv_bytes_per_pos = 0;
@@ -74,8 +82,37 @@ class Model {
     std::vector<LayerW> layers;
     DTensor tok_embd, output_norm, output;
 
+    // tensor-parallel hooks (tp.cu)
+    enum TPMode { TP_NCCL = 0, TP_FUSED = 1 };
+    void tp_set_mode(int mode);      // TP_NCCL: per-layer kernels + ncclAllReduce; TP_FUSED: persistent kernels that exchange partial rows over peer memory
+    double tp_last_allreduce_ms = 0; // TP_NCCL: time inside the all-reduces of the last forward, measured with events on shard 0
+    int tp_n_allreduce = 0;          // all-reduces per decode step
+    void tp_timing(bool on);
+    double tp_allreduce_ms();
+    void tp_sync();
+    int tp_mode() const { return tp_mode_; }
+
   private:
-    DTensor upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required);
+    friend struct TPGroup;
+    TPGroup *tp_ = nullptr;          // shard 0 only
+    void tp_destroy();
+    Model *tp_root_ = nullptr;       // shards > 0: shard 0
+    int tp_mode_ = TP_FUSED;
+    float *xp_ = nullptr;            // [n_batch][n_embd] partial output of the row-parallel mat-muls (input of the all-reduce)
+    void tp_init(const GGUFFile &f, const b2_load_opts &o);
+    void tp_build_fused();                               // phase lists + weight streams of the fused decode kernels, all shards
+    bool tp_fused_ready_ = false;
+    uint2 *tp_part_[2] = {nullptr, nullptr};             // [tp_size][n_embd] LL words: the shards' partial rows (attn_output / ffn_down alternate)
+    cudaEvent_t tp_done_ = nullptr, tp_in_ = nullptr;
+    void forward_tp(const Batch &b);
+    void forward_device_inputs_tp(int n);
+    void tp_step(int n, int t0, int out_row0);           // forward of tokens [t0, t0 + n) on THIS shard (called on its worker thread)
+    void run_layer_tp(const LayerW &L, const KVLayout &kv, int n, int t0);
+    void run_decode_mega_tp(int t0, int out_row0);
+    void tp_allreduce(int t0, int n);                    // xp_ -> x_ (sum over the shards)
+    // column / K slices of a tensor: rows [row0, row0 + nrows) x columns [col0, col0 + ncols) (col ranges on block boundaries)
+    DTensor upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required,
+                   int64_t row0 = 0, int64_t nrows = -1, int64_t col0 = 0, int64_t ncols = -1);
     void quantize_for(const DTensor &W, const float *x, int64_t x_stride, int n, uint8_t **out, ActFmt *fmt);
     void matmul(const DTensor &W, const float *x, int64_t x_stride, int n, float *out, int64_t out_stride,
                 const float *residual, int64_t res_stride);

@@ -19,8 +19,8 @@ stall_cols = [i for i, h in enumerate(hdr) if h.startswith('stall_') and 'Not Is
 src = open(src_path).read().split('\n')
 def find(s): return [i + 1 for i, l in enumerate(src) if s in l][0]
 marks = sorted([(1, "prims"), (find("struct MgLane {"), "dots"), (find("float mg_row_sum"), "reduce"),
-    (find("__device__ __noinline__ void mg_attention("), "attention-1cta"), (find("void mg_attention_split("), "attention-split"),
-    (find("void mg_prefetch_kv("), "kv-prefetch"), (find("void mg_quant_block_global("), "dist-quant"), (find("void mg_prologue("), "prologue fn"),
+    (find("void mg_attention_ll("), "attention"),
+    (find("void mg_prefetch_kv("), "kv-prefetch"), (find("void mg_quant_block_ll("), "dist-quant"), (find("void mg_copy_xq("), "xq copy"), (find("void mg_prologue("), "prologue fn"),
     (find("decode_mega_kernel(const MegaArgs a)"), "kernel init + boundary copy"), (find("for (int p = 0; p < a.n_phases; p++) {"), "phase head"),
     (find("// ---- this lane's slice of the quantised row"), "slice"), (find("// ---- this warp's tiles of the phase"), "tile loop"),
     (find("// ---- epilogue: combine the K-split partials"), "epilogue"), (find("// ---- phase boundary"), "boundary")])

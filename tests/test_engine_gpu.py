@@ -407,3 +407,35 @@ def test_replica_pool_over_real_devices(model_files):
         assert pool.load() == [0] * n_dev
     finally:
         pool.close()
+
+
+def test_top_k_gather_with_masked_logits_and_large_ties():
+    """The top-k candidate gather when fewer than K logits are finite (a grammar mask) or many are tied at the K-th value:
+    masked (-inf) tokens are never candidates, allowed tokens with HIGH ids are not crowded out of the on-chip buffer
+    (the vocabulary is larger than it), and a tie is resolved towards the lowest ids, deterministically."""
+    n_vocab = 16384  # > the 2048-entry candidate buffer
+    rng = np.random.default_rng(12)
+    allowed = np.sort(rng.choice(np.arange(12000, n_vocab), 7, replace=False))
+    logits = np.full(n_vocab, -np.inf, dtype=np.float32)
+    logits[allowed] = rng.standard_normal(7).astype(np.float32)
+    toks, _ = capi.sample(logits, n_draws=400, temperature=1.0, top_k=40, top_p=1.0, seed=5)
+    assert set(toks.tolist()) <= set(allowed.tolist())
+    assert len(set(toks.tolist())) >= 5  # the draw really ranges over the allowed set
+    p = np.exp(logits[allowed] - logits[allowed].max())
+    p /= p.sum()
+    freq = np.array([(toks == a).mean() for a in allowed])
+    assert np.abs(freq - p).max() < 0.08
+    # one allowed token: always that one
+    one = np.full(n_vocab, -np.inf, dtype=np.float32)
+    one[n_vocab - 3] = 0.5
+    toks, _ = capi.sample(one, n_draws=16, temperature=0.7, top_k=40, top_p=0.95, seed=1)
+    assert (toks == n_vocab - 3).all()
+    # a tie across the whole vocabulary at the K-th value: the K lowest ids, every run
+    flat = np.zeros(n_vocab, dtype=np.float32)
+    a, _ = capi.sample(flat, n_draws=300, temperature=1.0, top_k=40, top_p=1.0, seed=9)
+    b, _ = capi.sample(flat, n_draws=300, temperature=1.0, top_k=40, top_p=1.0, seed=9)
+    assert a.max() < 40 and np.array_equal(a, b) and len(set(a.tolist())) > 30
+    # two values above a big tie: both kept, the rest of K filled from the tie in id order
+    flat[[9000, 15000]] = 3.0
+    c, _ = capi.sample(flat, n_draws=400, temperature=1.0, top_k=10, top_p=1.0, seed=3)
+    assert set(c.tolist()) <= set(range(8)) | {9000, 15000} and {9000, 15000} <= set(c.tolist())

@@ -119,7 +119,7 @@ def test_predict_stream_embedding_grammar_metrics(backend, model_files):
     # Embedding: one text -> one vector of n_embd floats, the same for the same input (core/http/app_test.go:856-881)
     e1 = backend.Embedding(pb.PredictOptions(Embeddings="hello world"))
     e2 = backend.Embedding(pb.PredictOptions(Embeddings="hello world"))
-    assert len(e1.embeddings) == 256 and list(e1.embeddings) == list(e2.embeddings)
+    assert len(e1.embeddings) == 512 and list(e1.embeddings) == list(e2.embeddings)  # n_embd of the mini model
     assert np.isfinite(np.asarray(e1.embeddings)).all()
     # Grammar (backend.proto:98; every tools / function-call request carries one): the output fits the grammar
     g = 'root ::= ("yes" | "no") " " [0-9]+'

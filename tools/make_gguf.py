@@ -72,7 +72,7 @@ ARCHS = {
     "micro": Arch("micro", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm"),
     "mini": Arch("mini", 3, 512, 8, 2, 1024, 4608, 1024, 500000.0, 1e-5, "bpe"),
     "small": Arch("small", 8, 1024, 16, 4, 2816, 8192, 1024, 500000.0, 1e-5, "bpe"),          # deeper: error growth over 8 layers
-    "mini-70b": Arch("mini-70b", 4, 1024, 16, 8, 3584, 8192, 1024, 500000.0, 1e-5, "bpe", True),  # 70B type mix (Q5_K attn_v), 8 KV heads
+    "mini-70b": Arch("mini-70b", 4, 2048, 16, 8, 4096, 8192, 1024, 500000.0, 1e-5, "bpe", True),  # 70B type mix (Q5_K attn_v), 8 KV heads; shards 2 / 4 / 8 ways
     # BASELINE.json configs
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 5632, 32000, 2048, 10000.0, 1e-5, "spm"),
     "llama3-8b": Arch("llama3-8b", 32, 4096, 32, 8, 14336, 128256, 8192, 500000.0, 1e-5, "bpe"),
