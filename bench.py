@@ -327,6 +327,57 @@ def bench_pool(path, rank, world, ranks):
 
 
 
+def bench_70b_one_gpu(peak):
+    """Llama-3-70B-arch Q4_K_M batch-1 decode on ONE GPU (the baseline of the tensor-parallel scaling curve)."""
+    from localai_b200 import capi
+
+    path, _ = ensure_model("llama3-70b", "q4_k_m", 0, 0, lambda: None)
+    with capi.Engine(path, n_ctx=512, n_batch=32, n_parallel=1, device=0) as e:
+        ms, launches = e.bench_decode(1, 128, 32, 3)
+        b = e.info.decode_stream_bytes + e.info.kv_bytes_per_pos * 128
+        return {"metric": "Llama-3-70B Q4_K_M decode tok/s (b=1)", "tp": 1,
+                "one_gpu": {"tok_s": 1e3 / ms, "ms_per_step": ms, "hbm_frac": b / (ms * 1e-3) / 1e9 / peak, "launches_per_step": launches}}
+
+
+def bench_tp70b(rank, world, ranks, peak, with_one_gpu=True):
+    """BASELINE configs[4]: Llama-3-70B-arch Q4_K_M, batch-1 decode, ONE engine sharded over the N devices (tensor
+    parallel: column-parallel wq|wk|wv|gate|up|output, row-parallel wo|down, the partial rows summed after attn_output
+    and ffn_down) -- driven by rank 0 alone, the other ranks wait at the barrier.  Both exchange modes are timed: per-layer
+    kernels + ncclAllReduce (what north_star names; the time inside the collectives is reported separately) and the
+    persistent kernels that store their partial rows into the peers' memory.  The one-GPU number is the scaling baseline."""
+    out = None
+    ranks.barrier()
+    if rank == 0:
+        from localai_b200 import capi
+
+        path, _ = ensure_model("llama3-70b", "q4_k_m", 0, 0, lambda: None)
+        out = {"metric": "Llama-3-70B Q4_K_M decode tok/s (b=1), tensor-parallel", "tp": world}
+        ctx, steps = 128, 32
+        if with_one_gpu:
+            try:
+                with capi.Engine(path, n_ctx=512, n_batch=32, n_parallel=1, device=0) as e:
+                    ms, _ = e.bench_decode(1, ctx, steps, 3)
+                    b = e.info.decode_stream_bytes + e.info.kv_bytes_per_pos * ctx
+                    out["one_gpu"] = {"tok_s": 1e3 / ms, "ms_per_step": ms, "hbm_frac": b / (ms * 1e-3) / 1e9 / peak}
+            except Exception as ex:  # noqa: BLE001
+                out["one_gpu"] = {"error": str(ex)}
+        with capi.Engine(path, n_ctx=512, n_batch=32, n_parallel=1, device=0, tp_size=world) as e:
+            for mode, name in ((capi.B2_TP_NCCL, "nccl"), (capi.B2_TP_FUSED, "fused")):
+                try:
+                    e.tp_set_mode(mode)
+                    ms, launches = e.bench_decode(1, ctx, steps, 3)
+                    info = e.tp_info()
+                    b = info["shard_stream_bytes"] + e.info.kv_bytes_per_pos * ctx  # per GPU
+                    out[name] = {"tok_s": 1e3 / ms, "ms_per_step": ms, "hbm_frac_per_gpu": b / (ms * 1e-3) / 1e9 / peak,
+                                 "n_allreduce": info["n_allreduce_per_step"], "launches_per_step": launches}
+                    if mode == capi.B2_TP_NCCL:
+                        out[name]["allreduce_us_per_token"] = info["allreduce_ms_per_step"] * 1e3
+                except Exception as ex:  # noqa: BLE001
+                    out[name] = {"error": str(ex)}
+    ranks.barrier()
+    return out
+
+
 def run_bert(args, rank, local_rank, world, ranks, emit, warmup):
     """BASELINE config 4: BERT-base F16, texts of 512 WordPiece tokens, through b2_bert_embed_batch (host ids in, host
     vectors out -- the call is synchronous, so every timed step holds its own H2D and D2H copies).  A step = one call
@@ -420,6 +471,7 @@ def main():
     ap.add_argument("--prefill", type=int, default=2048)
     ap.add_argument("--batch", type=int, default=64, help="concurrent streams for the batched-decode extra")
     ap.add_argument("--no-extras", action="store_true", help="skip the b=64 / prefill / cpu legs")
+    ap.add_argument("--with-70b", action="store_true", help="N = 1: also time Llama-3-70B Q4_K_M b=1 decode on the one GPU (a 42.5 GB file is generated)")
     ap.add_argument("--workload", default="decode", choices=["decode", "bert"],
                     help="decode: the headline (Llama-3-8B Q4_K_M b=1 decode); bert: BASELINE config 4, BERT-base F16 embeddings of 512-token texts")
     args = ap.parse_args()
@@ -582,6 +634,11 @@ def main():
                 extra["pool"] = bench_pool(path, rank, world, ranks)
             except Exception as ex:  # noqa: BLE001
                 extra["pool"] = {"error": str(ex)}
+        if world > 1 or args.with_70b:
+            try:
+                extra["tp70b"] = bench_tp70b(rank, world, ranks, peak) if world > 1 else bench_70b_one_gpu(peak)
+            except Exception as ex:  # noqa: BLE001
+                extra["tp70b"] = {"error": str(ex)}
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,

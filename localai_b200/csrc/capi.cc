@@ -258,9 +258,12 @@ int64_t b2_mega_plan_check(const int64_t *desc, int n_phases, int n_cta, int64_t
         m.fmt = act_format_for(m.job[0].type);
         m.units = (int)(m.kind == PH_SWIGLU ? m.job[0].rows : rows / 2);
         if (m.kind == PH_PLAIN && m.K / 256 > 32 && m.K <= 32768) m.xq_ll = (uint2 *)16; // as Model::build_mega: quantised once per GPU
-        B2_CHECK(mega_phase_prepare(m, n_cta), B2_EUNSUPPORTED, "phase " + std::to_string(p) + ": no lane mapping for this shape/type");
     }
-    return mega_plan_check(ph.data(), n_phases, n_cta, n_tiles);
+    const MegaGeo geo = mega_geometry(ph.data(), n_phases, 2048, 128);
+    for (int p = 0; p < n_phases; p++)
+        if (ph[(size_t)p].kind != PH_ATT)
+            B2_CHECK(mega_phase_prepare(ph[(size_t)p], n_cta, geo), B2_EUNSUPPORTED, "phase " + std::to_string(p) + ": no lane mapping for this shape/type");
+    return mega_plan_check(ph.data(), n_phases, n_cta, n_tiles, geo);
     B2_API_END(0)
 }
 
@@ -376,14 +379,18 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
         ph.x = dx.as<float>(); ph.out = dout.as<float>(); ph.units = (int)(rows / 2);
         int n_sm = 0;
         B2_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0));
-        B2_CHECK(mega_phase_prepare(ph, n_sm), B2_EUNSUPPORTED, "mega path: shape/type not supported");
+        const MegaGeo geo = mega_geometry(&ph, 1, 64, 64);
+        B2_CHECK(mega_phase_prepare(ph, n_sm, geo), B2_EUNSUPPORTED, "mega path: shape/type not supported");
         MegaStreams ms;
-        ms.build(&ph, 1, n_sm, 0);
+        ms.build(&ph, 1, n_sm, 0, geo);
         struct Guard { MegaStreams &m; ~Guard() { m.free(); } } guard{ms};
         DevBuf dph(sizeof(MegaPhase)), dps(64);
         B2_CUDA(cudaMemcpy(dph.p, &ph, sizeof(ph), cudaMemcpyHostToDevice));
         B2_CUDA(cudaMemset(dps.p, 0, 64));
         MegaArgs a;
+        a.geo = geo;
+        mega_fill_knobs(a);
+        a.hint = dps.as<unsigned>() + 8; // (a single phase never waits on it)
         a.phases = dph.as<MegaPhase>(); a.n_phases = 1; a.starts = ms.starts; a.pos = dps.as<int32_t>(); a.slot = dps.as<int32_t>() + 4;
         a.page_size = 32; a.page_shift = 5; a.max_pages = 1; a.hd = 64; a.n_head = 1; a.n_head_kv = 1;
         launch_decode_mega(a, n_sm, 0);

@@ -144,7 +144,21 @@ struct MegaStreamStart {
     uint32_t total = 0;            // bytes of the whole stream
     int32_t pad[2] = {0, 0};
 };
+// Shared-memory geometry of the decode kernel, chosen per model at load (mega_geometry): the activation row / attention
+// scratch takes what the model's longest row and context need, the weight rings get the rest of the 227 KB.
+struct MegaGeo {
+    int stage_bytes = 9232; // one ring stage: 16-byte tile header + tile data (multiple of 16); 2 stages per warp
+    int xs_bytes = 34816;   // quantised activation row (and, together with the partial sums, the attention scratch)
+};
+MegaGeo mega_geometry(const struct MegaPhase *phases, int n_phases, int n_ctx_slot, int hd); // declared below
 struct MegaArgs {
+    MegaGeo geo;
+    int ll_poll_ns = 32;     // sleep between two polls of an LL word (B200LLM_LL_POLL_NS)
+    int ll_probe = 2;        // how a CTA waits for its input row before loading it (B200LLM_LL_PROBE): 0 = every warp polls its slice,
+                             // 1 = one warp polls a sample of the row, 2 = one thread polls the phase counter `hint`
+    unsigned *hint = nullptr; // phase counter: every CTA adds 1 (relaxed, no fence: the tags stay the proof) when it has stored a phase's outputs
+    unsigned hint_base = 0;   // its value when this launch starts; the host adds n_cta * n_phases per launch
+    unsigned l2_ahead = 0;   // bytes of its stream every warp keeps requested into L2 beyond its ring (B200LLM_MEGA_L2_AHEAD; 0: off)
     const MegaPhase *phases = nullptr; // device
     int n_phases = 0;
     const MegaStreamStart *starts = nullptr; // device, [n_cta][warps per CTA]
@@ -166,8 +180,9 @@ struct MegaArgs {
     long long *dbg = nullptr; // optional [n_cta][n_phases][16] clock64 stamps and per-phase cycle counts (scratch/mega_dbg.py)
 };
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s);
-bool mega_phase_prepare(MegaPhase &ph, int n_cta); // fills the lane geometry; false = shape/type the kernel has no mapping for
+bool mega_phase_prepare(MegaPhase &ph, int n_cta, const MegaGeo &geo = MegaGeo()); // fills the lane geometry; false = shape/type the kernel has no mapping for
 bool mega_phase_supported(const MegaPhase &ph);
+void mega_fill_knobs(MegaArgs &a); // the environment's tuning knobs
 // The weights of a phase list, repacked into one contiguous byte stream per (CTA, warp) in the order that warp
 // consumes them: tile = [16-byte header][n row-splits x rb bytes].  Built once per model (device-side scatter from the
 // GGUF-layout rows); the decode kernel then needs no schedule arithmetic, only "copy the next tile of my stream".
@@ -177,13 +192,13 @@ struct MegaStreams {
     MegaStreamStart *starts = nullptr; // device
     int64_t n_tiles = 0;
     // phases: prepared (mega_phase_prepare) host copies.  Allocates with cudaMalloc; free() releases.
-    void build(const MegaPhase *phases, int n_phases, int n_cta, cudaStream_t s);
+    void build(const MegaPhase *phases, int n_phases, int n_cta, cudaStream_t s, const MegaGeo &geo = MegaGeo());
     void free();
 };
 // host-only: plan the streams of a phase list and replay every warp's walk (throws b2::Error on an inconsistency);
 // returns the stream bytes.  Needs no device: the unit test of the planner (tests/test_capi_cpu.py).
-int64_t mega_plan_check(const MegaPhase *phases, int n_phases, int n_cta, int64_t *n_tiles);
-size_t mega_attention_ctx_limit(int hd);
+int64_t mega_plan_check(const MegaPhase *phases, int n_phases, int n_cta, int64_t *n_tiles, const MegaGeo &geo = MegaGeo());
+size_t mega_attention_ctx_limit(int hd, const MegaGeo &geo = MegaGeo());
 
 // --- tensor-core GEMM for prefill / batched decode (kernels_gemm.cu) ----------------------------------------------
 size_t gemm_w_tiles_bytes(int64_t rows, int64_t cols);

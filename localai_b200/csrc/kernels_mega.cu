@@ -36,38 +36,32 @@ namespace b2 {
 
 constexpr int MG_WARPS = 8;
 constexpr int MG_THREADS = MG_WARPS * 32;
-// ring geometry (overridable at build time for A/B measurements: make VARIANT=...)
-#ifndef B2_MG_STAGES
-#define B2_MG_STAGES 2
-#endif
-#ifndef B2_MG_TILE_DATA
-#define B2_MG_TILE_DATA 9216
-#endif
-#ifndef B2_MG_XS_KB
-#define B2_MG_XS_KB 34
-#endif
-constexpr int MG_STAGES = B2_MG_STAGES;      // per warp
+constexpr int MG_STAGES = 2;                 // per warp
 constexpr int MG_TILE_HDR = 16;              // tile header, in-band
-constexpr int MG_TILE_DATA = B2_MG_TILE_DATA; // weight bytes of a tile, at most
-constexpr int MG_STAGE_BYTES = MG_TILE_HDR + MG_TILE_DATA;
-constexpr int MG_RING_BYTES = MG_WARPS * MG_STAGES * MG_STAGE_BYTES;
-constexpr int MG_XS_BYTES = B2_MG_XS_KB * 1024; // quantised activation row, K <= 28672 at 34 KB (attention: scratch, together with the partials)
 constexpr int MG_MAX_PART = 2048;            // per-phase partial sums: rows of this CTA x K-splits
 constexpr int MG_PB = 8;                     // prologue: 256-element blocks a warp holds in registers (K <= 16384)
 constexpr int MG_MAX_PASS = 8;               // warp passes per tile
-
-constexpr size_t MG_OFF_XS = MG_RING_BYTES;
-constexpr size_t MG_OFF_PART = MG_OFF_XS + MG_XS_BYTES;
-constexpr size_t MG_OFF_RED = MG_OFF_PART + MG_MAX_PART * sizeof(float);
-constexpr size_t MG_OFF_BAR = MG_OFF_RED + 32 * sizeof(double);
 constexpr int MG_MAX_PAGES = 512;            // page-table entries of the sequence kept in shared memory
 constexpr int MG_PH_WIN = 3;                 // phase descriptors kept in shared memory: phases p - 1, p, p + 1
-constexpr size_t MG_OFF_PH = MG_OFF_BAR + MG_WARPS * MG_STAGES * sizeof(uint64_t);
-constexpr size_t MG_OFF_PT = MG_OFF_PH + MG_PH_WIN * ((sizeof(MegaPhase) + 15) / 16 * 16);
-constexpr size_t MG_SMEM = MG_OFF_PT + MG_MAX_PAGES * sizeof(int);
+constexpr int MG_PH_SLOT = (int)((sizeof(MegaPhase) + 15) / 16 * 16);
+constexpr int MG_SMEM_MAX = 227 * 1024;
 static_assert(sizeof(MegaPhase) % 4 == 0, "MegaPhase is copied word by word");
-static_assert(MG_SMEM <= 227 * 1024, "mega-kernel shared memory");
-static_assert(MG_STAGE_BYTES % 16 == 0 && MG_OFF_XS % 16 == 0, "bulk copies need 16-byte aligned stages");
+// Shared memory: [rings: 8 warps x 2 stages][activation row / attention scratch][partial sums][reduction scratch][mbarriers]
+// [phase descriptors][page table].  The first two are sized per model (MegaGeo).
+struct MgSmem {
+    uint32_t xs, part, red, bar, ph, pt, total;
+};
+__host__ __device__ inline MgSmem mg_smem_layout(const MegaGeo &g) {
+    MgSmem l;
+    l.xs = (uint32_t)(MG_WARPS * MG_STAGES * g.stage_bytes);
+    l.part = l.xs + (uint32_t)g.xs_bytes;
+    l.red = l.part + MG_MAX_PART * (uint32_t)sizeof(float);
+    l.bar = l.red + 32 * (uint32_t)sizeof(double);
+    l.ph = l.bar + MG_WARPS * MG_STAGES * (uint32_t)sizeof(uint64_t);
+    l.pt = l.ph + MG_PH_WIN * MG_PH_SLOT;
+    l.total = l.pt + MG_MAX_PAGES * (uint32_t)sizeof(int);
+    return l;
+}
 constexpr long long MG_WATCHDOG = 40000000000ll; // cycles (~20 s) after which a wait gives up and traps instead of hanging the GPU
 
 // ------------------------------------------------------------------------------------------------ geometry
@@ -105,15 +99,15 @@ inline bool mg_split(int fmt, int64_t K, bool pre_quantised, int &S, int &lpr, i
 // Tile geometry of one matrix: rb = bytes of one row's K-split inside a tile (= the row pitch), R = rows per tile.
 //   Q4_K / Q5_K: the K-split's blocks.  Q6_K: its 208-byte blocks, then its fp16 super-block scales (padded to 16).
 //   Q8_0: its int8 range, then its fp16 block scales.
-inline bool mg_job_geo(int type, int64_t K, int S, int rpp, int &rb, int &R) {
+inline bool mg_job_geo(int type, int64_t K, int S, int rpp, int tile_data, int &rb, int &R) {
     const int64_t nbs = K / 256 / S;
     if (type == B2_T_Q4_K) rb = (int)(144 * nbs);
     else if (type == B2_T_Q5_K) rb = (int)(176 * nbs);
     else if (type == B2_T_Q6_K) rb = (int)(Q6_BLK * nbs + (2 * nbs + 15) / 16 * 16);
     else if (type == B2_T_Q8_0) rb = (int)(K / S + K / S / 16);
     else return false;
-    if (rb <= 0 || rb % 16 || rb > MG_TILE_DATA) return false;
-    R = MG_TILE_DATA / rb;
+    if (rb <= 0 || rb % 16 || rb > tile_data) return false;
+    R = tile_data / rb;
     if (R > MG_MAX_PASS * rpp) R = MG_MAX_PASS * rpp;
     R = R / rpp * rpp;
     if (rpp == 1) { // the row loops work on groups of 2 rows with a merged reduction
@@ -155,6 +149,11 @@ __device__ __forceinline__ void mg_bulk(uint32_t dst, const void *src, uint32_t 
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
                  "r"(bytes), "r"(bar)
                  : "memory");
+}
+__device__ __forceinline__ long long mg_gtime() { // nanoseconds, one clock for all SMs (profiling build only)
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
 }
 // ask for [p, p + bytes) to be brought into L2 (fire and forget; 16-byte granularity)
 __device__ __forceinline__ void mg_prefetch_l2(const void *p, uint32_t bytes) {
@@ -217,13 +216,26 @@ __device__ __forceinline__ uint32_t ll_tag(unsigned long long w) { return (uint3
 __device__ __forceinline__ float ll_val(unsigned long long w) { return __uint_as_float((uint32_t)w); }
 // Spin budget of every LL wait: a wait that long is a bug (a producer that never ran), and traps instead of hanging.
 constexpr unsigned MG_SPIN_LIMIT = 1u << 27;
-__device__ unsigned g_mega_l2_ahead = 32768; // B200LLM_MEGA_L2_AHEAD: bytes of its weight stream every warp keeps requested into L2 beyond its ring (0: off)
-__device__ unsigned g_ll_probe = 1;   // B200LLM_LL_PROBE=0: no light probe before the full-slice poll
-__device__ unsigned g_ll_poll_ns = 32; // B200LLM_LL_POLL_NS (tuning knob): sleep between two polls of an LL word
+__constant__ unsigned g_ll_poll_ns = 32; // sleep between two polls of an LL word (set per launch from MegaArgs.ll_poll_ns when it changes)
 __device__ __forceinline__ void ll_backoff(unsigned &spins) {
     const unsigned ns = g_ll_poll_ns;
     if (ns) __nanosleep(ns);
     if (++spins > MG_SPIN_LIMIT) __trap();
+}
+// The phase counter: a HINT that lets a CTA wait quietly.  Every CTA adds 1 after storing a phase's outputs -- a relaxed
+// reduction, not ordered against those stores -- and a consumer's thread 0 polls the one word until all CTAs of the
+// producing phase have added theirs; only then do its warps load the row.  The LL tags remain the proof that a word is
+// there: a word that lags behind the counter is simply polled again.
+__device__ __forceinline__ void mg_hint_arrive(unsigned *cnt) {
+    asm volatile("red.relaxed.gpu.global.add.u32 [%0], 1;" ::"l"(cnt) : "memory");
+}
+__device__ __forceinline__ void mg_hint_wait(const unsigned *cnt, unsigned target) {
+    unsigned v, spins = 0;
+    while (true) {
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(cnt) : "memory");
+        if ((int)(v - target) >= 0) return;
+        ll_backoff(spins);
+    }
 }
 // one word, polled by one thread until it carries `tag`
 __device__ __forceinline__ float ll_wait(const uint2 *p, uint32_t tag) {
@@ -717,7 +729,7 @@ __device__ __noinline__ void mg_copy_xq(const uint2 *xq_ll, uint32_t tag, int64_
 // quantize_row_q8_K_ref / quantize_row_q8_0_ref (act_quant.cuh holds the same arithmetic for the other kernels).
 template <int PBN>
 __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, float eps, uint8_t *xs, double *s_part, int nb, int k_first,
-                                         int warp, int lane, float *xn_out) {
+                                         int warp, int lane, float *xn_out, bool probe) { // probe: warp 0 polls a sample of the row first
     const bool write_xn = xn_out != nullptr;
     const int64_t K = ph.K;
     const bool has_norm = ph.norm_w != nullptr;
@@ -746,19 +758,22 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, f
             v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
         }
     } else {
-        // LL words written by phase src_p, possibly still on their way.  First a light probe -- one word per lane and
-        // block, 8 elements apart, so every producer CTA (each owns >= 8 consecutive rows) has a word in the sample --
-        // then the whole slice; the probe keeps the polling traffic of early CTAs off the L2 that streams the weights.
+        // LL words written by phase src_p, possibly still on their way.  ONE warp waits for them: it polls a sample of the
+        // row -- every 16th word, so every producer CTA (each owns >= 16 consecutive rows of a model this kernel is meant
+        // for; the full check below does not depend on it) has a word in the sample -- while the other warps sleep at the
+        // barrier instead of spinning beside the warps of other phases' weight streams.  Then every warp loads its slice.
         unsigned spins = 0;
-        while (g_ll_probe) {
-            bool ok = true;
-#pragma unroll
-            for (int k = 0; k < PBN; k++) {
-                const int b = warp + (k_first + k) * MG_WARPS;
-                ok = ok && ll_tag(ll_ld(ph.x_ll + (valid[k] ? b : 0) * 256 + lane * 8 + 7)) == tag_in;
+        if (probe) {
+            if (warp == 0) {
+                const int n_s = (int)(K >> 4);
+                while (true) {
+                    bool ok = true;
+                    for (int i = lane; i < n_s; i += 32) ok = ok && ll_tag(ll_ld(ph.x_ll + i * 16 + 15)) == tag_in;
+                    if (__all_sync(0xffffffffu, ok)) break;
+                    ll_backoff(spins);
+                }
             }
-            if (__all_sync(0xffffffffu, ok)) break;
-            ll_backoff(spins);
+            __syncthreads();
         }
         while (true) {
             bool ok = true;
@@ -896,26 +911,29 @@ template <bool DBG>
 __global__ void __launch_bounds__(MG_THREADS, 1)
 decode_mega_kernel(const MegaArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *xs = smem + MG_OFF_XS;
-    float *partial = (float *)(smem + MG_OFF_PART);
-    double *s_part = (double *)(smem + MG_OFF_RED);
-    uint64_t *bars = (uint64_t *)(smem + MG_OFF_BAR);
+    const MgSmem lay = mg_smem_layout(a.geo);
+    const uint32_t stage_bytes = (uint32_t)a.geo.stage_bytes;
+    uint8_t *xs = smem + lay.xs;
+    float *partial = (float *)(smem + lay.part);
+    double *s_part = (double *)(smem + lay.red);
+    uint64_t *bars = (uint64_t *)(smem + lay.bar);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int cta = blockIdx.x, n_cta = gridDim.x;
 
-    MegaPhase *sph = (MegaPhase *)(smem + MG_OFF_PH);
+    MegaPhase *sph = (MegaPhase *)(smem + lay.ph);
     constexpr int PH_WORDS = (int)(sizeof(MegaPhase) / 4);
     static_assert(PH_WORDS <= MG_THREADS, "phase descriptor copy");
+    static_assert(MG_PH_SLOT % 16 == 0, "phase slots");
     // Phase p's descriptor sits in slot p % 3.  It is copied in during phase p - 2, right after that phase's mid-phase
     // __syncthreads (every thread is then past phase p - 3, the slot's previous tenant), and first read after phase
     // p - 1's mid-phase __syncthreads.
     auto stage_phase = [&](int p) {
-        if (p < a.n_phases && tid < PH_WORDS) ((uint32_t *)&sph[p % MG_PH_WIN])[tid] = ((const uint32_t *)&a.phases[p])[tid];
+        if (p < a.n_phases && tid < PH_WORDS) ((uint32_t *)((uint8_t *)sph + (p % MG_PH_WIN) * MG_PH_SLOT))[tid] = ((const uint32_t *)&a.phases[p])[tid];
     };
     stage_phase(0);
     stage_phase(1);
     const int pos = a.pos[0], sl = a.slot[0];
-    int *pbase = (int *)(smem + MG_OFF_PT); // page of every 32-position block of this sequence (static during the step)
+    int *pbase = (int *)(smem + lay.pt); // page of every 32-position block of this sequence (static during the step)
     for (int i = tid; a.page_table && i < (pos + a.page_size) / a.page_size && i < MG_MAX_PAGES; i += MG_THREADS) pbase[i] = a.page_table[(int64_t)sl * a.max_pages + i];
     if (tid == 0) {
         for (int i = 0; i < MG_WARPS * MG_STAGES; i++) mg_mbar_init(bars + i, 1);
@@ -924,10 +942,10 @@ decode_mega_kernel(const MegaArgs a) {
     __syncthreads();
 
     // ---- this warp's ring and its weight stream: the first two tiles are requested right away
-    const uint32_t ring = mg_s32(smem) + warp * (MG_STAGES * MG_STAGE_BYTES);
+    const uint32_t ring = mg_s32(smem) + warp * (MG_STAGES * stage_bytes);
     const uint32_t bar0 = mg_s32(bars + warp * MG_STAGES);
     const uint8_t *src; // next tile to request into the ring
-    uint32_t rem;       // bytes of the stream from src on (the L2 prefetch front runs g_mega_l2_ahead bytes ahead of src)
+    uint32_t rem;       // bytes of the stream from src on (the L2 prefetch front runs a.l2_ahead bytes ahead of src)
     int next_p; // the next phase in which this warp has tiles
     {
         const MegaStreamStart st = a.starts[cta * MG_WARPS + warp];
@@ -935,23 +953,24 @@ decode_mega_kernel(const MegaArgs a) {
         next_p = st.first_p;
         if (lane == 0) {
             if (st.size0) { mg_expect_tx(bar0, st.size0); mg_bulk(ring, src, st.size0, bar0); }
-            if (st.size1) { mg_expect_tx(bar0 + 8, st.size1); mg_bulk(ring + MG_STAGE_BYTES, src + st.size0, st.size1, bar0 + 8); }
+            if (st.size1) { mg_expect_tx(bar0 + 8, st.size1); mg_bulk(ring + stage_bytes, src + st.size0, st.size1, bar0 + 8); }
         }
         src += st.size0 + st.size1;
         // Beyond the ring, the stream is kept requested into L2 a fixed distance ahead: while the CTA sits in the latency-bound
         // phases (QKV, attention, attn_output: a few MB of weights between many hand-overs) HBM keeps working on the rows
         // of the big phases that follow, and their ring refills then come from L2.
         rem = st.total - st.size0 - st.size1;
-        const uint32_t ahead = g_mega_l2_ahead;
+        const uint32_t ahead = a.l2_ahead;
         if (ahead && lane == 0 && rem) mg_prefetch_l2(src, min(ahead, rem));
     }
     uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
 
     for (int p = 0; p < a.n_phases; p++) {
-        const MegaPhase &ph = sph[p % MG_PH_WIN];
+        const MegaPhase &ph = *(const MegaPhase *)((const uint8_t *)sph + (p % MG_PH_WIN) * MG_PH_SLOT);
         const uint32_t tag_in = a.tag_base + (uint32_t)ph.src_p + 1u, tag_out = a.tag_base + (uint32_t)p + 1u;
         long long t0 = 0, t1 = 0, t2 = 0, t_wait = 0, t_comp = 0, t_epi = 0, n_tiles = 0, tp0 = 0, tp3 = 0, tl_end = 0;
-        if (DBG && tid == 0) t0 = clock64();
+        long long g0 = 0, g1 = 0, g2 = 0;
+        if (DBG && tid == 0) { t0 = clock64(); g0 = mg_gtime(); }
         int u = 0, u_end = 0;
         if (ph.kind == PH_ATT) {
             // a head is shared by att_parts CTAs (att_parts * n_head <= n_cta whenever att_parts > 1)
@@ -969,6 +988,11 @@ decode_mega_kernel(const MegaArgs a) {
                 __syncthreads();
                 stage_phase(p + 2);
             }
+        }
+        if (a.ll_probe == 2 && ph.kind != PH_ATT && ph.src_p >= 0 && u < u_end) {
+            // wait quietly until every CTA has stored the outputs of the producing phase (see mg_hint_arrive)
+            if (tid == 0) mg_hint_wait(a.hint, a.hint_base + ((unsigned)ph.src_p + 1u) * (unsigned)n_cta);
+            __syncthreads();
         }
         if (ph.kind != PH_ATT && ph.reduce_n > 0) {
             // Tensor parallelism: the input row is the sum of reduce_n partial rows, one from every shard (they arrive in
@@ -1017,10 +1041,10 @@ decode_mega_kernel(const MegaArgs a) {
                 mg_copy_xq(ph.xq_ll, tag_out, K, nb, xs, tid);
             } else {
                 float *wx = ph.xn_out && cta == 0 ? (a.xn_override ? a.xn_override : ph.xn_out) : nullptr;
-                if (nb <= MG_WARPS) mg_prologue<1>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
-                else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
+                if (nb <= MG_WARPS) mg_prologue<1>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx, a.ll_probe == 1);
+                else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx, a.ll_probe == 1);
                 else // 4 blocks per warp at a time; rows longer than 32 blocks have no norm (mega_phase_prepare)
-                    for (int k0 = 0; k0 * MG_WARPS < nb; k0 += 4) mg_prologue<4>(ph, tag_in, a.eps, xs, s_part, nb, k0, warp, lane, wx);
+                    for (int k0 = 0; k0 * MG_WARPS < nb; k0 += 4) mg_prologue<4>(ph, tag_in, a.eps, xs, s_part, nb, k0, warp, lane, wx, a.ll_probe == 1 && k0 == 0);
             }
             if (DBG && tid == 0) tp3 = clock64();
             if (ph.kind == PH_QKV) // the attention phase comes next: start its K/V rows on their way into L2
@@ -1068,12 +1092,12 @@ decode_mega_kernel(const MegaArgs a) {
                 if (ph.res_ll) res_pre = ll_val(ll_ld(ph.res_ll + u + tid));
                 else if (ph.residual) res_pre = __ldcg(ph.residual + u + tid);
             }
-            if (DBG && tid == 0) t1 = clock64();
+            if (DBG && tid == 0) { t1 = clock64(); g1 = mg_gtime(); }
 
             // ---- this warp's tiles of the phase
             if (next_p == p) {
                 while (true) {
-                    const uint32_t st = ring + stg * MG_STAGE_BYTES, bar = bar0 + stg * 8;
+                    const uint32_t st = ring + stg * stage_bytes, bar = bar0 + stg * 8;
                     long long tw0 = 0, tw1 = 0;
                     if (DBG && tid == 0) tw0 = clock64();
                     mg_wait(bar, parity);
@@ -1177,7 +1201,7 @@ decode_mega_kernel(const MegaArgs a) {
                         if (lane == 0) {
                             mg_expect_tx(bar, (uint32_t)th.z);
                             mg_bulk(st, src, (uint32_t)th.z, bar);
-                            const uint32_t ahead = g_mega_l2_ahead;
+                            const uint32_t ahead = a.l2_ahead;
                             if (ahead && ahead < rem) mg_prefetch_l2(src + ahead, min((uint32_t)th.z, rem - ahead));
                         }
                         src += (uint32_t)th.z;
@@ -1190,7 +1214,7 @@ decode_mega_kernel(const MegaArgs a) {
             if (DBG && tid == 0) tl_end = clock64();
             __syncthreads(); // the mid-phase sync: every warp's partial sums are in shared memory
             stage_phase(p + 2);
-            if (DBG && tid == 0) t_epi = clock64();
+            if (DBG && tid == 0) { t_epi = clock64(); g2 = mg_gtime(); }
 
             // ---- epilogue: combine the K-split partials in a fixed order (deterministic), then the phase's tail op.  Outputs
             // that a later phase consumes leave as LL words tagged with this phase: no fence and no barrier follow.
@@ -1249,44 +1273,74 @@ decode_mega_kernel(const MegaArgs a) {
                 }
             }
         }
-        if (DBG && tid == 0) t2 = clock64();
+        if (a.ll_probe == 2 && p + 1 < a.n_phases) { // this CTA's outputs of phase p are stored (or it had none)
+            __syncthreads();
+            if (tid == 0) mg_hint_arrive(a.hint);
+        }
         if (DBG && tid == 0) {
+            t2 = clock64();
+            // per (CTA, phase): [0..3] global-timer ns at phase start / input row ready (prologue + slice done) / this warp past the
+            // mid-phase sync / phase end; [4..7] warp 0's tile wait cycles, tile compute cycles, tiles, epilogue cycles
             long long *dd = a.dbg + ((int64_t)cta * a.n_phases + p) * 16;
-            dd[0] = t0; dd[1] = t1 ? t1 : t0; dd[2] = t2; dd[3] = clock64();
-            if (u < u_end) {
-                dd[4] = t_wait; dd[5] = t_comp; dd[6] = t_epi ? t2 - t_epi : 0; dd[7] = n_tiles;
-                dd[8] = tp0 - t0; dd[9] = 0; dd[10] = tp3 - tp0; dd[11] = 0; dd[12] = t1 - tp3; dd[13] = t_epi - tl_end; dd[14] = tl_end - t1; dd[15] = 0;
-            }
+            dd[0] = g0; dd[1] = g1 ? g1 : g0; dd[2] = g2 ? g2 : (g1 ? g1 : g0); dd[3] = mg_gtime();
+            dd[4] = t_wait; dd[5] = t_comp; dd[6] = n_tiles; dd[7] = t_epi ? t2 - t_epi : 0;
+            dd[8] = tp0 ? tp0 - t0 : 0; dd[9] = tp3 ? tp3 - tp0 : 0; dd[10] = t1 ? t1 - tp3 : 0; dd[11] = tl_end ? tl_end - t1 : 0; dd[12] = u_end - u;
         }
     }
 }
 
+void mega_fill_knobs(MegaArgs &a) {
+    static const int poll_ns = getenv("B200LLM_LL_POLL_NS") ? atoi(getenv("B200LLM_LL_POLL_NS")) : 32;
+    static const int probe = getenv("B200LLM_LL_PROBE") ? atoi(getenv("B200LLM_LL_PROBE")) : 0; // measured on Llama-3-8B: 0 -> 1.67 ms, 1 -> 1.99 ms, 2 -> 1.88 ms per token
+    static const unsigned ahead = getenv("B200LLM_MEGA_L2_AHEAD") ? (unsigned)atoi(getenv("B200LLM_MEGA_L2_AHEAD")) / 16 * 16 : 0u;
+    a.ll_poll_ns = poll_ns;
+    a.ll_probe = probe;
+    a.l2_ahead = ahead;
+}
+
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s) {
+    const MgSmem lay = mg_smem_layout(a.geo);
+    B2_CHECK(lay.total <= (uint32_t)MG_SMEM_MAX && a.geo.stage_bytes % 16 == 0 && a.geo.xs_bytes % 16 == 0, B2_EINVAL, "decode kernel: shared-memory geometry");
     static PerDeviceOnce configured;
     configured.run([&] {
-        B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
-        B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MG_SMEM));
-    });
-    static PerDeviceOnce knobs;
-    knobs.run([&] {
-        if (getenv("B200LLM_LL_POLL_NS")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_LL_POLL_NS")); B2_CUDA(cudaMemcpyToSymbol(g_ll_poll_ns, &v, sizeof(v))); }
-        if (getenv("B200LLM_MEGA_L2_AHEAD")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_MEGA_L2_AHEAD")) / 16 * 16; B2_CUDA(cudaMemcpyToSymbol(g_mega_l2_ahead, &v, sizeof(v))); }
-        if (getenv("B200LLM_LL_PROBE")) { const unsigned v = (unsigned)atoi(getenv("B200LLM_LL_PROBE")); B2_CUDA(cudaMemcpyToSymbol(g_ll_probe, &v, sizeof(v))); }
+        B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, MG_SMEM_MAX));
+        B2_CUDA(cudaFuncSetAttribute(decode_mega_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, MG_SMEM_MAX));
+        const unsigned v = (unsigned)a.ll_poll_ns;
+        B2_CUDA(cudaMemcpyToSymbol(g_ll_poll_ns, &v, sizeof(v)));
     });
     void *args[] = {(void *)&a};
     const void *fn = a.dbg ? (const void *)decode_mega_kernel<true> : (const void *)decode_mega_kernel<false>;
-    B2_CUDA(cudaLaunchCooperativeKernel(fn, dim3(n_sm), dim3(MG_THREADS), args, MG_SMEM, s));
+    B2_CUDA(cudaLaunchCooperativeKernel(fn, dim3(n_sm), dim3(MG_THREADS), args, lay.total, s));
     g_launch_count++;
 }
 
-bool mega_phase_prepare(MegaPhase &ph, int n_cta) {
+// Shared memory per model: the activation row takes what the longest row needs (or the attention scratch of the longest
+// context, whichever is larger), the 16 ring stages share the rest.
+MegaGeo mega_geometry(const MegaPhase *phases, int n_phases, int n_ctx_slot, int hd) {
+    MegaGeo g;
+    int64_t row = 0;
+    for (int p = 0; p < n_phases; p++)
+        if (phases[p].kind != PH_ATT) row = std::max(row, mg_act_row_bytes_host(phases[p].fmt, phases[p].K));
+    const int64_t att = (int64_t)sizeof(float) * ((int64_t)hd + 32 + (int64_t)MG_WARPS * hd + 16 + n_ctx_slot + 8) - (int64_t)MG_MAX_PART * (int64_t)sizeof(float);
+    int64_t xs = std::max<int64_t>(std::max(row, att), 4096);
+    xs = (xs + 255) / 256 * 256;
+    g.xs_bytes = (int)xs;
+    MegaGeo probe = g;
+    probe.stage_bytes = 0;
+    const int64_t fixed = mg_smem_layout(probe).total;
+    g.stage_bytes = (int)((MG_SMEM_MAX - fixed) / (MG_WARPS * MG_STAGES) / 16 * 16);
+    if (g.stage_bytes > 16384 + MG_TILE_HDR) g.stage_bytes = 16384 + MG_TILE_HDR;
+    return g;
+}
+
+bool mega_phase_prepare(MegaPhase &ph, int n_cta, const MegaGeo &geo) {
     if (ph.kind == PH_ATT) return true;
     if (n_cta < 1) return false;
     ph.units_q = ph.units / n_cta;
     ph.units_r = ph.units % n_cta;
     int S, lpr, rpp, np;
     if (!mg_split(ph.fmt, ph.K, ph.xq_ll != nullptr, S, lpr, rpp, np)) return false;
-    if (mg_act_row_bytes_host(ph.fmt, ph.K) > MG_XS_BYTES) return false;
+    if (mg_act_row_bytes_host(ph.fmt, ph.K) > geo.xs_bytes || geo.stage_bytes <= MG_TILE_HDR) return false;
     if (ph.norm_w && ph.K / 256 > 4 * MG_WARPS) return false; // the prologue norms at most 4 blocks per warp in one go
     ph.S = S; ph.lpr = lpr; ph.rpp = rpp; ph.np = np;
     ph.s_log = 0;
@@ -1297,7 +1351,7 @@ bool mega_phase_prepare(MegaPhase &ph, int n_cta) {
     for (int j = 0; j < ph.n_jobs; j++) {
         ph.j0[j] = (int)rows;
         if (act_format_for(ph.job[j].type) != ph.fmt) return false;
-        if (!mg_job_geo(ph.job[j].type, ph.K, S, rpp, ph.rb[j], ph.R[j])) return false;
+        if (!mg_job_geo(ph.job[j].type, ph.K, S, rpp, geo.stage_bytes - MG_TILE_HDR, ph.rb[j], ph.R[j])) return false;
         if (ph.job[j].rows % 2 != 0 || ph.job[j].rows >= (1 << 22)) return false;
         rows += ph.job[j].rows;
     }
@@ -1309,10 +1363,10 @@ bool mega_phase_supported(const MegaPhase &ph) {
     return mega_phase_prepare(t, 128);
 }
 
-size_t mega_attention_ctx_limit(int hd) {
+size_t mega_attention_ctx_limit(int hd, const MegaGeo &geo) {
     // q + reduction scratch + per-warp partials + scores live in the activation-row and partial regions; the page
     // table of the sequence has MG_MAX_PAGES entries (page size >= 16 assumed by the caller)
-    const size_t avail = MG_XS_BYTES + MG_MAX_PART * sizeof(float);
+    const size_t avail = (size_t)geo.xs_bytes + MG_MAX_PART * sizeof(float);
     const size_t fixed = sizeof(float) * ((size_t)hd + 32 + (size_t)MG_WARPS * hd + 16);
     if (fixed >= avail) return 0;
     return std::min((size_t)((avail - fixed) / 4) - 8, (size_t)MG_MAX_PAGES * 16);
@@ -1358,11 +1412,59 @@ void MegaStreams::free() {
 
 // Plan the streams (pure host arithmetic): the tile table in stream order, the per-warp starts, the first tile's offset
 // of every stream; returns the bytes of the stream buffer.
-static uint64_t mega_plan_streams(const MegaPhase *phases, int n_phases, int n_cta, std::vector<MgTileSrc> &tab,
+// This warp's rows of matrix j of a phase: [r0, r1) in the matrix's own row numbering, and the offset dr_off that turns a
+// row number into an index of the CTA's partial-sum rows.  Empty when the warp has none.
+static bool mg_warp_rows(const MegaPhase &ph, int j, int cta, int n_cta, int warp, int &r0, int &r1, int &dr_off) {
+    int u, u_end;
+    mg_cta_range(ph, cta, n_cta, u, u_end);
+    if (u >= u_end) return false;
+    const int g_log = 3 - ph.s_log, g = warp >> ph.s_log; // MG_WARPS = S K-splits x 2^g_log row groups: warp = (row group g, K-split q)
+    int lo, hi;
+    if (ph.kind == PH_SWIGLU) { // gate rows [u, u_end) and the same rows of up
+        lo = u; hi = u_end;
+        dr_off = j * (u_end - u) - u;
+    } else {
+        const int j0 = ph.j0[j];
+        lo = std::max(u, j0) - j0;
+        hi = std::min(u_end, j0 + (int)ph.job[j].rows) - j0;
+        dr_off = j0 - u;
+    }
+    if (hi <= lo) return false;
+    const int n = hi - lo;
+    r0 = lo + ((n * g) >> g_log);
+    r1 = lo + ((n * (g + 1)) >> g_log);
+    return r1 > r0;
+}
+
+// Plan the streams (pure host arithmetic): the tile table in stream order, the per-warp starts, the first tile's offset
+// of every stream; returns the bytes of the stream buffer.
+// Tiles per warp are EQUALISED per matrix: a warp's ring holds two tiles, so a phase lasts as many memory round trips as
+// the warp with the most tiles needs -- one warp with 7 tiles among warps with 6 keeps the whole GPU waiting for one more
+// round trip at the end of the phase.  Every warp therefore cuts its rows into the same number of tiles (the number the
+// warp with the most rows needs), in units of row pairs.
+static const bool g_taper = getenv("B200LLM_MEGA_TAPER") && atoi(getenv("B200LLM_MEGA_TAPER")) != 0; // B200LLM_MEGA_TAPER=1 (measured: 1.672 ms per token with it, 1.652 without: off by default)
+
+static uint64_t mega_plan_streams(const MegaPhase *phases, int n_phases, int n_cta, const MegaGeo &geo, std::vector<MgTileSrc> &tab,
                                   std::vector<MegaStreamStart> &st, std::vector<uint64_t> &first_off) {
     tab.clear();
     st.assign((size_t)n_cta * MG_WARPS, MegaStreamStart{});
     first_off.assign(st.size(), 0);
+    // tiles per warp of every (phase, matrix)
+    std::vector<int> n_tiles_of((size_t)n_phases * 3, 0);
+    for (int p = 0; p < n_phases; p++) {
+        const MegaPhase &ph = phases[p];
+        if (ph.kind == PH_ATT) continue;
+        for (int j = 0; j < ph.n_jobs; j++) {
+            int most = 0;
+            for (int cta = 0; cta < n_cta; cta++)
+                for (int warp = 0; warp < MG_WARPS; warp++) {
+                    int r0, r1, dr_off;
+                    if (mg_warp_rows(ph, j, cta, n_cta, warp, r0, r1, dr_off)) most = std::max(most, r1 - r0);
+                }
+            const int unit = ph.rpp == 1 ? 2 : ph.rpp, upt = std::max(1, ph.R[j] / unit); // units (row pairs / passes) per tile at most
+            n_tiles_of[(size_t)p * 3 + j] = ((most + unit - 1) / unit + upt - 1) / upt;
+        }
+    }
     uint64_t off = 0;
     for (int cta = 0; cta < n_cta; cta++)
         for (int warp = 0; warp < MG_WARPS; warp++) {
@@ -1374,50 +1476,58 @@ static uint64_t mega_plan_streams(const MegaPhase *phases, int n_phases, int n_c
                 const MegaPhase &ph = phases[p];
                 if (ph.kind == PH_ATT) continue;
                 const size_t before = tab.size();
-                int u, u_end;
-                mg_cta_range(ph, cta, n_cta, u, u_end);
-                // MG_WARPS = S K-splits x 2^g_log row groups: warp = (row group g, K-split q)
-                const int S = ph.S, g_log = 3 - ph.s_log, g = warp >> ph.s_log, q = warp & (S - 1);
+                const int S = ph.S, q = warp & (S - 1);
                 const int64_t nb = ph.K >> 8, nbs = nb >> ph.s_log, ks = ph.K >> ph.s_log;
-                for (int j = 0; j < ph.n_jobs && u < u_end; j++) {
+                for (int j = 0; j < ph.n_jobs; j++) {
                     const FusedJob &job = ph.job[j];
-                    int lo, hi, dr_off;
-                    if (ph.kind == PH_SWIGLU) { // gate rows [u, u_end) and the same rows of up
-                        lo = u; hi = u_end;
-                        dr_off = j * (u_end - u) - u;
-                    } else {
-                        const int j0 = ph.j0[j];
-                        lo = std::max(u, j0) - j0;
-                        hi = std::min(u_end, j0 + (int)job.rows) - j0;
-                        dr_off = j0 - u;
-                    }
-                    if (hi <= lo) continue;
-                    const int n = hi - lo;
-                    const int r0 = lo + ((n * g) >> g_log), r1 = lo + ((n * (g + 1)) >> g_log);
-                    if (r1 <= r0) continue;
+                    int r0, r1, dr_off;
+                    if (!mg_warp_rows(ph, j, cta, n_cta, warp, r0, r1, dr_off)) continue;
                     int64_t off0 = 0, len0 = 0, off1 = 0, len1 = 0;
                     if (job.type == B2_T_Q4_K) { off0 = q * nbs * 144; len0 = nbs * 144; }
                     else if (job.type == B2_T_Q5_K) { off0 = q * nbs * 176; len0 = nbs * 176; }
                     else if (job.type == B2_T_Q6_K) { off0 = q * nbs * Q6_BLK; len0 = nbs * Q6_BLK; off1 = nb * Q6_BLK + 2 * q * nbs; len1 = 2 * nbs; }
                     else { off0 = q * ks; len0 = ks; off1 = ph.K + q * (ks / 16); len1 = ks / 16; }
                     const int rb = ph.rb[j], R = ph.R[j];
-                    B2_CHECK(len0 % 16 == 0 && len0 + len1 <= rb && MG_TILE_HDR + (int64_t)R * rb <= MG_STAGE_BYTES, B2_EINVAL, "mega streams: tile geometry");
-                    for (int r = r0; r < r1; r += R) {
-                        const int nr = std::min(R, r1 - r);
-                        MgTileSrc t;
-                        const uint8_t *row = job.W + (int64_t)r * job.row_stride;
-                        t.src0 = row + off0;
-                        t.src1 = row + off1;
-                        t.dst = 0;
-                        t.hdr[0] = (uint32_t)job.type | ((uint32_t)nr << 8) | ((uint32_t)rb << 16);
-                        t.hdr[1] = (uint32_t)(dr_off + r);
-                        t.hdr[2] = 0;
-                        t.hdr[3] = 0;
-                        t.stride = (int32_t)job.row_stride;
-                        t.len0 = (int32_t)len0; t.len1 = (int32_t)len1;
-                        t.rb = rb; t.n = nr; t.pad = p;
-                        tab.push_back(t);
+                    B2_CHECK(len0 % 16 == 0 && len0 + len1 <= rb && MG_TILE_HDR + (int64_t)R * rb <= geo.stage_bytes, B2_EINVAL, "mega streams: tile geometry");
+                    const int unit = ph.rpp == 1 ? 2 : ph.rpp, upt = std::max(1, R / unit);
+                    const int n_rows = r1 - r0, n_units = (n_rows + unit - 1) / unit;
+                    int T = std::min(n_tiles_of[(size_t)p * 3 + j], n_units);
+                    // Tapered: when the warp's share of the LAST matrix of the phase is several tiles long, its last two tiles
+                    // are one unit each.  The final round trips of a phase are what every other SM ends up waiting for; with small
+                    // final tiles they deliver few bytes, so the warps of the GPU finish within a fraction of a microsecond of
+                    // each other instead of a whole tile time apart.
+                    const bool taper = g_taper && j == ph.n_jobs - 1 && T >= 4 && n_units >= T + 0 && (n_units - 2 + upt - 1) / upt + 2 <= T + 1;
+                    std::vector<int> sizes;
+                    if (taper) {
+                        const int body = n_units - 2, Tb = std::max(1, std::min(T + 1 - 2, body));
+                        for (int t = 0; t < Tb; t++) sizes.push_back(body / Tb + (t < body % Tb ? 1 : 0));
+                        sizes.push_back(1);
+                        sizes.push_back(1);
+                    } else {
+                        for (int t = 0; t < T; t++) sizes.push_back(n_units / T + (t < n_units % T ? 1 : 0));
                     }
+                    T = (int)sizes.size();
+                    int r = r0;
+                    for (int t = 0; t < T; t++) {
+                        const int units = sizes[(size_t)t];
+                        const int nr = std::min(units * unit, r1 - r);
+                        B2_CHECK(nr > 0 && nr <= R, B2_EINVAL, "mega streams: tile rows");
+                        MgTileSrc ts;
+                        const uint8_t *row = job.W + (int64_t)r * job.row_stride;
+                        ts.src0 = row + off0;
+                        ts.src1 = row + off1;
+                        ts.dst = 0;
+                        ts.hdr[0] = (uint32_t)job.type | ((uint32_t)nr << 8) | ((uint32_t)rb << 16);
+                        ts.hdr[1] = (uint32_t)(dr_off + r);
+                        ts.hdr[2] = 0;
+                        ts.hdr[3] = 0;
+                        ts.stride = (int32_t)job.row_stride;
+                        ts.len0 = (int32_t)len0; ts.len1 = (int32_t)len1;
+                        ts.rb = rb; ts.n = nr; ts.pad = p;
+                        tab.push_back(ts);
+                        r += nr;
+                    }
+                    B2_CHECK(r == r1, B2_EINVAL, "mega streams: rows left over");
                 }
                 if (tab.size() > before) {
                     if (first_p == n_phases) first_p = p;
@@ -1447,7 +1557,7 @@ static uint64_t mega_plan_streams(const MegaPhase *phases, int n_phases, int n_c
 // Replay every warp's walk over its stream the way the kernel does it (sizes from the start entry and the headers'
 // look-ahead field, phase hand-over from the last-tile flag) and check that each (row, K-split) of each phase is
 // produced exactly once, from the right source bytes.  Throws on the first inconsistency.
-static void mega_plan_verify(const MegaPhase *phases, int n_phases, int n_cta, const std::vector<MgTileSrc> &tab,
+static void mega_plan_verify(const MegaPhase *phases, int n_phases, int n_cta, const MegaGeo &geo, const std::vector<MgTileSrc> &tab,
                              const std::vector<MegaStreamStart> &st, const std::vector<uint64_t> &first_off, uint64_t total) {
     auto fail = [](const std::string &m) { throw Error(B2_EINVAL, "mega stream plan: " + m); };
     std::vector<std::vector<uint8_t>> cover((size_t)n_phases * n_cta);
@@ -1481,7 +1591,7 @@ static void mega_plan_verify(const MegaPhase *phases, int n_phases, int n_cta, c
                     const uint32_t sz = (uint32_t)(MG_TILE_HDR + t.n * t.rb);
                     if (t.pad != p) fail("tile of another phase");
                     if (pend[0] != sz || t.dst != src) fail("tile size / offset chain broken");
-                    if (sz > (uint32_t)MG_STAGE_BYTES || sz % 16 || t.dst % 16 || t.dst + sz > total) fail("tile does not fit");
+                    if (sz > (uint32_t)geo.stage_bytes || sz % 16 || t.dst % 16 || t.dst + sz > total) fail("tile does not fit");
                     const int type = t.hdr[0] & 0xFF, n = (t.hdr[0] >> 8) & 0xFF, rb = (int)(t.hdr[0] >> 16);
                     if (n != t.n || rb != t.rb || n <= 0) fail("header fields");
                     auto &cv = cover[(size_t)p * n_cta + cta];
@@ -1517,22 +1627,22 @@ static void mega_plan_verify(const MegaPhase *phases, int n_phases, int n_cta, c
             if (c != 1) fail("row-split not produced");
 }
 
-int64_t mega_plan_check(const MegaPhase *phases, int n_phases, int n_cta, int64_t *n_tiles) {
+int64_t mega_plan_check(const MegaPhase *phases, int n_phases, int n_cta, int64_t *n_tiles, const MegaGeo &geo) {
     std::vector<MgTileSrc> tab;
     std::vector<MegaStreamStart> st;
     std::vector<uint64_t> first_off;
-    const uint64_t total = mega_plan_streams(phases, n_phases, n_cta, tab, st, first_off);
-    mega_plan_verify(phases, n_phases, n_cta, tab, st, first_off, total);
+    const uint64_t total = mega_plan_streams(phases, n_phases, n_cta, geo, tab, st, first_off);
+    mega_plan_verify(phases, n_phases, n_cta, geo, tab, st, first_off, total);
     if (n_tiles) *n_tiles = (int64_t)tab.size();
     return (int64_t)total;
 }
 
-void MegaStreams::build(const MegaPhase *phases, int n_phases, int n_cta, cudaStream_t s) {
+void MegaStreams::build(const MegaPhase *phases, int n_phases, int n_cta, cudaStream_t s, const MegaGeo &geo) {
     free();
     std::vector<MgTileSrc> tab;
     std::vector<MegaStreamStart> st;
     std::vector<uint64_t> first_off;
-    const uint64_t off = mega_plan_streams(phases, n_phases, n_cta, tab, st, first_off) - 128;
+    const uint64_t off = mega_plan_streams(phases, n_phases, n_cta, geo, tab, st, first_off) - 128;
     bytes = (size_t)off + 128;
     n_tiles = (int64_t)tab.size();
     B2_CUDA(cudaMalloc((void **)&data, bytes));

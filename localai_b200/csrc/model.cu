@@ -575,6 +575,12 @@ void Model::build_mega() {
             *bufs[i] = (uint2 *)dalloc(sizes[i] * sizeof(uint2));
             B2_CUDA(cudaMemcpyAsync(*bufs[i], init.data(), sizes[i] * sizeof(uint2), cudaMemcpyHostToDevice, stream));
         }
+        mega_hint_ = (unsigned *)dalloc(256);
+        mega_hint_base_ = c0;
+        {
+            std::vector<unsigned> h0(64, c0);
+            B2_CUDA(cudaMemcpyAsync(mega_hint_, h0.data(), 256, cudaMemcpyHostToDevice, stream));
+        }
         B2_CUDA(cudaStreamSynchronize(stream));
     }
     // ffn_down's input (n_ff >= 8192) is quantised once per GPU, not once per CTA (B200LLM_NO_DIST_QUANT=1: per CTA)
@@ -622,9 +628,10 @@ void Model::build_mega() {
     h.x = x_; h.x_ll = x_ll_; h.src_p = prev;
     h.norm_w = (const float *)output_norm.data; h.out = logits_; h.xn_out = xn_out_; h.units = (int)(output.rows / 2);
     ph.push_back(h);
+    if (!mega_streams_.data) mega_geo_ = mega_geometry(ph.data(), (int)ph.size(), n_ctx_slot, hd); // (the streams are cut for this geometry)
     for (auto &p : ph)
-        if (!mega_phase_prepare(p, n_sm_)) return;
-    if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1)) ||
+        if (!mega_phase_prepare(p, n_sm_, mega_geo_)) return;
+    if ((size_t)n_ctx_slot > mega_attention_ctx_limit(hd, mega_geo_) || hd % 64 != 0 || hd > 128 || page_size < 16 || (page_size & (page_size - 1)) ||
         (uint64_t)pool_layer_stride_ >= (1ull << 31) || kvd % 2 != 0)
         return;
     if (!mega_streams_.data) {
@@ -634,7 +641,7 @@ void Model::build_mega() {
         size_t free_b = 0, total_b = 0;
         const bool off = getenv("B200LLM_NO_MEGA_STREAMS") && atoi(getenv("B200LLM_NO_MEGA_STREAMS"));
         if (off || cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < (size_t)decode_stream_bytes + shadow_reserve_) return;
-        mega_streams_.build(ph.data(), (int)ph.size(), n_sm_, stream);
+        mega_streams_.build(ph.data(), (int)ph.size(), n_sm_, stream, mega_geo_);
     }
     if (!mega_phases_) mega_phases_ = (MegaPhase *)dalloc(ph.size() * sizeof(MegaPhase));
     B2_CUDA(cudaMemcpyAsync(mega_phases_, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice, stream));
@@ -666,6 +673,11 @@ void Model::run_decode_mega() {
     a.kcur_ll = kcur_ll_; a.vcur_ll = vcur_ll_;
     a.tag_base = mega_tag_base_;
     mega_tag_base_ += (unsigned)mega_n_phases_;
+    a.geo = mega_geo_;
+    mega_fill_knobs(a);
+    a.hint = mega_hint_;
+    a.hint_base = mega_hint_base_;
+    if (a.ll_probe == 2) mega_hint_base_ += (unsigned)n_sm_ * (unsigned)(mega_n_phases_ - 1);
     a.dbg = mega_dbg_;
     const bool timed = mega_timing_ && mega_ev_n_ + 2 <= mega_ev_.size();
     if (timed) B2_CUDA(cudaEventRecord(mega_ev_[mega_ev_n_++], stream));

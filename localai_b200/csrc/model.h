@@ -142,8 +142,11 @@ class Model {
     void build_mega();
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;
+    MegaGeo mega_geo_;         // shared-memory split of the decode kernel for this model (activation row vs weight rings)
     MegaStreams mega_streams_; // the decode kernel's copy of the weights: one contiguous stream per (CTA, warp)
     unsigned mega_tag_base_ = 0;   // LL tag base of the next launch (advances by the number of phases)
+    unsigned *mega_hint_ = nullptr; // phase counter of the decode kernel (MegaArgs.hint)
+    unsigned mega_hint_base_ = 0;
     // LL-word buffers ({fp32, tag} pairs) through which the phases of the decode kernel hand activations to each other
     uint2 *x_ll_ = nullptr, *q_ll_ = nullptr, *att_ll_ = nullptr, *gate_ll_ = nullptr, *kcur_ll_ = nullptr, *vcur_ll_ = nullptr,
           *xq_ll_ = nullptr, *mega_att_scores_ = nullptr, *mega_att_part_ = nullptr;

@@ -323,6 +323,12 @@ void Model::tp_build_fused() {
             *bufs[i] = (uint2 *)m.dalloc(sizes[i] * sizeof(uint2));
             B2_CUDA(cudaMemcpyAsync(*bufs[i], init.data(), sizes[i] * sizeof(uint2), cudaMemcpyHostToDevice, m.stream));
         }
+        m.mega_hint_ = (unsigned *)m.dalloc(256);
+        m.mega_hint_base_ = c0;
+        {
+            std::vector<unsigned> h0(64, c0);
+            B2_CUDA(cudaMemcpyAsync(m.mega_hint_, h0.data(), 256, cudaMemcpyHostToDevice, m.stream));
+        }
         B2_CUDA(cudaStreamSynchronize(m.stream));
     }
     const bool dist_quant = !(getenv("B200LLM_NO_DIST_QUANT") && atoi(getenv("B200LLM_NO_DIST_QUANT")));
@@ -389,14 +395,15 @@ void Model::tp_build_fused() {
         if (prev >= 0) h.red_res_ll = m.x_ll_;
         h.norm_w = (const float *)m.output_norm.data; h.out = m.logits_ + (size_t)r * m.vocab_l; h.xn_out = m.xn_out_; h.units = (int)(m.output.rows / 2);
         ph.push_back(h);
+        m.mega_geo_ = mega_geometry(ph.data(), (int)ph.size(), m.n_ctx_slot, hd);
         for (auto &p : ph)
-            if (!mega_phase_prepare(p, m.n_sm_)) { ok = false; break; }
+            if (!mega_phase_prepare(p, m.n_sm_, m.mega_geo_)) { ok = false; break; }
         if (!ok) break;
-        if ((size_t)m.n_ctx_slot > mega_attention_ctx_limit(hd) || hd % 64 != 0 || hd > 128 || m.page_size < 16 || (m.page_size & (m.page_size - 1)) ||
+        if ((size_t)m.n_ctx_slot > mega_attention_ctx_limit(hd, m.mega_geo_) || hd % 64 != 0 || hd > 128 || m.page_size < 16 || (m.page_size & (m.page_size - 1)) ||
             (uint64_t)m.pool_layer_stride_ >= (1ull << 31) || m.kvd_l % 2 != 0) { ok = false; break; }
         size_t free_b = 0, total_b = 0;
         if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < (size_t)m.decode_stream_bytes + m.shadow_reserve_) { ok = false; break; }
-        m.mega_streams_.build(ph.data(), (int)ph.size(), m.n_sm_, m.stream);
+        m.mega_streams_.build(ph.data(), (int)ph.size(), m.n_sm_, m.stream, m.mega_geo_);
         m.mega_phases_ = (MegaPhase *)m.dalloc(ph.size() * sizeof(MegaPhase));
         B2_CUDA(cudaMemcpyAsync(m.mega_phases_, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice, m.stream));
         B2_CUDA(cudaStreamSynchronize(m.stream));
@@ -431,6 +438,11 @@ void Model::run_decode_mega_tp(int t0, int out_row0) {
     a.kcur_ll = kcur_ll_; a.vcur_ll = vcur_ll_;
     a.tag_base = mega_tag_base_;
     mega_tag_base_ += (unsigned)mega_n_phases_;
+    a.geo = mega_geo_;
+    mega_fill_knobs(a);
+    a.hint = mega_hint_;
+    a.hint_base = mega_hint_base_;
+    if (a.ll_probe == 2) mega_hint_base_ += (unsigned)n_sm_ * (unsigned)(mega_n_phases_ - 1);
     // the logits row of this step (unwanted rows go to a spare row past the last one the caller can ask for)
     const int row = out_row0 >= 0 ? out_row0 : logits_rows_cap_ - 1;
     a.out_override = logits_ + (size_t)row * hp.n_vocab + (size_t)tp_rank * vocab_l;
