@@ -299,7 +299,7 @@ def bench_pool(path, rank, world, ranks):
     import numpy as np
 
     out = None
-    ranks.barrier()
+    ranks.host_barrier()
     if rank == 0:
         from localai_b200.replicas import ReplicaPool
 
@@ -322,7 +322,7 @@ def bench_pool(path, rank, world, ranks):
                    "path": "one process, ReplicaPool over %d devices, b2_submit / b2_poll with host buffers (prompt + decode inside the timed region)" % world}
         finally:
             pool.close()
-    ranks.barrier()
+    ranks.host_barrier()
     return out
 
 
@@ -346,7 +346,7 @@ def bench_tp70b(rank, world, ranks, peak, with_one_gpu=True):
     kernels + ncclAllReduce (what north_star names; the time inside the collectives is reported separately) and the
     persistent kernels that store their partial rows into the peers' memory.  The one-GPU number is the scaling baseline."""
     out = None
-    ranks.barrier()
+    ranks.host_barrier()
     if rank == 0:
         from localai_b200 import capi
 
@@ -374,7 +374,7 @@ def bench_tp70b(rank, world, ranks, peak, with_one_gpu=True):
                         out[name]["allreduce_us_per_token"] = info["allreduce_ms_per_step"] * 1e3
                 except Exception as ex:  # noqa: BLE001
                     out[name] = {"error": str(ex)}
-    ranks.barrier()
+    ranks.host_barrier()
     return out
 
 

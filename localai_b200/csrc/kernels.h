@@ -154,11 +154,10 @@ MegaGeo mega_geometry(const struct MegaPhase *phases, int n_phases, int n_ctx_sl
 struct MegaArgs {
     MegaGeo geo;
     int ll_poll_ns = 32;     // sleep between two polls of an LL word (B200LLM_LL_POLL_NS)
-    int ll_probe = 2;        // how a CTA waits for its input row before loading it (B200LLM_LL_PROBE): 0 = every warp polls its slice,
-                             // 1 = one warp polls a sample of the row, 2 = one thread polls the phase counter `hint`
+    int ll_probe = 0;        // how a CTA waits for its input row before loading it (B200LLM_LL_PROBE): 0 = every warp polls its slice,
+                             // 2 = one thread polls the phase counter `hint` first
     unsigned *hint = nullptr; // phase counter: every CTA adds 1 (relaxed, no fence: the tags stay the proof) when it has stored a phase's outputs
     unsigned hint_base = 0;   // its value when this launch starts; the host adds n_cta * n_phases per launch
-    unsigned l2_ahead = 0;   // bytes of its stream every warp keeps requested into L2 beyond its ring (B200LLM_MEGA_L2_AHEAD; 0: off)
     const MegaPhase *phases = nullptr; // device
     int n_phases = 0;
     const MegaStreamStart *starts = nullptr; // device, [n_cta][warps per CTA]

@@ -181,7 +181,8 @@ void launch_fused_gemv(FusedGemv a, int n_tok, cudaStream_t s) {
 #define B2_FUSED_CASE(N)                                                                                                  \
     case N: {                                                                                                             \
         auto kfn = fused_gemv_kernel<N>;                                                                                  \
-        if (smem > 48 * 1024) B2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+        static PerDeviceOnce cfg; /* once per device and instantiation, not per launch (the call takes a driver lock) */   \
+        if (smem > 48 * 1024) cfg.run([&] { B2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); }); \
         kfn<<<ctas, FW * 32, smem, s>>>(a);                                                                               \
     } break;
         switch (nt) {

@@ -69,7 +69,8 @@ static void launch_gemv_typed(const DTensor &W, const uint8_t *xq, int64_t xrb, 
 #define B2_GEMV_CASE(N)                                                                                             \
     case N: {                                                                                                       \
         auto kfn = gemv_kernel<TYPE, N>;                                                                            \
-        if (smem > 48 * 1024) B2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+        static PerDeviceOnce cfg; /* once per device and instantiation, not per launch (the call takes a driver lock) */   \
+        if (smem > 48 * 1024) cfg.run([&] { B2_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); }); \
         kfn<<<(int)ctas, GEMV_WARPS * 32, smem, s>>>(W.data, W.rows, W.cols, W.row_stride, xp, xrb, op, out_stride, rp, \
                                                      res_stride);                                                  \
     } break;

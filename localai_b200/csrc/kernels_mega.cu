@@ -155,10 +155,6 @@ __device__ __forceinline__ long long mg_gtime() { // nanoseconds, one clock for 
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-// ask for [p, p + bytes) to be brought into L2 (fire and forget; 16-byte granularity)
-__device__ __forceinline__ void mg_prefetch_l2(const void *p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
-}
 __device__ __forceinline__ int4 mg_lds128(uint32_t a) {
     int4 r;
     asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
@@ -437,7 +433,7 @@ __device__ __forceinline__ const __half *mg_kv_row(const __half *pool, const int
 __device__ __noinline__ void mg_attention_ll(const uint2 *__restrict__ q_ll, const uint2 *__restrict__ kcur_ll, const uint2 *__restrict__ vcur_ll,
                                              uint32_t tag_in, int n_kv, const int *pbase, const __half *k_pool, const __half *v_pool,
                                              int page_shift, int kvd, int hk, int hd, float scale, uint2 *__restrict__ out_ll, float *scratch,
-                                             int tid, int part, int parts, uint2 *g_scores, uint2 *g_part, uint32_t tag) {
+                                             int tid, int part, int parts, uint2 *g_scores, uint2 *g_part, uint32_t tag, bool combine_here) {
     const int lane = tid & 31, warp = tid >> 5;
     float *qs = scratch, *red = qs + hd, *pw = red + 32, *sc = pw + MG_WARPS * hd;
     const int pos = n_kv - 1;                // the current token's position
@@ -599,8 +595,8 @@ __device__ __noinline__ void mg_attention_ll(const uint2 *__restrict__ q_ll, con
         float o = 0.f;
 #pragma unroll
         for (int w = 0; w < MG_WARPS; w++) o += pw[w * hd + i];
-        if (part != 0) {
-            ll_st(g_part + part * hd + i, o, tag);
+        if (part != 0 || !combine_here) {
+            ll_st(g_part + part * hd + i, o, tag); // (parts == 1 never gets here without combine_here)
         } else { // part 0 adds the partial rows in part order (fixed order: deterministic) and publishes the head's output
             float pv[3] = {0.f, 0.f, 0.f}; // parts <= 4
             unsigned spins = 0;
@@ -623,6 +619,33 @@ __device__ __noinline__ void mg_attention_ll(const uint2 *__restrict__ q_ll, con
         }
     }
     __syncthreads(); // the scratch is reused by the next phase's prologue
+}
+
+// The partial output rows of a head's parts -> the head's output, added in part order.  Run by the CTAs that have no share
+// of the attention itself (148 CTAs, 128 shares for 32 heads x 4 parts): the CTAs that do the attention then all carry the
+// same load, and none of them starts the next phase late because it also had to collect its peers' rows.
+__device__ __noinline__ void mg_attention_combine(const uint2 *g_part, int parts, int hd, uint2 *out_ll, uint32_t tag, int tid) {
+    for (int i = tid; i < hd; i += MG_THREADS) {
+        float pv[4] = {0.f, 0.f, 0.f, 0.f};
+        unsigned spins = 0;
+        while (true) {
+            bool ok = true;
+#pragma unroll
+            for (int pp = 0; pp < 4; pp++)
+                if (pp < parts) {
+                    const unsigned long long w = ll_ld(g_part + pp * hd + i);
+                    ok = ok && ll_tag(w) == tag;
+                    pv[pp] = ll_val(w);
+                }
+            if (ok) break;
+            ll_backoff(spins);
+        }
+        float o = pv[0];
+#pragma unroll
+        for (int pp = 1; pp < 4; pp++)
+            if (pp < parts) o += pv[pp];
+        ll_st(out_ll + i, o, tag);
+    }
 }
 
 // Pull the K/V rows (positions < n_kv) of one KV head into L2 ahead of the attention phase.
@@ -729,7 +752,7 @@ __device__ __noinline__ void mg_copy_xq(const uint2 *xq_ll, uint32_t tag, int64_
 // quantize_row_q8_K_ref / quantize_row_q8_0_ref (act_quant.cuh holds the same arithmetic for the other kernels).
 template <int PBN>
 __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, float eps, uint8_t *xs, double *s_part, int nb, int k_first,
-                                         int warp, int lane, float *xn_out, bool probe) { // probe: warp 0 polls a sample of the row first
+                                         int warp, int lane, float *xn_out) {
     const bool write_xn = xn_out != nullptr;
     const int64_t K = ph.K;
     const bool has_norm = ph.norm_w != nullptr;
@@ -758,23 +781,11 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, f
             v[k][4] = a1.x; v[k][5] = a1.y; v[k][6] = a1.z; v[k][7] = a1.w;
         }
     } else {
-        // LL words written by phase src_p, possibly still on their way.  ONE warp waits for them: it polls a sample of the
-        // row -- every 16th word, so every producer CTA (each owns >= 16 consecutive rows of a model this kernel is meant
-        // for; the full check below does not depend on it) has a word in the sample -- while the other warps sleep at the
-        // barrier instead of spinning beside the warps of other phases' weight streams.  Then every warp loads its slice.
+        // LL words written by phase src_p, possibly still on their way: every warp polls its own slice until all of it
+        // carries the producing phase's tag (all loads of a round in flight together).  Measured alternatives: one warp
+        // polling a sample of the row for the CTA 1.99 ms per token, every warp a sample of its slice first 1.85, one
+        // thread polling a relaxed phase counter (B200LLM_LL_PROBE=2) 1.88, this 1.67.
         unsigned spins = 0;
-        if (probe) {
-            if (warp == 0) {
-                const int n_s = (int)(K >> 4);
-                while (true) {
-                    bool ok = true;
-                    for (int i = lane; i < n_s; i += 32) ok = ok && ll_tag(ll_ld(ph.x_ll + i * 16 + 15)) == tag_in;
-                    if (__all_sync(0xffffffffu, ok)) break;
-                    ll_backoff(spins);
-                }
-            }
-            __syncthreads();
-        }
         while (true) {
             bool ok = true;
 #pragma unroll
@@ -902,6 +913,99 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, f
     __syncthreads();
 }
 
+// Tensor parallelism: the input row of a phase is the sum of reduce_n partial rows, one from every shard (they arrive in
+// this GPU's memory as LL words stored by the peers), plus the residual.  Every CTA assembles a slice of it -- the partial
+// rows are added in rank order, so all shards compute the same bits -- and publishes the slice in x_ll, with the tag the
+// phase's prologue waits for.
+__device__ __noinline__ void mg_reduce_partials(const MegaPhase &ph, uint32_t tag_in, int cta, int n_cta, int tid) {
+    const int per = (ph.reduce_len + n_cta - 1) / n_cta;
+    for (int k = tid; k < per; k += MG_THREADS) {
+        const int e = cta * per + k;
+        if (e >= ph.reduce_len) break;
+        float pv[8];
+        unsigned spins = 0;
+        while (true) {
+            bool ok = true;
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                if (j < ph.reduce_n) {
+                    const unsigned long long w = ll_ld_sys(ph.part_ll + (size_t)j * ph.reduce_len + e);
+                    ok = ok && ll_tag(w) == tag_in;
+                    pv[j] = ll_val(w);
+                }
+            if (ok) break;
+            ll_backoff(spins);
+        }
+        float sum = ph.red_res_ll ? ll_val(ll_ld(ph.red_res_ll + e)) : ph.red_residual ? __ldcg(ph.red_residual + e) : 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            if (j < ph.reduce_n) sum += pv[j];
+        ll_st(ph.x_ll_w + e, sum, tag_in);
+    }
+}
+
+// ---- epilogue of a mat-vec phase: combine the K-split partials in a fixed order (deterministic), then the phase's tail op.
+// Outputs that a later phase consumes leave as LL words tagged with this phase: no fence and no barrier follow.
+__device__ __noinline__ void mg_epilogue(const MegaPhase &ph, const MegaArgs &a, const float *partial, const int *pbase, int u, int u_end, int pos,
+                                         uint32_t tag_out, float res_pre, int tid) {
+    const int S = ph.S, n_r = u_end - u;
+    auto dot_sum = [&](int dr) {
+        float s = 0.f;
+        for (int sg = 0; sg < S; sg++) s += partial[dr * S + sg];
+        return s;
+    };
+    if (ph.kind == PH_SWIGLU) {
+        for (int r = tid; r < n_r; r += MG_THREADS) {
+            const float g = dot_sum(r), up = dot_sum(n_r + r);
+            ll_st(ph.out_ll + u + r, __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), up), tag_out);
+        }
+    } else if (ph.kind == PH_PLAIN && ph.n_peers > 0) {
+        // a partial row of a tensor-parallel model: one plain 64-bit store per shard, this one included
+        // (measured and dropped: a system fence after the stores +0.2 ms per token, 16-byte stores and polling with an
+        // atomic no change)
+        for (int r = tid; r < n_r; r += MG_THREADS) {
+            const float sv = dot_sum(r);
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                if (j < ph.n_peers) ll_st_sys(ph.peer_part[j] + u + r, sv, tag_out);
+        }
+    } else if (ph.kind == PH_PLAIN) {
+        float *outp = a.out_override && !ph.out_ll ? a.out_override : ph.out;
+        for (int r = tid; r < n_r; r += MG_THREADS) {
+            float s = dot_sum(r);
+            if (r == tid) s += res_pre; // requested before the tile loop
+            else if (ph.res_ll) s += ll_val(ll_ld(ph.res_ll + u + r));
+            else if (ph.residual) s += __ldcg(ph.residual + u + r);
+            if (ph.out_ll) ll_st(ph.out_ll + u + r, s, tag_out);
+            else outp[u + r] = s;
+        }
+    } else { // PH_QKV: job 0 = q, 1 = k, 2 = v; rows (r, r+1) form a rotary pair inside one head
+        const int64_t cell = ((((int64_t)pbase[pos >> a.page_shift]) << a.page_shift) + (pos & (a.page_size - 1))) * a.kvd;
+        for (int pr = tid; pr < n_r / 2; pr += MG_THREADS) {
+            int jb, r;
+            mg_locate_row(ph, u + 2 * pr, jb, r);
+            const float v0 = dot_sum(2 * pr), v1 = dot_sum(2 * pr + 1);
+            if (jb == 2) { // V: into the cache for later tokens, and as LL words for this token's attention
+                const __half2 hv = __halves2half2(__float2half_rn(v0), __float2half_rn(v1));
+                *(__half2 *)(ph.v_pool + cell + r) = hv;
+                ll_st2(a.vcur_ll + r, __low2float(hv), __high2float(hv), tag_out);
+            } else {
+                const float *cs = a.rope_table + (int64_t)pos * a.hd + (r % a.hd);
+                const float c = cs[0], sn = cs[1];
+                const float o0 = __fsub_rn(__fmul_rn(v0, c), __fmul_rn(v1, sn));
+                const float o1 = __fadd_rn(__fmul_rn(v0, sn), __fmul_rn(v1, c));
+                if (jb == 0) {
+                    ll_st2(ph.out_ll + r, o0, o1, tag_out);
+                } else {
+                    const __half2 hk2 = __halves2half2(__float2half_rn(o0), __float2half_rn(o1));
+                    *(__half2 *)(ph.k_pool + cell + r) = hk2;
+                    ll_st2(a.kcur_ll + r, __low2float(hk2), __high2float(hk2), tag_out);
+                }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ the kernel
 // Tile header, the first 16 bytes of every tile of a warp's stream (written by MegaStreams::build):
 //   w0: ggml type | rows << 8 | row pitch << 16        w1: first row's index in the phase's partial-sum rows
@@ -909,7 +1013,7 @@ __device__ __noinline__ void mg_prologue(const MegaPhase &ph, uint32_t tag_in, f
 //   w3: bit 0: the warp's last tile of this phase; bits 8..: the next phase in which the warp has tiles
 template <bool DBG>
 __global__ void __launch_bounds__(MG_THREADS, 1)
-decode_mega_kernel(const MegaArgs a) {
+decode_mega_kernel(const __grid_constant__ MegaArgs a) {
     extern __shared__ __align__(128) uint8_t smem[];
     const MgSmem lay = mg_smem_layout(a.geo);
     const uint32_t stage_bytes = (uint32_t)a.geo.stage_bytes;
@@ -945,7 +1049,6 @@ decode_mega_kernel(const MegaArgs a) {
     const uint32_t ring = mg_s32(smem) + warp * (MG_STAGES * stage_bytes);
     const uint32_t bar0 = mg_s32(bars + warp * MG_STAGES);
     const uint8_t *src; // next tile to request into the ring
-    uint32_t rem;       // bytes of the stream from src on (the L2 prefetch front runs a.l2_ahead bytes ahead of src)
     int next_p; // the next phase in which this warp has tiles
     {
         const MegaStreamStart st = a.starts[cta * MG_WARPS + warp];
@@ -956,12 +1059,6 @@ decode_mega_kernel(const MegaArgs a) {
             if (st.size1) { mg_expect_tx(bar0 + 8, st.size1); mg_bulk(ring + stage_bytes, src + st.size0, st.size1, bar0 + 8); }
         }
         src += st.size0 + st.size1;
-        // Beyond the ring, the stream is kept requested into L2 a fixed distance ahead: while the CTA sits in the latency-bound
-        // phases (QKV, attention, attn_output: a few MB of weights between many hand-overs) HBM keeps working on the rows
-        // of the big phases that follow, and their ring refills then come from L2.
-        rem = st.total - st.size0 - st.size1;
-        const uint32_t ahead = a.l2_ahead;
-        if (ahead && lane == 0 && rem) mg_prefetch_l2(src, min(ahead, rem));
     }
     uint32_t stg = 0, parity = 0; // ring position of the next tile to consume
 
@@ -974,12 +1071,16 @@ decode_mega_kernel(const MegaArgs a) {
         int u = 0, u_end = 0;
         if (ph.kind == PH_ATT) {
             // a head is shared by att_parts CTAs (att_parts * n_head <= n_cta whenever att_parts > 1)
-            for (int hp = cta; hp < a.n_head * a.att_parts; hp += n_cta) {
+            const int n_att = a.n_head * a.att_parts, n_comb = a.att_parts > 1 ? n_cta - n_att : 0; // CTAs left over collect the parts' rows
+            for (int hp = cta; hp < n_att; hp += n_cta) {
                 const int h = hp >> a.att_parts_log, part = hp & (a.att_parts - 1), hk = h / (a.n_head / a.n_head_kv);
                 mg_attention_ll(ph.x_ll + (int64_t)h * a.hd, a.kcur_ll, a.vcur_ll, tag_in, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift,
                                 a.kvd, hk, a.hd, a.att_scale, ph.out_ll + (int64_t)h * a.hd, (float *)xs, tid, part, a.att_parts,
-                                a.att_scores + (int64_t)h * a.att_scores_stride, a.att_part_out + (int64_t)h * a.att_parts * a.hd, tag_out);
+                                a.att_scores + (int64_t)h * a.att_scores_stride, a.att_part_out + (int64_t)h * a.att_parts * a.hd, tag_out, n_comb <= 0);
             }
+            if (n_comb > 0 && cta >= n_att)
+                for (int h = cta - n_att; h < a.n_head; h += n_comb)
+                    mg_attention_combine(a.att_part_out + (int64_t)h * a.att_parts * a.hd, a.att_parts, a.hd, ph.out_ll + (int64_t)h * a.hd, tag_out, tid);
             __syncthreads(); // the mid-phase sync of a phase without rows
             stage_phase(p + 2);
         } else {
@@ -994,36 +1095,7 @@ decode_mega_kernel(const MegaArgs a) {
             if (tid == 0) mg_hint_wait(a.hint, a.hint_base + ((unsigned)ph.src_p + 1u) * (unsigned)n_cta);
             __syncthreads();
         }
-        if (ph.kind != PH_ATT && ph.reduce_n > 0) {
-            // Tensor parallelism: the input row is the sum of reduce_n partial rows, one from every shard (they arrive in
-            // this GPU's memory as LL words stored by the peers), plus the residual.  Every CTA assembles a slice of it --
-            // the partial rows are added in rank order, so all shards compute the same bits -- and publishes the slice
-            // in x_ll, with the tag the prologue below waits for.
-            const int per = (ph.reduce_len + n_cta - 1) / n_cta;
-            for (int k = tid; k < per; k += MG_THREADS) {
-                const int e = cta * per + k;
-                if (e >= ph.reduce_len) break;
-                float pv[8];
-                unsigned spins = 0;
-                while (true) {
-                    bool ok = true;
-#pragma unroll
-                    for (int j = 0; j < 8; j++)
-                        if (j < ph.reduce_n) {
-                            const unsigned long long w = ll_ld_sys(ph.part_ll + (size_t)j * ph.reduce_len + e);
-                            ok = ok && ll_tag(w) == tag_in;
-                            pv[j] = ll_val(w);
-                        }
-                    if (ok) break;
-                    ll_backoff(spins);
-                }
-                float sum = ph.red_res_ll ? ll_val(ll_ld(ph.red_res_ll + e)) : ph.red_residual ? __ldcg(ph.red_residual + e) : 0.f;
-#pragma unroll
-                for (int j = 0; j < 8; j++)
-                    if (j < ph.reduce_n) sum += pv[j];
-                ll_st(ph.x_ll_w + e, sum, tag_in);
-            }
-        }
+        if (ph.kind != PH_ATT && ph.reduce_n > 0) mg_reduce_partials(ph, tag_in, cta, n_cta, tid);
         if (ph.kind != PH_ATT && ph.xq_ll) {
             // A long activation row is quantised ONCE per GPU (block b by warp 0 of CTA b, as soon as its inputs are
             // there), not once per CTA; the prologue below then copies the 16 KB image.
@@ -1041,10 +1113,10 @@ decode_mega_kernel(const MegaArgs a) {
                 mg_copy_xq(ph.xq_ll, tag_out, K, nb, xs, tid);
             } else {
                 float *wx = ph.xn_out && cta == 0 ? (a.xn_override ? a.xn_override : ph.xn_out) : nullptr;
-                if (nb <= MG_WARPS) mg_prologue<1>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx, a.ll_probe == 1);
-                else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx, a.ll_probe == 1);
+                if (nb <= MG_WARPS) mg_prologue<1>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
+                else if (nb <= 2 * MG_WARPS) mg_prologue<2>(ph, tag_in, a.eps, xs, s_part, nb, 0, warp, lane, wx);
                 else // 4 blocks per warp at a time; rows longer than 32 blocks have no norm (mega_phase_prepare)
-                    for (int k0 = 0; k0 * MG_WARPS < nb; k0 += 4) mg_prologue<4>(ph, tag_in, a.eps, xs, s_part, nb, k0, warp, lane, wx, a.ll_probe == 1 && k0 == 0);
+                    for (int k0 = 0; k0 * MG_WARPS < nb; k0 += 4) mg_prologue<4>(ph, tag_in, a.eps, xs, s_part, nb, k0, warp, lane, wx);
             }
             if (DBG && tid == 0) tp3 = clock64();
             if (ph.kind == PH_QKV) // the attention phase comes next: start its K/V rows on their way into L2
@@ -1201,11 +1273,8 @@ decode_mega_kernel(const MegaArgs a) {
                         if (lane == 0) {
                             mg_expect_tx(bar, (uint32_t)th.z);
                             mg_bulk(st, src, (uint32_t)th.z, bar);
-                            const uint32_t ahead = a.l2_ahead;
-                            if (ahead && ahead < rem) mg_prefetch_l2(src + ahead, min((uint32_t)th.z, rem - ahead));
                         }
                         src += (uint32_t)th.z;
-                        rem -= (uint32_t)th.z;
                     }
                     if (++stg == MG_STAGES) { stg = 0; parity ^= 1; }
                     if (th.w & 1) { next_p = (int)((uint32_t)th.w >> 8); break; }
@@ -1216,62 +1285,7 @@ decode_mega_kernel(const MegaArgs a) {
             stage_phase(p + 2);
             if (DBG && tid == 0) { t_epi = clock64(); g2 = mg_gtime(); }
 
-            // ---- epilogue: combine the K-split partials in a fixed order (deterministic), then the phase's tail op.  Outputs
-            // that a later phase consumes leave as LL words tagged with this phase: no fence and no barrier follow.
-            const int n_r = u_end - u;
-            auto dot_sum = [&](int dr) {
-                float s = 0.f;
-                for (int sg = 0; sg < S; sg++) s += partial[dr * S + sg];
-                return s;
-            };
-            if (ph.kind == PH_SWIGLU) {
-                for (int r = tid; r < n_r; r += MG_THREADS) {
-                    const float g = dot_sum(r), up = dot_sum(n_r + r);
-                    ll_st(ph.out_ll + u + r, __fmul_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))), up), tag_out);
-                }
-            } else if (ph.kind == PH_PLAIN && ph.n_peers > 0) {
-                // a partial row of a tensor-parallel model: one plain 64-bit store per shard, this one included
-                for (int r = tid; r < n_r; r += MG_THREADS) {
-                    const float s = dot_sum(r);
-#pragma unroll
-                    for (int j = 0; j < 8; j++)
-                        if (j < ph.n_peers) ll_st_sys(ph.peer_part[j] + u + r, s, tag_out);
-                }
-            } else if (ph.kind == PH_PLAIN) {
-                float *outp = a.out_override && !ph.out_ll ? a.out_override : ph.out;
-                for (int r = tid; r < n_r; r += MG_THREADS) {
-                    float s = dot_sum(r);
-                    if (r == tid) s += res_pre; // requested before the tile loop
-                    else if (ph.res_ll) s += ll_val(ll_ld(ph.res_ll + u + r));
-                    else if (ph.residual) s += __ldcg(ph.residual + u + r);
-                    if (ph.out_ll) ll_st(ph.out_ll + u + r, s, tag_out);
-                    else outp[u + r] = s;
-                }
-            } else { // PH_QKV: job 0 = q, 1 = k, 2 = v; rows (r, r+1) form a rotary pair inside one head
-                const int64_t cell = ((((int64_t)pbase[pos >> a.page_shift]) << a.page_shift) + (pos & (a.page_size - 1))) * a.kvd;
-                for (int pr = tid; pr < n_r / 2; pr += MG_THREADS) {
-                    int jb, r;
-                    mg_locate_row(ph, u + 2 * pr, jb, r);
-                    const float v0 = dot_sum(2 * pr), v1 = dot_sum(2 * pr + 1);
-                    if (jb == 2) { // V: into the cache for later tokens, and as LL words for this token's attention
-                        const __half2 hv = __halves2half2(__float2half_rn(v0), __float2half_rn(v1));
-                        *(__half2 *)(ph.v_pool + cell + r) = hv;
-                        ll_st2(a.vcur_ll + r, __low2float(hv), __high2float(hv), tag_out);
-                    } else {
-                        const float *cs = a.rope_table + (int64_t)pos * a.hd + (r % a.hd);
-                        const float c = cs[0], sn = cs[1];
-                        const float o0 = __fsub_rn(__fmul_rn(v0, c), __fmul_rn(v1, sn));
-                        const float o1 = __fadd_rn(__fmul_rn(v0, sn), __fmul_rn(v1, c));
-                        if (jb == 0) {
-                            ll_st2(ph.out_ll + r, o0, o1, tag_out);
-                        } else {
-                            const __half2 hk2 = __halves2half2(__float2half_rn(o0), __float2half_rn(o1));
-                            *(__half2 *)(ph.k_pool + cell + r) = hk2;
-                            ll_st2(a.kcur_ll + r, __low2float(hk2), __high2float(hk2), tag_out);
-                        }
-                    }
-                }
-            }
+            mg_epilogue(ph, a, partial, pbase, u, u_end, pos, tag_out, res_pre, tid);
         }
         if (a.ll_probe == 2 && p + 1 < a.n_phases) { // this CTA's outputs of phase p are stored (or it had none)
             __syncthreads();
@@ -1289,13 +1303,10 @@ decode_mega_kernel(const MegaArgs a) {
     }
 }
 
-void mega_fill_knobs(MegaArgs &a) {
-    static const int poll_ns = getenv("B200LLM_LL_POLL_NS") ? atoi(getenv("B200LLM_LL_POLL_NS")) : 32;
-    static const int probe = getenv("B200LLM_LL_PROBE") ? atoi(getenv("B200LLM_LL_PROBE")) : 0; // measured on Llama-3-8B: 0 -> 1.67 ms, 1 -> 1.99 ms, 2 -> 1.88 ms per token
-    static const unsigned ahead = getenv("B200LLM_MEGA_L2_AHEAD") ? (unsigned)atoi(getenv("B200LLM_MEGA_L2_AHEAD")) / 16 * 16 : 0u;
-    a.ll_poll_ns = poll_ns;
-    a.ll_probe = probe;
-    a.l2_ahead = ahead;
+void mega_fill_knobs(MegaArgs &a) { // read at every launch on purpose: the tests flip them inside one process
+    const char *ns = getenv("B200LLM_LL_POLL_NS"), *pr = getenv("B200LLM_LL_PROBE");
+    a.ll_poll_ns = ns ? atoi(ns) : 32;
+    a.ll_probe = pr ? atoi(pr) : 0; // measured on Llama-3-8B: 0 -> 1.67 ms per token, 2 -> 1.88
 }
 
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s) {

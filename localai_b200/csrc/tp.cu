@@ -411,6 +411,7 @@ void Model::tp_build_fused() {
         int coop = 0;
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, m.device);
         if (!coop) ok = false;
+        if (getenv("B200LLM_MEGA_DBG")) m.mega_dbg_ = (long long *)m.dalloc((size_t)m.n_sm_ * m.mega_n_phases_ * 16 * sizeof(long long));
     }
     B2_CUDA(cudaSetDevice(device));
     for (auto *mp : g.shard) mp->tp_fused_ready_ = ok;
@@ -443,6 +444,7 @@ void Model::run_decode_mega_tp(int t0, int out_row0) {
     a.hint = mega_hint_;
     a.hint_base = mega_hint_base_;
     if (a.ll_probe == 2) mega_hint_base_ += (unsigned)n_sm_ * (unsigned)(mega_n_phases_ - 1);
+    a.dbg = mega_dbg_;
     // the logits row of this step (unwanted rows go to a spare row past the last one the caller can ask for)
     const int row = out_row0 >= 0 ? out_row0 : logits_rows_cap_ - 1;
     a.out_override = logits_ + (size_t)row * hp.n_vocab + (size_t)tp_rank * vocab_l;

@@ -111,6 +111,15 @@ class Ranks:
         if self.dist is not None:
             self.dist.barrier()
 
+    def host_barrier(self):
+        """A barrier that keeps the GPUs free while ranks wait (a gloo group): for the legs where ONE rank drives several
+        devices -- the waiting ranks' NCCL barrier kernel would otherwise spin on the very GPUs being measured."""
+        if self.dist is None:
+            return
+        if getattr(self, "_gloo", None) is None:
+            self._gloo = self.dist.new_group(backend="gloo")
+        self.dist.barrier(group=self._gloo)
+
     def _reduce(self, x: float, op: str) -> float:
         if self.dist is None:
             return float(x)

@@ -14,6 +14,7 @@ L = capi.lib(); L.b2_mega_debug.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
 n = L.b2_mega_debug(e._h, None, 0)
 buf = np.zeros(n, dtype=np.int64); L.b2_mega_debug(e._h, buf.ctypes.data_as(C.c_void_p), n)
 nph = n // 16 // 148; d = buf.reshape(148, nph, 16).astype(np.float64)
+os.makedirs('gpurun_out', exist_ok=True); np.save('gpurun_out/r2_mega_dbg_raw.npy', buf.reshape(148, nph, 16))
 t00 = d[:, 0, 0].min()
 kinds = ["qkv", "att", "wo", "gateup", "down"]
 print("all times in ns (global timer); per phase kind, mean over layers 2..30")
@@ -35,3 +36,12 @@ last = d[:, 10:nph - 6, 3].argmax(0); cnt = np.bincount(last, minlength=148)
 print("CTAs that most often finish a phase last:", np.argsort(-cnt)[:10].tolist(), cnt[np.argsort(-cnt)[:10]].tolist())
 first_in = d[:, 10:nph - 6, 1].argmax(0); cnt = np.bincount(first_in, minlength=148)
 print("CTAs whose input is ready last most often:", np.argsort(-cnt)[:10].tolist(), cnt[np.argsort(-cnt)[:10]].tolist())
+
+# is the spread systematic?  per-CTA mean of (phase end - earliest phase end) for the two big phases, over layers
+for k, name in ((3, "gateup"), (4, "down"), (0, "qkv"), (2, "wo")):
+    idx = np.arange(k + 10, nph - 6, 5)
+    late = d[:, idx, 3] - d[:, idx, 3].min(0)            # how long after the first CTA this CTA ends the phase
+    til = d[:, idx, 2] - d[:, idx, 1]
+    print(f"{name}: lateness at phase end (ns): mean over CTAs {late.mean():.0f}; per-CTA means: std {late.mean(1).std():.0f}, min {late.mean(1).min():.0f}, max {late.mean(1).max():.0f}; "
+          f"within-CTA std over layers {late.std(1).mean():.0f}; tile time per-CTA means: std {til.mean(1).std():.0f} of {til.mean():.0f}")
+    worst = np.argsort(-late.mean(1))[:12]; print("   latest CTAs:", worst.tolist(), late.mean(1)[worst].round(0).tolist())

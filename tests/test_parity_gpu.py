@@ -236,19 +236,20 @@ def test_greedy_long_context(model_files, n_prompt, monkeypatch):
     assert got.tolist() == want.tolist()
 
 
-def test_mega_barrier_counters_wrap_around(model_files, monkeypatch):
-    """the persistent kernel's grid-barrier and per-head counters only grow and are compared modulo 2^32: start them
-    just below the wrap and decode across it"""
+def test_mega_tags_wrap_around(model_files, monkeypatch):
+    """the decode kernel's hand-over tags (phase number of the launch sequence, 16 per decode step for this model) and its
+    phase counter only grow and are compared modulo 2^32: start them just below the wrap and decode across it, in both
+    waiting modes (every warp polls its slice / one thread polls the phase counter first)"""
     path = model_files["mini_q4_k_m"]
     ref = O.OracleModel(path, n_ctx=160)
     prompt = np.random.default_rng(21).integers(0, ref.n_vocab, 40).astype(np.int32)
     want, _, _ = ref.generate_greedy(prompt, 48)
-    # the grid counter advances by CTAs x barriers (~2800) per step, the per-head counters by layers x parts (12)
-    for below in (3000, 100):
+    for probe, below in (("0", 300), ("0", 7), ("2", 20000), ("2", 300)):
+        monkeypatch.setenv("B200LLM_LL_PROBE", probe)
         monkeypatch.setenv("B200LLM_MEGA_COUNTER0", str(2 ** 32 - below))
         with capi.Engine(path, n_ctx=160, n_batch=32) as e:
             got, _, _ = e.decode_greedy(prompt, 48)
-        assert got.tolist() == want.tolist(), f"counters started {below} below the wrap"
+        assert got.tolist() == want.tolist(), f"tags started {below} below the wrap (waiting mode {probe})"
 
 
 @pytest.mark.parametrize("name", ["mini_q4_k_m", "micro_q8_0"])
