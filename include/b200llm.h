@@ -291,6 +291,8 @@ int b2_bench_prefill(b2_engine *e, int n_tokens, int n_iters, int n_warmup, doub
 /* b2_bench_gemv: times the streaming dequant-GEMV kernel alone (CUDA events on the engine's stream) over one
  * weight matrix of EVERY layer in turn (so each launch reads weights that are not in L2), n_rounds times.
  * which: 0 wq, 1 wk, 2 wv, 3 wo, 4 ffn_gate, 5 ffn_up, 6 ffn_down, 7 output (lm_head; single matrix).
+ * n_tok 1..4: the decode kernels; 5..64: the batched-decode GEMM that dequantises inside the kernel, for which
+ * which = 8 (wq|wk|wv) and 9 (ffn_gate|ffn_up) time the multi-matrix launches the engine makes.
  * Returns average ms per launch, algorithmic bytes per launch (rows x row bytes) and the ggml type id. */
 int b2_bench_gemv(b2_engine *e, int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch,
                   int *ggml_type);
@@ -306,7 +308,8 @@ int b2_bench_gemv(b2_engine *e, int which, int n_tok, int n_rounds, double *ms_p
  * b2_mul_mat: out[t][r] = dot(W[r,:], quantise(x[t,:])), W = rows x cols of `wtype`, x = n_tok x cols f32.
  *   path: 0 = auto, 1 = streaming dequant-GEMV (one op per kernel), 2 = tensor-core GEMM (prefill path),
  *         3 = fused decode kernel (quantises in its prologue), 5 = fused decode kernel on pre-quantised rows,
- *         4 = persistent decode mega-kernel with a single mat-vec phase (n_tok = 1, even rows).
+ *         4 = persistent decode mega-kernel with a single mat-vec phase (n_tok = 1, even rows),
+ *         6 = batched-decode GEMM that dequantises inside the kernel (Q4_K / Q5_K / Q6_K / Q8_0, n_tok <= 64).
  */
 int b2_dequantize(int type, const void *blocks, int64_t n_elems, float *out);
 int b2_quantize_act(int wtype, const float *x, int64_t n_elems, void *out, size_t out_cap);

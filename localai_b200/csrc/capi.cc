@@ -348,7 +348,7 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     B2_CHECK(rows > 0 && cols > 0 && n_tok > 0 && cols % (type_tiles_only(wtype) ? std::max(64, type_block_elems(wtype)) : 256) == 0, B2_EINVAL,
              "bad shape (cols must be a multiple of 256; 64 for the legacy 32-element block types)");
     B2_CHECK(!type_tiles_only(wtype) || path == 2, B2_EUNSUPPORTED, "Q4_0 / Q4_1 / Q5_0 / Q5_1 / Q2_K / Q3_K / IQ4_NL / IQ4_XS run on the tensor-core path (2) only");
-    B2_CHECK(path >= 0 && path <= 5, B2_EUNSUPPORTED, "unknown mat-mul path");
+    B2_CHECK(path >= 0 && path <= 6, B2_EUNSUPPORTED, "unknown mat-mul path");
     DevBuf staging((size_t)(rows * gguf_row_bytes(wtype, cols))), dst((size_t)(rows * device_row_stride(wtype, cols)));
     DTensor W = upload_matrix(wtype, blocks, rows, cols, staging, dst);
     const ActFmt f = act_format_for(wtype);
@@ -362,6 +362,18 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
         DevBuf wt(gemm_w_tiles_bytes(rows, cols)), xt(gemm_x_tiles_bytes(n_tok, cols)), sk((size_t)32 << 20);
         launch_gemm_prepare_x(dx.as<float>(), cols, n_tok, cols, xt.p, 0);
         launch_gemm_tc(W, xt.p, n_tok, dout.as<float>(), rows, nullptr, 0, wt.p, false, sk.as<float>(), (size_t)32 << 20, 0);
+        B2_CUDA(cudaDeviceSynchronize());
+    } else if (path == 6) { // batched-decode GEMM that dequantises inside the kernel (fp16 operands, fp32 accumulate)
+        B2_CHECK(qgemm_type_supported(wtype) && n_tok <= QGEMM_MAX_TOKENS, B2_EUNSUPPORTED, "qgemm path: Q4_K / Q5_K / Q6_K / Q8_0, at most 64 tokens");
+        int n_sm = 0;
+        B2_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, 0));
+        DevBuf qt(qgemm_w_bytes(wtype, rows, cols)), xt(qgemm_x_bytes(n_tok, cols)), part(qgemm_partial_bytes(n_sm)), cnt(QGEMM_COUNTERS * 4);
+        B2_CUDA(cudaMemset(cnt.p, 0, QGEMM_COUNTERS * 4));
+        launch_qgemm_repack(W, qt.p, 0);
+        launch_qgemm_prepare_x(dx.as<float>(), cols, n_tok, cols, xt.p, 0);
+        QGemmJob j{&W, qt.p, dout.as<float>(), rows};
+        for (int rep = 0; rep < 2; rep++) // twice: the second launch runs on the counters the first one left behind
+            launch_qgemm_multi(&j, 1, xt.p, n_tok, nullptr, 0, part.as<float>(), qgemm_partial_bytes(n_sm), cnt.as<unsigned>(), QGEMM_COUNTERS, n_sm, 0);
         B2_CUDA(cudaDeviceSynchronize());
     } else if (path == 3 || path == 5) { // fused decode kernel: 3 = quantise in the prologue, 5 = pre-quantised rows
         FusedGemv a;
@@ -402,6 +414,8 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     return 0;
     B2_API_END(0)
 }
+
+extern "C" int b2_qgemm_debug(long long *out, int n) { return b2::qgemm_debug_read(out, n); } // profiling builds only (not in the header)
 
 struct b2_bert {
     std::unique_ptr<BertModel> m;

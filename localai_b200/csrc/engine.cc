@@ -347,7 +347,7 @@ int Engine::mega_debug(long long *out, int cap) {
 
 int Engine::bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type) {
     Model &m = model();
-    B2_CHECK(which >= 0 && which <= 7 && n_tok >= 1 && n_tok <= 4 && n_rounds > 0, B2_EINVAL, "bench_gemv: bad arguments");
+    B2_CHECK(which >= 0 && which <= 9 && n_tok >= 1 && n_tok <= QGEMM_MAX_TOKENS && n_rounds > 0, B2_EINVAL, "bench_gemv: bad arguments");
     std::lock_guard<std::mutex> lk(dev_mu_);
     return m.bench_gemv(which, n_tok, n_rounds, ms_per_launch, bytes_per_launch, ggml_type);
 }

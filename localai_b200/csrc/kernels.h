@@ -233,6 +233,35 @@ struct GemmJob {
 void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,
                           float *splitk_scratch, size_t splitk_bytes, cudaStream_t s);
 
+// --- batched decode mat-mul with the dequantisation inside the GEMM (kernels_qgemm.cu) --------------------------------
+constexpr int QGEMM_MAX_TOKENS = 64;
+bool qgemm_type_supported(int type);                          // Q4_K, Q5_K, Q6_K, Q8_0
+size_t qgemm_w_bytes(int type, int64_t rows, int64_t cols);   // of the tile-major repacked copy of a matrix
+size_t qgemm_x_bytes(int n_tok, int64_t cols);                // of the fp16 activation tiles
+void launch_qgemm_repack(const DTensor &W, void *q_tiles, cudaStream_t s);
+// fp32 activations -> fp16 operand tiles (plain, RMSNorm(x) * w, silu(gate) * up)
+void launch_qgemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
+void launch_qgemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const float *w, int n_tok, int64_t K, float eps, void *x_tiles,
+                                    cudaStream_t s);
+void launch_qgemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
+struct QGemmJob {
+    const DTensor *W;
+    const void *q_tiles; // launch_qgemm_repack(W)
+    float *out;
+    int64_t out_stride;
+};
+struct QGemmPlan {
+    int T, panels, grid; // tiles per panel, panels, CTAs
+    int64_t units;       // panels * K / 256
+};
+int qgemm_debug_read(long long *host, int n); // profiling builds (-DQG_DBG) only; 0 otherwise
+void qgemm_plan(int n_tiles, int nkb, int n_sm, bool allow_pairs, QGemmPlan *pl);
+inline size_t qgemm_partial_bytes(int n_sm) { return (size_t)2 * n_sm * 2 * 64 * 128 * 4; } // two partial segments (of two 128 x 64 tiles) per CTA at most
+constexpr size_t QGEMM_COUNTERS = 1 << 16;                                   // tile quarters: 16384 tiles = 2 M rows
+// out[t][r] = W[r] . x[t] (+ residual) for up to three matrices that share x; 1..64 tokens; one launch, split-K reduced inside
+void launch_qgemm_multi(const QGemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,
+                        float *partial, size_t partial_bytes, unsigned *counters, size_t n_counters, int n_sm, cudaStream_t s);
+
 // --- sampling -------------------------------------------------------------------------------------------
 // out[r] = first argmax of row r.  If feed_tok/feed_pos are given (device-side decode loop) the sampled id is also
 // written to feed_tok[r] and feed_pos[r] is incremented, so the next step needs no host round trip.

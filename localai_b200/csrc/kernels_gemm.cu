@@ -336,15 +336,25 @@ __device__ __forceinline__ uint64_t gm_desc(uint32_t saddr, uint32_t lbo, uint32
 __device__ __forceinline__ void gm_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n"
-        ".reg .pred p;\n"
+        ".reg .pred p, e;\n"
+        "elect.sync _|e, 0xffffffff;\n"
         "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d),
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// gm_mma / gm_commit are called by a CONVERGED warp and issue from one elected lane: the operands of tcgen05.mma live in
+// uniform registers, and inside a `lane == 0` branch the compiler cannot prove them warp-uniform -- it then wraps every
+// MMA in an election loop (R2UR.BROADCAST + BRA.U.ANY), about 85 cycles of issue per instruction
 __device__ __forceinline__ void gm_commit(uint64_t *bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(gm_s32(bar)) : "memory");
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}\n" ::"r"(gm_s32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ bool gm_elect() {
+    uint32_t e;
+    asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(e));
+    return e != 0;
 }
 __device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
@@ -411,7 +421,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
     uint64_t *tfull = empty + GM_STAGES;   // [2] accumulator ready
     uint64_t *tempty = tfull + 2;          // [2] accumulator drained
     uint32_t *tmem_slot = (uint32_t *)(tempty + 2);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31; // (the shuffle marks it warp-uniform)
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full + i, 1); gm_mbar_init(empty + i, 1); }
@@ -425,13 +435,13 @@ gemm_tcgen05_kernel(const GemmArgs g) {
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
     const int n_tiles_total = g.m_tiles * g.n_tiles * g.ksplit; // work items
     // kind::f16, D = f32, A = B = bf16, both K-major, N = 256, M = 128
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(GM_BN >> 3) << 17) | ((uint32_t)(GM_BM >> 4) << 24);
 
     if (warp == 0) {
-        if (lane == 0) { // ===== producer: one bulk copy per operand tile
+        { // ===== producer: one bulk copy per operand tile (the whole warp walks the schedule, an elected lane issues)
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
                 const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
@@ -442,14 +452,16 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                     const int s = it % GM_STAGES;
                     gm_mbar_wait(empty + s, ((it / GM_STAGES) & 1) ^ 1);
                     uint8_t *sa = stages + (size_t)s * GM_STAGE_BYTES;
-                    gm_mbar_expect_tx(full + s, GM_STAGE_BYTES);
-                    gm_bulk_g2s(sa, g.a_tiles + ((int64_t)mt * g.k_tiles + kt) * (GM_BM * GM_BK), GM_A_BYTES, full + s);
-                    gm_bulk_g2s(sa + GM_A_BYTES, bt + (int64_t)kt * (GM_BN * GM_BK), GM_B_BYTES, full + s);
+                    if (gm_elect()) {
+                        gm_mbar_expect_tx(full + s, GM_STAGE_BYTES);
+                        gm_bulk_g2s(sa, g.a_tiles + ((int64_t)mt * g.k_tiles + kt) * (GM_BM * GM_BK), GM_A_BYTES, full + s);
+                        gm_bulk_g2s(sa + GM_A_BYTES, bt + (int64_t)kt * (GM_BN * GM_BK), GM_B_BYTES, full + s);
+                    }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) { // ===== MMA issuer
+        { // ===== MMA issuer (whole warp, elected lane)
             uint32_t it = 0, acc_it = 0;
             for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
                 const int acc = acc_it & 1;

@@ -86,6 +86,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     no_graph_ = getenv("B200LLM_NO_GRAPH") && atoi(getenv("B200LLM_NO_GRAPH")) != 0;
     no_mega_ = getenv("B200LLM_NO_MEGA") && atoi(getenv("B200LLM_NO_MEGA")) != 0;
     no_gemm_ = getenv("B200LLM_NO_GEMM") && atoi(getenv("B200LLM_NO_GEMM")) != 0;
+    no_qgemm_ = getenv("B200LLM_NO_QGEMM") && atoi(getenv("B200LLM_NO_QGEMM")) != 0;
     no_shadow_ = getenv("B200LLM_NO_BF16_TILES") && atoi(getenv("B200LLM_NO_BF16_TILES")) != 0;
     if (getenv("B200LLM_GEMM_MIN_TOKENS")) gemm_min_tokens_ = atoi(getenv("B200LLM_GEMM_MIN_TOKENS"));
     else gemm_min_tokens_ = -1; // automatic, see gemm_threshold()
@@ -251,6 +252,7 @@ Model::~Model() {
     mega_streams_.free();
     if (logits_) cudaFree(logits_);
     for (auto &kv : w_tiles_) cudaFree(kv.second);
+    for (auto &kv : q_tiles_) cudaFree(kv.second);
     if (gemm_w_) cudaFree(gemm_w_);
     if (gemm_x_) cudaFree(gemm_x_);
     if (staging_) cudaFree(staging_);
@@ -498,6 +500,85 @@ void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     gemm(L.down, n, x_, d, x_, d);
 }
 
+// ---- batched decode, 2..64 tokens: the weights stay quantised all the way into the tensor-core kernel (kernels_qgemm.cu)
+void *Model::resident_qtiles(const DTensor &W) {
+    auto it = q_tiles_.find(W.data);
+    if (it != q_tiles_.end()) return it->second;
+    if (!qgemm_type_supported(W.type) || W.cols % 256 != 0) return nullptr;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cs);
+    if (cs != cudaStreamCaptureStatusNone) return nullptr;
+    const size_t bytes = qgemm_w_bytes(W.type, W.rows, W.cols);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < bytes + shadow_reserve_) return nullptr;
+    void *p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    launch_qgemm_repack(W, p, stream);
+    q_tiles_[W.data] = p;
+    return p;
+}
+
+bool Model::qgemm_layer_ready(const LayerW &L) {
+    const DTensor *ws[7] = {&L.wq, &L.wk, &L.wv, &L.wo, &L.gate, &L.up, &L.down};
+    for (const DTensor *w : ws)
+        if (!resident_qtiles(*w)) return false;
+    return true;
+}
+
+bool Model::qgemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n, const float *residual,
+                        int64_t res_stride) {
+    if (n_sm_ <= 0) B2_CUDA(cudaDeviceGetAttribute(&n_sm_, cudaDevAttrMultiProcessorCount, device));
+    const size_t part_bytes = qgemm_partial_bytes(n_sm_);
+    if (!qg_part_) {
+        qg_part_ = (float *)dalloc(part_bytes);
+        qg_counters_ = (unsigned *)dalloc(QGEMM_COUNTERS * sizeof(unsigned));
+        B2_CUDA(cudaMemsetAsync(qg_counters_, 0, QGEMM_COUNTERS * sizeof(unsigned), stream));
+    }
+    QGemmJob jobs[3];
+    for (int j = 0; j < n_jobs; j++) {
+        void *t = resident_qtiles(*Ws[j]);
+        if (!t) return false;
+        jobs[j] = QGemmJob{Ws[j], t, outs[j], strides[j]};
+    }
+    launch_qgemm_multi(jobs, n_jobs, gemm_x_, n, residual, res_stride, qg_part_, part_bytes, qg_counters_, QGEMM_COUNTERS, n_sm_, stream);
+    return true;
+}
+
+void Model::run_layer_qgemm(const LayerW &L, const KVLayout &kv, int n) {
+    const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hd;
+    ensure_gemm_scratch(0, gemm_x_tiles_bytes(n, std::max(d, ff)));
+    launch_qgemm_prepare_x_rmsnorm(x_, d, (const float *)L.attn_norm.data, n, d, hp.rms_eps, gemm_x_, stream);
+    {
+        const DTensor *Ws[3] = {&L.wq, &L.wk, &L.wv};
+        float *outs[3] = {q_, k_, v_};
+        const int64_t strides[3] = {d, kvd, kvd};
+        B2_CHECK(qgemm_multi(Ws, outs, strides, 3, n, nullptr, 0), B2_ESTATE, "qgemm: tiles missing");
+    }
+    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+    attention(kv, n);
+    launch_qgemm_prepare_x(att_, d, n, d, gemm_x_, stream);
+    {
+        const DTensor *Ws[1] = {&L.wo};
+        float *outs[1] = {x_};
+        const int64_t strides[1] = {d};
+        B2_CHECK(qgemm_multi(Ws, outs, strides, 1, n, x_, d), B2_ESTATE, "qgemm: tiles missing");
+    }
+    launch_qgemm_prepare_x_rmsnorm(x_, d, (const float *)L.ffn_norm.data, n, d, hp.rms_eps, gemm_x_, stream);
+    {
+        const DTensor *Ws[2] = {&L.gate, &L.up};
+        float *outs[2] = {gate_, up_};
+        const int64_t strides[2] = {ff, ff};
+        B2_CHECK(qgemm_multi(Ws, outs, strides, 2, n, nullptr, 0), B2_ESTATE, "qgemm: tiles missing");
+    }
+    launch_qgemm_prepare_x_swiglu(gate_, up_, n, ff, gemm_x_, stream);
+    {
+        const DTensor *Ws[1] = {&L.down};
+        float *outs[1] = {x_};
+        const int64_t strides[1] = {d};
+        B2_CHECK(qgemm_multi(Ws, outs, strides, 1, n, x_, d), B2_ESTATE, "qgemm: tiles missing");
+    }
+}
+
 static bool layer_fusable(const LayerW &L) {
     const ActFmt f = act_format_for(L.wq.type);
     return f != ACT_F32 && act_format_for(L.wk.type) == f && act_format_for(L.wv.type) == f && L.gate.type == L.up.type &&
@@ -512,7 +593,8 @@ void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
         const LayerW &L = layers[l];
         KVLayout kv{k_pool_ + (size_t)l * pool_layer_stride_, v_pool_ + (size_t)l * pool_layer_stride_, page_table_, page_size,
                     max_pages, kvd};
-        if (!no_gemm_ && n > gemm_threshold()) run_layer_gemm(L, kv, n);
+        if (!no_gemm_ && !no_qgemm_ && n >= 2 && n <= QGEMM_MAX_TOKENS && qgemm_layer_ready(L)) run_layer_qgemm(L, kv, n);
+        else if (!no_gemm_ && n > gemm_threshold()) run_layer_gemm(L, kv, n);
         else if (!unfused_ && n <= 4 && layer_fusable(L)) run_layer_fused(L, kv, n); // larger batches: quantise once, not per CTA
         else run_layer_unfused(L, kv, n);
         if (dbg_hidden_)
@@ -521,7 +603,16 @@ void Model::run_graph(int n, const int32_t *out_rows_dev, int n_out) {
     if (n_out != 0) {
         const int rows = n_out < 0 ? n : n_out;
         ensure_logits_rows(rows);
-        if (!no_gemm_ && rows > gemm_threshold()) {
+        if (!no_gemm_ && !no_qgemm_ && rows >= 2 && rows <= QGEMM_MAX_TOKENS && resident_qtiles(output)) {
+            launch_rmsnorm(x_, d, n_out < 0 ? nullptr : out_rows_dev, (const float *)output_norm.data, xn_out_, d, rows, d, hp.rms_eps,
+                           stream);
+            ensure_gemm_scratch(0, gemm_x_tiles_bytes(rows, d));
+            launch_qgemm_prepare_x(xn_out_, d, rows, d, gemm_x_, stream);
+            const DTensor *Ws[1] = {&output};
+            float *outs[1] = {logits_};
+            const int64_t strides[1] = {hp.n_vocab};
+            B2_CHECK(qgemm_multi(Ws, outs, strides, 1, rows, nullptr, 0), B2_ESTATE, "qgemm: tiles missing");
+        } else if (!no_gemm_ && rows > gemm_threshold()) {
             launch_rmsnorm(x_, d, n_out < 0 ? nullptr : out_rows_dev, (const float *)output_norm.data, xn_out_, d, rows, d, hp.rms_eps,
                            stream);
             ensure_gemm_scratch(0, gemm_x_tiles_bytes(rows, d));
@@ -814,6 +905,7 @@ int Model::bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch,
         if (t) ws.push_back(t);
     }
     if (which == 7) ws.push_back(&output);
+    if (which >= 8) ws.push_back(which == 8 ? &layers[0].wq : &layers[0].gate); // 8 = wq|wk|wv, 9 = gate|up as one launch (batched decode)
     B2_CHECK(!ws.empty(), B2_EINVAL, "bench_gemv: no such tensor");
     const DTensor &W0 = *ws[0];
     const int64_t K = W0.cols;
@@ -824,6 +916,45 @@ int Model::bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch,
     std::vector<float> hx((size_t)n_tok * K);
     for (size_t i = 0; i < hx.size(); i++) hx[i] = sinf(0.37f * (float)i) * 1.5f;
     B2_CUDA(cudaMemcpyAsync(xin, hx.data(), hx.size() * 4, cudaMemcpyHostToDevice, stream));
+    if (n_tok > 4 || which >= 8) { // batched decode: the GEMM that dequantises inside the kernel, one launch per layer
+        std::vector<std::vector<const DTensor *>> jobs;
+        if (which >= 8) {
+            for (auto &L : layers) jobs.push_back(which == 8 ? std::vector<const DTensor *>{&L.wq, &L.wk, &L.wv} : std::vector<const DTensor *>{&L.gate, &L.up});
+        } else {
+            for (auto *w : ws) jobs.push_back({w});
+        }
+        ensure_gemm_scratch(0, gemm_x_tiles_bytes(n_tok, K));
+        launch_qgemm_prepare_x(xin, K, n_tok, K, gemm_x_, stream);
+        float *outs[3] = {which == 7 ? logits_ : q_, k_, v_};
+        if (which == 9 || which == 4 || which == 5) { outs[0] = gate_; outs[1] = up_; }
+        int64_t bytes = 0;
+        auto run = [&](bool count) {
+            for (auto &jb : jobs) {
+                int64_t strides[3];
+                for (size_t j = 0; j < jb.size(); j++) {
+                    strides[j] = jb[j]->rows;
+                    if (count) bytes += jb[j]->rows * gguf_row_bytes(jb[j]->type, jb[j]->cols);
+                }
+                B2_CHECK(qgemm_multi(jb.data(), outs, strides, (int)jb.size(), n_tok, nullptr, 0), B2_EUNSUPPORTED, "bench_gemv: no qgemm tiles for this tensor");
+            }
+        };
+        run(true); // warm-up round (builds the tile-major copies)
+        cudaEvent_t e0, e1;
+        B2_CUDA(cudaEventCreate(&e0));
+        B2_CUDA(cudaEventCreate(&e1));
+        B2_CUDA(cudaEventRecord(e0, stream));
+        for (int r = 0; r < n_rounds; r++) run(false);
+        B2_CUDA(cudaEventRecord(e1, stream));
+        B2_CUDA(cudaStreamSynchronize(stream));
+        float ms = 0;
+        B2_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        if (ms_per_launch) *ms_per_launch = ms / ((double)n_rounds * jobs.size());
+        if (bytes_per_launch) *bytes_per_launch = bytes / (int64_t)jobs.size();
+        if (ggml_type) *ggml_type = W0.type;
+        return 0;
+    }
     uint8_t *xq;
     ActFmt f;
     invalidate_acts();

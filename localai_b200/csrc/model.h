@@ -139,6 +139,16 @@ class Model {
     int gemm_min_tokens_ = -1; // B200LLM_GEMM_MIN_TOKENS; -1 = automatic
     int gemm_threshold() const;
     bool tiles_only_ = false; // some weight is in a format only the tensor-core path reads
+    // batched decode (2..64 tokens): mat-muls that dequantise inside the GEMM (kernels_qgemm.cu) on a tile-major copy of the weights
+    std::unordered_map<const uint8_t *, void *> q_tiles_;
+    float *qg_part_ = nullptr;
+    unsigned *qg_counters_ = nullptr;
+    bool no_qgemm_ = false;   // B200LLM_NO_QGEMM=1: the bf16-tile path for every batch size (A/B tests)
+    void *resident_qtiles(const DTensor &W);
+    bool qgemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n, const float *residual,
+                     int64_t res_stride);
+    bool qgemm_layer_ready(const LayerW &L);
+    void run_layer_qgemm(const LayerW &L, const KVLayout &kv, int n);
     void build_mega();
     void run_decode_mega();
     MegaPhase *mega_phases_ = nullptr;

@@ -1,2 +1,6 @@
-#!/bin/bash
-B200LLM_MEGA_DBG=1 timeout 900 python scratch/tp_bench.py llama3-70b 2 2>&1 | grep -v Warning | tail -10
+cd /root/repo
+timeout 300 python scratch/b64_bench.py 2>&1 | tail -2
+NB=16 timeout 300 python scratch/b64_bench.py 2>&1 | tail -1
+NB=4 timeout 300 python scratch/b64_bench.py 2>&1 | tail -1
+timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -8
+B200LLM_NO_GRAPH=1 STEPS=2 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/b64q_launches.csv python scratch/b64_bench.py > gpurun_out/b64q_ncu.log 2>&1; echo rc=$?

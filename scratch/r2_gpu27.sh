@@ -1,0 +1,2 @@
+cd /root/repo
+B200LLM_NO_GRAPH=1 STEPS=2 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/b64q_launches.csv python scratch/b64_bench.py > gpurun_out/b64q_ncu.log 2>&1; echo rc=$?

@@ -156,6 +156,29 @@ def test_gemm_tcgen05_matches_float_reference(wtype, rows, cols, n_tok):
     assert np.abs(got - ref).max() <= GEMM_TC_RTOL * np.abs(ref).max()
 
 
+# fp16 operands (q exact, d*sc and dmin*m rounded to fp16, one fused multiply-add), fp32 accumulation: each product is
+# off by about 3 x 2^-11 relative, the errors of a row's K products add like a random walk
+QGEMM_RTOL = 2e-3
+
+
+@pytest.mark.parametrize("wtype,rows,cols,n_tok", [
+    (capi.B2_T_Q4_K, 128, 256, 16), (capi.B2_T_Q4_K, 4096, 4096, 64), (capi.B2_T_Q4_K, 28672, 4096, 64), (capi.B2_T_Q4_K, 512, 8192, 17),
+    (capi.B2_T_Q6_K, 1024, 14336, 64), (capi.B2_T_Q6_K, 300, 512, 2), (capi.B2_T_Q6_K, 16384, 2048, 33),
+    (capi.B2_T_Q5_K, 1024, 4096, 48), (capi.B2_T_Q5_K, 200, 1024, 7), (capi.B2_T_Q8_0, 256, 2048, 5), (capi.B2_T_Q8_0, 2048, 2048, 64)])
+def test_qgemm_matches_float_reference(wtype, rows, cols, n_tok):
+    """batched decode (2..64 tokens): the GEMM that dequantises inside the kernel (fp16 operand in TMEM) vs float64"""
+    import make_gguf as mg
+    rng = np.random.default_rng(rows + cols + n_tok)
+    raw = mg.random_blocks(rng, wtype, rows * cols // mg.BLOCK[wtype][0], 1 / np.sqrt(cols)).reshape(-1)
+    w = O.dequantize(wtype, raw, rows * cols).reshape(rows, cols).astype(np.float64)
+    x = rng.standard_normal((n_tok, cols)).astype(np.float32)
+    ref = x.astype(np.float64) @ w.T
+    got = capi.mul_mat(wtype, raw, rows, cols, x, path=6)
+    assert np.isfinite(got).all()
+    err = np.abs(got - ref).max() / np.abs(ref).max()
+    assert err <= QGEMM_RTOL, err
+
+
 def test_mul_mat_linearity_in_rows():
     """size-independent property: rows are independent, so any row subset gives the same values."""
     import make_gguf as mg
