@@ -234,6 +234,16 @@ int b2_mega_debug(b2_engine *e, long long *out, int cap) {
     B2_API_END(0)
 }
 
+// undocumented test hook (not part of the ABI header; needs no device): replay the batched-decode GEMM's work split
+// (stream-K ranges, split-K segment arithmetic, partial slots) for a launch of n_tiles 128-row tiles x nkb super-blocks.
+// Returns the number of tiles whose K range is split over several CTAs, or a negative error code.
+int64_t b2_qgemm_plan_check(int n_tiles, int nkb, int n_sm) {
+    B2_API_BEGIN
+    B2_CHECK(n_tiles > 0 && nkb > 0 && n_sm > 0, B2_EINVAL, "b2_qgemm_plan_check: bad arguments");
+    return qgemm_plan_check(n_tiles, nkb, n_sm);
+    B2_API_END(0)
+}
+
 // undocumented test hook (not part of the ABI header; needs no device): plan the decode kernel's weight streams for a
 // phase list given as 9 int64 per phase {kind, K, n_jobs, type0, rows0, type1, rows1, type2, rows2} and replay every
 // warp's walk over them.  Returns the stream bytes, or a negative error code when the planner is inconsistent.

@@ -6,6 +6,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <utility>
 
 #include "../../include/b200llm.h"
 
@@ -47,6 +48,28 @@ struct PerDeviceOnce {
         if (dev < 64) done |= 1ull << dev;
     }
 };
+
+// Programmatic dependent launch (the kernels of a batched decode step, B200LLM_NO_PDL=1 turns it off): the next kernel of
+// the stream may be set up while this one still runs; it blocks in B2_PDL_WAIT() -- before its first access to anything an
+// earlier kernel of the stream may have written or may still read -- until the previous kernel has completed and flushed.
+// Every kernel launched this way waits before it exits, so completion is transitive along the stream.  Both instructions
+// are no-ops in a kernel launched without the attribute.
+#ifdef __CUDACC__
+#define B2_PDL_TRIGGER() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+#define B2_PDL_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    B2_CUDA(cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...));
+}
+#endif
 
 // ---- tensor types (ggml ids) and on-device layouts -------------------------------------------------
 // Q4_K / Q5_K / F16 / F32 rows keep the GGUF layout (their blocks are 16-byte multiples).

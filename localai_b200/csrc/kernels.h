@@ -156,6 +156,7 @@ struct MegaArgs {
     int ll_poll_ns = 32;     // sleep between two polls of an LL word (B200LLM_LL_POLL_NS)
     int ll_probe = 0;        // how a CTA waits for its input row before loading it (B200LLM_LL_PROBE): 0 = every warp polls its slice,
                              // 2 = one thread polls the phase counter `hint` first
+    int wait_prefetch = 0;   // bytes of its stream a warp pulls into L2 when it finishes a phase (B200LLM_MEGA_WAIT_PREFETCH; 0 = off)
     unsigned *hint = nullptr; // phase counter: every CTA adds 1 (relaxed, no fence: the tags stay the proof) when it has stored a phase's outputs
     unsigned hint_base = 0;   // its value when this launch starts; the host adds n_cta * n_phases per launch
     const MegaPhase *phases = nullptr; // device
@@ -256,6 +257,7 @@ struct QGemmPlan {
 };
 int qgemm_debug_read(long long *host, int n); // profiling builds (-DQG_DBG) only; 0 otherwise
 void qgemm_plan(int n_tiles, int nkb, int n_sm, bool allow_pairs, QGemmPlan *pl);
+int64_t qgemm_plan_check(int n_tiles, int nkb, int n_sm); // host-only replay of the kernel's work split; throws on an inconsistency
 inline size_t qgemm_partial_bytes(int n_sm) { return (size_t)2 * n_sm * 2 * 64 * 128 * 4; } // two partial segments (of two 128 x 64 tiles) per CTA at most
 constexpr size_t QGEMM_COUNTERS = 1 << 16;                                   // tile quarters: 16384 tiles = 2 M rows
 // out[t][r] = W[r] . x[t] (+ residual) for up to three matrices that share x; 1..64 tokens; one launch, split-K reduced inside

@@ -121,6 +121,9 @@ __device__ __forceinline__ uint32_t mg_s32(const void *p) { return (uint32_t)__c
 __device__ __forceinline__ void mg_mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mg_s32(bar)), "r"(count));
 }
+__device__ __forceinline__ void mg_prefetch_l2(const void *p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void mg_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
@@ -1277,7 +1280,13 @@ decode_mega_kernel(const __grid_constant__ MegaArgs a) {
                         src += (uint32_t)th.z;
                     }
                     if (++stg == MG_STAGES) { stg = 0; parity ^= 1; }
-                    if (th.w & 1) { next_p = (int)((uint32_t)th.w >> 8); break; }
+                    if (th.w & 1) {
+                        next_p = (int)((uint32_t)th.w >> 8);
+                        // this warp is done with the phase and its ring holds the next two tiles: what it would idle through
+                        // (the hand-over) HBM can spend on pulling the tiles after those into L2
+                        if (a.wait_prefetch && lane == 0 && th.z) mg_prefetch_l2(src, (uint32_t)a.wait_prefetch);
+                        break;
+                    }
                 }
             }
             if (DBG && tid == 0) tl_end = clock64();
@@ -1307,6 +1316,8 @@ void mega_fill_knobs(MegaArgs &a) { // read at every launch on purpose: the test
     const char *ns = getenv("B200LLM_LL_POLL_NS"), *pr = getenv("B200LLM_LL_PROBE");
     a.ll_poll_ns = ns ? atoi(ns) : 32;
     a.ll_probe = pr ? atoi(pr) : 0; // measured on Llama-3-8B: 0 -> 1.67 ms per token, 2 -> 1.88
+    const char *wp = getenv("B200LLM_MEGA_WAIT_PREFETCH");
+    a.wait_prefetch = wp ? std::min(64 << 10, std::max(0, atoi(wp))) / 16 * 16 : 0;
 }
 
 void launch_decode_mega(const MegaArgs &a, int n_sm, cudaStream_t s) {
@@ -1654,7 +1665,7 @@ void MegaStreams::build(const MegaPhase *phases, int n_phases, int n_cta, cudaSt
     std::vector<MegaStreamStart> st;
     std::vector<uint64_t> first_off;
     const uint64_t off = mega_plan_streams(phases, n_phases, n_cta, geo, tab, st, first_off) - 128;
-    bytes = (size_t)off + 128;
+    bytes = (size_t)off + 128 + (64 << 10); // (slack: the L2 prefetch at a phase end may reach past the last stream)
     n_tiles = (int64_t)tab.size();
     B2_CUDA(cudaMalloc((void **)&data, bytes));
     B2_CUDA(cudaMalloc((void **)&starts, st.size() * sizeof(MegaStreamStart)));

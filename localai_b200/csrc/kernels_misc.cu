@@ -7,10 +7,17 @@
 
 namespace b2 {
 
+bool pdl_enabled() {
+    static const bool on = !(getenv("B200LLM_NO_PDL") && atoi(getenv("B200LLM_NO_PDL")));
+    return on;
+}
+
 // ------------------------------------------------------------------------------------------ RMSNorm (* weight)
 __global__ void __launch_bounds__(256)
 rmsnorm_kernel(const float *__restrict__ x, int64_t x_stride, const int32_t *__restrict__ rows, const float *__restrict__ w,
                float *__restrict__ y, int64_t y_stride, int d, float eps) {
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const float *xr = x + (int64_t)(rows ? rows[blockIdx.x] : blockIdx.x) * x_stride;
     float *yr = y + (int64_t)blockIdx.x * y_stride;
     double sum = 0.0;
@@ -37,7 +44,7 @@ rmsnorm_kernel(const float *__restrict__ x, int64_t x_stride, const int32_t *__r
 void launch_rmsnorm(const float *x, int64_t x_stride, const int32_t *rows, const float *w, float *y, int64_t y_stride, int n_tok,
                     int d, float eps, cudaStream_t s) {
     if (n_tok <= 0) return;
-    rmsnorm_kernel<<<n_tok, 256, 0, s>>>(x, x_stride, rows, w, y, y_stride, d, eps);
+    launch_pdl(rmsnorm_kernel, dim3(n_tok), dim3(256), 0, s, x, x_stride, rows, w, y, y_stride, d, eps);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -63,6 +70,8 @@ void launch_swiglu(const float *gate, const float *up, float *out, int64_t n, cu
 __global__ void rope_kv_store_kernel(float *__restrict__ q, float *__restrict__ k, const float *__restrict__ v,
                                      const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head, int n_head_kv,
                                      int hd, const float *__restrict__ rope_table, KVLayout kv) {
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const int t = blockIdx.x;
     const int p = pos[t];
     const int sl = slot[t];
@@ -74,7 +83,8 @@ __global__ void rope_kv_store_kernel(float *__restrict__ q, float *__restrict__ 
     float *kt = k + (int64_t)t * n_head_kv * hd;
     const float *vt = v + (int64_t)t * n_head_kv * hd;
     const int nq = n_head * half, nk = n_head_kv * half;
-    for (int i = threadIdx.x; i < nq + nk; i += blockDim.x) {
+    // blockIdx.y: the pairs (and the V row) are split over gridDim.y CTAs per token -- a decode batch is few tokens
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < nq + nk; i += gridDim.y * blockDim.x) {
         const bool is_q = i < nq;
         const int ii = is_q ? i : i - nq;
         const int h = ii / half, pr = ii % half;
@@ -90,13 +100,14 @@ __global__ void rope_kv_store_kernel(float *__restrict__ q, float *__restrict__ 
             *(__half2 *)(kv.k_pool + cell + h * hd + 2 * pr) = __halves2half2(__float2half_rn(r0), __float2half_rn(r1));
         }
     }
-    for (int i = threadIdx.x; i < kv.kvd; i += blockDim.x) kv.v_pool[cell + i] = __float2half_rn(vt[i]);
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < kv.kvd; i += gridDim.y * blockDim.x) kv.v_pool[cell + i] = __float2half_rn(vt[i]);
 }
 
 void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok, int n_head,
                           int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, cudaStream_t s) {
     if (n_tok <= 0) return;
-    rope_kv_store_kernel<<<n_tok, 256, 0, s>>>(q, k, v, pos, slot, n_head, n_head_kv, hd, rope_table, kv);
+    const int split = n_tok >= 512 ? 1 : n_tok >= 128 ? 2 : 8;
+    launch_pdl(rope_kv_store_kernel, dim3(n_tok, split), dim3(256), 0, s, q, k, v, pos, slot, n_head, n_head_kv, hd, rope_table, kv);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -113,6 +124,8 @@ __global__ void __launch_bounds__(ATT_THREADS)
 attention_kernel(const float *__restrict__ q, const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head,
                  int n_head_kv, int hd, KVLayout kv, float *__restrict__ out, float scale) {
     extern __shared__ __align__(16) float smem[];
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const int h = blockIdx.x, t = blockIdx.y;
     attention_head(q + ((int64_t)t * n_head + h) * hd, pos[t] + 1, kv.page_table + (int64_t)slot[t] * kv.max_pages, kv,
                    h / (n_head / n_head_kv), hd, scale, out + ((int64_t)t * n_head + h) * hd, smem, threadIdx.x, ATT_THREADS);
@@ -124,6 +137,8 @@ __global__ void __launch_bounds__(ATT_THREADS)
 attention_group_kernel(const float *__restrict__ q, const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head,
                        int hd, KVLayout kv, float *__restrict__ out, float scale) {
     extern __shared__ __align__(16) float smem[];
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const int hk = blockIdx.x, t = blockIdx.y;
     const int64_t row0 = ((int64_t)t * n_head + (int64_t)hk * G) * hd; // heads hk*G .. hk*G+G-1 are consecutive
     attention_group<G>(q + row0, pos[t] + 1, kv.page_table + (int64_t)slot[t] * kv.max_pages, kv, hk, hd, scale, out + row0, smem,
@@ -138,7 +153,7 @@ static bool try_launch_attention_group(const float *q, const int32_t *pos, const
     static PerDeviceOnce configured;
     configured.run([&] { B2_CUDA(cudaFuncSetAttribute(attention_group_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); });
     const float scale = 1.0f / sqrtf((float)hd);
-    attention_group_kernel<G><<<dim3(n_head_kv, n_tok), ATT_THREADS, smem, s>>>(q, pos, slot, n_head, hd, kv, out, scale);
+    launch_pdl(attention_group_kernel<G>, dim3(n_head_kv, n_tok), dim3(ATT_THREADS), smem, s, q, pos, slot, n_head, hd, kv, out, scale);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
     return true;
@@ -162,7 +177,7 @@ void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, i
     if (smem > 48 * 1024)
         configured.run([&] { B2_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024)); });
     const float scale = 1.0f / sqrtf((float)hd);
-    attention_kernel<<<dim3(n_head, n_tok), ATT_THREADS, smem, s>>>(q, pos, slot, n_head, n_head_kv, hd, kv, out, scale);
+    launch_pdl(attention_kernel, dim3(n_head, n_tok), dim3(ATT_THREADS), smem, s, q, pos, slot, n_head, n_head_kv, hd, kv, out, scale);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -187,6 +202,8 @@ __device__ __forceinline__ unsigned long long argmax_pack(float v, int i) {
 __global__ void __launch_bounds__(256)
 argmax_kernel(const float *__restrict__ logits, int64_t stride, int n_vocab, int32_t *__restrict__ out,
               int32_t *__restrict__ feed_tok, int32_t *__restrict__ feed_pos) {
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const int row = blockIdx.y;
     const float *x = logits + (int64_t)row * stride;
     const int per = (n_vocab + ARGMAX_SPLIT - 1) / ARGMAX_SPLIT;
@@ -221,7 +238,7 @@ void launch_argmax(const float *logits, int64_t stride, int n_rows, int n_vocab,
                    int32_t *feed_pos, cudaStream_t s) {
     if (n_rows <= 0) return;
     B2_CHECK(n_rows <= ARGMAX_MAX_ROWS, B2_EINVAL, "argmax: too many rows");
-    argmax_kernel<<<dim3(ARGMAX_SPLIT, n_rows), 256, 0, s>>>(logits, stride, n_vocab, out, feed_tok, feed_pos);
+    launch_pdl(argmax_kernel, dim3(ARGMAX_SPLIT, n_rows), dim3(256), 0, s, logits, stride, n_vocab, out, feed_tok, feed_pos);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }

@@ -19,12 +19,15 @@
 //   output directly; otherwise it writes an fp32 partial tile, and the LAST segment of that tile to arrive (one
 //   atomic counter per tile and lane quarter) adds all partials in segment order (+ residual) -- deterministic, no
 //   second launch, no spinning.
-// * warps: 0 producer (bulk copies), 1 MMA issuer, 2 TMEM allocator, 4..7 epilogue (one TMEM lane quarter each),
+// * warps: 0 weight producer, 3 activation producer (bulk copies), 1 MMA issuer, 2 TMEM allocator, 4..7 epilogue (one TMEM
+//   lane quarter each),
 //   8..23 dequant (lane quarter = warp % 4; (warp - 8) / 4 = which 32 of the 128 k of an operand stage).
 // fp16 arithmetic of the dequantisation: q exact, d*sc and dmin*m rounded to fp16, one fused multiply-add -- about 3
 // fp16 roundings per weight (relative 2^-11 each), against 2^-9 of the bf16 tiles the large-batch path uses.
 // HBM-bound: algorithmic bytes = the quantised weights once; roofline = MEASURED_PEAKS.json hbm_gbs.
 #include <cuda_fp16.h>
+
+#include <vector>
 
 #include "kernels.h"
 #include "quant.cuh"
@@ -122,6 +125,8 @@ __device__ __forceinline__ void qg_store8(__half *out, int r, int64_t k0, int n_
 
 __global__ void qgemm_convert_x_kernel(const float *__restrict__ x, int64_t x_stride, int n_tok, int64_t cols, __half *__restrict__ out,
                                        int n_pad) {
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const int64_t kc = cols / 8, total = (int64_t)n_pad * kc;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int r = (int)(i / kc);
@@ -139,6 +144,8 @@ __global__ void qgemm_convert_x_kernel(const float *__restrict__ x, int64_t x_st
 __global__ void __launch_bounds__(256)
 qgemm_rmsnorm_x_kernel(const float *__restrict__ x, int64_t x_stride, const float *__restrict__ w, int n_tok, int64_t cols, float eps,
                        __half *__restrict__ out, int n_pad) {
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const int r = blockIdx.x;
     __shared__ double part[8];
     __shared__ float s_scale;
@@ -178,6 +185,8 @@ qgemm_rmsnorm_x_kernel(const float *__restrict__ x, int64_t x_stride, const floa
 
 __global__ void qgemm_swiglu_x_kernel(const float *__restrict__ g, const float *__restrict__ u, int n_tok, int64_t cols,
                                       __half *__restrict__ out, int n_pad) {
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
     const int64_t kc = cols / 8, total = (int64_t)n_pad * kc;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int r = (int)(i / kc);
@@ -198,7 +207,7 @@ void launch_qgemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t
     B2_CHECK(K % 256 == 0 && n_tok >= 1 && n_tok <= QGEMM_MAX_TOKENS, B2_EINVAL, "qgemm: K must be a multiple of 256, 1..64 tokens");
     const int n_pad = (int)align_up(n_tok, 16);
     const int64_t total = (int64_t)n_pad * (K / 8);
-    qgemm_convert_x_kernel<<<(int)std::min<int64_t>((total + 255) / 256, 148 * 8), 256, 0, s>>>(x, x_stride, n_tok, K, (__half *)x_tiles, n_pad);
+    launch_pdl(qgemm_convert_x_kernel, dim3((unsigned)std::min<int64_t>((total + 255) / 256, 148 * 8)), dim3(256), 0, s, x, x_stride, n_tok, K, (__half *)x_tiles, n_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -206,7 +215,7 @@ void launch_qgemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const floa
                                     cudaStream_t s) {
     B2_CHECK(K % 256 == 0 && n_tok >= 1 && n_tok <= QGEMM_MAX_TOKENS, B2_EINVAL, "qgemm: K must be a multiple of 256, 1..64 tokens");
     const int n_pad = (int)align_up(n_tok, 16);
-    qgemm_rmsnorm_x_kernel<<<n_pad, 256, 0, s>>>(x, x_stride, w, n_tok, K, eps, (__half *)x_tiles, n_pad);
+    launch_pdl(qgemm_rmsnorm_x_kernel, dim3(n_pad), dim3(256), 0, s, x, x_stride, w, n_tok, K, eps, (__half *)x_tiles, n_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -214,7 +223,7 @@ void launch_qgemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok
     B2_CHECK(K % 256 == 0 && n_tok >= 1 && n_tok <= QGEMM_MAX_TOKENS, B2_EINVAL, "qgemm: K must be a multiple of 256, 1..64 tokens");
     const int n_pad = (int)align_up(n_tok, 16);
     const int64_t total = (int64_t)n_pad * (K / 8);
-    qgemm_swiglu_x_kernel<<<(int)std::min<int64_t>((total + 255) / 256, 148 * 8), 256, 0, s>>>(gate, up, n_tok, K, (__half *)x_tiles, n_pad);
+    launch_pdl(qgemm_swiglu_x_kernel, dim3((unsigned)std::min<int64_t>((total + 255) / 256, 148 * 8)), dim3(256), 0, s, gate, up, n_tok, K, (__half *)x_tiles, n_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -450,11 +459,12 @@ __device__ __forceinline__ const QGemmJobDev &qg_job_of(const QGemmArgs &g, int 
     return g.job[(g.n_jobs > 2 && tile >= g.job[2].nt0) ? 2 : (g.n_jobs > 1 && tile >= g.job[1].nt0) ? 1 : 0];
 }
 // the CTA whose unit range [c * U / G, (c + 1) * U / G) holds unit x
-__device__ __forceinline__ int qg_cta_of(int64_t x, int64_t U, int64_t G) { return (int)(((x + 1) * G + U - 1) / U - 1); }
+__host__ __device__ __forceinline__ int qg_cta_of(int64_t x, int64_t U, int64_t G) { return (int)(((x + 1) * G + U - 1) / U - 1); }
 
 __global__ void __launch_bounds__(QG_THREADS, 1)
 qgemm_kernel(const __grid_constant__ QGemmArgs g) {
     extern __shared__ __align__(1024) uint8_t qsm[];
+    B2_PDL_TRIGGER();
 #ifdef QG_DBG
     const long long qg_kstart = clock64();
 #endif
@@ -487,6 +497,9 @@ qgemm_kernel(const __grid_constant__ QGemmArgs g) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+    // (programmatic dependent launch: the roles that touch what earlier kernels of the stream wrote or still read -- the
+    // activation producer, the epilogue warps, the fix-up -- wait for the previous kernel themselves; the weight producer,
+    // the dequant and MMA warps start at once)
 #ifdef QG_DBG
     if (threadIdx.x == 0) g_qg_dbg[blockIdx.x][13] = clock64() - qg_kstart; // prologue
 #endif
@@ -495,8 +508,9 @@ qgemm_kernel(const __grid_constant__ QGemmArgs g) {
     const int nkb = g.nkb, T = g.T;
 
     if (warp == 0) {
-        { // ===== producer (the whole warp walks the schedule; one elected lane issues the copies)
-            uint32_t rit = 0, bit = 0;
+        { // ===== weight producer (the whole warp walks the schedule; one elected lane issues the copies).  The weights are
+          // immutable, so this warp does not wait for the previous kernel of the stream: the ring fills while that one drains.
+            uint32_t rit = 0;
 #ifdef QG_DBG
             long long qg_acc[4] = {0, 0, 0, 0};
 #endif
@@ -504,15 +518,6 @@ qgemm_kernel(const __grid_constant__ QGemmArgs g) {
             for (int u = u0; u < u1;) {
                 const int p = u / nkb, kb0 = u - p * nkb, kb1 = min(nkb, kb0 + (u1 - u));
                 for (int kb = kb0; kb < kb1; kb++) {
-                    const int bs = bit % QG_B_STAGES;
-                    QG_ACC(2);
-                    qg_wait(b_empty + bs, ((bit / QG_B_STAGES) & 1) ^ 1);
-                    QG_ACC(0);
-                    if (qg_elect()) {
-                        qg_expect_tx(b_full + bs, b_bytes);
-                        qg_bulk_g2s(bst + (size_t)bs * b_bytes, g.x_tiles + (int64_t)kb * g.n_pad * 256, b_bytes, b_full + bs);
-                    }
-                    bit++;
                     for (int t = 0; t < T; t++, rit++) {
                         const int tile = p * T + t;
                         const QGemmJobDev &J = qg_job_of(g, tile);
@@ -532,6 +537,23 @@ qgemm_kernel(const __grid_constant__ QGemmArgs g) {
 #ifdef QG_DBG
             for (int i = 0; i < 3; i++) g_qg_dbg[blockIdx.x][10 + i] = qg_acc[i];
 #endif
+        }
+    } else if (warp == 3) {
+        { // ===== activation producer: one 256-k stage of all tokens per unit (written by the previous kernel: wait for it)
+            B2_PDL_WAIT();
+            uint32_t bit = 0;
+            for (int u = u0; u < u1;) {
+                const int p = u / nkb, kb0 = u - p * nkb, kb1 = min(nkb, kb0 + (u1 - u));
+                for (int kb = kb0; kb < kb1; kb++, bit++) {
+                    const int bs = bit % QG_B_STAGES;
+                    qg_wait(b_empty + bs, ((bit / QG_B_STAGES) & 1) ^ 1);
+                    if (qg_elect()) {
+                        qg_expect_tx(b_full + bs, b_bytes);
+                        qg_bulk_g2s(bst + (size_t)bs * b_bytes, g.x_tiles + (int64_t)kb * g.n_pad * 256, b_bytes, b_full + bs);
+                    }
+                }
+                u += kb1 - kb0;
+            }
         }
     } else if (warp == 1) {
         { // ===== MMA issuer (whole warp, elected lane)
@@ -637,6 +659,7 @@ qgemm_kernel(const __grid_constant__ QGemmArgs g) {
     } else if (warp >= 4) { // ===== epilogue: TMEM -> registers -> global (direct, or partial + last-arriver reduce)
         const int q = warp & 3;
         uint32_t sit = 0;
+        B2_PDL_WAIT();
         for (int u = u0; u < u1; sit++) {
             const int p = u / nkb, kb0 = u - p * nkb, kb1 = min(nkb, kb0 + (u1 - u));
             const int buf = sit & 1;
@@ -706,49 +729,64 @@ qgemm_kernel(const __grid_constant__ QGemmArgs g) {
 #ifdef QG_DBG
     if (threadIdx.x == 0) g_qg_dbg[blockIdx.x][14] = clock64() - qg_kstart; // main loops done (all roles)
 #endif
-    // ===== fix-up: the tiles whose last partial segment arrived in this CTA.  All threads: thread = (row, token mod 6),
-    // 11 tokens each, the loads of one segment all in flight; partials are added in segment order, so the sum does not
-    // depend on which CTA happens to be last.
+    // ===== fix-up: the tiles whose last partial segment arrived in this CTA.  All 24 warps: a warp takes whole tokens (lane =
+    // four consecutive rows, 16-byte loads), three tokens each, four segments' loads in flight; partials are added in
+    // segment order, so the sum does not depend on which CTA happens to be last.
     const int nf = *n_fix;
+    B2_PDL_WAIT();
     for (int e = 0; e < nf; e++) {
         const int4 f = fix[e];
         const int p = f.x, t = f.y, c_first = f.z, nseg = f.w;
         const int tile = p * T + t;
         const QGemmJobDev &J = qg_job_of(g, tile);
-        const int r = threadIdx.x & 127, row = (tile - J.nt0) * QG_ROWS + r;
+        const int r = lane * 4, row = (tile - J.nt0) * QG_ROWS + r;
         const int64_t slot_floats = (int64_t)T * g.n_pad * QG_ROWS;
         const float *p0 = g.partial + (2 * (int64_t)c_first + 1) * slot_floats + (int64_t)t * g.n_pad * QG_ROWS + r; // segment 0: starts at the panel's first k-block
         const float *p1 = g.partial + (2 * (int64_t)c_first) * slot_floats + (int64_t)t * g.n_pad * QG_ROWS + r;     // segment s: + 2 s slots
-        constexpr int TL = QG_THREADS / 128, NJ = (QGEMM_MAX_TOKENS + TL - 1) / TL; // token lanes; tokens per thread
-        float acc[NJ];
+        constexpr int NW = QG_THREADS / 32, NJ = (QGEMM_MAX_TOKENS + NW - 1) / NW; // warps; tokens per warp
+        const int w = threadIdx.x >> 5;
+        float4 acc[NJ];
 #pragma unroll
         for (int j = 0; j < NJ; j++) {
-            const int tok = (threadIdx.x >> 7) + TL * j;
-            acc[j] = tok < g.n_pad ? __ldcg(p0 + (int64_t)tok * QG_ROWS) : 0.f;
+            const int tok = w + NW * j;
+            acc[j] = tok < g.n_pad ? __ldcg((const float4 *)(p0 + (int64_t)tok * QG_ROWS)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        for (int s0 = 1; s0 < nseg; s0 += 4) { // four segments' loads in flight; added in segment order
-            float v[4][NJ];
+        for (int s0 = 1; s0 < nseg; s0 += 4) {
+            float4 v[4][NJ];
 #pragma unroll
             for (int ss = 0; ss < 4; ss++)
 #pragma unroll
                 for (int j = 0; j < NJ; j++) {
-                    const int tok = (threadIdx.x >> 7) + TL * j;
-                    v[ss][j] = (s0 + ss < nseg && tok < g.n_pad) ? __ldcg(p1 + 2 * (s0 + ss) * slot_floats + (int64_t)tok * QG_ROWS) : 0.f;
+                    const int tok = w + NW * j;
+                    v[ss][j] = (s0 + ss < nseg && tok < g.n_pad) ? __ldcg((const float4 *)(p1 + 2 * (s0 + ss) * slot_floats + (int64_t)tok * QG_ROWS))
+                                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
 #pragma unroll
             for (int ss = 0; ss < 4; ss++)
 #pragma unroll
-                for (int j = 0; j < NJ; j++) acc[j] += v[ss][j]; // (+ 0 for a segment past the last: the same value in every run)
-        }
-        if (row < J.N) {
-#pragma unroll
-            for (int j = 0; j < NJ; j++) {
-                const int tok = (threadIdx.x >> 7) + TL * j;
-                if (tok < g.n_tok) {
-                    float v = acc[j];
-                    if (g.residual) v += g.residual[(int64_t)tok * g.res_stride + row];
-                    J.out[(int64_t)tok * J.out_stride + row] = v;
+                for (int j = 0; j < NJ; j++) { // (+ 0 for a segment past the last: the same value in every run)
+                    acc[j].x += v[ss][j].x; acc[j].y += v[ss][j].y; acc[j].z += v[ss][j].z; acc[j].w += v[ss][j].w;
                 }
+        }
+        const bool vec = row + 3 < J.N && (J.out_stride & 3) == 0 && (((uintptr_t)J.out) & 15) == 0 &&
+                         (!g.residual || ((g.res_stride & 3) == 0 && (((uintptr_t)g.residual) & 15) == 0));
+#pragma unroll
+        for (int j = 0; j < NJ; j++) {
+            const int tok = w + NW * j;
+            if (tok >= g.n_tok) continue;
+            float *o = J.out + (int64_t)tok * J.out_stride + row;
+            const float *res = g.residual ? g.residual + (int64_t)tok * g.res_stride + row : nullptr;
+            if (vec) {
+                float4 v = acc[j];
+                if (res) {
+                    const float4 rr = *(const float4 *)res;
+                    v.x += rr.x; v.y += rr.y; v.z += rr.z; v.w += rr.w;
+                }
+                *(float4 *)o = v;
+            } else {
+                const float a4[4] = {acc[j].x, acc[j].y, acc[j].z, acc[j].w};
+                for (int i = 0; i < 4; i++)
+                    if (row + i < J.N) o[i] = a4[i] + (res ? res[i] : 0.f);
             }
         }
     }
@@ -761,7 +799,7 @@ qgemm_kernel(const __grid_constant__ QGemmArgs g) {
 // ------------------------------------------------------------------------------------------------ host side
 constexpr size_t QG_SMEM = (size_t)QG_RAW_RING + (size_t)QG_B_STAGES * 64 * 512 + 512;
 
-// the plan of one launch (host arithmetic only; tests/test_capi_cpu.py checks it through b2_qgemm_plan_check)
+// the plan of one launch (host arithmetic only; tests/test_capi_cpu.py replays it through b2_qgemm_plan_check)
 void qgemm_plan(int n_tiles, int nkb, int n_sm, bool allow_pairs, QGemmPlan *pl) {
     int T = 1;
     // pairs of tiles share the activation stage; only when a CTA's range then still spans whole panels (few split tiles)
@@ -770,6 +808,43 @@ void qgemm_plan(int n_tiles, int nkb, int n_sm, bool allow_pairs, QGemmPlan *pl)
     pl->panels = n_tiles / T;
     pl->units = (int64_t)pl->panels * nkb;
     pl->grid = (int)std::min<int64_t>(n_sm, pl->units);
+}
+
+// host-only replay of the kernel's work split (the CPU unit test of the planner): every (panel, kb) unit belongs to exactly
+// one CTA range; the segment arithmetic the epilogue uses (first CTA of a panel, number of segments) matches the ranges; a
+// CTA never needs more than its two partial slots.  Throws b2::Error on an inconsistency; returns the number of split tiles.
+int64_t qgemm_plan_check(int n_tiles, int nkb, int n_sm) {
+    QGemmPlan pl;
+    qgemm_plan(n_tiles, nkb, n_sm, true, &pl);
+    B2_CHECK(pl.T >= 1 && pl.T <= 2 && pl.panels * pl.T == n_tiles && pl.units == (int64_t)pl.panels * nkb, B2_EINVAL, "qgemm plan: panels");
+    B2_CHECK(pl.grid >= 1 && pl.grid <= n_sm && pl.grid <= pl.units, B2_EINVAL, "qgemm plan: grid");
+    const int64_t U = pl.units, G = pl.grid;
+    std::vector<int> seen_first(pl.panels, -1), seen_n(pl.panels, 0);
+    int64_t covered = 0, split = 0;
+    for (int c = 0; c < G; c++) {
+        const int64_t u0 = c * U / G, u1 = (c + 1) * U / G;
+        B2_CHECK(u1 > u0, B2_EINVAL, "qgemm plan: empty CTA range");
+        int slots_used[2] = {0, 0};
+        for (int64_t u = u0; u < u1;) {
+            const int64_t p = u / nkb, kb0 = u - p * nkb, kb1 = std::min<int64_t>(nkb, kb0 + (u1 - u));
+            const bool full = kb0 == 0 && kb1 == nkb;
+            if (!full) {
+                const int c_first = qg_cta_of(p * nkb, U, G), c_last = qg_cta_of((p + 1) * nkb - 1, U, G);
+                B2_CHECK(c >= c_first && c <= c_last, B2_EINVAL, "qgemm plan: CTA outside its panel's segment range");
+                // segment index c - c_first: 0 must be the one that starts at the panel's first k-block
+                B2_CHECK((kb0 == 0) == (c == c_first), B2_EINVAL, "qgemm plan: segment 0 is not the panel's first");
+                B2_CHECK(++slots_used[kb0 == 0] == 1, B2_EINVAL, "qgemm plan: a CTA needs a partial slot twice");
+                if (seen_first[p] < 0) seen_first[p] = c_first;
+                seen_n[p]++;
+                if (c == c_last) B2_CHECK(seen_n[p] == c_last - c_first + 1 && kb1 == nkb, B2_EINVAL, "qgemm plan: segment count");
+            }
+            covered += kb1 - kb0;
+            u += kb1 - kb0;
+        }
+    }
+    B2_CHECK(covered == U, B2_EINVAL, "qgemm plan: units not covered exactly once");
+    for (int p = 0; p < pl.panels; p++) split += seen_n[p] > 0 ? pl.T : 0;
+    return split;
 }
 
 void launch_qgemm_multi(const QGemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,
@@ -805,7 +880,7 @@ void launch_qgemm_multi(const QGemmJob *jobs, int n_jobs, const void *x_tiles, i
     g.partial = partial; g.counters = counters;
     B2_CHECK((size_t)2 * pl.grid * pl.T * g.n_pad * QG_ROWS * sizeof(float) <= partial_bytes, B2_EINVAL, "qgemm: partial-tile scratch too small");
     B2_CHECK((size_t)nt <= n_counters, B2_EINVAL, "qgemm: too few tile counters");
-    qgemm_kernel<<<pl.grid, QG_THREADS, QG_SMEM, s>>>(g);
+    launch_pdl(qgemm_kernel, dim3(pl.grid), dim3(QG_THREADS), QG_SMEM, s, g);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }

@@ -109,6 +109,17 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     const int rope_dims = (int)f.get_u(a + "rope.dimension_count", hp.head_dim);
     B2_CHECK(rope_dims == hp.head_dim, B2_EUNSUPPORTED, "partial rotary dimensions are not supported");
     B2_CHECK(hp.n_head % hp.n_head_kv == 0, B2_EIO, "head_count not a multiple of head_count_kv");
+    // RoPE scaling as llama.cpp derives it from the metadata (llm_load_hparams, llama_new_context_with_model): linear and
+    // YaRN scale the frequencies by 1 / rope.scaling.factor, YaRN additionally blends towards the unscaled frequencies
+    // (ext_factor 1) inside its correction range; rope_freqs.weight holds per-dimension divisors (the Llama-3.1 scheme)
+    {
+        const std::string st = f.get_s(a + "rope.scaling.type", "none");
+        const float factor = (float)f.get_f(a + "rope.scaling.factor", 1.0);
+        B2_CHECK(st == "none" || st == "linear" || st == "yarn", B2_EUNSUPPORTED, "gguf: unknown rope.scaling.type");
+        if ((st == "linear" || st == "yarn") && factor > 0) hp.rope_scale = 1.0f / factor;
+        hp.rope_ext_factor = st == "yarn" ? 1.0f : 0.0f;
+        hp.rope_n_ctx_orig = (int)f.get_u(a + "rope.scaling.original_context_length", hp.n_ctx_train);
+    }
     if (o.rope_freq_base > 0) hp.rope_base = o.rope_freq_base;
     if (o.rope_freq_scale > 0) hp.rope_scale = o.rope_freq_scale;
 
@@ -192,12 +203,37 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
         const int hd = hp.head_dim;
         std::vector<float> tab((size_t)n_ctx_slot * hd);
         const float theta_scale = powf(hp.rope_base, -2.0f / hd);
+        // per-dimension frequency divisors (rope_freqs.weight, f32 [hd / 2]), read straight from the mapping
+        const float *ff = nullptr;
+        if (const GGUFTensorInfo *tf = f.tensor("rope_freqs.weight")) {
+            B2_CHECK(tf->type == B2_T_F32 && tf->n_bytes == (int64_t)(hd / 2) * 4 && tf->data, B2_EIO, "gguf: rope_freqs.weight must be f32 [head_dim / 2]");
+            ff = (const float *)tf->data;
+        }
+        // YaRN correction range (ggml_rope_yarn_corr_dims, beta_fast 32, beta_slow 1)
+        float corr[2] = {0.f, 0.f};
+        if (hp.rope_ext_factor != 0.0f) {
+            auto corr_dim = [&](float n_rot) { return hd * logf(hp.rope_n_ctx_orig / (n_rot * 2 * (float)M_PI)) / (2 * logf(hp.rope_base)); };
+            corr[0] = std::max(0.f, floorf(corr_dim(32.0f)));
+            corr[1] = std::min((float)hd - 1, ceilf(corr_dim(1.0f)));
+        }
         for (int p = 0; p < n_ctx_slot; p++) {
             float theta = (float)p;
             for (int i0 = 0; i0 < hd; i0 += 2) {
-                const float t = hp.rope_scale * theta;
-                tab[(size_t)p * hd + i0] = cosf(t);
-                tab[(size_t)p * hd + i0 + 1] = sinf(t);
+                float t, mscale = 1.0f;
+                if (!ff && hp.rope_ext_factor == 0.0f) {
+                    t = hp.rope_scale * theta; // the unscaled / linear path keeps its exact arithmetic
+                } else {
+                    const float extrap = theta / (ff ? ff[i0 / 2] : 1.0f), interp = hp.rope_scale * extrap;
+                    t = interp;
+                    if (hp.rope_ext_factor != 0.0f) { // rope_yarn
+                        const float y = (i0 / 2 - corr[0]) / std::max(0.001f, corr[1] - corr[0]);
+                        const float ramp_mix = (1.0f - std::min(1.0f, std::max(0.0f, y))) * hp.rope_ext_factor;
+                        t = interp * (1 - ramp_mix) + extrap * ramp_mix;
+                        mscale *= 1.0f + 0.1f * logf(1.0f / hp.rope_scale);
+                    }
+                }
+                tab[(size_t)p * hd + i0] = cosf(t) * mscale;
+                tab[(size_t)p * hd + i0 + 1] = sinf(t) * mscale;
                 theta *= theta_scale;
             }
         }

@@ -18,6 +18,8 @@ struct SampleSpec;
 struct HParams {
     int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_ctx_train = 0;
     float rms_eps = 1e-5f, rope_base = 10000.f, rope_scale = 1.f;
+    float rope_ext_factor = 0.f; // 1 for YaRN (llama.rope.scaling.type)
+    int rope_n_ctx_orig = 0;     // llama.rope.scaling.original_context_length
     std::string arch, name;
 };
 

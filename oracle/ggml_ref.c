@@ -786,6 +786,10 @@ enum { TK_TOK_EMBD = 0, TK_OUTPUT_NORM, TK_OUTPUT, TK_ATTN_NORM, TK_WQ, TK_WK, T
 typedef struct {
     int n_layer, n_embd, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_ctx;
     float rms_eps, rope_theta, rope_freq_scale;
+    /* RoPE scaling (llama.cpp cparams / hparams): ext_factor 1 for YaRN else 0, attn_factor, the YaRN correction range,
+     * optional per-dimension frequency divisors (rope_freqs.weight, the Llama-3.1 scheme) */
+    float rope_ext_factor, rope_attn_factor, rope_corr_dims[2];
+    const float *rope_freq_factors;
     ref_tensor global[3];
     ref_tensor *layer[TK_COUNT]; /* indices >= TK_ATTN_NORM used */
     fp16_t *k_cache, *v_cache;   /* [n_layer][n_ctx][n_head_kv*head_dim] */
@@ -798,11 +802,21 @@ ref_ctx *ref_ctx_new(int n_layer, int n_embd, int n_head, int n_head_kv, int n_f
     c->n_layer = n_layer; c->n_embd = n_embd; c->n_head = n_head; c->n_head_kv = n_head_kv;
     c->head_dim = n_embd / n_head; c->n_ff = n_ff; c->n_vocab = n_vocab; c->n_ctx = n_ctx;
     c->rms_eps = rms_eps; c->rope_theta = rope_theta; c->rope_freq_scale = rope_freq_scale;
+    c->rope_ext_factor = 0.0f; c->rope_attn_factor = 1.0f; c->rope_corr_dims[0] = c->rope_corr_dims[1] = 0.0f; c->rope_freq_factors = NULL;
     for (int k = TK_ATTN_NORM; k < TK_COUNT; k++) c->layer[k] = (ref_tensor *)calloc(n_layer, sizeof(ref_tensor));
     size_t kv = (size_t)n_layer * n_ctx * n_head_kv * c->head_dim;
     c->k_cache = (fp16_t *)calloc(kv, sizeof(fp16_t));
     c->v_cache = (fp16_t *)calloc(kv, sizeof(fp16_t));
     return c;
+}
+
+void ref_rope_yarn_corr_dims(int n_dims, int n_ctx_orig, float freq_base, float beta_fast, float beta_slow, float dims[2]);
+/* llama.cpp: freq_scale = 1 / rope.scaling.factor (linear and YaRN), ext_factor = 1 for YaRN, beta_fast 32, beta_slow 1 */
+void ref_ctx_set_rope_scaling(ref_ctx *c, float freq_scale, float ext_factor, float attn_factor, int n_ctx_orig, float beta_fast,
+                              float beta_slow, const float *freq_factors) {
+    c->rope_freq_scale = freq_scale; c->rope_ext_factor = ext_factor; c->rope_attn_factor = attn_factor;
+    c->rope_freq_factors = freq_factors;
+    if (ext_factor != 0.0f) ref_rope_yarn_corr_dims(c->head_dim, n_ctx_orig, c->rope_theta, beta_fast, beta_slow, c->rope_corr_dims);
 }
 
 void ref_ctx_free(ref_ctx *c) {
@@ -836,6 +850,43 @@ void ref_rope_cache(float theta_base, float freq_scale, float freq_base, int n_d
         const float t = freq_scale * theta;
         cache[i0 + 0] = cosf(t);
         cache[i0 + 1] = sinf(t);
+        theta *= theta_scale;
+    }
+}
+
+/* The scaled variants, restated from ggml's published algorithm (ggml.c: rope_yarn, rope_yarn_ramp,
+ * ggml_rope_yarn_corr_dims, ggml_rope_cache_init with freq_factors; YaRN: arXiv 2309.00071).  llama.cpp is an
+ * un-vendored submodule of the reference, so this part of the oracle is NOT pinned against upstream code or vectors:
+ * "parity unpinned" for the scaled RoPE paths (the unscaled path above is pinned through the transformers cross-check). */
+static float rope_yarn_ramp(float low, float high, int i0) {
+    const float y = (i0 / 2 - low) / fmaxf(0.001f, high - low);
+    return 1.0f - fminf(1.0f, fmaxf(0.0f, y));
+}
+static float rope_yarn_corr_dim(int n_dims, int n_ctx_orig, float n_rot, float base) {
+    return n_dims * logf(n_ctx_orig / (n_rot * 2 * (float)M_PI)) / (2 * logf(base));
+}
+void ref_rope_yarn_corr_dims(int n_dims, int n_ctx_orig, float freq_base, float beta_fast, float beta_slow, float dims[2]) {
+    const float start = floorf(rope_yarn_corr_dim(n_dims, n_ctx_orig, beta_fast, freq_base));
+    const float end = ceilf(rope_yarn_corr_dim(n_dims, n_ctx_orig, beta_slow, freq_base));
+    dims[0] = fmaxf(0, start);
+    dims[1] = fminf(n_dims - 1, end);
+}
+void ref_rope_cache_ext(float theta_base, float freq_scale, float freq_base, int n_dims, const float *freq_factors, float ext_factor,
+                        float attn_factor, const float corr_dims[2], float *cache) {
+    const float theta_scale = powf(freq_base, -2.0f / n_dims);
+    float theta = theta_base;
+    for (int i0 = 0; i0 < n_dims; i0 += 2) {
+        const float ff = freq_factors ? freq_factors[i0 / 2] : 1.0f;
+        const float theta_extrap = theta / ff;
+        const float theta_interp = freq_scale * theta_extrap;
+        float t = theta_interp, mscale = attn_factor;
+        if (ext_factor != 0.0f) {
+            const float ramp_mix = rope_yarn_ramp(corr_dims[0], corr_dims[1], i0) * ext_factor;
+            t = theta_interp * (1 - ramp_mix) + theta_extrap * ramp_mix;
+            mscale *= 1.0f + 0.1f * logf(1.0f / freq_scale);
+        }
+        cache[i0 + 0] = cosf(t) * mscale;
+        cache[i0 + 1] = sinf(t) * mscale;
         theta *= theta_scale;
     }
 }
@@ -880,7 +931,13 @@ int ref_eval(ref_ctx *c, const int32_t *tokens, int n_tokens, int n_past, float 
     const ref_tensor *te = &c->global[TK_TOK_EMBD];
     const int64_t erb = ref_row_bytes(te->type, d);
     for (int t = 0; t < T; t++) ref_dequantize_row(te->type, (const uint8_t *)te->data + (int64_t)tokens[t] * erb, inpL + t * d, d);
-    for (int t = 0; t < T; t++) ref_rope_cache((float)(n_past + t), c->rope_freq_scale, c->rope_theta, hd, ropec + t * hd);
+    for (int t = 0; t < T; t++) {
+        if (c->rope_ext_factor == 0.0f && c->rope_attn_factor == 1.0f && !c->rope_freq_factors)
+            ref_rope_cache((float)(n_past + t), c->rope_freq_scale, c->rope_theta, hd, ropec + t * hd);
+        else
+            ref_rope_cache_ext((float)(n_past + t), c->rope_freq_scale, c->rope_theta, hd, c->rope_freq_factors, c->rope_ext_factor,
+                               c->rope_attn_factor, c->rope_corr_dims, ropec + t * hd);
+    }
 
     for (int il = 0; il < c->n_layer; il++) {
         fp16_t *kc = c->k_cache + (size_t)il * c->n_ctx * kvd;

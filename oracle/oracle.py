@@ -146,6 +146,27 @@ class OracleModel:
         self.ctx = L.ref_ctx_new(self.n_layer, self.n_embd, self.n_head, self.n_head_kv, self.n_ff, self.n_vocab, n_ctx,
                                  self.rms_eps, self.rope_theta, 1.0)
         self._keep = []
+        # RoPE scaling as llama.cpp derives it from the metadata (llama.cpp: llm_load_hparams / llama_new_context_with_model)
+        def string(key, default):
+            if key not in f:
+                return default
+            fld = f[key]
+            return bytes(fld.parts[fld.data[0]]).decode()
+
+        stype = string("llama.rope.scaling.type", "none")
+        factor = float(scalar("llama.rope.scaling.factor", 1.0))
+        self.rope_freq_scale = 1.0 / factor if stype in ("linear", "yarn") and factor > 0 else 1.0
+        self.rope_ext_factor = 1.0 if stype == "yarn" else 0.0
+        n_ctx_orig = int(scalar("llama.rope.scaling.original_context_length", scalar("llama.context_length", 2048)))
+        ff = None
+        if "rope_freqs.weight" in self.tensors:
+            ff = np.ascontiguousarray(np.array(self.tensors["rope_freqs.weight"].data, dtype=np.float32))
+            self._keep.append(ff)
+        if stype != "none" or ff is not None:
+            L.ref_ctx_set_rope_scaling.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int,
+                                                   C.c_float, C.c_float, C.c_void_p]
+            L.ref_ctx_set_rope_scaling(self.ctx, self.rope_freq_scale, self.rope_ext_factor, 1.0, n_ctx_orig, 32.0, 1.0,
+                                       ff.ctypes.data if ff is not None else None)
         for name, t in self.tensors.items():
             base = name.rsplit(".weight", 1)[0]
             data = np.ascontiguousarray(t.data).view(np.uint8).reshape(-1)

@@ -43,6 +43,10 @@ def model_files(gguf_dir):
         "mini_q3_k": ("mini", "q3_k"),
         "mini_iq4_nl": ("mini", "iq4_nl"),
         "mini_iq4_xs": ("mini", "iq4_xs"),
+        # RoPE scaling variants (linear, YaRN, per-dimension divisors a la Llama-3.1)
+        "micro_linear": ("micro-linear", "mixed"),
+        "micro_yarn": ("micro-yarn", "mixed"),
+        "micro_l31": ("micro-l31", "mixed"),
     }
     out = {}
     for name, (arch, preset) in specs.items():

@@ -162,6 +162,23 @@ def test_mega_stream_plan_is_consistent(name, args, expect_bytes, n_cta):
         assert abs(r - expect_bytes) < 0.02 * expect_bytes
 
 
+@pytest.mark.parametrize("n_tiles,nkb", [
+    (48, 16), (32, 16), (224, 16), (32, 56), (1002, 16),      # llama3-8b: wq|wk|wv, attn_output, gate|up, ffn_down, output
+    (80, 32), (64, 32), (448, 32), (64, 112),                  # llama3-70b
+    (1, 1), (3, 7), (148, 1), (149, 1), (2, 300), (7, 4)])
+@pytest.mark.parametrize("n_sm", [148, 132, 8])
+def test_qgemm_work_split_is_consistent(n_tiles, nkb, n_sm):
+    """The batched-decode GEMM cuts its (panel, super-block) units into equal contiguous CTA ranges; every unit belongs to
+    exactly one range, the epilogue's arithmetic for "first CTA / number of segments of this panel" matches the ranges,
+    and no CTA needs more than its two partial-tile slots.  The check itself is qgemm_plan_check in the library."""
+    L = capi.lib()
+    L.b2_qgemm_plan_check.restype = ctypes.c_int64
+    L.b2_qgemm_plan_check.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    r = L.b2_qgemm_plan_check(n_tiles, nkb, n_sm)
+    assert r >= 0, (L.b2_last_error() or b"").decode()
+    assert r <= n_tiles
+
+
 def test_corrupt_gguf_headers_are_rejected(tmp_path, model_files):
     """Header fields are not trusted: a zero / non-power-of-two alignment, tensor offsets that wrap, element counts that
     overflow and counts beyond the file are parse errors, not divisions by zero, wild reads or huge allocations."""

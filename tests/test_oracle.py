@@ -170,3 +170,49 @@ def test_oracle_matches_transformers():
     assert r["bert_mini_f16"]["max_err_sigma"] <= 1e-4, r["bert_mini_f16"]
     for k in r:  # the run is deterministic: the committed numbers are reproduced
         assert abs(r[k]["max_err_sigma"] - gold[k]["max_err_sigma"]) <= 0.2 * gold[k]["max_err_sigma"] + 1e-7, (k, r[k], gold[k])
+
+
+def test_rope_scaling_changes_the_rotation_as_specified(model_files):
+    """RoPE scaling in the oracle (restated from ggml's rope_yarn; not pinned upstream): linear scaling by f is the
+    unscaled table at position p / f; YaRN leaves the highest frequencies unscaled and the lowest fully interpolated, with
+    the magnitude correction 1 + 0.1 ln(f); per-dimension divisors divide each frequency; and the fixtures that carry the
+    metadata evaluate differently from the unscaled model from the first rotated position on."""
+    import ctypes as C
+    L = O.lib()
+    L.ref_rope_cache_ext.argtypes = [C.c_float, C.c_float, C.c_float, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+    L.ref_rope_yarn_corr_dims.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p]
+    hd, base = 64, 10000.0
+
+    def ext(pos, scale, ff=None, ext_factor=0.0, corr=(0.0, 0.0)):
+        out = np.zeros(hd, np.float32)
+        c = np.array(corr, np.float32)
+        L.ref_rope_cache_ext(float(pos), scale, base, hd, ff.ctypes.data if ff is not None else None, ext_factor, 1.0, c.ctypes.data, out.ctypes.data)
+        return out
+
+    plain = lambda pos: O.rope_cache(pos, 1.0, base, hd)
+    # linear: theta(p) * (1/4) == theta(p/4)
+    np.testing.assert_allclose(ext(40, 0.25), plain(10), atol=2e-6)
+    # divisors: dimension pair i rotates at theta_i / ff_i
+    ff = np.linspace(1.0, 8.0, hd // 2).astype(np.float32)
+    got = ext(24, 1.0, ff)
+    theta = 24 * base ** (-2.0 * np.arange(hd // 2) / hd) / ff
+    np.testing.assert_allclose(got[0::2], np.cos(theta), atol=2e-5)
+    np.testing.assert_allclose(got[1::2], np.sin(theta), atol=2e-5)
+    # YaRN: correction range from the published formula; pair 0 (fastest) unscaled, last pair fully interpolated, both x mscale
+    corr = np.zeros(2, np.float32)
+    L.ref_rope_yarn_corr_dims(hd, 128, base, 32.0, 1.0, corr.ctypes.data)
+    want0 = np.floor(hd * np.log(128 / (32 * 2 * np.pi)) / (2 * np.log(base)))
+    want1 = np.ceil(hd * np.log(128 / (1 * 2 * np.pi)) / (2 * np.log(base)))
+    assert corr[0] == max(0.0, want0) and corr[1] == min(hd - 1.0, want1)
+    y = ext(50, 0.25, None, 1.0, tuple(corr))
+    ms = 1.0 + 0.1 * np.log(4.0)
+    np.testing.assert_allclose(y[0:2], plain(50)[0:2] * ms, atol=2e-5)
+    np.testing.assert_allclose(y[-2:], plain(12.5)[-2:] * ms, atol=2e-5)
+    # the fixtures: same tensors as the unscaled micro model except for the rotary tables
+    toks = np.arange(5, 25, dtype=np.int32)
+    ref = O.OracleModel(model_files["micro_mixed"], n_ctx=64).eval(toks, logits_all=True)
+    for name in ("micro_linear", "micro_yarn", "micro_l31"):
+        got = O.OracleModel(model_files[name], n_ctx=64).eval(toks, logits_all=True)
+        if name == "micro_linear":  # same tensors, and position 0 is not rotated: identical there (YaRN scales q and k by its
+            np.testing.assert_array_equal(got[0], ref[0])  # magnitude factor even at 0; micro_l31 has one more tensor, hence other weights)
+        assert np.abs(got[5:] - ref[5:]).max() > 1e-3, name

@@ -191,7 +191,8 @@ def test_mul_mat_linearity_in_rows():
     assert np.array_equal(full[:, 512:1024], part)
 
 
-MODELS = ["micro_mixed", "micro_q8_0", "mini_q4_k_m", "mini_q5_k", "mini_f16", "mini_q4_0", "mini_q5_1", "mini_q2_k", "mini_q3_k", "mini_iq4_nl", "mini_iq4_xs"]
+MODELS = ["micro_mixed", "micro_q8_0", "mini_q4_k_m", "mini_q5_k", "mini_f16", "mini_q4_0", "mini_q5_1", "mini_q2_k", "mini_q3_k", "mini_iq4_nl", "mini_iq4_xs",
+          "micro_linear", "micro_yarn", "micro_l31"]  # the last three: RoPE scaling (linear, YaRN, rope_freqs.weight divisors)
 
 
 @pytest.mark.parametrize("name", MODELS)

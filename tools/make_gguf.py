@@ -61,6 +61,10 @@ class Arch:
     rms_eps: float = 1e-5
     tokenizer: str = "spm"  # "spm" | "bpe"
     is_70b: bool = False
+    rope_scaling: str = "none"   # "none" | "linear" | "yarn"  (llama.rope.scaling.type)
+    rope_factor: float = 1.0     # llama.rope.scaling.factor
+    rope_orig_ctx: int = 0       # llama.rope.scaling.original_context_length
+    rope_freqs: bool = False     # write rope_freqs.weight (per-dimension frequency divisors, the Llama-3.1 scheme)
     head_dim: int = field(init=False)
 
     def __post_init__(self):
@@ -72,6 +76,10 @@ ARCHS = {
     "micro": Arch("micro", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm"),
     "mini": Arch("mini", 3, 512, 8, 2, 1024, 4608, 1024, 500000.0, 1e-5, "bpe"),
     "small": Arch("small", 8, 1024, 16, 4, 2816, 8192, 1024, 500000.0, 1e-5, "bpe"),          # deeper: error growth over 8 layers
+    # RoPE scaling variants of "micro" (the tokens and tensors are the same; only the rotary tables differ)
+    "micro-linear": Arch("micro-linear", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "linear", 4.0, 128),
+    "micro-yarn": Arch("micro-yarn", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "yarn", 4.0, 128),
+    "micro-l31": Arch("micro-l31", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "none", 1.0, 0, True),
     "mini-70b": Arch("mini-70b", 4, 2048, 16, 8, 4096, 8192, 1024, 500000.0, 1e-5, "bpe", True),  # 70B type mix (Q5_K attn_v), 8 KV heads; shards 2 / 4 / 8 ways
     # BASELINE.json configs
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 5632, 32000, 2048, 10000.0, 1e-5, "spm"),
@@ -433,10 +441,30 @@ def tensor_plan(arch: Arch, preset: str, gain_out: float):
             t = tensor_type(preset, arch, p + nm, i)
             norm = nm.endswith("_norm.weight")
             plan.append((p + nm, rows, cols, t, 0.0 if norm else 1.0 / np.sqrt(cols), norm))
+    if arch.rope_freqs:
+        plan.append(("rope_freqs.weight", 1, hd // 2, F32, 0.0, True))
     plan.append(("output_norm.weight", 1, d, F32, 0.0, True))
     plan.append(("output.weight", arch.n_vocab, d, tensor_type(preset, arch, "output.weight", 0),
                  gain_out / np.sqrt(d), False))
     return plan
+
+
+def llama31_rope_factors(head_dim: int, theta: float, orig_ctx: int, factor: float = 8.0, low: float = 1.0, high: float = 4.0):
+    """Per-dimension frequency divisors of the Llama-3.1 long-context scheme (what convert_hf_to_gguf stores as
+    rope_freqs.weight): wavelengths shorter than orig_ctx / high keep their frequency, longer than orig_ctx / low are
+    divided by `factor`, in between a smooth blend."""
+    out = np.empty(head_dim // 2, dtype=np.float64)
+    for i in range(head_dim // 2):
+        freq = theta ** (-2.0 * i / head_dim)
+        wavelen = 2 * np.pi / freq
+        if wavelen < orig_ctx / high:
+            out[i] = 1.0
+        elif wavelen > orig_ctx / low:
+            out[i] = factor
+        else:
+            smooth = (orig_ctx / wavelen - low) / (high - low)
+            out[i] = 1.0 / ((1 - smooth) / factor + smooth)
+    return out
 
 
 def tensor_nbytes(rows, cols, t):
@@ -446,12 +474,16 @@ def tensor_nbytes(rows, cols, t):
 
 def _write_tensor(job):
     """Generate one tensor (its own RNG stream) and write it at its offset in the file."""
-    path, off, idx, name, rows, cols, t, sigma, is_norm, seed, structured = job
+    path, off, idx, name, rows, cols, t, sigma, is_norm, seed, structured = job[:11]
     rng = np.random.default_rng([seed, idx])
     n = 0
     with open(path, "r+b") as f:
         f.seek(off)
-        if is_norm:
+        if name == "rope_freqs.weight":
+            w = llama31_rope_factors(cols * 2, *job[11]).astype(np.float32)
+            f.write(w.tobytes())
+            n = w.nbytes
+        elif is_norm:
             w = (1.0 + 0.1 * rng.standard_normal(cols)).astype(np.float32)
             f.write(w.tobytes())
             n = w.nbytes
@@ -503,6 +535,11 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
         kv_bytes("tokenizer.ggml.add_bos_token", T_BOOL, bool(vocab.get("add_bos", True))),
         kv_bytes("tokenizer.ggml.add_eos_token", T_BOOL, False),
     ]
+    if arch.rope_scaling != "none":
+        kvs.append(kv_bytes("llama.rope.scaling.type", T_STR, arch.rope_scaling))
+        kvs.append(kv_bytes("llama.rope.scaling.factor", T_F32, arch.rope_factor))
+        if arch.rope_orig_ctx:
+            kvs.append(kv_bytes("llama.rope.scaling.original_context_length", T_U32, arch.rope_orig_ctx))
     if vocab.get("unk", -1) >= 0:
         kvs.append(kv_bytes("tokenizer.ggml.unknown_token_id", T_U32, vocab["unk"]))
     if vocab["merges"]:
@@ -513,7 +550,7 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     infos = []
     off = 0
     for name, rows, cols, t, _, _ in plan:
-        dims = [cols] if rows == 1 and name.endswith("_norm.weight") else [cols, rows]
+        dims = [cols] if rows == 1 and (name.endswith("_norm.weight") or name == "rope_freqs.weight") else [cols, rows]
         infos.append(_s(name.encode()) + struct.pack("<I", len(dims)) + b"".join(struct.pack("<Q", x) for x in dims)
                      + struct.pack("<IQ", t, off))
         nb = tensor_nbytes(rows, cols, t)
@@ -529,7 +566,7 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     type_bytes: dict[str, int] = {}
     for idx, (name, rows, cols, t, sigma, is_norm) in enumerate(plan):
         nb = tensor_nbytes(rows, cols, t)
-        jobs.append((path, off, idx, name, rows, cols, t, sigma, is_norm, seed, structured))
+        jobs.append((path, off, idx, name, rows, cols, t, sigma, is_norm, seed, structured, (arch.rope_theta, arch.rope_orig_ctx or 64)))
         off += (nb + ALIGN - 1) // ALIGN * ALIGN
         type_bytes[TYPE_NAMES[t]] = type_bytes.get(TYPE_NAMES[t], 0) + nb
     total = off
