@@ -573,6 +573,8 @@ def main():
             b_flops = 2.0 * (lin_params + head_params) * n_par
             extra["decode_b%d" % n_par] = {
                 "tok_s": world * n_par * 1e3 / bms, "ms_per_step": bms, "launches_per_step": bl,
+                "kernel": "qgemm_kernel (2..64 tokens: GGUF blocks dequantised inside the tcgen05 GEMM, fp16 operand in TMEM; "
+                          "B200LLM_NO_QGEMM=1 selects the bf16-tile GEMM)" if n_par <= 64 and not os.environ.get("B200LLM_NO_QGEMM") else "gemm_tcgen05_kernel (bf16 tiles)",
                 "hbm": {"bound": "hbm", "achieved": b_bytes / (bms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                         "frac": b_bytes / (bms * 1e-3) / 1e9 / peak},
                 "tensor": {"bound": "tensor", "achieved": b_flops / (bms * 1e-3) / 1e12, "peak": tf_peak, "unit": "TFLOP/s",

@@ -217,9 +217,13 @@ int b2_metrics(b2_engine *e, b2_metrics_t *out);
  * b2_eval: evaluate `n` tokens at positions [n_past, n_past+n) of `slot`.
  *   logits: NULL, or host [n_vocab] (last token) / [n][n_vocab] if logits_all.
  *   embd:   NULL or host [n_embd]: final-norm hidden state of the last token (llama_get_embeddings).
+ * b2_eval_step: ONE decode step over several slots -- token i at position pos[i] of slot slots[i] (1 <= n <= n_batch) --
+ *   the batch shape the scheduler issues for concurrent streams (llama_decode on a multi-sequence batch,
+ *   grpc-server.cpp:1885-1915); logits: NULL or host [n][n_vocab].
  * b2_decode_greedy: prompt -> n_gen greedy tokens, sampling on device; only token ids cross PCIe.
  */
 int b2_eval(b2_engine *e, int slot, const int32_t *tokens, int n, int n_past, float *logits, int logits_all, float *embd);
+int b2_eval_step(b2_engine *e, const int32_t *tokens, const int32_t *pos, const int32_t *slots, int n, float *logits);
 int b2_decode_greedy(b2_engine *e, int slot, const int32_t *prompt, int n_prompt, int n_gen, int32_t *out,
                      double *prefill_ms, double *decode_ms);
 /* hidden state of the last evaluated token after each layer: host [n_layer+1][n_embd] (parity bisecting) */

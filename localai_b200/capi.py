@@ -26,7 +26,7 @@ EV_FINAL, EV_STOP_EOS, EV_STOP_WORD, EV_STOP_LIMIT, EV_ERROR, EV_EMBEDDING = 1, 
 EXPORTS = [
     "b2_tp_set_mode", "b2_tp_info", "b2_abi_version", "b2_last_error", "b2_device_count", "b2_create", "b2_destroy", "b2_model_info", "b2_tokenize",
     "b2_token_to_piece", "b2_submit", "b2_poll", "b2_cancel", "b2_embed_result", "b2_release", "b2_metrics", "b2_eval",
-    "b2_decode_greedy", "b2_debug_hidden", "b2_bench_decode", "b2_bench_prefill", "b2_bench_gemv", "b2_dequantize", "b2_quantize_act",
+    "b2_decode_greedy", "b2_eval_step", "b2_debug_hidden", "b2_bench_decode", "b2_bench_prefill", "b2_bench_gemv", "b2_dequantize", "b2_quantize_act",
     "b2_mul_mat", "b2_mul_mat_noalloc", "b2_sample", "b2_grammar_match", "b2_grammar_token_mask",
     "b2_bert_load", "b2_bert_free", "b2_bert_info", "b2_bert_tokenize", "b2_bert_embed_text", "b2_bert_embed_tokens",
     "b2_bert_embed_batch", "b2_bert_hidden",
@@ -316,6 +316,16 @@ class Engine:
         _check(lib().b2_eval(self._h, slot, _ptr(t), t.size, n_past, _ptr(logits), int(logits_all),
                              _ptr(embd) if want_embd else None))
         return (logits, embd) if want_embd else logits
+
+    def eval_step(self, tokens: Sequence[int], pos: Sequence[int], slots: Sequence[int]) -> np.ndarray:
+        """one decode step over several slots: logits [n][n_vocab]"""
+        t = np.ascontiguousarray(tokens, dtype=np.int32)
+        p = np.ascontiguousarray(pos, dtype=np.int32)
+        s = np.ascontiguousarray(slots, dtype=np.int32)
+        assert t.size == p.size == s.size
+        logits = np.empty((t.size, self.info.n_vocab), dtype=np.float32)
+        _check(lib().b2_eval_step(self._h, _ptr(t), _ptr(p), _ptr(s), t.size, _ptr(logits)))
+        return logits
 
     def decode_greedy(self, prompt: Sequence[int], n_gen: int, slot: int = 0):
         p = np.ascontiguousarray(prompt, dtype=np.int32)

@@ -1,6 +1,7 @@
 // attention.cuh -- paged-KV attention for one (head, query token), callable by any group of `nthreads` threads
 // (a whole CTA in attention_kernel, the CTA of the decode mega-kernel).  See kernels_misc.cu for the description.
 #pragma once
+#include <cuda_fp16.h>
 #include "kernels.h"
 #include "quant.cuh"
 
@@ -130,10 +131,22 @@ __host__ __device__ inline size_t attention_group_smem_bytes(int G, int hd, int 
     return sizeof(float) * ((size_t)G * hd + (size_t)G * 32 + (size_t)(nthreads / 32) * G * hd + (size_t)G * n_pad + (size_t)max_ctx / 8 + 8);
 }
 
+// Element offset of (token r, feature k) in the fp16 activation tiles of the batched-decode GEMM (kernels_qgemm.cu):
+// [k / 256][r / 8][(k % 256) / 8][r % 8][k % 8], and inside every group of four k the positions hold elements (0, 2, 1, 3).
+__host__ __device__ inline int64_t qg_x_offset(int r, int64_t k, int n_pad) {
+    return (k >> 8) * ((int64_t)n_pad * 256) + (int64_t)(r >> 3) * 2048 + (int64_t)((k & 255) >> 3) * 64 + (r & 7) * 8 + (k & 7);
+}
+__host__ __device__ inline int64_t qg_x_offset_of_element(int r, int64_t k, int n_pad) { // k = the element's true index
+    return qg_x_offset(r, (k & ~(int64_t)3) | ((k & 1) << 1) | ((k >> 1) & 1), n_pad);
+}
+
+// x16 (optional): write the G output rows as fp16 into the GEMM's activation tiles (token x16_tok, features x16_k0 ..)
+// instead of fp32 rows -- the fused decode-attention kernel feeds attn_output's GEMM directly.
 template <int G>
 __device__ __forceinline__ void attention_group(const float *__restrict__ qrows, int n_kv, const int32_t *__restrict__ pt,
                                                 const KVLayout &kv, int hk, int hd, float scale, float *__restrict__ orows,
-                                                float *smem, int tid, int nthreads) {
+                                                float *smem, int tid, int nthreads, __half *__restrict__ x16 = nullptr,
+                                                int x16_tok = 0, int64_t x16_k0 = 0, int x16_n_pad = 0) {
     const int lane = tid & 31, warp = tid >> 5, nwarps = nthreads >> 5;
     const int n_pad = (n_kv + 3) & ~3;
     float *qs = smem;                            // [G][hd]   (the G heads are consecutive rows of q)
@@ -229,11 +242,12 @@ __device__ __forceinline__ void attention_group(const float *__restrict__ qrows,
     for (int g = 0; g < G; g++)
 #pragma unroll
         for (int i = 0; i < 8; i++) acc[g][i] = 0.f;
-    for (int j0 = warp * 4; j0 < n_kv; j0 += nwarps * 4) {
-        uint32_t raw[4][4];
-        int jj[4];
+    constexpr int PP = 4; // V rows in flight per warp
+    for (int j0 = warp * PP; j0 < n_kv; j0 += nwarps * PP) {
+        uint32_t raw[PP][4];
+        int jj[PP];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < PP; u++) {
             const int j = j0 + u;
             jj[u] = j < n_kv ? j : -1;
             const int jc = j < n_kv ? j : 0;
@@ -244,7 +258,7 @@ __device__ __forceinline__ void attention_group(const float *__restrict__ qrows,
             else { raw[u][0] = *(const uint32_t *)vr; raw[u][1] = 0; raw[u][2] = 0; raw[u][3] = 0; }
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < PP; u++) {
 #pragma unroll
             for (int g = 0; g < G; g++) {
                 const float p = jj[u] >= 0 ? sc[g * n_pad + jj[u]] : 0.f;
@@ -268,7 +282,8 @@ __device__ __forceinline__ void attention_group(const float *__restrict__ qrows,
     for (int i = tid; i < G * hd; i += nthreads) { // i = g * hd + dim; the G output rows are consecutive
         float o = 0.f;
         for (int w = 0; w < nwarps; w++) o += part[(size_t)w * G * hd + i];
-        orows[i] = o;
+        if (x16) x16[qg_x_offset_of_element(x16_tok, x16_k0 + i, x16_n_pad)] = __float2half_rn(fminf(fmaxf(o, -65504.f), 65504.f));
+        else orows[i] = o;
     }
     att_sync(nthreads);
 }

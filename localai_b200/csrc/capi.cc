@@ -177,6 +177,12 @@ int b2_eval(b2_engine *e, int slot, const int32_t *tokens, int n, int n_past, fl
     B2_API_END(0)
 }
 
+int b2_eval_step(b2_engine *e, const int32_t *tokens, const int32_t *pos, const int32_t *slots, int n, float *logits) {
+    B2_API_BEGIN
+    return E(e)->eval_step(tokens, pos, slots, n, logits);
+    B2_API_END(0)
+}
+
 int b2_decode_greedy(b2_engine *e, int slot, const int32_t *prompt, int n_prompt, int n_gen, int32_t *out, double *prefill_ms,
                      double *decode_ms) {
     B2_API_BEGIN

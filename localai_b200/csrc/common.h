@@ -49,7 +49,7 @@ struct PerDeviceOnce {
     }
 };
 
-// Programmatic dependent launch (the kernels of a batched decode step, B200LLM_NO_PDL=1 turns it off): the next kernel of
+// Programmatic dependent launch (the kernels of a batched decode step; opt-in with B200LLM_PDL=1): the next kernel of
 // the stream may be set up while this one still runs; it blocks in B2_PDL_WAIT() -- before its first access to anything an
 // earlier kernel of the stream may have written or may still read -- until the previous kernel has completed and flushed.
 // Every kernel launched this way waits before it exits, so completion is transitive along the stream.  Both instructions

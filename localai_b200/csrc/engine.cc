@@ -230,6 +230,24 @@ int Engine::eval(int slot, const int32_t *tokens, int n, int n_past, float *logi
     return 0;
 }
 
+// one decode step over several slots (what the scheduler issues for concurrent streams): token i at position pos[i] of
+// slot slots[i], every row's logits back.  Test / measurement hook (b2_eval_step).
+int Engine::eval_step(const int32_t *tokens, const int32_t *pos, const int32_t *slots, int n, float *logits) {
+    Model &m = model();
+    B2_CHECK(tokens && pos && slots && n > 0 && n <= m.n_batch, B2_EINVAL, "eval_step: 1..n_batch tokens");
+    std::lock_guard<std::mutex> lk(dev_mu_);
+    Batch b;
+    b.n = n;
+    b.tokens = tokens;
+    b.pos = pos;
+    b.slot = slots;
+    b.n_out = -1;
+    m.forward(b);
+    if (logits) B2_CUDA(cudaMemcpyAsync(logits, m.logits_dev(), (size_t)n * m.hp.n_vocab * 4, cudaMemcpyDeviceToHost, m.stream));
+    m.sync();
+    return 0;
+}
+
 int Engine::decode_greedy(int slot, const int32_t *prompt, int n_prompt, int n_gen, int32_t *out, double *prefill_ms,
                           double *decode_ms) {
     Model &m = model();

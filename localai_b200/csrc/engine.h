@@ -43,6 +43,7 @@ class Engine {
     double last_mega_ms() const { return last_mega_ms_; } // mean decode_mega_kernel launch of the last bench_decode(batch 1)
     double last_mega_ms_ = 0.0;
     double last_tp_allreduce_ms_ = 0.0; // tensor-parallel model, TP_NCCL mode: ms inside ncclAllReduce per step of the last bench_decode
+    int eval_step(const int32_t *tokens, const int32_t *pos, const int32_t *slots, int n, float *logits);
     int bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type);
     int bench_prefill(int n_tokens, int n_iters, int n_warmup, double *ms_per_iter, int64_t *launches);
 

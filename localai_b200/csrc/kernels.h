@@ -245,6 +245,11 @@ void launch_qgemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t
 void launch_qgemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const float *w, int n_tok, int64_t K, float eps, void *x_tiles,
                                     cudaStream_t s);
 void launch_qgemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
+// decode batches whose tokens sit in different slots: RoPE + KV store + attention + fp16 activation tiles in one launch;
+// false = no mapping for this head geometry / context (the caller runs the three separate kernels)
+bool launch_attention_decode_fused(float *q, const float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok, int n_head,
+                                   int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, int max_ctx, void *x_tiles, int n_pad,
+                                   cudaStream_t s);
 struct QGemmJob {
     const DTensor *W;
     const void *q_tiles; // launch_qgemm_repack(W)

@@ -7,9 +7,10 @@
 
 namespace b2 {
 
-bool pdl_enabled() {
-    static const bool on = !(getenv("B200LLM_NO_PDL") && atoi(getenv("B200LLM_NO_PDL")));
-    return on;
+bool pdl_enabled() { // B200LLM_PDL=1; read at every launch on purpose: the A/B test flips it inside one process.
+    // Off by default: measured on a 64-stream decode step of Llama-3-8B, 5.00 ms with it against 4.79 ms without.
+    const char *e = getenv("B200LLM_PDL");
+    return e && atoi(e);
 }
 
 // ------------------------------------------------------------------------------------------ RMSNorm (* weight)
@@ -143,6 +144,81 @@ attention_group_kernel(const float *__restrict__ q, const int32_t *__restrict__ 
     const int64_t row0 = ((int64_t)t * n_head + (int64_t)hk * G) * hd; // heads hk*G .. hk*G+G-1 are consecutive
     attention_group<G>(q + row0, pos[t] + 1, kv.page_table + (int64_t)slot[t] * kv.max_pages, kv, hk, hd, scale, out + row0, smem,
                        threadIdx.x, ATT_THREADS);
+}
+
+// Decode batches whose tokens all sit in different slots: RoPE of q (in place) and k, the KV store of this token, the
+// attention of the G query heads and the conversion of the output into the next GEMM's fp16 activation tiles in ONE
+// launch (rope_kv_store_kernel + attention_group_kernel + qgemm_convert_x_kernel otherwise).  The CTA (KV head hk,
+// token t) owns everything it touches: the G query heads of the group, row hk of k and v, one cache cell.
+template <int G, int MINB>
+__global__ void __launch_bounds__(ATT_THREADS, MINB)
+attention_decode_fused_kernel(float *__restrict__ q, const float *__restrict__ k, const float *__restrict__ v,
+                              const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head, int n_head_kv, int hd,
+                              const float *__restrict__ rope_table, KVLayout kv, float scale, __half *__restrict__ x16, int n_pad) {
+    extern __shared__ __align__(16) float smem[];
+    B2_PDL_TRIGGER();
+    B2_PDL_WAIT();
+    const int hk = blockIdx.x, t = blockIdx.y;
+    const int p = pos[t], sl = slot[t];
+    const float *cs = rope_table + (int64_t)p * hd;
+    const int half = hd / 2;
+    const int page = kv.page_table[(int64_t)sl * kv.max_pages + p / kv.page_size];
+    const int64_t cell = ((int64_t)page * kv.page_size + p % kv.page_size) * kv.kvd;
+    const int64_t row0 = ((int64_t)t * n_head + (int64_t)hk * G) * hd;
+    float *qt = q + row0;
+    const float *kt = k + ((int64_t)t * n_head_kv + hk) * hd, *vt = v + ((int64_t)t * n_head_kv + hk) * hd;
+    for (int i = threadIdx.x; i < (G + 1) * half; i += blockDim.x) { // the arithmetic of rope_kv_store_kernel
+        const bool is_q = i < G * half;
+        const int ii = is_q ? i : i - G * half;
+        const int h = ii / half, pr = ii % half;
+        const float *x = (is_q ? qt + h * hd : kt) + 2 * pr;
+        const float c = cs[2 * pr], sn = cs[2 * pr + 1];
+        const float x0 = x[0], x1 = x[1];
+        const float r0 = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn));
+        const float r1 = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
+        if (is_q) {
+            qt[h * hd + 2 * pr] = r0;
+            qt[h * hd + 2 * pr + 1] = r1;
+        } else {
+            *(__half2 *)(kv.k_pool + cell + hk * hd + 2 * pr) = __halves2half2(__float2half_rn(r0), __float2half_rn(r1));
+        }
+    }
+    for (int i = threadIdx.x; i < hd; i += blockDim.x) kv.v_pool[cell + hk * hd + i] = __float2half_rn(vt[i]);
+    __threadfence_block();
+    __syncthreads(); // this CTA's q rows and cache cell are written: the attention below reads them back (L2 / L1 of this SM)
+    attention_group<G>(qt, p + 1, kv.page_table + (int64_t)sl * kv.max_pages, kv, hk, hd, scale, nullptr, smem, threadIdx.x, ATT_THREADS, x16, t,
+                       ((int64_t)hk * G) * hd, n_pad);
+}
+
+template <int G>
+static bool try_launch_attention_decode_fused(float *q, const float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok,
+                                              int n_head, int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, int max_ctx,
+                                              void *x16, int n_pad, cudaStream_t s) {
+    const size_t smem = attention_group_smem_bytes(G, hd, max_ctx, ATT_THREADS);
+    if (smem > 96 * 1024) return false;
+    const float scale = 1.0f / sqrtf((float)hd);
+    // 4 CTAs per SM where the registers allow (G <= 4): a 64-stream step of 8 KV heads is 512 CTAs = one wave of 148 x 4.
+    // Measured on Llama-3-8B, 64 streams: 4.61 ms per step against 4.76 at 3 CTAs/SM; 8 V rows in flight per warp and
+    // scores by lane groups (coalesced K rows) were slower (4.70 / 4.93 ms: registers, hence fewer resident CTAs).
+    constexpr int MINB = G <= 4 ? 4 : 3;
+    static PerDeviceOnce configured;
+    configured.run([&] { B2_CUDA(cudaFuncSetAttribute(attention_decode_fused_kernel<G, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); });
+    launch_pdl(attention_decode_fused_kernel<G, MINB>, dim3(n_head_kv, n_tok), dim3(ATT_THREADS), smem, s, q, k, v, pos, slot, n_head, n_head_kv, hd,
+               rope_table, kv, scale, (__half *)x16, n_pad);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+    return true;
+}
+
+bool launch_attention_decode_fused(float *q, const float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok, int n_head,
+                                   int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, int max_ctx, void *x_tiles, int n_pad,
+                                   cudaStream_t s) {
+    if (n_tok <= 0 || n_head % n_head_kv != 0 || hd > 128 || hd % 32 != 0) return false;
+    const int G = n_head / n_head_kv;
+    if (G == 2) return try_launch_attention_decode_fused<2>(q, k, v, pos, slot, n_tok, n_head, n_head_kv, hd, rope_table, kv, max_ctx, x_tiles, n_pad, s);
+    if (G == 4) return try_launch_attention_decode_fused<4>(q, k, v, pos, slot, n_tok, n_head, n_head_kv, hd, rope_table, kv, max_ctx, x_tiles, n_pad, s);
+    if (G == 8) return try_launch_attention_decode_fused<8>(q, k, v, pos, slot, n_tok, n_head, n_head_kv, hd, rope_table, kv, max_ctx, x_tiles, n_pad, s);
+    return false;
 }
 
 template <int G>

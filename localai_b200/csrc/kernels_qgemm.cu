@@ -29,6 +29,7 @@
 
 #include <vector>
 
+#include "attention.cuh"
 #include "kernels.h"
 #include "quant.cuh"
 
@@ -110,9 +111,7 @@ void launch_qgemm_repack(const DTensor &W, void *q_tiles, cudaStream_t s) {
 // ------------------------------------------------------------------------------------------------ activation tiles
 // x tiles: [kb = K/256][tok/8][k/8 = 32][8 tok][8 k] fp16 -- one 256-k stage of all (padded) tokens is contiguous, and a
 // K = 16 MMA step is two adjacent 128-byte core matrices (LBO 128 B along K, SBO 4096 B between 8-token groups).
-__device__ __forceinline__ int64_t qg_x_offset(int r, int64_t k, int n_pad) {
-    return (k >> 8) * ((int64_t)n_pad * 256) + (int64_t)(r >> 3) * 2048 + (int64_t)((k & 255) >> 3) * 64 + (r & 7) * 8 + (k & 7);
-}
+// (qg_x_offset: attention.cuh -- the fused decode-attention kernel writes these tiles too)
 __device__ __forceinline__ void qg_store8(__half *out, int r, int64_t k0, int n_pad, const float (&v)[8]) {
     __half2 p[4];
 #pragma unroll
@@ -804,6 +803,10 @@ void qgemm_plan(int n_tiles, int nkb, int n_sm, bool allow_pairs, QGemmPlan *pl)
     int T = 1;
     // pairs of tiles share the activation stage; only when a CTA's range then still spans whole panels (few split tiles)
     if (allow_pairs && n_tiles % 2 == 0 && (int64_t)(n_tiles / 2) * nkb >= (int64_t)nkb * n_sm) T = 2;
+    if (const char *e = getenv("B200LLM_QG_T")) { // A/B measurements: 1 / 2 force the panel width where it divides
+        const int f = atoi(e);
+        if (f == 1 || (f == 2 && n_tiles % 2 == 0 && n_tiles / 2 * (int64_t)nkb >= n_sm)) T = f;
+    }
     pl->T = T;
     pl->panels = n_tiles / T;
     pl->units = (int64_t)pl->panels * nkb;

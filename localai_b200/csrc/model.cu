@@ -87,6 +87,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     no_mega_ = getenv("B200LLM_NO_MEGA") && atoi(getenv("B200LLM_NO_MEGA")) != 0;
     no_gemm_ = getenv("B200LLM_NO_GEMM") && atoi(getenv("B200LLM_NO_GEMM")) != 0;
     no_qgemm_ = getenv("B200LLM_NO_QGEMM") && atoi(getenv("B200LLM_NO_QGEMM")) != 0;
+    no_fused_att_ = getenv("B200LLM_NO_FUSED_ATT") && atoi(getenv("B200LLM_NO_FUSED_ATT")) != 0;
     no_shadow_ = getenv("B200LLM_NO_BF16_TILES") && atoi(getenv("B200LLM_NO_BF16_TILES")) != 0;
     if (getenv("B200LLM_GEMM_MIN_TOKENS")) gemm_min_tokens_ = atoi(getenv("B200LLM_GEMM_MIN_TOKENS"));
     else gemm_min_tokens_ = -1; // automatic, see gemm_threshold()
@@ -590,9 +591,15 @@ void Model::run_layer_qgemm(const LayerW &L, const KVLayout &kv, int n) {
         const int64_t strides[3] = {d, kvd, kvd};
         B2_CHECK(qgemm_multi(Ws, outs, strides, 3, n, nullptr, 0), B2_ESTATE, "qgemm: tiles missing");
     }
-    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
-    attention(kv, n);
-    launch_qgemm_prepare_x(att_, d, n, d, gemm_x_, stream);
+    // tokens in different slots (a decode step over many streams): RoPE, KV store, attention and the conversion of its
+    // output into attn_output's activation tiles are one launch; otherwise (several tokens of one slot) three
+    if (!(slots_distinct_ && !no_fused_att_ &&
+          launch_attention_decode_fused(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, n_ctx_slot, gemm_x_,
+                                        (int)align_up(n, 16), stream))) {
+        launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+        attention(kv, n);
+        launch_qgemm_prepare_x(att_, d, n, d, gemm_x_, stream);
+    }
     {
         const DTensor *Ws[1] = {&L.wo};
         float *outs[1] = {x_};
@@ -898,6 +905,13 @@ void Model::forward(const Batch &b) {
     int n_out = b.n_out;
     bool pure_decode = n_out == b.n && b.n < (int)decode_graphs_.size(); // every row wants logits, in order
     for (int i = 0; pure_decode && i < n_out; i++) pure_decode = b.out_rows[i] == i;
+    // every token in its own slot?  (then no token of the batch attends to another one's K/V row, and the captured decode
+    // graphs -- which hold the fused RoPE + attention kernel -- apply)
+    slots_distinct_ = true;
+    for (int i = 1; slots_distinct_ && i < b.n; i++)
+        for (int j = 0; j < i; j++)
+            if (b.slot[j] == b.slot[i]) { slots_distinct_ = false; break; }
+    if (pure_decode && !slots_distinct_ && b.n > 1) pure_decode = false; // several tokens of one slot: the un-captured path, all rows
     if (pure_decode) {
         runs_.clear(); // one per-token attention launch for the whole batch (and what the captured graph holds)
         run_decode_graphed(b.n);
@@ -914,8 +928,9 @@ void Model::set_device_inputs(const int32_t *tokens, const int32_t *pos, const i
     B2_CUDA(cudaMemcpyAsync(slot_, slot, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
 }
 
-void Model::forward_device_inputs(int n) {
+void Model::forward_device_inputs(int n) { // (device-resident decode loops: one token per slot by construction)
     B2_CUDA(cudaSetDevice(device));
+    slots_distinct_ = true;
     if (tp_size > 1) {
         forward_device_inputs_tp(n);
         return;

@@ -145,6 +145,8 @@ class Model {
     std::unordered_map<const uint8_t *, void *> q_tiles_;
     float *qg_part_ = nullptr;
     unsigned *qg_counters_ = nullptr;
+    bool slots_distinct_ = false; // the current batch has one token per slot (set by forward / forward_device_inputs)
+    bool no_fused_att_ = false;   // B200LLM_NO_FUSED_ATT=1: RoPE / attention / tile conversion as three launches (A/B tests)
     bool no_qgemm_ = false;   // B200LLM_NO_QGEMM=1: the bf16-tile path for every batch size (A/B tests)
     void *resident_qtiles(const DTensor &W);
     bool qgemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n, const float *residual,

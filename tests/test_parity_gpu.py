@@ -331,3 +331,72 @@ def test_tinyllama_q8_0_greedy_64_full_size(gguf_dir):
     assert_logits_close(logits, wl, "tinyllama prompt logits")
     assert got.tolist() == want.tolist()
     os.remove(path)
+
+
+@pytest.mark.parametrize("n_tok", [2, 5, 16, 40, 64])
+def test_batched_decode_paths_agree(model_files, n_tok, monkeypatch):
+    """A step of 2..64 tokens that all want logits (the shape of a decode step over many streams; the engine runs it as one
+    step) through (a) the GEMM that dequantises inside the kernel (the default), (b) the same launched with programmatic
+    dependent launch, (c) the bf16-tile GEMM.  (a) and (b) are bit-identical --
+    the launch attribute changes scheduling, not arithmetic -- and stay so when the graph is replayed; all three hold the
+    oracle's logits within the stated tolerance."""
+    path = model_files["mini_q4_k_m"]
+    toks = np.random.default_rng(n_tok).integers(0, 4000, n_tok + 8).astype(np.int32)
+
+    def run():
+        with capi.Engine(path, n_ctx=128, n_batch=64) as e:
+            e.eval(toks[:8])                                             # a short prompt first: the step attends to a non-empty cache
+            first = e.eval(toks[8:], n_past=8, logits_all=True).copy()   # builds the graph
+            again = e.eval(toks[8:], n_past=8, logits_all=True)          # replays it
+            assert np.array_equal(first, again)
+            return first
+
+    a = run()
+    monkeypatch.setenv("B200LLM_PDL", "1")
+    b = run()
+    monkeypatch.delenv("B200LLM_PDL")
+    monkeypatch.setenv("B200LLM_NO_QGEMM", "1")
+    c = run()
+    assert np.array_equal(a, b)
+    ref = O.OracleModel(path, n_ctx=128).eval(toks, logits_all=True)[8:]
+    assert_logits_close(a, ref, "qgemm")
+    assert_logits_close(c, ref, "bf16 tiles")
+
+
+@pytest.mark.parametrize("n_streams", [2, 7, 16, 33, 64])
+def test_decode_step_over_many_slots(model_files, n_streams, monkeypatch):
+    """ONE decode step over n_streams slots with prompts of different lengths (b2_eval_step: the batch shape the scheduler
+    issues for concurrent streams).  The default path is a CUDA graph of: RMSNorm -> fp16 tiles, the GEMM that dequantises
+    inside the kernel, the fused RoPE + KV-store + attention + tile-conversion kernel, ....  Its logits equal, bit for bit,
+    those of the same step (a) replayed and (b) launched with programmatic dependent launch (the attribute changes
+    scheduling, not arithmetic) and (c) run with RoPE / attention / conversion as three launches (the same arithmetic in
+    the same order); they hold the oracle's logits of each stream within the stated tolerance, as does (d) the bf16-tile
+    GEMM path."""
+    path = model_files["mini_q4_k_m"]
+    rng = np.random.default_rng(100 + n_streams)
+    prompts = [rng.integers(0, 4000, 5 + (3 * i) % 17).astype(np.int32) for i in range(n_streams)]
+    toks = np.array([int(rng.integers(0, 4000)) for _ in prompts], np.int32)
+    pos = np.array([len(p) for p in prompts], np.int32)
+    slots = np.arange(n_streams, dtype=np.int32)
+
+    def run(replay=False):
+        with capi.Engine(path, n_ctx=32 * n_streams, n_batch=64, n_parallel=n_streams) as e:
+            for s_, p in enumerate(prompts):
+                e.eval(p, slot=s_)
+            out = e.eval_step(toks, pos, slots).copy()
+            if replay:  # the same step again overwrites the same cache cells with the same values
+                assert np.array_equal(out, e.eval_step(toks, pos, slots))
+            return out
+
+    a = run(replay=True)
+    monkeypatch.setenv("B200LLM_PDL", "1")
+    assert np.array_equal(a, run())
+    monkeypatch.delenv("B200LLM_PDL")
+    monkeypatch.setenv("B200LLM_NO_FUSED_ATT", "1")
+    assert np.array_equal(a, run())
+    monkeypatch.delenv("B200LLM_NO_FUSED_ATT")
+    monkeypatch.setenv("B200LLM_NO_QGEMM", "1")
+    d = run()
+    ref = np.stack([O.OracleModel(path, n_ctx=64).eval(np.append(p, t))[0] for p, t in zip(prompts, toks)])
+    assert_logits_close(a, ref, "default path")
+    assert_logits_close(d, ref, "bf16 tiles")
