@@ -303,12 +303,13 @@ def bench_pool(path, rank, world, ranks):
     if rank == 0:
         from localai_b200.replicas import ReplicaPool
 
-        n_streams, n_predict = 64 * world, 32
+        n_streams, n_predict = 64 * world, 128
         pool = ReplicaPool(path, devices=list(range(world)), n_ctx=64 * 256, n_batch=512, n_parallel=64)
         try:
             rng = np.random.default_rng(5)
             prompts = [rng.integers(3, 4000, 16).astype(np.int32) for _ in range(n_streams)]
-            warm = [pool.submit(prompt_ids=p, n_predict=4, temperature=0.0, ignore_eos=True, stream=False) for p in prompts[:world]]
+            # warm-up: the same wave of requests once, short (captures the decode graphs of the batch sizes the wave goes through)
+            warm = [pool.submit(prompt_ids=p, n_predict=8, temperature=0.0, ignore_eos=True, stream=False) for p in prompts]
             for h in warm:
                 list(pool.events(h))
             pool.assigned = [0] * len(pool.devices)
