@@ -1073,17 +1073,21 @@ decode_mega_kernel(const __grid_constant__ MegaArgs a) {
         if (DBG && tid == 0) { t0 = clock64(); g0 = mg_gtime(); }
         int u = 0, u_end = 0;
         if (ph.kind == PH_ATT) {
-            // a head is shared by att_parts CTAs (att_parts * n_head <= n_cta whenever att_parts > 1)
-            const int n_att = a.n_head * a.att_parts, n_comb = a.att_parts > 1 ? n_cta - n_att : 0; // CTAs left over collect the parts' rows
+            // a head is shared by `parts` CTAs (att_parts * n_head <= n_cta whenever att_parts > 1): att_parts for long
+            // contexts, 2 below 192 positions, where the second split costs more in exchanges than it saves in rows
+            // (Llama-3-8B: 1.658 against 1.672 ms per token at 128 positions, 1.82 against 1.74 at 512; every CTA reads
+            // the same position, so all of them take the same branch)
+            const int parts = (a.att_parts > 2 && pos + 1 < 192) ? 2 : a.att_parts, parts_log = parts > 2 ? a.att_parts_log : (parts == 2 ? 1 : 0);
+            const int n_att = a.n_head * parts, n_comb = parts > 1 ? n_cta - n_att : 0; // CTAs left over collect the parts' rows
             for (int hp = cta; hp < n_att; hp += n_cta) {
-                const int h = hp >> a.att_parts_log, part = hp & (a.att_parts - 1), hk = h / (a.n_head / a.n_head_kv);
+                const int h = hp >> parts_log, part = hp & (parts - 1), hk = h / (a.n_head / a.n_head_kv);
                 mg_attention_ll(ph.x_ll + (int64_t)h * a.hd, a.kcur_ll, a.vcur_ll, tag_in, pos + 1, pbase, ph.k_pool, ph.v_pool, a.page_shift,
-                                a.kvd, hk, a.hd, a.att_scale, ph.out_ll + (int64_t)h * a.hd, (float *)xs, tid, part, a.att_parts,
-                                a.att_scores + (int64_t)h * a.att_scores_stride, a.att_part_out + (int64_t)h * a.att_parts * a.hd, tag_out, n_comb <= 0);
+                                a.kvd, hk, a.hd, a.att_scale, ph.out_ll + (int64_t)h * a.hd, (float *)xs, tid, part, parts,
+                                a.att_scores + (int64_t)h * a.att_scores_stride, a.att_part_out + (int64_t)h * parts * a.hd, tag_out, n_comb <= 0);
             }
             if (n_comb > 0 && cta >= n_att)
                 for (int h = cta - n_att; h < a.n_head; h += n_comb)
-                    mg_attention_combine(a.att_part_out + (int64_t)h * a.att_parts * a.hd, a.att_parts, a.hd, ph.out_ll + (int64_t)h * a.hd, tag_out, tid);
+                    mg_attention_combine(a.att_part_out + (int64_t)h * parts * a.hd, parts, a.hd, ph.out_ll + (int64_t)h * a.hd, tag_out, tid);
             __syncthreads(); // the mid-phase sync of a phase without rows
             stage_phase(p + 2);
         } else {
