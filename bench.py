@@ -445,7 +445,7 @@ def run_bert(args, rank, local_rank, world, ranks, emit, warmup):
     launches_per_step = 2 + a.n_layer * 10 + 2
     emit({"metric": "BERT-base F16 embeddings seq/s (512-token texts)", "value": v, "unit": "seq/s", "n_gpus": world, "steps": args.steps,
           "warmup": warmup, "ms_per_step": dt * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-          "dtype": "bf16 operands, f32 accumulate (weights F16 in the file)", "data": "synthetic",
+          "dtype": "fp16 GEMM operands (the file's F16 weights exactly), bf16 attention operands, f32 accumulate", "data": "synthetic",
           "config": {"workload": "bert-base f16 random-init GGUF, 16 texts x 512 tokens per b2_bert_embed_batch call", "replicas": world,
                      "l2": "inputs larger than L2: a step moves 25-100 MB per activation tensor, 24 tensors per layer pass"},
           "e2e": {"value": v, "unit": "seq/s", "h2d_bytes_per_step": int(ids.nbytes + offs.nbytes), "d2h_bytes_per_step": int(out.nbytes),
@@ -575,7 +575,7 @@ def main():
             extra["decode_b%d" % n_par] = {
                 "tok_s": world * n_par * 1e3 / bms, "ms_per_step": bms, "launches_per_step": bl,
                 "kernel": "qgemm_kernel (2..64 tokens: GGUF blocks dequantised inside the tcgen05 GEMM, fp16 operand in TMEM; "
-                          "B200LLM_NO_QGEMM=1 selects the bf16-tile GEMM)" if n_par <= 64 and not os.environ.get("B200LLM_NO_QGEMM") else "gemm_tcgen05_kernel (bf16 tiles)",
+                          "B200LLM_NO_QGEMM=1 selects the fp16-tile GEMM)" if n_par <= 64 and not os.environ.get("B200LLM_NO_QGEMM") else "gemm_tcgen05_kernel (fp16 tiles)",
                 "hbm": {"bound": "hbm", "achieved": b_bytes / (bms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                         "frac": b_bytes / (bms * 1e-3) / 1e9 / peak},
                 "tensor": {"bound": "tensor", "achieved": b_flops / (bms * 1e-3) / 1e12, "peak": tf_peak, "unit": "TFLOP/s",

@@ -42,7 +42,7 @@ enum { B2_T_F32 = 0, B2_T_F16 = 1, B2_T_Q4_0 = 2, B2_T_Q4_1 = 3, B2_T_Q5_0 = 6, 
        B2_T_Q3_K = 11, B2_T_IQ4_NL = 20, B2_T_IQ4_XS = 23, B2_T_Q4_K = 12,
        B2_T_Q5_K = 13, B2_T_Q6_K = 14 };
 /* Q4_0 / Q4_1 / Q5_0 / Q5_1 (legacy 32-element blocks) and Q2_K / Q3_K / IQ4_NL / IQ4_XS run on the tensor-core path only: dequantised once into resident
- * bf16 operand tiles; the integer decode kernels cover Q8_0 and the K-quants. */
+ * fp16 operand tiles; the integer decode kernels cover Q8_0 and the K-quants. */
 
 typedef struct b2_engine b2_engine;
 

@@ -3,7 +3,7 @@
 // model stored as GGUF (general.architecture = "bert"), which the llama-cpp backend serves through `Embedding`
 // (backend/cpp/llama/grpc-server.cpp:2410-2432).  One text -> one vector: mean over tokens, L2-normalised.
 //
-// Device layout: every linear weight is dequantised once into resident bf16 UMMA operand tiles (the tcgen05 GEMM of
+// Device layout: every linear weight is dequantised once into resident fp16 UMMA operand tiles (the tcgen05 GEMM of
 // kernels_gemm.cu runs all six mat-muls of a layer); biases, LayerNorm parameters and the position / token-type tables
 // are fp32; activations fp32 rows [token][feature].  Several sequences are packed into one forward (the GEMMs see
 // the total token count, attention and pooling work per sequence) -- there is no KV cache and no causal mask.
@@ -35,7 +35,7 @@ class WpmTokenizer {
 
 struct BertLayer {
     DTensor wq, wk, wv, wo, up, down;
-    void *tq = nullptr, *tk = nullptr, *tv = nullptr, *to = nullptr, *tup = nullptr, *tdown = nullptr; // bf16 tiles
+    void *tq = nullptr, *tk = nullptr, *tv = nullptr, *to = nullptr, *tup = nullptr, *tdown = nullptr; // fp16 tiles
     float *bq = nullptr, *bk = nullptr, *bv = nullptr, *bo = nullptr, *bup = nullptr, *bdown = nullptr;
     float *ln1_w = nullptr, *ln1_b = nullptr, *ln2_w = nullptr, *ln2_b = nullptr;
 };

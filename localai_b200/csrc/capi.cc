@@ -374,7 +374,7 @@ int b2_mul_mat(int wtype, const void *blocks, int64_t rows, int64_t cols, const 
     const uint8_t *xq = dq.as<uint8_t>();
     if (f == ACT_F32) xq = dx.as<uint8_t>();
     else launch_quantize_act(f, dx.as<float>(), cols, n_tok, cols, dq.as<uint8_t>(), 0);
-    if (path == 2) { // tensor-core GEMM (bf16 operands, fp32 accumulate)
+    if (path == 2) { // tensor-core GEMM (fp16 operands, fp32 accumulate)
         DevBuf wt(gemm_w_tiles_bytes(rows, cols)), xt(gemm_x_tiles_bytes(n_tok, cols)), sk((size_t)32 << 20);
         launch_gemm_prepare_x(dx.as<float>(), cols, n_tok, cols, xt.p, 0);
         launch_gemm_tc(W, xt.p, n_tok, dout.as<float>(), rows, nullptr, 0, wt.p, false, sk.as<float>(), (size_t)32 << 20, 0);

@@ -110,7 +110,7 @@ inline int64_t gguf_row_bytes(int t, int64_t cols) { return cols / type_block_el
 // bytes of one row on the device (after repack)
 inline int64_t device_row_stride(int t, int64_t cols) { return align_up(gguf_row_bytes(t, cols), 16); }
 
-// formats without an integer decode kernel: tensor-core path (bf16 tiles) only
+// formats without an integer decode kernel: tensor-core path (fp16 tiles) only
 inline bool type_tiles_only(int t) {
     return t == B2_T_Q4_0 || t == B2_T_Q4_1 || t == B2_T_Q5_0 || t == B2_T_Q5_1 || t == B2_T_Q2_K || t == B2_T_Q3_K ||
            t == B2_T_IQ4_NL || t == B2_T_IQ4_XS;

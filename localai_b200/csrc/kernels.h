@@ -203,7 +203,7 @@ size_t mega_attention_ctx_limit(int hd, const MegaGeo &geo = MegaGeo());
 // --- tensor-core GEMM for prefill / batched decode (kernels_gemm.cu) ----------------------------------------------
 size_t gemm_w_tiles_bytes(int64_t rows, int64_t cols);
 size_t gemm_x_tiles_bytes(int n_tok, int64_t cols);
-// fp32 activations [n_tok][K] -> bf16 operand tiles (do once per activation, shared by several matrices)
+// fp32 activations [n_tok][K] -> fp16 operand tiles (do once per activation, shared by several matrices)
 void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
 // the same with the producer of the activations fused in: RMSNorm(x) * w (optionally also written as fp32 rows to
 // xn_out), silu(gate) * up
@@ -215,9 +215,9 @@ void launch_gemm_prepare_x_bias_residual_ln(float *x, const float *h, const floa
                                             int64_t K, float eps, void *x_tiles, cudaStream_t s);
 // gelu(x + bias): the BERT feed-forward activation (bert.cu)
 void launch_gemm_prepare_x_bias_gelu(const float *x, const float *bias, int n_tok, int64_t K, void *x_tiles, cudaStream_t s);
-// quantised W -> bf16 operand tiles (gemm_w_tiles_bytes of them)
+// quantised W -> fp16 operand tiles (gemm_w_tiles_bytes of them)
 void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s);
-// out[t][r] = W[r] . x[t] (+ residual): tcgen05/TMEM GEMM on bf16 operand tiles; W is dequantised into w_tiles first
+// out[t][r] = W[r] . x[t] (+ residual): tcgen05/TMEM GEMM on fp16 operand tiles; W is dequantised into w_tiles first
 // unless w_tiles_ready (the caller keeps W's tiles resident)
 // splitk_scratch (optional, fp32): with <= 128 tokens and fewer output tiles than SMs the K range is split over the
 // idle SMs; the slices' partial tiles go through this buffer and are summed in slice order

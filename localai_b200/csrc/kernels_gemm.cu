@@ -1,9 +1,9 @@
 // kernels_gemm.cu -- prefill / batched-decode mat-mul on the 5th-generation tensor cores (tcgen05 + TMEM).
 //
 // out[M tokens][N rows] = X[M][K] . W[N][K]^T, a real dense contraction once M is in the tens or more.
-//   1. dequant_tiles_kernel   quantised W (GGUF blocks in HBM) -> bf16, written straight into the UMMA "core matrix"
+//   1. dequant_tiles_kernel   quantised W (GGUF blocks in HBM) -> fp16, written straight into the UMMA "core matrix"
 //                             tile layout (below), so that a whole 256 x 64 operand tile is ONE contiguous 32 KB chunk
-//   2. convert_x_tiles_kernel fp32 activations -> bf16 in the same layout (128 x 64 tiles, rows zero-padded)
+//   2. convert_x_tiles_kernel fp32 activations -> fp16 in the same layout (128 x 64 tiles, rows zero-padded)
 //   3. gemm_tcgen05_kernel    persistent, warp-specialised: warp 0 = producer (one cp.async.bulk per operand tile,
 //                             mbarrier ring of 4 stages), warp 1 = MMA issuer (one elected lane issues
 //                             tcgen05.mma.cta_group::1.kind::f16, 128 x 256 x 16, fp32 accumulators in TMEM, two
@@ -14,8 +14,8 @@
 // descriptor therefore has LBO (K direction) = 128 B and SBO (row direction) = 1024 B, and one K = 16 MMA step
 // advances the start address by 256 B.  Because the tiles are laid out this way in global memory already, no TMA
 // tensor map is needed.
-// Tensor-bound: 2 M N K flops; roofline = MEASURED_PEAKS.json bf16 (1392 TF/s sustained).
-#include <cuda_bf16.h>
+// Tensor-bound: 2 M N K flops; roofline = MEASURED_PEAKS.json dense bf16 figure (1392 TF/s sustained; kind::f16 runs fp16 at the same rate).
+#include <cuda_fp16.h>
 
 #include "kernels.h"
 #include "quant.cuh"
@@ -30,6 +30,12 @@ constexpr int GM_STAGE_BYTES = GM_A_BYTES + GM_B_BYTES;
 constexpr int GM_THREADS = 256;
 constexpr size_t GM_SMEM = (size_t)GM_STAGES * GM_STAGE_BYTES + 1024;
 
+// fp32 pair -> fp16 pair, saturated (an inf would poison a whole accumulator row; llama.cpp's CUDA path makes the same
+// fp16 trade for these mat-muls)
+__device__ __forceinline__ __half2 gm_pack2(float a, float b) {
+    return __floats2half2_rn(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
+}
+
 __host__ __device__ inline int64_t tile_elem_offset(int r, int k) { // element offset inside a tile (rows x 64)
     return (int64_t)(r >> 3) * 512 + (k >> 3) * 64 + (r & 7) * 8 + (k & 7);
 }
@@ -37,7 +43,7 @@ __host__ __device__ inline int64_t tile_elem_offset(int r, int k) { // element o
 // ------------------------------------------------------------------------------------------------ operand preparation
 // one thread = 8 consecutive k of one row = one 16-byte core-matrix row
 __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, int64_t rows, int64_t cols, int64_t row_stride,
-                                     __nv_bfloat16 *__restrict__ out, int64_t rows_pad) {
+                                     __half *__restrict__ out, int64_t rows_pad) {
     const int64_t kc_per_row = cols / 8;
     const int64_t total = rows_pad * kc_per_row;
     const int64_t k_tiles = cols / GM_BK;
@@ -103,16 +109,16 @@ __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, in
             }
         }
         const int64_t nt = r / GM_BN, kt = k0 / GM_BK;
-        __nv_bfloat16 *dst = out + (nt * k_tiles + kt) * (int64_t)(GM_BN * GM_BK) + tile_elem_offset((int)(r % GM_BN), k0 % GM_BK);
-        __nv_bfloat162 p[4];
+        __half *dst = out + (nt * k_tiles + kt) * (int64_t)(GM_BN * GM_BK) + tile_elem_offset((int)(r % GM_BN), k0 % GM_BK);
+        __half2 p[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) p[j] = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+        for (int j = 0; j < 4; j++) p[j] = gm_pack2(v[2 * j], v[2 * j + 1]);
         *(int4 *)dst = *(const int4 *)p;
     }
 }
 
 __global__ void convert_x_tiles_kernel(const float *__restrict__ x, int64_t x_stride, int n_tok, int64_t cols,
-                                       __nv_bfloat16 *__restrict__ out, int64_t m_pad) {
+                                       __half *__restrict__ out, int64_t m_pad) {
     const int64_t kc_per_row = cols / 8;
     const int64_t total = m_pad * kc_per_row;
     const int64_t k_tiles = cols / GM_BK;
@@ -125,22 +131,22 @@ __global__ void convert_x_tiles_kernel(const float *__restrict__ x, int64_t x_st
             b = *(const float4 *)(x + r * x_stride + k0 + 4);
         }
         const int64_t mt = r / GM_BM, kt = k0 / GM_BK;
-        __nv_bfloat16 *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
-        __nv_bfloat162 p[4] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w), __floats2bfloat162_rn(b.x, b.y),
-                               __floats2bfloat162_rn(b.z, b.w)};
+        __half *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
+        __half2 p[4] = {gm_pack2(a.x, a.y), gm_pack2(a.z, a.w), gm_pack2(b.x, b.y),
+                               gm_pack2(b.z, b.w)};
         *(int4 *)dst = *(const int4 *)p;
     }
 }
 
-// RMSNorm (ggml arithmetic: double-precision sum, (x * scale) * w) fused with the bf16 tile conversion: one CTA per
+// RMSNorm (ggml arithmetic: double-precision sum, (x * scale) * w) fused with the fp16 tile conversion: one CTA per
 // token row; rows m >= n_tok of the last tile are zeroed by the CTAs of the same tile index range.
 __global__ void __launch_bounds__(256)
 rmsnorm_x_tiles_kernel(const float *__restrict__ x, int64_t x_stride, const float *__restrict__ w, int n_tok, int64_t cols, float eps,
-                       __nv_bfloat16 *__restrict__ out, float *__restrict__ xn_out) {
+                       __half *__restrict__ out, float *__restrict__ xn_out) {
     const int r = blockIdx.x; // < m_pad
     const int64_t k_tiles = cols / GM_BK;
     const int64_t mt = r / GM_BM;
-    __nv_bfloat16 *tile0 = out + mt * k_tiles * (int64_t)(GM_BM * GM_BK);
+    __half *tile0 = out + mt * k_tiles * (int64_t)(GM_BM * GM_BK);
     __shared__ double part[8];
     __shared__ float s_scale;
     float scale = 0.f;
@@ -177,23 +183,23 @@ rmsnorm_x_tiles_kernel(const float *__restrict__ x, int64_t x_stride, const floa
                 *(float4 *)(xn_out + (int64_t)r * cols + k0 + 4) = make_float4(v[4], v[5], v[6], v[7]);
             }
         }
-        __nv_bfloat16 *dst = tile0 + (k0 / GM_BK) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset(r % GM_BM, (int)(k0 % GM_BK));
-        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
-                                __floats2bfloat162_rn(v[6], v[7])};
+        __half *dst = tile0 + (k0 / GM_BK) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset(r % GM_BM, (int)(k0 % GM_BK));
+        __half2 p4[4] = {gm_pack2(v[0], v[1]), gm_pack2(v[2], v[3]), gm_pack2(v[4], v[5]),
+                                gm_pack2(v[6], v[7])};
         *(int4 *)dst = *(const int4 *)p4;
     }
 }
 
 // BERT: x = LayerNorm(x + h + bias) * w + b (ggml_norm: mean, variance of the centred values), the row written back as
-// fp32 (it is the next residual) AND as bf16 operand tiles of the next GEMM.  One CTA per token row, the row lives in
+// fp32 (it is the next residual) AND as fp16 operand tiles of the next GEMM.  One CTA per token row, the row lives in
 // registers (8 features per thread, cols <= 2048); rows >= n_tok of the last tile get zero tiles.
 __global__ void __launch_bounds__(256)
 bias_residual_ln_x_tiles_kernel(float *__restrict__ x, const float *__restrict__ h, const float *__restrict__ bias,
                                 const float *__restrict__ w, const float *__restrict__ b, int n_tok, int64_t cols, float eps,
-                                __nv_bfloat16 *__restrict__ out) {
+                                __half *__restrict__ out) {
     const int r = blockIdx.x; // < m_pad
     const int64_t k_tiles = cols / GM_BK;
-    __nv_bfloat16 *tile0 = out + (int64_t)(r / GM_BM) * k_tiles * (int64_t)(GM_BM * GM_BK);
+    __half *tile0 = out + (int64_t)(r / GM_BM) * k_tiles * (int64_t)(GM_BM * GM_BK);
     __shared__ float red[2][8];
     const int64_t k0 = (int64_t)threadIdx.x * 8;
     const bool mine = k0 < cols;
@@ -243,16 +249,16 @@ bias_residual_ln_x_tiles_kernel(float *__restrict__ x, const float *__restrict__
         }
     }
     if (mine) {
-        __nv_bfloat16 *dst = tile0 + (k0 / GM_BK) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset(r % GM_BM, (int)(k0 % GM_BK));
-        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
-                                __floats2bfloat162_rn(v[6], v[7])};
+        __half *dst = tile0 + (k0 / GM_BK) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset(r % GM_BM, (int)(k0 % GM_BK));
+        __half2 p4[4] = {gm_pack2(v[0], v[1]), gm_pack2(v[2], v[3]), gm_pack2(v[4], v[5]),
+                                gm_pack2(v[6], v[7])};
         *(int4 *)dst = *(const int4 *)p4;
     }
 }
 
-// silu(gate) * up (ggml arithmetic) fused with the bf16 tile conversion
+// silu(gate) * up (ggml arithmetic) fused with the fp16 tile conversion
 __global__ void swiglu_x_tiles_kernel(const float *__restrict__ g, const float *__restrict__ u, int n_tok, int64_t cols,
-                                      __nv_bfloat16 *__restrict__ out, int64_t m_pad) {
+                                      __half *__restrict__ out, int64_t m_pad) {
     const int64_t kc_per_row = cols / 8;
     const int64_t total = m_pad * kc_per_row;
     const int64_t k_tiles = cols / GM_BK;
@@ -268,16 +274,16 @@ __global__ void swiglu_x_tiles_kernel(const float *__restrict__ g, const float *
             for (int j = 0; j < 8; j++) v[j] = __fmul_rn(__fdiv_rn(gg[j], __fadd_rn(1.0f, expf(-gg[j]))), uu[j]);
         }
         const int64_t mt = r / GM_BM, kt = k0 / GM_BK;
-        __nv_bfloat16 *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
-        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
-                                __floats2bfloat162_rn(v[6], v[7])};
+        __half *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
+        __half2 p4[4] = {gm_pack2(v[0], v[1]), gm_pack2(v[2], v[3]), gm_pack2(v[4], v[5]),
+                                gm_pack2(v[6], v[7])};
         *(int4 *)dst = *(const int4 *)p4;
     }
 }
 
-// gelu(x + bias) (ggml_gelu's tanh form) fused with the bf16 tile conversion: the BERT feed-forward activation
+// gelu(x + bias) (ggml_gelu's tanh form) fused with the fp16 tile conversion: the BERT feed-forward activation
 __global__ void bias_gelu_x_tiles_kernel(const float *__restrict__ x, const float *__restrict__ bias, int n_tok, int64_t cols,
-                                         __nv_bfloat16 *__restrict__ out, int64_t m_pad) {
+                                         __half *__restrict__ out, int64_t m_pad) {
     const int64_t kc_per_row = cols / 8;
     const int64_t total = m_pad * kc_per_row;
     const int64_t k_tiles = cols / GM_BK;
@@ -293,9 +299,9 @@ __global__ void bias_gelu_x_tiles_kernel(const float *__restrict__ x, const floa
             for (int j = 0; j < 8; j++) v[j] = 0.5f * t[j] * (1.f + tanhf(0.7978845608028654f * t[j] * (1.f + 0.044715f * t[j] * t[j])));
         }
         const int64_t mt = r / GM_BM, kt = k0 / GM_BK;
-        __nv_bfloat16 *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
-        __nv_bfloat162 p4[4] = {__floats2bfloat162_rn(v[0], v[1]), __floats2bfloat162_rn(v[2], v[3]), __floats2bfloat162_rn(v[4], v[5]),
-                                __floats2bfloat162_rn(v[6], v[7])};
+        __half *dst = out + (mt * k_tiles + kt) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset((int)(r % GM_BM), k0 % GM_BK);
+        __half2 p4[4] = {gm_pack2(v[0], v[1]), gm_pack2(v[2], v[3]), gm_pack2(v[4], v[5]),
+                                gm_pack2(v[6], v[7])};
         *(int4 *)dst = *(const int4 *)p4;
     }
 }
@@ -370,14 +376,14 @@ __device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) 
 }
 
 struct GemmJobDev {             // one weight matrix of a launch: several matrices that share the activation
-    const __nv_bfloat16 *b_tiles; // [n_tiles][k_tiles][256 x 64]   (wq|wk|wv, gate|up) run as ONE launch
+    const __half *b_tiles; // [n_tiles][k_tiles][256 x 64]   (wq|wk|wv, gate|up) run as ONE launch
     float *out;
     int64_t out_stride;
     int N, n_tiles, nt0;          // nt0: first n-tile of this matrix in the launch's concatenated n-tile space
     int col0;                     // first column of this matrix in the split-K partial rows
 };
 struct GemmArgs {
-    const __nv_bfloat16 *a_tiles; // [m_tiles][k_tiles][128 x 64]
+    const __half *a_tiles; // [m_tiles][k_tiles][128 x 64]
     GemmJobDev job[3];
     int n_jobs;
     const float *residual;        // single-matrix launches only
@@ -437,8 +443,8 @@ gemm_tcgen05_kernel(const GemmArgs g) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
     const int n_tiles_total = g.m_tiles * g.n_tiles * g.ksplit; // work items
-    // kind::f16, D = f32, A = B = bf16, both K-major, N = 256, M = 128
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(GM_BN >> 3) << 17) | ((uint32_t)(GM_BM >> 4) << 24);
+    // kind::f16, D = f32 (bit 4), A = B = f16 (format 0), both K-major, N = 256, M = 128
+    const uint32_t idesc = (1u << 4) | ((uint32_t)(GM_BN >> 3) << 17) | ((uint32_t)(GM_BM >> 4) << 24);
 
     if (warp == 0) {
         { // ===== producer: one bulk copy per operand tile (the whole warp walks the schedule, an elected lane issues)
@@ -446,7 +452,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
             for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
                 const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
                 const int jb = (g.n_jobs > 2 && nt >= g.job[2].nt0) ? 2 : (g.n_jobs > 1 && nt >= g.job[1].nt0) ? 1 : 0;
-                const __nv_bfloat16 *bt = g.job[jb].b_tiles + (int64_t)(nt - g.job[jb].nt0) * g.k_tiles * (GM_BN * GM_BK);
+                const __half *bt = g.job[jb].b_tiles + (int64_t)(nt - g.job[jb].nt0) * g.k_tiles * (GM_BN * GM_BK);
                 const int kt0 = ks * g.k_per_split, kt1 = min(g.k_tiles, kt0 + g.k_per_split);
                 for (int kt = kt0; kt < kt1; kt++, it++) {
                     const int s = it % GM_STAGES;
@@ -537,7 +543,7 @@ void launch_gemm_prepare_x(const float *x, int64_t x_stride, int n_tok, int64_t 
     const int64_t m_pad = align_up(n_tok, GM_BM);
     const int64_t total = m_pad * (K / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
-    convert_x_tiles_kernel<<<blocks, 256, 0, s>>>(x, x_stride, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
+    convert_x_tiles_kernel<<<blocks, 256, 0, s>>>(x, x_stride, n_tok, K, (__half *)x_tiles, m_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -546,7 +552,7 @@ void launch_gemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const float
                                    float *xn_out, cudaStream_t s) {
     B2_CHECK(K % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
     const int m_pad = (int)align_up(n_tok, GM_BM);
-    rmsnorm_x_tiles_kernel<<<m_pad, 256, 0, s>>>(x, x_stride, w, n_tok, K, eps, (__nv_bfloat16 *)x_tiles, xn_out);
+    rmsnorm_x_tiles_kernel<<<m_pad, 256, 0, s>>>(x, x_stride, w, n_tok, K, eps, (__half *)x_tiles, xn_out);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -556,7 +562,7 @@ void launch_gemm_prepare_x_swiglu(const float *gate, const float *up, int n_tok,
     const int64_t m_pad = align_up(n_tok, GM_BM);
     const int64_t total = m_pad * (K / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
-    swiglu_x_tiles_kernel<<<blocks, 256, 0, s>>>(gate, up, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
+    swiglu_x_tiles_kernel<<<blocks, 256, 0, s>>>(gate, up, n_tok, K, (__half *)x_tiles, m_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -565,7 +571,7 @@ void launch_gemm_prepare_x_bias_residual_ln(float *x, const float *h, const floa
                                             int64_t K, float eps, void *x_tiles, cudaStream_t s) {
     B2_CHECK(K % GM_BK == 0 && K <= 2048, B2_EINVAL, "gemm: LayerNorm rows must be a multiple of 64 and at most 2048 wide");
     const int m_pad = (int)align_up(n_tok, GM_BM);
-    bias_residual_ln_x_tiles_kernel<<<m_pad, 256, 0, s>>>(x, h, bias, w, b, n_tok, K, eps, (__nv_bfloat16 *)x_tiles);
+    bias_residual_ln_x_tiles_kernel<<<m_pad, 256, 0, s>>>(x, h, bias, w, b, n_tok, K, eps, (__half *)x_tiles);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -575,7 +581,7 @@ void launch_gemm_prepare_x_bias_gelu(const float *x, const float *bias, int n_to
     const int64_t m_pad = align_up(n_tok, GM_BM);
     const int64_t total = m_pad * (K / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
-    bias_gelu_x_tiles_kernel<<<blocks, 256, 0, s>>>(x, bias, n_tok, K, (__nv_bfloat16 *)x_tiles, m_pad);
+    bias_gelu_x_tiles_kernel<<<blocks, 256, 0, s>>>(x, bias, n_tok, K, (__half *)x_tiles, m_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -585,7 +591,7 @@ void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s) {
     const int64_t rows_pad = align_up(W.rows, GM_BN);
     const int64_t total = rows_pad * (W.cols / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
-    dequant_tiles_kernel<<<blocks, 256, 0, s>>>(W.data, W.type, W.rows, W.cols, W.row_stride, (__nv_bfloat16 *)w_tiles, rows_pad);
+    dequant_tiles_kernel<<<blocks, 256, 0, s>>>(W.data, W.type, W.rows, W.cols, W.row_stride, (__half *)w_tiles, rows_pad);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -601,15 +607,15 @@ void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, 
     static const bool umma_swap = getenv("B200LLM_UMMA_SWAP") && atoi(getenv("B200LLM_UMMA_SWAP"));
     const uint32_t lbo = umma_swap ? 1024 : 128, sbo = umma_swap ? 128 : 1024;
     GemmArgs g;
-    g.a_tiles = (const __nv_bfloat16 *)x_tiles;
+    g.a_tiles = (const __half *)x_tiles;
     g.n_jobs = n_jobs;
     int nt = 0, col = 0;
     bool rows4 = true;
     for (int j = 0; j < n_jobs; j++) {
         const DTensor &W = *jobs[j].W;
         B2_CHECK(W.cols == cols, B2_EINVAL, "gemm: matrices of one launch share K");
-        if (!jobs[j].w_tiles_ready) launch_gemm_dequant_w(W, jobs[j].w_tiles, s); // quantised W -> bf16 tiles (unless kept resident)
-        g.job[j].b_tiles = (const __nv_bfloat16 *)jobs[j].w_tiles;
+        if (!jobs[j].w_tiles_ready) launch_gemm_dequant_w(W, jobs[j].w_tiles, s); // quantised W -> fp16 tiles (unless kept resident)
+        g.job[j].b_tiles = (const __half *)jobs[j].w_tiles;
         g.job[j].out = jobs[j].out; g.job[j].out_stride = jobs[j].out_stride;
         g.job[j].N = (int)W.rows; g.job[j].n_tiles = (int)(align_up(W.rows, GM_BN) / GM_BN);
         g.job[j].nt0 = nt; g.job[j].col0 = col;

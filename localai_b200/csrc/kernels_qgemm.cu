@@ -3,7 +3,7 @@
 // out[tok][row] = W[row] . x[tok] (+ residual) for W in GGUF block formats (Q4_K, Q5_K, Q6_K, Q8_0), x in fp16.
 // At 64 tokens the step is bound by streaming the weights once from HBM (ggml-cuda's mul_mat_q does the same job on
 // mma.sync; the reference calls it through llama.cpp's ggml_mul_mat, ggml/src/ggml-cuda/mmq.cu).  The round-1 path read
-// 3.3 x the bytes (bf16 shadow tiles); this kernel reads the 4.5-bit blocks and never writes a dequantised copy:
+// 3.3 x the bytes (fp16 shadow tiles); this kernel reads the 4.5-bit blocks and never writes a dequantised copy:
 //
 //   HBM --cp.async.bulk--> raw block ring (smem) --dequant warps--> fp16 A operand in TMEM --tcgen05.mma--> D in TMEM
 //                                                 x tiles (fp16) --cp.async.bulk--> smem B operand ----^
@@ -23,7 +23,7 @@
 //   lane quarter each),
 //   8..23 dequant (lane quarter = warp % 4; (warp - 8) / 4 = which 32 of the 128 k of an operand stage).
 // fp16 arithmetic of the dequantisation: q exact, d*sc and dmin*m rounded to fp16, one fused multiply-add -- about 3
-// fp16 roundings per weight (relative 2^-11 each), against 2^-9 of the bf16 tiles the large-batch path uses.
+// fp16 roundings per weight (relative 2^-11 each), (the large-batch path, kernels_gemm.cu, rounds the dequantised fp32 value once: 2^-11).
 // HBM-bound: algorithmic bytes = the quantised weights once; roofline = MEASURED_PEAKS.json hbm_gbs.
 #include <cuda_fp16.h>
 

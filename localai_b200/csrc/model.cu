@@ -38,7 +38,7 @@ DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_r
              "tensor " + name + ": slice outside the tensor or off the block boundaries");
     if (type_tiles_only(ti->type)) {
         B2_CHECK(cols % std::max(64, be) == 0, B2_EUNSUPPORTED, "tensor " + name + ": row length must be a multiple of 64 and of the block size");
-        tiles_only_ = true; // these formats have no integer decode kernel: everything goes through the bf16 tiles
+        tiles_only_ = true; // these formats have no integer decode kernel: everything goes through the fp16 tiles
     } else if (ti->type != B2_T_F32 && ti->type != B2_T_F16) {
         B2_CHECK(cols % 256 == 0, B2_EUNSUPPORTED, "tensor " + name + ": quantised row length must be a multiple of 256");
     }
@@ -447,11 +447,11 @@ void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
         }
 }
 
-// bf16 operand tiles of W for the tensor-core path.  180 GB of HBM is room to keep them resident (15 GB for an 8B
+// fp16 operand tiles of W for the tensor-core path.  180 GB of HBM is room to keep them resident (15 GB for an 8B
 // model) next to the quantised weights the decode kernels stream: prefill chunks and batched decode steps then skip
 // the dequantisation pass.  Built on first use (never inside a graph capture: run_decode_graphed warms up first);
 // when memory is short the tiles are rebuilt into a scratch buffer on every call instead.
-// Batches above this many tokens take the tensor-core path.  With the bf16 tiles resident it wins from 2 tokens on
+// Batches above this many tokens take the tensor-core path.  With the fp16 tiles resident it wins from 2 tokens on
 // (measured on Llama-3-8B: 4.3 ms per step for 2..16 streams against 5.4 / 6.9 / 8.5 ms of the integer kernels at 2 / 3 / 4);
 // when the tiles have to be rebuilt on every call the integer kernels keep the small batches.
 int Model::gemm_threshold() const {
@@ -489,7 +489,7 @@ void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const 
     launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, false, gemm_part_, gemm_part_bytes_, stream);
 }
 
-// Several matrices that share the activation tiles in ONE launch (wq|wk|wv, gate|up) when their bf16 tiles are
+// Several matrices that share the activation tiles in ONE launch (wq|wk|wv, gate|up) when their fp16 tiles are
 // resident; otherwise one launch each through the scratch tile buffer.
 void Model::gemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n) {
     if (!gemm_part_) {
@@ -510,7 +510,7 @@ void Model::gemm_multi(const DTensor *const *Ws, float *const *outs, const int64
     for (int j = 0; j < n_jobs; j++) gemm(*Ws[j], n, outs[j], strides[j], nullptr, 0);
 }
 
-// Prefill / batched decode: every mat-mul is a tcgen05 tensor-core GEMM on bf16 operands (weights dequantised into
+// Prefill / batched decode: every mat-mul is a tcgen05 tensor-core GEMM on fp16 operands (weights dequantised into
 // operand tiles on the fly); attention, norms and RoPE as in the other paths.
 void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     const int d = hp.n_embd, ff = hp.n_ff, hd = hp.head_dim, kvd = hp.n_head_kv * hd;

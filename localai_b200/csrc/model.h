@@ -130,7 +130,7 @@ class Model {
     void gemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n);
     void ensure_gemm_scratch(size_t w_bytes, size_t x_bytes);
     void *resident_tiles(const DTensor &W);
-    std::unordered_map<const uint8_t *, void *> w_tiles_; // resident bf16 operand tiles, keyed by the weight pointer
+    std::unordered_map<const uint8_t *, void *> w_tiles_; // resident fp16 operand tiles, keyed by the weight pointer
     bool no_shadow_ = false;
     size_t shadow_reserve_ = (size_t)6 << 30;            // leave this much HBM free
     void *gemm_w_ = nullptr, *gemm_x_ = nullptr;
@@ -147,7 +147,7 @@ class Model {
     unsigned *qg_counters_ = nullptr;
     bool slots_distinct_ = false; // the current batch has one token per slot (set by forward / forward_device_inputs)
     bool no_fused_att_ = false;   // B200LLM_NO_FUSED_ATT=1: RoPE / attention / tile conversion as three launches (A/B tests)
-    bool no_qgemm_ = false;   // B200LLM_NO_QGEMM=1: the bf16-tile path for every batch size (A/B tests)
+    bool no_qgemm_ = false;   // B200LLM_NO_QGEMM=1: the fp16-tile path for every batch size (A/B tests)
     void *resident_qtiles(const DTensor &W);
     bool qgemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n, const float *residual,
                      int64_t res_stride);

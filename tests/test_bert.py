@@ -4,8 +4,8 @@ CPU part: the WordPiece tokeniser through the C ABI vs the restatement in oracle
 GPU part: hidden states and embeddings vs the float32 numpy restatement, plus the behaviour the reference's own test
 pins (core/http/app_test.go:856-881: vector length, same input -> same vector).
 
-Tolerance: the mat-muls run on bf16 operand tiles with fp32 accumulation (weights are F16 in the file), everything else
-is fp32: after every layer the rows are re-normalised, so the bf16 rounding (2^-8 relative per operand) shows as an
+Tolerance: the mat-muls run on fp16 operand tiles with fp32 accumulation (the file's F16 weights exactly; activations
+rounded to fp16), everything else is fp32: after every layer the rows are re-normalised, so the operand rounding shows as an
 absolute error on unit-variance values: max <= 8 % of the standard deviation, median <= 1.2 %, cosine(embedding) >= 0.9995.
 The default attention kernel also rounds Q, K, P and V to bf16 for its MMAs (the usual flash-attention numerics); the
 scores are exponentiated, so its worst element may be off by up to 15 % of the standard deviation -- the median bound
@@ -90,8 +90,8 @@ def test_same_input_same_vector_and_batch_equals_single(bert_files):
         for s, row in zip(seqs, batch):
             single = b.embed_tokens(s)
             # same kernels, but the GEMM sees another row count, so its split-K slices and with them the fp32 summation
-            # order differ; a last-bit difference can flip the bf16 rounding of an activation before the next GEMM
-            # (2^-8 relative on that element), which is what remains: 1e-3 on unit vectors, cosine 1 - 1e-5
+            # order differ; a last-bit difference can flip the fp16 rounding of an activation before the next GEMM
+            # (2^-11 relative on that element), which is what remains: 1e-3 on unit vectors, cosine 1 - 1e-5
             assert np.abs(row - single).max() <= 1e-3 and float(row @ single) >= 1.0 - 1e-5
         with pytest.raises(RuntimeError, match="tokens"):
             b.embed_tokens(list(range(5)) * 200)  # 1000 tokens > context

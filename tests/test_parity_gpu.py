@@ -128,8 +128,9 @@ def test_fused_and_mega_kernels_match_oracle(wtype, rows, cols, n_tok, path):
     assert np.abs(got - ref).max() <= MATMUL_RTOL * np.abs(ref).max()
 
 
-# bf16 operands, fp32 accumulation: the error of one output is a sum of K products each off by <= 2^-8 relative
-GEMM_TC_RTOL = 1.5e-2
+# fp16 operands (one rounding of the dequantised fp32 weight and of the activation, 2^-11 relative each), fp32
+# accumulation: the errors of a row's K products add like a random walk.  (Round 1 used bf16 operands: 1.5e-2.)
+GEMM_TC_RTOL = 2e-3
 
 
 @pytest.mark.parametrize("wtype,rows,cols,n_tok", [
@@ -141,7 +142,7 @@ GEMM_TC_RTOL = 1.5e-2
     (capi.B2_T_Q4_0, 512, 1024, 1), (capi.B2_T_Q4_1, 300, 576, 9), (capi.B2_T_Q5_0, 1024, 4096, 64), (capi.B2_T_Q5_1, 256, 2048, 130),
     (capi.B2_T_Q2_K, 512, 1024, 3), (capi.B2_T_Q3_K, 300, 2048, 70), (capi.B2_T_IQ4_NL, 300, 576, 5), (capi.B2_T_IQ4_XS, 512, 2048, 40)])
 def test_gemm_tcgen05_matches_float_reference(wtype, rows, cols, n_tok):
-    """the tensor-core path (prefill, batched decode): tcgen05 GEMM on bf16 tiles vs dequantised weights in float64"""
+    """the tensor-core path (prefill, batched decode): tcgen05 GEMM on fp16 tiles vs dequantised weights in float64"""
     import make_gguf as mg
     rng = np.random.default_rng(rows + cols + n_tok)
     if wtype == capi.B2_T_F16:
@@ -214,7 +215,7 @@ def test_logits_match_oracle_prefill_and_decode(model_files, name):
         # embedding = final-norm hidden state of the last token
         _, embd = e.eval(toks[:8], want_embd=True)
         _, wembd = O.OracleModel(path, n_ctx=128).eval(toks[:8], want_embd=True)
-        assert_logits_close(embd[None], wembd[None], "embedding")  # 8 tokens: tensor-core (bf16 operand) prefill path
+        assert_logits_close(embd[None], wembd[None], "embedding")  # 8 tokens: tensor-core (fp16 operand) path
 
 
 def test_hidden_states_per_layer(model_files):
@@ -248,7 +249,7 @@ def test_greedy_64_tokens_identical(model_files, name):
 def test_greedy_long_context(model_files, n_prompt, monkeypatch):
     """decode at a context where the mega-kernel's attention runs several rounds per CTA (each of the 4 CTAs that share
     a head owns > 64 positions) -- greedy tokens identical to the oracle.  The prompt goes through the integer kernels
-    (B200LLM_GEMM_MIN_TOKENS) so that the KV cache holds the oracle's numerics, not the bf16 tensor-core path's."""
+    (B200LLM_GEMM_MIN_TOKENS) so that the KV cache holds the oracle's numerics, not the fp16 tensor-core path's."""
     monkeypatch.setenv("B200LLM_GEMM_MIN_TOKENS", "1000000")
     path = model_files["mini_q4_k_m"]
     ref = O.OracleModel(path, n_ctx=n_prompt + 40)
@@ -337,7 +338,7 @@ def test_tinyllama_q8_0_greedy_64_full_size(gguf_dir):
 def test_batched_decode_paths_agree(model_files, n_tok, monkeypatch):
     """A step of 2..64 tokens that all want logits (the shape of a decode step over many streams; the engine runs it as one
     step) through (a) the GEMM that dequantises inside the kernel (the default), (b) the same launched with programmatic
-    dependent launch, (c) the bf16-tile GEMM.  (a) and (b) are bit-identical --
+    dependent launch, (c) the fp16-tile GEMM.  (a) and (b) are bit-identical --
     the launch attribute changes scheduling, not arithmetic -- and stay so when the graph is replayed; all three hold the
     oracle's logits within the stated tolerance."""
     path = model_files["mini_q4_k_m"]
@@ -360,7 +361,7 @@ def test_batched_decode_paths_agree(model_files, n_tok, monkeypatch):
     assert np.array_equal(a, b)
     ref = O.OracleModel(path, n_ctx=128).eval(toks, logits_all=True)[8:]
     assert_logits_close(a, ref, "qgemm")
-    assert_logits_close(c, ref, "bf16 tiles")
+    assert_logits_close(c, ref, "fp16 tiles")
 
 
 @pytest.mark.parametrize("n_streams", [2, 7, 16, 33, 64])
@@ -370,7 +371,7 @@ def test_decode_step_over_many_slots(model_files, n_streams, monkeypatch):
     inside the kernel, the fused RoPE + KV-store + attention + tile-conversion kernel, ....  Its logits equal, bit for bit,
     those of the same step (a) replayed and (b) launched with programmatic dependent launch (the attribute changes
     scheduling, not arithmetic) and (c) run with RoPE / attention / conversion as three launches (the same arithmetic in
-    the same order); they hold the oracle's logits of each stream within the stated tolerance, as does (d) the bf16-tile
+    the same order); they hold the oracle's logits of each stream within the stated tolerance, as does (d) the fp16-tile
     GEMM path."""
     path = model_files["mini_q4_k_m"]
     rng = np.random.default_rng(100 + n_streams)
@@ -399,4 +400,4 @@ def test_decode_step_over_many_slots(model_files, n_streams, monkeypatch):
     d = run()
     ref = np.stack([O.OracleModel(path, n_ctx=64).eval(np.append(p, t))[0] for p, t in zip(prompts, toks)])
     assert_logits_close(a, ref, "default path")
-    assert_logits_close(d, ref, "bf16 tiles")
+    assert_logits_close(d, ref, "fp16 tiles")
