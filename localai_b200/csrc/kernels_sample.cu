@@ -507,6 +507,7 @@ void resample_row_masked(Model &m, int row, const SampleSpec &spec, const uint32
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
     SampleSpec *dev = m.sample_specs_dev(row + 1) + row;
+    m.sample_specs_held().clear(); // (the device copy of this row changes under sample_rows' cache)
     B2_CUDA(cudaMemcpyAsync(dev, &spec, sizeof(SampleSpec), cudaMemcpyHostToDevice, m.stream));
     int32_t *out = const_cast<int32_t *>(m.next_tok_dev()) + row;
     launch_sample(logits, n_vocab, 1, n_vocab, dev, false, out, m.sample_mu_dev() + row, m.stream, spec.temperature <= 0.f);
@@ -523,11 +524,28 @@ void sample_rows(Model &m, const std::vector<SampleSpec> &specs, int32_t *out_ho
         all_greedy &= sp.temperature <= 0.f;
     }
     SampleSpec *dev = m.sample_specs_dev(n);
-    B2_CUDA(cudaMemcpyAsync(dev, specs.data(), sizeof(SampleSpec) * n, cudaMemcpyHostToDevice, m.stream));
+    // A greedy step without penalties reads two fields of a row's spec (the banned token, the mirostat state it passes
+    // through): when those are what the device already holds, the 584-byte upload per row is skipped -- in a b = 1 greedy
+    // stream that is every step after the first.
+    bool any_miro = false;
+    for (const auto &sp : specs) any_miro |= sp.mirostat != 0;
+    std::vector<std::pair<int32_t, float>> &held = m.sample_specs_held();
+    bool same = all_greedy && !any_pen && !any_miro && (int)held.size() == n;
+    for (int i = 0; same && i < n; i++) same = held[i].first == specs[i].ban_token && held[i].second == specs[i].mirostat_mu;
+    if (!same) {
+        B2_CUDA(cudaMemcpyAsync(dev, specs.data(), sizeof(SampleSpec) * n, cudaMemcpyHostToDevice, m.stream));
+        held.clear();
+        if (all_greedy && !any_pen && !any_miro)
+            for (const auto &sp : specs) held.emplace_back(sp.ban_token, sp.mirostat_mu);
+    }
     launch_sample(m.logits_dev_mut(), m.hp.n_vocab, n, m.hp.n_vocab, dev, any_pen, const_cast<int32_t *>(m.next_tok_dev()),
                   m.sample_mu_dev(), m.stream, all_greedy);
     B2_CUDA(cudaMemcpyAsync(out_host, m.next_tok_dev(), sizeof(int32_t) * n, cudaMemcpyDeviceToHost, m.stream));
-    if (mu_out_host) B2_CUDA(cudaMemcpyAsync(mu_out_host, m.sample_mu_dev(), sizeof(float) * n, cudaMemcpyDeviceToHost, m.stream));
+    if (mu_out_host) {
+        if (any_miro) B2_CUDA(cudaMemcpyAsync(mu_out_host, m.sample_mu_dev(), sizeof(float) * n, cudaMemcpyDeviceToHost, m.stream));
+        else
+            for (int i = 0; i < n; i++) mu_out_host[i] = specs[i].mirostat_mu; // without mirostat the state passes through unchanged
+    }
 }
 
 } // namespace b2

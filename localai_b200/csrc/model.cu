@@ -255,9 +255,10 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     if (tp_size > 1) xp_ = (float *)dalloc(nb * d * 4);
     const int64_t kmax = std::max(d, ff_l);
     for (int fmt = ACT_F16; fmt <= ACT_Q8_K; fmt++) actq_[fmt] = (uint8_t *)dalloc(nb * (size_t)act_row_bytes((ActFmt)fmt, kmax));
-    tok_ = (int32_t *)dalloc(nb * 4);
-    pos_ = (int32_t *)dalloc(nb * 4);
-    slot_ = (int32_t *)dalloc(nb * 4);
+    tok_ = (int32_t *)dalloc(3 * nb * 4); // tokens | positions | slots, one allocation: a step's inputs go up in ONE copy
+    pos_ = tok_ + nb;
+    slot_ = pos_ + nb;
+    in_host_.resize(3 * nb);
     out_rows_ = (int32_t *)dalloc(nb * 4);
     next_tok_ = (int32_t *)dalloc(nb * 4);
     xn_out_ = (float *)dalloc(nb * d * 4);
@@ -892,9 +893,15 @@ void Model::forward(const Batch &b) {
         forward_tp(b);
         return;
     }
-    if (b.tokens) B2_CUDA(cudaMemcpyAsync(tok_, b.tokens, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
-    B2_CUDA(cudaMemcpyAsync(pos_, b.pos, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
-    B2_CUDA(cudaMemcpyAsync(slot_, b.slot, (size_t)b.n * 4, cudaMemcpyHostToDevice, stream));
+    { // one host->device copy for the step's inputs (three rows of n ints into the three device arrays, n_batch apart)
+        const size_t n = (size_t)b.n;
+        const int rows0 = b.tokens ? 0 : 1; // without tokens (embeddings fed on the device) only positions and slots go up
+        if (b.tokens) memcpy(in_host_.data(), b.tokens, n * 4);
+        memcpy(in_host_.data() + n, b.pos, n * 4);
+        memcpy(in_host_.data() + 2 * n, b.slot, n * 4);
+        B2_CUDA(cudaMemcpy2DAsync(tok_ + (size_t)rows0 * n_batch, (size_t)n_batch * 4, in_host_.data() + rows0 * n, n * 4, n * 4, 3 - rows0,
+                                  cudaMemcpyHostToDevice, stream));
+    }
     runs_.clear();
     for (int i = 0; i < b.n;) { // maximal runs of consecutive positions of one slot
         int j = i + 1;

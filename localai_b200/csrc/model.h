@@ -69,6 +69,7 @@ class Model {
     const int32_t *next_tok_dev() const { return next_tok_; }
     float *debug_hidden_dev() { return dbg_hidden_; }
     SampleSpec *sample_specs_dev(int n);
+    std::vector<std::pair<int32_t, float>> &sample_specs_held() { return sample_specs_held_; } // what sample_rows knows the device copy to hold
     uint32_t *token_mask_dev(); // (n_vocab + 31) / 32 words, allocated on first use (grammar resample)
     void enable_debug_hidden();
     int bench_gemv(int which, int n_tok, int n_rounds, double *ms_per_launch, int64_t *bytes_per_launch, int *ggml_type);
@@ -201,6 +202,8 @@ class Model {
     uint8_t *actq_[4] = {nullptr, nullptr, nullptr, nullptr}; // per ActFmt quantised activation rows
     bool actq_valid_[4] = {false, false, false, false};
     int32_t *tok_ = nullptr, *pos_ = nullptr, *slot_ = nullptr, *out_rows_ = nullptr, *next_tok_ = nullptr;
+    std::vector<std::pair<int32_t, float>> sample_specs_held_;
+    std::vector<int32_t> in_host_; // staging of a step's tokens | positions | slots (pageable: the copy returns once it is staged)
     int logits_rows_cap_ = 0;
     SampleSpec *sample_specs_ = nullptr;
     float *sample_mu_ = nullptr;
