@@ -223,6 +223,14 @@ void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s);
 // idle SMs; the slices' partial tiles go through this buffer and are summed in slice order
 void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,
                     int64_t res_stride, void *w_tiles, bool w_tiles_ready, float *splitk_scratch, size_t splitk_bytes, cudaStream_t s);
+// GEMMs whose epilogue applies the activation and writes the next GEMM's operand tiles directly:
+//   SwiGLU over an interleaved ffn_gate | ffn_up tile set (launch_gemm_dequant_w_pair; ff a multiple of 128),
+//   gelu(W x + bias) (the BERT feed-forward; N a multiple of 256)
+size_t gemm_w_pair_tiles_bytes(int64_t rows, int64_t cols);
+void launch_gemm_dequant_w_pair(const DTensor &gate, const DTensor &up, void *w_tiles, cudaStream_t s);
+void launch_gemm_tc_swiglu(int64_t ff, int64_t cols, const void *pair_tiles, const void *x_tiles, int n_tok, void *x2_tiles, cudaStream_t s);
+void launch_gemm_tc_bias_gelu(int64_t N, int64_t cols, const void *w_tiles, const void *x_tiles, int n_tok, const float *bias, void *x2_tiles,
+                              cudaStream_t s);
 // up to three matrices that share the activation (wq|wk|wv, gate|up) in ONE launch; residual only with one matrix
 struct GemmJob {
     const DTensor *W;

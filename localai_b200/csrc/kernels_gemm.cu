@@ -42,8 +42,11 @@ __host__ __device__ inline int64_t tile_elem_offset(int r, int k) { // element o
 
 // ------------------------------------------------------------------------------------------------ operand preparation
 // one thread = 8 consecutive k of one row = one 16-byte core-matrix row
+// half >= 0: the matrix is one half of an interleaved pair (ffn_gate | ffn_up): its rows [128 j, 128 j + 128) become rows
+// [128 half, 128 half + 128) of the pair's 256-row tile j, so that one accumulator tile holds gate and up of the same 128
+// features and the GEMM epilogue can apply SwiGLU itself (rows_pad is then a multiple of 128).
 __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, int64_t rows, int64_t cols, int64_t row_stride,
-                                     __half *__restrict__ out, int64_t rows_pad) {
+                                     __half *__restrict__ out, int64_t rows_pad, int half) {
     const int64_t kc_per_row = cols / 8;
     const int64_t total = rows_pad * kc_per_row;
     const int64_t k_tiles = cols / GM_BK;
@@ -108,8 +111,9 @@ __global__ void dequant_tiles_kernel(const uint8_t *__restrict__ W, int type, in
                 }
             }
         }
-        const int64_t nt = r / GM_BN, kt = k0 / GM_BK;
-        __half *dst = out + (nt * k_tiles + kt) * (int64_t)(GM_BN * GM_BK) + tile_elem_offset((int)(r % GM_BN), k0 % GM_BK);
+        const int64_t nt = half < 0 ? r / GM_BN : r / 128, kt = k0 / GM_BK;
+        const int rt = half < 0 ? (int)(r % GM_BN) : (int)(r % 128) + 128 * half;
+        __half *dst = out + (nt * k_tiles + kt) * (int64_t)(GM_BN * GM_BK) + tile_elem_offset(rt, k0 % GM_BK);
         __half2 p[4];
 #pragma unroll
         for (int j = 0; j < 4; j++) p[j] = gm_pack2(v[2 * j], v[2 * j + 1]);
@@ -388,6 +392,12 @@ struct GemmArgs {
     int n_jobs;
     const float *residual;        // single-matrix launches only
     int64_t res_stride;
+    // epilogue that feeds the next GEMM: instead of fp32 rows, write fp16 operand tiles [m_tiles][K2 / 64][128 x 64] of
+    // 1: silu(gate) * up over an interleaved gate|up matrix (columns c and c + 128 of a tile; K2 = N_total / 2),
+    // 2: gelu(acc + bias[col]) (BERT feed-forward; K2 = N).  ksplit == 1 only.
+    int epi_tiles;
+    __half *x2_tiles;
+    const float *bias;
     int M, N_total, k_tiles, m_tiles, n_tiles; // n_tiles: over all matrices
     uint32_t lbo, sbo;
     // split-K for small M (batched decode): with one m-tile and few n-tiles most SMs would have no work item, and the
@@ -501,6 +511,42 @@ gemm_tcgen05_kernel(const GemmArgs g) {
             gm_mbar_wait(tfull + acc, (acc_it >> 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const int row = mt * GM_BM + q * 32 + lane;
+            if (g.epi_tiles) { // activation fused, output = the next GEMM's operand tiles (every row of the tile is written: padding rows are zeros in, zeros out)
+                const int ncol = g.epi_tiles == 1 ? GM_BN / 2 : GM_BN;
+                const int64_t k2_tiles = (g.epi_tiles == 1 ? g.N_total / 2 : g.N_total) / GM_BK;
+                for (int c0 = 0; c0 < ncol; c0 += 32) {
+                    uint32_t r[32];
+                    float v[32];
+                    gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
+                    const int64_t k2 = (int64_t)nt * ncol + c0; // feature index of v[0] in the next GEMM's K
+                    if (g.epi_tiles == 1) {
+                        uint32_t u[32];
+                        gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + 128 + c0, u);
+#pragma unroll
+                        for (int j = 0; j < 32; j++) { // ggml's silu(gate) * up
+                            const float gt = __uint_as_float(r[j]);
+                            v[j] = __fmul_rn(__fdiv_rn(gt, __fadd_rn(1.0f, expf(-gt))), __uint_as_float(u[j]));
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; j++) { // ggml_gelu's tanh form on acc + bias
+                            const float t = __uint_as_float(r[j]) + g.bias[k2 + j];
+                            v[j] = 0.5f * t * (1.f + tanhf(0.7978845608028654f * t * (1.f + 0.044715f * t * t)));
+                        }
+                    }
+                    if (k2 < (int64_t)k2_tiles * GM_BK) {
+                        __half *dst = g.x2_tiles + ((int64_t)mt * k2_tiles + k2 / GM_BK) * (int64_t)(GM_BM * GM_BK) +
+                                      tile_elem_offset(q * 32 + lane, (int)(k2 % GM_BK));
+#pragma unroll
+                        for (int j8 = 0; j8 < 4; j8++) { // 8 features = one 16-byte core-matrix row; consecutive groups are 64 halves apart
+                            __half2 pk[4];
+#pragma unroll
+                            for (int j = 0; j < 4; j++) pk[j] = gm_pack2(v[8 * j8 + 2 * j], v[8 * j8 + 2 * j + 1]);
+                            *(int4 *)(dst + j8 * 64) = *(const int4 *)pk;
+                        }
+                    }
+                }
+            } else
             for (int c0 = 0; c0 < GM_BN; c0 += 32) {
                 uint32_t r[32];
                 gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
@@ -591,7 +637,7 @@ void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s) {
     const int64_t rows_pad = align_up(W.rows, GM_BN);
     const int64_t total = rows_pad * (W.cols / 8);
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
-    dequant_tiles_kernel<<<blocks, 256, 0, s>>>(W.data, W.type, W.rows, W.cols, W.row_stride, (__half *)w_tiles, rows_pad);
+    dequant_tiles_kernel<<<blocks, 256, 0, s>>>(W.data, W.type, W.rows, W.cols, W.row_stride, (__half *)w_tiles, rows_pad, -1);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }
@@ -623,6 +669,7 @@ void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, 
         rows4 = rows4 && W.rows % 4 == 0;
     }
     g.residual = residual; g.res_stride = res_stride;
+    g.epi_tiles = 0; g.x2_tiles = nullptr; g.bias = nullptr;
     g.M = n_tok; g.N_total = col; g.k_tiles = (int)(cols / GM_BK);
     g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = nt;
     g.lbo = lbo; g.sbo = sbo;
@@ -651,6 +698,53 @@ void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, 
             B2_CUDA(cudaGetLastError());
         }
     }
+}
+
+// ---- GEMMs whose epilogue applies the activation and writes the NEXT GEMM's operand tiles (no fp32 round trip through HBM)
+size_t gemm_w_pair_tiles_bytes(int64_t rows, int64_t cols) { return (size_t)align_up(rows, 128) * 2 * cols * 2; }
+
+void launch_gemm_dequant_w_pair(const DTensor &gate, const DTensor &up, void *w_tiles, cudaStream_t s) {
+    B2_CHECK(gate.rows == up.rows && gate.cols == up.cols && gate.cols % GM_BK == 0, B2_EINVAL, "gemm: gate / up shapes differ");
+    const int64_t rows_pad = align_up(gate.rows, 128);
+    const int64_t total = rows_pad * (gate.cols / 8);
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
+    dequant_tiles_kernel<<<blocks, 256, 0, s>>>(gate.data, gate.type, gate.rows, gate.cols, gate.row_stride, (__half *)w_tiles, rows_pad, 0);
+    dequant_tiles_kernel<<<blocks, 256, 0, s>>>(up.data, up.type, up.rows, up.cols, up.row_stride, (__half *)w_tiles, rows_pad, 1);
+    g_launch_count += 2;
+    B2_CUDA(cudaGetLastError());
+}
+
+static void launch_gemm_fused_epilogue(int epi, const void *w_tiles, int64_t N, int64_t cols, const void *x_tiles, int n_tok, const float *bias,
+                                       void *x2_tiles, cudaStream_t s) {
+    B2_CHECK(cols % GM_BK == 0 && N % GM_BN == 0, B2_EINVAL, "gemm: fused epilogue needs whole 256-column tiles");
+    static PerDeviceOnce configured;
+    configured.run([&] { B2_CUDA(cudaFuncSetAttribute(gemm_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GM_SMEM)); });
+    GemmArgs g;
+    memset(&g, 0, sizeof(g));
+    g.a_tiles = (const __half *)x_tiles;
+    g.n_jobs = 1;
+    g.job[0].b_tiles = (const __half *)w_tiles;
+    g.job[0].N = (int)N; g.job[0].n_tiles = (int)(N / GM_BN); g.job[0].nt0 = 0; g.job[0].col0 = 0;
+    g.M = n_tok; g.N_total = (int)N; g.k_tiles = (int)(cols / GM_BK);
+    g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = g.job[0].n_tiles;
+    g.lbo = 128; g.sbo = 1024;
+    g.ksplit = 1; g.k_per_split = g.k_tiles;
+    g.epi_tiles = epi; g.x2_tiles = (__half *)x2_tiles; g.bias = bias;
+    const int tiles = g.m_tiles * g.n_tiles;
+    gemm_tcgen05_kernel<<<std::min(tiles, 148), GM_THREADS, GM_SMEM, s>>>(g);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+// x2 tiles [n_tok][ff] = silu(W_gate x) * (W_up x); pair_tiles from launch_gemm_dequant_w_pair (ff a multiple of 128)
+void launch_gemm_tc_swiglu(int64_t ff, int64_t cols, const void *pair_tiles, const void *x_tiles, int n_tok, void *x2_tiles, cudaStream_t s) {
+    B2_CHECK(ff % 128 == 0, B2_EINVAL, "gemm: fused SwiGLU needs ffn_gate rows in whole 128-row tiles");
+    launch_gemm_fused_epilogue(1, pair_tiles, 2 * ff, cols, x_tiles, n_tok, nullptr, x2_tiles, s);
+}
+// x2 tiles [n_tok][N] = gelu(W x + bias)  (N a multiple of 256)
+void launch_gemm_tc_bias_gelu(int64_t N, int64_t cols, const void *w_tiles, const void *x_tiles, int n_tok, const float *bias, void *x2_tiles,
+                              cudaStream_t s) {
+    launch_gemm_fused_epilogue(2, w_tiles, N, cols, x_tiles, n_tok, bias, x2_tiles, s);
 }
 
 void launch_gemm_tc(const DTensor &W, const void *x_tiles, int n_tok, float *out, int64_t out_stride, const float *residual,

@@ -88,6 +88,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     no_gemm_ = getenv("B200LLM_NO_GEMM") && atoi(getenv("B200LLM_NO_GEMM")) != 0;
     no_qgemm_ = getenv("B200LLM_NO_QGEMM") && atoi(getenv("B200LLM_NO_QGEMM")) != 0;
     no_fused_att_ = getenv("B200LLM_NO_FUSED_ATT") && atoi(getenv("B200LLM_NO_FUSED_ATT")) != 0;
+    no_fused_swiglu_ = getenv("B200LLM_NO_FUSED_SWIGLU") && atoi(getenv("B200LLM_NO_FUSED_SWIGLU")) != 0;
     no_shadow_ = getenv("B200LLM_NO_BF16_TILES") && atoi(getenv("B200LLM_NO_BF16_TILES")) != 0;
     if (getenv("B200LLM_GEMM_MIN_TOKENS")) gemm_min_tokens_ = atoi(getenv("B200LLM_GEMM_MIN_TOKENS"));
     else gemm_min_tokens_ = -1; // automatic, see gemm_threshold()
@@ -291,6 +292,8 @@ Model::~Model() {
     if (logits_) cudaFree(logits_);
     for (auto &kv : w_tiles_) cudaFree(kv.second);
     for (auto &kv : q_tiles_) cudaFree(kv.second);
+    for (auto &kv : pair_tiles_) cudaFree(kv.second);
+    if (gemm_x2_) cudaFree(gemm_x2_);
     if (gemm_w_) cudaFree(gemm_w_);
     if (gemm_x_) cudaFree(gemm_x_);
     if (staging_) cudaFree(staging_);
@@ -421,13 +424,23 @@ void Model::run_layer_fused(const LayerW &L, const KVLayout &kv, int n) {
     launch_fused_gemv(w, n, stream);
 }
 
-void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes) {
+void Model::ensure_gemm_scratch(size_t w_bytes, size_t x_bytes, size_t x2_bytes) {
     bool realloc = false;
+    if (x2_bytes > gemm_x2_bytes_) {
+        B2_CUDA(cudaStreamSynchronize(stream));
+        if (gemm_x2_) cudaFree(gemm_x2_);
+        gemm_x2_ = nullptr;
+        B2_CUDA(cudaMalloc(&gemm_x2_, x2_bytes));
+        gemm_x2_bytes_ = x2_bytes;
+        realloc = true;
+    }
     if (w_bytes > gemm_w_bytes_) {
         realloc = true;
         B2_CUDA(cudaStreamSynchronize(stream));
         for (auto &kv : w_tiles_) cudaFree(kv.second); // memory is short (no_shadow_): give the resident tiles back too
         w_tiles_.clear();
+        for (auto &kv : pair_tiles_) cudaFree(kv.second);
+        pair_tiles_.clear();
         if (gemm_w_) cudaFree(gemm_w_);
         gemm_w_ = nullptr;
         B2_CUDA(cudaMalloc(&gemm_w_, w_bytes));
@@ -477,17 +490,37 @@ void *Model::resident_tiles(const DTensor &W) {
     return p;
 }
 
-void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride) {
+// interleaved ffn_gate | ffn_up operand tiles (the GEMM over them applies SwiGLU in its epilogue), resident like the others
+void *Model::resident_pair_tiles(const LayerW &L) {
+    if (no_shadow_ || no_fused_swiglu_ || L.gate.rows % 128 != 0 || L.gate.rows != L.up.rows || L.gate.cols != L.up.cols) return nullptr;
+    auto it = pair_tiles_.find(L.gate.data);
+    if (it != pair_tiles_.end()) return it->second;
+    if (w_tiles_.count(L.gate.data)) return nullptr; // the separate tiles of this layer exist already: keep using them
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(stream, &cs);
+    if (cs != cudaStreamCaptureStatusNone) return nullptr;
+    const size_t bytes = gemm_w_pair_tiles_bytes(L.gate.rows, L.gate.cols);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess || free_b < bytes + shadow_reserve_) return nullptr;
+    void *p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    launch_gemm_dequant_w_pair(L.gate, L.up, p, stream);
+    pair_tiles_[L.gate.data] = p;
+    return p;
+}
+
+void Model::gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride, const void *x_tiles) {
+    if (!x_tiles) x_tiles = gemm_x_;
     if (!gemm_part_) { // split-K partial tiles for batched decode (<= 128 tokens): 148 slices x 128 tokens x 256 rows at most
         gemm_part_bytes_ = (size_t)32 << 20;
         gemm_part_ = (float *)dalloc(gemm_part_bytes_);
     }
     if (void *t = resident_tiles(W)) {
-        launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, t, true, gemm_part_, gemm_part_bytes_, stream);
+        launch_gemm_tc(W, x_tiles, n, out, out_stride, residual, res_stride, t, true, gemm_part_, gemm_part_bytes_, stream);
         return;
     }
     ensure_gemm_scratch(gemm_w_tiles_bytes(W.rows, W.cols), 0);
-    launch_gemm_tc(W, gemm_x_, n, out, out_stride, residual, res_stride, gemm_w_, false, gemm_part_, gemm_part_bytes_, stream);
+    launch_gemm_tc(W, x_tiles, n, out, out_stride, residual, res_stride, gemm_w_, false, gemm_part_, gemm_part_bytes_, stream);
 }
 
 // Several matrices that share the activation tiles in ONE launch (wq|wk|wv, gate|up) when their fp16 tiles are
@@ -528,6 +561,12 @@ void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
     gemm(L.wo, n, x_, d, x_, d);
     launch_gemm_prepare_x_rmsnorm(x_, d, (const float *)L.ffn_norm.data, n, d, hp.rms_eps, gemm_x_, nullptr, stream);
+    if (void *pt = resident_pair_tiles(L)) { // gate | up interleaved: SwiGLU in the GEMM's epilogue, which writes ffn_down's operand tiles
+        ensure_gemm_scratch(0, 0, gemm_x_tiles_bytes(n, ff));
+        launch_gemm_tc_swiglu(ff, d, pt, gemm_x_, n, gemm_x2_, stream);
+        gemm(L.down, n, x_, d, x_, d, gemm_x2_);
+        return;
+    }
     {
         const DTensor *Ws[2] = {&L.gate, &L.up};
         float *outs[2] = {gate_, up_};

@@ -127,9 +127,14 @@ class Model {
     std::vector<Run> runs_; // host view of the current batch (empty: inputs only on the device)
     void attention(const KVLayout &kv, int n);
     void run_layer_gemm(const LayerW &L, const KVLayout &kv, int n);
-    void gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride);
+    void gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride, const void *x_tiles = nullptr);
+    void *resident_pair_tiles(const LayerW &L);
+    std::unordered_map<const uint8_t *, void *> pair_tiles_; // interleaved ffn_gate | ffn_up operand tiles, keyed by the gate pointer
+    void *gemm_x2_ = nullptr;                                // operand tiles written by a GEMM epilogue (SwiGLU output -> ffn_down)
+    size_t gemm_x2_bytes_ = 0;
+    bool no_fused_swiglu_ = false;                           // B200LLM_NO_FUSED_SWIGLU=1 (A/B tests)
     void gemm_multi(const DTensor *const *Ws, float *const *outs, const int64_t *strides, int n_jobs, int n);
-    void ensure_gemm_scratch(size_t w_bytes, size_t x_bytes);
+    void ensure_gemm_scratch(size_t w_bytes, size_t x_bytes, size_t x2_bytes = 0);
     void *resident_tiles(const DTensor &W);
     std::unordered_map<const uint8_t *, void *> w_tiles_; // resident fp16 operand tiles, keyed by the weight pointer
     bool no_shadow_ = false;
