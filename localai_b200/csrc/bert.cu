@@ -212,6 +212,7 @@ BertModel::BertModel(const std::string &path, int device, bool vocab_only) : tok
     u_ = (float *)dalloc(T * ff * 4);
     out_ = (float *)dalloc(T * d * 4);
     x_tiles_ = dalloc(gemm_x_tiles_bytes((int)T, std::max(d, ff)));
+    x2_tiles_ = dalloc(gemm_x_tiles_bytes((int)T, ff)); // written by the feed-forward GEMM's epilogue (gelu(u + b) as operand tiles)
     splitk_bytes_ = (size_t)32 << 20;
     splitk_ = (float *)dalloc(splitk_bytes_);
     B2_CUDA(cudaStreamSynchronize(stream_));
@@ -311,6 +312,9 @@ void BertModel::run_kernels(int T, int n_seq, int max_len) {
             launch_gemm_prepare_x(x_, d, T, d, x_tiles_, s);
         }
     };
+    // the fused epilogue runs without split-K: only where the feed-forward GEMM has enough output tiles for the SMs anyway
+    const bool fused_gelu = ff % 256 == 0 && (int64_t)((T + 127) / 128) * (ff / 256) > 74 &&
+                            !(getenv("B200LLM_BERT_UNFUSED_GELU") && atoi(getenv("B200LLM_BERT_UNFUSED_GELU")) != 0);
     launch_gemm_prepare_x(x_, d, T, d, x_tiles_, s);
     for (const BertLayer &L : layers_) { // on entry x_tiles_ holds x_
         const GemmJob qkv[3] = {{&L.wq, L.tq, true, q_, d}, {&L.wk, L.tk, true, k_, d}, {&L.wv, L.tv, true, v_, d}};
@@ -319,9 +323,14 @@ void BertModel::run_kernels(int T, int n_seq, int max_len) {
         launch_gemm_prepare_x(att_, d, T, d, x_tiles_, s);
         launch_gemm_tc(L.wo, x_tiles_, T, h_, d, nullptr, 0, L.to, true, splitk_, splitk_bytes_, s);
         ln(L.bo, L.ln1_w, L.ln1_b);
-        launch_gemm_tc(L.up, x_tiles_, T, u_, ff, nullptr, 0, L.tup, true, splitk_, splitk_bytes_, s);
-        launch_gemm_prepare_x_bias_gelu(u_, L.bup, T, ff, x_tiles_, s); // gelu(u + b) straight into the operand tiles
-        launch_gemm_tc(L.down, x_tiles_, T, h_, d, nullptr, 0, L.tdown, true, splitk_, splitk_bytes_, s);
+        if (fused_gelu) { // bias + GELU in the GEMM's epilogue, which writes the down projection's operand tiles
+            launch_gemm_tc_bias_gelu(ff, d, L.tup, x_tiles_, T, L.bup, x2_tiles_, s);
+            launch_gemm_tc(L.down, x2_tiles_, T, h_, d, nullptr, 0, L.tdown, true, splitk_, splitk_bytes_, s);
+        } else {
+            launch_gemm_tc(L.up, x_tiles_, T, u_, ff, nullptr, 0, L.tup, true, splitk_, splitk_bytes_, s);
+            launch_gemm_prepare_x_bias_gelu(u_, L.bup, T, ff, x_tiles_, s); // gelu(u + b) straight into the operand tiles
+            launch_gemm_tc(L.down, x_tiles_, T, h_, d, nullptr, 0, L.tdown, true, splitk_, splitk_bytes_, s);
+        }
         ln(L.bdown, L.ln2_w, L.ln2_b);
     }
 }

@@ -82,7 +82,7 @@ class BertModel {
     // scratch for MAX_TOKENS tokens
     int32_t *ids_dev_ = nullptr, *pos_dev_ = nullptr, *seq_dev_ = nullptr, *offs_dev_ = nullptr;
     float *x_ = nullptr, *q_ = nullptr, *k_ = nullptr, *v_ = nullptr, *att_ = nullptr, *h_ = nullptr, *u_ = nullptr, *out_ = nullptr;
-    void *x_tiles_ = nullptr;
+    void *x_tiles_ = nullptr, *x2_tiles_ = nullptr;
     float *splitk_ = nullptr;
     size_t splitk_bytes_ = 0;
 };
