@@ -401,3 +401,24 @@ def test_decode_step_over_many_slots(model_files, n_streams, monkeypatch):
     ref = np.stack([O.OracleModel(path, n_ctx=64).eval(np.append(p, t))[0] for p, t in zip(prompts, toks)])
     assert_logits_close(a, ref, "default path")
     assert_logits_close(d, ref, "fp16 tiles")
+
+
+@pytest.mark.parametrize("name", ["mini_q4_k_m", "mini_f16", "micro_mixed"])
+def test_prefill_fused_swiglu_epilogue(model_files, name, monkeypatch):
+    """Prompt chunks above 64 tokens run the tcgen05 GEMM on fp16 tiles; ffn_gate | ffn_up are one interleaved tile set and
+    the GEMM's epilogue applies SwiGLU and writes ffn_down's operand tiles.  Same logits as with the separate SwiGLU kernel
+    (the activation is computed from the same fp32 accumulators, rounded to fp16 once either way: bit-identical) and within
+    the stated tolerance of the oracle."""
+    path = model_files[name]
+    toks = np.random.default_rng(5).integers(0, 4000, 150).astype(np.int32)
+
+    def run():
+        with capi.Engine(path, n_ctx=256, n_batch=128) as e:
+            return e.eval(toks, logits_all=True)  # chunks of 128 + 22 tokens
+
+    a = run()
+    monkeypatch.setenv("B200LLM_NO_FUSED_SWIGLU", "1")
+    b = run()
+    assert np.array_equal(a[:128], b[:128])
+    ref = O.OracleModel(path, n_ctx=256).eval(toks, logits_all=True)
+    assert_logits_close(a, ref, "fused SwiGLU epilogue")
