@@ -406,9 +406,9 @@ def test_decode_step_over_many_slots(model_files, n_streams, monkeypatch):
 @pytest.mark.parametrize("name", ["mini_q4_k_m", "mini_f16", "micro_mixed"])
 def test_prefill_fused_swiglu_epilogue(model_files, name, monkeypatch):
     """Prompt chunks above 64 tokens run the tcgen05 GEMM on fp16 tiles; ffn_gate | ffn_up are one interleaved tile set and
-    the GEMM's epilogue applies SwiGLU and writes ffn_down's operand tiles.  Same logits as with the separate SwiGLU kernel
-    (the activation is computed from the same fp32 accumulators, rounded to fp16 once either way: bit-identical) and within
-    the stated tolerance of the oracle."""
+    the GEMM's epilogue applies SwiGLU and writes ffn_down's operand tiles.  Against the separate SwiGLU kernel only the fp32
+    summation order differs (at 128 tokens the unfused gate / up GEMM splits K over the idle SMs, the fused one does not):
+    the logits agree to a few 1e-3 sigma; both hold the oracle's within the stated tolerance."""
     path = model_files[name]
     toks = np.random.default_rng(5).integers(0, 4000, 150).astype(np.int32)
 
@@ -419,6 +419,7 @@ def test_prefill_fused_swiglu_epilogue(model_files, name, monkeypatch):
     a = run()
     monkeypatch.setenv("B200LLM_NO_FUSED_SWIGLU", "1")
     b = run()
-    assert np.array_equal(a[:128], b[:128])
     ref = O.OracleModel(path, n_ctx=256).eval(toks, logits_all=True)
+    assert np.abs(a - b).max() <= 0.02 * ref.std()
     assert_logits_close(a, ref, "fused SwiGLU epilogue")
+    assert_logits_close(b, ref, "separate SwiGLU kernel")
