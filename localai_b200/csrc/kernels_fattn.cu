@@ -13,7 +13,7 @@
 
 namespace b2 {
 
-constexpr int FA_BQ = 64, FA_BK = 64, FA_THREADS = 128;
+constexpr int FA_BK = 64; // keys per tile; a CTA has BQ queries (64 or 128), 16 per warp
 
 __device__ __forceinline__ void fa_cp16(void *smem, const void *gmem) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
@@ -31,11 +31,12 @@ __device__ __forceinline__ uint32_t fa_pack(float lo, float hi) {
 }
 
 // q: [n_tok][n_head*HD] fp32 (rotated); tokens [t0, t0 + n_q) belong to `slot`, token t0 + i sits at position pos0 + i
-template <int HD>
-__global__ void __launch_bounds__(FA_THREADS)
+template <int HD, int FA_BQ>
+__global__ void __launch_bounds__(FA_BQ * 2)
 fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, KVLayout kv,
                      float *__restrict__ out, float scale) {
     constexpr int LD = HD + 8; // padded row (halves): conflict-free fragment loads
+    constexpr int FA_THREADS = FA_BQ * 2;
     extern __shared__ __align__(16) __half fsm[];
     __half *sK = fsm;                       // [2][FA_BK][LD]
     __half *sV = fsm + 2 * FA_BK * LD;      // [2][FA_BK][LD]
@@ -87,6 +88,7 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
         if (it + 1 < n_tiles) { load_tile(buf ^ 1, j0 + FA_BK); fa_wait<1>(); } else { fa_wait<0>(); }
         __syncthreads();
         const __half *K = sK + (size_t)buf * FA_BK * LD, *V = sV + (size_t)buf * FA_BK * LD;
+        if (j0 <= pos0 + q_lo + warp * 16 + 15) { // (a tile wholly after this warp's last query is masked out: nothing to add)
         // ---- S = Q K^T : 8 n-tiles of 8 keys
         float s[FA_BK / 8][4];
 #pragma unroll
@@ -146,6 +148,7 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
                 fa_mma(o[dt], pa[kc], b0, b1);
             }
         }
+        }
         __syncthreads(); // the other buffer is refilled at the top of the next iteration
     }
     // ---- normalise and write: rows r0 / r1, dims dt*8 + tq*2 (+1)
@@ -172,14 +175,23 @@ void launch_fattn_prefill(const float *q, int t0, int n_q, int pos0, int slot, i
                           const KVLayout &kv, float *out, cudaStream_t s) {
     if (n_q <= 0) return;
     const float scale = 1.0f / sqrtf((float)hd);
-    const dim3 grid((n_q + FA_BQ - 1) / FA_BQ, n_head);
+    // 64 queries per CTA; 128 (8 warps: half the K / V tile traffic and barriers per query) measured slower on a 2048-token
+    // prefill of Llama-3-8B (34.4 against 33.7 ms), kept behind B200LLM_FATTN_BQ=128
+    static const int bq_env = getenv("B200LLM_FATTN_BQ") ? atoi(getenv("B200LLM_FATTN_BQ")) : 0;
+    const int bq = bq_env == 128 ? 128 : 64;
+    const dim3 grid((n_q + bq - 1) / bq, n_head);
     const size_t smem = (size_t)4 * FA_BK * (hd + 8) * sizeof(__half);
     if (hd == 128) {
         static PerDeviceOnce cfg;
-        cfg.run([&] { B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); });
-        fattn_prefill_kernel<128><<<grid, FA_THREADS, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+        cfg.run([&] {
+            B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        });
+        if (bq == 128) fattn_prefill_kernel<128, 128><<<grid, 256, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+        else fattn_prefill_kernel<128, 64><<<grid, 128, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
     } else if (hd == 64) {
-        fattn_prefill_kernel<64><<<grid, FA_THREADS, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+        if (bq == 128) fattn_prefill_kernel<64, 128><<<grid, 256, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+        else fattn_prefill_kernel<64, 64><<<grid, 128, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
     } else {
         throw Error(B2_EUNSUPPORTED, "flash prefill attention: head_dim must be 64 or 128");
     }
