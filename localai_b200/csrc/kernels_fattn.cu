@@ -13,6 +13,9 @@
 
 namespace b2 {
 
+#ifndef FA_MINB
+#define FA_MINB 2 // CTAs per SM the 64-query variant is compiled for (171 registers; 3 = 168 registers measured the same, 4 = 128 registers spills: 40.6 against 33.7 ms per 2048-token prefill)
+#endif
 constexpr int FA_BK = 64; // keys per tile; a CTA has BQ queries (64 or 128), 16 per warp
 
 __device__ __forceinline__ void fa_cp16(void *smem, const void *gmem) {
@@ -32,7 +35,7 @@ __device__ __forceinline__ uint32_t fa_pack(float lo, float hi) {
 
 // q: [n_tok][n_head*HD] fp32 (rotated); tokens [t0, t0 + n_q) belong to `slot`, token t0 + i sits at position pos0 + i
 template <int HD, int FA_BQ>
-__global__ void __launch_bounds__(FA_BQ * 2)
+__global__ void __launch_bounds__(FA_BQ * 2, FA_BQ == 64 ? FA_MINB : 1)
 fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, KVLayout kv,
                      float *__restrict__ out, float scale) {
     constexpr int LD = HD + 8; // padded row (halves): conflict-free fragment loads
