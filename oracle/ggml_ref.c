@@ -13,10 +13,13 @@
  *   llama_decode            grpc-server.cpp:1910        -> ref_eval()
  *   gpt_sampler_sample      grpc-server.cpp:1946 (temp<=0 greedy) -> ref_argmax()
  *   llama_get_embeddings    grpc-server.cpp:1313        -> ref_eval(..., embd_out)
- * Dequantisation is PINNED bit-exactly against gguf-py 0.19.0 (llama.cpp's own Python package) through
- * tests/golden/dequant_*.npz; the forward pass has no upstream golden vectors (SURVEY.md §8c:
- * "parity unpinned") and is cross-checked against an independent float32 numpy model in
- * tests/test_oracle.py.
+ * PINNED: dequantisation of 13 formats and Q8_0 quantisation bit-exactly against gguf-py 0.19.0 (llama.cpp's own
+ * Python package; tests/golden/dequant_*.npz); the forward pass (RoPE pairing, GQA, norm placement, SwiGLU, head)
+ * against HuggingFace transformers' LlamaForCausalLM loaded from the same GGUF (tools/crosscheck_transformers.py,
+ * tests/golden/transformers_crosscheck.json, tests/test_oracle.py::test_oracle_matches_transformers) -- the
+ * reference's own tests hold no logits or token-id vectors for this path.
+ * NOT PINNED ("parity unpinned" for these paths only): the scaled RoPE variants (linear, YaRN, rope_freqs.weight),
+ * restated from ggml's published algorithm and checked against closed forms only (ref_rope_cache_ext below).
  *
  * Build: see oracle/Makefile (gcc -O3 -fopenmp -ffp-contract=off).  Contraction is disabled so
  * that `d*q - m` is two roundings, as in gguf-py.
