@@ -200,7 +200,7 @@ static bool try_launch_attention_decode_fused(float *q, const float *k, const fl
     // 4 CTAs per SM where the registers allow (G <= 4): a 64-stream step of 8 KV heads is 512 CTAs = one wave of 148 x 4.
     // Measured on Llama-3-8B, 64 streams: 4.61 ms per step against 4.76 at 3 CTAs/SM; 8 V rows in flight per warp and
     // scores by lane groups (coalesced K rows) were slower (4.70 / 4.93 ms: registers, hence fewer resident CTAs).
-    constexpr int MINB = G <= 4 ? 4 : 3;
+    constexpr int MINB = G <= 4 ? 4 : 2; // (G = 8 at 80 registers spills 364 B)
     static PerDeviceOnce configured;
     configured.run([&] { B2_CUDA(cudaFuncSetAttribute(attention_decode_fused_kernel<G, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); });
     launch_pdl(attention_decode_fused_kernel<G, MINB>, dim3(n_head_kv, n_tok), dim3(ATT_THREADS), smem, s, q, k, v, pos, slot, n_head, n_head_kv, hd,

@@ -47,6 +47,7 @@ def model_files(gguf_dir):
         "micro_linear": ("micro-linear", "mixed"),
         "micro_yarn": ("micro-yarn", "mixed"),
         "micro_l31": ("micro-l31", "mixed"),
+        "micro_g8": ("micro-g8", "q4_k_m"),  # 8 query heads per KV head
     }
     out = {}
     for name, (arch, preset) in specs.items():

@@ -193,7 +193,8 @@ def test_mul_mat_linearity_in_rows():
 
 
 MODELS = ["micro_mixed", "micro_q8_0", "mini_q4_k_m", "mini_q5_k", "mini_f16", "mini_q4_0", "mini_q5_1", "mini_q2_k", "mini_q3_k", "mini_iq4_nl", "mini_iq4_xs",
-          "micro_linear", "micro_yarn", "micro_l31"]  # the last three: RoPE scaling (linear, YaRN, rope_freqs.weight divisors)
+          "micro_linear", "micro_yarn", "micro_l31",  # RoPE scaling (linear, YaRN, rope_freqs.weight divisors)
+          "micro_g8"]                                 # 8 query heads per KV head
 
 
 @pytest.mark.parametrize("name", MODELS)
@@ -364,8 +365,9 @@ def test_batched_decode_paths_agree(model_files, n_tok, monkeypatch):
     assert_logits_close(c, ref, "fp16 tiles")
 
 
-@pytest.mark.parametrize("n_streams", [2, 7, 16, 33, 64])
-def test_decode_step_over_many_slots(model_files, n_streams, monkeypatch):
+@pytest.mark.parametrize("n_streams,model", [(2, "mini_q4_k_m"), (7, "mini_q4_k_m"), (16, "mini_q4_k_m"), (33, "mini_q4_k_m"), (64, "mini_q4_k_m"),
+                                             (5, "micro_g8"), (40, "micro_g8")])
+def test_decode_step_over_many_slots(model_files, n_streams, model, monkeypatch):
     """ONE decode step over n_streams slots with prompts of different lengths (b2_eval_step: the batch shape the scheduler
     issues for concurrent streams).  The default path is a CUDA graph of: RMSNorm -> fp16 tiles, the GEMM that dequantises
     inside the kernel, the fused RoPE + KV-store + attention + tile-conversion kernel, ....  Its logits equal, bit for bit,
@@ -373,7 +375,7 @@ def test_decode_step_over_many_slots(model_files, n_streams, monkeypatch):
     scheduling, not arithmetic) and (c) run with RoPE / attention / conversion as three launches (the same arithmetic in
     the same order); they hold the oracle's logits of each stream within the stated tolerance, as does (d) the fp16-tile
     GEMM path."""
-    path = model_files["mini_q4_k_m"]
+    path = model_files[model]
     rng = np.random.default_rng(100 + n_streams)
     prompts = [rng.integers(0, 4000, 5 + (3 * i) % 17).astype(np.int32) for i in range(n_streams)]
     toks = np.array([int(rng.integers(0, 4000)) for _ in prompts], np.int32)

@@ -80,6 +80,7 @@ ARCHS = {
     "micro-linear": Arch("micro-linear", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "linear", 4.0, 128),
     "micro-yarn": Arch("micro-yarn", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "yarn", 4.0, 128),
     "micro-l31": Arch("micro-l31", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "none", 1.0, 0, True),
+    "micro-g8": Arch("micro-g8", 2, 512, 8, 1, 1024, 4352, 512, 10000.0, 1e-5, "spm"),  # 8 query heads per KV head (the 70B grouping), head_dim 64
     "mini-70b": Arch("mini-70b", 4, 2048, 16, 8, 4096, 8192, 1024, 500000.0, 1e-5, "bpe", True),  # 70B type mix (Q5_K attn_v), 8 KV heads; shards 2 / 4 / 8 ways
     # BASELINE.json configs
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 5632, 32000, 2048, 10000.0, 1e-5, "spm"),
