@@ -75,6 +75,20 @@ func (l *LLM) Load(opts *pb.ModelOptions) error {
 	}
 	o.rope_freq_base = C.float(opts.RopeFreqBase)
 	o.rope_freq_scale = C.float(opts.RopeFreqScale)
+	// RopeScaling as the reference reads it (grpc-server.cpp:2279-2281): "none", "yarn", anything else (the empty
+	// default included) = linear with the scale the GGUF was trained with
+	switch opts.RopeScaling {
+	case "none":
+		o.rope_scaling = C.B2_ROPE_NONE
+	case "yarn":
+		o.rope_scaling = C.B2_ROPE_YARN
+	default:
+		o.rope_scaling = C.B2_ROPE_LINEAR
+	}
+	o.yarn_ext_factor = C.float(opts.YarnExtFactor)
+	o.yarn_attn_factor = C.float(opts.YarnAttnFactor)
+	o.yarn_beta_fast = C.float(opts.YarnBetaFast)
+	o.yarn_beta_slow = C.float(opts.YarnBetaSlow)
 
 	// which devices: MainGPU set => that one; else every sm_100 device, capped by B200_REPLICAS
 	devices := []int{}

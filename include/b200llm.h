@@ -72,8 +72,15 @@ typedef struct {
     int32_t tp_size;        /* tensor-parallel degree (ModelOptions.TensorSplit names that many GPUs; backend.proto:175-176,
                                grpc-server.cpp:2240-2262): 0 / 1 = one GPU; 2, 4, 8 = the model is sharded over the devices
                                device .. device + tp_size - 1 of this process (70B-class models) */
-    int32_t reserved[6];
+    int32_t rope_scaling;   /* ModelOptions.RopeScaling (grpc-server.cpp:2279-2281): 0 = as the GGUF says, B2_ROPE_NONE / _LINEAR / _YARN
+                               override it (the reference maps "none" / "yarn" / anything else to none / YaRN / linear) */
+    float yarn_ext_factor;  /* YarnExtFactor, YarnAttnFactor, YarnBetaFast, YarnBetaSlow (grpc-server.cpp:2282-2293): 0 = llama.cpp's */
+    float yarn_attn_factor; /* defaults (ext_factor 1 for YaRN else 0, attn_factor 1, beta_fast 32, beta_slow 1) */
+    float yarn_beta_fast;
+    float yarn_beta_slow;
+    int32_t reserved[1];
 } b2_load_opts;
+enum { B2_ROPE_FROM_GGUF = 0, B2_ROPE_NONE = 1, B2_ROPE_LINEAR = 2, B2_ROPE_YARN = 3 };
 
 b2_engine *b2_create(const b2_load_opts *opts);
 void b2_destroy(b2_engine *e);

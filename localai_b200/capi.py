@@ -20,6 +20,7 @@ B2_T_Q4_0, B2_T_Q4_1, B2_T_Q5_0, B2_T_Q5_1, B2_T_Q2_K, B2_T_Q3_K = 2, 3, 6, 7, 1
 B2_T_IQ4_NL, B2_T_IQ4_XS = 20, 23  # likewise
 B2_ETIMEOUT = -8
 B2_TP_NCCL, B2_TP_FUSED = 0, 1
+B2_ROPE_FROM_GGUF, B2_ROPE_NONE, B2_ROPE_LINEAR, B2_ROPE_YARN = 0, 1, 2, 3
 B2_EUNSUPPORTED = -9
 EV_FINAL, EV_STOP_EOS, EV_STOP_WORD, EV_STOP_LIMIT, EV_ERROR, EV_EMBEDDING = 1, 2, 4, 8, 16, 32
 
@@ -44,7 +45,8 @@ class LoadOpts(C.Structure):
         ("struct_size", C.c_uint32), ("model_path", C.c_char_p), ("n_ctx", C.c_int32), ("n_batch", C.c_int32),
         ("n_parallel", C.c_int32), ("device", C.c_int32), ("embeddings", C.c_int32), ("rope_freq_base", C.c_float),
         ("rope_freq_scale", C.c_float), ("kv_page_size", C.c_int32), ("vocab_only", C.c_int32),
-        ("tp_size", C.c_int32), ("reserved", C.c_int32 * 6),
+        ("tp_size", C.c_int32), ("rope_scaling", C.c_int32), ("yarn_ext_factor", C.c_float), ("yarn_attn_factor", C.c_float),
+        ("yarn_beta_fast", C.c_float), ("yarn_beta_slow", C.c_float), ("reserved", C.c_int32 * 1),
     ]
 
 
@@ -260,8 +262,11 @@ class Engine:
 
     def __init__(self, model_path: str, n_ctx: int = 1024, n_batch: int = 512, n_parallel: int = 1, device: int = 0,
                  embeddings: bool = False, rope_freq_base: float = 0.0, rope_freq_scale: float = 0.0,
-                 kv_page_size: int = 0, vocab_only: bool = False, tp_size: int = 0):
+                 kv_page_size: int = 0, vocab_only: bool = False, tp_size: int = 0, rope_scaling: str | int = 0,
+                 yarn_ext_factor: float = 0.0, yarn_attn_factor: float = 0.0, yarn_beta_fast: float = 0.0, yarn_beta_slow: float = 0.0):
         o = LoadOpts()
+        o.rope_scaling = {"": 0, "none": B2_ROPE_NONE, "linear": B2_ROPE_LINEAR, "yarn": B2_ROPE_YARN}.get(rope_scaling, rope_scaling)
+        o.yarn_ext_factor, o.yarn_attn_factor, o.yarn_beta_fast, o.yarn_beta_slow = yarn_ext_factor, yarn_attn_factor, yarn_beta_fast, yarn_beta_slow
         o.struct_size = C.sizeof(LoadOpts)
         o.model_path = os.fsencode(model_path)
         o.n_ctx, o.n_batch, o.n_parallel, o.device = n_ctx, n_batch, n_parallel, device

@@ -115,11 +115,20 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     // YaRN scale the frequencies by 1 / rope.scaling.factor, YaRN additionally blends towards the unscaled frequencies
     // (ext_factor 1) inside its correction range; rope_freqs.weight holds per-dimension divisors (the Llama-3.1 scheme)
     {
-        const std::string st = f.get_s(a + "rope.scaling.type", "none");
+        std::string st = f.get_s(a + "rope.scaling.type", "none");
         const float factor = (float)f.get_f(a + "rope.scaling.factor", 1.0);
         B2_CHECK(st == "none" || st == "linear" || st == "yarn", B2_EUNSUPPORTED, "gguf: unknown rope.scaling.type");
-        if ((st == "linear" || st == "yarn") && factor > 0) hp.rope_scale = 1.0f / factor;
-        hp.rope_ext_factor = st == "yarn" ? 1.0f : 0.0f;
+        B2_CHECK(o.rope_scaling >= B2_ROPE_FROM_GGUF && o.rope_scaling <= B2_ROPE_YARN, B2_EINVAL, "rope_scaling: 0 .. 3");
+        if (o.rope_scaling == B2_ROPE_NONE) st = "none"; // ModelOptions.RopeScaling overrides the file's type (grpc-server.cpp:2279-2281)
+        else if (o.rope_scaling == B2_ROPE_LINEAR) st = "linear";
+        else if (o.rope_scaling == B2_ROPE_YARN) st = "yarn";
+        // the trained scale 1 / factor applies whatever the type (llama.cpp: rope_freq_scale_train is read unconditionally)
+        if (factor > 0) hp.rope_scale = 1.0f / factor;
+        if (st == "none") hp.rope_scale = 1.0f; // LLAMA_ROPE_SCALING_TYPE_NONE: never scale contexts
+        hp.rope_ext_factor = o.yarn_ext_factor != 0.f ? o.yarn_ext_factor : (st == "yarn" ? 1.0f : 0.0f);
+        hp.rope_attn_factor = o.yarn_attn_factor != 0.f ? o.yarn_attn_factor : 1.0f;
+        hp.rope_beta_fast = o.yarn_beta_fast != 0.f ? o.yarn_beta_fast : 32.0f;
+        hp.rope_beta_slow = o.yarn_beta_slow != 0.f ? o.yarn_beta_slow : 1.0f;
         hp.rope_n_ctx_orig = (int)f.get_u(a + "rope.scaling.original_context_length", hp.n_ctx_train);
     }
     if (o.rope_freq_base > 0) hp.rope_base = o.rope_freq_base;
@@ -215,14 +224,14 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
         float corr[2] = {0.f, 0.f};
         if (hp.rope_ext_factor != 0.0f) {
             auto corr_dim = [&](float n_rot) { return hd * logf(hp.rope_n_ctx_orig / (n_rot * 2 * (float)M_PI)) / (2 * logf(hp.rope_base)); };
-            corr[0] = std::max(0.f, floorf(corr_dim(32.0f)));
-            corr[1] = std::min((float)hd - 1, ceilf(corr_dim(1.0f)));
+            corr[0] = std::max(0.f, floorf(corr_dim(hp.rope_beta_fast)));
+            corr[1] = std::min((float)hd - 1, ceilf(corr_dim(hp.rope_beta_slow)));
         }
         for (int p = 0; p < n_ctx_slot; p++) {
             float theta = (float)p;
             for (int i0 = 0; i0 < hd; i0 += 2) {
-                float t, mscale = 1.0f;
-                if (!ff && hp.rope_ext_factor == 0.0f) {
+                float t, mscale = hp.rope_attn_factor;
+                if (!ff && hp.rope_ext_factor == 0.0f && hp.rope_attn_factor == 1.0f) {
                     t = hp.rope_scale * theta; // the unscaled / linear path keeps its exact arithmetic
                 } else {
                     const float extrap = theta / (ff ? ff[i0 / 2] : 1.0f), interp = hp.rope_scale * extrap;

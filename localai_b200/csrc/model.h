@@ -19,6 +19,7 @@ struct HParams {
     int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_ctx_train = 0;
     float rms_eps = 1e-5f, rope_base = 10000.f, rope_scale = 1.f;
     float rope_ext_factor = 0.f; // 1 for YaRN (llama.rope.scaling.type)
+    float rope_attn_factor = 1.f, rope_beta_fast = 32.f, rope_beta_slow = 1.f; // llama.cpp's defaults, b2_load_opts overrides
     int rope_n_ctx_orig = 0;     // llama.rope.scaling.original_context_length
     std::string arch, name;
 };

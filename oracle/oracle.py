@@ -120,7 +120,9 @@ def rope_cache(pos: int, freq_scale: float, freq_base: float, n_dims: int) -> np
 class OracleModel:
     """llama-arch GGUF evaluated by the C restatement (grpc-server.cpp:1910 llama_decode call site)."""
 
-    def __init__(self, path: str, n_ctx: int = 512):
+    def __init__(self, path: str, n_ctx: int = 512, rope_scaling: str | None = None, yarn_ext_factor: float = 0.0,
+                 yarn_attn_factor: float = 0.0, yarn_beta_fast: float = 0.0, yarn_beta_slow: float = 0.0):
+        """rope_scaling / yarn_*: the overrides ModelOptions carries (grpc-server.cpp:2279-2293); None / 0 = what the GGUF says"""
         import gguf  # llama.cpp's own reader
 
         self.reader = gguf.GGUFReader(path)  # keeps the mmap alive
@@ -153,20 +155,21 @@ class OracleModel:
             fld = f[key]
             return bytes(fld.parts[fld.data[0]]).decode()
 
-        stype = string("llama.rope.scaling.type", "none")
+        stype = rope_scaling or string("llama.rope.scaling.type", "none")
         factor = float(scalar("llama.rope.scaling.factor", 1.0))
         self.rope_freq_scale = 1.0 / factor if stype in ("linear", "yarn") and factor > 0 else 1.0
-        self.rope_ext_factor = 1.0 if stype == "yarn" else 0.0
+        self.rope_ext_factor = yarn_ext_factor or (1.0 if stype == "yarn" else 0.0)
+        overridden = bool(rope_scaling or yarn_ext_factor or yarn_attn_factor or yarn_beta_fast or yarn_beta_slow)
         n_ctx_orig = int(scalar("llama.rope.scaling.original_context_length", scalar("llama.context_length", 2048)))
         ff = None
         if "rope_freqs.weight" in self.tensors:
             ff = np.ascontiguousarray(np.array(self.tensors["rope_freqs.weight"].data, dtype=np.float32))
             self._keep.append(ff)
-        if stype != "none" or ff is not None:
+        if stype != "none" or ff is not None or overridden:
             L.ref_ctx_set_rope_scaling.argtypes = [C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int,
                                                    C.c_float, C.c_float, C.c_void_p]
-            L.ref_ctx_set_rope_scaling(self.ctx, self.rope_freq_scale, self.rope_ext_factor, 1.0, n_ctx_orig, 32.0, 1.0,
-                                       ff.ctypes.data if ff is not None else None)
+            L.ref_ctx_set_rope_scaling(self.ctx, self.rope_freq_scale, self.rope_ext_factor, yarn_attn_factor or 1.0, n_ctx_orig,
+                                       yarn_beta_fast or 32.0, yarn_beta_slow or 1.0, ff.ctypes.data if ff is not None else None)
         for name, t in self.tensors.items():
             base = name.rsplit(".weight", 1)[0]
             data = np.ascontiguousarray(t.data).view(np.uint8).reshape(-1)

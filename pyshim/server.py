@@ -74,7 +74,11 @@ class Backend:
             dev = int(req.MainGPU) if req.MainGPU.strip().isdigit() else 0
             eng = capi.Engine(req.ModelFile or req.Model, n_ctx=req.ContextSize or 1024, n_batch=req.NBatch or 512,
                               n_parallel=max(1, n_par), device=dev, embeddings=req.Embeddings, vocab_only=req.VocabOnly,
-                              rope_freq_base=req.RopeFreqBase, rope_freq_scale=req.RopeFreqScale)
+                              rope_freq_base=req.RopeFreqBase, rope_freq_scale=req.RopeFreqScale,
+                              # grpc-server.cpp:2279-2293: "none" / "yarn" / anything else (the empty default too) = linear
+                              rope_scaling=req.RopeScaling if req.RopeScaling in ("none", "yarn") else "linear",
+                              yarn_ext_factor=req.YarnExtFactor, yarn_attn_factor=req.YarnAttnFactor,
+                              yarn_beta_fast=req.YarnBetaFast, yarn_beta_slow=req.YarnBetaSlow)
         except Exception as ex:  # pkg/grpc/server.go:50-53: Result{success:false} AND a gRPC error
             ctx.set_code(grpc.StatusCode.UNKNOWN)
             ctx.set_details(f"Error loading model: {ex}")

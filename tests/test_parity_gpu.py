@@ -425,3 +425,23 @@ def test_prefill_fused_swiglu_epilogue(model_files, name, monkeypatch):
     assert np.abs(a - b).max() <= 0.02 * ref.std()
     assert_logits_close(a, ref, "fused SwiGLU epilogue")
     assert_logits_close(b, ref, "separate SwiGLU kernel")
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("micro_yarn", dict(rope_scaling="linear")),   # what the reference does with an empty ModelOptions.RopeScaling on a YaRN file
+    ("micro_yarn", dict(rope_scaling="none")),
+    ("micro_linear", dict(rope_scaling="yarn")),
+    ("micro_yarn", dict(yarn_ext_factor=0.5, yarn_attn_factor=1.25, yarn_beta_fast=16.0, yarn_beta_slow=2.0)),
+])
+def test_rope_scaling_overrides_of_model_options(model_files, name, kw):
+    """ModelOptions.RopeScaling / Yarn* override what the GGUF says (grpc-server.cpp:2279-2293): the engine with
+    b2_load_opts.rope_scaling / yarn_* holds the logits of the oracle configured the same way, and they differ from the
+    file's own configuration."""
+    path = model_files[name]
+    toks = np.arange(7, 47, dtype=np.int32)
+    ref = O.OracleModel(path, n_ctx=64, **kw).eval(toks, logits_all=True)
+    plain = O.OracleModel(path, n_ctx=64).eval(toks, logits_all=True)
+    assert np.abs(ref[8:] - plain[8:]).max() > 1e-3
+    with capi.Engine(path, n_ctx=64, n_batch=16, **kw) as e:
+        got = e.eval(toks, logits_all=True)
+    assert_logits_close(got, ref, f"{name} {kw}")
