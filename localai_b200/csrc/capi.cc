@@ -6,6 +6,7 @@
 #include <mutex>
 #include <vector>
 
+#include "stream_text.h"
 #include "bert.h"
 #include "engine.h"
 #include "grammar.h"
@@ -237,6 +238,43 @@ int b2_tp_info(b2_engine *e, b2_tp_info_t *out) {
 int b2_mega_debug(b2_engine *e, long long *out, int cap) {
     B2_API_BEGIN
     return E(e)->mega_debug(out, cap);
+    B2_API_END(0)
+}
+
+// undocumented test hooks (not part of the ABI header; need no device): the request path's text and prompt rules
+// (stream_text.h) driven piece by piece.  b2_stream_text: pieces = the tokens' bytes back to back with their lengths; returns
+// the bytes a streaming client would have received in `streamed`, the final text in `final_text`, *n_used = pieces consumed
+// (generation stops at a stop word).  Return value: 1 if a stop word ended it, 0 if not, negative on error.
+extern "C" int b2_stream_text(const char *pieces, const int *lens, int n, const char *const *stops, int n_stops, char *streamed, int cap_s,
+                              char *final_text, int cap_f, int *n_used) {
+    B2_API_BEGIN
+    std::vector<std::string> sw;
+    for (int i = 0; i < n_stops; i++) sw.emplace_back(stops[i]);
+    StreamText t;
+    t.reset(&sw);
+    std::string out;
+    int used = 0, stopped = 0;
+    size_t off = 0;
+    for (int i = 0; i < n && !stopped; i++, used++) {
+        StreamText::Step st = t.append(std::string(pieces + off, (size_t)lens[i]));
+        off += (size_t)lens[i];
+        out += st.release;
+        stopped = st.stop_word ? 1 : 0;
+    }
+    B2_CHECK((int)out.size() < cap_s && (int)t.text().size() < cap_f, B2_ENOSPC, "b2_stream_text: buffers too small");
+    memcpy(streamed, out.c_str(), out.size() + 1);
+    memcpy(final_text, t.text().c_str(), t.text().size() + 1);
+    if (n_used) *n_used = used;
+    return stopped;
+    B2_API_END(0)
+}
+// b2_fit_prompt: the truncation rule on a token list in place; returns the new length (tokens dropped iff it changed)
+extern "C" int b2_fit_prompt(int32_t *tokens, int n, int n_ctx, int n_keep) {
+    B2_API_BEGIN
+    std::vector<int32_t> v(tokens, tokens + n);
+    fit_prompt_to_context(v, n_ctx, n_keep);
+    std::copy(v.begin(), v.end(), tokens);
+    return (int)v.size();
     B2_API_END(0)
 }
 

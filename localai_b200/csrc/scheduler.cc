@@ -235,8 +235,7 @@ void Scheduler::launch_slot(Slot &s, std::shared_ptr<Request> r) {
     s.req = r;
     s.state = PROMPT;
     s.n_decoded = 0;
-    s.generated_text.clear();
-    s.sent_count = 0;
+    s.out.reset(&r->stop);
     s.has_next_token = true;
     s.stopped_eos = s.stopped_word = s.stopped_limit = s.truncated = false;
     s.t_start_prompt = clk::now();
@@ -254,29 +253,15 @@ void Scheduler::launch_slot(Slot &s, std::shared_ptr<Request> r) {
     int n_keep = r->n_keep < 0 ? s.n_prompt : r->n_keep;
     n_keep = std::min(n_ctx - 4, n_keep);
     if (n_keep < 0) n_keep = 0;
-    if (s.n_prompt >= n_ctx) { // truncate keeping n_keep + the tail half-blocks (grpc-server.cpp:1700-1721)
-        const int n_left = n_ctx - n_keep;
-        const int n_block = std::max(1, n_left / 2);
-        const int erased = (s.n_prompt - n_keep - n_block) / n_block;
-        std::vector<int32_t> nt(toks.begin(), toks.begin() + n_keep);
-        nt.insert(nt.end(), toks.begin() + n_keep + erased * n_block, toks.end());
-        toks.swap(nt);
-        while ((int)toks.size() >= n_ctx) toks.erase(toks.begin() + n_keep); // defensive: must fit
+    if (fit_prompt_to_context(toks, n_ctx, n_keep)) { // (stream_text.h; the reference's rule, grpc-server.cpp:1700-1721)
         s.truncated = true;
         s.n_prompt = (int)toks.size();
     }
-    if (!r->cache_prompt) {
-        s.n_past = 0;
-    } else { // in-memory prefix reuse (grpc-server.cpp:1740-1749)
-        size_t i = 0;
-        while (i < s.cache_tokens.size() && i < toks.size() && s.cache_tokens[i] == toks[i]) i++;
-        s.n_past = (int)i;
-        if (s.n_past > 0 && s.n_past == (int)s.cache_tokens.size()) s.n_past -= 1;
-    }
+    s.n_past = r->cache_prompt ? reusable_prefix(s.cache_tokens, toks) : 0; // in-memory prefix reuse (grpc-server.cpp:1740-1749)
     s.n_prompt_processed = s.n_prompt - s.n_past;
     s.cache_tokens = toks;
     s.prompt_tokens.swap(toks);
-    if (s.n_past == s.n_prompt && s.n_past > 0) s.n_past--; // at least one token must be evaluated
+    if (s.n_past == s.n_prompt && s.n_past > 0) s.n_past--; // at least one token must be evaluated (after the metric above, as in the reference)
 }
 
 void Scheduler::finish_slot(Slot &s, bool error, const std::string &msg) {
@@ -285,7 +270,7 @@ void Scheduler::finish_slot(Slot &s, bool error, const std::string &msg) {
     ev.flags = B2_EV_FINAL | (error ? B2_EV_ERROR : 0) | (s.stopped_eos ? B2_EV_STOP_EOS : 0) | (s.stopped_word ? B2_EV_STOP_WORD : 0) |
                (s.stopped_limit ? B2_EV_STOP_LIMIT : 0);
     if (error) ev.text = msg;
-    else if (!s.req->stream) ev.text = s.generated_text; // send_final_response: content only when not streaming
+    else if (!s.req->stream) ev.text = s.out.text(); // send_final_response: content only when not streaming
     ev.n_prompt = s.n_prompt;
     ev.n_decoded = s.n_decoded;
     ev.slot_id = s.id;
@@ -306,83 +291,32 @@ void Scheduler::finish_slot(Slot &s, bool error, const std::string &msg) {
     s.t_last_used = clk::now();
 }
 
-static size_t find_partial_stop(const std::string &stop, const std::string &text) { // grpc-server.cpp:88-107
-    if (!text.empty() && !stop.empty()) {
-        const char last = text.back();
-        for (int64_t i = (int64_t)stop.size() - 1; i >= 0; i--) {
-            if (stop[i] == last) {
-                const size_t n = (size_t)i + 1;
-                if (text.size() >= n && text.compare(text.size() - n, n, stop, 0, n) == 0) return text.size() - n;
-            }
-        }
-    }
-    return std::string::npos;
-}
-
-// process_token (grpc-server.cpp:1010-1123): returns has_next_token
+// The token just sampled for a slot: its bytes go through the slot's StreamText (UTF-8 hold-back, stop words), then the
+// budget and end-of-sequence rules decide whether the slot goes on (the behaviour of grpc-server.cpp:1010-1123).
 bool Scheduler::process_token(Slot &s, int32_t tok) {
     Request &r = *s.req;
-    const std::string piece = eng_->tokenizer()->token_to_piece(tok, true);
     s.sampled = tok;
-    s.generated_text += piece;
-    s.has_next_token = true;
-    bool incomplete = false; // incomplete UTF-8 sequence at the end?
-    for (unsigned i = 1; i < 5 && i <= s.generated_text.size(); ++i) {
-        const unsigned char c = s.generated_text[s.generated_text.size() - i];
-        if ((c & 0xC0) == 0x80) continue;
-        if ((c & 0xE0) == 0xC0) incomplete = i < 2;
-        else if ((c & 0xF0) == 0xE0) incomplete = i < 3;
-        else if ((c & 0xF8) == 0xF0) incomplete = i < 4;
-        break;
+    StreamText::Step step = s.out.append(eng_->tokenizer()->token_to_piece(tok, true));
+    bool go_on = !step.stop_word;
+    s.stopped_word = s.stopped_word || step.stop_word;
+    if (r.stream && !step.release.empty()) {
+        EventData ev;
+        ev.text = std::move(step.release);
+        ev.n_prompt = s.n_prompt;
+        ev.n_decoded = s.n_decoded;
+        ev.slot_id = s.id;
+        push_event(r, std::move(ev));
     }
-    if (!incomplete) {
-        size_t pos = std::min(s.sent_count, s.generated_text.size());
-        const std::string str_test = s.generated_text.substr(pos);
-        bool is_stop_full = false;
-        size_t stop_pos = std::string::npos;
-        for (const std::string &w : r.stop) { // full match
-            const size_t tmp = w.size() + piece.size();
-            const size_t from = str_test.size() > tmp ? str_test.size() - tmp : 0;
-            const size_t p = str_test.find(w, from);
-            if (p != std::string::npos && (stop_pos == std::string::npos || p < stop_pos)) {
-                s.stopped_word = true;
-                s.has_next_token = false;
-                stop_pos = p;
-            }
-        }
-        if (stop_pos != std::string::npos) {
-            is_stop_full = true;
-            s.generated_text.erase(pos + stop_pos);
-            pos = std::min(s.sent_count, s.generated_text.size());
-        } else {
-            for (const std::string &w : r.stop) { // partial match: hold the tail back
-                const size_t p = find_partial_stop(w, str_test);
-                if (p != std::string::npos && (stop_pos == std::string::npos || p < stop_pos)) stop_pos = p;
-            }
-        }
-        if (stop_pos == std::string::npos || (!s.has_next_token && !is_stop_full && stop_pos > 0)) {
-            std::string to_send = s.generated_text.substr(pos);
-            s.sent_count += to_send.size();
-            if (r.stream && !to_send.empty()) {
-                EventData ev;
-                ev.text = std::move(to_send);
-                ev.n_prompt = s.n_prompt;
-                ev.n_decoded = s.n_decoded;
-                ev.slot_id = s.id;
-                push_event(r, std::move(ev));
-            }
-        }
-    }
-    if (incomplete) s.has_next_token = true;
-    if (s.n_decoded > 0 && s.has_next_token && !has_budget(s)) {
+    if (go_on && s.n_decoded > 0 && !has_budget(s)) {
         s.stopped_limit = true;
-        s.has_next_token = false;
+        go_on = false;
     }
     if (tok == eng_->tokenizer()->eos_id()) { // EOS only; EOT is the caller's stop word (grpc-server.cpp:1103)
         s.stopped_eos = true;
-        s.has_next_token = false;
+        go_on = false;
     }
-    return s.has_next_token;
+    s.has_next_token = go_on;
+    return go_on;
 }
 
 // one update_slots() (grpc-server.cpp:1546-1982)

@@ -179,6 +179,51 @@ def test_qgemm_work_split_is_consistent(n_tiles, nkb, n_sm):
     assert r <= n_tiles
 
 
+def _stream(pieces, stops):
+    L = capi.lib()
+    buf = b"".join(pieces)
+    lens = (ctypes.c_int * len(pieces))(*[len(p) for p in pieces])
+    arr = (ctypes.c_char_p * max(1, len(stops)))(*stops) if stops else (ctypes.c_char_p * 1)()
+    s1, s2, used = ctypes.create_string_buffer(4096), ctypes.create_string_buffer(4096), ctypes.c_int(0)
+    L.b2_stream_text.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_int,
+                                 ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p]
+    r = L.b2_stream_text(buf, lens, len(pieces), arr, len(stops), s1, 4096, s2, 4096, ctypes.byref(used))
+    assert r >= 0, (L.b2_last_error() or b"").decode()
+    return s1.value, s2.value, bool(r), used.value
+
+
+def test_stream_text_holds_back_utf8_and_stop_words():
+    """The text rules of the request path (stream_text.h; behaviour of grpc-server.cpp:1010-1123), no device needed: a
+    character split over tokens is released whole; the beginning of a possible stop word is held back and released if it
+    turns out not to be one; a completed stop word ends the generation, and neither it nor what followed reaches the client
+    -- nor, as in the reference, do bytes of the completing token that precede the stop word in a stream."""
+    e = "\u20ac".encode()  # 3 bytes
+    assert _stream([b"a", e[:1], e[1:2], e[2:], b"b"], []) == (b"a" + e + b"b", b"a" + e + b"b", False, 5)
+    assert _stream([b"x", e[:2]], [])[0] == b"x"                                        # still incomplete: nothing of it released
+    assert _stream([b"Hello", b" wor", b"ld", b"!"], [b"world"]) == (b"Hello", b"Hello ", True, 3)   # " wor" is held back whole once "wor" may begin the word
+    assert _stream([b"Hi", b" ##", b"x", b"y"], [b"###"]) == (b"Hi ##xy", b"Hi ##xy", False, 4)     # held back, then released
+    assert _stream([b"Hi", b" ##", b"#", b"z"], [b"###"]) == (b"Hi", b"Hi ", True, 3)
+    assert _stream([b"Hel", b"lo STOP rest"], [b"STOP"]) == (b"Hel", b"Hello ", True, 2)            # stream loses "lo ", the final text keeps it
+    assert _stream([b"ab", b"cd"], [b"zz", b"cd", b"bc"]) == (b"", b"a", True, 2)                   # "b" may begin "bc": held; the earliest stop position wins
+
+
+def test_prompt_truncation_rule():
+    """A prompt that does not fit keeps n_keep tokens and its tail, dropping whole half-window blocks from the middle
+    (grpc-server.cpp:1700-1721); one that fits is untouched."""
+    L = capi.lib()
+    L.b2_fit_prompt.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    for n, n_ctx, n_keep in [(10, 16, 4), (16, 16, 4), (100, 16, 4), (1000, 256, 0), (257, 256, 252), (300, 64, 60)]:
+        t = np.arange(n, dtype=np.int32)
+        m = L.b2_fit_prompt(t.ctypes.data, n, n_ctx, n_keep)
+        if n < n_ctx:
+            assert m == n
+            continue
+        block = max(1, (n_ctx - n_keep) // 2)
+        erased = (n - n_keep - block) // block * block
+        want = np.concatenate([np.arange(n_keep), np.arange(n_keep + erased, n)])
+        assert m == len(want) < n_ctx and np.array_equal(t[:m], want), (n, n_ctx, n_keep)
+
+
 def test_corrupt_gguf_headers_are_rejected(tmp_path, model_files):
     """Header fields are not trusted: a zero / non-power-of-two alignment, tensor offsets that wrap, element counts that
     overflow and counts beyond the file are parse errors, not divisions by zero, wild reads or huge allocations."""
