@@ -784,7 +784,7 @@ void ref_mul_mat(int wtype, const void *W, int64_t rows, int64_t cols, const flo
 typedef struct { const void *data; int type; int64_t rows, cols; } ref_tensor;
 
 enum { TK_TOK_EMBD = 0, TK_OUTPUT_NORM, TK_OUTPUT, TK_ATTN_NORM, TK_WQ, TK_WK, TK_WV, TK_WO, TK_FFN_NORM, TK_GATE, TK_UP,
-       TK_DOWN, TK_COUNT };
+       TK_DOWN, TK_BQ, TK_BK, TK_BV, TK_COUNT }; /* TK_BQ/BK/BV: attn_q/k/v.bias (f32 rows; qwen2) */
 
 typedef struct {
     int n_layer, n_embd, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_ctx;
@@ -793,6 +793,7 @@ typedef struct {
      * optional per-dimension frequency divisors (rope_freqs.weight, the Llama-3.1 scheme) */
     float rope_ext_factor, rope_attn_factor, rope_corr_dims[2];
     const float *rope_freq_factors;
+    int rope_neox; /* LLAMA_ROPE_TYPE_NEOX (qwen2): the rotated pairs are (i, i + n_dims / 2) instead of (2i, 2i + 1) */
     ref_tensor global[3];
     ref_tensor *layer[TK_COUNT]; /* indices >= TK_ATTN_NORM used */
     fp16_t *k_cache, *v_cache;   /* [n_layer][n_ctx][n_head_kv*head_dim] */
@@ -821,6 +822,8 @@ void ref_ctx_set_rope_scaling(ref_ctx *c, float freq_scale, float ext_factor, fl
     c->rope_freq_factors = freq_factors;
     if (ext_factor != 0.0f) ref_rope_yarn_corr_dims(c->head_dim, n_ctx_orig, c->rope_theta, beta_fast, beta_slow, c->rope_corr_dims);
 }
+
+void ref_ctx_set_rope_neox(ref_ctx *c, int neox) { c->rope_neox = neox; }
 
 void ref_ctx_free(ref_ctx *c) {
     if (!c) return;
@@ -894,6 +897,17 @@ void ref_rope_cache_ext(float theta_base, float freq_scale, float freq_base, int
     }
 }
 
+/* mode 2 ("NEOX", ggml.c rope_neox): pair i = (x[i], x[i + n_dims / 2]), rotated by cache entry i */
+static void rope_neox(float *x, const float *cache, int n_dims) {
+    for (int i0 = 0; i0 < n_dims; i0 += 2) {
+        const int ic = i0 / 2;
+        const float c = cache[i0], s = cache[i0 + 1];
+        const float x0 = x[ic], x1 = x[ic + n_dims / 2];
+        x[ic] = x0 * c - x1 * s;
+        x[ic + n_dims / 2] = x0 * s + x1 * c;
+    }
+}
+
 /* mode 0 ("NORM"): adjacent pairs */
 static void rope_norm(float *x, const float *cache, int n_dims) {
     for (int i0 = 0; i0 < n_dims; i0 += 2) {
@@ -950,9 +964,17 @@ int ref_eval(ref_ctx *c, const int32_t *tokens, int n_tokens, int n_past, float 
         mat(&c->layer[TK_WQ][il], cur, (int)T, q);
         mat(&c->layer[TK_WK][il], cur, (int)T, k);
         mat(&c->layer[TK_WV][il], cur, (int)T, v);
+        /* qwen2 (llm_build_qwen2): Qcur = ggml_add(Qcur, bq) etc. before the rotation */
+        const float *bq = (const float *)c->layer[TK_BQ][il].data, *bk = (const float *)c->layer[TK_BK][il].data,
+                    *bv = (const float *)c->layer[TK_BV][il].data;
         for (int t = 0; t < T; t++) {
-            for (int h = 0; h < nh; h++) rope_norm(q + t * d + h * hd, ropec + t * hd, hd);
-            for (int h = 0; h < nkv; h++) rope_norm(k + t * kvd + h * hd, ropec + t * hd, hd);
+            if (bq) for (int i = 0; i < d; i++) q[t * d + i] += bq[i];
+            if (bk) for (int i = 0; i < kvd; i++) k[t * kvd + i] += bk[i];
+            if (bv) for (int i = 0; i < kvd; i++) v[t * kvd + i] += bv[i];
+        }
+        for (int t = 0; t < T; t++) {
+            for (int h = 0; h < nh; h++) (c->rope_neox ? rope_neox : rope_norm)(q + t * d + h * hd, ropec + t * hd, hd);
+            for (int h = 0; h < nkv; h++) (c->rope_neox ? rope_neox : rope_norm)(k + t * kvd + h * hd, ropec + t * hd, hd);
             for (int i = 0; i < kvd; i++) {
                 kc[(size_t)(n_past + t) * kvd + i] = fp32_to_fp16(k[t * kvd + i]);
                 vc[(size_t)(n_past + t) * kvd + i] = fp32_to_fp16(v[t * kvd + i]);

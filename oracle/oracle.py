@@ -22,12 +22,13 @@ T_Q4_0, T_Q4_1, T_Q5_0, T_Q5_1 = 2, 3, 6, 7
 T_Q2_K, T_Q3_K = 10, 11
 T_IQ4_NL, T_IQ4_XS = 20, 23
 (TK_TOK_EMBD, TK_OUTPUT_NORM, TK_OUTPUT, TK_ATTN_NORM, TK_WQ, TK_WK, TK_WV, TK_WO, TK_FFN_NORM, TK_GATE, TK_UP,
- TK_DOWN) = range(12)
+ TK_DOWN, TK_BQ, TK_BK, TK_BV) = range(15)
 
 _LAYER_TENSORS = {
     "attn_norm": TK_ATTN_NORM, "attn_q": TK_WQ, "attn_k": TK_WK, "attn_v": TK_WV, "attn_output": TK_WO,
     "ffn_norm": TK_FFN_NORM, "ffn_gate": TK_GATE, "ffn_up": TK_UP, "ffn_down": TK_DOWN,
 }
+_LAYER_BIASES = {"attn_q": TK_BQ, "attn_k": TK_BK, "attn_v": TK_BV}  # blk.N.attn_q.bias ... (qwen2)
 _GLOBAL_TENSORS = {"token_embd": TK_TOK_EMBD, "output_norm": TK_OUTPUT_NORM, "output": TK_OUTPUT}
 
 
@@ -134,13 +135,21 @@ class OracleModel:
             fld = f[key]
             return fld.parts[fld.data[0]][0]
 
-        self.n_layer = int(scalar("llama.block_count"))
-        self.n_embd = int(scalar("llama.embedding_length"))
-        self.n_head = int(scalar("llama.attention.head_count"))
-        self.n_head_kv = int(scalar("llama.attention.head_count_kv", self.n_head))
-        self.n_ff = int(scalar("llama.feed_forward_length"))
-        self.rms_eps = float(scalar("llama.attention.layer_norm_rms_epsilon", 1e-5))
-        self.rope_theta = float(scalar("llama.rope.freq_base", 10000.0))
+        def string(key, default):
+            if key not in f:
+                return default
+            fld = f[key]
+            return bytes(fld.parts[fld.data[0]]).decode()
+
+        A = string("general.architecture", "llama") + "."
+        self.arch = A[:-1]
+        self.n_layer = int(scalar(A + "block_count"))
+        self.n_embd = int(scalar(A + "embedding_length"))
+        self.n_head = int(scalar(A + "attention.head_count"))
+        self.n_head_kv = int(scalar(A + "attention.head_count_kv", self.n_head))
+        self.n_ff = int(scalar(A + "feed_forward_length"))
+        self.rms_eps = float(scalar(A + "attention.layer_norm_rms_epsilon", 1e-5))
+        self.rope_theta = float(scalar(A + "rope.freq_base", 10000.0))
         self.n_ctx = n_ctx
         self.tensors = {t.name: t for t in self.reader.tensors}
         self.n_vocab = int(self.tensors["token_embd.weight"].shape[1])
@@ -149,18 +158,12 @@ class OracleModel:
                                  self.rms_eps, self.rope_theta, 1.0)
         self._keep = []
         # RoPE scaling as llama.cpp derives it from the metadata (llama.cpp: llm_load_hparams / llama_new_context_with_model)
-        def string(key, default):
-            if key not in f:
-                return default
-            fld = f[key]
-            return bytes(fld.parts[fld.data[0]]).decode()
-
-        stype = rope_scaling or string("llama.rope.scaling.type", "none")
-        factor = float(scalar("llama.rope.scaling.factor", 1.0))
+        stype = rope_scaling or string(A + "rope.scaling.type", "none")
+        factor = float(scalar(A + "rope.scaling.factor", 1.0))
         self.rope_freq_scale = 1.0 / factor if stype in ("linear", "yarn") and factor > 0 else 1.0
         self.rope_ext_factor = yarn_ext_factor or (1.0 if stype == "yarn" else 0.0)
         overridden = bool(rope_scaling or yarn_ext_factor or yarn_attn_factor or yarn_beta_fast or yarn_beta_slow)
-        n_ctx_orig = int(scalar("llama.rope.scaling.original_context_length", scalar("llama.context_length", 2048)))
+        n_ctx_orig = int(scalar(A + "rope.scaling.original_context_length", scalar(A + "context_length", 2048)))
         ff = None
         if "rope_freqs.weight" in self.tensors:
             ff = np.ascontiguousarray(np.array(self.tensors["rope_freqs.weight"].data, dtype=np.float32))
@@ -170,7 +173,17 @@ class OracleModel:
                                                    C.c_float, C.c_float, C.c_void_p]
             L.ref_ctx_set_rope_scaling(self.ctx, self.rope_freq_scale, self.rope_ext_factor, yarn_attn_factor or 1.0, n_ctx_orig,
                                        yarn_beta_fast or 32.0, yarn_beta_slow or 1.0, ff.ctypes.data if ff is not None else None)
+        if self.arch == "qwen2":  # LLAMA_ROPE_TYPE_NEOX (llama.cpp llama_rope_type)
+            L.ref_ctx_set_rope_neox.argtypes = [C.c_void_p, C.c_int]
+            L.ref_ctx_set_rope_neox(self.ctx, 1)
         for name, t in self.tensors.items():
+            if name.endswith(".bias"):  # blk.N.attn_{q,k,v}.bias: one f32 row
+                _, il, nm = name[:-len(".bias")].split(".", 2)
+                if nm in _LAYER_BIASES:
+                    data = np.ascontiguousarray(np.array(t.data, dtype=np.float32)).view(np.uint8).reshape(-1)
+                    self._keep.append(data)
+                    L.ref_ctx_set_tensor(self.ctx, _LAYER_BIASES[nm], int(il), _ptr(data), 0, 1, int(t.shape[0]))
+                continue
             base = name.rsplit(".weight", 1)[0]
             data = np.ascontiguousarray(t.data).view(np.uint8).reshape(-1)
             self._keep.append(data)

@@ -65,6 +65,8 @@ class Arch:
     rope_factor: float = 1.0     # llama.rope.scaling.factor
     rope_orig_ctx: int = 0       # llama.rope.scaling.original_context_length
     rope_freqs: bool = False     # write rope_freqs.weight (per-dimension frequency divisors, the Llama-3.1 scheme)
+    gguf_arch: str = "llama"     # general.architecture and the prefix of the hyper-parameter keys ("llama" | "qwen2")
+    qkv_bias: bool = False       # attn_q/k/v.bias tensors (qwen2)
     head_dim: int = field(init=False)
 
     def __post_init__(self):
@@ -80,6 +82,8 @@ ARCHS = {
     "micro-linear": Arch("micro-linear", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "linear", 4.0, 128),
     "micro-yarn": Arch("micro-yarn", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "yarn", 4.0, 128),
     "micro-l31": Arch("micro-l31", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "none", 1.0, 0, True),
+    # qwen2: QKV biases, NEOX rotary pairs (i, i + head_dim / 2), its own BPE pre-tokeniser (digits one at a time)
+    "mini-qwen2": Arch("mini-qwen2", 3, 512, 8, 2, 1024, 4608, 1024, 1000000.0, 1e-6, "bpe", False, "none", 1.0, 0, False, "qwen2", True),
     "micro-g8": Arch("micro-g8", 2, 512, 8, 1, 1024, 4352, 512, 10000.0, 1e-5, "spm"),  # 8 query heads per KV head (the 70B grouping), head_dim 64
     "mini-70b": Arch("mini-70b", 4, 2048, 16, 8, 4096, 8192, 1024, 500000.0, 1e-5, "bpe", True),  # 70B type mix (Q5_K attn_v), 8 KV heads; shards 2 / 4 / 8 ways
     # BASELINE.json configs
@@ -442,6 +446,8 @@ def tensor_plan(arch: Arch, preset: str, gain_out: float):
             t = tensor_type(preset, arch, p + nm, i)
             norm = nm.endswith("_norm.weight")
             plan.append((p + nm, rows, cols, t, 0.0 if norm else 1.0 / np.sqrt(cols), norm))
+            if arch.qkv_bias and nm in ("attn_q.weight", "attn_k.weight", "attn_v.weight"):
+                plan.append((p + nm.replace(".weight", ".bias"), 1, rows, F32, 0.0, True))
     if arch.rope_freqs:
         plan.append(("rope_freqs.weight", 1, hd // 2, F32, 0.0, True))
     plan.append(("output_norm.weight", 1, d, F32, 0.0, True))
@@ -480,7 +486,11 @@ def _write_tensor(job):
     n = 0
     with open(path, "r+b") as f:
         f.seek(off)
-        if name == "rope_freqs.weight":
+        if name.endswith(".bias"):
+            w = (0.3 * rng.standard_normal(cols)).astype(np.float32)
+            f.write(w.tobytes())
+            n = w.nbytes
+        elif name == "rope_freqs.weight":
             w = llama31_rope_factors(cols * 2, *job[11]).astype(np.float32)
             f.write(w.tobytes())
             n = w.nbytes
@@ -511,23 +521,23 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     ftype = {"f32": 0, "f16": 1, "q8_0": 7, "q4_k_m": 15, "q4_k": 14, "q5_k": 16, "q6_k": 18, "mixed": 15,
              "q4_0": 2, "q4_1": 3, "q5_0": 8, "q5_1": 9, "q2_k": 10, "q3_k": 12, "iq4_nl": 25, "iq4_xs": 30}[preset]  # llama_ftype
     kvs = [
-        kv_bytes("general.architecture", T_STR, "llama"),
+        kv_bytes("general.architecture", T_STR, arch.gguf_arch),
         kv_bytes("general.name", T_STR, f"{arch.name}-{preset}-random-seed{seed}"),
         kv_bytes("general.file_type", T_U32, ftype),
         kv_bytes("general.quantization_version", T_U32, 2),
         kv_bytes("general.alignment", T_U32, ALIGN),
-        kv_bytes("llama.context_length", T_U32, n_ctx_train or arch.n_ctx_train),
-        kv_bytes("llama.embedding_length", T_U32, arch.n_embd),
-        kv_bytes("llama.block_count", T_U32, arch.n_layer),
-        kv_bytes("llama.feed_forward_length", T_U32, arch.n_ff),
-        kv_bytes("llama.attention.head_count", T_U32, arch.n_head),
-        kv_bytes("llama.attention.head_count_kv", T_U32, arch.n_head_kv),
-        kv_bytes("llama.attention.layer_norm_rms_epsilon", T_F32, arch.rms_eps),
-        kv_bytes("llama.rope.freq_base", T_F32, arch.rope_theta),
-        kv_bytes("llama.rope.dimension_count", T_U32, arch.head_dim),
-        kv_bytes("llama.vocab_size", T_U32, arch.n_vocab),
+        kv_bytes(arch.gguf_arch + ".context_length", T_U32, n_ctx_train or arch.n_ctx_train),
+        kv_bytes(arch.gguf_arch + ".embedding_length", T_U32, arch.n_embd),
+        kv_bytes(arch.gguf_arch + ".block_count", T_U32, arch.n_layer),
+        kv_bytes(arch.gguf_arch + ".feed_forward_length", T_U32, arch.n_ff),
+        kv_bytes(arch.gguf_arch + ".attention.head_count", T_U32, arch.n_head),
+        kv_bytes(arch.gguf_arch + ".attention.head_count_kv", T_U32, arch.n_head_kv),
+        kv_bytes(arch.gguf_arch + ".attention.layer_norm_rms_epsilon", T_F32, arch.rms_eps),
+        kv_bytes(arch.gguf_arch + ".rope.freq_base", T_F32, arch.rope_theta),
+        kv_bytes(arch.gguf_arch + ".rope.dimension_count", T_U32, arch.head_dim),
+        kv_bytes(arch.gguf_arch + ".vocab_size", T_U32, arch.n_vocab),
         kv_bytes("tokenizer.ggml.model", T_STR, vocab["model"]),
-        kv_bytes("tokenizer.ggml.pre", T_STR, vocab["pre"]),
+        kv_bytes("tokenizer.ggml.pre", T_STR, "qwen2" if arch.gguf_arch == "qwen2" else vocab["pre"]),
         kv_bytes("tokenizer.ggml.tokens", T_ARR, (T_STR, vocab["tokens"])),
         kv_bytes("tokenizer.ggml.scores", T_ARR, (T_F32, vocab["scores"])),
         kv_bytes("tokenizer.ggml.token_type", T_ARR, (T_I32, vocab["types"])),
@@ -537,10 +547,10 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
         kv_bytes("tokenizer.ggml.add_eos_token", T_BOOL, False),
     ]
     if arch.rope_scaling != "none":
-        kvs.append(kv_bytes("llama.rope.scaling.type", T_STR, arch.rope_scaling))
-        kvs.append(kv_bytes("llama.rope.scaling.factor", T_F32, arch.rope_factor))
+        kvs.append(kv_bytes(arch.gguf_arch + ".rope.scaling.type", T_STR, arch.rope_scaling))
+        kvs.append(kv_bytes(arch.gguf_arch + ".rope.scaling.factor", T_F32, arch.rope_factor))
         if arch.rope_orig_ctx:
-            kvs.append(kv_bytes("llama.rope.scaling.original_context_length", T_U32, arch.rope_orig_ctx))
+            kvs.append(kv_bytes(arch.gguf_arch + ".rope.scaling.original_context_length", T_U32, arch.rope_orig_ctx))
     if vocab.get("unk", -1) >= 0:
         kvs.append(kv_bytes("tokenizer.ggml.unknown_token_id", T_U32, vocab["unk"]))
     if vocab["merges"]:
@@ -551,7 +561,7 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
     infos = []
     off = 0
     for name, rows, cols, t, _, _ in plan:
-        dims = [cols] if rows == 1 and (name.endswith("_norm.weight") or name == "rope_freqs.weight") else [cols, rows]
+        dims = [cols] if rows == 1 and (name.endswith("_norm.weight") or name == "rope_freqs.weight" or name.endswith(".bias")) else [cols, rows]
         infos.append(_s(name.encode()) + struct.pack("<I", len(dims)) + b"".join(struct.pack("<Q", x) for x in dims)
                      + struct.pack("<IQ", t, off))
         nb = tensor_nbytes(rows, cols, t)
