@@ -39,8 +39,10 @@ struct KVLayout {
     int page_size, max_pages, kvd;
 };
 // q: [n_tok][n_head*hd] rotated in place; k,v: [n_tok][kvd]; pos/slot: per-token position and slot id (device)
+// bq / bk / bv: optional projection biases added first (qwen2); neox: rotate pairs (i, i + hd/2) instead of (2i, 2i+1)
 void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok,
-                          int n_head, int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, cudaStream_t s);
+                          int n_head, int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, cudaStream_t s, const float *bq = nullptr,
+                          const float *bk = nullptr, const float *bv = nullptr, bool neox = false);
 // out[t][h*hd + i] = sum_j softmax_j(q_t . k_j * scale) v_j over positions j <= pos[t] of slot[t]
 void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, int n_tok, int n_head, int n_head_kv,
                       int hd, const KVLayout &kv, float *out, int max_ctx, cudaStream_t s);

@@ -68,9 +68,12 @@ void launch_swiglu(const float *gate, const float *up, float *out, int64_t n, cu
 }
 
 // ------------------------------------------------------------------------------------------ RoPE (NORM pairs) + KV store
+// bq / bk / bv (optional, qwen2): added to the projections before the rotation (ggml_add(Qcur, bq) in llm_build_qwen2);
+// neox: the rotated pairs are (i, i + hd / 2) (LLAMA_ROPE_TYPE_NEOX) instead of (2i, 2i + 1)
 __global__ void rope_kv_store_kernel(float *__restrict__ q, float *__restrict__ k, const float *__restrict__ v,
                                      const int32_t *__restrict__ pos, const int32_t *__restrict__ slot, int n_head, int n_head_kv,
-                                     int hd, const float *__restrict__ rope_table, KVLayout kv) {
+                                     int hd, const float *__restrict__ rope_table, KVLayout kv, const float *__restrict__ bq,
+                                     const float *__restrict__ bk, const float *__restrict__ bv, int neox) {
     B2_PDL_TRIGGER();
     B2_PDL_WAIT();
     const int t = blockIdx.x;
@@ -89,26 +92,38 @@ __global__ void rope_kv_store_kernel(float *__restrict__ q, float *__restrict__ 
         const bool is_q = i < nq;
         const int ii = is_q ? i : i - nq;
         const int h = ii / half, pr = ii % half;
-        float *x = (is_q ? qt : kt) + h * hd + 2 * pr;
+        const int i0 = neox ? pr : 2 * pr, i1 = neox ? pr + half : 2 * pr + 1; // the two elements of pair pr inside the head
+        float *x = (is_q ? qt : kt) + h * hd;
+        const float *bias = is_q ? bq : bk;
         const float c = cs[2 * pr], sn = cs[2 * pr + 1];
-        const float x0 = x[0], x1 = x[1];
+        float x0 = x[i0], x1 = x[i1];
+        if (bias) {
+            x0 = __fadd_rn(x0, bias[h * hd + i0]);
+            x1 = __fadd_rn(x1, bias[h * hd + i1]);
+        }
         const float r0 = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, sn));
         const float r1 = __fadd_rn(__fmul_rn(x0, sn), __fmul_rn(x1, c));
         if (is_q) {
-            x[0] = r0;
-            x[1] = r1;
-        } else {
+            x[i0] = r0;
+            x[i1] = r1;
+        } else if (!neox) {
             *(__half2 *)(kv.k_pool + cell + h * hd + 2 * pr) = __halves2half2(__float2half_rn(r0), __float2half_rn(r1));
+        } else {
+            kv.k_pool[cell + h * hd + i0] = __float2half_rn(r0);
+            kv.k_pool[cell + h * hd + i1] = __float2half_rn(r1);
         }
     }
-    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < kv.kvd; i += gridDim.y * blockDim.x) kv.v_pool[cell + i] = __float2half_rn(vt[i]);
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < kv.kvd; i += gridDim.y * blockDim.x)
+        kv.v_pool[cell + i] = __float2half_rn(bv ? __fadd_rn(vt[i], bv[i]) : vt[i]);
 }
 
 void launch_rope_kv_store(float *q, float *k, const float *v, const int32_t *pos, const int32_t *slot, int n_tok, int n_head,
-                          int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, cudaStream_t s) {
+                          int n_head_kv, int hd, const float *rope_table, const KVLayout &kv, cudaStream_t s, const float *bq,
+                          const float *bk, const float *bv, bool neox) {
     if (n_tok <= 0) return;
     const int split = n_tok >= 512 ? 1 : n_tok >= 128 ? 2 : 8;
-    launch_pdl(rope_kv_store_kernel, dim3(n_tok, split), dim3(256), 0, s, q, k, v, pos, slot, n_head, n_head_kv, hd, rope_table, kv);
+    launch_pdl(rope_kv_store_kernel, dim3(n_tok, split), dim3(256), 0, s, q, k, v, pos, slot, n_head, n_head_kv, hd, rope_table, kv, bq, bk, bv,
+               neox ? 1 : 0);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }

@@ -94,7 +94,9 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     else gemm_min_tokens_ = -1; // automatic, see gemm_threshold()
 
     hp.arch = f.get_s("general.architecture", "");
-    B2_CHECK(hp.arch == "llama", B2_EUNSUPPORTED, "unsupported architecture '" + hp.arch + "' (only llama-family GGUF)");
+    B2_CHECK(hp.arch == "llama" || hp.arch == "qwen2", B2_EUNSUPPORTED,
+             "unsupported architecture '" + hp.arch + "' (llama and qwen2 GGUFs)");
+    hp.rope_neox = hp.arch == "qwen2"; // llama.cpp llama_rope_type: NEOX pairs (i, i + head_dim / 2)
     hp.name = f.get_s("general.name", "");
     const std::string a = hp.arch + ".";
     hp.n_layer = (int)f.get_u(a + "block_count", 0);
@@ -169,11 +171,27 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
         L.wk = upload(f, p + "attn_k.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
         L.wv = upload(f, p + "attn_v.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
         L.wo = upload(f, p + "attn_output.weight", d, d, true, 0, -1, (int64_t)r * dq_l, dq_l);
+        if (f.tensor(p + "attn_q.bias")) { // qwen2: biases of the three projections (F32 rows)
+            B2_CHECK(tp_size == 1, B2_EUNSUPPORTED, "tensor-parallel loading of models with QKV biases is not built");
+            L.bq = upload(f, p + "attn_q.bias", 1, d, true);
+            L.bk = upload(f, p + "attn_k.bias", 1, kvd, true);
+            L.bv = upload(f, p + "attn_v.bias", 1, kvd, true);
+            B2_CHECK(L.bq.type == B2_T_F32 && L.bk.type == B2_T_F32 && L.bv.type == B2_T_F32, B2_EUNSUPPORTED, "QKV biases must be F32");
+            qkv_bias_ = true;
+        }
         L.ffn_norm = upload(f, p + "ffn_norm.weight", 1, d, true);
         L.gate = upload(f, p + "ffn_gate.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
         L.up = upload(f, p + "ffn_up.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
         L.down = upload(f, p + "ffn_down.weight", d, ff, true, 0, -1, (int64_t)r * ff_l, ff_l);
         B2_CHECK(L.attn_norm.type == B2_T_F32 && L.ffn_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
+    }
+    if (qkv_bias_ || hp.rope_neox) {
+        // Biases and NEOX rotary pairs live in rope_kv_store_kernel only: such models take the per-operator kernels for small
+        // batches (no persistent decode kernel, no fused QKV epilogue, no fused decode attention); the GEMM paths are shared.
+        B2_CHECK(tp_size == 1, B2_EUNSUPPORTED, "tensor-parallel loading is built for the llama architecture only");
+        no_mega_ = true;
+        unfused_ = true;
+        no_fused_att_ = true;
     }
     output_norm = upload(f, "output_norm.weight", 1, d, true);
     B2_CHECK(output_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
@@ -394,7 +412,8 @@ void Model::run_layer_unfused(const LayerW &L, const KVLayout &kv, int n) {
     matmul(L.wq, xn_, d, n, q_, d, nullptr, 0);
     matmul(L.wk, xn_, d, n, k_, kvd, nullptr, 0);
     matmul(L.wv, xn_, d, n, v_, kvd, nullptr, 0);
-    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream, (const float *)L.bq.data,
+                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox);
     attention(kv, n);
     invalidate(actq_valid_);
     matmul(L.wo, att_, d, n, x_, d, x_, d); // x = x + wo.att
@@ -565,7 +584,8 @@ void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
         const int64_t strides[3] = {d, kvd, kvd};
         gemm_multi(Ws, outs, strides, 3, n);
     }
-    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+    launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream, (const float *)L.bq.data,
+                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox);
     attention(kv, n);
     launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
     gemm(L.wo, n, x_, d, x_, d);
@@ -645,7 +665,8 @@ void Model::run_layer_qgemm(const LayerW &L, const KVLayout &kv, int n) {
     if (!(slots_distinct_ && !no_fused_att_ &&
           launch_attention_decode_fused(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, n_ctx_slot, gemm_x_,
                                         (int)align_up(n, 16), stream))) {
-        launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream);
+        launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream, (const float *)L.bq.data,
+                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox);
         attention(kv, n);
         launch_qgemm_prepare_x(att_, d, n, d, gemm_x_, stream);
     }

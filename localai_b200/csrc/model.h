@@ -18,6 +18,7 @@ struct SampleSpec;
 struct HParams {
     int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_ctx_train = 0;
     float rms_eps = 1e-5f, rope_base = 10000.f, rope_scale = 1.f;
+    bool rope_neox = false;      // rotary pairs (i, i + head_dim / 2) (qwen2) instead of (2i, 2i + 1)
     float rope_ext_factor = 0.f; // 1 for YaRN (llama.rope.scaling.type)
     float rope_attn_factor = 1.f, rope_beta_fast = 32.f, rope_beta_slow = 1.f; // llama.cpp's defaults, b2_load_opts overrides
     int rope_n_ctx_orig = 0;     // llama.rope.scaling.original_context_length
@@ -26,6 +27,7 @@ struct HParams {
 
 struct LayerW {
     DTensor attn_norm, wq, wk, wv, wo, ffn_norm, gate, up, down;
+    DTensor bq, bk, bv; // attn_{q,k,v}.bias (qwen2); data == nullptr when the model has none
 };
 
 // A batch for one forward pass: n tokens, each with its own position and slot (sequence).
@@ -153,6 +155,7 @@ class Model {
     float *qg_part_ = nullptr;
     unsigned *qg_counters_ = nullptr;
     bool slots_distinct_ = false; // the current batch has one token per slot (set by forward / forward_device_inputs)
+    bool qkv_bias_ = false;       // the model has attn_{q,k,v}.bias tensors
     bool no_fused_att_ = false;   // B200LLM_NO_FUSED_ATT=1: RoPE / attention / tile conversion as three launches (A/B tests)
     bool no_qgemm_ = false;   // B200LLM_NO_QGEMM=1: the fp16-tile path for every batch size (A/B tests)
     void *resident_qtiles(const DTensor &W);

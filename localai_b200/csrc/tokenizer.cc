@@ -88,7 +88,8 @@ static const ByteMap &byte_map() {
 
 // ------------------------------------------------------------------------------------------ llama-3 pre-tokeniser
 // "(?i:'s|'t|'re|'ve|'m|'ll|'d)|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}{1,3}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]+|\s+(?!\S)|\s+"
-std::vector<std::string> llama3_pretokenize(const std::string &text) {
+// The qwen2 pre-tokeniser is the same expression with "\p{N}" (one digit per word) in place of "\p{N}{1,3}": `max_digits` 1.
+std::vector<std::string> llama3_pretokenize(const std::string &text, int max_digits) {
     std::vector<uint32_t> off;
     const std::vector<uint32_t> cpts = utf8_to_cpts(text, &off);
     const size_t n = cpts.size();
@@ -124,10 +125,10 @@ std::vector<std::string> llama3_pretokenize(const std::string &text) {
                 continue;
             }
         }
-        if (is_n(pos)) { // \p{N}{1,3}
+        if (is_n(pos)) { // \p{N}{1,max_digits}
             size_t ini = pos;
             while (is_n(pos)) {
-                if (++pos - ini >= 3) { add(pos); ini = pos; }
+                if (++pos - ini >= (size_t)max_digits) { add(pos); ini = pos; }
             }
             add(pos);
             continue;
@@ -184,9 +185,11 @@ Tokenizer::Tokenizer(const GGUFFile &f) {
         kind_ = BPE;
         bos_ = 11; eos_ = 11;
         add_bos_ = false;
-        B2_CHECK(pre_ == "llama-bpe" || pre_ == "llama3" || pre_ == "llama-v3" || pre_ == "default", B2_EUNSUPPORTED,
-                 "unsupported BPE pre-tokeniser '" + pre_ + "' (only llama-bpe)");
-        ignore_merges_ = pre_ != "default";
+        B2_CHECK(pre_ == "llama-bpe" || pre_ == "llama3" || pre_ == "llama-v3" || pre_ == "default" || pre_ == "qwen2", B2_EUNSUPPORTED,
+                 "unsupported BPE pre-tokeniser '" + pre_ + "' (llama-bpe, qwen2)");
+        // llama-3 emits a word that is itself a token without merging and adds a BOS; qwen2 does neither (llama.cpp's
+        // per-pre-tokeniser defaults; the add_bos_token key below still overrides)
+        ignore_merges_ = pre_ != "default" && pre_ != "qwen2";
         if (ignore_merges_) add_bos_ = true;
         if (const GGUFValue *m = f.get("tokenizer.ggml.merges")) {
             bpe_ranks_.reserve(m->arr_s.size() * 2);
@@ -328,7 +331,7 @@ struct BpeBigram {
 
 void Tokenizer::bpe_tokenize(const std::string &text, std::vector<int32_t> &out) const {
     const ByteMap &bm = byte_map();
-    for (const std::string &raw : llama3_pretokenize(text)) {
+    for (const std::string &raw : llama3_pretokenize(text, pre_ == "qwen2" ? 1 : 3)) {
         std::string word;
         for (unsigned char c : raw) word += bm.b2u[c];
         std::vector<Sym> syms;

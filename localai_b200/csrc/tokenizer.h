@@ -54,6 +54,6 @@ class Tokenizer {
 };
 
 // exposed for tests
-std::vector<std::string> llama3_pretokenize(const std::string &text);
+std::vector<std::string> llama3_pretokenize(const std::string &text, int max_digits = 3);
 
 } // namespace b2

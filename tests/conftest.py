@@ -48,6 +48,7 @@ def model_files(gguf_dir):
         "micro_yarn": ("micro-yarn", "mixed"),
         "micro_l31": ("micro-l31", "mixed"),
         "micro_g8": ("micro-g8", "q4_k_m"),  # 8 query heads per KV head
+        "mini_qwen2": ("mini-qwen2", "q4_k_m"),  # qwen2: QKV biases, NEOX rotary pairs, its own pre-tokeniser
     }
     out = {}
     for name, (arch, preset) in specs.items():

@@ -68,6 +68,15 @@ def test_tokenizer_matches_upstream_library_goldens(model_files, kind, model, pa
             assert ids == g["ids"], g["text"]
 
 
+def test_qwen2_pretokenizer_matches_upstream_library_goldens(model_files):
+    """One digit per word, no ignore_merges, no BOS (tools/make_qwen2_tok_goldens.py; ids from the HF tokenizers library)."""
+    gold = json.load(open(os.path.join(GOLD, "tok_bpe_qwen2.json"), encoding="utf-8"))
+    with capi.Engine(model_files["mini_qwen2"], vocab_only=True) as e:
+        assert e.info.arch == b"qwen2"
+        for g in gold:
+            assert e.tokenize(g["text"], add_bos=True, parse_special=False) == g["ids"], g["text"]
+
+
 @pytest.mark.parametrize("model", ["micro_mixed", "mini_q4_k_m"])
 def test_detokenize_round_trip(model_files, model):
     texts = ["Hello world", "naïve café 日本語 🙂", "tabs\tand\nnewlines  ", "x = {'a': 1}"]

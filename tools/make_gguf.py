@@ -543,7 +543,7 @@ def write_gguf(path: str, arch: Arch, preset: str, seed: int = 0, gain_out: floa
         kv_bytes("tokenizer.ggml.token_type", T_ARR, (T_I32, vocab["types"])),
         kv_bytes("tokenizer.ggml.bos_token_id", T_U32, vocab["bos"]),
         kv_bytes("tokenizer.ggml.eos_token_id", T_U32, vocab["eos"]),
-        kv_bytes("tokenizer.ggml.add_bos_token", T_BOOL, bool(vocab.get("add_bos", True))),
+        kv_bytes("tokenizer.ggml.add_bos_token", T_BOOL, bool(vocab.get("add_bos", True)) and arch.gguf_arch != "qwen2"),
         kv_bytes("tokenizer.ggml.add_eos_token", T_BOOL, False),
     ]
     if arch.rope_scaling != "none":
