@@ -315,12 +315,22 @@ void BertModel::run_kernels(int T, int n_seq, int max_len) {
     // the fused epilogue runs without split-K: only where the feed-forward GEMM has enough output tiles for the SMs anyway
     const bool fused_gelu = ff % 256 == 0 && (int64_t)((T + 127) / 128) * (ff / 256) > 74 &&
                             !(getenv("B200LLM_BERT_UNFUSED_GELU") && atoi(getenv("B200LLM_BERT_UNFUSED_GELU")) != 0);
+    // More than one token tile (the projection is not split over K then) and heads of 64: attention on fp16 rows
+    const bool f16_att = head_dim == 64 && T > 128 && d % 8 == 0 &&
+                         !(getenv("B200LLM_BERT_ATT_F32") && atoi(getenv("B200LLM_BERT_ATT_F32")) != 0) &&
+                         !(getenv("B200LLM_BERT_ATT_SIMPLE") && atoi(getenv("B200LLM_BERT_ATT_SIMPLE")) != 0);
     launch_gemm_prepare_x(x_, d, T, d, x_tiles_, s);
     for (const BertLayer &L : layers_) { // on entry x_tiles_ holds x_
-        const GemmJob qkv[3] = {{&L.wq, L.tq, true, q_, d}, {&L.wk, L.tk, true, k_, d}, {&L.wv, L.tv, true, v_, d}};
-        launch_gemm_tc_multi(qkv, 3, x_tiles_, T, nullptr, 0, splitk_, splitk_bytes_, s);
-        launch_bert_attention(q_, k_, v_, L.bq, L.bk, L.bv, offs_dev_, n_seq, max_len, n_head, head_dim, att_, s);
-        launch_gemm_prepare_x(att_, d, T, d, x_tiles_, s);
+        if (f16_att) { // q | k | v leave the GEMM as fp16 rows with their biases; the attention writes attn_output's operand tiles
+            const GemmJob qkv[3] = {{&L.wq, L.tq, true, q_, d, L.bq}, {&L.wk, L.tk, true, k_, d, L.bk}, {&L.wv, L.tv, true, v_, d, L.bv}};
+            launch_gemm_tc_multi(qkv, 3, x_tiles_, T, nullptr, 0, nullptr, 0, s, true);
+            launch_bert_attention_f16(q_, k_, v_, offs_dev_, n_seq, max_len, n_head, x_tiles_, s);
+        } else {
+            const GemmJob qkv[3] = {{&L.wq, L.tq, true, q_, d}, {&L.wk, L.tk, true, k_, d}, {&L.wv, L.tv, true, v_, d}};
+            launch_gemm_tc_multi(qkv, 3, x_tiles_, T, nullptr, 0, splitk_, splitk_bytes_, s);
+            launch_bert_attention(q_, k_, v_, L.bq, L.bk, L.bv, offs_dev_, n_seq, max_len, n_head, head_dim, att_, s);
+            launch_gemm_prepare_x(att_, d, T, d, x_tiles_, s);
+        }
         launch_gemm_tc(L.wo, x_tiles_, T, h_, d, nullptr, 0, L.to, true, splitk_, splitk_bytes_, s);
         ln(L.bo, L.ln1_w, L.ln1_b);
         if (fused_gelu) { // bias + GELU in the GEMM's epilogue, which writes the down projection's operand tiles

@@ -93,6 +93,9 @@ void launch_bert_embed_ln(float *x, const float *pos_embd, const float *type0, c
 void launch_bert_bias_residual_ln(float *x, const float *h, const float *bias, const float *w, const float *b, int n_tok, int d,
                                   float eps, cudaStream_t s);
 // bidirectional attention inside each sequence; q/k/v: [n_tok][n_head * hd] without their biases (added on load)
+// head size 64, q | k | v as fp16 rows with their biases (the projection GEMM's out_f16 epilogue): writes attn_output's operand tiles
+void launch_bert_attention_f16(const void *q, const void *k, const void *v, const int32_t *offs, int n_seq, int max_len, int n_head,
+                               void *x_tiles, cudaStream_t s);
 void launch_bert_attention(const float *q, const float *k, const float *v, const float *bq, const float *bk, const float *bv,
                            const int32_t *offs, int n_seq, int max_len, int n_head, int hd, float *out, cudaStream_t s);
 void launch_bert_mean_pool_l2(const float *x, const int32_t *offs, int n_seq, int d, float *out, cudaStream_t s);

@@ -240,9 +240,11 @@ struct GemmJob {
     bool w_tiles_ready;
     float *out;
     int64_t out_stride;
+    const float *bias = nullptr; // with out_f16 only
 };
+// out_f16: the outputs are rows of fp16 (out_stride in halves) with the matrices' biases added; never split over K
 void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,
-                          float *splitk_scratch, size_t splitk_bytes, cudaStream_t s);
+                          float *splitk_scratch, size_t splitk_bytes, cudaStream_t s, bool out_f16 = false);
 
 // --- batched decode mat-mul with the dequantisation inside the GEMM (kernels_qgemm.cu) --------------------------------
 constexpr int QGEMM_MAX_TOKENS = 64;

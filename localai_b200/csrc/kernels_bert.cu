@@ -285,6 +285,157 @@ __global__ void __launch_bounds__(MMA_THREADS) bert_attention_mma_kernel(const f
     }
 }
 
+// ---- the same attention on fp16 rows (q | k | v as the projection GEMM's epilogue wrote them, biases included), for
+// head size 64.  K and V tiles of 64 keys arrive by cp.async into a two-stage ring (the next tile loads while this one is
+// multiplied), fragments come out of shared memory with ldmatrix.x4 (two k-steps of K, two feature groups of V per
+// instruction), the 1/sqrt(hd) scale is folded into the exponent (exp2(s c - m c), c = scale log2 e), and the result goes
+// straight into attn_output's operand tiles: [token tile][k tile = head][128 x 64] in core-matrix order, the layout
+// convert_x_tiles_kernel would have produced from fp32 rows.
+constexpr int F16_ROW = 64 + 8; // halves per staged row: 144 B, the 8 rows of an 8 x 8 matrix fall into different banks
+
+__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void mma_16816_f16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
+    const __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<const uint32_t *>(&v);
+}
+
+__global__ void __launch_bounds__(MMA_THREADS, 2)
+bert_attention_f16_kernel(const __half *__restrict__ q, const __half *__restrict__ k, const __half *__restrict__ v,
+                          const int32_t *__restrict__ offs, int n_head, __half *__restrict__ x_tiles) {
+    constexpr int HD = 64, KS = HD / 16, ND = HD / 8, NB = MMA_KT / 8;
+    __shared__ __align__(16) __half Kb[2][MMA_KT][F16_ROW];
+    __shared__ __align__(16) __half Vb[2][MMA_KT][F16_ROW];
+    const int seq = blockIdx.z, head = blockIdx.y, t0 = offs[seq], len = offs[seq + 1] - t0;
+    const int q0 = blockIdx.x * MMA_QB;
+    if (q0 >= len) return;
+    const int d = n_head * HD, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, tq = lane & 3;
+    const int r0 = q0 + warp * 16 + g, r1 = r0 + 8;
+    const int n_kt = (len + MMA_KT - 1) / MMA_KT;
+    auto load_tile = [&](int kt, int buf) { // 64 keys x 128 B of K and of V: 2 + 2 copies of 16 B per thread; keys past the end re-read the last one
+#pragma unroll
+        for (int i = tid; i < MMA_KT * 8; i += MMA_THREADS) {
+            const int r = i >> 3, c = (i & 7) * 8;
+            const size_t gi = (size_t)(t0 + min(kt * MMA_KT + r, len - 1)) * d + head * HD + c;
+            cp_async16(&Kb[buf][r][c], k + gi);
+            cp_async16(&Vb[buf][r][c], v + gi);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    load_tile(0, 0);
+    uint32_t qa[KS][4];
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int c = head * HD + ks * 16 + h * 8 + tq * 2;
+            qa[ks][2 * h + 0] = r0 < len ? *reinterpret_cast<const uint32_t *>(q + (size_t)(t0 + r0) * d + c) : 0u;
+            qa[ks][2 * h + 1] = r1 < len ? *reinterpret_cast<const uint32_t *>(q + (size_t)(t0 + r1) * d + c) : 0u;
+        }
+    }
+    const float cexp = rsqrtf((float)HD) * 1.4426950408889634f;
+    float o[ND][4];
+#pragma unroll
+    for (int i = 0; i < ND; i++) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -CUDART_INF_F, m1 = -CUDART_INF_F, l0 = 0.f, l1 = 0.f;
+    for (int kt = 0; kt < n_kt; kt++) {
+        const int buf = kt & 1, k0 = kt * MMA_KT;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads(); // tile kt is visible to everyone, and everyone is done with tile kt - 1
+        if (kt + 1 < n_kt) load_tile(kt + 1, buf ^ 1);
+        float s[NB][4];
+#pragma unroll
+        for (int nb = 0; nb < NB; nb++) {
+            s[nb][0] = s[nb][1] = s[nb][2] = s[nb][3] = 0.f;
+#pragma unroll
+            for (int kp = 0; kp < KS / 2; kp++) { // matrices: (k-step 2 kp: dims +0, +8), (k-step 2 kp + 1: dims +0, +8)
+                uint32_t b[4];
+                const uint32_t addr = (uint32_t)__cvta_generic_to_shared(&Kb[buf][nb * 8 + (lane & 7)][kp * 32 + (lane >> 3) * 8]);
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]) : "r"(addr));
+                mma_16816_f16(s[nb], qa[2 * kp], b[0], b[1]);
+                mma_16816_f16(s[nb], qa[2 * kp + 1], b[2], b[3]);
+            }
+        }
+        float mt0 = -CUDART_INF_F, mt1 = -CUDART_INF_F;
+#pragma unroll
+        for (int nb = 0; nb < NB; nb++) {
+            const int key = k0 + nb * 8 + tq * 2;
+            if (key >= len) s[nb][0] = s[nb][2] = -CUDART_INF_F;
+            if (key + 1 >= len) s[nb][1] = s[nb][3] = -CUDART_INF_F;
+            mt0 = fmaxf(mt0, fmaxf(s[nb][0], s[nb][1]));
+            mt1 = fmaxf(mt1, fmaxf(s[nb][2], s[nb][3]));
+        }
+        mt0 = fmaxf(mt0, __shfl_xor_sync(0xffffffffu, mt0, 1));
+        mt0 = fmaxf(mt0, __shfl_xor_sync(0xffffffffu, mt0, 2));
+        mt1 = fmaxf(mt1, __shfl_xor_sync(0xffffffffu, mt1, 1));
+        mt1 = fmaxf(mt1, __shfl_xor_sync(0xffffffffu, mt1, 2));
+        const float mn0 = fmaxf(m0, mt0), mn1 = fmaxf(m1, mt1); // finite: key k0 of every tile exists
+        const float sc0 = exp2f((m0 - mn0) * cexp), sc1 = exp2f((m1 - mn1) * cexp);
+        m0 = mn0;
+        m1 = mn1;
+        const float off0 = mn0 * cexp, off1 = mn1 * cexp;
+        float ps0 = 0.f, ps1 = 0.f;
+#pragma unroll
+        for (int nb = 0; nb < NB; nb++) {
+            s[nb][0] = exp2f(fmaf(s[nb][0], cexp, -off0));
+            s[nb][1] = exp2f(fmaf(s[nb][1], cexp, -off0));
+            s[nb][2] = exp2f(fmaf(s[nb][2], cexp, -off1));
+            s[nb][3] = exp2f(fmaf(s[nb][3], cexp, -off1));
+            ps0 += s[nb][0] + s[nb][1];
+            ps1 += s[nb][2] + s[nb][3];
+        }
+        l0 = l0 * sc0 + ps0;
+        l1 = l1 * sc1 + ps1;
+#pragma unroll
+        for (int nd = 0; nd < ND; nd++) {
+            o[nd][0] *= sc0;
+            o[nd][1] *= sc0;
+            o[nd][2] *= sc1;
+            o[nd][3] *= sc1;
+        }
+#pragma unroll
+        for (int kk = 0; kk < MMA_KT / 16; kk++) {
+            uint32_t pa[4];
+            pa[0] = pack_f16(s[2 * kk][0], s[2 * kk][1]);
+            pa[1] = pack_f16(s[2 * kk][2], s[2 * kk][3]);
+            pa[2] = pack_f16(s[2 * kk + 1][0], s[2 * kk + 1][1]);
+            pa[3] = pack_f16(s[2 * kk + 1][2], s[2 * kk + 1][3]);
+#pragma unroll
+            for (int np = 0; np < ND / 2; np++) { // V[16 keys][8 features] transposed, for feature groups 2 np and 2 np + 1
+                uint32_t b[4];
+                const uint32_t addr = (uint32_t)__cvta_generic_to_shared(&Vb[buf][kk * 16 + (lane & 15)][(2 * np + (lane >> 4)) * 8]);
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]) : "r"(addr));
+                mma_16816_f16(o[2 * np], pa, b[0], b[1]);
+                mma_16816_f16(o[2 * np + 1], pa, b[2], b[3]);
+            }
+        }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.f / l0, i1 = 1.f / l1;
+    // operand tile of (token tile, head): element (r, c) at (r >> 3) * 512 + (c >> 3) * 64 + (r & 7) * 8 + (c & 7)
+    const int64_t k_tiles = n_head;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int r = h ? r1 : r0;
+        if (r >= len) continue;
+        const int64_t row = t0 + r;
+        __half *tile = x_tiles + ((row >> 7) * k_tiles + head) * (int64_t)(128 * 64) + (int64_t)((row & 127) >> 3) * 512 + (row & 7) * 8 + tq * 2;
+        const float inv = h ? i1 : i0;
+#pragma unroll
+        for (int nd = 0; nd < ND; nd++) *reinterpret_cast<__half2 *>(tile + nd * 64) = __floats2half2_rn(o[nd][2 * h] * inv, o[nd][2 * h + 1] * inv);
+    }
+}
+
 // mean over the tokens of a sequence (bert.cpp: mul_mat with a vector of 1/N): one CTA per (sequence, 32 features),
 // 8 warps stride over the tokens; then x / sqrt(sum x^2) per sequence
 __global__ void __launch_bounds__(256) bert_mean_pool_kernel(const float *x, const int32_t *offs, int d, float *out) {
@@ -325,6 +476,14 @@ void launch_bert_embed_ln(float *x, const float *pos_embd, const float *type0, c
 void launch_bert_bias_residual_ln(float *x, const float *h, const float *bias, const float *w, const float *b, int n_tok, int d,
                                   float eps, cudaStream_t s) {
     bert_bias_residual_ln_kernel<<<n_tok, LN_THREADS, 0, s>>>(x, h, bias, w, b, d, eps);
+    g_launch_count++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void launch_bert_attention_f16(const void *q, const void *k, const void *v, const int32_t *offs, int n_seq, int max_len, int n_head,
+                               void *x_tiles, cudaStream_t s) {
+    const dim3 grid((max_len + MMA_QB - 1) / MMA_QB, n_head, n_seq);
+    bert_attention_f16_kernel<<<grid, MMA_THREADS, 0, s>>>((const __half *)q, (const __half *)k, (const __half *)v, offs, n_head, (__half *)x_tiles);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
 }

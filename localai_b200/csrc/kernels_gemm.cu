@@ -452,8 +452,9 @@ __device__ __forceinline__ void gm_tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) 
 
 struct GemmJobDev {             // one weight matrix of a launch: several matrices that share the activation
     const __half *b_tiles; // [n_tiles][k_tiles][256 x 64]   (wq|wk|wv, gate|up) run as ONE launch
-    float *out;
+    float *out;            // fp32 rows, or fp16 rows when GemmArgs::out_f16
     int64_t out_stride;
+    const float *bias;     // added to the fp16 rows (may be null)
     int N, n_tiles, nt0;          // nt0: first n-tile of this matrix in the launch's concatenated n-tile space
     int col0;                     // first column of this matrix in the split-K partial rows
 };
@@ -467,6 +468,7 @@ struct GemmArgs {
     // 1: silu(gate) * up over an interleaved gate|up matrix (columns c and c + 128 of a tile; K2 = N_total / 2),
     // 2: gelu(acc + bias[col]) (BERT feed-forward; K2 = N).  ksplit == 1 only.
     int epi_tiles;
+    int out_f16;           // plain epilogue: rows of fp16 (+ the matrix's bias) instead of fp32 -- BERT's q | k | v
     __half *x2_tiles;
     const float *bias;
     int M, N_total, k_tiles, m_tiles, n_tiles; // n_tiles: over all matrices
@@ -622,7 +624,26 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                 uint32_t r[32];
                 gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
                 const int col = (nt - J.nt0) * GM_BN + c0; // column inside this matrix
-                if (row < g.M && col < J.N) {
+                if (g.out_f16) {
+                    if (row < g.M && col < J.N) {
+                        __half *oh = (__half *)J.out + (int64_t)row * J.out_stride + col;
+                        const float *bj = J.bias ? J.bias + col : nullptr;
+                        if (col + 32 <= J.N) {
+#pragma unroll
+                            for (int j8 = 0; j8 < 4; j8++) {
+                                __half2 pk[4];
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    const int e = 8 * j8 + 2 * j;
+                                    pk[j] = gm_pack2(__uint_as_float(r[e]) + (bj ? bj[e] : 0.f), __uint_as_float(r[e + 1]) + (bj ? bj[e + 1] : 0.f));
+                                }
+                                *(int4 *)(oh + 8 * j8) = *(const int4 *)pk;
+                            }
+                        } else {
+                            for (int j = 0; j < 32 && col + j < J.N; j++) oh[j] = __float2half_rn(fminf(fmaxf(__uint_as_float(r[j]) + (bj ? bj[j] : 0.f), -65504.f), 65504.f));
+                        }
+                    }
+                } else if (row < g.M && col < J.N) {
                     float *o = g.ksplit > 1 ? g.partial + ((int64_t)ks * g.M + row) * g.N_total + J.col0 + col : J.out + (int64_t)row * J.out_stride + col;
                     const float *res = (g.residual && g.ksplit == 1) ? g.residual + (int64_t)row * g.res_stride + col : nullptr;
                     if (col + 32 <= J.N) {
@@ -717,8 +738,9 @@ void launch_gemm_dequant_w(const DTensor &W, void *w_tiles, cudaStream_t s) {
 }
 
 void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,
-                          float *splitk_scratch, size_t splitk_bytes, cudaStream_t s) {
+                          float *splitk_scratch, size_t splitk_bytes, cudaStream_t s, bool out_f16) {
     B2_CHECK(n_jobs >= 1 && n_jobs <= 3, B2_EINVAL, "gemm: 1 to 3 matrices per launch");
+    B2_CHECK(!out_f16 || !residual, B2_EINVAL, "gemm: fp16 rows carry a bias, not a residual");
     B2_CHECK(!residual || n_jobs == 1, B2_EINVAL, "gemm: the residual add needs a single matrix");
     const int64_t cols = jobs[0].W->cols;
     B2_CHECK(cols % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
@@ -736,20 +758,21 @@ void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, 
         B2_CHECK(W.cols == cols, B2_EINVAL, "gemm: matrices of one launch share K");
         if (!jobs[j].w_tiles_ready) launch_gemm_dequant_w(W, jobs[j].w_tiles, s); // quantised W -> fp16 tiles (unless kept resident)
         g.job[j].b_tiles = (const __half *)jobs[j].w_tiles;
-        g.job[j].out = jobs[j].out; g.job[j].out_stride = jobs[j].out_stride;
+        g.job[j].out = jobs[j].out; g.job[j].out_stride = jobs[j].out_stride; g.job[j].bias = jobs[j].bias;
+        B2_CHECK(!out_f16 || jobs[j].out_stride % 8 == 0, B2_EINVAL, "gemm: fp16 rows must be 16-byte aligned");
         g.job[j].N = (int)W.rows; g.job[j].n_tiles = (int)(align_up(W.rows, GM_BN) / GM_BN);
         g.job[j].nt0 = nt; g.job[j].col0 = col;
         nt += g.job[j].n_tiles; col += (int)W.rows;
         rows4 = rows4 && W.rows % 4 == 0;
     }
     g.residual = residual; g.res_stride = res_stride;
-    g.epi_tiles = 0; g.x2_tiles = nullptr; g.bias = nullptr;
+    g.epi_tiles = 0; g.out_f16 = out_f16 ? 1 : 0; g.x2_tiles = nullptr; g.bias = nullptr;
     g.M = n_tok; g.N_total = col; g.k_tiles = (int)(cols / GM_BK);
     g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = nt;
     g.lbo = lbo; g.sbo = sbo;
     g.ksplit = 1; g.k_per_split = g.k_tiles; g.partial = nullptr;
     const int tiles = g.m_tiles * g.n_tiles;
-    if (splitk_scratch && g.m_tiles == 1 && tiles <= 148 / 2 && rows4) { // at least 2 slices per tile or not worth a reduce pass
+    if (!out_f16 && splitk_scratch && g.m_tiles == 1 && tiles <= 148 / 2 && rows4) { // at least 2 slices per tile or not worth a reduce pass
         int ks = std::min(148 / tiles, g.k_tiles / 4);
         while (ks > 1 && (size_t)ks * n_tok * g.N_total * sizeof(float) > splitk_bytes) ks--;
         if (ks > 1) {

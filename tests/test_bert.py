@@ -136,6 +136,30 @@ def test_engine_embedding_request_on_a_bert_gguf(bert_files):
 
 
 @pytest.mark.gpu
+def test_fp16_attention_path_on_ragged_batches(bert_files, monkeypatch):
+    """heads of 64 and more than one token tile: q | k | v leave the projection GEMM as fp16 rows with their biases and
+    the attention kernel writes attn_output's operand tiles.  Against the restatement, and against the fp32-row path."""
+    ref = BertRef(bert_files["bert-mini"])
+    rng = np.random.default_rng(11)
+    seqs = [[2] + rng.integers(5, 2000, n - 2).tolist() + [3] for n in (512, 3, 129, 64, 200, 511, 65, 128, 17, 300)]
+    with capi.Bert(bert_files["bert-mini"]) as b:
+        batch = b.embed_batch(seqs)
+        for s, row in zip(seqs, batch):
+            want = ref.embed_tokens(s)
+            assert abs(np.linalg.norm(row) - 1.0) < 1e-5 and float(row @ want) >= 0.9995, (len(s), float(row @ want))
+        again = b.embed_batch(seqs)
+        assert np.array_equal(batch, again)
+        h = b.hidden(seqs[4])  # one text of 200 tokens: two token tiles, the same path
+        want = ref.embed_tokens(seqs[4], return_hidden=True)
+        err = np.abs(h - want)
+        assert err.max() <= 0.15 * want.std() and np.median(err) <= 0.012 * want.std()
+        monkeypatch.setenv("B200LLM_BERT_ATT_F32", "1")
+        other = b.embed_batch(seqs)
+        assert not np.array_equal(batch, other)  # another kernel, another rounding ...
+        assert np.abs(batch - other).max() <= 3e-3  # ... of the same numbers (unit vectors)
+
+
+@pytest.mark.gpu
 def test_single_text_graph_replay_equals_plain_launches(bert_files, monkeypatch):
     """one text per call: first call plain, second captures a CUDA graph for the 32-token length bucket, later ones
     replay it; padding rows must not leak into the vector"""
