@@ -240,7 +240,7 @@ def bench_tinyllama(args, rank, local_rank, world, ranks, peak):
 
 
 def bench_bert_extra(rank, local_rank, world, ranks):
-    """BASELINE configs[3]: BERT-base F16 embeddings of 512-token texts: 16 texts per call, and one text per call (the
+    """BASELINE configs[3]: BERT-base F16 embeddings of 512-token texts: 64 and 16 texts per call, and one text per call (the
     shape of the reference API, backend.proto:141)."""
     import numpy as np
 
@@ -264,7 +264,7 @@ def bench_bert_extra(rank, local_rank, world, ranks):
     out = {"metric": "BERT-base F16 embeddings seq/s (512-token texts)"}
     with capi.Bert(path, device=local_rank) as b:
         L = capi.lib()
-        for per_call, n_calls in ((16, 16), (1, 64)):
+        for per_call, n_calls in ((64, 8), (16, 16), (1, 64)):
             ids = np.ascontiguousarray(np.concatenate([np.concatenate([[2], rng.integers(5, 30000, n_tok - 2), [3]]) for _ in range(per_call)]), dtype=np.int32)
             offs = (np.arange(per_call + 1) * n_tok).astype(np.int32)
             vec = np.empty((per_call, b.n_embd), dtype=np.float32)

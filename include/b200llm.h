@@ -274,7 +274,7 @@ int b2_bert_tokenize(b2_bert *b, const char *text, size_t text_len, int32_t *out
 int b2_bert_embed_text(b2_bert *b, const char *text, size_t text_len, float *out, int cap);
 int b2_bert_embed_tokens(b2_bert *b, const int32_t *ids, int n_ids, float *out, int cap);
 /* several token sequences in one forward (no counterpart in the reference, whose API carries one text per call):
- * ids back to back, offsets[n_seq + 1]; out [n_seq][n_embd]; at most 8192 tokens per call */
+ * ids back to back, offsets[n_seq + 1]; out [n_seq][n_embd]; at most 32768 tokens per call */
 int b2_bert_embed_batch(b2_bert *b, const int32_t *ids, const int32_t *offsets, int n_seq, float *out);
 /* test hook: last hidden states [n_ids][n_embd] of one sequence */
 int b2_bert_hidden(b2_bert *b, const int32_t *ids, int n_ids, float *out);

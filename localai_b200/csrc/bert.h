@@ -58,7 +58,7 @@ class BertModel {
     int n_layer = 0, n_embd = 0, n_head = 0, head_dim = 0, n_ff = 0, n_ctx = 0, n_vocab = 0;
     float eps = 1e-12f;
     int64_t weight_bytes = 0;
-    static constexpr int MAX_TOKENS = 8192; // per forward (16 full-length sequences)
+    static constexpr int MAX_TOKENS = 32768; // per forward (64 full-length sequences; 1.5 GB of scratch for BERT-base)
 
   private:
     void *dalloc(size_t bytes);

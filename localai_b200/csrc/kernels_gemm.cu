@@ -27,7 +27,7 @@ constexpr int GM_STAGES = 4;
 constexpr int GM_A_BYTES = GM_BM * GM_BK * 2; // 16 KB
 constexpr int GM_B_BYTES = GM_BN * GM_BK * 2; // 32 KB
 constexpr int GM_STAGE_BYTES = GM_A_BYTES + GM_B_BYTES;
-constexpr int GM_THREADS = 256;
+constexpr int GM_THREADS = 384; // warp 0 producer, 1 MMA issuer, 2 TMEM allocation, 4 .. 11 epilogue (two per TMEM lane quarter)
 constexpr size_t GM_SMEM = (size_t)GM_STAGES * GM_STAGE_BYTES + 1024;
 
 // fp32 pair -> fp16 pair, saturated (an inf would poison a whole accumulator row; llama.cpp's CUDA path makes the same
@@ -514,7 +514,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < GM_STAGES; i++) { gm_mbar_init(full + i, 1); gm_mbar_init(empty + i, 1); }
-        for (int i = 0; i < 2; i++) { gm_mbar_init(tfull + i, 1); gm_mbar_init(tempty + i, 4); }
+        for (int i = 0; i < 2; i++) { gm_mbar_init(tfull + i, 1); gm_mbar_init(tempty + i, 8); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) { // TMEM: 512 columns = two 128 x 256 fp32 accumulators
@@ -576,6 +576,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
         }
     } else if (warp >= 4) { // ===== epilogue: TMEM -> registers -> global
         const int q = warp & 3; // TMEM lane quarter this warp may access
+        const int chalf = (warp - 4) >> 2; // ... and the half of the tile's columns it drains (the other warp of the quarter takes the rest)
         uint32_t acc_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
             const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
@@ -587,7 +588,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
             if (g.epi_tiles) { // activation fused, output = the next GEMM's operand tiles (every row of the tile is written: padding rows are zeros in, zeros out)
                 const int ncol = g.epi_tiles == 1 ? GM_BN / 2 : GM_BN;
                 const int64_t k2_tiles = (g.epi_tiles == 1 ? g.N_total / 2 : g.N_total) / GM_BK;
-                for (int c0 = 0; c0 < ncol; c0 += 32) {
+                for (int c0 = chalf * (ncol / 2); c0 < (chalf + 1) * (ncol / 2); c0 += 32) {
                     uint32_t r[32];
                     float v[32];
                     gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
@@ -620,7 +621,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                     }
                 }
             } else
-            for (int c0 = 0; c0 < GM_BN; c0 += 32) {
+            for (int c0 = chalf * (GM_BN / 2); c0 < (chalf + 1) * (GM_BN / 2); c0 += 32) {
                 uint32_t r[32];
                 gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
                 const int col = (nt - J.nt0) * GM_BN + c0; // column inside this matrix

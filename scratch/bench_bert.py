@@ -14,7 +14,7 @@ with capi.Bert(path) as b:
     seqs = [[2] + rng.integers(5, 300, 510).tolist() + [3] for _ in range(256)]
     import ctypes as C
     L = capi.lib()
-    for per_call in (1, 4, 16):
+    for per_call in (1, 16, 32, 64):
         calls = []
         for i in range(0, 256, per_call):  # host buffers ready, as a gRPC handler would hold them
             ss = seqs[i:i + per_call]
