@@ -382,7 +382,7 @@ def bench_tp70b(rank, world, ranks, peak, with_one_gpu=True):
 def run_bert(args, rank, local_rank, world, ranks, emit, warmup):
     """BASELINE config 4: BERT-base F16, texts of 512 WordPiece tokens, through b2_bert_embed_batch (host ids in, host
     vectors out -- the call is synchronous, so every timed step holds its own H2D and D2H copies).  A step = one call
-    with 16 sequences (8192 tokens, larger than nothing L2 could keep: activations of a step are 25-100 MB per tensor)."""
+    with 64 sequences (32768 tokens: the activations of a step are 100-400 MB per tensor, nothing the L2 could keep)."""
     import numpy as np
 
     sys.path.insert(0, os.path.join(ROOT, "tools"))
@@ -396,7 +396,7 @@ def run_bert(args, rank, local_rank, world, ranks, emit, warmup):
         mb.write_bert_gguf(path + ".tmp", mb.BERT_ARCHS["bert-base"], seed=0)
         os.replace(path + ".tmp", path)
     ranks.barrier()
-    per_call, n_tok = 16, 512
+    per_call, n_tok = 64, 512
     rng = np.random.default_rng(rank)
     b = capi.Bert(path, device=local_rank)
     ids = np.ascontiguousarray(np.concatenate([np.concatenate([[2], rng.integers(5, 300, n_tok - 2), [3]]) for _ in range(per_call)]), dtype=np.int32)
@@ -446,7 +446,7 @@ def run_bert(args, rank, local_rank, world, ranks, emit, warmup):
     emit({"metric": "BERT-base F16 embeddings seq/s (512-token texts)", "value": v, "unit": "seq/s", "n_gpus": world, "steps": args.steps,
           "warmup": warmup, "ms_per_step": dt * 1e3 / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
           "dtype": "fp16 GEMM operands (the file's F16 weights exactly), bf16 attention operands, f32 accumulate", "data": "synthetic",
-          "config": {"workload": "bert-base f16 random-init GGUF, 16 texts x 512 tokens per b2_bert_embed_batch call", "replicas": world,
+          "config": {"workload": "bert-base f16 random-init GGUF, 64 texts x 512 tokens per b2_bert_embed_batch call", "replicas": world,
                      "l2": "inputs larger than L2: a step moves 25-100 MB per activation tensor, 24 tensors per layer pass"},
           "e2e": {"value": v, "unit": "seq/s", "h2d_bytes_per_step": int(ids.nbytes + offs.nbytes), "d2h_bytes_per_step": int(out.nbytes),
                   "path": "b2_bert_embed_batch (host ids -> host vectors, synchronous); value is this same measurement"},

@@ -304,8 +304,23 @@ void BertModel::run_kernels(int T, int n_seq, int max_len) {
     launch_bert_embed_ln(x_, pos_embd_, type0_, pos_dev_, ln0_w_, ln0_b_, T, d, eps, s);
     // LayerNorm rows of up to 2048 features are produced together with their operand tiles (one pass over the row)
     const bool fused_ln = d <= 2048 && !(getenv("B200LLM_BERT_UNFUSED_LN") && atoi(getenv("B200LLM_BERT_UNFUSED_LN")) != 0);
+    // A/B switch, off: the projections back into the residual stream add their bias and the residual in the GEMM's epilogue, in
+    // place in x_, and the LayerNorm reads one fp32 row instead of two.  Measured slower (BERT-base, 64 x 512 tokens per call:
+    // 5.27 k against 5.84 k seq/s): these K = 768 GEMMs are bound by their epilogue, which the extra reads lengthen by more
+    // than the LayerNorm saves.
+    const bool fused_res = fused_ln && T > 128 && getenv("B200LLM_BERT_FUSED_RES") && atoi(getenv("B200LLM_BERT_FUSED_RES")) != 0;
+    auto to_residual = [&](const DTensor &W, void *tiles, const void *in_tiles, const float *bias) {
+        if (fused_res) {
+            const GemmJob j = {&W, tiles, true, x_, d, bias};
+            launch_gemm_tc_multi(&j, 1, in_tiles, T, x_, d, nullptr, 0, s);
+        } else {
+            launch_gemm_tc(W, in_tiles, T, h_, d, nullptr, 0, tiles, true, splitk_, splitk_bytes_, s);
+        }
+    };
     auto ln = [&](const float *bias, const float *w, const float *b) {
-        if (fused_ln) {
+        if (fused_res) {
+            launch_gemm_prepare_x_bias_residual_ln(x_, nullptr, nullptr, w, b, T, d, eps, x_tiles_, s);
+        } else if (fused_ln) {
             launch_gemm_prepare_x_bias_residual_ln(x_, h_, bias, w, b, T, d, eps, x_tiles_, s);
         } else {
             launch_bert_bias_residual_ln(x_, h_, bias, w, b, T, d, eps, s);
@@ -331,15 +346,15 @@ void BertModel::run_kernels(int T, int n_seq, int max_len) {
             launch_bert_attention(q_, k_, v_, L.bq, L.bk, L.bv, offs_dev_, n_seq, max_len, n_head, head_dim, att_, s);
             launch_gemm_prepare_x(att_, d, T, d, x_tiles_, s);
         }
-        launch_gemm_tc(L.wo, x_tiles_, T, h_, d, nullptr, 0, L.to, true, splitk_, splitk_bytes_, s);
+        to_residual(L.wo, L.to, x_tiles_, L.bo);
         ln(L.bo, L.ln1_w, L.ln1_b);
         if (fused_gelu) { // bias + GELU in the GEMM's epilogue, which writes the down projection's operand tiles
             launch_gemm_tc_bias_gelu(ff, d, L.tup, x_tiles_, T, L.bup, x2_tiles_, s);
-            launch_gemm_tc(L.down, x2_tiles_, T, h_, d, nullptr, 0, L.tdown, true, splitk_, splitk_bytes_, s);
+            to_residual(L.down, L.tdown, x2_tiles_, L.bdown);
         } else {
             launch_gemm_tc(L.up, x_tiles_, T, u_, ff, nullptr, 0, L.tup, true, splitk_, splitk_bytes_, s);
             launch_gemm_prepare_x_bias_gelu(u_, L.bup, T, ff, x_tiles_, s); // gelu(u + b) straight into the operand tiles
-            launch_gemm_tc(L.down, x_tiles_, T, h_, d, nullptr, 0, L.tdown, true, splitk_, splitk_bytes_, s);
+            to_residual(L.down, L.tdown, x_tiles_, L.bdown);
         }
         ln(L.bdown, L.ln2_w, L.ln2_b);
     }

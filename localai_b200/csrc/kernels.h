@@ -240,7 +240,7 @@ struct GemmJob {
     bool w_tiles_ready;
     float *out;
     int64_t out_stride;
-    const float *bias = nullptr; // with out_f16 only
+    const float *bias = nullptr; // added in the epilogue (such a launch is never split over K)
 };
 // out_f16: the outputs are rows of fp16 (out_stride in halves) with the matrices' biases added; never split over K
 void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, int n_tok, const float *residual, int64_t res_stride,

@@ -28,7 +28,8 @@ constexpr int GM_A_BYTES = GM_BM * GM_BK * 2; // 16 KB
 constexpr int GM_B_BYTES = GM_BN * GM_BK * 2; // 32 KB
 constexpr int GM_STAGE_BYTES = GM_A_BYTES + GM_B_BYTES;
 constexpr int GM_THREADS = 384; // warp 0 producer, 1 MMA issuer, 2 TMEM allocation, 4 .. 11 epilogue (two per TMEM lane quarter)
-constexpr size_t GM_SMEM = (size_t)GM_STAGES * GM_STAGE_BYTES + 1024;
+constexpr int GM_EPI_WARPS = 8;
+constexpr size_t GM_SMEM = (size_t)GM_STAGES * GM_STAGE_BYTES + 1024 + GM_EPI_WARPS * 4096; // ring, barriers, 4 KB of row staging per epilogue warp
 
 // fp32 pair -> fp16 pair, saturated (an inf would poison a whole accumulator row; llama.cpp's CUDA path makes the same
 // fp16 trade for these mat-muls)
@@ -213,10 +214,14 @@ bias_residual_ln_x_tiles_kernel(float *__restrict__ x, const float *__restrict__
         if (mine) {
             float *xr = x + (int64_t)r * cols + k0;
             const float *hr = h + (int64_t)r * cols + k0;
-            const float4 xa = *(const float4 *)xr, xb = *(const float4 *)(xr + 4), ha = *(const float4 *)hr, hb = *(const float4 *)(hr + 4);
-            const float4 ba = *(const float4 *)(bias + k0), bb = *(const float4 *)(bias + k0 + 4);
-            v[0] = xa.x + (ha.x + ba.x); v[1] = xa.y + (ha.y + ba.y); v[2] = xa.z + (ha.z + ba.z); v[3] = xa.w + (ha.w + ba.w);
-            v[4] = xb.x + (hb.x + bb.x); v[5] = xb.y + (hb.y + bb.y); v[6] = xb.z + (hb.z + bb.z); v[7] = xb.w + (hb.w + bb.w);
+            const float4 xa = *(const float4 *)xr, xb = *(const float4 *)(xr + 4);
+            v[0] = xa.x; v[1] = xa.y; v[2] = xa.z; v[3] = xa.w; v[4] = xb.x; v[5] = xb.y; v[6] = xb.z; v[7] = xb.w;
+            if (h) { // (h == nullptr: the producing GEMM's epilogue already added its output and bias into x)
+                const float4 ha = *(const float4 *)hr, hb = *(const float4 *)(hr + 4);
+                const float4 ba = *(const float4 *)(bias + k0), bb = *(const float4 *)(bias + k0 + 4);
+                v[0] = xa.x + (ha.x + ba.x); v[1] = xa.y + (ha.y + ba.y); v[2] = xa.z + (ha.z + ba.z); v[3] = xa.w + (ha.w + ba.w);
+                v[4] = xb.x + (hb.x + bb.x); v[5] = xb.y + (hb.y + bb.y); v[6] = xb.z + (hb.z + bb.z); v[7] = xb.w + (hb.w + bb.w);
+            }
 #pragma unroll
             for (int j = 0; j < 8; j++) s += v[j];
         }
@@ -284,10 +289,14 @@ bias_residual_ln_x_tiles_warp_kernel(float *__restrict__ x, const float *__restr
             const int64_t k0 = 256 * i + 8 * lane;
             if (k0 < cols) {
                 const float *xr = x + (int64_t)r * cols + k0, *hr = h + (int64_t)r * cols + k0;
-                const float4 xa = *(const float4 *)xr, xb = *(const float4 *)(xr + 4), ha = *(const float4 *)hr, hb = *(const float4 *)(hr + 4);
-                const float4 ba = *(const float4 *)(bias + k0), bb = *(const float4 *)(bias + k0 + 4);
-                v[i][0] = xa.x + (ha.x + ba.x); v[i][1] = xa.y + (ha.y + ba.y); v[i][2] = xa.z + (ha.z + ba.z); v[i][3] = xa.w + (ha.w + ba.w);
-                v[i][4] = xb.x + (hb.x + bb.x); v[i][5] = xb.y + (hb.y + bb.y); v[i][6] = xb.z + (hb.z + bb.z); v[i][7] = xb.w + (hb.w + bb.w);
+                const float4 xa = *(const float4 *)xr, xb = *(const float4 *)(xr + 4);
+                v[i][0] = xa.x; v[i][1] = xa.y; v[i][2] = xa.z; v[i][3] = xa.w; v[i][4] = xb.x; v[i][5] = xb.y; v[i][6] = xb.z; v[i][7] = xb.w;
+                if (h) { // (h == nullptr: the producing GEMM's epilogue already added its output and bias into x)
+                    const float4 ha = *(const float4 *)hr, hb = *(const float4 *)(hr + 4);
+                    const float4 ba = *(const float4 *)(bias + k0), bb = *(const float4 *)(bias + k0 + 4);
+                    v[i][0] = xa.x + (ha.x + ba.x); v[i][1] = xa.y + (ha.y + ba.y); v[i][2] = xa.z + (ha.z + ba.z); v[i][3] = xa.w + (ha.w + ba.w);
+                    v[i][4] = xb.x + (hb.x + bb.x); v[i][5] = xb.y + (hb.y + bb.y); v[i][6] = xb.z + (hb.z + bb.z); v[i][7] = xb.w + (hb.w + bb.w);
+                }
 #pragma unroll
                 for (int j = 0; j < 8; j++) s += v[i][j];
             }
@@ -577,6 +586,7 @@ gemm_tcgen05_kernel(const GemmArgs g) {
     } else if (warp >= 4) { // ===== epilogue: TMEM -> registers -> global
         const int q = warp & 3; // TMEM lane quarter this warp may access
         const int chalf = (warp - 4) >> 2; // ... and the half of the tile's columns it drains (the other warp of the quarter takes the rest)
+        float4 *stage4 = (float4 *)(gsm + (size_t)GM_STAGES * GM_STAGE_BYTES + 1024 + (size_t)(warp - 4) * 4096);
         uint32_t acc_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
             const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
@@ -622,46 +632,75 @@ gemm_tcgen05_kernel(const GemmArgs g) {
                 }
             } else
             for (int c0 = chalf * (GM_BN / 2); c0 < (chalf + 1) * (GM_BN / 2); c0 += 32) {
+                // A lane holds 32 columns of ONE row: stored like that, a warp's store touches 32 rows.  The 32 x 32 block goes
+                // through this warp's 4 KB of shared memory instead (16-byte chunks, chunk index xor row: no bank conflicts
+                // either way) and leaves as whole 128-byte row segments, four rows per instruction -- and the bias / residual
+                // are read the same way.
                 uint32_t r[32];
                 gm_tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * GM_BN + c0, r);
                 const int col = (nt - J.nt0) * GM_BN + c0; // column inside this matrix
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    stage4[lane * 8 + (j ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                                                      __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+                __syncwarp();
+                const int row_base = mt * GM_BM + q * 32;
                 if (g.out_f16) {
-                    if (row < g.M && col < J.N) {
-                        __half *oh = (__half *)J.out + (int64_t)row * J.out_stride + col;
-                        const float *bj = J.bias ? J.bias + col : nullptr;
-                        if (col + 32 <= J.N) {
+                    const int cc = (lane & 3) * 8; // 8 columns = 16 bytes of fp16 per lane, 8 rows per instruction
+                    const bool vec = J.out_stride % 8 == 0 && col + cc + 8 <= J.N;
 #pragma unroll
-                            for (int j8 = 0; j8 < 4; j8++) {
-                                __half2 pk[4];
+                    for (int i = 0; i < 4; i++) {
+                        const int rr = i * 8 + (lane >> 2), grow = row_base + rr;
+                        const float4 v0 = stage4[rr * 8 + ((2 * (lane & 3)) ^ (rr & 7))], v1 = stage4[rr * 8 + ((2 * (lane & 3) + 1) ^ (rr & 7))];
+                        float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+                        if (grow < g.M && col + cc < J.N) {
+                            __half *oh = (__half *)J.out + (int64_t)grow * J.out_stride + col + cc;
+                            if (J.bias) {
 #pragma unroll
-                                for (int j = 0; j < 4; j++) {
-                                    const int e = 8 * j8 + 2 * j;
-                                    pk[j] = gm_pack2(__uint_as_float(r[e]) + (bj ? bj[e] : 0.f), __uint_as_float(r[e + 1]) + (bj ? bj[e + 1] : 0.f));
-                                }
-                                *(int4 *)(oh + 8 * j8) = *(const int4 *)pk;
+                                for (int e = 0; e < 8; e++)
+                                    if (col + cc + e < J.N) v[e] += J.bias[col + cc + e];
                             }
-                        } else {
-                            for (int j = 0; j < 32 && col + j < J.N; j++) oh[j] = __float2half_rn(fminf(fmaxf(__uint_as_float(r[j]) + (bj ? bj[j] : 0.f), -65504.f), 65504.f));
+                            if (vec) {
+                                const __half2 pk[4] = {gm_pack2(v[0], v[1]), gm_pack2(v[2], v[3]), gm_pack2(v[4], v[5]), gm_pack2(v[6], v[7])};
+                                *(int4 *)oh = *(const int4 *)pk;
+                            } else {
+                                for (int e = 0; e < 8 && col + cc + e < J.N; e++) oh[e] = __float2half_rn(fminf(fmaxf(v[e], -65504.f), 65504.f));
+                            }
                         }
                     }
-                } else if (row < g.M && col < J.N) {
-                    float *o = g.ksplit > 1 ? g.partial + ((int64_t)ks * g.M + row) * g.N_total + J.col0 + col : J.out + (int64_t)row * J.out_stride + col;
-                    const float *res = (g.residual && g.ksplit == 1) ? g.residual + (int64_t)row * g.res_stride + col : nullptr;
-                    if (col + 32 <= J.N) {
+                } else {
+                    const int cc = (lane & 7) * 4; // 4 columns = 16 bytes of fp32 per lane, 4 rows per instruction
+                    const bool split = g.ksplit > 1;
+                    const int64_t ostride = split ? g.N_total : J.out_stride;
+                    float *obase = split ? g.partial + (int64_t)ks * g.M * g.N_total + J.col0 : J.out;
+                    const float *rbase = (g.residual && !split) ? g.residual : nullptr;
+                    const float *bj = (J.bias && !split) ? J.bias : nullptr;
+                    const bool vec = ((ostride | (split ? J.col0 : 0) | (rbase ? g.res_stride : 0)) % 4) == 0 && col + cc + 4 <= J.N;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                                   __uint_as_float(r[j + 3]));
-                            if (res) {
-                                const float4 rr = *(const float4 *)(res + j);
-                                v.x += rr.x; v.y += rr.y; v.z += rr.z; v.w += rr.w;
+                    for (int i = 0; i < 8; i++) {
+                        const int rr = i * 4 + (lane >> 3), grow = row_base + rr;
+                        float4 v = stage4[rr * 8 + ((lane & 7) ^ (rr & 7))];
+                        if (grow < g.M && col + cc < J.N) {
+                            float *o = obase + (int64_t)grow * ostride + col + cc;
+                            const float *res = rbase ? rbase + (int64_t)grow * g.res_stride + col + cc : nullptr;
+                            if (vec) {
+                                if (bj) {
+                                    const float4 bb = *(const float4 *)(bj + col + cc);
+                                    v.x += bb.x; v.y += bb.y; v.z += bb.z; v.w += bb.w;
+                                }
+                                if (res) {
+                                    const float4 rv = *(const float4 *)res;
+                                    v.x += rv.x; v.y += rv.y; v.z += rv.z; v.w += rv.w;
+                                }
+                                *(float4 *)o = v;
+                            } else {
+                                const float ve[4] = {v.x, v.y, v.z, v.w};
+                                for (int e = 0; e < 4 && col + cc + e < J.N; e++) o[e] = ve[e] + (bj ? bj[col + cc + e] : 0.f) + (res ? res[e] : 0.f);
                             }
-                            *(float4 *)(o + j) = v;
                         }
-                    } else {
-                        for (int j = 0; j < 32 && col + j < J.N; j++) o[j] = __uint_as_float(r[j]) + (res ? res[j] : 0.f);
                     }
                 }
+                __syncwarp(); // the block is out before the next one overwrites the staging rows
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
@@ -773,7 +812,9 @@ void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, 
     g.lbo = lbo; g.sbo = sbo;
     g.ksplit = 1; g.k_per_split = g.k_tiles; g.partial = nullptr;
     const int tiles = g.m_tiles * g.n_tiles;
-    if (!out_f16 && splitk_scratch && g.m_tiles == 1 && tiles <= 148 / 2 && rows4) { // at least 2 slices per tile or not worth a reduce pass
+    bool any_bias = false;
+    for (int j = 0; j < n_jobs; j++) any_bias = any_bias || jobs[j].bias;
+    if (!out_f16 && !any_bias && splitk_scratch && g.m_tiles == 1 && tiles <= 148 / 2 && rows4) { // at least 2 slices per tile or not worth a reduce pass
         int ks = std::min(148 / tiles, g.k_tiles / 4);
         while (ks > 1 && (size_t)ks * n_tok * g.N_total * sizeof(float) > splitk_bytes) ks--;
         if (ks > 1) {
