@@ -85,11 +85,13 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
     const int p_r0 = pos0 + r0, p_r1 = pos0 + r1; // absolute positions of this thread's two query rows
 
     const int n_tiles = (n_kv + FA_BK - 1) / FA_BK;
+    const float sl = scale * 1.4426950408889634f; // scores are kept in units of log2: p = exp2(s sl - max)
     load_tile(0, 0);
     for (int it = 0; it < n_tiles; it++) {
         const int buf = it & 1, j0 = it * FA_BK;
-        if (it + 1 < n_tiles) { load_tile(buf ^ 1, j0 + FA_BK); fa_wait<1>(); } else { fa_wait<0>(); }
-        __syncthreads();
+        fa_wait<0>();
+        __syncthreads(); // tile `it` is visible to everyone, and everyone is done with tile it - 1: its buffer may be refilled
+        if (it + 1 < n_tiles) load_tile(buf ^ 1, j0 + FA_BK);
         const __half *K = sK + (size_t)buf * FA_BK * LD, *V = sV + (size_t)buf * FA_BK * LD;
         if (j0 <= pos0 + q_lo + warp * 16 + 15) { // (a tile wholly after this warp's last query is masked out: nothing to add)
         // ---- S = Q K^T : 8 n-tiles of 8 keys
@@ -97,20 +99,27 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
 #pragma unroll
         for (int nt = 0; nt < FA_BK / 8; nt++) {
             s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
-            const __half *kr = K + (size_t)(nt * 8 + g) * LD + tq * 2; // B fragment: key (nt*8+g), dims k*16 + tq*2 (+8)
+            // B fragments of two k-steps per ldmatrix.x4: matrices (dims +0, +8) of k-step 2 kp and of 2 kp + 1, 8 keys each
+            const uint32_t kaddr = (uint32_t)__cvta_generic_to_shared(K + (size_t)(nt * 8 + (lane & 7)) * LD + (lane >> 3) * 8);
 #pragma unroll
-            for (int kc = 0; kc < HD / 16; kc++)
-                fa_mma(s[nt], qa[kc], *(const uint32_t *)(kr + kc * 16), *(const uint32_t *)(kr + kc * 16 + 8));
+            for (int kp = 0; kp < HD / 32; kp++) {
+                uint32_t b[4];
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3])
+                             : "r"(kaddr + kp * 64));
+                fa_mma(s[nt], qa[2 * kp], b[0], b[1]);
+                fa_mma(s[nt], qa[2 * kp + 1], b[2], b[3]);
+            }
         }
         // ---- scale, causal mask, online soft-max (rows r0: regs 0,1 ; r1: regs 2,3)
         float mx0 = m0, mx1 = m1;
 #pragma unroll
         for (int nt = 0; nt < FA_BK / 8; nt++) {
             const int j = j0 + nt * 8 + tq * 2;
-            s[nt][0] = (j <= p_r0) ? s[nt][0] * scale : -INFINITY;
-            s[nt][1] = (j + 1 <= p_r0) ? s[nt][1] * scale : -INFINITY;
-            s[nt][2] = (j <= p_r1) ? s[nt][2] * scale : -INFINITY;
-            s[nt][3] = (j + 1 <= p_r1) ? s[nt][3] * scale : -INFINITY;
+            s[nt][0] = (j <= p_r0) ? s[nt][0] * sl : -INFINITY;
+            s[nt][1] = (j + 1 <= p_r0) ? s[nt][1] * sl : -INFINITY;
+            s[nt][2] = (j <= p_r1) ? s[nt][2] * sl : -INFINITY;
+            s[nt][3] = (j + 1 <= p_r1) ? s[nt][3] * sl : -INFINITY;
             mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
             mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
         }
@@ -118,7 +127,8 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
         mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
         mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
         mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-        const float c0 = (m0 == -INFINITY) ? 0.f : expf(m0 - mx0), c1 = (m1 == -INFINITY) ? 0.f : expf(m1 - mx1);
+        // (position 0 is visible to every query, so after the first tile every maximum is finite: exp2(-inf - finite) = 0)
+        const float c0 = exp2f(m0 - mx0), c1 = exp2f(m1 - mx1);
         m0 = mx0;
         m1 = mx1;
         l0 *= c0;
@@ -128,8 +138,7 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
         uint32_t pa[FA_BK / 16][4];
 #pragma unroll
         for (int nt = 0; nt < FA_BK / 8; nt++) {
-            const float e0 = (mx0 == -INFINITY) ? 0.f : expf(s[nt][0] - mx0), e1 = (mx0 == -INFINITY) ? 0.f : expf(s[nt][1] - mx0);
-            const float e2 = (mx1 == -INFINITY) ? 0.f : expf(s[nt][2] - mx1), e3 = (mx1 == -INFINITY) ? 0.f : expf(s[nt][3] - mx1);
+            const float e0 = exp2f(s[nt][0] - mx0), e1 = exp2f(s[nt][1] - mx0), e2 = exp2f(s[nt][2] - mx1), e3 = exp2f(s[nt][3] - mx1);
             const __half2 h01 = __floats2half2_rn(e0, e1), h23 = __floats2half2_rn(e2, e3);
             // the row sums use the f16-rounded probabilities, i.e. exactly what multiplies V
             const float2 f01 = __half22float2(h01), f23 = __half22float2(h23);
@@ -141,18 +150,19 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
         // ---- O += P V : B fragments straight from the row-major V tile with ldmatrix.trans
 #pragma unroll
         for (int kc = 0; kc < FA_BK / 16; kc++) {
-            const __half *vr = V + (size_t)(kc * 16 + (lane & 15)) * LD;
+            // V[16 keys][8 dims] transposed, two groups of 8 dims per ldmatrix.x4 (lanes 16-31 name the rows of the second)
+            const uint32_t vaddr = (uint32_t)__cvta_generic_to_shared(V + (size_t)(kc * 16 + (lane & 15)) * LD + (lane >> 4) * 8);
 #pragma unroll
-            for (int dt = 0; dt < HD / 8; dt++) {
-                uint32_t b0, b1;
-                asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];"
-                             : "=r"(b0), "=r"(b1)
-                             : "r"((uint32_t)__cvta_generic_to_shared(vr + dt * 8)));
-                fa_mma(o[dt], pa[kc], b0, b1);
+            for (int dp = 0; dp < HD / 16; dp++) {
+                uint32_t b[4];
+                asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3])
+                             : "r"(vaddr + dp * 32));
+                fa_mma(o[2 * dp], pa[kc], b[0], b[1]);
+                fa_mma(o[2 * dp + 1], pa[kc], b[2], b[3]);
             }
         }
         }
-        __syncthreads(); // the other buffer is refilled at the top of the next iteration
     }
     // ---- normalise and write: rows r0 / r1, dims dt*8 + tq*2 (+1)
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
