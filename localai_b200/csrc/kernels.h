@@ -50,8 +50,9 @@ void launch_attention(const float *q, const int32_t *pos, const int32_t *slot, i
 // flash-style prefill attention (kernels_fattn.cu): tokens [t0, t0 + n_q) are one sequence (`slot`), token t0 + i at
 // position pos0 + i; their K/V must already be in the cache
 bool fattn_supported(int hd);
+// x_tiles != nullptr: the result goes into the next GEMM's fp16 operand tiles (rows t0 .. of the batch) instead of `out`
 void launch_fattn_prefill(const float *q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, int hd,
-                          const KVLayout &kv, float *out, cudaStream_t s);
+                          const KVLayout &kv, float *out, cudaStream_t s, void *x_tiles = nullptr);
 
 // --- fused decode mat-vec (kernels_fused.cu) -----------------------------------------------------------------
 enum { EPI_PLAIN = 0, EPI_SWIGLU = 1, EPI_QKV = 2 };

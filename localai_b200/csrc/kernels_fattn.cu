@@ -37,7 +37,7 @@ __device__ __forceinline__ uint32_t fa_pack(float lo, float hi) {
 template <int HD, int FA_BQ>
 __global__ void __launch_bounds__(FA_BQ * 2, FA_BQ == 64 ? FA_MINB : 1)
 fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, KVLayout kv,
-                     float *__restrict__ out, float scale) {
+                     float *__restrict__ out, float scale, __half *__restrict__ x_tiles) {
     constexpr int LD = HD + 8; // padded row (halves): conflict-free fragment loads
     constexpr int FA_THREADS = FA_BQ * 2;
     extern __shared__ __align__(16) __half fsm[];
@@ -170,6 +170,23 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
     const float i0 = 1.f / l0, i1 = 1.f / l1;
+    if (x_tiles) { // straight into attn_output's fp16 operand tiles ([token tile][k tile][128 x 64], core-matrix order; kernels_gemm.cu)
+        const int64_t k_tiles = (int64_t)n_head * HD / 64;
+#pragma unroll
+        for (int hh = 0; hh < 2; hh++) {
+            const int r = hh ? r1 : r0;
+            if (r >= n_q) continue;
+            const int64_t row = t0 + r;
+            const float inv = hh ? i1 : i0;
+            __half *tile_row = x_tiles + (row >> 7) * k_tiles * 8192 + (int64_t)((row & 127) >> 3) * 512 + (row & 7) * 8 + tq * 2;
+#pragma unroll
+            for (int dt = 0; dt < HD / 8; dt++) {
+                const int kc = h * (HD / 8) + dt; // 8-feature chunk index along K
+                *(__half2 *)(tile_row + (int64_t)(kc >> 3) * 8192 + (kc & 7) * 64) = __floats2half2_rn(o[dt][2 * hh] * inv, o[dt][2 * hh + 1] * inv);
+            }
+        }
+        return;
+    }
     if (r0 < n_q) {
         float *orow = out + ((int64_t)(t0 + r0) * n_head + h) * HD + tq * 2;
 #pragma unroll
@@ -185,7 +202,8 @@ fattn_prefill_kernel(const float *__restrict__ q, int t0, int n_q, int pos0, int
 bool fattn_supported(int hd) { return hd == 64 || hd == 128; }
 
 void launch_fattn_prefill(const float *q, int t0, int n_q, int pos0, int slot, int n_head, int n_head_kv, int hd,
-                          const KVLayout &kv, float *out, cudaStream_t s) {
+                          const KVLayout &kv, float *out, cudaStream_t s, void *x_tiles) {
+    __half *xt = (__half *)x_tiles;
     if (n_q <= 0) return;
     const float scale = 1.0f / sqrtf((float)hd);
     // 64 queries per CTA; 128 (8 warps: half the K / V tile traffic and barriers per query) measured slower on a 2048-token
@@ -200,11 +218,11 @@ void launch_fattn_prefill(const float *q, int t0, int n_q, int pos0, int slot, i
             B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             B2_CUDA(cudaFuncSetAttribute(fattn_prefill_kernel<128, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         });
-        if (bq == 128) fattn_prefill_kernel<128, 128><<<grid, 256, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
-        else fattn_prefill_kernel<128, 64><<<grid, 128, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+        if (bq == 128) fattn_prefill_kernel<128, 128><<<grid, 256, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale, xt);
+        else fattn_prefill_kernel<128, 64><<<grid, 128, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale, xt);
     } else if (hd == 64) {
-        if (bq == 128) fattn_prefill_kernel<64, 128><<<grid, 256, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
-        else fattn_prefill_kernel<64, 64><<<grid, 128, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale);
+        if (bq == 128) fattn_prefill_kernel<64, 128><<<grid, 256, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale, xt);
+        else fattn_prefill_kernel<64, 64><<<grid, 128, smem, s>>>(q, t0, n_q, pos0, slot, n_head, n_head_kv, kv, out, scale, xt);
     } else {
         throw Error(B2_EUNSUPPORTED, "flash prefill attention: head_dim must be 64 or 128");
     }

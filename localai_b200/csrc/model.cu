@@ -385,6 +385,18 @@ void Model::invalidate_acts() { invalidate(actq_valid_); }
 
 // attention over a batch: consecutive tokens of one sequence (a prompt chunk) go through the flash kernel, single decode
 // tokens through the per-token kernel
+// every run of the batch is long enough for the flash kernel: it writes attn_output's operand tiles itself
+bool Model::attention_to_tiles(const KVLayout &kv, int n, void *x_tiles) {
+    static const bool off = getenv("B200LLM_NO_ATT_TILES") && atoi(getenv("B200LLM_NO_ATT_TILES")) != 0;
+    if (off || runs_.empty() || !fattn_supported(hp.head_dim) || hp.n_embd % 64 != 0 || hp.n_head * hp.head_dim != hp.n_embd) return false;
+    for (const Run &r : runs_)
+        if (r.n < 16) return false;
+    (void)n;
+    for (const Run &r : runs_)
+        launch_fattn_prefill(q_, r.t0, r.n, r.pos0, r.slot, hp.n_head, hp.n_head_kv, hp.head_dim, kv, att_, stream, x_tiles);
+    return true;
+}
+
 void Model::attention(const KVLayout &kv, int n) {
     const int hd = hp.head_dim, d = hp.n_embd;
     if (runs_.empty()) {
@@ -586,8 +598,10 @@ void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
     }
     launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream, (const float *)L.bq.data,
                          (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox);
-    attention(kv, n);
-    launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
+    if (!attention_to_tiles(kv, n, gemm_x_)) {
+        attention(kv, n);
+        launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
+    }
     gemm(L.wo, n, x_, d, x_, d);
     launch_gemm_prepare_x_rmsnorm(x_, d, (const float *)L.ffn_norm.data, n, d, hp.rms_eps, gemm_x_, nullptr, stream);
     if (void *pt = resident_pair_tiles(L)) { // gate | up interleaved: SwiGLU in the GEMM's epilogue, which writes ffn_down's operand tiles

@@ -129,6 +129,7 @@ class Model {
     struct Run { int t0, n, pos0, slot; };
     std::vector<Run> runs_; // host view of the current batch (empty: inputs only on the device)
     void attention(const KVLayout &kv, int n);
+    bool attention_to_tiles(const KVLayout &kv, int n, void *x_tiles);
     void run_layer_gemm(const LayerW &L, const KVLayout &kv, int n);
     void gemm(const DTensor &W, int n, float *out, int64_t out_stride, const float *residual, int64_t res_stride, const void *x_tiles = nullptr);
     void *resident_pair_tiles(const LayerW &L);
