@@ -94,9 +94,10 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
     else gemm_min_tokens_ = -1; // automatic, see gemm_threshold()
 
     hp.arch = f.get_s("general.architecture", "");
-    B2_CHECK(hp.arch == "llama" || hp.arch == "qwen2", B2_EUNSUPPORTED,
-             "unsupported architecture '" + hp.arch + "' (llama and qwen2 GGUFs)");
-    hp.rope_neox = hp.arch == "qwen2"; // llama.cpp llama_rope_type: NEOX pairs (i, i + head_dim / 2)
+    B2_CHECK(hp.arch == "llama" || hp.arch == "qwen2" || hp.arch == "phi3", B2_EUNSUPPORTED,
+             "unsupported architecture '" + hp.arch + "' (llama, qwen2 and phi3 GGUFs)");
+    hp.rope_neox = hp.arch == "qwen2" || hp.arch == "phi3"; // llama.cpp llama_rope_type: NEOX pairs (i, i + head_dim / 2)
+    const bool fused_qkv = hp.arch == "phi3"; // attn_qkv.weight = [q; k; v] rows, ffn_up.weight = [gate; up] rows
     hp.name = f.get_s("general.name", "");
     const std::string a = hp.arch + ".";
     hp.n_layer = (int)f.get_u(a + "block_count", 0);
@@ -167,9 +168,15 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
         const std::string p = "blk." + std::to_string(l) + ".";
         LayerW &L = layers[l];
         L.attn_norm = upload(f, p + "attn_norm.weight", 1, d, true);
-        L.wq = upload(f, p + "attn_q.weight", d, d, true, (int64_t)r * dq_l, dq_l);
-        L.wk = upload(f, p + "attn_k.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
-        L.wv = upload(f, p + "attn_v.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
+        if (fused_qkv) { // rows are contiguous in the file: the three projections are row ranges of the one tensor
+            L.wq = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, 0, d);
+            L.wk = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, d, kvd);
+            L.wv = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, d + kvd, kvd);
+        } else {
+            L.wq = upload(f, p + "attn_q.weight", d, d, true, (int64_t)r * dq_l, dq_l);
+            L.wk = upload(f, p + "attn_k.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
+            L.wv = upload(f, p + "attn_v.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
+        }
         L.wo = upload(f, p + "attn_output.weight", d, d, true, 0, -1, (int64_t)r * dq_l, dq_l);
         if (f.tensor(p + "attn_q.bias")) { // qwen2: biases of the three projections (F32 rows)
             B2_CHECK(tp_size == 1, B2_EUNSUPPORTED, "tensor-parallel loading of models with QKV biases is not built");
@@ -180,10 +187,24 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
             qkv_bias_ = true;
         }
         L.ffn_norm = upload(f, p + "ffn_norm.weight", 1, d, true);
-        L.gate = upload(f, p + "ffn_gate.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
-        L.up = upload(f, p + "ffn_up.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
+        if (fused_qkv) { // llama.cpp build_phi3 / LLM_FFN_SWIGLU on one tensor: silu(first half) * second half
+            L.gate = upload(f, p + "ffn_up.weight", 2 * (int64_t)ff, d, true, 0, ff);
+            L.up = upload(f, p + "ffn_up.weight", 2 * (int64_t)ff, d, true, ff, ff);
+        } else {
+            L.gate = upload(f, p + "ffn_gate.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
+            L.up = upload(f, p + "ffn_up.weight", ff, d, true, (int64_t)r * ff_l, ff_l);
+        }
         L.down = upload(f, p + "ffn_down.weight", d, ff, true, 0, -1, (int64_t)r * ff_l, ff_l);
         B2_CHECK(L.attn_norm.type == B2_T_F32 && L.ffn_norm.type == B2_T_F32, B2_EUNSUPPORTED, "norm weights must be F32");
+    }
+    if (fused_qkv) {
+        // the long-context variants carry per-dimension frequency factors chosen by context length, and the model attends
+        // through a sliding window beyond phi3.attention.sliding_window positions: neither is built
+        B2_CHECK(!f.tensor("rope_factors_long.weight") && !f.tensor("rope_factors_short.weight"), B2_EUNSUPPORTED,
+                 "phi3: long-context rope factors (rope_factors_long / _short) are not supported");
+        const int64_t window = (int64_t)f.get_u(a + "attention.sliding_window", 0);
+        B2_CHECK(window <= 0 || n_ctx_slot <= window, B2_EUNSUPPORTED,
+                 "phi3: contexts beyond the model's sliding window (" + std::to_string(window) + " positions per slot) are not supported");
     }
     if (qkv_bias_ || hp.rope_neox) {
         // Biases and NEOX rotary pairs live in rope_kv_store_kernel only: such models take the per-operator kernels for small

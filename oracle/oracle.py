@@ -173,7 +173,7 @@ class OracleModel:
                                                    C.c_float, C.c_float, C.c_void_p]
             L.ref_ctx_set_rope_scaling(self.ctx, self.rope_freq_scale, self.rope_ext_factor, yarn_attn_factor or 1.0, n_ctx_orig,
                                        yarn_beta_fast or 32.0, yarn_beta_slow or 1.0, ff.ctypes.data if ff is not None else None)
-        if self.arch == "qwen2":  # LLAMA_ROPE_TYPE_NEOX (llama.cpp llama_rope_type)
+        if self.arch in ("qwen2", "phi3"):  # LLAMA_ROPE_TYPE_NEOX (llama.cpp llama_rope_type)
             L.ref_ctx_set_rope_neox.argtypes = [C.c_void_p, C.c_int]
             L.ref_ctx_set_rope_neox(self.ctx, 1)
         for name, t in self.tensors.items():
@@ -193,6 +193,16 @@ class OracleModel:
                 L.ref_ctx_set_tensor(self.ctx, _GLOBAL_TENSORS[base], 0, _ptr(data), int(t.tensor_type), rows, cols)
             elif base.startswith("blk."):
                 _, il, nm = base.split(".", 2)
+                if self.arch == "phi3" and nm in ("attn_qkv", "ffn_up"):
+                    # phi3 stores [q; k; v] and [gate; up] as the rows of one tensor each (llama.cpp build_phi3 takes
+                    # views of the product; rows are contiguous, so the slices are byte ranges)
+                    rb = data.size // rows
+                    kvd = self.n_head_kv * (self.n_embd // self.n_head)
+                    parts = ([(TK_WQ, 0, self.n_embd), (TK_WK, self.n_embd, kvd), (TK_WV, self.n_embd + kvd, kvd)] if nm == "attn_qkv"
+                             else [(TK_GATE, 0, rows // 2), (TK_UP, rows // 2, rows // 2)])
+                    for kind, r0, nr in parts:
+                        L.ref_ctx_set_tensor(self.ctx, kind, int(il), _ptr(data[r0 * rb:]), int(t.tensor_type), nr, cols)
+                    continue
                 if nm in _LAYER_TENSORS:
                     L.ref_ctx_set_tensor(self.ctx, _LAYER_TENSORS[nm], int(il), _ptr(data), int(t.tensor_type), rows,
                                          cols)

@@ -49,6 +49,7 @@ def model_files(gguf_dir):
         "micro_l31": ("micro-l31", "mixed"),
         "micro_g8": ("micro-g8", "q4_k_m"),  # 8 query heads per KV head
         "mini_qwen2": ("mini-qwen2", "q4_k_m"),  # qwen2: QKV biases, NEOX rotary pairs, its own pre-tokeniser
+        "mini_phi3": ("mini-phi3", "q4_k_m"),  # phi3: fused attn_qkv and gate|up tensors, NEOX rotary pairs
     }
     out = {}
     for name, (arch, preset) in specs.items():

@@ -50,6 +50,15 @@ def test_vocab_only_reads_metadata(model_files):
             e.submit("hi")
 
 
+def test_other_architectures_are_recognised(model_files):
+    """qwen2 and phi3 GGUFs load (metadata keys carry the architecture's prefix; phi3 has no ffn_gate / attn_q tensors)"""
+    for name, arch, tok in (("mini_qwen2", b"qwen2", b"gpt2"), ("mini_phi3", b"phi3", b"llama")):
+        with capi.Engine(model_files[name], vocab_only=True) as e:
+            i = e.info
+            assert i.arch == arch and i.tokenizer_model == tok
+            assert (i.n_layer, i.n_embd, i.n_head, i.n_head_kv, i.n_ff) == (3, 512, 8, 2, 1024)
+
+
 def test_bad_files_are_rejected(tmp_path):
     p = tmp_path / "junk.gguf"
     p.write_bytes(b"not a gguf file at all, definitely" * 4)

@@ -162,10 +162,10 @@ def test_oracle_matches_transformers():
     r = X.measure()
     gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "transformers_crosscheck.json")))
     assert set(r) == set(gold)
-    for k in ("llama_mini_f16", "qwen2_mini_f16"):  # qwen2: Qwen2ForCausalLM -- QKV biases, rotate-half RoPE on un-permuted weights
+    for k in ("llama_mini_f16", "qwen2_mini_f16", "phi3_mini_f16"):  # Qwen2ForCausalLM (QKV biases, rotate-half RoPE on un-permuted weights), Phi3ForCausalLM (fused qkv | gate_up)
         f16 = r[k]
         assert f16["rel_to_max"] <= 1e-3 and f16["argmax_agree"] == f16["n_tokens"], (k, f16)
-    for k in ("llama_mini_q4_k_m", "llama_mini_q8_0", "qwen2_mini_q4_k_m"):
+    for k in ("llama_mini_q4_k_m", "llama_mini_q8_0", "qwen2_mini_q4_k_m", "phi3_mini_q4_k_m"):
         q = r[k]
         assert q["max_err_sigma"] <= 0.25 and q["median_err_sigma"] <= 0.03 and q["argmax_agree"] == q["n_tokens"], (k, q)
     assert r["bert_mini_f16"]["max_err_sigma"] <= 1e-4, r["bert_mini_f16"]

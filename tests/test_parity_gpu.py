@@ -195,7 +195,8 @@ def test_mul_mat_linearity_in_rows():
 MODELS = ["micro_mixed", "micro_q8_0", "mini_q4_k_m", "mini_q5_k", "mini_f16", "mini_q4_0", "mini_q5_1", "mini_q2_k", "mini_q3_k", "mini_iq4_nl", "mini_iq4_xs",
           "micro_linear", "micro_yarn", "micro_l31",  # RoPE scaling (linear, YaRN, rope_freqs.weight divisors)
           "micro_g8",                                 # 8 query heads per KV head
-          "mini_qwen2"]                               # qwen2 architecture (QKV biases, NEOX rotary pairs)
+          "mini_qwen2",                               # qwen2 architecture (QKV biases, NEOX rotary pairs)
+          "mini_phi3"]                                # phi3 architecture (fused attn_qkv / gate|up tensors, NEOX rotary pairs)
 
 
 @pytest.mark.parametrize("name", MODELS)

@@ -36,6 +36,10 @@ def hf_llama_logits(path: str, ids) -> np.ndarray:
         from transformers import Qwen2Config, Qwen2ForCausalLM
 
         model = Qwen2ForCausalLM(Qwen2Config(**{k: v for k, v in cfg.items() if k != "model_type"})).to(torch.float32).eval()
+    elif cfg.get("model_type") == "phi3":  # fused qkv_proj / gate_up_proj tensors, rotate-half RoPE
+        from transformers import Phi3Config, Phi3ForCausalLM
+
+        model = Phi3ForCausalLM(Phi3Config(**{k: v for k, v in cfg.items() if k != "model_type"}, pad_token_id=0)).to(torch.float32).eval()
     else:
         model = LlamaForCausalLM(LlamaConfig(**{k: v for k, v in cfg.items() if k != "model_type"})).to(torch.float32).eval()
     tensors = load_gguf_checkpoint(path, return_tensors=True, model_to_load=model)["tensors"]
@@ -92,19 +96,20 @@ def measure() -> dict:
     res = {}
     rng = np.random.default_rng(5)
     with tempfile.TemporaryDirectory() as td:
-        for arch, preset in (("mini", "f16"), ("mini", "q4_k_m"), ("mini", "q8_0"), ("mini-qwen2", "f16"), ("mini-qwen2", "q4_k_m")):
+        for arch, preset in (("mini", "f16"), ("mini", "q4_k_m"), ("mini", "q8_0"), ("mini-qwen2", "f16"), ("mini-qwen2", "q4_k_m"),
+                             ("mini-phi3", "f16"), ("mini-phi3", "q4_k_m")):
             path = os.path.join(td, f"{arch}_{preset}.gguf")
             try:
                 mg.write_gguf(path, mg.ARCHS[arch], preset, seed=7, quiet=True)
             except Exception as ex:  # preset not defined for this arch
-                res[f"llama_{arch}_{preset}".replace("llama_mini-qwen2", "qwen2_mini")] = {"skipped": str(ex)}
+                res[f"llama_{arch}_{preset}".replace("llama_mini-qwen2", "qwen2_mini").replace("llama_mini-phi3", "phi3_mini")] = {"skipped": str(ex)}
                 continue
             ids = rng.integers(0, 4000, 32)
             want = hf_llama_logits(path, ids)
             got = O.OracleModel(path, n_ctx=64).eval(ids, logits_all=True)
             sig = float(want.std())
             err = np.abs(got - want)
-            res[f"llama_{arch}_{preset}".replace("llama_mini-qwen2", "qwen2_mini")] = {
+            res[f"llama_{arch}_{preset}".replace("llama_mini-qwen2", "qwen2_mini").replace("llama_mini-phi3", "phi3_mini")] = {
                 "n_tokens": int(len(ids)), "sigma_logits": sig, "max_err_sigma": float(err.max() / sig),
                 "median_err_sigma": float(np.median(err) / sig), "rel_to_max": float(err.max() / np.abs(want).max()),
                 "argmax_agree": int((got.argmax(-1) == want.argmax(-1)).sum())}

@@ -67,6 +67,7 @@ class Arch:
     rope_freqs: bool = False     # write rope_freqs.weight (per-dimension frequency divisors, the Llama-3.1 scheme)
     gguf_arch: str = "llama"     # general.architecture and the prefix of the hyper-parameter keys ("llama" | "qwen2")
     qkv_bias: bool = False       # attn_q/k/v.bias tensors (qwen2)
+    fused_qkv: bool = False      # phi3: attn_qkv.weight = [q; k; v] rows, ffn_up.weight = [gate; up] rows, no ffn_gate
     head_dim: int = field(init=False)
 
     def __post_init__(self):
@@ -84,6 +85,8 @@ ARCHS = {
     "micro-l31": Arch("micro-l31", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "none", 1.0, 0, True),
     # qwen2: QKV biases, NEOX rotary pairs (i, i + head_dim / 2), its own BPE pre-tokeniser (digits one at a time)
     "mini-qwen2": Arch("mini-qwen2", 3, 512, 8, 2, 1024, 4608, 1024, 1000000.0, 1e-6, "bpe", False, "none", 1.0, 0, False, "qwen2", True),
+    # phi3: fused attn_qkv and gate|up tensors, NEOX rotary pairs, SentencePiece vocabulary, no biases
+    "mini-phi3": Arch("mini-phi3", 3, 512, 8, 2, 1024, 4352, 1024, 10000.0, 1e-5, "spm", False, "none", 1.0, 0, False, "phi3", False, True),
     "micro-g8": Arch("micro-g8", 2, 512, 8, 1, 1024, 4352, 512, 10000.0, 1e-5, "spm"),  # 8 query heads per KV head (the 70B grouping), head_dim 64
     "mini-70b": Arch("mini-70b", 4, 2048, 16, 8, 4096, 8192, 1024, 500000.0, 1e-5, "bpe", True),  # 70B type mix (Q5_K attn_v), 8 KV heads; shards 2 / 4 / 8 ways
     # BASELINE.json configs
@@ -438,11 +441,17 @@ def tensor_plan(arch: Arch, preset: str, gain_out: float):
     plan = [("token_embd.weight", arch.n_vocab, d, tensor_type(preset, arch, "token_embd.weight", 0), 1.0, False)]
     for i in range(arch.n_layer):
         p = f"blk.{i}."
-        for nm, rows, cols in [
+        names = [
             ("attn_norm.weight", 1, d), ("attn_q.weight", d, d), ("attn_k.weight", kvd, d),
             ("attn_v.weight", kvd, d), ("attn_output.weight", d, d), ("ffn_norm.weight", 1, d),
             ("ffn_gate.weight", ff, d), ("ffn_up.weight", ff, d), ("ffn_down.weight", d, ff),
-        ]:
+        ]
+        if arch.fused_qkv:
+            names = [
+                ("attn_norm.weight", 1, d), ("attn_qkv.weight", d + 2 * kvd, d), ("attn_output.weight", d, d),
+                ("ffn_norm.weight", 1, d), ("ffn_up.weight", 2 * ff, d), ("ffn_down.weight", d, ff),
+            ]
+        for nm, rows, cols in names:
             t = tensor_type(preset, arch, p + nm, i)
             norm = nm.endswith("_norm.weight")
             plan.append((p + nm, rows, cols, t, 0.0 if norm else 1.0 / np.sqrt(cols), norm))
