@@ -85,6 +85,7 @@ struct FusedGemv {
     const float *rope_table = nullptr;
     KVLayout kv{};
     int hd = 0;
+    const float *qkv_bias[3] = {nullptr, nullptr, nullptr}; // added to q / k / v before the rotation (qwen2)
     // filled by the launcher
     int64_t xrb = 0;
     int n_tasks = 0;

@@ -108,7 +108,7 @@ fused_gemv_kernel(const FusedGemv a) {
         rows2_dot<LdGlobal, 2, NT>(a.job[jb].type, r0, r1, K, 0, 1, xs, a.xrb, lane, acc);
 #pragma unroll
         for (int t = 0; t < NT; t++) {
-            const float v0 = warp_sum(acc[0][t]), v1 = warp_sum(acc[1][t]);
+            float v0 = warp_sum(acc[0][t]), v1 = warp_sum(acc[1][t]);
             if (lane != 0) continue;
             if (a.epi == EPI_PLAIN) {
                 float *o = a.out + (int64_t)t * a.out_stride + r_local;
@@ -119,6 +119,10 @@ fused_gemv_kernel(const FusedGemv a) {
                 const float s = __fdiv_rn(v0, __fadd_rn(1.0f, expf(-v0)));
                 a.out[(int64_t)t * a.out_stride + r_local] = __fmul_rn(s, v1);
             } else { // EPI_QKV: jb 0 = q, 1 = k, 2 = v; (r_local, r_local + 1) is a rotary pair inside one head
+                if (const float *bj = a.qkv_bias[jb]) { // ggml_add after the mat-mul, before the rotation
+                    v0 = __fadd_rn(v0, bj[r_local]);
+                    v1 = __fadd_rn(v1, bj[r_local + 1]);
+                }
                 const int pos = a.pos[t], sl = a.slot[t];
                 const int page = a.kv.page_table[(int64_t)sl * a.kv.max_pages + pos / a.kv.page_size];
                 const int64_t cell = ((int64_t)page * a.kv.page_size + pos % a.kv.page_size) * a.kv.kvd;

@@ -19,7 +19,7 @@ void *Model::dalloc(size_t bytes) {
 }
 
 DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required,
-                      int64_t row0, int64_t nrows, int64_t col0, int64_t ncols) {
+                      int64_t row0, int64_t nrows, int64_t col0, int64_t ncols, int pair_heads) {
     const GGUFTensorInfo *ti = f.tensor(name);
     if (!ti) {
         B2_CHECK(!required, B2_EIO, "gguf: missing tensor " + name);
@@ -56,6 +56,22 @@ DTensor Model::upload(const GGUFFile &f, const std::string &name, int64_t want_r
         B2_CUDA(cudaMalloc((void **)&staging_, staging_bytes_));
     }
     const uint8_t *src = ti->data + row0 * row_bytes_all;
+    std::vector<uint8_t> shuffled;
+    if (pair_heads > 0) {
+        // NEOX rotary pairs (i, i + h/2) of every head become neighbours (2i, 2i + 1): the rotation the llama kernels apply to
+        // neighbouring rows is then the architecture's own, on the same numbers, and q . k does not care in which order its
+        // dimensions are summed as long as q and k agree (llama.cpp's converter does the same to HF llama checkpoints).
+        // A row is a byte range whatever the quantisation, so this is a copy of rows.
+        B2_CHECK(cols == cols_all && rows % pair_heads == 0 && pair_heads % 2 == 0, B2_EINVAL, "tensor " + name + ": cannot interleave the rows of its heads");
+        shuffled.resize(n_bytes);
+        const int64_t half = pair_heads / 2;
+        for (int64_t j = 0; j < rows; j++) {
+            const int64_t h0 = j / pair_heads * pair_heads, i = j % pair_heads;
+            const int64_t from = h0 + (i & 1 ? i / 2 + half : i / 2);
+            memcpy(shuffled.data() + j * row_bytes, src + from * row_bytes, (size_t)row_bytes);
+        }
+        src = shuffled.data();
+    }
     if (cols == cols_all) { // whole rows: one contiguous range of the file
         B2_CUDA(cudaMemcpyAsync(staging_, src, n_bytes, cudaMemcpyHostToDevice, stream));
     } else { // a K-slice: the blocks [col0 / be, (col0 + cols) / be) of every row
@@ -98,6 +114,7 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
              "unsupported architecture '" + hp.arch + "' (llama, qwen2 and phi3 GGUFs)");
     hp.rope_neox = hp.arch == "qwen2" || hp.arch == "phi3"; // llama.cpp llama_rope_type: NEOX pairs (i, i + head_dim / 2)
     const bool fused_qkv = hp.arch == "phi3"; // attn_qkv.weight = [q; k; v] rows, ffn_up.weight = [gate; up] rows
+    hp.rope_neox_kernel = hp.rope_neox && getenv("B200LLM_NEOX_KERNEL") && atoi(getenv("B200LLM_NEOX_KERNEL")) != 0;
     hp.name = f.get_s("general.name", "");
     const std::string a = hp.arch + ".";
     hp.n_layer = (int)f.get_u(a + "block_count", 0);
@@ -168,13 +185,16 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
         const std::string p = "blk." + std::to_string(l) + ".";
         LayerW &L = layers[l];
         L.attn_norm = upload(f, p + "attn_norm.weight", 1, d, true);
+        // NEOX architectures: the rows of wq / wk (and their biases) are interleaved per head, after which the model is a
+        // llama model to every kernel (see upload)
+        const int pair = (hp.rope_neox && !hp.rope_neox_kernel) ? hp.head_dim : 0;
         if (fused_qkv) { // rows are contiguous in the file: the three projections are row ranges of the one tensor
-            L.wq = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, 0, d);
-            L.wk = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, d, kvd);
+            L.wq = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, 0, d, 0, -1, pair);
+            L.wk = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, d, kvd, 0, -1, pair);
             L.wv = upload(f, p + "attn_qkv.weight", d + 2 * kvd, d, true, d + kvd, kvd);
         } else {
-            L.wq = upload(f, p + "attn_q.weight", d, d, true, (int64_t)r * dq_l, dq_l);
-            L.wk = upload(f, p + "attn_k.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
+            L.wq = upload(f, p + "attn_q.weight", d, d, true, (int64_t)r * dq_l, dq_l, 0, -1, pair);
+            L.wk = upload(f, p + "attn_k.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l, 0, -1, pair);
             L.wv = upload(f, p + "attn_v.weight", kvd, d, true, (int64_t)r * kvd_l, kvd_l);
         }
         L.wo = upload(f, p + "attn_output.weight", d, d, true, 0, -1, (int64_t)r * dq_l, dq_l);
@@ -185,6 +205,18 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
             L.bv = upload(f, p + "attn_v.bias", 1, kvd, true);
             B2_CHECK(L.bq.type == B2_T_F32 && L.bk.type == B2_T_F32 && L.bv.type == B2_T_F32, B2_EUNSUPPORTED, "QKV biases must be F32");
             qkv_bias_ = true;
+            if (pair > 0) { // the biases of q and k follow their rows
+                for (const auto &nb : {std::make_pair("attn_q.bias", &L.bq), std::make_pair("attn_k.bias", &L.bk)}) {
+                    const float *src = (const float *)f.tensor(p + nb.first)->data;
+                    const int64_t n = nb.second->cols, half = pair / 2;
+                    std::vector<float> v((size_t)n);
+                    for (int64_t j = 0; j < n; j++) {
+                        const int64_t h0 = j / pair * pair, i = j % pair;
+                        v[(size_t)j] = src[h0 + (i & 1 ? i / 2 + half : i / 2)];
+                    }
+                    B2_CUDA(cudaMemcpy((void *)nb.second->data, v.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
+                }
+            }
         }
         L.ffn_norm = upload(f, p + "ffn_norm.weight", 1, d, true);
         if (fused_qkv) { // llama.cpp build_phi3 / LLM_FFN_SWIGLU on one tensor: silu(first half) * second half
@@ -206,10 +238,12 @@ Model::Model(const GGUFFile &f, const b2_load_opts &o, int tp_rank_arg, int tp_s
         B2_CHECK(window <= 0 || n_ctx_slot <= window, B2_EUNSUPPORTED,
                  "phi3: contexts beyond the model's sliding window (" + std::to_string(window) + " positions per slot) are not supported");
     }
-    if (qkv_bias_ || hp.rope_neox) {
-        // Biases and NEOX rotary pairs live in rope_kv_store_kernel only: such models take the per-operator kernels for small
-        // batches (no persistent decode kernel, no fused QKV epilogue, no fused decode attention); the GEMM paths are shared.
-        B2_CHECK(tp_size == 1, B2_EUNSUPPORTED, "tensor-parallel loading is built for the llama architecture only");
+    B2_CHECK(tp_size == 1 || hp.arch == "llama", B2_EUNSUPPORTED, "tensor-parallel loading is built for the llama architecture only");
+    if (qkv_bias_) { // the biases are added by rope_kv_store_kernel and by the fused mat-vec's QKV epilogue: no persistent decode
+        no_mega_ = true; // kernel, no fused RoPE + attention kernel for such models; everything else is shared
+        no_fused_att_ = true;
+    }
+    if (hp.rope_neox_kernel) { // A/B switch: NEOX pairs rotated by rope_kv_store_kernel on un-interleaved rows, per-operator path only
         no_mega_ = true;
         unfused_ = true;
         no_fused_att_ = true;
@@ -446,7 +480,7 @@ void Model::run_layer_unfused(const LayerW &L, const KVLayout &kv, int n) {
     matmul(L.wk, xn_, d, n, k_, kvd, nullptr, 0);
     matmul(L.wv, xn_, d, n, v_, kvd, nullptr, 0);
     launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream, (const float *)L.bq.data,
-                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox);
+                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox_kernel);
     attention(kv, n);
     invalidate(actq_valid_);
     matmul(L.wo, att_, d, n, x_, d, x_, d); // x = x + wo.att
@@ -468,6 +502,7 @@ void Model::run_layer_fused(const LayerW &L, const KVLayout &kv, int n) {
     a.fmt = act_format_for(L.wq.type);
     a.n_jobs = 3; a.job[0] = job_of(L.wq); a.job[1] = job_of(L.wk); a.job[2] = job_of(L.wv);
     a.epi = EPI_QKV; a.out = q_; a.out_stride = d; a.pos = pos_; a.slot = slot_; a.rope_table = rope_table_; a.kv = kv; a.hd = hd;
+    a.qkv_bias[0] = (const float *)L.bq.data; a.qkv_bias[1] = (const float *)L.bk.data; a.qkv_bias[2] = (const float *)L.bv.data;
     launch_fused_gemv(a, n, stream);
     attention(kv, n);
     FusedGemv o;
@@ -618,7 +653,7 @@ void Model::run_layer_gemm(const LayerW &L, const KVLayout &kv, int n) {
         gemm_multi(Ws, outs, strides, 3, n);
     }
     launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream, (const float *)L.bq.data,
-                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox);
+                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox_kernel);
     if (!attention_to_tiles(kv, n, gemm_x_)) {
         attention(kv, n);
         launch_gemm_prepare_x(att_, d, n, d, gemm_x_, stream);
@@ -701,7 +736,7 @@ void Model::run_layer_qgemm(const LayerW &L, const KVLayout &kv, int n) {
           launch_attention_decode_fused(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, n_ctx_slot, gemm_x_,
                                         (int)align_up(n, 16), stream))) {
         launch_rope_kv_store(q_, k_, v_, pos_, slot_, n, hp.n_head, hp.n_head_kv, hd, rope_table_, kv, stream, (const float *)L.bq.data,
-                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox);
+                         (const float *)L.bk.data, (const float *)L.bv.data, hp.rope_neox_kernel);
         attention(kv, n);
         launch_qgemm_prepare_x(att_, d, n, d, gemm_x_, stream);
     }

@@ -18,7 +18,8 @@ struct SampleSpec;
 struct HParams {
     int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_ctx_train = 0;
     float rms_eps = 1e-5f, rope_base = 10000.f, rope_scale = 1.f;
-    bool rope_neox = false;      // rotary pairs (i, i + head_dim / 2) (qwen2) instead of (2i, 2i + 1)
+    bool rope_neox = false;      // the architecture rotates pairs (i, i + head_dim / 2) (qwen2, phi3) instead of (2i, 2i + 1)
+    bool rope_neox_kernel = false; // ... and the kernels do it (A/B switch); normally the rows of wq / wk are interleaved at load instead
     float rope_ext_factor = 0.f; // 1 for YaRN (llama.rope.scaling.type)
     float rope_attn_factor = 1.f, rope_beta_fast = 32.f, rope_beta_slow = 1.f; // llama.cpp's defaults, b2_load_opts overrides
     int rope_n_ctx_orig = 0;     // llama.rope.scaling.original_context_length
@@ -117,8 +118,9 @@ class Model {
     void run_decode_mega_tp(int t0, int out_row0);
     void tp_allreduce(int t0, int n);                    // xp_ -> x_ (sum over the shards)
     // column / K slices of a tensor: rows [row0, row0 + nrows) x columns [col0, col0 + ncols) (col ranges on block boundaries)
+    // pair_heads > 0: the kept rows are `pair_heads`-row heads whose rows are interleaved on the way (i, i + h/2 -> 2i, 2i + 1)
     DTensor upload(const GGUFFile &f, const std::string &name, int64_t want_rows, int64_t want_cols, bool required,
-                   int64_t row0 = 0, int64_t nrows = -1, int64_t col0 = 0, int64_t ncols = -1);
+                   int64_t row0 = 0, int64_t nrows = -1, int64_t col0 = 0, int64_t ncols = -1, int pair_heads = 0);
     void quantize_for(const DTensor &W, const float *x, int64_t x_stride, int n, uint8_t **out, ActFmt *fmt);
     void matmul(const DTensor &W, const float *x, int64_t x_stride, int n, float *out, int64_t out_stride,
                 const float *residual, int64_t res_stride);

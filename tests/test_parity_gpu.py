@@ -447,3 +447,40 @@ def test_rope_scaling_overrides_of_model_options(model_files, name, kw):
     with capi.Engine(path, n_ctx=64, n_batch=16, **kw) as e:
         got = e.eval(toks, logits_all=True)
     assert_logits_close(got, ref, f"{name} {kw}")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["mini_qwen2", "mini_phi3"])
+def test_neox_architectures_on_the_llama_kernels(model_files, name, monkeypatch):
+    """qwen2 / phi3 rotate the pairs (i, i + head_dim / 2).  LoadModel interleaves the rows of wq / wk (and their biases) per
+    head instead, after which every llama kernel -- the persistent decode kernel included, for phi3 -- applies the
+    architecture's own rotation.  Against the oracle (which rotates the un-interleaved rows), and against the engine with the
+    rotation done by the per-operator kernel on un-interleaved rows (B200LLM_NEOX_KERNEL=1): prompt logits, then the decode
+    path token by token."""
+    path = model_files[name]
+    toks = np.arange(11, 43, dtype=np.int32)
+    ref = O.OracleModel(path, n_ctx=128)
+    want = ref.eval(toks, logits_all=True)
+    outs = {}
+    for mode in ("interleaved", "kernel"):
+        monkeypatch.setenv("B200LLM_NEOX_KERNEL", "1" if mode == "kernel" else "0")
+        with capi.Engine(path, n_ctx=128, n_batch=64) as e:
+            lg = e.eval(toks, logits_all=True)
+            assert_logits_close(lg, want, f"{name} {mode} prompt")
+            step = [lg[-1]]
+            n_past, tok = len(toks), int(lg[-1].argmax())
+            for _ in range(6):  # one token at a time: the decode path of this architecture
+                l1 = e.eval(np.array([tok], dtype=np.int32), n_past=n_past)[-1]
+                step.append(l1)
+                n_past, tok = n_past + 1, int(l1.argmax())
+            outs[mode] = (lg, np.stack(step))
+    sig = float(want.std())
+    assert np.abs(outs["interleaved"][0] - outs["kernel"][0]).max() <= 0.02 * sig
+    assert np.array_equal(outs["interleaved"][1].argmax(-1), outs["kernel"][1].argmax(-1))
+    # the oracle, fed the same tokens, agrees with the decode path step by step
+    n_past = len(toks)
+    for i in range(6):
+        tok = int(outs["interleaved"][1][i].argmax())
+        w1 = ref.eval(np.array([tok], dtype=np.int32), n_past=n_past)[-1]
+        assert_logits_close(outs["interleaved"][1][i + 1][None], w1[None], f"{name} decode step {i}")
+        n_past += 1
