@@ -195,6 +195,62 @@ rmsnorm_x_tiles_kernel(const float *__restrict__ x, int64_t x_stride, const floa
     }
 }
 
+// The same with one WARP per token row and the row held in registers (cols = 256 NCH, 8 NCH features per lane): one pass over
+// x instead of two, and the four rows of a CTA fill neighbouring 16-byte pieces of the same 128-byte lines of the tile (a row
+// per CTA writes 16 bytes into each of 512 different lines).  Used for long batches (prefill).
+template <int NCH>
+__global__ void __launch_bounds__(128)
+rmsnorm_x_tiles_warp_kernel(const float *__restrict__ x, int64_t x_stride, const float *__restrict__ w, int n_tok, float eps,
+                            __half *__restrict__ out, float *__restrict__ xn_out, int m_pad) {
+    constexpr int64_t cols = 256 * NCH;
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (r >= m_pad) return;
+    constexpr int64_t k_tiles = cols / GM_BK;
+    __half *tile0 = out + (int64_t)(r / GM_BM) * k_tiles * (int64_t)(GM_BM * GM_BK);
+    float v[NCH][8];
+    if (r < n_tok) { // warp-uniform
+        const float *xr = x + (int64_t)r * x_stride;
+#pragma unroll
+        for (int i = 0; i < NCH; i++) {
+            const float4 a = *(const float4 *)(xr + 256 * i + 8 * lane), b = *(const float4 *)(xr + 256 * i + 8 * lane + 4);
+            v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w; v[i][4] = b.x; v[i][5] = b.y; v[i][6] = b.z; v[i][7] = b.w;
+        }
+        double sum = 0.0;
+#pragma unroll
+        for (int i = 0; i < NCH; i++)
+#pragma unroll
+            for (int j = 0; j < 8; j++) sum += (double)__fmul_rn(v[i][j], v[i][j]);
+        sum = warp_sum_d(sum);
+        const float mean = (float)(sum / (double)cols);
+        const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+#pragma unroll
+        for (int i = 0; i < NCH; i++) {
+            const int k0 = 256 * i + 8 * lane;
+            const float4 wa = *(const float4 *)(w + k0), wb = *(const float4 *)(w + k0 + 4);
+            const float ww[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[i][j] = __fmul_rn(__fmul_rn(v[i][j], scale), ww[j]);
+            if (xn_out) {
+                *(float4 *)(xn_out + (int64_t)r * cols + k0) = make_float4(v[i][0], v[i][1], v[i][2], v[i][3]);
+                *(float4 *)(xn_out + (int64_t)r * cols + k0 + 4) = make_float4(v[i][4], v[i][5], v[i][6], v[i][7]);
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < NCH; i++)
+#pragma unroll
+            for (int j = 0; j < 8; j++) v[i][j] = 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < NCH; i++) {
+        const int k0 = 256 * i + 8 * lane;
+        __half *dst = tile0 + (k0 / GM_BK) * (int64_t)(GM_BM * GM_BK) + tile_elem_offset(r % GM_BM, k0 % GM_BK);
+        const __half2 p4[4] = {gm_pack2(v[i][0], v[i][1]), gm_pack2(v[i][2], v[i][3]), gm_pack2(v[i][4], v[i][5]), gm_pack2(v[i][6], v[i][7])};
+        *(int4 *)dst = *(const int4 *)p4;
+    }
+}
+
 // BERT: x = LayerNorm(x + h + bias) * w + b (ggml_norm: mean, variance of the centred values), the row written back as
 // fp32 (it is the next residual) AND as fp16 operand tiles of the next GEMM.  One CTA per token row, the row lives in
 // registers (8 features per thread, cols <= 2048); rows >= n_tok of the last tile get zero tiles.
@@ -730,6 +786,11 @@ void launch_gemm_prepare_x_rmsnorm(const float *x, int64_t x_stride, const float
                                    float *xn_out, cudaStream_t s) {
     B2_CHECK(K % GM_BK == 0, B2_EINVAL, "gemm: K must be a multiple of 64");
     const int m_pad = (int)align_up(n_tok, GM_BM);
+    static const bool row_per_cta = getenv("B200LLM_RMSNORM_ROW_PER_CTA") && atoi(getenv("B200LLM_RMSNORM_ROW_PER_CTA")); // A/B
+    const bool warp_rows = m_pad >= 1024 && x_stride % 4 == 0 && !row_per_cta;
+    if (warp_rows && K == 4096) rmsnorm_x_tiles_warp_kernel<16><<<m_pad / 4, 128, 0, s>>>(x, x_stride, w, n_tok, eps, (__half *)x_tiles, xn_out, m_pad);
+    else if (warp_rows && K == 2048) rmsnorm_x_tiles_warp_kernel<8><<<m_pad / 4, 128, 0, s>>>(x, x_stride, w, n_tok, eps, (__half *)x_tiles, xn_out, m_pad);
+    else
     rmsnorm_x_tiles_kernel<<<m_pad, 256, 0, s>>>(x, x_stride, w, n_tok, K, eps, (__half *)x_tiles, xn_out);
     g_launch_count++;
     B2_CUDA(cudaGetLastError());
