@@ -49,6 +49,7 @@ def model_files(gguf_dir):
         "micro_l31": ("micro-l31", "mixed"),
         "micro_g8": ("micro-g8", "q4_k_m"),  # 8 query heads per KV head
         "mini_qwen2": ("mini-qwen2", "q4_k_m"),  # qwen2: QKV biases, NEOX rotary pairs, its own pre-tokeniser
+        "mini_qwen2_g7": ("mini-qwen2-g7", "q4_k_m"),  # 7 query heads per KV head: no grouped attention kernel for it
         "mini_phi3": ("mini-phi3", "q4_k_m"),  # phi3: fused attn_qkv and gate|up tensors, NEOX rotary pairs
     }
     out = {}

@@ -196,6 +196,7 @@ MODELS = ["micro_mixed", "micro_q8_0", "mini_q4_k_m", "mini_q5_k", "mini_f16", "
           "micro_linear", "micro_yarn", "micro_l31",  # RoPE scaling (linear, YaRN, rope_freqs.weight divisors)
           "micro_g8",                                 # 8 query heads per KV head
           "mini_qwen2",                               # qwen2 architecture (QKV biases, NEOX rotary pairs)
+          "mini_qwen2_g7",                            # ... with 7 query heads per KV head (Qwen2.5-7B's grouping)
           "mini_phi3"]                                # phi3 architecture (fused attn_qkv / gate|up tensors, NEOX rotary pairs)
 
 

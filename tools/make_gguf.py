@@ -85,6 +85,7 @@ ARCHS = {
     "micro-l31": Arch("micro-l31", 2, 256, 4, 2, 512, 4352, 512, 10000.0, 1e-5, "spm", False, "none", 1.0, 0, True),
     # qwen2: QKV biases, NEOX rotary pairs (i, i + head_dim / 2), its own BPE pre-tokeniser (digits one at a time)
     "mini-qwen2": Arch("mini-qwen2", 3, 512, 8, 2, 1024, 4608, 1024, 1000000.0, 1e-6, "bpe", False, "none", 1.0, 0, False, "qwen2", True),
+    "mini-qwen2-g7": Arch("mini-qwen2-g7", 2, 1792, 14, 2, 1024, 4608, 1024, 1000000.0, 1e-6, "bpe", False, "none", 1.0, 0, False, "qwen2", True),  # 7 query heads per KV head (Qwen2.5-7B's grouping), head_dim 128
     # phi3: fused attn_qkv and gate|up tensors, NEOX rotary pairs, SentencePiece vocabulary, no biases
     "mini-phi3": Arch("mini-phi3", 3, 512, 8, 2, 1024, 4352, 1024, 10000.0, 1e-5, "spm", False, "none", 1.0, 0, False, "phi3", False, True),
     "micro-g8": Arch("micro-g8", 2, 512, 8, 1, 1024, 4352, 512, 10000.0, 1e-5, "spm"),  # 8 query heads per KV head (the 70B grouping), head_dim 64
