@@ -537,6 +537,11 @@ struct GemmArgs {
     __half *x2_tiles;
     const float *bias;
     int M, N_total, k_tiles, m_tiles, n_tiles; // n_tiles: over all matrices
+    // Which index runs fastest over the CTAs: the tiles that run at the same time share the operand tile of the OTHER index
+    // out of L2, so the smaller operand is the one streamed repeatedly.  0: m fastest (a weight tile is shared, the
+    // activations are re-read per weight tile -- prefill, where they fit L2); 1: n fastest (long batches against a small
+    // matrix, BERT: 32768 x 3072 activations were read three times for ffn_down's three weight tiles).
+    int n_fastest;
     uint32_t lbo, sbo;
     // split-K for small M (batched decode): with one m-tile and few n-tiles most SMs would have no work item, and the
     // weight tiles are the bytes that have to stream.  A work item is (m-tile, n-tile, k-slice); slices write fp32
@@ -598,7 +603,8 @@ gemm_tcgen05_kernel(const GemmArgs g) {
         { // ===== producer: one bulk copy per operand tile (the whole warp walks the schedule, an elected lane issues)
             uint32_t it = 0;
             for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
-                const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
+                const int ks = tile / (g.m_tiles * g.n_tiles), t2 = tile % (g.m_tiles * g.n_tiles);
+                const int mt = g.n_fastest ? t2 / g.n_tiles : t2 % g.m_tiles, nt = g.n_fastest ? t2 % g.n_tiles : t2 / g.m_tiles;
                 const int jb = (g.n_jobs > 2 && nt >= g.job[2].nt0) ? 2 : (g.n_jobs > 1 && nt >= g.job[1].nt0) ? 1 : 0;
                 const __half *bt = g.job[jb].b_tiles + (int64_t)(nt - g.job[jb].nt0) * g.k_tiles * (GM_BN * GM_BK);
                 const int kt0 = ks * g.k_per_split, kt1 = min(g.k_tiles, kt0 + g.k_per_split);
@@ -645,7 +651,8 @@ gemm_tcgen05_kernel(const GemmArgs g) {
         float4 *stage4 = (float4 *)(gsm + (size_t)GM_STAGES * GM_STAGE_BYTES + 1024 + (size_t)(warp - 4) * 4096);
         uint32_t acc_it = 0;
         for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x, acc_it++) {
-            const int mt = tile % g.m_tiles, nt = (tile / g.m_tiles) % g.n_tiles, ks = tile / (g.m_tiles * g.n_tiles);
+            const int ks = tile / (g.m_tiles * g.n_tiles), t2 = tile % (g.m_tiles * g.n_tiles);
+            const int mt = g.n_fastest ? t2 / g.n_tiles : t2 % g.m_tiles, nt = g.n_fastest ? t2 % g.n_tiles : t2 / g.m_tiles;
             const int acc = acc_it & 1;
             const GemmJobDev &J = g.job[(g.n_jobs > 2 && nt >= g.job[2].nt0) ? 2 : (g.n_jobs > 1 && nt >= g.job[1].nt0) ? 1 : 0];
             gm_mbar_wait(tfull + acc, (acc_it >> 1) & 1);
@@ -871,6 +878,7 @@ void launch_gemm_tc_multi(const GemmJob *jobs, int n_jobs, const void *x_tiles, 
     g.M = n_tok; g.N_total = col; g.k_tiles = (int)(cols / GM_BK);
     g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = nt;
     g.lbo = lbo; g.sbo = sbo;
+    g.n_fastest = (int64_t)g.m_tiles * GM_BM > (int64_t)g.n_tiles * GM_BN ? 1 : 0;
     g.ksplit = 1; g.k_per_split = g.k_tiles; g.partial = nullptr;
     const int tiles = g.m_tiles * g.n_tiles;
     bool any_bias = false;
@@ -927,6 +935,7 @@ static void launch_gemm_fused_epilogue(int epi, const void *w_tiles, int64_t N, 
     g.job[0].N = (int)N; g.job[0].n_tiles = (int)(N / GM_BN); g.job[0].nt0 = 0; g.job[0].col0 = 0;
     g.M = n_tok; g.N_total = (int)N; g.k_tiles = (int)(cols / GM_BK);
     g.m_tiles = (int)(align_up(n_tok, GM_BM) / GM_BM); g.n_tiles = g.job[0].n_tiles;
+    g.n_fastest = (int64_t)g.m_tiles * GM_BM > (int64_t)g.n_tiles * GM_BN ? 1 : 0;
     g.lbo = 128; g.sbo = 1024;
     g.ksplit = 1; g.k_per_split = g.k_tiles;
     g.epi_tiles = epi; g.x2_tiles = (__half *)x2_tiles; g.bias = bias;
