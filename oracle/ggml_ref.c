@@ -18,8 +18,10 @@
  * against HuggingFace transformers' LlamaForCausalLM loaded from the same GGUF (tools/crosscheck_transformers.py,
  * tests/golden/transformers_crosscheck.json, tests/test_oracle.py::test_oracle_matches_transformers) -- the
  * reference's own tests hold no logits or token-id vectors for this path.
- * NOT PINNED ("parity unpinned" for these paths only): the scaled RoPE variants (linear, YaRN, rope_freqs.weight),
- * restated from ggml's published algorithm and checked against closed forms only (ref_rope_cache_ext below).
+ * The scaled RoPE variants (linear, YaRN, the rope_freqs.weight divisors of Llama-3.1; ref_rope_cache_ext below), the
+ * qwen2 graph (QKV biases, NEOX pairs) and the phi3 graph (fused tensors) are pinned the same way: against transformers'
+ * "linear" / "yarn" / "llama3" rotary scaling, Qwen2ForCausalLM and Phi3ForCausalLM on the same GGUFs (same script and
+ * golden file; 2-3e-3 sigma on F16 files, where leaving the scaling out costs more than one sigma).
  *
  * Build: see oracle/Makefile (gcc -O3 -fopenmp -ffp-contract=off).  Contraction is disabled so
  * that `d*q - m` is two roundings, as in gguf-py.
@@ -862,8 +864,9 @@ void ref_rope_cache(float theta_base, float freq_scale, float freq_base, int n_d
 
 /* The scaled variants, restated from ggml's published algorithm (ggml.c: rope_yarn, rope_yarn_ramp,
  * ggml_rope_yarn_corr_dims, ggml_rope_cache_init with freq_factors; YaRN: arXiv 2309.00071).  llama.cpp is an
- * un-vendored submodule of the reference, so this part of the oracle is NOT pinned against upstream code or vectors:
- * "parity unpinned" for the scaled RoPE paths (the unscaled path above is pinned through the transformers cross-check). */
+ * un-vendored submodule of the reference, so this part of the oracle is pinned the way the unscaled path is: against
+ * transformers' implementations of the same three schemes (tools/crosscheck_transformers.py: rope_linear / rope_yarn /
+ * rope_l31 entries of tests/golden/transformers_crosscheck.json). */
 static float rope_yarn_ramp(float low, float high, int i0) {
     const float y = (i0 / 2 - low) / fmaxf(0.001f, high - low);
     return 1.0f - fminf(1.0f, fmaxf(0.0f, y));

@@ -162,7 +162,9 @@ def test_oracle_matches_transformers():
     r = X.measure()
     gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "transformers_crosscheck.json")))
     assert set(r) == set(gold)
-    for k in ("llama_mini_f16", "qwen2_mini_f16", "phi3_mini_f16"):  # Qwen2ForCausalLM (QKV biases, rotate-half RoPE on un-permuted weights), Phi3ForCausalLM (fused qkv | gate_up)
+    for k in ("rope_linear_f16", "rope_yarn_f16", "rope_l31_f16"):  # transformers' own "linear" / "yarn" / "llama3" rotary scaling
+        assert r[k]["unscaled_max_err_sigma"] >= 0.5, (k, r[k])  # ... which is not a detail at these positions
+    for k in ("llama_mini_f16", "qwen2_mini_f16", "phi3_mini_f16", "rope_linear_f16", "rope_yarn_f16", "rope_l31_f16"):  # Qwen2ForCausalLM (QKV biases, rotate-half RoPE on un-permuted weights), Phi3ForCausalLM (fused qkv | gate_up)
         f16 = r[k]
         assert f16["rel_to_max"] <= 1e-3 and f16["argmax_agree"] == f16["n_tokens"], (k, f16)
     for k in ("llama_mini_q4_k_m", "llama_mini_q8_0", "qwen2_mini_q4_k_m", "phi3_mini_q4_k_m"):

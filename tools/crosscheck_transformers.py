@@ -24,8 +24,10 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 
-def hf_llama_logits(path: str, ids) -> np.ndarray:
-    """logits [n_tok][n_vocab] of the GGUF at `path` from transformers' LlamaForCausalLM in fp32 on the CPU."""
+def hf_llama_logits(path: str, ids, rope_scaling=None) -> np.ndarray:
+    """logits [n_tok][n_vocab] of the GGUF at `path` from transformers' LlamaForCausalLM in fp32 on the CPU.
+    rope_scaling: the HF config entry that says what the GGUF's rope.scaling.* metadata / rope_freqs.weight say (transformers'
+    GGUF reader does not map them)"""
     import torch
     from transformers import LlamaConfig, LlamaForCausalLM
     from transformers.modeling_gguf_pytorch_utils import load_gguf_checkpoint
@@ -41,7 +43,8 @@ def hf_llama_logits(path: str, ids) -> np.ndarray:
 
         model = Phi3ForCausalLM(Phi3Config(**{k: v for k, v in cfg.items() if k != "model_type"}, pad_token_id=0)).to(torch.float32).eval()
     else:
-        model = LlamaForCausalLM(LlamaConfig(**{k: v for k, v in cfg.items() if k != "model_type"})).to(torch.float32).eval()
+        extra = {"rope_scaling": rope_scaling} if rope_scaling else {}
+        model = LlamaForCausalLM(LlamaConfig(**{k: v for k, v in cfg.items() if k != "model_type"}, **extra)).to(torch.float32).eval()
     tensors = load_gguf_checkpoint(path, return_tensors=True, model_to_load=model)["tensors"]
     missing, unexpected = model.load_state_dict(tensors, strict=False)
     assert not missing and not unexpected, (missing, unexpected)
@@ -113,6 +116,27 @@ def measure() -> dict:
                 "n_tokens": int(len(ids)), "sigma_logits": sig, "max_err_sigma": float(err.max() / sig),
                 "median_err_sigma": float(np.median(err) / sig), "rel_to_max": float(err.max() / np.abs(want).max()),
                 "argmax_agree": int((got.argmax(-1) == want.argmax(-1)).sum())}
+        # RoPE scaling: linear, YaRN, and the per-dimension divisors of Llama-3.1 (rope_freqs.weight) against transformers'
+        # own implementations of the three (modeling_rope_utils: "linear", "yarn", "llama3"); 96 positions, so that the
+        # scaled rotations differ from the unscaled ones by more than a sigma of the logits
+        for arch, rs in (("micro-linear", {"rope_type": "linear", "factor": mg.ARCHS["micro-linear"].rope_factor}),
+                         ("micro-yarn", {"rope_type": "yarn", "factor": mg.ARCHS["micro-yarn"].rope_factor,
+                                         "original_max_position_embeddings": mg.ARCHS["micro-yarn"].rope_orig_ctx}),
+                         ("micro-l31", {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+                                        "original_max_position_embeddings": mg.ARCHS["micro-l31"].rope_orig_ctx or 64})):
+            path = os.path.join(td, f"{arch}_f16.gguf")
+            mg.write_gguf(path, mg.ARCHS[arch], "f16", seed=7, quiet=True)
+            ids = rng.integers(0, 4000, 96)
+            want = hf_llama_logits(path, ids, rope_scaling=rs)
+            plain = hf_llama_logits(path, ids)
+            got = O.OracleModel(path, n_ctx=128).eval(ids, logits_all=True)
+            sig = float(want.std())
+            err = np.abs(got - want)
+            res["rope_" + arch.split("-")[1] + "_f16"] = {
+                "n_tokens": int(len(ids)), "sigma_logits": sig, "max_err_sigma": float(err.max() / sig),
+                "median_err_sigma": float(np.median(err) / sig), "rel_to_max": float(err.max() / np.abs(want).max()),
+                "argmax_agree": int((got.argmax(-1) == want.argmax(-1)).sum()),
+                "unscaled_max_err_sigma": float(np.abs(got - plain).max() / sig)}
         bpath = os.path.join(td, "bert_mini.gguf")
         mb.write_bert_gguf(bpath, mb.BERT_ARCHS["bert-mini"], seed=3)
         ids = np.concatenate([[2], rng.integers(5, 2048, 30), [3]])
