@@ -219,3 +219,30 @@ def test_rope_scaling_changes_the_rotation_as_specified(model_files):
         if name == "micro_linear":  # same tensors, and position 0 is not rotated: identical there (YaRN scales q and k by its
             np.testing.assert_array_equal(got[0], ref[0])  # magnitude factor even at 0; micro_l31 has one more tensor, hence other weights)
         assert np.abs(got[5:] - ref[5:]).max() > 1e-3, name
+
+
+def test_sampler_references_match_transformers_processors():
+    """The restated sampler steps that have a counterpart in HuggingFace transformers, against that counterpart on random
+    rows: the repeat penalty (RepetitionPenaltyLogitsProcessor: divide positive logits, multiply negative ones -- the rule
+    of llama_sampler_penalties_apply) and locally-typical truncation (TypicalLogitsWarper: sort by |surprise - entropy|,
+    keep until the mass is covered -- llama_sampler_typical_apply).  Tail-free and mirostat have no counterpart there;
+    they are checked against their closed forms in the GPU tests."""
+    torch = pytest.importorskip("torch")
+    tr = pytest.importorskip("transformers")
+    rng = np.random.default_rng(23)
+    for trial in range(12):
+        n = 500 + 37 * trial
+        x = (rng.standard_normal(n) * 3).astype(np.float32)
+        prev = rng.integers(0, n, 40).astype(np.int64)
+        pen = 1.1 + 0.07 * trial
+        want = tr.RepetitionPenaltyLogitsProcessor(penalty=pen)(torch.from_numpy(prev)[None], torch.from_numpy(x.copy())[None])[0].numpy()
+        got = O.penalties_ref(x, prev, repeat_penalty=pen)
+        assert np.allclose(got, want, rtol=1e-6, atol=0), trial
+        mass = 0.2 + 0.06 * trial
+        z = (np.log(1.0 / np.arange(1, n + 1) ** 1.05) + 0.3 * rng.standard_normal(n)).astype(np.float32)
+        kept_hf = tr.TypicalLogitsWarper(mass=mass, min_tokens_to_keep=1)(None, torch.from_numpy(z.copy())[None])[0].numpy()
+        kept_hf = set(np.nonzero(np.isfinite(kept_hf))[0].tolist())
+        kept = O.typical_ref(z, mass)
+        # the two differ at most in the boundary token when the cumulative mass lands within rounding of `mass` (fp32 there, fp64 here)
+        assert len(kept ^ kept_hf) <= 1 and (kept <= kept_hf or kept_hf <= kept), (trial, len(kept), len(kept_hf))
+        assert len(kept) >= 1 and len(kept) < n
