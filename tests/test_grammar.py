@@ -156,3 +156,55 @@ def test_token_mask_equals_viable_prefix_definition():
         m = capi.grammar_token_mask(g, acc, [p.encode() for p in pieces] + [b"</s>"], eog)
         want = [G.viable(rules, acc + p) for p in pieces] + [G.match(rules, acc)[1]]
         assert m.tolist() == want, cut
+
+
+def test_sentences_agree_with_xgrammar():
+    """An independent GBNF implementation (xgrammar, the grammar engine vLLM ships; it reads llama.cpp's grammar format)
+    decides "is this text a complete sentence of the grammar" like this engine's matcher: on the reference's own grammar
+    texts with calls, wrapped calls, prefixes and random mutations of them, and on the known-answer grammars above."""
+    xg = pytest.importorskip("xgrammar")
+    from xgrammar.testing import _is_grammar_accept_string as accepts
+
+    rng = np.random.default_rng(9)
+    alphabet = list('{}[]":, \\abcdefu0123456789é\n')
+    n_checked = n_sentences = 0
+    for name in sorted(GOLDEN):
+        g = GOLDEN[name]
+        theirs = xg.Grammar.from_ebnf(g, root_rule_name="root")
+        key = "name" if '\\"name\\"' in g else "function"
+        calls = [c.replace("function", key) for c in (CALL_EVENT, CALL_SEARCH)]
+        if name.startswith("testllama31"):
+            calls = ['<function=create_event>{{"date":"d","time":"t","title":"x"}}</function>', '<function=search>{{"query": "q" }}</function>']
+        texts = []
+        for c in calls:
+            texts += [c, "suffix" + c, "suffix[\n" + c + ",\n" + c + "]", "[\n" + c + "]", c[:-1], c[:len(c) // 2], "plain text", ""]
+            for _ in range(25):
+                s = list(c)
+                for _ in range(int(rng.integers(1, 3))):
+                    i = int(rng.integers(0, len(s)))
+                    op = int(rng.integers(0, 3))
+                    if op == 0:
+                        s[i] = alphabet[int(rng.integers(0, len(alphabet)))]
+                    elif op == 1:
+                        del s[i]
+                    else:
+                        s.insert(i, alphabet[int(rng.integers(0, len(alphabet)))])
+                texts.append("".join(s))
+        for t in texts:
+            nb, stop = capi.grammar_match(g, t)
+            mine = bool(stop) and nb == len(t.encode("utf-8"))
+            assert mine == bool(accepts(theirs, t)), (name, t, nb, stop)
+            n_checked += 1
+            n_sentences += mine
+    for gbnf, text, nb_want, stop_want in KNOWN:
+        try:
+            theirs = xg.Grammar.from_ebnf(gbnf, root_rule_name="root")
+        except Exception:  # a construct xgrammar does not read
+            continue
+        for t in (text, text[:-1], text + "a", text[:nb_want]):
+            nb, stop = capi.grammar_match(gbnf, t)
+            mine = bool(stop) and nb == len(t.encode("utf-8"))
+            assert mine == bool(accepts(theirs, t)), (gbnf, t, nb, stop)
+            n_checked += 1
+            n_sentences += mine
+    assert n_checked > 600 and 40 < n_sentences < n_checked - 200  # both answers occur often enough to mean something
