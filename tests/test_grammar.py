@@ -208,3 +208,41 @@ def test_sentences_agree_with_xgrammar():
             n_checked += 1
             n_sentences += mine
     assert n_checked > 600 and 40 < n_sentences < n_checked - 200  # both answers occur often enough to mean something
+
+
+def test_token_masks_agree_with_xgrammar():
+    """... and the vocabulary mask after an accepted prefix (what constrains the sampler) is xgrammar's next-token bitmask,
+    over a vocabulary of real substrings, junk and an end-of-generation token."""
+    xg = pytest.importorskip("xgrammar")
+    rng = np.random.default_rng(11)
+    pieces = set()
+    for s in (CALL_EVENT, CALL_SEARCH, 'xyz "\\ {}[]:, 0123 \\u00e9 \\n', "suffix[\n"):
+        for _ in range(400):
+            i = int(rng.integers(0, len(s)))
+            pieces.add(s[i:i + int(rng.integers(1, 7))])
+    pieces = sorted(p for p in pieces if p)
+    vocab = [p.encode() for p in pieces] + [b"</s>"]
+    ti = xg.TokenizerInfo(vocab, vocab_type=xg.VocabType.RAW, stop_token_ids=[len(vocab) - 1])
+    compiler = xg.GrammarCompiler(ti)
+    idx = np.arange(len(vocab))
+    n_masks = 0
+    for name in ("inputResult1", "inputResult2", "inputResult4", "rootResult0", "rootResult3", "rootResult5"):
+        g = GOLDEN[name]
+        compiled = compiler.compile_grammar(xg.Grammar.from_ebnf(g, root_rule_name="root"))
+        key = "name" if '\\"name\\"' in g else "function"
+        call = CALL_EVENT.replace("function", key)
+        forms = [f for f in (call, "suffix" + call, "[\n" + call + "]") if capi.grammar_match(g, f) == (len(f.encode()), True)]
+        assert forms, name
+        text = forms[0]
+        for cut in sorted({0, 1, 2, 15, 30, 47, 80, len(text) // 2, len(text) - 1, len(text)}):
+            acc = text[:cut]
+            m = xg.GrammarMatcher(compiled)
+            assert not acc or m.accept_string(acc)
+            bm = xg.allocate_token_bitmask(1, ti.vocab_size)
+            m.fill_next_token_bitmask(bm)
+            bits = bm.numpy()[0].view(np.uint32)
+            theirs = ((bits[idx >> 5] >> (idx & 31).astype(np.uint32)) & 1).astype(bool)
+            mine = capi.grammar_token_mask(g, acc, vocab, [0] * len(pieces) + [1])
+            assert mine.tolist() == theirs.tolist(), (name, cut, [vocab[i] for i in np.nonzero(mine != theirs)[0][:5]])
+            n_masks += 1
+    assert n_masks >= 50
