@@ -48,6 +48,30 @@ def test_wordpiece_matches_restatement(bert_files):
             b.embed("x")
 
 
+def test_wordpiece_matches_hf_tokenizers(bert_files):
+    """The WordPiece tokeniser (and its restatement) against the HF `tokenizers` library's: lower-casing normaliser, split on
+    white space and punctuation, greedy longest match with [UNK] for a word with an unmatched rest.  The GGUF vocabulary
+    marks word starts ("▁the") where BERT's marks continuations ("##e"); converted, the ids must be the same -- on ASCII
+    text, where bert.cpp's ASCII-only case folding and punctuation table say what the full Unicode ones say."""
+    tk = pytest.importorskip("tokenizers")
+    ref = BertRef(bert_files["bert-mini"])
+    vocab = {}
+    for i, s in enumerate(ref.tokens):
+        hf = s if (s.startswith("[") and s.endswith("]")) else (s[1:] if s.startswith("▁") else "##" + s)
+        vocab.setdefault(hf, i)
+    tok = tk.Tokenizer(tk.models.WordPiece(vocab=vocab, unk_token="[UNK]", max_input_chars_per_word=10000))
+    tok.normalizer = tk.normalizers.BertNormalizer(clean_text=False, handle_chinese_chars=True, strip_accents=False, lowercase=True)
+    tok.pre_tokenizer = tk.pre_tokenizers.BertPreTokenizer()
+    texts = ["The quick brown fox, jumping over 2 lazy dogs! xyzzy", "Hello,World!!", "tokenization embeddings unusedword", "",
+             "LocalAI is a drop-in replacement REST API", "[CLS] is just text here", "a" * 90, "  spaces\tand\nlines  ",
+             "model's vector-search (query) & documents: 100% local_ai", "UPPER lower MiXeD 0123456789 ~`^|<>"]
+    with capi.Bert(bert_files["bert-mini"], vocab_only=True) as b:
+        for t in texts:
+            want = [ref.cls] + tok.encode(t, add_special_tokens=False).ids + [ref.sep]
+            assert ref.tokenize(t) == want, t
+            assert b.tokenize(t) == want, t
+
+
 def test_load_errors(model_files):
     with pytest.raises(RuntimeError, match="bert"):
         capi.Bert(model_files["micro_q8_0"], vocab_only=True)  # a llama GGUF is not a BERT encoder
