@@ -657,7 +657,6 @@ gemm_tcgen05_kernel(const GemmArgs g) {
             const GemmJobDev &J = g.job[(g.n_jobs > 2 && nt >= g.job[2].nt0) ? 2 : (g.n_jobs > 1 && nt >= g.job[1].nt0) ? 1 : 0];
             gm_mbar_wait(tfull + acc, (acc_it >> 1) & 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int row = mt * GM_BM + q * 32 + lane;
             if (g.epi_tiles) { // activation fused, output = the next GEMM's operand tiles (every row of the tile is written: padding rows are zeros in, zeros out)
                 const int ncol = g.epi_tiles == 1 ? GM_BN / 2 : GM_BN;
                 const int64_t k2_tiles = (g.epi_tiles == 1 ? g.N_total / 2 : g.N_total) / GM_BK;
