@@ -185,6 +185,7 @@ Tokenizer::Tokenizer(const GGUFFile &f) {
         kind_ = BPE;
         bos_ = 11; eos_ = 11;
         add_bos_ = false;
+        if (pre_ == "smaug-bpe") pre_ = "llama-bpe"; // llama.cpp maps it onto the llama-3 pre-tokeniser as well
         B2_CHECK(pre_ == "llama-bpe" || pre_ == "llama3" || pre_ == "llama-v3" || pre_ == "default" || pre_ == "qwen2", B2_EUNSUPPORTED,
                  "unsupported BPE pre-tokeniser '" + pre_ + "' (llama-bpe, qwen2)");
         // llama-3 emits a word that is itself a token without merging and adds a BOS; qwen2 does neither (llama.cpp's
