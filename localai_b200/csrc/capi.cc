@@ -268,6 +268,14 @@ extern "C" int b2_stream_text(const char *pieces, const int *lens, int n, const 
     return stopped;
     B2_API_END(0)
 }
+// b2_partial_stop: where in `text` its longest suffix that is a prefix of `word` begins (-1: none) -- the hold-back rule
+// of the streamed text (undocumented test hook, needs no device)
+extern "C" int64_t b2_partial_stop(const char *text, size_t n, const char *word, size_t m) {
+    B2_API_BEGIN
+    const size_t at = StreamText::prefix_overlap(std::string(text, n), std::string(word, m));
+    return at == std::string::npos ? (int64_t)-1 : (int64_t)at;
+    B2_API_END(-2)
+}
 // b2_fit_prompt: the truncation rule on a token list in place; returns the new length (tokens dropped iff it changed)
 extern "C" int b2_fit_prompt(int32_t *tokens, int n, int n_ctx, int n_keep) {
     B2_API_BEGIN

@@ -1,0 +1,19 @@
+// stop_harness.cc -- C face of two helpers of the reference's server, compiled FROM THE REFERENCE'S OWN SOURCE.
+//
+// Test infrastructure only.  backend/cpp/llama/grpc-server.cpp as a whole needs llama.cpp, gRPC and protobuf and does not
+// build here, but `ends_with` and `find_partial_stop_string` (the rule that decides which tail of the generated text is
+// held back because it may be the beginning of a stop word, called from process_token at :1056-1089) use nothing but
+// std::string.  oracle/Makefile cuts those two functions out of the file where it lies under /root/reference into
+// oracle/_ref/stop_extract.inc (a build artefact, git-ignored; nothing of the reference is committed) and this file wraps
+// them, so that tests/test_capi_cpu.py can hold the product's own rule (StreamText::prefix_overlap) to the reference's
+// code rather than to a restatement of it.
+#include <cstddef>
+#include <cstdint>
+#include <string>
+
+#include "_ref/stop_extract.inc"
+
+extern "C" int64_t ref_find_partial_stop_string(const char *stop, size_t n_stop, const char *text, size_t n_text) {
+    const size_t at = find_partial_stop_string(std::string(stop, n_stop), std::string(text, n_text));
+    return at == std::string::npos ? (int64_t)-1 : (int64_t)at;
+}

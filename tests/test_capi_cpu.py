@@ -225,6 +225,36 @@ def test_stream_text_holds_back_utf8_and_stop_words():
     assert _stream([b"ab", b"cd"], [b"zz", b"cd", b"bc"]) == (b"", b"a", True, 2)                   # "b" may begin "bc": held; the earliest stop position wins
 
 
+def test_partial_stop_rule_equals_the_references_own_code():
+    """Which tail of the text is held back as the possible beginning of a stop word: the product's rule against
+    find_partial_stop_string of the reference's server, compiled from the reference's own source (oracle/Makefile builds
+    oracle/_ref/libstop_ref.so where /root/reference exists; the .so travels, the source does not)."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libstop_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libstop_ref.so was not built (no /root/reference on this machine)")
+    R = ctypes.CDLL(path)
+    R.ref_find_partial_stop_string.restype = ctypes.c_int64
+    R.ref_find_partial_stop_string.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t]
+    L = capi.lib()
+    L.b2_partial_stop.restype = ctypes.c_int64
+    L.b2_partial_stop.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t]
+    rng = np.random.default_rng(31)
+    cases = [(b"", b""), (b"abc", b""), (b"", b"abc"), (b"Hello ##", b"###"), (b"say STO", b"STOP"), (b"STOP", b"STOP"),
+             (b"aaa", b"aa"), (b"xab", b"abab"), (b"\xc3\xa9", b"\xa9\xc3")]
+    for _ in range(4000):
+        alphabet = b"ab#\n" if rng.integers(0, 2) else b"abcdefgh \xc3\xa9"
+        text = bytes(alphabet[i] for i in rng.integers(0, len(alphabet), int(rng.integers(0, 12))))
+        word = bytes(alphabet[i] for i in rng.integers(0, len(alphabet), int(rng.integers(0, 6))))
+        cases.append((text, word))
+    hits = 0
+    for text, word in cases:
+        want = R.ref_find_partial_stop_string(word, len(word), text, len(text))
+        got = L.b2_partial_stop(text, len(text), word, len(word))
+        assert got == want, (text, word, got, want)
+        hits += want >= 0
+    assert 500 < hits < len(cases) - 500
+
+
 def test_prompt_truncation_rule():
     """A prompt that does not fit keeps n_keep tokens and its tail, dropping whole half-window blocks from the middle
     (grpc-server.cpp:1700-1721); one that fits is untouched."""
