@@ -276,6 +276,12 @@ extern "C" int64_t b2_partial_stop(const char *text, size_t n, const char *word,
     return at == std::string::npos ? (int64_t)-1 : (int64_t)at;
     B2_API_END(-2)
 }
+// b2_reusable_prefix: how many tokens of `prompt` a slot that holds `cached` need not evaluate again (undocumented test hook)
+extern "C" int b2_reusable_prefix(const int32_t *cached, int n_cached, const int32_t *prompt, int n_prompt) {
+    B2_API_BEGIN
+    return reusable_prefix(std::vector<int32_t>(cached, cached + n_cached), std::vector<int32_t>(prompt, prompt + n_prompt));
+    B2_API_END(-1)
+}
 // b2_fit_prompt: the truncation rule on a token list in place; returns the new length (tokens dropped iff it changed)
 extern "C" int b2_fit_prompt(int32_t *tokens, int n, int n_ctx, int n_keep) {
     B2_API_BEGIN

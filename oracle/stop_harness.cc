@@ -1,17 +1,25 @@
 // stop_harness.cc -- C face of two helpers of the reference's server, compiled FROM THE REFERENCE'S OWN SOURCE.
 //
 // Test infrastructure only.  backend/cpp/llama/grpc-server.cpp as a whole needs llama.cpp, gRPC and protobuf and does not
-// build here, but `ends_with` and `find_partial_stop_string` (the rule that decides which tail of the generated text is
-// held back because it may be the beginning of a stop word, called from process_token at :1056-1089) use nothing but
-// std::string.  oracle/Makefile cuts those two functions out of the file where it lies under /root/reference into
-// oracle/_ref/stop_extract.inc (a build artefact, git-ignored; nothing of the reference is committed) and this file wraps
-// them, so that tests/test_capi_cpu.py can hold the product's own rule (StreamText::prefix_overlap) to the reference's
-// code rather than to a restatement of it.
+// build here, but `common_part` (how much of a prompt a slot's cache already holds, :1740), `ends_with` and
+// `find_partial_stop_string` (the rule that decides which tail of the generated text is held back because it may be the
+// beginning of a stop word, called from process_token at :1056-1089) use nothing but std::string / std::vector.
+// oracle/Makefile cuts those functions out of the file where it lies under /root/reference into
+// oracle/_ref/stop_extract.inc (a build artefact, deleted after the compile; nothing of the reference is committed) and
+// this file wraps them, so that tests/test_capi_cpu.py can hold the product's own rules (stream_text.h) to the
+// reference's code rather than to a restatement of it.
 #include <cstddef>
 #include <cstdint>
 #include <string>
+#include <vector>
+
+typedef int32_t llama_token; // llama.h
 
 #include "_ref/stop_extract.inc"
+
+extern "C" int64_t ref_common_part(const int32_t *a, size_t na, const int32_t *b, size_t nb) {
+    return (int64_t)common_part(std::vector<llama_token>(a, a + na), std::vector<llama_token>(b, b + nb));
+}
 
 extern "C" int64_t ref_find_partial_stop_string(const char *stop, size_t n_stop, const char *text, size_t n_text) {
     const size_t at = find_partial_stop_string(std::string(stop, n_stop), std::string(text, n_text));

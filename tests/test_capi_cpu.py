@@ -255,6 +255,32 @@ def test_partial_stop_rule_equals_the_references_own_code():
     assert 500 < hits < len(cases) - 500
 
 
+def test_prefix_reuse_equals_the_references_own_code():
+    """How much of a new prompt a slot's cache already holds: common_part of the reference's server (compiled from its source,
+    oracle/_ref) followed by its caller's rule that the cache's last token is evaluated again (grpc-server.cpp:1740-1749)."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libstop_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libstop_ref.so was not built (no /root/reference on this machine)")
+    R = ctypes.CDLL(path)
+    R.ref_common_part.restype = ctypes.c_int64
+    R.ref_common_part.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t]
+    L = capi.lib()
+    L.b2_reusable_prefix.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int]
+    rng = np.random.default_rng(37)
+    seen = set()
+    for _ in range(2000):
+        base = rng.integers(0, 5, int(rng.integers(0, 24))).astype(np.int32)
+        a = np.ascontiguousarray(base[:int(rng.integers(0, len(base) + 1))])
+        b = base.copy()
+        if len(b) and rng.integers(0, 2):
+            b[int(rng.integers(0, len(b)))] ^= 1
+        common = R.ref_common_part(a.ctypes.data, len(a), b.ctypes.data, len(b))
+        want = common - 1 if (common > 0 and common == len(a)) else common
+        assert L.b2_reusable_prefix(a.ctypes.data, len(a), b.ctypes.data, len(b)) == want, (a, b)
+        seen.add((common == len(a), common == len(b), common == 0))
+    assert len(seen) >= 5
+
+
 def test_prompt_truncation_rule():
     """A prompt that does not fit keeps n_keep tokens and its tail, dropping whole half-window blocks from the middle
     (grpc-server.cpp:1700-1721); one that fits is untouched."""
