@@ -276,6 +276,16 @@ extern "C" int64_t b2_partial_stop(const char *text, size_t n, const char *word,
     return at == std::string::npos ? (int64_t)-1 : (int64_t)at;
     B2_API_END(-2)
 }
+// b2_fit_request_prompt: what LoadModel's slot does to a prompt of n tokens for a request that asks for n_keep (raw, as the
+// request carries it): returns the new length (undocumented test hook)
+extern "C" int b2_fit_request_prompt(int32_t *tokens, int n, int n_ctx, int n_keep) {
+    B2_API_BEGIN
+    std::vector<int32_t> v(tokens, tokens + n);
+    fit_prompt_to_context(v, n_ctx, effective_n_keep(n_keep, n, n_ctx));
+    std::copy(v.begin(), v.end(), tokens);
+    return (int)v.size();
+    B2_API_END(-1)
+}
 // b2_reusable_prefix: how many tokens of `prompt` a slot that holds `cached` need not evaluate again (undocumented test hook)
 extern "C" int b2_reusable_prefix(const int32_t *cached, int n_cached, const int32_t *prompt, int n_prompt) {
     B2_API_BEGIN

@@ -250,9 +250,7 @@ void Scheduler::launch_slot(Slot &s, std::shared_ptr<Request> r) {
     else if (!r->prompt.empty()) toks = eng_->tokenizer()->tokenize(r->prompt, true, true);
     for (int32_t t : toks) B2_CHECK(t >= 0 && t < m.hp.n_vocab, B2_EINVAL, "prompt token id out of range");
     s.n_prompt = (int)toks.size();
-    int n_keep = r->n_keep < 0 ? s.n_prompt : r->n_keep;
-    n_keep = std::min(n_ctx - 4, n_keep);
-    if (n_keep < 0) n_keep = 0;
+    const int n_keep = effective_n_keep(r->n_keep, s.n_prompt, n_ctx);
     if (fit_prompt_to_context(toks, n_ctx, n_keep)) { // (stream_text.h; the reference's rule, grpc-server.cpp:1700-1721)
         s.truncated = true;
         s.n_prompt = (int)toks.size();

@@ -98,6 +98,13 @@ inline bool fit_prompt_to_context(std::vector<int32_t> &tokens, int n_ctx, int n
     return true;
 }
 
+// the request's n_keep as the truncation uses it: negative = the whole prompt, never more than n_ctx - 4 (grpc-server.cpp:1694-1698)
+inline int effective_n_keep(int n_keep, int n_prompt, int n_ctx) {
+    if (n_keep < 0) n_keep = n_prompt;
+    n_keep = std::min(n_ctx - 4, n_keep);
+    return n_keep < 0 ? 0 : n_keep;
+}
+
 // tokens of `prompt` whose K/V the slot still holds from its previous request (never the whole cached sequence: its last
 // token is evaluated again)
 inline int reusable_prefix(const std::vector<int32_t> &cached, const std::vector<int32_t> &prompt) {

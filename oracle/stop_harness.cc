@@ -25,3 +25,23 @@ extern "C" int64_t ref_find_partial_stop_string(const char *stop, size_t n_stop,
     const size_t at = find_partial_stop_string(std::string(stop, n_stop), std::string(text, n_text));
     return at == std::string::npos ? (int64_t)-1 : (int64_t)at;
 }
+
+// The prompt truncation of update_slots (:1692-1721) is a block inside a 400-line function: the Makefile cuts the block
+// out (from "slot.num_prompt_tokens = prompt_tokens.size();" to the closing brace after its GGML_ASSERT) and it is compiled
+// here inside a scope that provides the four names it uses.
+#include <algorithm>
+#include <cstdlib>
+#define LOG_VERBOSE(...)
+#define GGML_ASSERT(x) do { if (!(x)) abort(); } while (0)
+namespace {
+struct ref_params { int n_keep; };
+struct ref_slot { int num_prompt_tokens; int n_ctx; ref_params params; bool truncated; };
+}
+extern "C" int ref_truncate_prompt(int32_t *tokens, int n, int n_ctx, int n_keep, int *truncated) {
+    ref_slot slot{0, n_ctx, {n_keep}, false};
+    std::vector<llama_token> prompt_tokens(tokens, tokens + n);
+#include "_ref/truncate_block.inc"
+    std::copy(prompt_tokens.begin(), prompt_tokens.end(), tokens);
+    if (truncated) *truncated = slot.truncated ? 1 : 0;
+    return slot.num_prompt_tokens;
+}

@@ -281,6 +281,34 @@ def test_prefix_reuse_equals_the_references_own_code():
     assert len(seen) >= 5
 
 
+def test_prompt_truncation_equals_the_references_own_code():
+    """The truncation block of update_slots (grpc-server.cpp:1692-1721), compiled from the reference's source inside a scope
+    that provides the names it uses (oracle/stop_harness.cc), against what the scheduler does to a prompt: n_keep negative,
+    zero, small, beyond the window; prompts shorter than, equal to and far beyond the context."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libstop_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libstop_ref.so was not built (no /root/reference on this machine)")
+    R = ctypes.CDLL(path)
+    R.ref_truncate_prompt.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    L = capi.lib()
+    L.b2_fit_request_prompt.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int]
+    rng = np.random.default_rng(41)
+    n_trunc = 0
+    for trial in range(3000):
+        n_ctx = int(rng.integers(8, 300))
+        n = int(rng.integers(1, 4 * n_ctx))
+        n_keep = int(rng.choice([-1, 0, 1, 4, n_ctx // 2, n_ctx - 5, n_ctx - 4, n_ctx, 2 * n_ctx, int(rng.integers(0, n_ctx + 8))]))
+        a = rng.integers(0, 1000, n).astype(np.int32)
+        b = a.copy()
+        flag = ctypes.c_int(0)
+        want_n = R.ref_truncate_prompt(a.ctypes.data, n, n_ctx, n_keep, ctypes.byref(flag))
+        got_n = L.b2_fit_request_prompt(b.ctypes.data, n, n_ctx, n_keep)
+        assert got_n == want_n and np.array_equal(a[:want_n], b[:got_n]), (n, n_ctx, n_keep, want_n, got_n)
+        assert bool(flag.value) == (want_n != n) and want_n < max(n_ctx, n + 1)
+        n_trunc += flag.value
+    assert 500 < n_trunc < 2900
+
+
 def test_prompt_truncation_rule():
     """A prompt that does not fit keeps n_keep tokens and its tail, dropping whole half-window blocks from the middle
     (grpc-server.cpp:1700-1721); one that fits is untouched."""
