@@ -286,6 +286,12 @@ extern "C" int b2_fit_request_prompt(int32_t *tokens, int n, int n_ctx, int n_ke
     return (int)v.size();
     B2_API_END(-1)
 }
+// b2_utf8_incomplete: does the text end inside a multi-byte character (its bytes are then held back)? (undocumented test hook)
+extern "C" int b2_utf8_incomplete(const char *text, size_t n) {
+    B2_API_BEGIN
+    return StreamText::ends_inside_utf8(std::string(text, n)) ? 1 : 0;
+    B2_API_END(-1)
+}
 // b2_reusable_prefix: how many tokens of `prompt` a slot that holds `cached` need not evaluate again (undocumented test hook)
 extern "C" int b2_reusable_prefix(const int32_t *cached, int n_cached, const int32_t *prompt, int n_prompt) {
     B2_API_BEGIN

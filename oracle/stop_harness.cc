@@ -45,3 +45,13 @@ extern "C" int ref_truncate_prompt(int32_t *tokens, int n, int n_ctx, int n_keep
     if (truncated) *truncated = slot.truncated ? 1 : 0;
     return slot.num_prompt_tokens;
 }
+
+// The check for an incomplete UTF-8 character at the end of the generated text (process_token, :1027-1054), cut out the same way.
+namespace {
+struct ref_text_slot { std::string generated_text; };
+}
+extern "C" int ref_utf8_incomplete(const char *text, size_t n) {
+    ref_text_slot slot{std::string(text, n)};
+#include "_ref/utf8_block.inc"
+    return incomplete ? 1 : 0;
+}

@@ -281,6 +281,32 @@ def test_prefix_reuse_equals_the_references_own_code():
     assert len(seen) >= 5
 
 
+def test_utf8_hold_back_equals_the_references_own_code():
+    """"Does the generated text end inside a multi-byte character" -- the product's test against the block of process_token
+    (grpc-server.cpp:1027-1054) compiled from the reference's source: random byte strings biased towards lead and
+    continuation bytes, valid text cut at every byte, and invalid sequences."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libstop_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libstop_ref.so was not built (no /root/reference on this machine)")
+    R = ctypes.CDLL(path)
+    R.ref_utf8_incomplete.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+    L = capi.lib()
+    L.b2_utf8_incomplete.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+    rng = np.random.default_rng(43)
+    cases = [b"", b"a", b"\xc3", b"\xc3\xa9", b"\xe6\x97", b"\xe6\x97\xa5", b"\xf0\x9f\x98", b"\xf0\x9f\x98\x80", b"\x80\x80\x80\x80\x80", b"\xff\xc3"]
+    text = "naïve café 日本語 🙂🚀 x".encode()
+    cases += [text[:i] for i in range(len(text) + 1)]
+    pool = [0x41, 0x20, 0x80, 0xA9, 0xBF, 0xC3, 0xE6, 0xF0, 0xF8, 0xFF]
+    for _ in range(4000):
+        cases.append(bytes(pool[i] for i in rng.integers(0, len(pool), int(rng.integers(0, 8)))))
+    n_inc = 0
+    for c in cases:
+        want = R.ref_utf8_incomplete(c, len(c))
+        assert L.b2_utf8_incomplete(c, len(c)) == want, c
+        n_inc += want
+    assert 300 < n_inc < len(cases) - 300
+
+
 def test_prompt_truncation_equals_the_references_own_code():
     """The truncation block of update_slots (grpc-server.cpp:1692-1721), compiled from the reference's source inside a scope
     that provides the names it uses (oracle/stop_harness.cc), against what the scheduler does to a prompt: n_keep negative,
