@@ -55,3 +55,49 @@ extern "C" int ref_utf8_incomplete(const char *text, size_t n) {
 #include "_ref/utf8_block.inc"
     return incomplete ? 1 : 0;
 }
+
+// The text half of process_token as a whole (:1027-1096: incomplete UTF-8, full and partial stop words, what is sent), with
+// find_stopping_strings (:976-1008) and the stop_type enum it takes, driven piece by piece.  The scope below provides the
+// names the block uses: the slot's text fields, a result with text_to_send, and two no-op callees.
+#include "_ref/stop_type.inc"
+namespace {
+struct ref_stream_params { std::vector<std::string> antiprompt; bool stream = true; };
+struct completion_token_output { std::string text_to_send; };
+struct llama_client_slot {
+    std::string generated_text;
+    size_t sent_count = 0;
+    bool has_next_token = true, stopped_word = false;
+    std::string stopping_word;
+    ref_stream_params params;
+    void add_token_string(const completion_token_output &) {}
+};
+void send_partial_response(llama_client_slot &, const completion_token_output &) {}
+}
+#include "_ref/find_stopping.inc"
+
+extern "C" int ref_stream_text(const char *pieces, const int *lens, int n, const char *const *stops, int n_stops, char *streamed, int cap_s,
+                               char *final_text, int cap_f, int *n_used) {
+    llama_client_slot slot;
+    for (int i = 0; i < n_stops; i++) slot.params.antiprompt.emplace_back(stops[i]);
+    std::string out;
+    int used = 0;
+    size_t off = 0;
+    for (int i = 0; i < n; i++) {
+        completion_token_output result;
+        const std::string token_str(pieces + off, (size_t)lens[i]);
+        off += (size_t)lens[i];
+        slot.generated_text += token_str; // (:1016-1017)
+        slot.has_next_token = true;
+#include "_ref/process_block.inc"
+        out += result.text_to_send;
+        used++;
+        if (!slot.has_next_token) break;
+    }
+    if ((int)out.size() >= cap_s || (int)slot.generated_text.size() >= cap_f) return -1;
+    std::copy(out.begin(), out.end(), streamed);
+    streamed[out.size()] = 0;
+    std::copy(slot.generated_text.begin(), slot.generated_text.end(), final_text);
+    final_text[slot.generated_text.size()] = 0;
+    if (n_used) *n_used = used;
+    return slot.stopped_word ? 1 : 0;
+}

@@ -281,6 +281,42 @@ def test_prefix_reuse_equals_the_references_own_code():
     assert len(seen) >= 5
 
 
+def test_streamed_text_equals_the_references_own_code():
+    """The whole text half of process_token (grpc-server.cpp:1027-1096 with find_stopping_strings :976-1008), compiled from
+    the reference's source and driven piece by piece, against StreamText on the same pieces and stop words: the bytes a
+    streaming client receives, the final text, whether a stop word ended it and after how many tokens -- 5000 random
+    sequences of pieces that split UTF-8 characters and stop words every possible way."""
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "libstop_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/libstop_ref.so was not built (no /root/reference on this machine)")
+    R = ctypes.CDLL(path)
+    L = capi.lib()
+    sig = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_int,
+           ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p]
+    R.ref_stream_text.argtypes = sig
+    L.b2_stream_text.argtypes = sig
+
+    def run(fn, pieces, stops):
+        lens = (ctypes.c_int * len(pieces))(*[len(p) for p in pieces])
+        arr = (ctypes.c_char_p * max(1, len(stops)))(*stops) if stops else (ctypes.c_char_p * 1)()
+        s1, s2, used = ctypes.create_string_buffer(4096), ctypes.create_string_buffer(4096), ctypes.c_int(0)
+        r = fn(b"".join(pieces), lens, len(pieces), arr, len(stops), s1, 4096, s2, 4096, ctypes.byref(used))
+        assert r >= 0
+        return s1.value, s2.value, r, used.value
+
+    rng = np.random.default_rng(47)
+    alpha = [b"a", b"b", b"#", b" ", b"ST", b"OP", b"\xc3", b"\xa9", b"\xe6", b"\x97", b"\xa5", b"ab", b"b#", b"##"]
+    n_stopped = n_held = 0
+    for _ in range(5000):
+        pieces = [b"".join(alpha[i] for i in rng.integers(0, len(alpha), int(rng.integers(1, 4)))) for _ in range(int(rng.integers(1, 12)))]
+        stops = [b"".join(alpha[i] for i in rng.integers(0, 6, int(rng.integers(1, 4)))) for _ in range(int(rng.integers(0, 4)))]
+        want = run(R.ref_stream_text, pieces, stops)
+        assert run(L.b2_stream_text, pieces, stops) == want, (pieces, stops, want)
+        n_stopped += want[2]
+        n_held += want[0] != want[1]
+    assert n_stopped > 1000 and n_held > 1000
+
+
 def test_utf8_hold_back_equals_the_references_own_code():
     """"Does the generated text end inside a multi-byte character" -- the product's test against the block of process_token
     (grpc-server.cpp:1027-1054) compiled from the reference's source: random byte strings biased towards lead and
