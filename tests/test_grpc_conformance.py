@@ -131,3 +131,66 @@ def test_predict_stream_embedding_grammar_metrics(backend, model_files):
     m = backend.GetMetrics(pb.MetricsRequest())
     assert m.tokens_generated > 0 and m.prompt_tokens_processed > 0
     assert backend.Status(pb.HealthMessage()).memory.total > 0
+
+
+def test_option_mapping_equals_the_references_own_parse_options():
+    """PredictOptions -> request fields: pyshim's request_kwargs (the Python twin of the Go shim's mapping) against the
+    json that parse_options of the reference's server makes of the same message -- the function compiled from the
+    reference's source with a stand-in for the generated protobuf class (oracle/options_harness.cc, oracle/_ref).
+    Deliberate differences, all on values LocalAI's core never sends because it fills in its defaults first
+    (core/config/backend_config.go:286-320): a zero repeat penalty / typical-p / tail-free z means "off" here, where the
+    reference would divide by zero or truncate to nothing."""
+    import ctypes
+    import json
+
+    from pyshim.server import request_kwargs
+
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "liboptions_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/liboptions_ref.so was not built (no /root/reference on this machine)")
+
+    class RefOpts(ctypes.Structure):
+        _fields_ = ([(n, ctypes.c_int32) for n in ("tokens", "topk", "repeat", "mirostat", "nkeep", "seed")] +
+                    [(n, ctypes.c_float) for n in ("topp", "tailfreesamplingz", "typicalp", "temperature", "penalty", "frequencypenalty",
+                                                   "presencepenalty", "mirostattau", "mirostateta")] +
+                    [(n, ctypes.c_int32) for n in ("promptcacheall", "penalizenl", "ignoreeos", "embeddings")] +
+                    [(n, ctypes.c_char_p) for n in ("grammar", "prompt", "correlationid")] +
+                    [("stopprompts", ctypes.POINTER(ctypes.c_char_p)), ("n_stopprompts", ctypes.c_int32)])
+
+    R = ctypes.CDLL(path)
+    R.ref_parse_options.argtypes = [ctypes.c_int, ctypes.POINTER(RefOpts), ctypes.c_char_p, ctypes.c_int]
+    rng = np.random.default_rng(53)
+    f32 = lambda x: float(np.float32(x))  # noqa: E731
+    for trial in range(300):
+        zeros = trial % 5 == 0  # every fifth message leaves the float knobs at the proto default
+        o = pb.PredictOptions(
+            Prompt="p%d" % trial, Tokens=int(rng.integers(0, 3)) * 64, TopK=int(rng.integers(0, 100)), Seed=int(rng.integers(-1, 1000)),
+            TopP=0 if zeros else f32(rng.uniform(0.1, 1)), Temperature=f32(rng.uniform(0, 2)), Repeat=int(rng.integers(-1, 128)),
+            Penalty=0 if zeros else f32(rng.uniform(1, 1.5)), FrequencyPenalty=f32(rng.uniform(0, 1)), PresencePenalty=f32(rng.uniform(0, 1)),
+            Mirostat=int(rng.integers(0, 3)), MirostatTAU=f32(rng.uniform(1, 8)), MirostatETA=f32(rng.uniform(0.05, 0.5)),
+            TypicalP=0 if zeros else f32(rng.uniform(0.2, 1)), TailFreeSamplingZ=0 if zeros else f32(rng.uniform(0.2, 1)),
+            PenalizeNL=bool(rng.integers(0, 2)), NKeep=int(rng.integers(-1, 64)), IgnoreEOS=bool(rng.integers(0, 2)),
+            PromptCacheAll=bool(rng.integers(0, 2)), Grammar="" if trial % 3 else 'root ::= "a"', StopPrompts=["</s>", "###"][:trial % 3])
+        stops = [s.encode() for s in o.StopPrompts]
+        arr = (ctypes.c_char_p * max(1, len(stops)))(*stops)
+        r = RefOpts(o.Tokens, o.TopK, o.Repeat, o.Mirostat, o.NKeep, o.Seed, o.TopP, o.TailFreeSamplingZ, o.TypicalP, o.Temperature, o.Penalty,
+                    o.FrequencyPenalty, o.PresencePenalty, o.MirostatTAU, o.MirostatETA, int(o.PromptCacheAll), int(o.PenalizeNL),
+                    int(o.IgnoreEOS), 0, o.Grammar.encode(), o.Prompt.encode(), b"", arr, len(stops))
+        buf = ctypes.create_string_buffer(1 << 16)
+        assert R.ref_parse_options(1, ctypes.byref(r), buf, len(buf)) > 0
+        want = json.loads(buf.value)
+        got = request_kwargs(o)
+        assert want["stream"] is True and want["prompt"] == o.Prompt
+        assert want["n_predict"] == (got["n_predict"] if got["n_predict"] != 0 else -1)  # 0 = until EOS / context in both, spelled -1 there
+        for jk, kk in (("top_k", "top_k"), ("seed", "seed"), ("repeat_last_n", "repeat_last_n"), ("mirostat", "mirostat"), ("n_keep", "n_keep"),
+                       ("ignore_eos", "ignore_eos"), ("cache_prompt", "cache_prompt"), ("penalize_nl", "penalize_nl"), ("stop", "stop")):
+            assert want[jk] == got[kk], (jk, want[jk], got[kk])
+        for jk, kk in (("top_p", "top_p"), ("temperature", "temperature"), ("frequency_penalty", "frequency_penalty"),
+                       ("presence_penalty", "presence_penalty"), ("mirostat_tau", "mirostat_tau"), ("mirostat_eta", "mirostat_eta")):
+            assert f32(want[jk]) == f32(got[kk]), (jk, want[jk], got[kk])
+        assert want["grammar"] == (got["grammar"] or "")
+        for jk, kk in (("repeat_penalty", "repeat_penalty"), ("typical_p", "typical_p"), ("tfs_z", "tfs_z")):
+            if f32(want[jk]) != 0.0:
+                assert f32(want[jk]) == f32(got[kk]), (jk, want[jk], got[kk])
+            else:
+                assert got[kk] == 1.0, (jk, got[kk])  # the deliberate difference: zero means "off"
