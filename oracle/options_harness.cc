@@ -73,3 +73,82 @@ extern "C" int ref_parse_options(int streaming, const ref_predict_options *o, ch
     memcpy(out, s.c_str(), s.size() + 1);
     return (int)s.size();
 }
+
+// params_parse (:2205-2300): ModelOptions -> gpt_params, compiled the same way.  gpt_params below has the members the
+// function assigns, initialised to llama.cpp's defaults where the function only overrides on non-zero input (common.h @
+// d5cb868: rope_freq_base / rope_freq_scale 0 = from the model, yarn_ext_factor -1, yarn_attn_factor 1, beta_fast 32,
+// beta_slow 1, n_parallel 1); the enum values are llama.h's.
+#include <cstdlib>
+#include <regex>
+#define GGML_ASSERT(x) do { if (!(x)) abort(); } while (0)
+enum llama_rope_scaling_type { LLAMA_ROPE_SCALING_TYPE_UNSPECIFIED = -1, LLAMA_ROPE_SCALING_TYPE_NONE = 0, LLAMA_ROPE_SCALING_TYPE_LINEAR = 1, LLAMA_ROPE_SCALING_TYPE_YARN = 2 };
+static size_t llama_max_devices() { return 16; }
+struct ref_lora { std::string path; float scale; };
+struct ref_cpuparams { int n_threads = -1; };
+struct gpt_params {
+    std::string model, mmproj, model_alias, rpc_servers;
+    int n_ctx = 0, n_gpu_layers = -1, n_batch = 2048, n_parallel = 1, main_gpu = 0;
+    bool cont_batching = true, use_mlock = false, use_mmap = true, flash_attn = false, no_kv_offload = false, embedding = false;
+    ref_cpuparams cpuparams;
+    float tensor_split[128] = {0};
+    std::vector<ref_lora> lora_adapters;
+    llama_rope_scaling_type rope_scaling_type = LLAMA_ROPE_SCALING_TYPE_UNSPECIFIED;
+    float yarn_ext_factor = -1.0f, yarn_attn_factor = 1.0f, yarn_beta_fast = 32.0f, yarn_beta_slow = 1.0f;
+    float rope_freq_base = 0.0f, rope_freq_scale = 0.0f;
+};
+
+extern "C" struct ref_model_options {
+    const char *modelfile, *mmproj, *tensorsplit, *maingpu, *loraadapter, *lorabase, *ropescaling;
+    int32_t contextsize, threads, ngpulayers, nbatch, mlock, mmap, flashattention, nokvoffload, embeddings;
+    float lorascale, yarnextfactor, yarnattnfactor, yarnbetafast, yarnbetaslow, ropefreqbase, ropefreqscale;
+};
+namespace backend {
+class ModelOptions {
+  public:
+    explicit ModelOptions(const ref_model_options &o) : o_(o) {}
+    std::string modelfile() const { return s(o_.modelfile); }
+    std::string mmproj() const { return s(o_.mmproj); }
+    std::string tensorsplit() const { return s(o_.tensorsplit); }
+    std::string maingpu() const { return s(o_.maingpu); }
+    std::string loraadapter() const { return s(o_.loraadapter); }
+    std::string lorabase() const { return s(o_.lorabase); }
+    std::string ropescaling() const { return s(o_.ropescaling); }
+    int32_t contextsize() const { return o_.contextsize; }
+    int32_t threads() const { return o_.threads; }
+    int32_t ngpulayers() const { return o_.ngpulayers; }
+    int32_t nbatch() const { return o_.nbatch; }
+    bool mlock() const { return o_.mlock != 0; }
+    bool mmap() const { return o_.mmap != 0; }
+    bool flashattention() const { return o_.flashattention != 0; }
+    bool nokvoffload() const { return o_.nokvoffload != 0; }
+    bool embeddings() const { return o_.embeddings != 0; }
+    float lorascale() const { return o_.lorascale; }
+    float yarnextfactor() const { return o_.yarnextfactor; }
+    float yarnattnfactor() const { return o_.yarnattnfactor; }
+    float yarnbetafast() const { return o_.yarnbetafast; }
+    float yarnbetaslow() const { return o_.yarnbetaslow; }
+    float ropefreqbase() const { return o_.ropefreqbase; }
+    float ropefreqscale() const { return o_.ropefreqscale; }
+
+  private:
+    static std::string s(const char *p) { return p ? p : ""; }
+    ref_model_options o_;
+};
+} // namespace backend
+
+#include "_ref/params_parse.inc"
+
+extern "C" int ref_params_parse(const ref_model_options *o, char *out, int cap) {
+    gpt_params p;
+    const backend::ModelOptions m(*o);
+    params_parse(&m, p);
+    json j = {{"model", p.model}, {"n_ctx", p.n_ctx}, {"n_batch", p.n_batch}, {"n_parallel", p.n_parallel}, {"main_gpu", p.main_gpu},
+              {"embedding", p.embedding}, {"rope_scaling_type", (int)p.rope_scaling_type}, {"yarn_ext_factor", p.yarn_ext_factor},
+              {"yarn_attn_factor", p.yarn_attn_factor}, {"yarn_beta_fast", p.yarn_beta_fast}, {"yarn_beta_slow", p.yarn_beta_slow},
+              {"rope_freq_base", p.rope_freq_base}, {"rope_freq_scale", p.rope_freq_scale}, {"flash_attn", p.flash_attn},
+              {"use_mmap", p.use_mmap}, {"use_mlock", p.use_mlock}, {"n_threads", p.cpuparams.n_threads}, {"n_gpu_layers", p.n_gpu_layers}};
+    const std::string s = j.dump();
+    if ((int)s.size() >= cap) return -1;
+    memcpy(out, s.c_str(), s.size() + 1);
+    return (int)s.size();
+}

@@ -48,6 +48,20 @@ def request_kwargs(o) -> dict:
         tfs_z=o.TailFreeSamplingZ or 1.0, grammar=o.Grammar or None, penalize_nl=o.PenalizeNL)
 
 
+def load_kwargs(o, environ=os.environ) -> dict:
+    """ModelOptions -> b2_load_opts fields, the mapping of params_parse (grpc-server.cpp:2205-2300) and of
+    backend/go/llm/b200/llm.go.  0 / "" keep the engine's (= the reference's) defaults."""
+    n_par = int(environ.get("LLAMACPP_PARALLEL", "1") or 1)  # :2225-2231
+    return dict(
+        n_ctx=o.ContextSize or 1024, n_batch=o.NBatch or 512, n_parallel=max(1, n_par),
+        device=int(o.MainGPU) if o.MainGPU.strip().isdigit() else 0, embeddings=o.Embeddings,
+        rope_freq_base=o.RopeFreqBase, rope_freq_scale=o.RopeFreqScale,
+        # :2279-2281: "none" / "yarn" / anything else (the empty default too) = linear
+        rope_scaling=o.RopeScaling if o.RopeScaling in ("none", "yarn") else "linear",
+        yarn_ext_factor=o.YarnExtFactor, yarn_attn_factor=o.YarnAttnFactor, yarn_beta_fast=o.YarnBetaFast,
+        yarn_beta_slow=o.YarnBetaSlow)
+
+
 class Backend:
     def __init__(self):
         self.engine: capi.Engine | None = None
@@ -70,15 +84,7 @@ class Backend:
 
     def LoadModel(self, req, ctx):
         try:
-            n_par = int(os.environ.get("LLAMACPP_PARALLEL", "1") or 1)  # grpc-server.cpp:2225-2231
-            dev = int(req.MainGPU) if req.MainGPU.strip().isdigit() else 0
-            eng = capi.Engine(req.ModelFile or req.Model, n_ctx=req.ContextSize or 1024, n_batch=req.NBatch or 512,
-                              n_parallel=max(1, n_par), device=dev, embeddings=req.Embeddings, vocab_only=req.VocabOnly,
-                              rope_freq_base=req.RopeFreqBase, rope_freq_scale=req.RopeFreqScale,
-                              # grpc-server.cpp:2279-2293: "none" / "yarn" / anything else (the empty default too) = linear
-                              rope_scaling=req.RopeScaling if req.RopeScaling in ("none", "yarn") else "linear",
-                              yarn_ext_factor=req.YarnExtFactor, yarn_attn_factor=req.YarnAttnFactor,
-                              yarn_beta_fast=req.YarnBetaFast, yarn_beta_slow=req.YarnBetaSlow)
+            eng = capi.Engine(req.ModelFile or req.Model, vocab_only=req.VocabOnly, **load_kwargs(req))
         except Exception as ex:  # pkg/grpc/server.go:50-53: Result{success:false} AND a gRPC error
             ctx.set_code(grpc.StatusCode.UNKNOWN)
             ctx.set_details(f"Error loading model: {ex}")

@@ -194,3 +194,66 @@ def test_option_mapping_equals_the_references_own_parse_options():
                 assert f32(want[jk]) == f32(got[kk]), (jk, want[jk], got[kk])
             else:
                 assert got[kk] == 1.0, (jk, got[kk])  # the deliberate difference: zero means "off"
+
+
+def test_load_option_mapping_equals_the_references_own_params_parse(monkeypatch):
+    """ModelOptions -> load options: pyshim's load_kwargs (the twin of the Go shim's Load) against the gpt_params that
+    params_parse of the reference's server fills from the same message (compiled from the reference's source,
+    oracle/options_harness.cc).  A zero ContextSize / NBatch -- which LocalAI's core never sends -- means this engine's
+    default here and llama.cpp's there; the YaRN fields are "0 = default" here and "left at llama.cpp's default" there."""
+    import ctypes
+    import json
+
+    from pyshim.server import load_kwargs
+
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "liboptions_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref/liboptions_ref.so was not built (no /root/reference on this machine)")
+
+    class RefModel(ctypes.Structure):
+        _fields_ = ([(n, ctypes.c_char_p) for n in ("modelfile", "mmproj", "tensorsplit", "maingpu", "loraadapter", "lorabase", "ropescaling")] +
+                    [(n, ctypes.c_int32) for n in ("contextsize", "threads", "ngpulayers", "nbatch", "mlock", "mmap", "flashattention", "nokvoffload",
+                                                   "embeddings")] +
+                    [(n, ctypes.c_float) for n in ("lorascale", "yarnextfactor", "yarnattnfactor", "yarnbetafast", "yarnbetaslow", "ropefreqbase",
+                                                   "ropefreqscale")])
+
+    R = ctypes.CDLL(path)
+    R.ref_params_parse.argtypes = [ctypes.POINTER(RefModel), ctypes.c_char_p, ctypes.c_int]
+    rng = np.random.default_rng(59)
+    f32 = lambda x: float(np.float32(x))  # noqa: E731
+    defaults = {"yarn_ext_factor": -1.0, "yarn_attn_factor": 1.0, "yarn_beta_fast": 32.0, "yarn_beta_slow": 1.0}
+    for trial in range(200):
+        if trial % 2:
+            monkeypatch.setenv("LLAMACPP_PARALLEL", str(1 + trial % 7))
+        else:
+            monkeypatch.delenv("LLAMACPP_PARALLEL", raising=False)
+        z = trial % 4 == 0
+        o = pb.ModelOptions(
+            ModelFile="/models/m%d.gguf" % trial, ContextSize=0 if trial % 9 == 0 else int(rng.integers(1, 64)) * 128,
+            NBatch=0 if trial % 11 == 0 else int(rng.integers(1, 16)) * 128, MainGPU=["", "0", "3", "7"][trial % 4],
+            Embeddings=bool(trial % 3 == 0), RopeScaling=["", "none", "yarn", "linear", "something"][trial % 5],
+            YarnExtFactor=0 if z else f32(rng.uniform(0.1, 1)), YarnAttnFactor=0 if z else f32(rng.uniform(0.5, 2)),
+            YarnBetaFast=0 if z else f32(rng.uniform(8, 64)), YarnBetaSlow=0 if z else f32(rng.uniform(0.5, 4)),
+            RopeFreqBase=0 if z else f32(rng.uniform(1e4, 1e6)), RopeFreqScale=0 if z else f32(rng.uniform(0.1, 1)),
+            Threads=int(rng.integers(1, 64)), NGPULayers=99, MMap=True, FlashAttention=bool(trial % 2))
+        r = RefModel(o.ModelFile.encode(), b"", b"", o.MainGPU.encode(), b"", b"", o.RopeScaling.encode(), o.ContextSize, o.Threads, o.NGPULayers,
+                     o.NBatch, int(o.MLock), int(o.MMap), int(o.FlashAttention), int(o.NoKVOffload), int(o.Embeddings), 0.0, o.YarnExtFactor,
+                     o.YarnAttnFactor, o.YarnBetaFast, o.YarnBetaSlow, o.RopeFreqBase, o.RopeFreqScale)
+        buf = ctypes.create_string_buffer(1 << 14)
+        assert R.ref_params_parse(ctypes.byref(r), buf, len(buf)) > 0
+        want = json.loads(buf.value)
+        got = load_kwargs(o)
+        assert want["model"] == o.ModelFile
+        if o.ContextSize:
+            assert want["n_ctx"] == got["n_ctx"]
+        if o.NBatch:
+            assert want["n_batch"] == got["n_batch"]
+        assert want["n_parallel"] == got["n_parallel"] and want["main_gpu"] == got["device"] and want["embedding"] == got["embeddings"]
+        assert {0: "none", 1: "linear", 2: "yarn"}[want["rope_scaling_type"]] == got["rope_scaling"]
+        for k in ("rope_freq_base", "rope_freq_scale"):
+            assert f32(want[k]) == f32(got[k]), k
+        for k, dflt in defaults.items():
+            if got[k] == 0:
+                assert f32(want[k]) == f32(dflt), k  # untouched there = "0: default" here
+            else:
+                assert f32(want[k]) == f32(got[k]), k
